@@ -1,0 +1,174 @@
+"""ctypes binding of libbotorch_b200.so (the C ABI in include/botorch_b200.h).
+
+There is no fallback: if the library is missing or the device is not a B200-class
+GPU every call raises.  PyTorch is used only for device memory and streams.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+from typing import Optional
+
+import torch
+
+from .build import LIB_PATH
+
+c_double_p = C.POINTER(C.c_double)
+
+
+class BoGP(C.Structure):
+    _fields_ = [
+        ("kernel_id", C.c_int32),
+        ("n", C.c_int32),
+        ("d", C.c_int32),
+        ("M", C.c_int32),
+        ("y_mean", C.c_double),
+        ("y_std", C.c_double),
+        ("train_X", C.c_void_p),
+        ("center", C.c_void_p),
+        ("inv_ls", C.c_void_p),
+        ("outputscale", C.c_void_p),
+        ("noise", C.c_void_p),
+        ("mean", C.c_void_p),
+        ("targets", C.c_void_p),
+        ("jitter", C.c_void_p),
+        ("aug_train", C.c_void_p),
+        ("linv_aug", C.c_void_p),
+        ("linv_aug_t", C.c_void_p),
+        ("chol", C.c_void_p),
+    ]
+
+
+class BoNEI(C.Structure):
+    _fields_ = [
+        ("n_b", C.c_int32),
+        ("S", C.c_int32),
+        ("baseline_is_train", C.c_int32),
+        ("X_b", C.c_void_p),
+        ("Z_b", C.c_void_p),
+        ("jitter", C.c_void_p),
+        ("aug_b", C.c_void_p),
+        ("vb", C.c_void_p),
+        ("vb_t", C.c_void_p),
+        ("lb", C.c_void_p),
+        ("lb_inv", C.c_void_p),
+        ("lb_inv_t", C.c_void_p),
+        ("zb_pad", C.c_void_p),
+        ("zb_t", C.c_void_p),
+        ("mean_b", C.c_void_p),
+        ("best_f", C.c_void_p),
+    ]
+
+
+class BoError(RuntimeError):
+    pass
+
+
+_lib: Optional[C.CDLL] = None
+_ctx = {}
+
+
+def _declare(lib: C.CDLL) -> None:
+    vp, i32, i64, dbl, sz = C.c_void_p, C.c_int, C.c_long, C.c_double, C.c_size_t
+    gp, nei = C.POINTER(BoGP), C.POINTER(BoNEI)
+    lib.bo_strerror.restype = C.c_char_p
+    lib.bo_strerror.argtypes = [i32]
+    lib.bo_last_cuda_error.restype = C.c_char_p
+    lib.bo_ctx_create.argtypes = [i32, C.POINTER(vp)]
+    lib.bo_ctx_destroy.argtypes = [vp]
+    lib.bo_ctx_destroy.restype = None
+    lib.bo_launch_count.restype = i64
+    lib.bo_launch_count_reset.restype = None
+    lib.bo_pad8.restype = i64
+    lib.bo_pad8.argtypes = [i64]
+    lib.bo_kp.restype = i64
+    lib.bo_kp.argtypes = [i32]
+    lib.bo_gp_setup_workspace_bytes.restype = sz
+    lib.bo_gp_setup_workspace_bytes.argtypes = [gp]
+    lib.bo_gp_setup.argtypes = [vp, gp, vp, sz, vp, vp]
+    lib.bo_nei_setup_workspace_bytes.restype = sz
+    lib.bo_nei_setup_workspace_bytes.argtypes = [gp, nei]
+    lib.bo_nei_setup.argtypes = [vp, gp, nei, vp, sz, vp, vp]
+    lib.bo_qlognei_workspace_bytes.restype = sz
+    lib.bo_qlognei_workspace_bytes.argtypes = [gp, nei, i32, i32, i32]
+    lib.bo_qlognei_fwd.argtypes = [vp, gp, nei, i32, i32, vp, vp, dbl, dbl, vp, vp, vp, sz, i32, vp]
+    lib.bo_qlognei_bwd.argtypes = [vp, gp, nei, i32, i32, vp, vp, dbl, dbl, vp, vp, vp, sz, vp]
+    lib.bo_posterior_workspace_bytes.restype = sz
+    lib.bo_posterior_workspace_bytes.argtypes = [gp, i64]
+    lib.bo_posterior_joint.argtypes = [vp, gp, i32, i32, vp, vp, vp, vp, sz, vp]
+    lib.bo_posterior_mean_var.argtypes = [vp, gp, i64, vp, vp, vp, vp, sz, vp]
+    lib.bo_ts_argmax.argtypes = [vp, i32, i64, vp, vp, vp, vp, vp, vp]
+    lib.bo_argmax.argtypes = [vp, i64, vp, vp, vp, vp]
+    lib.bo_dgemm.argtypes = [vp, i32, i32, i32, i32, dbl, vp, i64, i64, vp, i64, i64, dbl, vp, i64, i64, i32, vp]
+    lib.bo_kernel_matrix.argtypes = [vp, gp, i64, vp, vp, vp, sz, vp]
+    lib.bo_potrf_workspace_bytes.restype = sz
+    lib.bo_potrf_workspace_bytes.argtypes = [i32, i32]
+    lib.bo_potrf.argtypes = [vp, i32, i32, vp, i64, i64, vp, vp, sz, vp, vp]
+    for name in (
+        "bo_ctx_create bo_gp_setup bo_nei_setup bo_qlognei_fwd bo_qlognei_bwd bo_posterior_joint "
+        "bo_posterior_mean_var bo_ts_argmax bo_argmax bo_dgemm bo_kernel_matrix bo_potrf"
+    ).split():
+        getattr(lib, name).restype = i32
+
+
+def lib() -> C.CDLL:
+    """The loaded shared library; raises if it has not been built (run __graft_entry__.build())."""
+    global _lib
+    if _lib is None:
+        if not os.path.exists(LIB_PATH):
+            raise BoError(
+                f"{LIB_PATH} not found: the CUDA extension is not built. There is no CPU fallback; "
+                "run `python -m botorch_b200.build` (needs nvcc)."
+            )
+        _lib = C.CDLL(LIB_PATH)
+        _declare(_lib)
+    return _lib
+
+
+def check(code: int) -> None:
+    if code != 0:
+        l = lib()
+        msg = l.bo_strerror(code).decode()
+        if code == 2:
+            msg += ": " + l.bo_last_cuda_error().decode()
+        raise BoError(f"libbotorch_b200: {msg}")
+
+
+def ctx(device: torch.device) -> C.c_void_p:
+    """One bo_ctx per device (not thread-safe; the path is driven single-threaded from SciPy's callback)."""
+    if device.type != "cuda":
+        raise BoError(f"botorch_b200 runs on CUDA devices only (sm_100a); got device {device}. No CPU fallback.")
+    idx = device.index if device.index is not None else torch.cuda.current_device()
+    if idx not in _ctx:
+        h = C.c_void_p()
+        check(lib().bo_ctx_create(idx, C.byref(h)))
+        _ctx[idx] = h
+    return _ctx[idx]
+
+
+def stream_ptr(device: torch.device) -> C.c_void_p:
+    return C.c_void_p(torch.cuda.current_stream(device).cuda_stream)
+
+
+def ptr(t: Optional[torch.Tensor]) -> Optional[int]:
+    if t is None:
+        return None
+    assert t.is_cuda and t.is_contiguous() and t.dtype in (torch.float64, torch.int32, torch.int64), (
+        t.device,
+        t.dtype,
+        t.is_contiguous(),
+    )
+    return t.data_ptr()
+
+
+def pad8(x: int) -> int:
+    return (x + 7) // 8 * 8
+
+
+def kp(d: int) -> int:
+    return (d + 2 + 3) // 4 * 4
+
+
+def workspace(nbytes: int, device: torch.device) -> torch.Tensor:
+    """Caller-owned scratch (torch caching allocator => no cudaMalloc on the hot path)."""
+    return torch.empty(max(int(nbytes), 256), dtype=torch.uint8, device=device)

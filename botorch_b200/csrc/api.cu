@@ -1,0 +1,552 @@
+// C ABI of libbotorch_b200 (declared in include/botorch_b200.h): orchestration of the DMMA GEMM
+// pipeline and the per-candidate kernels.  No allocation, no synchronisation: every buffer is the
+// caller's, every launch goes to the caller's stream.
+#include "../../include/botorch_b200.h"
+
+#include <cstring>
+
+#include "cand.cuh"
+#include "common.cuh"
+#include "linalg.cuh"
+
+struct bo_ctx {
+    int device;
+    int sms;
+};
+
+static char g_last_cuda_err[512] = "";
+
+void bo_set_last_cuda_error(cudaError_t e, const char* file, int line) {
+    snprintf(g_last_cuda_err, sizeof(g_last_cuda_err), "%s (%s) at %s:%d", cudaGetErrorName(e),
+             cudaGetErrorString(e), file, line);
+}
+
+namespace {
+
+struct Bump {  // carve the caller's workspace; 256-byte aligned regions
+    char* base;
+    size_t cap, off;
+    bool ok;
+    Bump(void* p, size_t c) : base((char*)p), cap(c), off(0), ok(true) {}
+    double* doubles(long count) {
+        size_t bytes = (size_t)bo_round_up((long)(count * sizeof(double)), 256);
+        if (base != nullptr && off + bytes > cap) ok = false;
+        double* r = base ? (double*)(base + off) : nullptr;
+        off += bytes;
+        return r;
+    }
+};
+
+__global__ void vec_add_kernel(const double* a, const double* b, double* out, int n) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) out[i] = a[i] + (b ? b[i] : 0.0);
+}
+// r[z][i][0] = targets[i] - mean[z];  r[z][i][1] = 0
+__global__ void resid_kernel(const double* targets, const double* mean, double* r, int n) {
+    const int z = blockIdx.y, i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) {
+        r[((long)z * n + i) * 2] = targets[i] - mean[z];
+        r[((long)z * n + i) * 2 + 1] = 0.0;
+    }
+}
+// alpha (stored as [n x 2] column) -> row n of linv_aug and column n of linv_aug_t
+__global__ void scatter_alpha_kernel(const double* av, double* linv_aug, long np, double* linv_aug_t, long n1p, int n) {
+    const int z = blockIdx.y, i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) {
+        const double v = av[((long)z * n + i) * 2];
+        linv_aug[(long)z * (n + 1) * np + (long)n * np + i] = v;
+        linv_aug_t[(long)z * n * n1p + (long)i * n1p + n] = v;
+    }
+}
+// mean_b[z][i] = y_mean + y_std * (m_z + vb[z][n][i])
+__global__ void mean_b_kernel(const double* vb, long strideVb, long nbp, int n, int n_b, double y_mean, double y_std,
+                              const double* mean, double* out) {
+    const int z = blockIdx.y, i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n_b) out[(long)z * nbp + i] = y_mean + y_std * (mean[z] + vb[(long)z * strideVb + (long)n * nbp + i]);
+}
+
+BoKernelHyper hyper_of(const bo_gp* gp) {
+    BoKernelHyper h;
+    h.kernel_id = gp->kernel_id;
+    h.d = gp->d;
+    h.M = gp->M;
+    h.inv_ls = gp->inv_ls;
+    h.outputscale = gp->outputscale;
+    h.center = gp->center;
+    return h;
+}
+
+// covariance matrix from augmented operands: C[z] = k(A_aug[z] . B_aug[z])
+int kmat(const bo_gp* gp, const double* A_aug, int rows, const double* B_aug, long ldb, long cols, double* C, long ldc,
+         long strideC, int diag_exact, const double* diag_add, cudaStream_t st) {
+    const long Kp = bo_kp(gp->d);
+    BoGemm g{};
+    g.A = A_aug; g.lda = Kp; g.strideA = (long)rows * Kp;
+    g.B = B_aug; g.ldb = ldb; g.strideB = Kp * ldb;
+    g.C = C; g.ldc = ldc; g.strideC = strideC;
+    g.M = rows; g.N = (int)cols; g.K = (int)Kp; g.batch = gp->M;
+    g.epi = gp->kernel_id == BO_KERNEL_RBF ? BO_EPI_RBF : BO_EPI_MATERN52;
+    g.os = gp->outputscale; g.diag_add = diag_add; g.diag_exact = diag_exact;
+    return bo_gemm_launch(g, st);
+}
+
+int gemm(int M, int N, int K, int batch, double alpha, const double* A, long lda, long sA, const double* B, long ldb,
+         long sB, double beta, const double* D, long ldd, long sD, double* C, long ldc, long sC, int tri, int out_lower,
+         cudaStream_t st) {
+    BoGemm g{};
+    g.A = A; g.lda = lda; g.strideA = sA;
+    g.B = B; g.ldb = ldb; g.strideB = sB;
+    g.C = C; g.ldc = ldc; g.strideC = sC;
+    g.D = D; g.ldd = ldd; g.strideD = sD;
+    g.alpha = alpha; g.beta = beta; g.M = M; g.N = N; g.K = K; g.batch = batch;
+    g.tri = tri; g.out_lower = out_lower; g.epi = BO_EPI_LINEAR;
+    return bo_gemm_launch(g, st);
+}
+
+bool valid_gp(const bo_gp* gp) {
+    return gp && gp->n > 0 && gp->d > 0 && gp->d <= BO_MAX_D && gp->M > 0 &&
+           (gp->kernel_id == BO_KERNEL_RBF || gp->kernel_id == BO_KERNEL_MATERN52);
+}
+
+}  // namespace
+
+extern "C" {
+
+const char* bo_strerror(int code) {
+    switch (code) {
+        case BO_OK: return "ok";
+        case BO_ERR_INVALID: return "invalid argument (shape, alignment or null pointer)";
+        case BO_ERR_CUDA: return "CUDA runtime error (see bo_last_cuda_error)";
+        case BO_ERR_WORKSPACE: return "workspace too small";
+        case BO_ERR_UNSUPPORTED: return "unsupported size (q > 32, d > 128 or grid limit)";
+        default: return "unknown error";
+    }
+}
+const char* bo_last_cuda_error(void) { return g_last_cuda_err; }
+
+int bo_ctx_create(int device, bo_ctx** out) {
+    if (!out) return BO_ERR_INVALID;
+    int count = 0;
+    BO_CUDA_TRY(cudaGetDeviceCount(&count));
+    if (device < 0 || device >= count) return BO_ERR_INVALID;
+    cudaDeviceProp p;
+    BO_CUDA_TRY(cudaGetDeviceProperties(&p, device));
+    if (p.major != 10) return BO_ERR_UNSUPPORTED;  // built for sm_100a only
+    bo_ctx* c = new bo_ctx;
+    c->device = device;
+    c->sms = p.multiProcessorCount;
+    *out = c;
+    return BO_OK;
+}
+void bo_ctx_destroy(bo_ctx* ctx) { delete ctx; }
+long bo_launch_count(void) { return g_bo_launch_count; }
+void bo_launch_count_reset(void) { g_bo_launch_count = 0; }
+long bo_pad8(long x) { return bo_round_up(x, 8); }
+long bo_kp(int d) { return bo_round_up(d + 2, 4); }
+
+// ------------------------------------------------------------------------------------------------
+// setup
+// ------------------------------------------------------------------------------------------------
+static size_t gp_setup_layout(const bo_gp* gp, void* work, size_t cap, double** baug, double** scratch, double** rv,
+                              double** t1, double** av, double** nz, bool* ok) {
+    const long n = gp->n, M = gp->M, np = bo_pad8(n), Kp = bo_kp(gp->d);
+    Bump b(work, cap);
+    *baug = b.doubles(M * Kp * np);
+    *scratch = b.doubles(bo_linalg_scratch_doubles((int)n, (int)M));
+    *rv = b.doubles(M * n * 2);
+    *t1 = b.doubles(M * n * 2);
+    *av = b.doubles(M * n * 2);
+    *nz = b.doubles(M);
+    *ok = b.ok;
+    return b.off;
+}
+
+size_t bo_gp_setup_workspace_bytes(const bo_gp* gp) {
+    double *a, *b, *c, *d, *e, *f;
+    bool ok;
+    return gp_setup_layout(gp, nullptr, 0, &a, &b, &c, &d, &e, &f, &ok);
+}
+
+int bo_gp_setup(bo_ctx* ctx, const bo_gp* gp, void* work, size_t work_bytes, int32_t* info, void* stream) {
+    if (!ctx || !valid_gp(gp) || !work || !info) return BO_ERR_INVALID;
+    cudaStream_t st = (cudaStream_t)stream;
+    const long n = gp->n, M = gp->M, np = bo_pad8(n), n1p = bo_pad8(n + 1), Kp = bo_kp(gp->d);
+    double *baug, *scratch, *rv, *t1, *av, *nz;
+    bool ok;
+    gp_setup_layout(gp, work, work_bytes, &baug, &scratch, &rv, &t1, &av, &nz, &ok);
+    if (!ok) return BO_ERR_WORKSPACE;
+    const BoKernelHyper h = hyper_of(gp);
+    BO_CUDA_TRY(cudaMemsetAsync(info, 0, sizeof(int32_t) * M, st));
+    BO_TRY(bo_aug_rows(h, gp->train_X, n, gp->aug_train, Kp, n * Kp, st));
+    BO_TRY(bo_aug_cols(h, gp->train_X, n, baug, Kp, np, Kp * np, st));
+    vec_add_kernel<<<(unsigned)((M + 127) / 128), 128, 0, st>>>(gp->noise, gp->jitter, nz, (int)M);
+    g_bo_launch_count++;
+    // K + (s2 + jitter) I, unit diagonal of the kernel enforced exactly (x1_eq_x2 branch of gpytorch's sq_dist)
+    BO_TRY(kmat(gp, gp->aug_train, (int)n, baug, np, n, gp->chol, np, n * np, 1, nz, st));
+    BO_TRY(bo_potrf_blocked(gp->chol, np, n * np, (int)n, (int)M, gp->linv_aug, np, (n + 1) * np, scratch, info, st));
+    BO_TRY(bo_trtri_blocked(gp->chol, np, n * np, (int)n, (int)M, gp->linv_aug, np, (n + 1) * np, scratch, st));
+    BO_TRY(bo_fill(gp->linv_aug_t, M * n * n1p, 0.0, st));
+    BO_TRY(bo_transpose(gp->linv_aug, np, (n + 1) * np, gp->linv_aug_t, n1p, n * n1p, (int)n, (int)n, (int)M, st));
+    // alpha = inv(L)^T (inv(L) (y - m))
+    dim3 vgrid((unsigned)((n + 127) / 128), (unsigned)M);
+    resid_kernel<<<vgrid, 128, 0, st>>>(gp->targets, gp->mean, rv, (int)n);
+    g_bo_launch_count++;
+    BO_TRY(gemm((int)n, 1, (int)n, (int)M, 1.0, gp->linv_aug, np, (n + 1) * np, rv, 2, n * 2, 0.0, nullptr, 0, 0, t1, 2,
+                n * 2, BO_TRI_A_LOWER, 0, st));
+    BO_TRY(gemm((int)n, 1, (int)n, (int)M, 1.0, gp->linv_aug_t, n1p, n * n1p, t1, 2, n * 2, 0.0, nullptr, 0, 0, av, 2,
+                n * 2, BO_TRI_A_UPPER, 0, st));
+    scatter_alpha_kernel<<<vgrid, 128, 0, st>>>(av, gp->linv_aug, np, gp->linv_aug_t, n1p, (int)n);
+    g_bo_launch_count++;
+    BO_CUDA_TRY(cudaGetLastError());
+    return BO_OK;
+}
+
+static size_t nei_setup_layout(const bo_gp* gp, const bo_nei* nei, void* work, size_t cap, double** baug_b,
+                               double** kb, double** fb, double** scratch, double** nz, bool* ok) {
+    const long n = gp->n, M = gp->M, nb = nei->n_b, nbp = bo_pad8(nb), Sp = bo_pad8(nei->S), Kp = bo_kp(gp->d);
+    Bump b(work, cap);
+    *baug_b = b.doubles(M * Kp * nbp);
+    *kb = b.doubles(M * n * nbp);
+    *fb = b.doubles(M * nb * Sp);
+    *scratch = b.doubles(bo_linalg_scratch_doubles((int)nb, (int)M));
+    *nz = b.doubles(M);
+    *ok = b.ok;
+    return b.off;
+}
+
+size_t bo_nei_setup_workspace_bytes(const bo_gp* gp, const bo_nei* nei) {
+    double *a, *b, *c, *d, *e;
+    bool ok;
+    return nei_setup_layout(gp, nei, nullptr, 0, &a, &b, &c, &d, &e, &ok);
+}
+
+int bo_nei_setup(bo_ctx* ctx, const bo_gp* gp, const bo_nei* nei, void* work, size_t work_bytes, int32_t* info,
+                 void* stream) {
+    if (!ctx || !valid_gp(gp) || !nei || nei->n_b <= 0 || nei->S <= 0 || !work || !info) return BO_ERR_INVALID;
+    if (nei->baseline_is_train && nei->n_b != gp->n) return BO_ERR_INVALID;
+    cudaStream_t st = (cudaStream_t)stream;
+    const long n = gp->n, M = gp->M, np = bo_pad8(n), nb = nei->n_b, nbp = bo_pad8(nb), S = nei->S, Sp = bo_pad8(S);
+    const long Kp = bo_kp(gp->d);
+    const double ys2 = gp->y_std * gp->y_std;
+    double *baug_b, *kb, *fb, *scratch, *nz;
+    bool ok;
+    nei_setup_layout(gp, nei, work, work_bytes, &baug_b, &kb, &fb, &scratch, &nz, &ok);
+    if (!ok) return BO_ERR_WORKSPACE;
+    const BoKernelHyper h = hyper_of(gp);
+    BO_CUDA_TRY(cudaMemsetAsync(info, 0, sizeof(int32_t) * M, st));
+    // base samples with padded pitch, and transposed
+    BO_TRY(bo_fill(nei->zb_pad, S * nbp, 0.0, st));
+    BO_TRY(bo_copy2d(nei->Z_b, nb, 0, nei->zb_pad, nbp, 0, (int)S, (int)nb, 1, st));
+    BO_TRY(bo_fill(nei->zb_t, nb * Sp, 0.0, st));
+    BO_TRY(bo_transpose(nei->zb_pad, nbp, 0, nei->zb_t, Sp, 0, (int)S, (int)nb, 1, st));
+    // cross covariance K(X_tr, X_b) and V_b = inv(L) K, mean row
+    const double* rows_b = gp->aug_train;
+    if (!nei->baseline_is_train) {
+        BO_TRY(bo_aug_rows(h, nei->X_b, nb, nei->aug_b, Kp, nb * Kp, st));
+        rows_b = nei->aug_b;
+    }
+    BO_TRY(bo_aug_cols(h, nei->X_b, nb, baug_b, Kp, nbp, Kp * nbp, st));
+    BO_TRY(kmat(gp, gp->aug_train, (int)n, baug_b, nbp, nb, kb, nbp, n * nbp, 0, nullptr, st));
+    BO_TRY(gemm((int)n + 1, (int)nb, (int)n, (int)M, 1.0, gp->linv_aug, np, (n + 1) * np, kb, nbp, n * nbp, 0.0, nullptr,
+                0, 0, nei->vb, nbp, (n + 1) * nbp, BO_TRI_A_LOWER, 0, st));
+    BO_TRY(bo_fill(nei->vb_t, M * nb * np, 0.0, st));
+    BO_TRY(bo_transpose(nei->vb, nbp, (n + 1) * nbp, nei->vb_t, np, nb * np, (int)n, (int)nb, (int)M, st));
+    dim3 mgrid((unsigned)((nb + 127) / 128), (unsigned)M);
+    mean_b_kernel<<<mgrid, 128, 0, st>>>(nei->vb, (n + 1) * nbp, nbp, (int)n, (int)nb, gp->y_mean, gp->y_std, gp->mean,
+                                         nei->mean_b);
+    g_bo_launch_count++;
+    // Sigma_bb = ys^2 (K(X_b,X_b) - V_b^T V_b), lower block-triangle, then its Cholesky root and inverse
+    BO_TRY(kmat(gp, rows_b, (int)nb, baug_b, nbp, nb, nei->lb, nbp, nb * nbp, 1, nullptr, st));
+    BO_TRY(gemm((int)nb, (int)nb, (int)n, (int)M, -ys2, nei->vb_t, np, nb * np, nei->vb, nbp, (n + 1) * nbp, ys2, nei->lb,
+                nbp, nb * nbp, nei->lb, nbp, nb * nbp, BO_TRI_NONE, 1, st));
+    BO_TRY(bo_add_diag(nei->lb, nbp, nb * nbp, (int)nb, (int)M, nei->jitter, st));
+    BO_TRY(bo_potrf_blocked(nei->lb, nbp, nb * nbp, (int)nb, (int)M, nei->lb_inv, nbp, nb * nbp, scratch, info, st));
+    BO_TRY(bo_trtri_blocked(nei->lb, nbp, nb * nbp, (int)nb, (int)M, nei->lb_inv, nbp, nb * nbp, scratch, st));
+    BO_TRY(bo_fill(nei->lb_inv_t, M * nb * nbp, 0.0, st));
+    BO_TRY(bo_transpose(nei->lb_inv, nbp, nb * nbp, nei->lb_inv_t, nbp, nb * nbp, (int)nb, (int)nb, (int)M, st));
+    // baseline samples f_b[s] = mean_b + L_b z_s and best_f[s] = max_i f_b[s][i]
+    BO_TRY(gemm((int)nb, (int)S, (int)nb, (int)M, 1.0, nei->lb, nbp, nb * nbp, nei->zb_t, Sp, 0, 0.0, nullptr, 0, 0, fb, Sp,
+                nb * Sp, BO_TRI_A_LOWER, 0, st));
+    BO_TRY(bo_col_max(fb, nb * Sp, Sp, nei->mean_b, nbp, (int)nb, (int)S, (int)M, nei->best_f, Sp, st));
+    BO_CUDA_TRY(cudaGetLastError());
+    return BO_OK;
+}
+
+}  // extern "C"
+
+// ------------------------------------------------------------------------------------------------
+// the hot path
+// ------------------------------------------------------------------------------------------------
+namespace {
+
+struct QWork {
+    long ldn, R, regionStride;
+    double *baug, *W0, *W1, *W2, *W3, *F, *W5, *W6, *Lq, *lse, *Sbar;
+    int32_t* info;
+    bool ok;
+    size_t bytes;
+};
+
+QWork qlayout(const bo_gp* gp, const bo_nei* nei, int B, int q, int with_grad, void* work, size_t cap) {
+    QWork w{};
+    const long n = gp->n, nb = nei->n_b, M = gp->M, Kp = bo_kp(gp->d);
+    const long N = (long)B * q;
+    w.ldn = bo_pad8(N);
+    w.R = (n > nb ? n : nb) + 1;
+    w.regionStride = w.R * w.ldn;
+    Bump b(work, cap);
+    w.baug = b.doubles(M * Kp * w.ldn);
+    w.W0 = b.doubles(M * w.regionStride);
+    w.W1 = b.doubles(M * w.regionStride);
+    w.W2 = b.doubles(M * w.regionStride);
+    w.W3 = b.doubles(M * w.regionStride);
+    w.F = b.doubles(M * (long)nei->S * w.ldn);
+    w.Lq = b.doubles(M * (long)B * q * q);
+    w.lse = b.doubles(M * (long)B);
+    w.info = reinterpret_cast<int32_t*>(b.doubles((M * (long)B + 1) / 2));
+    w.W6 = nei->baseline_is_train ? nullptr : b.doubles(M * w.regionStride);
+    if (with_grad) {
+        w.W5 = b.doubles(M * w.regionStride);
+        w.Sbar = b.doubles(M * (long)B * q * q);
+    }
+    w.ok = b.ok;
+    w.bytes = b.off;
+    return w;
+}
+
+BoCandArgs cand_args(const bo_gp* gp, const bo_nei* nei, int B, int q, const double* X, const double* Zq,
+                     double tau_relu, double tau_max, const QWork& w) {
+    BoCandArgs a{};
+    a.h = hyper_of(gp);
+    a.n = gp->n; a.n_b = nei ? nei->n_b : 0; a.S = nei ? nei->S : 0; a.B = B; a.q = q;
+    a.y_mean = gp->y_mean; a.y_std = gp->y_std;
+    a.mean_const = gp->mean;
+    a.X = X; a.Zq = Zq;
+    a.best_f = nei ? nei->best_f : nullptr;
+    a.Sp = nei ? bo_pad8(nei->S) : 0;
+    a.tau_relu = tau_relu; a.tau_max = tau_max;
+    a.ldn = w.ldn;
+    a.V = w.W1; a.strideV = w.regionStride;
+    a.BL = w.W3; a.strideBL = w.regionStride;
+    a.F = w.F; a.strideF = nei ? (long)nei->S * w.ldn : 0;
+    a.Lq = w.Lq; a.lse = w.lse;
+    return a;
+}
+
+}  // namespace
+
+extern "C" {
+
+size_t bo_qlognei_workspace_bytes(const bo_gp* gp, const bo_nei* nei, int B, int q, int with_grad) {
+    return qlayout(gp, nei, B, q, with_grad, nullptr, 0).bytes;
+}
+
+int bo_qlognei_fwd(bo_ctx* ctx, const bo_gp* gp, const bo_nei* nei, int B, int q, const double* X,
+                   const double* Z_q, double tau_relu, double tau_max, double* acq, int32_t* info, void* work,
+                   size_t work_bytes, int with_grad, void* stream) {
+    if (!ctx || !valid_gp(gp) || !nei || B <= 0 || q <= 0 || !X || !Z_q || !acq || !info || !work)
+        return BO_ERR_INVALID;
+    if (q > BO_MAX_Q) return BO_ERR_UNSUPPORTED;
+    if (!(tau_relu > 0.0) || !(tau_max > 0.0)) return BO_ERR_INVALID;
+    cudaStream_t st = (cudaStream_t)stream;
+    const QWork w = qlayout(gp, nei, B, q, with_grad, work, work_bytes);
+    if (!w.ok) return BO_ERR_WORKSPACE;
+    const long n = gp->n, nb = nei->n_b, M = gp->M, np = bo_pad8(n), nbp = bo_pad8(nb), Kp = bo_kp(gp->d);
+    const long S = nei->S, N = (long)B * q;
+    const double ys2 = gp->y_std * gp->y_std;
+    const BoKernelHyper h = hyper_of(gp);
+    // 1. K(X_tr, X) (and K(X_b, X)) through the augmented squared-distance contraction
+    BO_TRY(bo_aug_cols(h, X, N, w.baug, Kp, w.ldn, Kp * w.ldn, st));
+    BO_TRY(kmat(gp, gp->aug_train, (int)n, w.baug, w.ldn, N, w.W0, w.ldn, w.regionStride, 0, nullptr, st));
+    const double* KB = w.W0;
+    if (!nei->baseline_is_train) {
+        BO_TRY(kmat(gp, nei->aug_b, (int)nb, w.baug, w.ldn, N, w.W6, w.ldn, w.regionStride, 0, nullptr, st));
+        KB = w.W6;
+    }
+    // 2. V = [inv(L); alpha^T] K(X_tr, X)           (n+1) x N
+    BO_TRY(gemm((int)n + 1, (int)N, (int)n, (int)M, 1.0, gp->linv_aug, np, (n + 1) * np, w.W0, w.ldn, w.regionStride, 0.0,
+                nullptr, 0, 0, w.W1, w.ldn, w.regionStride, BO_TRI_A_LOWER, 0, st));
+    // 3. Sigma(X_b, X) = ys^2 (K(X_b, X) - V_b^T V)   n_b x N
+    BO_TRY(gemm((int)nb, (int)N, (int)n, (int)M, -ys2, nei->vb_t, np, nb * np, w.W1, w.ldn, w.regionStride, ys2, KB, w.ldn,
+                w.regionStride, w.W2, w.ldn, w.regionStride, BO_TRI_NONE, 0, st));
+    // 4. bl_chol^T = inv(L_b) Sigma(X_b, X)
+    BO_TRY(gemm((int)nb, (int)N, (int)nb, (int)M, 1.0, nei->lb_inv, nbp, nb * nbp, w.W2, w.ldn, w.regionStride, 0.0,
+                nullptr, 0, 0, w.W3, w.ldn, w.regionStride, BO_TRI_A_LOWER, 0, st));
+    // 5. baseline part of the samples: Z_b bl_chol^T    S x N
+    BO_TRY(gemm((int)S, (int)N, (int)nb, (int)M, 1.0, nei->zb_pad, nbp, 0, w.W3, w.ldn, w.regionStride, 0.0, nullptr, 0, 0,
+                w.F, w.ldn, S * w.ldn, BO_TRI_NONE, 0, st));
+    // 6. Schur block, q x q Cholesky, samples, log_fatplus / fatmax / logmeanexp
+    BoCandArgs a = cand_args(gp, nei, B, q, X, Z_q, tau_relu, tau_max, w);
+    a.acq = acq;
+    a.info = w.info;  // kept in the workspace for the backward pass, copied out for the caller
+    BO_TRY(bo_cand_fwd(a, st));
+    BO_CUDA_TRY(cudaMemcpyAsync(info, w.info, sizeof(int32_t) * M * B, cudaMemcpyDeviceToDevice, st));
+    return BO_OK;
+}
+
+int bo_qlognei_bwd(bo_ctx* ctx, const bo_gp* gp, const bo_nei* nei, int B, int q, const double* X,
+                   const double* Z_q, double tau_relu, double tau_max, const double* grad_acq, double* grad_X,
+                   void* work, size_t work_bytes, void* stream) {
+    if (!ctx || !valid_gp(gp) || !nei || B <= 0 || q <= 0 || !X || !Z_q || !grad_acq || !grad_X || !work)
+        return BO_ERR_INVALID;
+    cudaStream_t st = (cudaStream_t)stream;
+    const QWork w = qlayout(gp, nei, B, q, 1, work, work_bytes);
+    if (!w.ok) return BO_ERR_WORKSPACE;
+    const long n = gp->n, nb = nei->n_b, M = gp->M, n1p = bo_pad8(n + 1), nbp = bo_pad8(nb), Sp = bo_pad8(nei->S);
+    const long S = nei->S, N = (long)B * q;
+    const double ys2 = gp->y_std * gp->y_std;
+    const BoKernelHyper h = hyper_of(gp);
+    // 1. reductions, samples and q x q Cholesky in reverse: F <- dF, Sbar, row n of Vbar, gradX <- k(X,X) part
+    BoCandArgs a = cand_args(gp, nei, B, q, X, Z_q, tau_relu, tau_max, w);
+    a.info = w.info;
+    a.grad_acq = grad_acq;
+    a.Sbar = w.Sbar;
+    a.Vbar_mu = w.W5 + n * w.ldn;
+    a.strideVbar = w.regionStride;
+    a.gradX = grad_X;
+    BO_TRY(bo_cand_bwd(a, st));
+    // 2. BLbar = Z_b^T dF - 2 BL Sbar                       (W2)
+    BO_TRY(gemm((int)nb, (int)N, (int)S, (int)M, 1.0, nei->zb_t, Sp, 0, w.F, w.ldn, S * w.ldn, 0.0, nullptr, 0, 0, w.W2,
+                w.ldn, w.regionStride, BO_TRI_NONE, 0, st));
+    BO_TRY(bo_colblock_update(w.W2, w.regionStride, w.W3, w.regionStride, w.Sbar, (int)nb, B, q, (int)M, w.ldn, -2.0, st));
+    // 3. Cbar = inv(L_b)^T BLbar                            (W0)
+    BO_TRY(gemm((int)nb, (int)N, (int)nb, (int)M, 1.0, nei->lb_inv_t, nbp, nb * nbp, w.W2, w.ldn, w.regionStride, 0.0,
+                nullptr, 0, 0, w.W0, w.ldn, w.regionStride, BO_TRI_A_UPPER, 0, st));
+    // 4. Vbar = -ys^2 V_b Cbar - 2 ys^2 V Sbar              (W5 rows 0..n-1; row n holds y_std * mubar)
+    BO_TRY(gemm((int)n, (int)N, (int)nb, (int)M, -ys2, nei->vb, nbp, (n + 1) * nbp, w.W0, w.ldn, w.regionStride, 0.0,
+                nullptr, 0, 0, w.W5, w.ldn, w.regionStride, BO_TRI_NONE, 0, st));
+    BO_TRY(bo_colblock_update(w.W5, w.regionStride, w.W1, w.regionStride, w.Sbar, (int)n, B, q, (int)M, w.ldn, -2.0 * ys2,
+                              st));
+    // 5. KXbar = [inv(L)^T | alpha] Vbar (+ ys^2 Cbar when X_baseline is train_X)      (W2)
+    const bool shared = nei->baseline_is_train != 0;
+    BO_TRY(gemm((int)n, (int)N, (int)n + 1, (int)M, 1.0, gp->linv_aug_t, n1p, n * n1p, w.W5, w.ldn, w.regionStride,
+                shared ? ys2 : 0.0, shared ? w.W0 : nullptr, w.ldn, w.regionStride, w.W2, w.ldn, w.regionStride,
+                BO_TRI_A_UPPER, 0, st));
+    // 6. chain through the covariance function to X
+    BO_TRY(bo_kgrad(h, gp->train_X, (int)n, w.W2, w.regionStride, w.ldn, X, B, q, 1.0, grad_X, st));
+    if (!shared) BO_TRY(bo_kgrad(h, nei->X_b, (int)nb, w.W0, w.regionStride, w.ldn, X, B, q, ys2, grad_X, st));
+    return BO_OK;
+}
+
+// ------------------------------------------------------------------------------------------------
+// posterior API
+// ------------------------------------------------------------------------------------------------
+static size_t post_layout(const bo_gp* gp, long Nc, void* work, size_t cap, double** baug, double** kx, double** v,
+                          long* ldn, bool* ok) {
+    const long n = gp->n, M = gp->M, Kp = bo_kp(gp->d);
+    *ldn = bo_pad8(Nc);
+    Bump b(work, cap);
+    *baug = b.doubles(M * Kp * *ldn);
+    *kx = b.doubles(M * n * *ldn);
+    *v = b.doubles(M * (n + 1) * *ldn);
+    *ok = b.ok;
+    return b.off;
+}
+
+size_t bo_posterior_workspace_bytes(const bo_gp* gp, long Nc) {
+    double *a, *b, *c;
+    long ldn;
+    bool ok;
+    return post_layout(gp, Nc, nullptr, 0, &a, &b, &c, &ldn, &ok);
+}
+
+static int posterior_v(const bo_gp* gp, long Nc, const double* Xc, void* work, size_t work_bytes, double** v_out,
+                       double** kx_out, long* ldn_out, cudaStream_t st) {
+    double *baug, *kx, *v;
+    long ldn;
+    bool ok;
+    post_layout(gp, Nc, work, work_bytes, &baug, &kx, &v, &ldn, &ok);
+    if (!ok) return BO_ERR_WORKSPACE;
+    const long n = gp->n, M = gp->M, np = bo_pad8(n), Kp = bo_kp(gp->d);
+    if (Nc > 0x7fffffffL) return BO_ERR_UNSUPPORTED;
+    const BoKernelHyper h = hyper_of(gp);
+    BO_TRY(bo_aug_cols(h, Xc, Nc, baug, Kp, ldn, Kp * ldn, st));
+    BO_TRY(kmat(gp, gp->aug_train, (int)n, baug, ldn, Nc, kx, ldn, n * ldn, 0, nullptr, st));
+    BO_TRY(gemm((int)n + 1, (int)Nc, (int)n, (int)M, 1.0, gp->linv_aug, np, (n + 1) * np, kx, ldn, n * ldn, 0.0, nullptr, 0,
+                0, v, ldn, (n + 1) * ldn, BO_TRI_A_LOWER, 0, st));
+    *v_out = v;
+    *kx_out = kx;
+    *ldn_out = ldn;
+    return BO_OK;
+}
+
+int bo_posterior_joint(bo_ctx* ctx, const bo_gp* gp, int B, int q, const double* X, double* mean, double* cov,
+                       void* work, size_t work_bytes, void* stream) {
+    if (!ctx || !valid_gp(gp) || B <= 0 || q <= 0 || !X || !mean || !cov || !work) return BO_ERR_INVALID;
+    if (q > BO_MAX_Q) return BO_ERR_UNSUPPORTED;
+    cudaStream_t st = (cudaStream_t)stream;
+    double *v, *kx;
+    long ldn;
+    BO_TRY(posterior_v(gp, (long)B * q, X, work, work_bytes, &v, &kx, &ldn, st));
+    BoCandArgs a{};
+    a.h = hyper_of(gp);
+    a.n = gp->n; a.B = B; a.q = q;
+    a.y_mean = gp->y_mean; a.y_std = gp->y_std;
+    a.mean_const = gp->mean;
+    a.X = X;
+    a.ldn = ldn;
+    a.V = v; a.strideV = (long)(gp->n + 1) * ldn;
+    return bo_cand_posterior(a, mean, cov, st);
+}
+
+int bo_posterior_mean_var(bo_ctx* ctx, const bo_gp* gp, long Nc, const double* Xc, double* mean, double* var,
+                          void* work, size_t work_bytes, void* stream) {
+    if (!ctx || !valid_gp(gp) || Nc <= 0 || !Xc || !mean || !var || !work) return BO_ERR_INVALID;
+    cudaStream_t st = (cudaStream_t)stream;
+    double *v, *kx;
+    long ldn;
+    BO_TRY(posterior_v(gp, Nc, Xc, work, work_bytes, &v, &kx, &ldn, st));
+    return bo_col_mean_var(v, (long)(gp->n + 1) * ldn, ldn, gp->n, Nc, gp->M, gp->y_mean, gp->y_std, gp->mean,
+                           gp->outputscale, mean, var, st);
+}
+
+int bo_ts_argmax(bo_ctx* ctx, int M, long Nc, const double* mean, const double* var, const double* z,
+                 double* out_val, int64_t* out_idx, void* stream) {
+    if (!ctx || !mean || !out_val || !out_idx || (z && !var)) return BO_ERR_INVALID;
+    return bo_ts_argmax_launch(M, Nc, mean, var, z, out_val, reinterpret_cast<long long*>(out_idx), (cudaStream_t)stream);
+}
+
+int bo_argmax(bo_ctx* ctx, long n, const double* v, double* out_val, int64_t* out_idx, void* stream) {
+    if (!ctx || !v || !out_val || !out_idx) return BO_ERR_INVALID;
+    return bo_ts_argmax_launch(1, n, v, nullptr, nullptr, out_val, reinterpret_cast<long long*>(out_idx),
+                               (cudaStream_t)stream);
+}
+
+// ------------------------------------------------------------------------------------------------
+// building blocks exported for the parity tests
+// ------------------------------------------------------------------------------------------------
+int bo_dgemm(bo_ctx* ctx, int M, int N, int K, int batch, double alpha, const double* A, long lda, long strideA,
+             const double* B, long ldb, long strideB, double beta, double* C, long ldc, long strideC, int tri,
+             void* stream) {
+    if (!ctx || !A || !B || !C) return BO_ERR_INVALID;
+    return gemm(M, N, K, batch, alpha, A, lda, strideA, B, ldb, strideB, beta, beta != 0.0 ? C : nullptr, ldc, strideC, C,
+                ldc, strideC, tri, 0, (cudaStream_t)stream);
+}
+
+int bo_kernel_matrix(bo_ctx* ctx, const bo_gp* gp, long Nc, const double* Xc, double* out, void* work,
+                     size_t work_bytes, void* stream) {
+    if (!ctx || !valid_gp(gp) || Nc <= 0 || !Xc || !out || !work) return BO_ERR_INVALID;
+    cudaStream_t st = (cudaStream_t)stream;
+    const long n = gp->n, M = gp->M, Kp = bo_kp(gp->d), ldn = bo_pad8(Nc);
+    Bump b(work, work_bytes);
+    double* baug = b.doubles(M * Kp * ldn);
+    if (!b.ok) return BO_ERR_WORKSPACE;
+    const BoKernelHyper h = hyper_of(gp);
+    BO_TRY(bo_aug_cols(h, Xc, Nc, baug, Kp, ldn, Kp * ldn, st));
+    return kmat(gp, gp->aug_train, (int)n, baug, ldn, Nc, out, ldn, n * ldn, 0, nullptr, st);
+}
+
+size_t bo_potrf_workspace_bytes(int n, int batch) { return sizeof(double) * (size_t)bo_linalg_scratch_doubles(n, batch); }
+
+int bo_potrf(bo_ctx* ctx, int n, int batch, double* A, long lda, long strideA, double* inv, void* work,
+             size_t work_bytes, int32_t* info, void* stream) {
+    if (!ctx || !A || !work || !info || n <= 0 || batch <= 0) return BO_ERR_INVALID;
+    if (work_bytes < bo_potrf_workspace_bytes(n, batch)) return BO_ERR_WORKSPACE;
+    cudaStream_t st = (cudaStream_t)stream;
+    BO_CUDA_TRY(cudaMemsetAsync(info, 0, sizeof(int32_t) * batch, st));
+    BO_TRY(bo_potrf_blocked(A, lda, strideA, n, batch, inv, lda, strideA, (double*)work, info, st));
+    if (inv) BO_TRY(bo_trtri_blocked(A, lda, strideA, n, batch, inv, lda, strideA, (double*)work, st));
+    return BO_OK;
+}
+
+}  // extern "C"

@@ -1,0 +1,728 @@
+// Per-candidate kernels of the fused qLogNEI path: Schur block + q x q Cholesky (with the
+// psd_safe_cholesky jitter schedule), reparameterised samples f = mu + L z, log_fatplus, fatmax over q,
+// logmeanexp over MC samples, and the hand-derived reverse pass of all of it.
+// Reference arithmetic: utils/low_rank.py:118-162, acquisition/logei.py:509-534,
+// utils/safe_math.py:149-187 (_inf_max_helper), :293-352 (log_fatplus, fatmax), :209-223 (logmeanexp).
+#include "cand.cuh"
+
+#include <cfloat>
+#include <cmath>
+
+namespace {
+
+constexpr int CAND_THREADS = 128;
+constexpr int PANEL_ROWS = 64;
+
+// ---------------------------------------------------------------------------------------------
+// covariance functions of a squared scaled distance
+// ---------------------------------------------------------------------------------------------
+__device__ __forceinline__ double kern_value(int kernel_id, double r2, double os) {
+    r2 = r2 > 0.0 ? r2 : 0.0;
+    if (kernel_id == BO_KERNEL_RBF) return os * exp(-0.5 * r2);
+    const double sqrt5 = 2.23606797749978969641;
+    const double r = sqrt(r2 > 1e-30 ? r2 : 1e-30);
+    return os * ((sqrt5 * r + 1.0) + (5.0 / 3.0) * (r * r)) * exp(-sqrt5 * r);
+}
+// g(r) with  d k / d x_a = -g * (x_a - x_b) / l^2
+__device__ __forceinline__ double kern_dfactor(int kernel_id, double r2, double os) {
+    r2 = r2 > 0.0 ? r2 : 0.0;
+    if (kernel_id == BO_KERNEL_RBF) return os * exp(-0.5 * r2);
+    if (r2 < 1e-30) return 0.0;  // gpytorch clamps the distance: no gradient below the clamp
+    const double sqrt5 = 2.23606797749978969641;
+    const double r = sqrt(r2);
+    return os * (5.0 / 3.0) * (1.0 + sqrt5 * r) * exp(-sqrt5 * r);
+}
+
+// ---------------------------------------------------------------------------------------------
+// reductions of safe_math.py
+// ---------------------------------------------------------------------------------------------
+// log(tau*(softplus(u) + 0.1/(1+u^2))), u = z/tau   (torch softplus: identity above threshold 20)
+__device__ __forceinline__ double log_fatplus(double z, double tau) {
+    const double u = z / tau;
+    const double sp = (u > 20.0) ? u : log1p(exp(u));
+    return log(tau * (sp + 0.1 * (1.0 / (1.0 + u * u))));
+}
+// d log_fatplus / dz
+__device__ __forceinline__ double dlog_fatplus(double z, double tau) {
+    const double u = z / tau;
+    double sp, sig;
+    if (u > 20.0) { sp = u; sig = 1.0; }
+    else { const double e = exp(u); sp = log1p(e); sig = e / (e + 1.0); }
+    const double c = 1.0 / (1.0 + u * u);
+    const double val = sp + 0.1 * c;
+    if (!(val > 0.0)) return 0.0;
+    return (sig - 0.2 * u * c * c) / (val * tau);
+}
+__device__ __forceinline__ double pareto2(double u) { return 2.0 / (2.0 + 2.0 * u + u * u); }
+
+// fatmax over x[0..q) (alpha = 2) with the infinity handling of _inf_max_helper
+__device__ __forceinline__ double fatmax_q(const double* x, int q, double tau) {
+    double M = x[0];
+    for (int j = 1; j < q; j++) M = fmax(M, x[j]);  // NaN-ignoring like amax is not needed: NaN flagged earlier
+    if (isinf(M)) {
+        double s = 0.0;
+        for (int j = 0; j < q; j++) if (x[j] == M) s += x[j];
+        return s;
+    }
+    double sum = 0.0;
+    for (int j = 0; j < q; j++) sum += pareto2(-(x[j] - M) / tau);
+    return M + tau * log(sum);
+}
+// gradient of fatmax w.r.t. x (g[0..q))
+__device__ __forceinline__ void fatmax_q_grad(const double* x, int q, double tau, double* g) {
+    double M = x[0];
+    for (int j = 1; j < q; j++) M = fmax(M, x[j]);
+    if (isinf(M)) {
+        for (int j = 0; j < q; j++) g[j] = (x[j] == M) ? 1.0 : 0.0;
+        return;
+    }
+    double sum = 0.0;
+    int nties = 0;
+    for (int j = 0; j < q; j++) {
+        sum += pareto2(-(x[j] - M) / tau);
+        nties += (x[j] == M);
+    }
+    double wsum = 0.0;
+    for (int j = 0; j < q; j++) {
+        const double u = -(x[j] - M) / tau;
+        const double p = pareto2(u);
+        g[j] = isinf(u) ? 0.0 : p * p * (1.0 + u) / sum;
+        wsum += g[j];
+    }
+    const double rest = (1.0 - wsum) / nties;  // amax subgradient, split evenly among ties (torch.amax)
+    for (int j = 0; j < q; j++) if (x[j] == M) g[j] += rest;
+}
+
+__device__ __forceinline__ double block_reduce_max(double v, double* red) {
+    for (int o = 16; o > 0; o >>= 1) v = fmax(v, __shfl_xor_sync(0xffffffffu, v, o));
+    const int w = threadIdx.x >> 5, l = threadIdx.x & 31;
+    __syncthreads();
+    if (l == 0) red[w] = v;
+    __syncthreads();
+    double r = red[0];
+    for (int i = 1; i < (int)(blockDim.x >> 5); i++) r = fmax(r, red[i]);
+    return r;
+}
+__device__ __forceinline__ double block_reduce_sum(double v, double* red) {
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    const int w = threadIdx.x >> 5, l = threadIdx.x & 31;
+    __syncthreads();
+    if (l == 0) red[w] = v;
+    __syncthreads();
+    double r = 0.0;
+    for (int i = 0; i < (int)(blockDim.x >> 5); i++) r += red[i];
+    return r;
+}
+
+// ---------------------------------------------------------------------------------------------
+// augmented operands
+// ---------------------------------------------------------------------------------------------
+__global__ void aug_rows_kernel(BoKernelHyper h, const double* X, long npts, double* out, long Kp, long strideOut) {
+    const int z = blockIdx.y;
+    const long i = blockIdx.x * (long)blockDim.x + threadIdx.x;
+    if (i >= npts) return;
+    const double* il = h.inv_ls + (long)z * h.d;
+    double* o = out + (long)z * strideOut + i * Kp;
+    double nrm = 0.0;
+    for (int t = 0; t < h.d; t++) {
+        const double v = (X[i * h.d + t] - h.center[t]) * il[t];
+        o[t] = -2.0 * v;
+        nrm += v * v;
+    }
+    o[h.d] = nrm;
+    o[h.d + 1] = 1.0;
+    for (long t = h.d + 2; t < Kp; t++) o[t] = 0.0;
+}
+
+__global__ void aug_cols_kernel(BoKernelHyper h, const double* X, long npts, double* out, long Kp, long ldo,
+                                long strideOut) {
+    const int z = blockIdx.y;
+    const long c = blockIdx.x * (long)blockDim.x + threadIdx.x;
+    if (c >= ldo) return;
+    double* o = out + (long)z * strideOut + c;
+    if (c >= npts) {  // padded columns: all-zero operand
+        for (long t = 0; t < Kp; t++) o[t * ldo] = 0.0;
+        return;
+    }
+    const double* il = h.inv_ls + (long)z * h.d;
+    double nrm = 0.0;
+    for (int t = 0; t < h.d; t++) {
+        const double v = (X[c * h.d + t] - h.center[t]) * il[t];
+        o[(long)t * ldo] = v;
+        nrm += v * v;
+    }
+    o[(long)h.d * ldo] = 1.0;
+    o[(long)(h.d + 1) * ldo] = nrm;
+    for (long t = h.d + 2; t < Kp; t++) o[t * ldo] = 0.0;
+}
+
+}  // namespace
+
+namespace {
+
+__device__ __forceinline__ void pair_decode(int pair, int& j, int& k) {
+    j = (int)((sqrt(8.0 * pair + 1.0) - 1.0) * 0.5);
+    while ((j + 1) * (j + 2) / 2 <= pair) j++;
+    while (j * (j + 1) / 2 > pair) j--;
+    k = pair - j * (j + 1) / 2;
+}
+
+// G[j][k] = sum_i Mtx[i][c0+j] * Mtx[i][c0+k]  for the q columns of one t-batch element.
+// Deterministic: fixed row -> group assignment and fixed-order final sum.
+__device__ void gram_block(const double* __restrict__ Mtx, long ld, int rows, int c0, int q, double* panel,
+                           double* part, double* G) {
+    const int T = blockDim.x, tid = threadIdx.x;
+    const int P = q * (q + 1) / 2;
+    const int ngroups = (T / P) > 1 ? (T / P) : 1;
+    for (int i = tid; i < P * ngroups; i += T) part[i] = 0.0;
+    __syncthreads();
+    for (int r0 = 0; r0 < rows; r0 += PANEL_ROWS) {
+        const int pr = (rows - r0 < PANEL_ROWS) ? rows - r0 : PANEL_ROWS;
+        for (int idx = tid; idx < pr * q; idx += T) {
+            const int r = idx / q, j = idx % q;
+            panel[idx] = Mtx[(long)(r0 + r) * ld + c0 + j];
+        }
+        __syncthreads();
+        for (int slot = tid; slot < P * ngroups; slot += T) {
+            const int grp = slot / P, pair = slot % P;
+            int j, k;
+            pair_decode(pair, j, k);
+            double acc = 0.0;
+            for (int r = grp; r < pr; r += ngroups) acc += panel[r * q + j] * panel[r * q + k];
+            part[slot] += acc;
+        }
+        __syncthreads();
+    }
+    for (int pair = tid; pair < P; pair += T) {
+        int j, k;
+        pair_decode(pair, j, k);
+        double s = 0.0;
+        for (int grp = 0; grp < ngroups; grp++) s += part[grp * P + pair];
+        G[j * q + k] = s;
+        G[k * q + j] = s;
+    }
+    __syncthreads();
+}
+
+// in-place lower Cholesky of the q x q matrix A (row-major); returns false on a non-positive pivot
+__device__ bool chol_small(double* A, int q) {
+    for (int j = 0; j < q; j++) {
+        double d = A[j * q + j];
+        for (int k = 0; k < j; k++) d -= A[j * q + k] * A[j * q + k];
+        if (!(d > 0.0)) return false;
+        d = sqrt(d);
+        A[j * q + j] = d;
+        for (int i = j + 1; i < q; i++) {
+            double s = A[i * q + j];
+            for (int k = 0; k < j; k++) s -= A[i * q + k] * A[j * q + k];
+            A[i * q + j] = s / d;
+        }
+    }
+    return true;
+}
+
+struct CandSmem {
+    double *panel, *part, *GV, *GB, *Lq, *mu, *fm;
+};
+__device__ __forceinline__ CandSmem carve(double* sm, int q, int T, int S) {
+    const int P = q * (q + 1) / 2;
+    CandSmem c;
+    c.panel = sm;
+    c.part = c.panel + PANEL_ROWS * q;
+    c.GV = c.part + (T > P ? T : P);
+    c.GB = c.GV + q * q;
+    c.Lq = c.GB + q * q;
+    c.mu = c.Lq + q * q;
+    c.fm = c.mu + q;
+    (void)S;
+    return c;
+}
+size_t cand_smem_bytes(int q, int T, int S) {
+    const int P = q * (q + 1) / 2;
+    return sizeof(double) * ((size_t)PANEL_ROWS * q + (T > P ? T : P) + 3 * q * q + q + S);
+}
+
+__device__ __forceinline__ double pair_r2(const double* X, int d, const double* il, int a, int b) {
+    double r2 = 0.0;
+    for (int t = 0; t < d; t++) {
+        const double v = (X[(long)a * d + t] - X[(long)b * d + t]) * il[t];
+        r2 += v * v;
+    }
+    return r2;
+}
+
+__global__ void __launch_bounds__(CAND_THREADS) cand_fwd_kernel(const BoCandArgs a) {
+    extern __shared__ __align__(16) double sm[];
+    __shared__ double red[CAND_THREADS / 32];
+    __shared__ int s_info;
+    const int q = a.q, b = blockIdx.x, z = blockIdx.y, tid = threadIdx.x, T = blockDim.x;
+    const CandSmem c = carve(sm, q, T, a.S);
+    const int c0 = b * q;
+    const double* V = a.V + (long)z * a.strideV;
+    const double* BL = a.BL + (long)z * a.strideBL;
+    double* F = a.F + (long)z * a.strideF;
+
+    gram_block(V, a.ldn, a.n, c0, q, c.panel, c.part, c.GV);
+    gram_block(BL, a.ldn, a.n_b, c0, q, c.panel, c.part, c.GB);
+
+    const double ys2 = a.y_std * a.y_std;
+    const double os = a.h.outputscale ? a.h.outputscale[z] : 1.0;
+    const double* il = a.h.inv_ls + (long)z * a.h.d;
+    for (int idx = tid; idx < q * q; idx += T) {
+        const int j = idx / q, k = idx % q;
+        const double kv = kern_value(a.h.kernel_id, pair_r2(a.X, a.h.d, il, c0 + j, c0 + k), os);
+        c.Lq[idx] = ys2 * (kv - c.GV[idx]) - c.GB[idx];  // Schur block  br - bl_chol bl_chol^T
+    }
+    if (tid < q) c.mu[tid] = a.y_mean + a.y_std * (a.mean_const[z] + V[(long)a.n * a.ldn + c0 + tid]);
+    __syncthreads();
+    if (tid == 0) {  // psd_safe_cholesky: plain attempt, then jitter 1e-8 * 10^i, i = 0..5
+        double* Sq = c.GV;  // backup of the Schur block
+        bool has_nan = false;
+        for (int i = 0; i < q * q; i++) {
+            Sq[i] = c.Lq[i];
+            has_nan |= isnan(Sq[i]);
+        }
+        int code = -2;
+        if (has_nan) {
+            code = -1;
+        } else {
+            double jit = 0.0;
+            for (int attempt = 0; attempt <= 6; attempt++) {
+                for (int i = 0; i < q * q; i++) c.Lq[i] = Sq[i];
+                for (int i = 0; i < q; i++) c.Lq[i * q + i] += jit;
+                if (chol_small(c.Lq, q)) { code = attempt; break; }
+                jit = (attempt == 0) ? 1e-8 : jit * 10.0;
+            }
+        }
+        if (code < 0)
+            for (int i = 0; i < q * q; i++) c.Lq[i] = 0.0;
+        for (int j = 0; j < q; j++)
+            for (int k = j + 1; k < q; k++) c.Lq[j * q + k] = 0.0;
+        s_info = code;
+    }
+    __syncthreads();
+
+    int bad = 0;
+    double local_max = -INFINITY;
+    for (int s = tid; s < a.S; s += T) {
+        double li[BO_MAX_Q];
+        const double bf = a.best_f[(long)z * a.Sp + s];
+        for (int j = 0; j < q; j++) {
+            double v = F[(long)s * a.ldn + c0 + j] + c.mu[j];
+            for (int k = 0; k <= j; k++) v += c.Lq[j * q + k] * a.Zq[(long)s * q + k];
+            F[(long)s * a.ldn + c0 + j] = v;
+            if (!isfinite(v)) bad = 1;
+            li[j] = log_fatplus(v - bf, a.tau_relu);
+        }
+        const double m = fatmax_q(li, q, a.tau_max);
+        c.fm[s] = m;
+        local_max = fmax(local_max, m);
+    }
+    const int anybad = __syncthreads_or(bad);
+    const double Mx = block_reduce_max(local_max, red);
+    double lse;
+    if (isinf(Mx)) {
+        lse = Mx;
+    } else {
+        double part = 0.0;
+        for (int s = tid; s < a.S; s += T) part += exp(c.fm[s] - Mx);
+        lse = Mx + log(block_reduce_sum(part, red));
+    }
+    if (tid == 0) {
+        const long o = (long)z * a.B + b;
+        a.acq[o] = lse - log((double)a.S);
+        a.lse[o] = lse;
+        a.info[o] = anybad ? -1 : s_info;
+    }
+    for (int idx = tid; idx < q * q; idx += T) a.Lq[((long)z * a.B + b) * q * q + idx] = c.Lq[idx];
+}
+
+}  // namespace
+
+namespace {
+
+// Reverse pass of cand_fwd_kernel for one (model, t-batch element).
+//   in : F holds the samples f[s][j];  Lq = br_chol;  lse;  grad_acq
+//   out: F <- d loss / d f ;  Sbar = adjoint of the Schur block (symmetric);
+//        Vbar row n <- y_std * d loss / d mu ;  gradX <- contribution of k(X, X)
+__global__ void __launch_bounds__(CAND_THREADS) cand_bwd_kernel(const BoCandArgs a) {
+    extern __shared__ __align__(16) double sm[];
+    const int q = a.q, b = blockIdx.x, z = blockIdx.y, tid = threadIdx.x, T = blockDim.x;
+    const int c0 = b * q;
+    const long o = (long)z * a.B + b;
+    double* L = sm;            // q*q
+    double* Lbar = L + q * q;  // q*q
+    double* Pm = Lbar + q * q; // q*q
+    double* Y = Pm + q * q;    // q*q
+    double* mubar = Y + q * q; // q
+    double* F = a.F + (long)z * a.strideF;
+    const double g = a.grad_acq[o];
+    const double lse = a.lse[o];
+    for (int idx = tid; idx < q * q; idx += T) L[idx] = a.Lq[o * q * q + idx];
+
+    // 1. d loss / d f, written in place
+    for (int s = tid; s < a.S; s += T) {
+        double f[BO_MAX_Q], li[BO_MAX_Q], gm[BO_MAX_Q];
+        const double bf = a.best_f[(long)z * a.Sp + s];
+        for (int j = 0; j < q; j++) {
+            f[j] = F[(long)s * a.ldn + c0 + j];
+            li[j] = log_fatplus(f[j] - bf, a.tau_relu);
+        }
+        const double m = fatmax_q(li, q, a.tau_max);
+        // logmeanexp over samples: softmax weight; +-inf maximum -> unit gradient on the infinite entries
+        const double w = isinf(lse) ? ((m == lse) ? 1.0 : 0.0) : exp(m - lse);
+        fatmax_q_grad(li, q, a.tau_max, gm);
+        for (int j = 0; j < q; j++) {
+            const double dli = isinf(li[j]) ? 0.0 : dlog_fatplus(f[j] - bf, a.tau_relu);
+            F[(long)s * a.ldn + c0 + j] = g * w * gm[j] * dli;
+        }
+    }
+    __syncthreads();  // block-scope visibility of the in-place writes
+
+    // 2. mu_bar[j] = sum_s df[s][j];  Lbar[j][k] = sum_s df[s][j] Zq[s][k]  (k <= j) -- fixed order
+    for (int idx = tid; idx < q + q * q; idx += T) {
+        if (idx < q) {
+            double s_ = 0.0;
+            for (int s = 0; s < a.S; s++) s_ += F[(long)s * a.ldn + c0 + idx];
+            mubar[idx] = s_;
+        } else {
+            const int j = (idx - q) / q, k = (idx - q) % q;
+            double s_ = 0.0;
+            if (k <= j)
+                for (int s = 0; s < a.S; s++) s_ += F[(long)s * a.ldn + c0 + j] * a.Zq[(long)s * q + k];
+            Lbar[j * q + k] = s_;
+        }
+    }
+    __syncthreads();
+    if (a.info[o] < 0) {  // forward failed: samples were not a function of the Schur block
+        for (int idx = tid; idx < q * q; idx += T) Lbar[idx] = 0.0;
+        __syncthreads();
+    }
+
+    // 3. Cholesky adjoint:  Sbar = sym( L^-T Phi(L^T Lbar) L^-1 ),  Phi = lower triangle with halved diagonal
+    for (int idx = tid; idx < q * q; idx += T) {
+        const int r = idx / q, cc = idx % q;
+        double s_ = 0.0;
+        if (cc <= r) {
+            for (int k = r; k < q; k++) s_ += L[k * q + r] * Lbar[k * q + cc];
+            if (cc == r) s_ *= 0.5;
+        }
+        Pm[idx] = s_;
+    }
+    __syncthreads();
+    const bool ok = (a.info[o] >= 0);
+    if (tid < q && ok) {  // solve L^T Y = Pm, one column per thread
+        const int cc = tid;
+        for (int i = q - 1; i >= 0; i--) {
+            double s_ = Pm[i * q + cc];
+            for (int k = i + 1; k < q; k++) s_ -= L[k * q + i] * Y[k * q + cc];
+            Y[i * q + cc] = s_ / L[i * q + i];
+        }
+    }
+    __syncthreads();
+    if (tid < q && ok) {  // solve W L = Y, one row per thread (result back into Pm)
+        const int r = tid;
+        for (int j = q - 1; j >= 0; j--) {
+            double s_ = Y[r * q + j];
+            for (int k = j + 1; k < q; k++) s_ -= Pm[r * q + k] * L[k * q + j];
+            Pm[r * q + j] = s_ / L[j * q + j];
+        }
+    }
+    __syncthreads();
+    double* Sbar = a.Sbar + o * q * q;
+    for (int idx = tid; idx < q * q; idx += T) {
+        const int r = idx / q, cc = idx % q;
+        const double v = ok ? 0.5 * (Pm[r * q + cc] + Pm[cc * q + r]) : 0.0;
+        Y[idx] = v;  // keep the symmetric adjoint in smem for step 4
+        Sbar[idx] = v;
+    }
+    if (tid < q) a.Vbar_mu[(long)z * a.strideVbar + c0 + tid] = a.y_std * mubar[tid];
+    __syncthreads();
+
+    // 4. gradient through k(X, X):  Schur = ys^2 (k(x_j,x_k) - ...) - ...   =>  kbar = ys^2 Sbar (symmetric)
+    const double ys2 = a.y_std * a.y_std;
+    const double os = a.h.outputscale ? a.h.outputscale[z] : 1.0;
+    const double* il = a.h.inv_ls + (long)z * a.h.d;
+    const int d = a.h.d;
+    double* gX = a.gradX + o * q * d;
+    for (int idx = tid; idx < q * d; idx += T) {
+        const int j = idx / d, t = idx % d;
+        double acc = 0.0;
+        for (int k = 0; k < q; k++) {
+            if (k == j) continue;
+            const double gf = kern_dfactor(a.h.kernel_id, pair_r2(a.X, d, il, c0 + j, c0 + k), os);
+            acc += 2.0 * ys2 * Y[j * q + k] * (-gf) * (a.X[(long)(c0 + j) * d + t] - a.X[(long)(c0 + k) * d + t]) *
+                   il[t] * il[t];
+        }
+        gX[idx] = acc;
+    }
+}
+size_t cand_bwd_smem_bytes(int q) { return sizeof(double) * (size_t)(4 * q * q + q); }
+
+__global__ void colblock_update_kernel(double* Y, long strideY, const double* Xm, long strideX, const double* Tm,
+                                       int rows, int B, int q, long ldn, double coef) {
+    extern __shared__ __align__(16) double st[];  // q*q block of T
+    const int b = blockIdx.x, z = blockIdx.z;
+    const double* T = Tm + ((long)z * B + b) * q * q;
+    for (int i = threadIdx.x; i < q * q; i += blockDim.x) st[i] = T[i];
+    __syncthreads();
+    const int c0 = b * q;
+    const int rows_per = (rows + gridDim.y - 1) / gridDim.y;
+    const int r_lo = blockIdx.y * rows_per, r_hi = min(rows, r_lo + rows_per);
+    double* Yz = Y + (long)z * strideY;
+    const double* Xz = Xm + (long)z * strideX;
+    for (int idx = threadIdx.x; idx < (r_hi - r_lo) * q; idx += blockDim.x) {
+        const int i = r_lo + idx / q, j = idx % q;
+        double s = 0.0;
+        for (int k = 0; k < q; k++) s += Xz[(long)i * ldn + c0 + k] * st[k * q + j];
+        Yz[(long)i * ldn + c0 + j] += coef * s;
+    }
+}
+
+// gradX[z][b][j][t] += scale * sum_i Kbar[i][c] * g(r_ic) * (x_i[t] - xc[t]) / l_t^2
+__global__ void __launch_bounds__(CAND_THREADS) kgrad_kernel(BoKernelHyper h, const double* Xpts, int npts,
+                                                             const double* Kbar, long strideK, long ldn,
+                                                             const double* X, int B, int q, double scale,
+                                                             double* gradX) {
+    extern __shared__ __align__(16) double sm[];
+    const int b = blockIdx.x, z = blockIdx.y, tid = threadIdx.x, T = blockDim.x;
+    const int d = h.d, c0 = b * q;
+    constexpr int R = 128;
+    double* w = sm;              // R*q
+    double* xc = w + R * q;      // q*d candidate points
+    double* il2 = xc + q * d;    // d
+    double* part = il2 + d;      // ngroups*q*d
+    const double* il = h.inv_ls + (long)z * d;
+    const double os = h.outputscale ? h.outputscale[z] : 1.0;
+    const double* Kz = Kbar + (long)z * strideK;
+    for (int i = tid; i < q * d; i += T) xc[i] = X[(long)c0 * d + i];
+    for (int i = tid; i < d; i += T) il2[i] = il[i] * il[i];
+    const int QD = q * d;
+    const int ngroups = (T / QD) > 1 ? (T / QD) : 1;
+    for (int i = tid; i < ngroups * QD; i += T) part[i] = 0.0;
+    __syncthreads();
+    for (int r0 = 0; r0 < npts; r0 += R) {
+        const int pr = (npts - r0 < R) ? npts - r0 : R;
+        for (int idx = tid; idx < pr * q; idx += T) {
+            const int r = idx / q, j = idx % q;
+            const double* xi = Xpts + (long)(r0 + r) * d;
+            double r2 = 0.0;
+            for (int t = 0; t < d; t++) {
+                const double v = (xi[t] - xc[j * d + t]) * il[t];
+                r2 += v * v;
+            }
+            w[idx] = Kz[(long)(r0 + r) * ldn + c0 + j] * kern_dfactor(h.kernel_id, r2, os);
+        }
+        __syncthreads();
+        for (int slot = tid; slot < ngroups * QD; slot += T) {
+            const int grp = slot / QD, jt = slot % QD;
+            const int j = jt / d, t = jt % d;
+            double acc = 0.0;
+            for (int r = grp; r < pr; r += ngroups) acc += w[r * q + j] * (Xpts[(long)(r0 + r) * d + t] - xc[jt]);
+            part[slot] += acc;
+        }
+        __syncthreads();
+    }
+    double* gX = gradX + ((long)z * B + b) * QD;
+    for (int jt = tid; jt < QD; jt += T) {
+        double s = 0.0;
+        for (int grp = 0; grp < ngroups; grp++) s += part[grp * QD + jt];
+        gX[jt] += scale * s * il2[jt % d];
+    }
+}
+size_t kgrad_smem_bytes(int q, int d, int T) {
+    const int QD = q * d;
+    const int ngroups = (T / QD) > 1 ? (T / QD) : 1;
+    return sizeof(double) * ((size_t)128 * q + QD + d + (size_t)ngroups * QD);
+}
+
+}  // namespace
+
+namespace {
+
+// joint posterior blocks of one t-batch element from V = [inv(L) K(X_tr, X); alpha . K]
+__global__ void __launch_bounds__(CAND_THREADS) cand_posterior_kernel(const BoCandArgs a, double* mean, double* cov) {
+    extern __shared__ __align__(16) double sm[];
+    const int q = a.q, b = blockIdx.x, z = blockIdx.y, tid = threadIdx.x, T = blockDim.x;
+    const CandSmem c = carve(sm, q, T, 0);
+    const int c0 = b * q;
+    const double* V = a.V + (long)z * a.strideV;
+    gram_block(V, a.ldn, a.n, c0, q, c.panel, c.part, c.GV);
+    const double ys2 = a.y_std * a.y_std;
+    const double os = a.h.outputscale ? a.h.outputscale[z] : 1.0;
+    const double* il = a.h.inv_ls + (long)z * a.h.d;
+    const long o = (long)z * a.B + b;
+    for (int idx = tid; idx < q * q; idx += T) {
+        const int j = idx / q, k = idx % q;
+        const double kv = kern_value(a.h.kernel_id, pair_r2(a.X, a.h.d, il, c0 + j, c0 + k), os);
+        cov[o * q * q + idx] = ys2 * (kv - c.GV[idx]);
+    }
+    if (tid < q) mean[o * q + tid] = a.y_mean + a.y_std * (a.mean_const[z] + V[(long)a.n * a.ldn + c0 + tid]);
+}
+
+__global__ void col_mean_var_kernel(const double* V, long strideV, long ldn, int n, long Nc, double y_mean,
+                                    double y_std, const double* mean_const, const double* outputscale, double* mean,
+                                    double* var) {
+    const int z = blockIdx.y;
+    const long c = blockIdx.x * (long)blockDim.x + threadIdx.x;
+    if (c >= Nc) return;
+    const double* Vz = V + (long)z * strideV;
+    double s0 = 0.0, s1 = 0.0, s2 = 0.0, s3 = 0.0;  // 4 independent chains, fixed order
+    int i = 0;
+    for (; i + 3 < n; i += 4) {
+        const double v0 = Vz[(long)i * ldn + c], v1 = Vz[(long)(i + 1) * ldn + c];
+        const double v2 = Vz[(long)(i + 2) * ldn + c], v3 = Vz[(long)(i + 3) * ldn + c];
+        s0 += v0 * v0; s1 += v1 * v1; s2 += v2 * v2; s3 += v3 * v3;
+    }
+    for (; i < n; i++) { const double v = Vz[(long)i * ldn + c]; s0 += v * v; }
+    const double os = outputscale ? outputscale[z] : 1.0;
+    mean[(long)z * Nc + c] = y_mean + y_std * (mean_const[z] + Vz[(long)n * ldn + c]);
+    var[(long)z * Nc + c] = y_std * y_std * (os - ((s0 + s1) + (s2 + s3)));
+}
+
+__global__ void col_max_kernel(const double* Fb, long strideF, long ldf, const double* mean_b, long strideMb,
+                               int rows, int cols, double* out, long strideOut) {
+    const int z = blockIdx.y;
+    const int s = blockIdx.x * blockDim.x + threadIdx.x;
+    if (s >= cols) return;
+    const double* Fz = Fb + (long)z * strideF;
+    const double* mb = mean_b + (long)z * strideMb;
+    double m = -INFINITY;
+    for (int i = 0; i < rows; i++) m = fmax(m, mb[i] + Fz[(long)i * ldf + s]);
+    out[(long)z * strideOut + s] = m;
+}
+
+// per-model first-occurrence argmax of mean + sqrt(var) * z  (z may be null -> argmax of mean)
+__global__ void __launch_bounds__(1024) ts_argmax_kernel(long Nc, const double* mean, const double* var,
+                                                         const double* zn, double* out_val, long long* out_idx) {
+    __shared__ double sv[32];
+    __shared__ long long si[32];
+    const int m = blockIdx.x;
+    double best = -INFINITY;
+    long long bi = 0x7fffffffffffffffLL;
+    for (long c = threadIdx.x; c < Nc; c += blockDim.x) {
+        double v = mean[(long)m * Nc + c];
+        if (zn) v += sqrt(fmax(var[(long)m * Nc + c], 0.0)) * zn[(long)m * Nc + c];
+        if (v > best || (v == best && c < bi)) { best = v; bi = c; }
+    }
+    for (int o = 16; o > 0; o >>= 1) {
+        const double ov = __shfl_xor_sync(0xffffffffu, best, o);
+        const long long oi = __shfl_xor_sync(0xffffffffu, bi, o);
+        if (ov > best || (ov == best && oi < bi)) { best = ov; bi = oi; }
+    }
+    const int w = threadIdx.x >> 5, l = threadIdx.x & 31;
+    if (l == 0) { sv[w] = best; si[w] = bi; }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        for (int i = 1; i < (int)(blockDim.x >> 5); i++)
+            if (sv[i] > best || (sv[i] == best && si[i] < bi)) { best = sv[i]; bi = si[i]; }
+        out_val[m] = best;
+        out_idx[m] = bi;
+    }
+}
+
+}  // namespace
+
+#define BO_LAUNCH_CHECK()        \
+    do {                         \
+        g_bo_launch_count++;     \
+        BO_CUDA_TRY(cudaGetLastError()); \
+    } while (0)
+
+int bo_aug_rows(const BoKernelHyper& h, const double* X, long npts, double* out, long Kp, long strideOut,
+                cudaStream_t stream) {
+    if (npts <= 0) return BO_OK;
+    dim3 grid((unsigned)((npts + 127) / 128), h.M);
+    aug_rows_kernel<<<grid, 128, 0, stream>>>(h, X, npts, out, Kp, strideOut);
+    BO_LAUNCH_CHECK();
+    return BO_OK;
+}
+int bo_aug_cols(const BoKernelHyper& h, const double* X, long npts, double* out, long Kp, long ldo, long strideOut,
+                cudaStream_t stream) {
+    if (npts <= 0) return BO_OK;
+    dim3 grid((unsigned)((ldo + 127) / 128), h.M);
+    aug_cols_kernel<<<grid, 128, 0, stream>>>(h, X, npts, out, Kp, ldo, strideOut);
+    BO_LAUNCH_CHECK();
+    return BO_OK;
+}
+
+static int set_smem_limit(const void* fn, size_t bytes) {
+    if (bytes > 48 * 1024) BO_CUDA_TRY(cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes));
+    return BO_OK;
+}
+
+int bo_cand_fwd(const BoCandArgs& a, cudaStream_t stream) {
+    if (a.q < 1 || a.q > BO_MAX_Q || a.h.d > BO_MAX_D) return BO_ERR_UNSUPPORTED;
+    if (a.B <= 0) return BO_OK;
+    const size_t smem = cand_smem_bytes(a.q, CAND_THREADS, a.S);
+    if (smem > 200 * 1024) return BO_ERR_UNSUPPORTED;
+    BO_TRY(set_smem_limit((const void*)cand_fwd_kernel, smem));
+    dim3 grid(a.B, a.h.M);
+    cand_fwd_kernel<<<grid, CAND_THREADS, smem, stream>>>(a);
+    BO_LAUNCH_CHECK();
+    return BO_OK;
+}
+int bo_cand_bwd(const BoCandArgs& a, cudaStream_t stream) {
+    if (a.q < 1 || a.q > BO_MAX_Q || a.h.d > BO_MAX_D) return BO_ERR_UNSUPPORTED;
+    if (a.B <= 0) return BO_OK;
+    dim3 grid(a.B, a.h.M);
+    cand_bwd_kernel<<<grid, CAND_THREADS, cand_bwd_smem_bytes(a.q), stream>>>(a);
+    BO_LAUNCH_CHECK();
+    return BO_OK;
+}
+int bo_colblock_update(double* Y, long strideY, const double* Xm, long strideX, const double* T, int rows, int B,
+                       int q, int M, long ldn, double coef, cudaStream_t stream) {
+    if (rows <= 0 || B <= 0) return BO_OK;
+    int ysplit = (rows + 255) / 256;  // ~256 rows per CTA
+    if (ysplit > 65535) ysplit = 65535;
+    dim3 grid(B, ysplit, M);
+    colblock_update_kernel<<<grid, 256, sizeof(double) * q * q, stream>>>(Y, strideY, Xm, strideX, T, rows, B, q, ldn,
+                                                                         coef);
+    BO_LAUNCH_CHECK();
+    return BO_OK;
+}
+int bo_kgrad(const BoKernelHyper& h, const double* Xpts, int npts, const double* Kbar, long strideK, long ldn,
+             const double* X, int B, int q, double scale, double* gradX, cudaStream_t stream) {
+    if (B <= 0 || npts <= 0) return BO_OK;
+    const size_t smem = kgrad_smem_bytes(q, h.d, CAND_THREADS);
+    if (smem > 200 * 1024) return BO_ERR_UNSUPPORTED;
+    BO_TRY(set_smem_limit((const void*)kgrad_kernel, smem));
+    dim3 grid(B, h.M);
+    kgrad_kernel<<<grid, CAND_THREADS, smem, stream>>>(h, Xpts, npts, Kbar, strideK, ldn, X, B, q, scale, gradX);
+    BO_LAUNCH_CHECK();
+    return BO_OK;
+}
+int bo_cand_posterior(const BoCandArgs& a, double* mean, double* cov, cudaStream_t stream) {
+    if (a.q < 1 || a.q > BO_MAX_Q) return BO_ERR_UNSUPPORTED;
+    if (a.B <= 0) return BO_OK;
+    const size_t smem = cand_smem_bytes(a.q, CAND_THREADS, 0);
+    BO_TRY(set_smem_limit((const void*)cand_posterior_kernel, smem));
+    dim3 grid(a.B, a.h.M);
+    cand_posterior_kernel<<<grid, CAND_THREADS, smem, stream>>>(a, mean, cov);
+    BO_LAUNCH_CHECK();
+    return BO_OK;
+}
+int bo_col_mean_var(const double* V, long strideV, long ldn, int n, long Nc, int M, double y_mean, double y_std,
+                    const double* mean_const, const double* outputscale, double* mean, double* var,
+                    cudaStream_t stream) {
+    if (Nc <= 0) return BO_OK;
+    dim3 grid((unsigned)((Nc + 127) / 128), M);
+    col_mean_var_kernel<<<grid, 128, 0, stream>>>(V, strideV, ldn, n, Nc, y_mean, y_std, mean_const, outputscale, mean,
+                                                  var);
+    BO_LAUNCH_CHECK();
+    return BO_OK;
+}
+int bo_col_max(const double* Fb, long strideF, long ldf, const double* mean_b, long strideMb, int rows, int cols,
+               int M, double* out, long strideOut, cudaStream_t stream) {
+    dim3 grid((cols + 127) / 128, M);
+    col_max_kernel<<<grid, 128, 0, stream>>>(Fb, strideF, ldf, mean_b, strideMb, rows, cols, out, strideOut);
+    BO_LAUNCH_CHECK();
+    return BO_OK;
+}
+int bo_ts_argmax_launch(int M, long Nc, const double* mean, const double* var, const double* z, double* out_val,
+                        long long* out_idx, cudaStream_t stream) {
+    if (M <= 0 || Nc <= 0) return BO_ERR_INVALID;
+    ts_argmax_kernel<<<M, 1024, 0, stream>>>(Nc, mean, var, z, out_val, out_idx);
+    BO_LAUNCH_CHECK();
+    return BO_OK;
+}

@@ -1,0 +1,74 @@
+// Shared declarations for the botorch_b200 CUDA library (sm_100a only).
+#pragma once
+#include <cuda_runtime.h>
+#include <cstdint>
+#include <cstdio>
+
+#define BO_OK 0
+#define BO_ERR_INVALID 1
+#define BO_ERR_CUDA 2
+#define BO_ERR_WORKSPACE 3
+#define BO_ERR_UNSUPPORTED 4
+
+#define BO_MAX_Q 32   // largest q-batch (incl. pending points) the per-candidate kernels accept
+#define BO_MAX_D 128  // largest input dimension
+
+#define BO_KERNEL_RBF 0
+#define BO_KERNEL_MATERN52 1
+
+#define BO_CUDA_TRY(expr)                                                                    \
+    do {                                                                                     \
+        cudaError_t _e = (expr);                                                             \
+        if (_e != cudaSuccess) {                                                             \
+            bo_set_last_cuda_error(_e, __FILE__, __LINE__);                                  \
+            return BO_ERR_CUDA;                                                              \
+        }                                                                                    \
+    } while (0)
+
+#define BO_TRY(expr)                 \
+    do {                             \
+        int _r = (expr);             \
+        if (_r != BO_OK) return _r;  \
+    } while (0)
+
+void bo_set_last_cuda_error(cudaError_t e, const char* file, int line);
+
+static inline long bo_round_up(long x, long m) { return (x + m - 1) / m * m; }
+
+// ---------------------------------------------------------------------------------------------
+// Batched FP64 GEMM on DMMA (gemm.cu).   C[z] = epilogue( A[z] (M x K) * B[z] (K x N) )
+// All matrices row-major; leading dimensions must be even and base pointers 16-byte aligned.
+// ---------------------------------------------------------------------------------------------
+enum BoEpilogue : int {
+    BO_EPI_LINEAR = 0,  // C = alpha*acc + beta*D
+    BO_EPI_RBF = 1,     // acc is a squared distance: C = os[z]*exp(-0.5*max(acc,0))   (+ diag options)
+    BO_EPI_MATERN52 = 2 // C = os[z]*(1+sqrt5 r+5/3 r^2) exp(-sqrt5 r), r = sqrt(max(acc,1e-30))
+};
+
+enum BoTri : int {
+    BO_TRI_NONE = 0,
+    BO_TRI_A_LOWER = 1,  // A[m][k] == 0 for k > m        -> k-loop stops at the row tile's last row
+    BO_TRI_A_UPPER = 2,  // A[m][k] == 0 for k < m        -> k-loop starts at the row tile's first row
+    BO_TRI_B_LOWER = 3   // B[k][n] == 0 for k < n        -> k-loop starts at the column tile's first col
+};
+
+struct BoGemm {
+    const double* A; long lda; long strideA;
+    const double* B; long ldb; long strideB;
+    double* C; long ldc; long strideC;
+    const double* D; long ldd; long strideD;   // optional addend (LINEAR only), may alias C
+    double* CT; long ldct; long strideCT;      // optional transposed copy of C
+    double alpha, beta;
+    int M, N, K, batch;
+    int tri;          // BoTri
+    int out_lower;    // 1: skip output tiles strictly above the block diagonal (syrk-style)
+    int epi;          // BoEpilogue
+    const double* os;        // [batch] outputscale (kernel epilogues), may be null (=1)
+    const double* diag_add;  // [batch] value added where row==col (noise), may be null
+    int diag_exact;          // 1: squared distance forced to 0 where row==col (x1_eq_x2)
+    int a_bcast, b_bcast;    // unused (strides of 0 already broadcast); kept for clarity
+};
+
+int bo_gemm_launch(const BoGemm& g, cudaStream_t stream);
+// number of kernels launched by this library since the last reset (bench.py's gpu_launches claim)
+extern long g_bo_launch_count;

@@ -1,0 +1,218 @@
+// Batched FP64 GEMM for sm_100a on the DMMA.8x8x4 tensor path (mma.sync m8n8k4 f64 -- the only
+// FP64 tensor-core instruction Blackwell has; tcgen05 has no f64 kind), cp.async multi-stage
+// shared-memory pipeline, triangular k-range skipping and fused epilogues (linear combine,
+// RBF / Matern-5/2 covariance from an augmented squared-distance contraction).
+//
+// Replaces, on the qLogNEI hot path, the cuBLAS/MKL calls behind
+//   gpytorch Kernel.covar_dist / sq_dist              (reference call site models/gpytorch.py:446)
+//   gpytorch exact_predictive_mean / _covar           (fast_pred_var, models/utils/assorted.py:292)
+//   torch.linalg.solve_triangular in low_rank.py:131  (as a multiply with the cached inverse factor)
+//   new_Lq.matmul(base_samples) in low_rank.py:156
+#include "common.cuh"
+
+long g_bo_launch_count = 0;
+
+namespace {
+
+__device__ __forceinline__ void cp_async16(void* smem, const void* gmem, int src_bytes) {
+    unsigned s = (unsigned)__cvta_generic_to_shared(smem);
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;\n" ::"r"(s), "l"(gmem), "r"(src_bytes));
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;\n" ::); }
+template <int N>
+__device__ __forceinline__ void cp_async_wait() {
+    asm volatile("cp.async.wait_group %0;\n" ::"n"(N));
+}
+__device__ __forceinline__ void dmma884(double& c0, double& c1, double a, double b) {
+    asm volatile("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%2}, {%3}, {%0,%1};\n"
+                 : "+d"(c0), "+d"(c1)
+                 : "d"(a), "d"(b));
+}
+
+template <int BM_, int BN_, int BK_, int WM_, int WN_, int STAGES_>
+struct Cfg {
+    static constexpr int BM = BM_, BN = BN_, BK = BK_, WM = WM_, WN = WN_, STAGES = STAGES_;
+    static constexpr int WARPS_M = BM / WM, WARPS_N = BN / WN;
+    static constexpr int THREADS = WARPS_M * WARPS_N * 32;
+    static constexpr int LDA_S = BK + 4;  // row pitch == 4 (mod 16) doubles: conflict-free LDS.64 fragments
+    static constexpr int LDB_S = BN + 4;
+    static constexpr int A_STAGE = BM * LDA_S, B_STAGE = BK * LDB_S;
+    static constexpr size_t SMEM = (size_t)STAGES * (A_STAGE + B_STAGE) * sizeof(double);
+    static_assert(BK % 4 == 0 && (BK + 4) % 16 == 4, "BK");
+    static_assert(BN % 16 == 0, "BN");
+};
+
+__device__ __forceinline__ double epilogue_value(const BoGemm& p, int z, double acc, int row, int col) {
+    if (p.epi == BO_EPI_LINEAR) {
+        double v = p.alpha * acc;
+        if (p.D != nullptr) v += p.beta * p.D[(long)z * p.strideD + (long)row * p.ldd + col];
+        return v;
+    }
+    double r2 = acc > 0.0 ? acc : 0.0;
+    const bool on_diag = (row == col);
+    if (p.diag_exact && on_diag) r2 = 0.0;
+    const double os = p.os ? p.os[z] : 1.0;
+    double v;
+    if (p.epi == BO_EPI_RBF) {
+        v = os * exp(-0.5 * r2);
+    } else {
+        const double sqrt5 = 2.23606797749978969641;
+        double r = sqrt(r2 > 1e-30 ? r2 : 1e-30);
+        v = os * ((sqrt5 * r + 1.0) + (5.0 / 3.0) * (r * r)) * exp(-sqrt5 * r);
+    }
+    if (p.diag_add && on_diag) v += p.diag_add[z];
+    return v;
+}
+
+template <class C>
+__global__ void __launch_bounds__(C::THREADS) dgemm_dmma_kernel(const BoGemm p) {
+    extern __shared__ __align__(16) double smem[];
+    double* As = smem;
+    double* Bs = smem + (size_t)C::STAGES * C::A_STAGE;
+
+    const int tid = threadIdx.x;
+    const int warp = tid >> 5, lane = tid & 31;
+    const int g = lane >> 2, t = lane & 3;
+    const int wm0 = (warp / C::WARPS_N) * C::WM;
+    const int wn0 = (warp % C::WARPS_N) * C::WN;
+    const int z = blockIdx.z;
+    // heavy (large-m) row tiles first when A is lower triangular: better tail balance
+    const int mt = (p.tri == BO_TRI_A_LOWER) ? (gridDim.x - 1 - blockIdx.x) : blockIdx.x;
+    const int m0 = mt * C::BM;
+    const int n0 = blockIdx.y * C::BN;
+    if (p.out_lower && n0 > m0 + C::BM - 1) return;
+
+    const double* __restrict__ A = p.A + (long)z * p.strideA;
+    const double* __restrict__ B = p.B + (long)z * p.strideB;
+
+    int kb = 0, ke = p.K;
+    if (p.tri == BO_TRI_A_LOWER) ke = min(p.K, m0 + C::BM);
+    else if (p.tri == BO_TRI_A_UPPER) kb = (m0 / C::BK) * C::BK;
+    else if (p.tri == BO_TRI_B_LOWER) kb = (n0 / C::BK) * C::BK;
+    const int ntiles = ke > kb ? (ke - kb + C::BK - 1) / C::BK : 0;
+
+    auto load_tile = [&](int tile, int stage) {
+        const int k0 = kb + tile * C::BK;
+        double* as = As + (size_t)stage * C::A_STAGE;
+        double* bs = Bs + (size_t)stage * C::B_STAGE;
+        constexpr int ACH = C::BK / 2;  // 16-byte chunks per A row
+#pragma unroll
+        for (int id = tid; id < C::BM * ACH; id += C::THREADS) {
+            const int r = id / ACH, cc = id % ACH;
+            const int row = m0 + r, k = k0 + 2 * cc;
+            int bytes = 0;
+            if (row < p.M) bytes = max(0, min(16, (ke - k) * 8));
+            const double* src = bytes > 0 ? (A + (long)row * p.lda + k) : A;
+            cp_async16(as + r * C::LDA_S + 2 * cc, src, bytes);
+        }
+        constexpr int BCH = C::BN / 2;
+#pragma unroll
+        for (int id = tid; id < C::BK * BCH; id += C::THREADS) {
+            const int r = id / BCH, cc = id % BCH;
+            const int k = k0 + r, col = n0 + 2 * cc;
+            int bytes = 0;
+            if (k < ke) bytes = max(0, min(16, (p.N - col) * 8));
+            const double* src = bytes > 0 ? (B + (long)k * p.ldb + col) : B;
+            cp_async16(bs + r * C::LDB_S + 2 * cc, src, bytes);
+        }
+    };
+
+    constexpr int TM = C::WM / 8, TN = C::WN / 8;
+    double acc[TM][TN][2];
+#pragma unroll
+    for (int i = 0; i < TM; i++)
+#pragma unroll
+        for (int j = 0; j < TN; j++) acc[i][j][0] = acc[i][j][1] = 0.0;
+
+#pragma unroll
+    for (int s = 0; s < C::STAGES - 1; s++) {
+        if (s < ntiles) load_tile(s, s);
+        cp_async_commit();
+    }
+
+    for (int kt = 0; kt < ntiles; kt++) {
+        cp_async_wait<C::STAGES - 2>();
+        __syncthreads();
+        {
+            const int nxt = kt + C::STAGES - 1;
+            if (nxt < ntiles) load_tile(nxt, nxt % C::STAGES);
+            cp_async_commit();
+        }
+        const double* as = As + (size_t)(kt % C::STAGES) * C::A_STAGE + (wm0 + g) * C::LDA_S + t;
+        const double* bs = Bs + (size_t)(kt % C::STAGES) * C::B_STAGE + t * C::LDB_S + wn0 + g;
+#pragma unroll
+        for (int kk = 0; kk < C::BK; kk += 4) {
+            double a[TM], b[TN];
+#pragma unroll
+            for (int i = 0; i < TM; i++) a[i] = as[i * 8 * C::LDA_S + kk];
+#pragma unroll
+            for (int j = 0; j < TN; j++) b[j] = bs[kk * C::LDB_S + j * 8];
+#pragma unroll
+            for (int i = 0; i < TM; i++)
+#pragma unroll
+                for (int j = 0; j < TN; j++) dmma884(acc[i][j][0], acc[i][j][1], a[i], b[j]);
+        }
+    }
+    cp_async_wait<0>();
+
+    double* __restrict__ Cz = p.C + (long)z * p.strideC;
+    double* __restrict__ CTz = p.CT ? p.CT + (long)z * p.strideCT : nullptr;
+#pragma unroll
+    for (int i = 0; i < TM; i++) {
+        const int row = m0 + wm0 + i * 8 + g;
+        if (row >= p.M) continue;
+#pragma unroll
+        for (int j = 0; j < TN; j++) {
+            const int col = n0 + wn0 + j * 8 + 2 * t;
+            if (col >= p.N) continue;
+            const double v0 = epilogue_value(p, z, acc[i][j][0], row, col);
+            if (col + 1 < p.N) {
+                const double v1 = epilogue_value(p, z, acc[i][j][1], row, col + 1);
+                *reinterpret_cast<double2*>(Cz + (long)row * p.ldc + col) = make_double2(v0, v1);
+                if (CTz) {
+                    CTz[(long)col * p.ldct + row] = v0;
+                    CTz[(long)(col + 1) * p.ldct + row] = v1;
+                }
+            } else {
+                Cz[(long)row * p.ldc + col] = v0;
+                if (CTz) CTz[(long)col * p.ldct + row] = v0;
+            }
+        }
+    }
+}
+
+using CfgBig = Cfg<128, 128, 16, 64, 32, 4>;
+using CfgMid = Cfg<64, 64, 16, 32, 32, 4>;
+using CfgSmall = Cfg<32, 32, 16, 16, 16, 3>;
+
+template <class C>
+int launch_cfg(const BoGemm& g, cudaStream_t stream) {
+    static bool attr_set = false;
+    if (!attr_set) {
+        BO_CUDA_TRY(cudaFuncSetAttribute(dgemm_dmma_kernel<C>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                         (int)C::SMEM));
+        attr_set = true;
+    }
+    dim3 grid((g.M + C::BM - 1) / C::BM, (g.N + C::BN - 1) / C::BN, g.batch);
+    if (grid.y > 65535u || grid.z > 65535u) return BO_ERR_UNSUPPORTED;
+    dgemm_dmma_kernel<C><<<grid, C::THREADS, C::SMEM, stream>>>(g);
+    g_bo_launch_count++;
+    BO_CUDA_TRY(cudaGetLastError());
+    return BO_OK;
+}
+
+}  // namespace
+
+int bo_gemm_launch(const BoGemm& g, cudaStream_t stream) {
+    if (g.M <= 0 || g.N <= 0 || g.batch <= 0) return BO_OK;
+    if ((g.lda & 1) || (g.ldb & 1) || (g.ldc & 1) || (g.D && (g.ldd & 1))) return BO_ERR_INVALID;
+    if ((reinterpret_cast<uintptr_t>(g.A) & 15) || (reinterpret_cast<uintptr_t>(g.B) & 15) ||
+        (reinterpret_cast<uintptr_t>(g.C) & 15))
+        return BO_ERR_INVALID;
+    if ((g.strideA & 1) || (g.strideB & 1) || (g.strideC & 1)) return BO_ERR_INVALID;
+    auto tiles = [&](int bm, int bn) { return (long)((g.M + bm - 1) / bm) * ((g.N + bn - 1) / bn) * g.batch; };
+    // Pick the largest tile that still fills the 148 SMs; small problems trade tile efficiency for occupancy.
+    if (tiles(128, 128) >= 120) return launch_cfg<CfgBig>(g, stream);
+    if (tiles(64, 64) >= 120 || (g.M >= 48 && g.N >= 48 && tiles(32, 32) > 2048)) return launch_cfg<CfgMid>(g, stream);
+    return launch_cfg<CfgSmall>(g, stream);
+}

@@ -1,0 +1,240 @@
+"""Device state of a fitted GP and of a qLogNEI baseline, driving libbotorch_b200 through its C ABI.
+
+Host-side logic only: buffer ownership, the psd_safe_cholesky retry schedule
+(linear_operator 0.5.2 semantics; botorch/__init__.py:47 sets 6 tries), warnings and errors.
+Every number is produced by the CUDA library.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import warnings
+from typing import Optional, Tuple
+
+import torch
+from torch import Tensor
+
+from . import _lib
+from ._lib import BoGP, BoNEI, check, kp, pad8, ptr
+from .exceptions import NanError, NotPSDError, NumericalWarning
+
+KERNEL_IDS = {"rbf": 0, "matern52": 1}
+CHOLESKY_MAX_TRIES = 6  # botorch/__init__.py:47
+CHOLESKY_JITTER = 1e-8  # linear_operator settings.cholesky_jitter for float64
+
+
+def _f64(t, device) -> Tensor:
+    return torch.as_tensor(t, dtype=torch.float64, device=device).contiguous()
+
+
+def _retry_with_jitter(run, M: int, device, what: str) -> Tensor:
+    """psd_safe_cholesky: plain attempt, then jitter 1e-8*10**i on the members that failed."""
+    jitter = torch.zeros(M, dtype=torch.float64, device=device)
+    info = run(None)
+    if not bool(info.any()):
+        return jitter
+    prev_fail = info > 0
+    for i in range(CHOLESKY_MAX_TRIES):
+        new = CHOLESKY_JITTER * (10**i)
+        jitter = torch.where(prev_fail, torch.full_like(jitter, new), jitter)
+        warnings.warn(f"{what} not p.d., added jitter of {new:.1e} to the diagonal", NumericalWarning)
+        info = run(jitter)
+        prev_fail = info > 0
+        if not bool(prev_fail.any()):
+            return jitter
+    raise NotPSDError(f"{what} not positive definite after repeatedly adding jitter up to {new:.1e}.")
+
+
+class GPState:
+    """Training-set factors of an exact GP (one or M batched hyperparameter sets) resident in HBM."""
+
+    def __init__(
+        self,
+        train_X: Tensor,
+        targets: Tensor,
+        kernel: str,
+        lengthscale: Tensor,
+        noise: Tensor,
+        mean: Tensor,
+        outputscale: Optional[Tensor] = None,
+        y_mean: float = 0.0,
+        y_std: float = 1.0,
+    ) -> None:
+        dev = train_X.device
+        self.device = dev
+        self.ctx = _lib.ctx(dev)
+        self.kernel = kernel
+        self.train_X = _f64(train_X, dev)
+        self.n, self.d = self.train_X.shape
+        ls = _f64(lengthscale, dev).reshape(-1, self.d)
+        self.M = ls.shape[0]
+        self.batched = _f64(lengthscale, dev).dim() > 1
+        self.inv_ls = (1.0 / ls).contiguous()
+        self.noise = _f64(noise, dev).reshape(-1).expand(self.M).contiguous()
+        self.mean = _f64(mean, dev).reshape(-1).expand(self.M).contiguous()
+        self.outputscale = None if outputscale is None else _f64(outputscale, dev).reshape(-1).expand(self.M).contiguous()
+        self.targets = _f64(targets, dev).reshape(-1)
+        self.center = self.train_X.mean(dim=0).contiguous()
+        self.y_mean, self.y_std = float(y_mean), float(y_std)
+        for name, t in (("train_X", self.train_X), ("targets", self.targets), ("lengthscale", ls), ("noise", self.noise)):
+            if bool(torch.isnan(t).any()):
+                raise NanError(f"{name} contains NaN")
+        n, M, d = self.n, self.M, self.d
+        self.np_, self.n1p, self.Kp = pad8(n), pad8(n + 1), kp(d)
+        z = lambda *s: torch.zeros(*s, dtype=torch.float64, device=dev)
+        self.aug_train = z(M, n, self.Kp)
+        self.linv_aug = z(M, n + 1, self.np_)
+        self.linv_aug_t = z(M, n, self.n1p)
+        self.chol = z(M, n, self.np_)
+        self.info = torch.zeros(M, dtype=torch.int32, device=dev)
+        self.c = BoGP(
+            kernel_id=KERNEL_IDS[kernel], n=n, d=d, M=M, y_mean=self.y_mean, y_std=self.y_std,
+            train_X=ptr(self.train_X), center=ptr(self.center), inv_ls=ptr(self.inv_ls),
+            outputscale=ptr(self.outputscale), noise=ptr(self.noise), mean=ptr(self.mean),
+            targets=ptr(self.targets), jitter=None,
+            aug_train=ptr(self.aug_train), linv_aug=ptr(self.linv_aug), linv_aug_t=ptr(self.linv_aug_t),
+            chol=ptr(self.chol),
+        )  # fmt: skip
+        lib = _lib.lib()
+        work = _lib.workspace(lib.bo_gp_setup_workspace_bytes(C.byref(self.c)), dev)
+
+        def run(jitter: Optional[Tensor]) -> Tensor:
+            self._jitter = jitter
+            self.c.jitter = ptr(jitter)
+            check(lib.bo_gp_setup(self.ctx, C.byref(self.c), work.data_ptr(), work.numel(), ptr(self.info),
+                                  _lib.stream_ptr(dev)))  # fmt: skip
+            return self.info.clone()
+
+        self.jitter = _retry_with_jitter(run, M, dev, "K + noise*I")
+
+    # -- factors exposed for tests / callers ------------------------------------------------------
+    @property
+    def L(self) -> Tensor:
+        return self.chol[:, :, : self.n]
+
+    @property
+    def L_inv(self) -> Tensor:
+        return self.linv_aug[:, : self.n, : self.n]
+
+    @property
+    def alpha(self) -> Tensor:
+        return self.linv_aug[:, self.n, : self.n]
+
+    # -- posterior --------------------------------------------------------------------------------
+    def posterior_joint(self, X: Tensor) -> Tuple[Tensor, Tensor]:
+        """X: B x q x d -> mean [M x B x q], cov [M x B x q x q] on the outcome scale."""
+        X = _f64(X, self.device)
+        B, q, _ = X.shape
+        lib = _lib.lib()
+        mean = torch.empty(self.M, B, q, dtype=torch.float64, device=self.device)
+        cov = torch.empty(self.M, B, q, q, dtype=torch.float64, device=self.device)
+        work = _lib.workspace(lib.bo_posterior_workspace_bytes(C.byref(self.c), B * q), self.device)
+        check(lib.bo_posterior_joint(self.ctx, C.byref(self.c), B, q, ptr(X), ptr(mean), ptr(cov), work.data_ptr(),
+                                     work.numel(), _lib.stream_ptr(self.device)))  # fmt: skip
+        return mean, cov
+
+    def posterior_mean_var(self, Xc: Tensor, work: Optional[Tensor] = None) -> Tuple[Tensor, Tensor]:
+        """Xc: Nc x d -> marginal mean, var [M x Nc]."""
+        Xc = _f64(Xc, self.device)
+        Nc = Xc.shape[0]
+        lib = _lib.lib()
+        mean = torch.empty(self.M, Nc, dtype=torch.float64, device=self.device)
+        var = torch.empty(self.M, Nc, dtype=torch.float64, device=self.device)
+        if work is None:
+            work = _lib.workspace(lib.bo_posterior_workspace_bytes(C.byref(self.c), Nc), self.device)
+        check(lib.bo_posterior_mean_var(self.ctx, C.byref(self.c), Nc, ptr(Xc), ptr(mean), ptr(var), work.data_ptr(),
+                                        work.numel(), _lib.stream_ptr(self.device)))  # fmt: skip
+        return mean, var
+
+    def posterior_workspace(self, Nc: int) -> Tensor:
+        return _lib.workspace(_lib.lib().bo_posterior_workspace_bytes(C.byref(self.c), Nc), self.device)
+
+    def kernel_matrix(self, Xc: Tensor) -> Tensor:
+        """K(train_X, Xc) per model: [M x n x Nc] (parity-test hook)."""
+        Xc = _f64(Xc, self.device)
+        Nc = Xc.shape[0]
+        out = torch.empty(self.M, self.n, pad8(Nc), dtype=torch.float64, device=self.device)
+        work = _lib.workspace(8 * self.M * self.Kp * pad8(Nc) + 512, self.device)
+        check(_lib.lib().bo_kernel_matrix(self.ctx, C.byref(self.c), Nc, ptr(Xc), ptr(out), work.data_ptr(),
+                                          work.numel(), _lib.stream_ptr(self.device)))  # fmt: skip
+        return out[:, :, :Nc]
+
+
+class NEIState:
+    """Baseline factors of qLogNEI (V_b, L_b and its inverse, base samples, best_f) and the fused fwd/bwd."""
+
+    def __init__(self, gp: GPState, X_baseline: Tensor, Z_b: Tensor) -> None:
+        dev = gp.device
+        self.gp = gp
+        self.device = dev
+        self.X_b = _f64(X_baseline, dev)
+        self.Z_b = _f64(Z_b, dev)
+        self.S, self.n_b = self.Z_b.shape
+        if self.X_b.shape != (self.n_b, gp.d):
+            raise ValueError(f"X_baseline {tuple(self.X_b.shape)} does not match base samples {tuple(self.Z_b.shape)}")
+        self.is_train = self.X_b.shape == gp.train_X.shape and bool(torch.equal(self.X_b, gp.train_X))
+        n, M, nb, S = gp.n, gp.M, self.n_b, self.S
+        nbp, Sp = pad8(nb), pad8(S)
+        self.nbp, self.Sp = nbp, Sp
+        z = lambda *s: torch.zeros(*s, dtype=torch.float64, device=dev)
+        self.aug_b = None if self.is_train else z(M, nb, gp.Kp)
+        self.vb = z(M, n + 1, nbp)
+        self.vb_t = z(M, nb, gp.np_)
+        self.lb = z(M, nb, nbp)
+        self.lb_inv = z(M, nb, nbp)
+        self.lb_inv_t = z(M, nb, nbp)
+        self.zb_pad = z(S, nbp)
+        self.zb_t = z(nb, Sp)
+        self.mean_b = z(M, nbp)
+        self.best_f_pad = z(M, Sp)
+        self.info = torch.zeros(M, dtype=torch.int32, device=dev)
+        self.c = BoNEI(
+            n_b=nb, S=S, baseline_is_train=int(self.is_train), X_b=ptr(self.X_b), Z_b=ptr(self.Z_b), jitter=None,
+            aug_b=ptr(self.aug_b), vb=ptr(self.vb), vb_t=ptr(self.vb_t), lb=ptr(self.lb), lb_inv=ptr(self.lb_inv),
+            lb_inv_t=ptr(self.lb_inv_t), zb_pad=ptr(self.zb_pad), zb_t=ptr(self.zb_t), mean_b=ptr(self.mean_b),
+            best_f=ptr(self.best_f_pad),
+        )  # fmt: skip
+        lib = _lib.lib()
+        work = _lib.workspace(lib.bo_nei_setup_workspace_bytes(C.byref(gp.c), C.byref(self.c)), dev)
+
+        def run(jitter: Optional[Tensor]) -> Tensor:
+            self._jitter = jitter
+            self.c.jitter = ptr(jitter)
+            check(lib.bo_nei_setup(gp.ctx, C.byref(gp.c), C.byref(self.c), work.data_ptr(), work.numel(),
+                                   ptr(self.info), _lib.stream_ptr(dev)))  # fmt: skip
+            return self.info.clone()
+
+        self.jitter = _retry_with_jitter(run, M, dev, "posterior covariance at X_baseline")
+
+    @property
+    def baseline_L(self) -> Tensor:
+        return self.lb[:, :, : self.n_b]
+
+    @property
+    def best_f(self) -> Tensor:
+        return self.best_f_pad[:, : self.S]
+
+    def workspace_bytes(self, B: int, q: int, with_grad: bool) -> int:
+        return _lib.lib().bo_qlognei_workspace_bytes(C.byref(self.gp.c), C.byref(self.c), B, q, int(with_grad))
+
+    def forward(self, X: Tensor, Z_q: Tensor, tau_relu: float, tau_max: float, with_grad: bool,
+                work: Optional[Tensor] = None):  # fmt: skip
+        """X: B x q x d, Z_q: S x q -> (acq [M x B], info [M x B] int32, workspace)."""
+        B, q, _ = X.shape
+        dev = self.device
+        acq = torch.empty(self.gp.M, B, dtype=torch.float64, device=dev)
+        info = torch.empty(self.gp.M, B, dtype=torch.int32, device=dev)
+        if work is None:
+            work = _lib.workspace(self.workspace_bytes(B, q, with_grad), dev)
+        check(_lib.lib().bo_qlognei_fwd(self.gp.ctx, C.byref(self.gp.c), C.byref(self.c), B, q, ptr(X), ptr(Z_q),
+                                        tau_relu, tau_max, ptr(acq), ptr(info), work.data_ptr(), work.numel(),
+                                        int(with_grad), _lib.stream_ptr(dev)))  # fmt: skip
+        return acq, info, work
+
+    def backward(self, X: Tensor, Z_q: Tensor, tau_relu: float, tau_max: float, grad_acq: Tensor, work: Tensor) -> Tensor:
+        """grad_acq: [M x B] -> grad_X [M x B x q x d] (per model)."""
+        B, q, d = X.shape
+        grad_X = torch.empty(self.gp.M, B, q, d, dtype=torch.float64, device=self.device)
+        check(_lib.lib().bo_qlognei_bwd(self.gp.ctx, C.byref(self.gp.c), C.byref(self.c), B, q, ptr(X), ptr(Z_q),
+                                        tau_relu, tau_max, ptr(grad_acq.contiguous()), ptr(grad_X), work.data_ptr(),
+                                        work.numel(), _lib.stream_ptr(self.device)))  # fmt: skip
+        return grad_X

@@ -1,0 +1,162 @@
+/* botorch_b200 -- C ABI of the B200-native qLogNEI / exact-GP posterior hot path.
+ *
+ * The reference (anand-12/botorch) is pure Python and has no FFI of its own:
+ * the drop-in boundary is its Python class contracts, implemented in botorch_b200/*.py.  This header
+ * is the C ABI those classes sit on -- every arithmetic step of the path runs behind these entry
+ * points.  Each entry point names the reference code it replaces (paths under /root/reference).
+ *
+ * Conventions
+ *   - all pointers are DEVICE pointers to float64 unless marked [host]; matrices are row-major;
+ *   - the caller owns every buffer (state and workspace sizes come from the *_bytes queries);
+ *   - all work is enqueued on `stream` (a cudaStream_t passed as void*); no hidden synchronisation
+ *     and no allocation inside the library;
+ *   - return value: BO_OK (0) or a BO_ERR_* code, text via bo_strerror(); numerical failures are
+ *     reported per batch element through `info` arrays, never by exception.
+ *   - M = number of models in the batch (1 for SingleTaskGP, #MCMC samples for SAAS).
+ */
+#ifndef BOTORCH_B200_H
+#define BOTORCH_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define BO_OK 0
+#define BO_ERR_INVALID 1
+#define BO_ERR_CUDA 2
+#define BO_ERR_WORKSPACE 3
+#define BO_ERR_UNSUPPORTED 4
+
+#define BO_KERNEL_RBF 0      /* gpytorch RBFKernel (ARD), models/utils/gpytorch_modules.py:100-127 */
+#define BO_KERNEL_MATERN52 1 /* gpytorch MaternKernel(nu=2.5, ARD), models/fully_bayesian.py:81-85,275-282 */
+
+/* info codes written per (model, t-batch element) by bo_qlognei_fwd */
+#define BO_INFO_OK 0
+#define BO_INFO_NAN (-1)      /* NaN/Inf in samples: low_rank.py:163-172 NanError */
+#define BO_INFO_NOT_PSD (-2)  /* q x q Schur block not PD after 6 jitter tries: NotPSDError */
+/* info > 0: number of jitter retries psd_safe_cholesky needed (NumericalWarning) */
+
+/* Fitted exact GP: inputs + factor buffers.  Replaces the state gpytorch's DefaultPredictionStrategy
+ * caches on first use (mean_cache, covar_cache) behind models/gpytorch.py:446 `mvn = self(X)`. */
+typedef struct bo_gp {
+    int32_t kernel_id; /* BO_KERNEL_* */
+    int32_t n, d, M;
+    double y_mean, y_std;      /* Standardize buffers (models/transforms/outcome.py:244-247); 0/1 if none */
+    /* inputs */
+    const double* train_X;     /* [n x d] */
+    const double* center;      /* [d]  centring point of the distance contraction (train_X.mean(0)) */
+    const double* inv_ls;      /* [M x d] 1/lengthscale */
+    const double* outputscale; /* [M] or NULL (=1) */
+    const double* noise;       /* [M] */
+    const double* mean;        /* [M] constant mean */
+    const double* targets;     /* [n] standardised train targets */
+    const double* jitter;      /* [M] extra diagonal jitter (psd_safe_cholesky retry) or NULL */
+    /* state filled by bo_gp_setup (caller-allocated, sizes from bo_gp_state_doubles) */
+    double* aug_train;         /* [M][n x Kp]        augmented distance operand, Kp = round_up(d+2,4) */
+    double* linv_aug;          /* [M][(n+1) x np]    rows 0..n-1: inv(L); row n: alpha = (K+s2 I)^-1 (y-m) */
+    double* linv_aug_t;        /* [M][n x n1p]       transpose of linv_aug */
+    double* chol;              /* [M][n x np]        L, K + s2 I = L L^T */
+} bo_gp;
+
+/* qLogNEI baseline state.  Replaces qLogNoisyExpectedImprovement._init_baseline
+ * (acquisition/logei.py:364-420) and CachedCholeskyMCSamplerMixin._compute_root_decomposition
+ * (acquisition/cached_cholesky.py:94-120). */
+typedef struct bo_nei {
+    int32_t n_b, S;
+    int32_t baseline_is_train; /* 1: X_baseline is train_X (shares the cross-covariance) */
+    const double* X_b;         /* [n_b x d] */
+    const double* Z_b;         /* [S x n_b] base samples of the baseline points (sampling/normal.py:178-209) */
+    const double* jitter;      /* [M] extra jitter for chol(Sigma_bb) or NULL */
+    /* state filled by bo_nei_setup */
+    double* aug_b;             /* [M][n_b x Kp]   (unused when baseline_is_train) */
+    double* vb;                /* [M][n x nbp]    V_b = inv(L) K(X, X_b) */
+    double* vb_t;              /* [M][n_b x np]   */
+    double* lb;                /* [M][n_b x nbp]  L_b = chol(Sigma(X_b,X_b)) on the outcome scale (_baseline_L) */
+    double* lb_inv;            /* [M][n_b x nbp]  */
+    double* lb_inv_t;          /* [M][n_b x nbp]  */
+    double* zb_pad;            /* [S x nbp]       Z_b with padded pitch */
+    double* zb_t;              /* [n_b x Sp]      */
+    double* mean_b;            /* [M][nbp]        posterior mean at X_b (outcome scale) */
+    double* best_f;            /* [M][Sp]         max_j baseline sample (acquisition/utils.py:125-129) */
+} bo_nei;
+
+typedef struct bo_ctx bo_ctx;
+
+const char* bo_strerror(int code);
+const char* bo_last_cuda_error(void);
+int bo_ctx_create(int device, bo_ctx** out);
+void bo_ctx_destroy(bo_ctx* ctx);
+/* kernels launched by this library so far (bench.py's gpu_launches) */
+long bo_launch_count(void);
+void bo_launch_count_reset(void);
+
+/* padded pitches used by every buffer of the ABI */
+long bo_pad8(long x);
+long bo_kp(int d);
+
+/* ---- setup -------------------------------------------------------------------------------- */
+size_t bo_gp_setup_workspace_bytes(const bo_gp* gp);
+/* K = k(X,X) + (noise+jitter) I; L = chol(K) (blocked right-looking, DMMA trailing updates);
+ * inv(L); alpha.  info[M] (device int32): 0 or 1-based index of the first bad pivot. */
+int bo_gp_setup(bo_ctx* ctx, const bo_gp* gp, void* work, size_t work_bytes, int32_t* info, void* stream);
+
+size_t bo_nei_setup_workspace_bytes(const bo_gp* gp, const bo_nei* nei);
+/* V_b, Sigma_bb, L_b (+inverse), baseline samples and best_f. info[M] as above for chol(Sigma_bb). */
+int bo_nei_setup(bo_ctx* ctx, const bo_gp* gp, const bo_nei* nei, void* work, size_t work_bytes, int32_t* info,
+                 void* stream);
+
+/* ---- the hot path ------------------------------------------------------------------------- */
+/* workspace for B t-batch elements of q points; with_grad != 0 adds the backward regions.
+ * The workspace of a with_grad forward must be kept untouched until bo_qlognei_bwd ran. */
+size_t bo_qlognei_workspace_bytes(const bo_gp* gp, const bo_nei* nei, int B, int q, int with_grad);
+
+/* acq[M x B] = qLogNEI value per model and t-batch element.  Replaces
+ * SampleReducingMCAcquisitionFunction.forward (acquisition/monte_carlo.py:253-289) with
+ * qLogNoisyExpectedImprovement._get_samples_and_objectives (acquisition/logei.py:448-481),
+ * model.posterior (models/gpytorch.py:405-466), sample_cached_cholesky (utils/low_rank.py:85-173),
+ * _log_improvement/log_fatplus, fatmax, logmeanexp (utils/safe_math.py:293-352,209-223).
+ * X [B x q x d]; Z_q [S x q] base samples of the q new points; info [M x B] int32. */
+int bo_qlognei_fwd(bo_ctx* ctx, const bo_gp* gp, const bo_nei* nei, int B, int q, const double* X,
+                   const double* Z_q, double tau_relu, double tau_max, double* acq, int32_t* info, void* work,
+                   size_t work_bytes, int with_grad, void* stream);
+
+/* grad_X[M x B x q x d] = d(sum_b grad_acq[m,b] * acq[m,b]) / dX per model.  Replaces torch.autograd
+ * through the whole forward (generation/gen.py:209-211). */
+int bo_qlognei_bwd(bo_ctx* ctx, const bo_gp* gp, const bo_nei* nei, int B, int q, const double* X,
+                   const double* Z_q, double tau_relu, double tau_max, const double* grad_acq, double* grad_X,
+                   void* work, size_t work_bytes, void* stream);
+
+/* ---- posterior API ------------------------------------------------------------------------- */
+size_t bo_posterior_workspace_bytes(const bo_gp* gp, long Nc);
+/* Joint posterior of B t-batches of q points: mean [M x B x q], cov [M x B x q x q] (outcome scale).
+ * Replaces BatchedMultiOutputGPyTorchModel.posterior (models/gpytorch.py:405-466). */
+int bo_posterior_joint(bo_ctx* ctx, const bo_gp* gp, int B, int q, const double* X, double* mean, double* cov,
+                       void* work, size_t work_bytes, void* stream);
+/* Marginal posterior at Nc points: mean, var [M x Nc].  The cross-covariance GEMM + triangular solve
+ * of MaxPosteriorSampling at scale (generation/sampling.py:95-113, config C5). */
+int bo_posterior_mean_var(bo_ctx* ctx, const bo_gp* gp, long Nc, const double* Xc, double* mean, double* var,
+                          void* work, size_t work_bytes, void* stream);
+/* argmax_i (mean_i + sqrt(var_i) * z_i) over Nc candidates per model: out_val[M], out_idx[M] (int64).
+ * Thompson draw + maximize_samples (generation/sampling.py:115-117); first occurrence wins ties. */
+int bo_ts_argmax(bo_ctx* ctx, int M, long Nc, const double* mean, const double* var, const double* z,
+                 double* out_val, int64_t* out_idx, void* stream);
+/* first-occurrence argmax of a vector (optim/initializers.py:944, optim/optimize.py:385) */
+int bo_argmax(bo_ctx* ctx, long n, const double* v, double* out_val, int64_t* out_idx, void* stream);
+
+/* ---- building blocks exported for the parity tests ------------------------------------------ */
+int bo_dgemm(bo_ctx* ctx, int M, int N, int K, int batch, double alpha, const double* A, long lda, long strideA,
+             const double* B, long ldb, long strideB, double beta, double* C, long ldc, long strideC, int tri,
+             void* stream);
+int bo_kernel_matrix(bo_ctx* ctx, const bo_gp* gp, long Nc, const double* Xc, double* out /* [M][n x pad8(Nc)] */,
+                     void* work, size_t work_bytes, void* stream);
+int bo_potrf(bo_ctx* ctx, int n, int batch, double* A, long lda, long strideA, double* inv /* or NULL */,
+             void* work, size_t work_bytes, int32_t* info, void* stream);
+size_t bo_potrf_workspace_bytes(int n, int batch);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* BOTORCH_B200_H */
