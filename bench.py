@@ -1,0 +1,363 @@
+#!/usr/bin/env python
+"""Benchmark of the qLogNEI hot path (BASELINE.json metric) on B200.
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--config C3]
+
+One "step" = one fused forward + backward of qLogNEI over the restart batch of the config (C3: B = 512 restarts of
+q = 8 points, n = 2000, d = 20, S = 256), i.e. exactly what one L-BFGS-B function evaluation of ``optimize_acqf``
+costs (botorch/generation/gen.py:194-222).  N > 1 (torchrun, one rank per GPU): rank 0 computes the training-set
+factors and broadcasts them (NCCL); every rank then steps its own block of B restarts -- weak scaling, no
+data-path collective.  Prints ONE JSON line on rank 0.
+
+``--impl reference`` times the CPU restatement of the reference algorithm (oracle/, faithful order of operations:
+posterior over [X_baseline; X], L^-T GEMM covariance, cached-Cholesky sampling, autograd backward) on the host cores.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import subprocess
+import sys
+import tempfile
+import time
+
+import torch
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+METRIC = "qLogNEI fwd+bwd candidate evals/s"
+UNIT = "candidate_evals/s"
+FP64_DMMA_PEAK_TFLOPS = 37.07  # measured on this pool's B200 with tools/fp64_peaks.cu (profiles/r01_fp64_peaks.txt)
+
+
+def _args():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--config", default="C3")
+    ap.add_argument("--restarts", type=int, default=None, help="override the restart batch per GPU")
+    ap.add_argument("--cpu-sample", type=int, default=None, help="candidates in the CPU baseline sample")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    return ap.parse_args()
+
+
+def _problem(cfg: str):
+    from botorch_b200.synthetic import make_problem
+
+    return make_problem(cfg)
+
+
+def _restart_batch(p, B: int, seed: int = 0) -> torch.Tensor:
+    """B x q x d synthetic restart batch (Sobol q-batches in the unit cube, seed != training-set seed)."""
+    from botorch_b200.sampling import draw_sobol_samples
+
+    bounds = torch.stack([torch.zeros(p.d), torch.ones(p.d)]).double()
+    return draw_sobol_samples(bounds, n=B, q=p.q, seed=777 + seed).contiguous()
+
+
+def _algorithmic_flops_per_eval(n, n_b, d, q, S):
+    """Forward and backward algorithmic flops of one candidate (t-batch) evaluation; DESIGN.md section 4."""
+    fwd = 2 * (d + 2) * q * n + 2 * q * n + q * n * n + q * q * n + 2 * q * n * n_b + q * n_b * n_b + q * q * n_b \
+        + q**3 / 3 + 2 * q * (n_b + q) * S + 30 * q * S  # fmt: skip
+    bwd = 2 * q * n_b * S + q * n_b * n_b + 2 * q * n * n_b + q * n * n + 2 * q * q * (n + n_b) + 4 * q * n * d \
+        + 40 * q * S  # fmt: skip
+    return fwd, bwd
+
+
+class _ClockSampler:
+    QUERY = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,"
+             "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+             "clocks_event_reasons.sw_power_cap")  # fmt: skip
+
+    def __init__(self, gpu_index: int):
+        self.f = tempfile.NamedTemporaryFile("w+", suffix=".csv", delete=False)
+        try:
+            self.p = subprocess.Popen(
+                ["nvidia-smi", f"--id={gpu_index}", f"--query-gpu={self.QUERY}", "--format=csv,noheader,nounits", "-lms", "100"],
+                stdout=self.f, stderr=subprocess.DEVNULL)  # fmt: skip
+        except Exception:
+            self.p = None
+
+    def stop(self):
+        out = {"sm_mhz": None, "sm_max_mhz": None, "reasons": [], "samples": 0}
+        if self.p is None:
+            return out
+        self.p.terminate()
+        try:
+            self.p.wait(timeout=5)
+        except Exception:
+            self.p.kill()
+        self.f.flush()
+        self.f.seek(0)
+        sm, mx, reasons = [], [], set()
+        for line in self.f.read().strip().splitlines():
+            c = [x.strip() for x in line.split(",")]
+            if len(c) < 9:
+                continue
+            try:
+                sm.append(float(c[1])); mx.append(float(c[2]))  # noqa: E702
+            except ValueError:
+                continue
+            for name, v in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), c[5:9]):
+                if v.lower().startswith("active"):
+                    reasons.add(name)
+        os.unlink(self.f.name)
+        if sm:
+            sm.sort()
+            out.update(sm_mhz=sm[len(sm) // 2], sm_max_mhz=max(mx), reasons=sorted(reasons), samples=len(sm))
+        return out
+
+
+# -------------------------------------------------------------------------------------------------
+# CPU leg (oracle): cpu_baseline of the default run and the whole --impl reference run
+# -------------------------------------------------------------------------------------------------
+def _cpu_setup(p):
+    from oracle.gp import GPHyper, OracleGP
+    from oracle.qlognei import OracleQLogNEI
+
+    h = p.hypers
+    gp = OracleGP(p.train_X, p.train_Y, GPHyper(p.kernel, h["lengthscale"], h["noise"], h["mean"], h.get("outputscale")),
+                  standardize=p.standardize)  # fmt: skip
+    return OracleQLogNEI(gp, p.train_X, num_samples=p.mc_samples, seed=1234)
+
+
+def _cpu_step(acq, X):
+    t0 = time.perf_counter()
+    acq.value_and_grad(X, mode="faithful")
+    return time.perf_counter() - t0
+
+
+def _cpu_baseline(p, sample: int, repeats: int = 1):
+    torch.set_num_threads(os.cpu_count() or 1)
+    acq = _cpu_setup(p)
+    X = _restart_batch(p, sample, seed=1)
+    _cpu_step(acq, X[:1])  # warm the caches (train Cholesky, L^-T) outside the timing
+    best = min(_cpu_step(acq, X) for _ in range(repeats))
+    return {
+        "value": sample / best,
+        "unit": UNIT,
+        "cores": torch.get_num_threads(),
+        "kind": "port",
+        "sample": f"{sample} of the config's restarts (B x q x d = {sample} x {p.q} x {p.d}), fwd + autograd bwd, "
+                  f"faithful reference order of operations, float64 torch CPU, {best:.2f} s",
+    }
+
+
+def _run_reference(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    p = _problem(args.config)
+    torch.set_num_threads(os.cpu_count() or 1)
+    sample = args.cpu_sample or (4 if p.n >= 1000 else 32)
+    acq = _cpu_setup(p)
+    X = _restart_batch(p, sample, seed=1)
+    for _ in range(max(args.warmup, 1)):
+        _cpu_step(acq, X[:1])
+    t = [_cpu_step(acq, X) for _ in range(args.steps)]
+    total = sum(t)
+    value = sample * args.steps / total
+    cores = torch.get_num_threads()
+    line = {
+        "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
+        "warmup": args.warmup, "ms_per_step": 1e3 * total / args.steps, "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+        "config": {"workload": _workload_name(p, sample), "note": "CPU oracle restatement of the reference algorithm"},
+        "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": "port",
+                         "sample": f"{sample} candidates per step, fwd + autograd bwd, faithful order of operations"},
+        "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }  # fmt: skip
+    print(json.dumps(line), flush=True)
+
+
+def _workload_name(p, B):
+    return (f"{p.name}: n={p.n} d={p.d} q={p.q} S={p.mc_samples} restarts/GPU={B} "
+            f"(BASELINE.json configs[{'C1 C2 C3 C4 C5'.split().index(p.name[:2])}])")  # fmt: skip
+
+
+# -------------------------------------------------------------------------------------------------
+# GPU leg
+# -------------------------------------------------------------------------------------------------
+def _run_ours(args):
+    import ctypes as C
+
+    import torch.distributed as dist
+
+    import botorch_b200 as bb
+    from botorch_b200 import _lib, distributed as bdist
+
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    ws = int(os.environ.get("WORLD_SIZE", "1"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device; the product path has no CPU fallback (use --impl reference)")
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if ws > 1:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=dev)
+    p = _problem(args.config)
+    B = args.restarts or p.num_restarts
+    lib = _lib.lib()
+
+    # ---- model + acquisition through the public API; factors built on rank 0 and broadcast --------------------
+    h = p.hypers
+    if p.kernel == "rbf":
+        model = bb.SingleTaskGP(p.train_X.to(dev), p.train_Y.to(dev), lengthscale=h["lengthscale"], noise=h["noise"],
+                                mean_constant=h["mean"], outcome_transform="DEFAULT" if p.standardize else None)  # fmt: skip
+    else:
+        model = bb.SaasFullyBayesianSingleTaskGP(p.train_X.to(dev), p.train_Y.to(dev))
+        model.load_mcmc_samples(h)
+    t_setup0 = time.perf_counter()
+    sampler = bb.SobolQMCNormalSampler(sample_shape=torch.Size([p.mc_samples]), seed=1234)
+    # rank 0 factors the training set and the baseline posterior; the other ranks receive them by NCCL broadcast
+    acqf, bcast_bytes = bdist.make_qlognei(model, p.train_X.to(dev), sampler=sampler)
+    torch.cuda.synchronize()
+    setup_s = time.perf_counter() - t_setup0
+
+    nei = acqf._nei
+    X_host = _restart_batch(p, B, seed=rank).pin_memory()
+    X = X_host.to(dev)
+    acqf._set_sampler(p.q)
+    Zq = acqf._Zq
+    work = _lib.workspace(nei.workspace_bytes(B, p.q, True), dev)
+    gin = -torch.ones(nei.gp.M, B, dtype=torch.float64, device=dev)
+    stream = torch.cuda.current_stream(dev)
+
+    def step():
+        acq, info, _ = nei.forward(X, Zq, acqf.tau_relu, acqf.tau_max, with_grad=True, work=work)
+        g = nei.backward(X, Zq, acqf.tau_relu, acqf.tau_max, gin, work)
+        return acq, g
+
+    def barrier():
+        torch.cuda.synchronize()
+        if ws > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    for _ in range(max(args.warmup, 3)):
+        step()
+    barrier()
+    # ---- timed region: K steps, inputs resident in HBM, CUDA events on the launching stream ------------------------
+    clocks = _ClockSampler(local) if rank == 0 else None
+    time.sleep(0.3)
+    lib.bo_launch_count_reset()
+    lib.bo_prof_enable(1)
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    barrier()
+    e0.record(stream)
+    for _ in range(args.steps):
+        acq, g = step()
+    e1.record(stream)
+    barrier()
+    ms = e0.elapsed_time(e1)
+    launches = int(lib.bo_launch_count())
+    gemm_ms, gemm_n, gemm_fl = C.c_double(), C.c_long(), C.c_double()
+    _lib.check(lib.bo_prof_read(C.byref(gemm_ms), C.byref(gemm_n), C.byref(gemm_fl)))
+    lib.bo_prof_enable(0)
+    assert bool(torch.isfinite(acq).all()) and bool(torch.isfinite(g).all())
+    t = torch.tensor([ms], dtype=torch.float64, device=dev)
+    if ws > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    ms_max = float(t)
+
+    # ---- e2e: the user-facing call with HOST buffers (gen_candidates_scipy's f_np_wrapper, gen.py:194-222) -----------
+    def e2e_step():
+        Xd = X_host.to(dev, non_blocking=True).requires_grad_(True)
+        loss = (-acqf(Xd)).sum()
+        grad = torch.autograd.grad(loss, Xd)[0]
+        return float(loss.detach()), grad.cpu()
+
+    for _ in range(3):
+        e2e_step()
+    barrier()
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        e2e_step()
+    torch.cuda.synchronize()
+    e2e_s = time.perf_counter() - t0
+    t = torch.tensor([e2e_s], dtype=torch.float64, device=dev)
+    if ws > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    e2e_s = float(t)
+    clk = clocks.stop() if clocks else None
+
+    # ---- posterior-only leg (second half of BASELINE.json's metric): marginal mean/var over a candidate stream --------
+    Nc = 32768
+    Xc = torch.rand(Nc, p.d, dtype=torch.float64, device=dev)
+    pw = nei.gp.posterior_workspace(Nc)
+    for _ in range(2):
+        nei.gp.posterior_mean_var(Xc, work=pw)
+    torch.cuda.synchronize()
+    p0, p1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    p0.record(stream)
+    for _ in range(5):
+        nei.gp.posterior_mean_var(Xc, work=pw)
+    p1.record(stream)
+    torch.cuda.synchronize()
+    post_ms = p0.elapsed_time(p1) / 5
+    post_flops = nei.gp.M * Nc * (2 * (p.d + 2) * p.n + 2 * p.n + p.n * p.n + 2 * p.n)
+
+    if rank != 0:
+        if ws > 1:
+            dist.destroy_process_group()
+        return
+    n_models = nei.gp.M
+    fwd_f, bwd_f = _algorithmic_flops_per_eval(p.n, nei.n_b, p.d, p.q, p.mc_samples)
+    per_eval = (fwd_f + bwd_f) * n_models
+    value = ws * B * args.steps / (ms_max * 1e-3)
+    gemm_tflops = gemm_fl.value / (gemm_ms.value * 1e-3) / 1e12 if gemm_ms.value > 0 else 0.0
+    line = {
+        "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": ws, "steps": args.steps, "warmup": max(args.warmup, 3),
+        "ms_per_step": ms_max / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+        "dtype": "f64", "data": "synthetic",
+        "config": {
+            "workload": _workload_name(p, B), "kernel": p.kernel, "models": n_models,
+            "l2": "inputs larger than L2: the six n x n factor matrices (192 MB at C3) plus the per-step workspace "
+                  f"({work.numel() / 2**20:.0f} MiB) exceed the 126 MB L2, no flush needed",
+            "timed": "bo_qlognei_fwd + bo_qlognei_bwd per step, X resident in HBM",
+        },
+        "tflops_fp64_algorithmic": value * per_eval / 1e12,
+        "flops_per_eval": per_eval,
+        "roofline": {
+            "bound": "tensor", "achieved": gemm_tflops, "peak": FP64_DMMA_PEAK_TFLOPS, "unit": "TFLOP/s",
+            "frac": gemm_tflops / FP64_DMMA_PEAK_TFLOPS, "traffic": None, "kernel": "dgemm_dmma_kernel",
+            "peak_source": "FP64 DMMA peak measured on this pool (tools/fp64_peaks.cu, profiles/r01_fp64_peaks.txt); "
+                           "MEASURED_PEAKS.json holds no FP64 figure",
+            "launches_per_step": gemm_n.value / args.steps, "avg_launch_ms": gemm_ms.value / max(gemm_n.value, 1),
+            "share_of_step": gemm_ms.value / ms,
+        },
+        "e2e": {
+            "value": ws * B * args.steps / e2e_s, "unit": UNIT, "h2d_bytes_per_step": X_host.numel() * 8,
+            "d2h_bytes_per_step": X_host.numel() * 8 + 8,
+            "api": "qLogNoisyExpectedImprovement.forward + torch.autograd.grad, pinned host X in, gradient + loss out",
+        },
+        "gpu_launches": launches,
+        "posterior": {"tflops_fp64": post_flops / (post_ms * 1e-3) / 1e12, "frac_of_fp64_peak":
+                      post_flops / (post_ms * 1e-3) / 1e12 / FP64_DMMA_PEAK_TFLOPS, "candidates": Nc,
+                      "ms": post_ms},  # fmt: skip
+        "setup_s": setup_s, "broadcast_bytes": bcast_bytes, "clocks": clk,
+    }  # fmt: skip
+    if not args.no_cpu_baseline and ws == 1:
+        sample = args.cpu_sample or (4 if p.n >= 1000 else 32)
+        line["cpu_baseline"] = _cpu_baseline(p, sample)
+    print(json.dumps(line), flush=True)
+    if ws > 1:
+        dist.destroy_process_group()
+
+
+def main():
+    args = _args()
+    if args.impl == "reference":
+        _run_reference(args)
+    else:
+        _run_ours(args)
+
+
+if __name__ == "__main__":
+    main()

@@ -1,0 +1,27 @@
+"""botorch_b200: the batched GP-posterior + qLogNEI hot path of BoTorch as hand-written sm_100a CUDA.
+
+Only the path lives here: model posterior, base samples, the fused qLogNEI forward/backward,
+the multi-start optimiser seam and its multi-GPU sharding.  Python is the host language because the reference is
+Python; every number is produced by ``csrc/libbotorch_b200.so`` through the C ABI in ``include/botorch_b200.h``.
+There is no CPU fallback: importing is cheap, the first compute call raises if the library or a B200 is missing.
+"""
+from .acquisition import AcquisitionFunction, qLogNoisyExpectedImprovement  # noqa: F401
+from .generation import MaxPosteriorSampling  # noqa: F401
+from .models import SaasFullyBayesianSingleTaskGP, SingleTaskGP, Standardize  # noqa: F401
+from .optim import (  # noqa: F401
+    gen_batch_initial_conditions,
+    gen_candidates_scipy,
+    get_best_candidates,
+    initialize_q_batch,
+    optimize_acqf,
+)
+from .posteriors import FusedGPPosterior, GaussianMixturePosterior  # noqa: F401
+from .sampling import (  # noqa: F401
+    IIDNormalSampler,
+    SobolQMCNormalSampler,
+    draw_sobol_normal_samples,
+    draw_sobol_samples,
+    get_sampler,
+)
+
+__version__ = "0.1.0"

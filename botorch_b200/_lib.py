@@ -79,6 +79,10 @@ def _declare(lib: C.CDLL) -> None:
     lib.bo_ctx_destroy.restype = None
     lib.bo_launch_count.restype = i64
     lib.bo_launch_count_reset.restype = None
+    lib.bo_prof_enable.argtypes = [i32]
+    lib.bo_prof_enable.restype = None
+    lib.bo_prof_read.argtypes = [C.POINTER(dbl), C.POINTER(i64), C.POINTER(dbl)]
+    lib.bo_prof_read.restype = i32
     lib.bo_pad8.restype = i64
     lib.bo_pad8.argtypes = [i64]
     lib.bo_kp.restype = i64
@@ -96,6 +100,9 @@ def _declare(lib: C.CDLL) -> None:
     lib.bo_posterior_workspace_bytes.restype = sz
     lib.bo_posterior_workspace_bytes.argtypes = [gp, i64]
     lib.bo_posterior_joint.argtypes = [vp, gp, i32, i32, vp, vp, vp, vp, sz, vp]
+    lib.bo_posterior_bwd_workspace_bytes.restype = sz
+    lib.bo_posterior_bwd_workspace_bytes.argtypes = [gp, i32, i32]
+    lib.bo_posterior_joint_bwd.argtypes = [vp, gp, i32, i32, vp, vp, vp, vp, vp, sz, vp]
     lib.bo_posterior_mean_var.argtypes = [vp, gp, i64, vp, vp, vp, vp, sz, vp]
     lib.bo_ts_argmax.argtypes = [vp, i32, i64, vp, vp, vp, vp, vp, vp]
     lib.bo_argmax.argtypes = [vp, i64, vp, vp, vp, vp]
@@ -105,7 +112,7 @@ def _declare(lib: C.CDLL) -> None:
     lib.bo_potrf_workspace_bytes.argtypes = [i32, i32]
     lib.bo_potrf.argtypes = [vp, i32, i32, vp, i64, i64, vp, vp, sz, vp, vp]
     for name in (
-        "bo_ctx_create bo_gp_setup bo_nei_setup bo_qlognei_fwd bo_qlognei_bwd bo_posterior_joint "
+        "bo_ctx_create bo_gp_setup bo_nei_setup bo_qlognei_fwd bo_qlognei_bwd bo_posterior_joint bo_posterior_joint_bwd "
         "bo_posterior_mean_var bo_ts_argmax bo_argmax bo_dgemm bo_kernel_matrix bo_potrf"
     ).split():
         getattr(lib, name).restype = i32

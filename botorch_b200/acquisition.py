@@ -1,0 +1,252 @@
+"""qLogNoisyExpectedImprovement on the fused CUDA path.
+
+Contract mirrored from the reference:
+  * ``AcquisitionFunction``            botorch/acquisition/acquisition.py:25-74
+  * ``qLogNoisyExpectedImprovement``   botorch/acquisition/logei.py:237-501 (constructor arguments, buffers
+                                        ``X_baseline`` / ``baseline_samples`` / ``_baseline_best_f``, attributes
+                                        ``_baseline_L`` / ``sampler`` / ``base_sampler`` / ``q_in`` / ``tau_relu`` / ``tau_max``)
+  * forward decorators                 botorch/utils/transforms.py:228-336 (t-batch handling, pending points, ensemble
+                                        logmeanexp, output-shape check)
+  * base-sample bookkeeping            botorch/acquisition/cached_cholesky.py:167-186, botorch/sampling/normal.py:68-131
+  * failure conventions                botorch/acquisition/cached_cholesky.py:139-153 (warning, never an exception)
+
+``forward`` is backed by a ``torch.autograd.Function`` whose forward and backward are the two C-ABI calls
+``bo_qlognei_fwd`` / ``bo_qlognei_bwd``; ``torch.autograd.grad`` (generation/gen.py:211) therefore runs the
+hand-written reverse kernels.  Nothing here computes on the CPU.
+"""
+from __future__ import annotations
+
+import math
+import warnings
+from copy import deepcopy
+from typing import Optional
+
+import torch
+from torch import Tensor
+from torch.nn import Module
+
+from . import engine
+from .exceptions import BotorchWarning, NumericalWarning, UnsupportedError
+from .models import Model, _FusedExactGP
+from .sampling import MCSampler, SobolQMCNormalSampler, get_sampler
+
+TAU_RELU = 1e-6  # logei.py:66
+TAU_MAX = 1e-2  # logei.py:67
+DEFAULT_MC_SAMPLES = 512  # acquisition/acquisition.py:116
+
+
+class AcquisitionFunction(Module):
+    """Abstract acquisition function (acquisition.py:25-74)."""
+
+    _log: bool = False
+
+    def __init__(self, model: Model) -> None:
+        super().__init__()
+        self.model: Model = model
+
+    def set_X_pending(self, X_pending: Optional[Tensor] = None) -> None:
+        if X_pending is not None:
+            if X_pending.requires_grad:
+                warnings.warn(
+                    "Pending points require a gradient but the acquisition function will not provide a gradient to "
+                    "these points.",
+                    BotorchWarning,
+                    stacklevel=2,
+                )
+            self.X_pending = X_pending.detach().clone()
+        else:
+            self.X_pending = None
+
+    def forward(self, X: Tensor) -> Tensor:  # pragma: no cover - abstract
+        raise NotImplementedError
+
+
+class _ShapeOnlyPosterior:
+    """What a sampler needs to size its base samples for r jointly sampled points (no arithmetic)."""
+
+    batch_range = (0, -1)
+
+    def __init__(self, model_batch: torch.Size, r: int, device, dtype) -> None:
+        self.base_sample_shape = torch.Size(model_batch) + torch.Size([r])
+        self.batch_shape = torch.Size(model_batch)
+        self.device, self.dtype = device, dtype
+
+
+class _QLogNEIFunction(torch.autograd.Function):
+    """acq[M x B] = fused qLogNEI; backward = the hand-derived reverse kernels."""
+
+    @staticmethod
+    def forward(ctx, X: Tensor, nei: engine.NEIState, Zq: Tensor, tau_relu: float, tau_max: float):
+        with_grad = ctx.needs_input_grad[0]
+        Xd = X.detach().to(torch.float64).contiguous()
+        acq, info, work = nei.forward(Xd, Zq, tau_relu, tau_max, with_grad=with_grad)
+        if with_grad:
+            ctx.nei, ctx.work, ctx.taus, ctx.in_dtype = nei, work, (tau_relu, tau_max), X.dtype
+            ctx.save_for_backward(Xd, Zq)
+        ctx.mark_non_differentiable(info)
+        return acq.to(X.dtype), info
+
+    @staticmethod
+    def backward(ctx, grad_acq: Tensor, _grad_info):
+        Xd, Zq = ctx.saved_tensors
+        g = ctx.nei.backward(Xd, Zq, ctx.taus[0], ctx.taus[1], grad_acq.to(torch.float64), ctx.work)
+        ctx.work = None  # the workspace may be recycled from here on
+        return g.sum(dim=0).to(ctx.in_dtype), None, None, None, None
+
+
+class qLogNoisyExpectedImprovement(AcquisitionFunction):
+    """MC batch log noisy expected improvement, evaluated by one fused GPU pipeline per call.
+
+    qLogNEI(X) ~ log E[ max(max_j f(x_j) - max f(X_baseline), 0) ] with the smooth fat-tailed approximations of
+    [Ament2023logei]: log_fatplus(tau_relu) for the ReLU, fatmax(tau_max) over the q points, logmeanexp over samples.
+    """
+
+    _log = True
+
+    def __init__(
+        self,
+        model: Model,
+        X_baseline: Tensor,
+        sampler: Optional[MCSampler] = None,
+        objective=None,
+        posterior_transform=None,
+        X_pending: Optional[Tensor] = None,
+        constraints=None,
+        eta=1e-3,
+        fat: bool = True,
+        prune_baseline: bool = False,
+        cache_root: bool = True,
+        tau_max: float = TAU_MAX,
+        tau_relu: float = TAU_RELU,
+        marginalize_dim: Optional[int] = None,
+        *,
+        _factor_setup: bool = True,
+    ) -> None:
+        super().__init__(model=model)
+        if not isinstance(model, _FusedExactGP):
+            raise UnsupportedError(
+                f"the fused qLogNEI needs a botorch_b200 exact GP model, got {type(model).__name__}; no generic fallback"
+            )
+        for name, arg in (("objective", objective), ("posterior_transform", posterior_transform),
+                          ("constraints", constraints), ("marginalize_dim", marginalize_dim)):  # fmt: skip
+            if arg is not None:
+                raise UnsupportedError(f"`{name}` is not on the fused path yet (SURVEY.md section 8f): pass None")
+        if not fat:
+            raise UnsupportedError("fat=False (plain softplus / logsumexp smoothing) is not on the fused path")
+        if prune_baseline:
+            raise UnsupportedError("prune_baseline=True is not on the fused path: prune X_baseline before constructing")
+        if X_baseline.dim() != 2:
+            raise UnsupportedError("X_baseline must be r x d (one baseline set shared by all t-batches)")
+        self.tau_relu, self.tau_max = float(tau_relu), float(tau_max)
+        self._fat = True
+        # cache_root=False only changes the order of operations in the reference (joint Cholesky of the
+        # (n_b+q) block); the block Cholesky computed here is that same factor, so both settings share the path.
+        self._cache_root = bool(cache_root)
+        self.sample_shape = torch.Size([DEFAULT_MC_SAMPLES]) if sampler is None else sampler.sample_shape
+        self.set_X_pending(X_pending)
+        self._init_baseline(X_baseline, sampler, _factor_setup)
+
+    # -- one-time setup (logei.py:364-420) ------------------------------------------------------------
+    def _init_baseline(self, X_baseline: Tensor, sampler: Optional[MCSampler], setup: bool = True) -> None:
+        gp: engine.GPState = self.model.gp_state
+        self.register_buffer("X_baseline", X_baseline.detach())
+        n_b = X_baseline.shape[-2]
+        shape_post = _ShapeOnlyPosterior(self.model.batch_shape, n_b, gp.device, X_baseline.dtype)
+        if sampler is None:
+            sampler = get_sampler(shape_post, sample_shape=self.sample_shape)
+        if len(sampler.sample_shape) != 1:
+            raise UnsupportedError("the fused path takes a one-dimensional sample_shape")
+        self.sampler = sampler
+        self.sampler._construct_base_samples(shape_post)  # S x (1 per model-batch dim) x n_b
+        self.base_sampler = deepcopy(self.sampler)
+        S = self.sample_shape[0]
+        Z_b = self.sampler.base_samples.reshape(S, n_b).to(device=gp.device, dtype=torch.float64).contiguous()
+        # setup=False: allocate only; botorch_b200.distributed broadcasts the factors from the rank that computed them
+        self._nei = engine.NEIState(gp, self.X_baseline.to(gp.device), Z_b, setup=setup)
+        self.q_in = -1
+        self._Zq: Optional[Tensor] = None
+        self.register_buffer("_baseline_best_f", None)
+        self._refresh_baseline_views()
+
+    def _refresh_baseline_views(self) -> None:
+        """(Re)derive the reference-named views of the device state (after setup or after a factor broadcast)."""
+        best = self._nei.best_f  # [M x S]
+        best = best.mT if self.model._is_ensemble else best[0]
+        self._baseline_best_f = best.to(self.X_baseline.dtype).clone()
+        L = self._nei.baseline_L
+        self._baseline_L = (L if self.model._is_ensemble else L[0]).to(self.X_baseline.dtype)
+
+    @property
+    def baseline_samples(self) -> Tensor:
+        """S x (M) x n_b x 1 posterior samples at X_baseline (materialised on request only)."""
+        nei = self._nei
+        Z = nei.Z_b.unsqueeze(1).expand(nei.S, nei.gp.M, nei.n_b)
+        out = engine.root_apply(nei.baseline_L.contiguous(), nei.mean_b[:, : nei.n_b], Z)
+        out = out if self.model._is_ensemble else out[:, 0]
+        return out.unsqueeze(-1).to(self.X_baseline.dtype)
+
+    @property
+    def baseline_obj(self) -> Tensor:
+        return self.baseline_samples.squeeze(-1)
+
+    def compute_best_f(self, obj: Tensor) -> Tensor:
+        val = self._baseline_best_f
+        view = torch.Size([val.shape[0], *(1,) * (obj.ndim - val.ndim - 1), *val.shape[1:]])
+        return val.view(view).to(obj)
+
+    # -- base samples of the q new points (cached_cholesky.py:167-186) -----------------------------------
+    def _set_sampler(self, q_in: int) -> None:
+        if self.q_in == q_in and self._Zq is not None:
+            return
+        n_b = self.X_baseline.shape[-2]
+        gp = self._nei.gp
+        # the t-batch dimension of X_full = [X_baseline; X] is collapsed to 1 by the sampler
+        post = _ShapeOnlyPosterior(torch.Size([1]) + self.model.batch_shape, n_b + q_in, gp.device, self.X_baseline.dtype)
+        self.sampler._update_base_samples(posterior=post, base_sampler=self.base_sampler)
+        S = self.sample_shape[0]
+        Z = self.sampler.base_samples.reshape(S, n_b + q_in)
+        self._Zq = Z[:, n_b:].to(device=gp.device, dtype=torch.float64).contiguous()
+        self.q_in = q_in
+
+    # -- forward --------------------------------------------------------------------------------------
+    def forward(self, X: Tensor) -> Tensor:
+        """X: (b) x q x d  ->  (b) acquisition values (one per t-batch)."""
+        if X.dim() < 2:
+            raise ValueError(
+                f"{type(self).__name__} requires X to have at least 2 dimensions, but received X with only "
+                f"{X.dim()} dimensions."
+            )
+        if self.X_pending is not None:  # concatenate_pending_points
+            pend = self.X_pending.expand(*X.shape[:-2], *self.X_pending.shape[-2:]).to(X)
+            X = torch.cat([X, pend], dim=-2)
+        X = X if X.dim() > 2 else X.unsqueeze(0)  # add the t-batch dimension
+        batch_shape = X.shape[:-2]
+        q, d = X.shape[-2:]
+        Xf = X.reshape(-1, q, d)
+        if Xf.device != self._nei.device:
+            raise engine._lib.BoError(
+                f"X is on {Xf.device}; the acquisition function lives on {self._nei.device}. There is no CPU path."
+            )
+        self._set_sampler(q_in=q)
+        acq, info = _QLogNEIFunction.apply(Xf, self._nei, self._Zq, self.tau_relu, self.tau_max)
+        self._warn_on_failures(info)
+        if self.model._is_ensemble:  # t_batch_mode_transform: logmeanexp over the hyperparameter samples
+            acq = torch.logsumexp(acq, dim=0) - math.log(acq.shape[0])
+        else:
+            acq = acq[0]
+        return acq.reshape(batch_shape)
+
+    def _warn_on_failures(self, info: Tensor) -> None:
+        lo, hi = torch.aminmax(info)
+        lo, hi = int(lo), int(hi)
+        if hi > 0:
+            warnings.warn(
+                f"A not p.d., added jitter of {1e-8 * 10 ** (hi - 1):.1e} to the diagonal", NumericalWarning, stacklevel=3
+            )
+        if lo < 0:
+            warnings.warn(
+                "Low-rank cholesky updates failed due NaNs or due to an ill-conditioned covariance matrix. "
+                "The affected t-batches were evaluated without their q x q root.",
+                BotorchWarning,
+                stacklevel=3,
+            )

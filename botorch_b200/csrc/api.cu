@@ -489,6 +489,48 @@ int bo_posterior_joint(bo_ctx* ctx, const bo_gp* gp, int B, int q, const double*
     return bo_cand_posterior(a, mean, cov, st);
 }
 
+size_t bo_posterior_bwd_workspace_bytes(const bo_gp* gp, int B, int q) {
+    const long Nc = (long)B * q, ldn = bo_pad8(Nc);
+    Bump b(nullptr, 0);
+    b.doubles((long)gp->M * (gp->n + 1) * ldn);
+    b.doubles((long)gp->M * B * q * q);
+    return bo_posterior_workspace_bytes(gp, Nc) + b.off;
+}
+
+int bo_posterior_joint_bwd(bo_ctx* ctx, const bo_gp* gp, int B, int q, const double* X, const double* mean_bar,
+                           const double* cov_bar, double* grad_X, void* work, size_t work_bytes, void* stream) {
+    if (!ctx || !valid_gp(gp) || B <= 0 || q <= 0 || !X || !mean_bar || !cov_bar || !grad_X || !work)
+        return BO_ERR_INVALID;
+    if (q > BO_MAX_Q) return BO_ERR_UNSUPPORTED;
+    cudaStream_t st = (cudaStream_t)stream;
+    const long n = gp->n, M = gp->M, n1p = bo_pad8(n + 1), Nc = (long)B * q;
+    const size_t fwd_bytes = bo_posterior_workspace_bytes(gp, Nc);
+    if (work_bytes < bo_posterior_bwd_workspace_bytes(gp, B, q)) return BO_ERR_WORKSPACE;
+    double *v, *kx;
+    long ldn;
+    BO_TRY(posterior_v(gp, Nc, X, work, fwd_bytes, &v, &kx, &ldn, st));  // recompute V (cheaper than keeping it)
+    Bump b((char*)work + fwd_bytes, work_bytes - fwd_bytes);
+    const long regionV = (n + 1) * ldn;
+    double* vbar = b.doubles(M * regionV);
+    double* tbuf = b.doubles(M * (long)B * q * q);
+    const double ys2 = gp->y_std * gp->y_std;
+    BoCandArgs a{};
+    a.h = hyper_of(gp);
+    a.n = gp->n; a.B = B; a.q = q;
+    a.y_mean = gp->y_mean; a.y_std = gp->y_std;
+    a.X = X; a.ldn = ldn;
+    a.Vbar_mu = vbar + n * ldn; a.strideVbar = regionV;
+    a.gradX = grad_X;
+    BO_TRY(bo_fill(vbar, M * regionV, 0.0, st));
+    BO_TRY(bo_cand_posterior_bwd(a, mean_bar, cov_bar, tbuf, st));
+    // Vbar = -ys^2 V (cov_bar + cov_bar^T)
+    BO_TRY(bo_colblock_update(vbar, regionV, v, regionV, tbuf, (int)n, B, q, (int)M, ldn, -ys2, st));
+    // KXbar = [inv(L)^T | alpha] Vbar     (into the kx region)
+    BO_TRY(gemm((int)n, (int)Nc, (int)n + 1, (int)M, 1.0, gp->linv_aug_t, n1p, n * n1p, vbar, ldn, regionV, 0.0, nullptr, 0,
+                0, kx, ldn, n * ldn, BO_TRI_A_UPPER, 0, st));
+    return bo_kgrad(hyper_of(gp), gp->train_X, (int)n, kx, n * ldn, ldn, X, B, q, 1.0, grad_X, st);
+}
+
 int bo_posterior_mean_var(bo_ctx* ctx, const bo_gp* gp, long Nc, const double* Xc, double* mean, double* var,
                           void* work, size_t work_bytes, void* stream) {
     if (!ctx || !valid_gp(gp) || Nc <= 0 || !Xc || !mean || !var || !work) return BO_ERR_INVALID;

@@ -560,6 +560,41 @@ __global__ void __launch_bounds__(CAND_THREADS) cand_posterior_kernel(const BoCa
     if (tid < q) mean[o * q + tid] = a.y_mean + a.y_std * (a.mean_const[z] + V[(long)a.n * a.ldn + c0 + tid]);
 }
 
+// Reverse pass of cand_posterior_kernel for one (model, t-batch element):
+//   T = cov_bar + cov_bar^T (adjoint of the symmetric block), row n of Vbar <- y_std * mean_bar,
+//   gradX <- contribution of k(X, X):  cov = ys^2 (k(x_j, x_k) - ...)
+__global__ void __launch_bounds__(CAND_THREADS) cand_posterior_bwd_kernel(const BoCandArgs a, const double* mean_bar,
+                                                                          const double* cov_bar, double* Tout) {
+    extern __shared__ __align__(16) double sm[];
+    const int q = a.q, b = blockIdx.x, z = blockIdx.y, tid = threadIdx.x, T = blockDim.x;
+    const int c0 = b * q, d = a.h.d;
+    const long o = (long)z * a.B + b;
+    double* Ts = sm;  // q*q
+    for (int idx = tid; idx < q * q; idx += T) {
+        const int j = idx / q, k = idx % q;
+        const double v = cov_bar[o * q * q + j * q + k] + cov_bar[o * q * q + k * q + j];
+        Ts[idx] = v;
+        Tout[o * q * q + idx] = v;
+    }
+    if (tid < q) a.Vbar_mu[(long)z * a.strideVbar + c0 + tid] = a.y_std * mean_bar[o * q + tid];
+    __syncthreads();
+    const double ys2 = a.y_std * a.y_std;
+    const double os = a.h.outputscale ? a.h.outputscale[z] : 1.0;
+    const double* il = a.h.inv_ls + (long)z * d;
+    double* gX = a.gradX + o * q * d;
+    for (int idx = tid; idx < q * d; idx += T) {
+        const int j = idx / d, t = idx % d;
+        double acc = 0.0;
+        for (int k = 0; k < q; k++) {
+            if (k == j) continue;
+            const double gf = kern_dfactor(a.h.kernel_id, pair_r2(a.X, d, il, c0 + j, c0 + k), os);
+            acc += ys2 * Ts[j * q + k] * (-gf) * (a.X[(long)(c0 + j) * d + t] - a.X[(long)(c0 + k) * d + t]) * il[t] *
+                   il[t];
+        }
+        gX[idx] = acc;
+    }
+}
+
 __global__ void col_mean_var_kernel(const double* V, long strideV, long ldn, int n, long Nc, double y_mean,
                                     double y_std, const double* mean_const, const double* outputscale, double* mean,
                                     double* var) {
@@ -699,6 +734,15 @@ int bo_cand_posterior(const BoCandArgs& a, double* mean, double* cov, cudaStream
     BO_TRY(set_smem_limit((const void*)cand_posterior_kernel, smem));
     dim3 grid(a.B, a.h.M);
     cand_posterior_kernel<<<grid, CAND_THREADS, smem, stream>>>(a, mean, cov);
+    BO_LAUNCH_CHECK();
+    return BO_OK;
+}
+int bo_cand_posterior_bwd(const BoCandArgs& a, const double* mean_bar, const double* cov_bar, double* Tout,
+                          cudaStream_t stream) {
+    if (a.q < 1 || a.q > BO_MAX_Q || a.h.d > BO_MAX_D) return BO_ERR_UNSUPPORTED;
+    if (a.B <= 0) return BO_OK;
+    dim3 grid(a.B, a.h.M);
+    cand_posterior_bwd_kernel<<<grid, CAND_THREADS, sizeof(double) * a.q * a.q, stream>>>(a, mean_bar, cov_bar, Tout);
     BO_LAUNCH_CHECK();
     return BO_OK;
 }

@@ -58,6 +58,10 @@ int bo_kgrad(const BoKernelHyper& h, const double* Xpts, int npts, const double*
 // joint posterior blocks from V: mean[z][b][j], cov[z][b][j][k] = ys^2 (k(x_j,x_k) - sum_i V_ij V_ik)
 int bo_cand_posterior(const BoCandArgs& a, double* mean, double* cov, cudaStream_t stream);
 
+// reverse of bo_cand_posterior: Tout[z][b] = cov_bar + cov_bar^T, Vbar_mu row, gradX <- k(X,X) part
+int bo_cand_posterior_bwd(const BoCandArgs& a, const double* mean_bar, const double* cov_bar, double* Tout,
+                          cudaStream_t stream);
+
 // marginal: mean[z][c] = y_mean + y_std*(m_z + V[n][c]); var[z][c] = ys^2 (os_z - sum_i V[i][c]^2)
 int bo_col_mean_var(const double* V, long strideV, long ldn, int n, long Nc, int M, double y_mean, double y_std,
                     const double* mean_const, const double* outputscale, double* mean, double* var,

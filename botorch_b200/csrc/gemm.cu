@@ -12,6 +12,36 @@
 
 long g_bo_launch_count = 0;
 
+// Optional per-launch CUDA-event timing of the GEMM kernel (bench.py's roofline leg): events are recorded on the
+// launching stream around every dgemm_dmma_kernel launch and summed by bo_prof_read after a synchronise.
+#include <vector>
+namespace {
+struct ProfRec { cudaEvent_t a, b; };
+bool g_prof_on = false;
+std::vector<ProfRec> g_prof_recs;
+size_t g_prof_used = 0;
+double g_prof_flops = 0.0;
+}  // namespace
+
+extern "C" void bo_prof_enable(int on) {
+    g_prof_on = on != 0;
+    g_prof_used = 0;
+    g_prof_flops = 0.0;
+}
+// total milliseconds, launches and algorithmic flops of the GEMM launches since bo_prof_enable(1); caller synchronises
+extern "C" int bo_prof_read(double* ms, long* launches, double* flops) {
+    double tot = 0.0;
+    for (size_t i = 0; i < g_prof_used; i++) {
+        float t = 0.f;
+        if (cudaEventElapsedTime(&t, g_prof_recs[i].a, g_prof_recs[i].b) != cudaSuccess) return BO_ERR_CUDA;
+        tot += t;
+    }
+    if (ms) *ms = tot;
+    if (launches) *launches = (long)g_prof_used;
+    if (flops) *flops = g_prof_flops;
+    return BO_OK;
+}
+
 namespace {
 
 __device__ __forceinline__ void cp_async16(void* smem, const void* gmem, int src_bytes) {
@@ -195,7 +225,22 @@ int launch_cfg(const BoGemm& g, cudaStream_t stream) {
     }
     dim3 grid((g.M + C::BM - 1) / C::BM, (g.N + C::BN - 1) / C::BN, g.batch);
     if (grid.y > 65535u || grid.z > 65535u) return BO_ERR_UNSUPPORTED;
+    ProfRec* rec = nullptr;
+    if (g_prof_on) {
+        if (g_prof_used == g_prof_recs.size()) {
+            ProfRec r;
+            BO_CUDA_TRY(cudaEventCreate(&r.a));
+            BO_CUDA_TRY(cudaEventCreate(&r.b));
+            g_prof_recs.push_back(r);
+        }
+        rec = &g_prof_recs[g_prof_used++];
+        double f = 2.0 * g.M * (double)g.N * g.K * g.batch;
+        if (g.tri != BO_TRI_NONE || g.out_lower) f *= 0.5;  // triangular operand / lower-only output
+        g_prof_flops += f;
+        BO_CUDA_TRY(cudaEventRecord(rec->a, stream));
+    }
     dgemm_dmma_kernel<C><<<grid, C::THREADS, C::SMEM, stream>>>(g);
+    if (rec) BO_CUDA_TRY(cudaEventRecord(rec->b, stream));
     g_bo_launch_count++;
     BO_CUDA_TRY(cudaGetLastError());
     return BO_OK;

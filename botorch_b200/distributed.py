@@ -1,0 +1,168 @@
+"""Sharding the multi-start batch across the GPUs of one box (one process per GPU, torch.distributed).
+
+The reference has no multi-device code; its seam is the ``batch_limit`` / ``init_batch_limit``
+chunking of ``optimize_acqf`` (botorch/optim/optimize.py:268-317, botorch/optim/initializers.py:411-423): chunks of
+t-batches never interact.  Here each chunk goes to one rank:
+
+  * training-set factors and the qLogNEI baseline state are computed ONCE on rank 0 and broadcast (NCCL over
+    NVLink) -- the only bulk transfer;
+  * raw samples: rank r evaluates the contiguous block ``shard_range(R, r, G)``; the R values are all-gathered
+    (R doubles) so every rank performs the identical host-side selection (global indices preserved => the
+    argmax of optim/initializers.py:944 is bit-identical to the single-GPU run);
+  * restarts: rank r optimises its block (== the reference with ``batch_limit = B/G``); per-rank
+    (best value, global index, candidate) are all-gathered and the winner is the largest value with the lowest
+    index on ties, i.e. ``torch.argmax`` first-occurrence semantics (optim/optimize.py:385).
+
+There is no per-iteration collective.  All functions degrade to the single-process case when torch.distributed is
+not initialised, and work on the gloo backend for the CPU tests of the host logic.
+"""
+from __future__ import annotations
+
+from typing import Callable, List, Optional, Tuple
+
+import torch
+import torch.distributed as dist
+from torch import Tensor
+
+
+def world() -> Tuple[int, int]:
+    """(rank, world_size); (0, 1) without an initialised process group."""
+    if dist.is_available() and dist.is_initialized():
+        return dist.get_rank(), dist.get_world_size()
+    return 0, 1
+
+
+def shard_range(total: int, rank: int, world_size: int) -> Tuple[int, int]:
+    """Contiguous block [lo, hi) of ``total`` units for ``rank``; the first ``total % world_size`` ranks get one more."""
+    base, extra = divmod(total, world_size)
+    lo = rank * base + min(rank, extra)
+    return lo, lo + base + (1 if rank < extra else 0)
+
+
+def broadcast_buffers(buffers: List[Tensor], src: int = 0) -> int:
+    """Broadcast every buffer in place from ``src``; returns the payload in bytes."""
+    nbytes = 0
+    _, ws = world()
+    for b in buffers:
+        nbytes += b.numel() * b.element_size()
+        if ws > 1:
+            dist.broadcast(b, src=src)
+    return nbytes
+
+
+def replicate_model(model, src: int = 0) -> int:
+    """Factor the training set on ``src`` only and broadcast the factors (K2 of SURVEY.md: once per model)."""
+    rank, ws = world()
+    if ws == 1:
+        model.gp_state
+        return 0
+    model.eval()
+    model._state = model._build_state(setup=(rank == src))
+    return broadcast_buffers(model._state.factor_buffers(), src)
+
+
+def make_qlognei(model, X_baseline: Tensor, sampler=None, src: int = 0, **kwargs):
+    """qLogNoisyExpectedImprovement whose baseline state is computed on ``src`` and broadcast.
+
+    Returns (acquisition function, broadcast bytes).  Base samples are drawn on every rank from the same seed
+    (host SobolEngine), so only factors travel.
+    """
+    from .acquisition import qLogNoisyExpectedImprovement
+
+    rank, ws = world()
+    nbytes = replicate_model(model, src)
+    acqf = qLogNoisyExpectedImprovement(model, X_baseline, sampler=sampler, _factor_setup=(ws == 1 or rank == src),
+                                        **kwargs)  # fmt: skip
+    if ws > 1:
+        nbytes += broadcast_buffers(acqf._nei.factor_buffers(), src)
+        acqf._refresh_baseline_views()
+    return acqf, nbytes
+
+
+def all_gather_blocks(local: Tensor, total: int) -> Tensor:
+    """Concatenate per-rank contiguous blocks (sizes given by ``shard_range``) into the full vector on every rank."""
+    rank, ws = world()
+    if ws == 1:
+        return local
+    sizes = [shard_range(total, r, ws) for r in range(ws)]
+    width = max(hi - lo for lo, hi in sizes)
+    pad = torch.zeros(width, *local.shape[1:], dtype=local.dtype, device=local.device)
+    pad[: local.shape[0]] = local
+    out = [torch.empty_like(pad) for _ in range(ws)]
+    dist.all_gather(out, pad)
+    return torch.cat([o[: hi - lo] for o, (lo, hi) in zip(out, sizes)], dim=0)
+
+
+def sharded_raw_sample_values(acq_function, X_rnd: Tensor, device, batch_limit: Optional[int] = None) -> Tensor:
+    """Acquisition values of all raw q-batches; each rank evaluates its contiguous block (global order kept)."""
+    from .optim import evaluate_raw_samples
+
+    rank, ws = world()
+    lo, hi = shard_range(X_rnd.shape[0], rank, ws)
+    y_local = evaluate_raw_samples(acq_function, X_rnd[lo:hi], device, batch_limit)
+    if ws == 1:
+        return y_local
+    backend = dist.get_backend()
+    y_dev = y_local.to(device) if backend == "nccl" else y_local
+    return all_gather_blocks(y_dev, X_rnd.shape[0]).cpu()
+
+
+def gather_best(values: Tensor, candidates: Tensor, index_offset: int) -> Tuple[Tensor, Tensor, int]:
+    """Global best over all ranks' (values [b], candidates [b x q x d]).
+
+    Each rank contributes its local argmax (first occurrence), the winner is the largest value, lowest global index
+    on ties.  Returns (candidate q x d, value, global index) on every rank.
+    """
+    rank, ws = world()
+    li = int(torch.argmax(values.view(-1)))
+    best_val = values.view(-1)[li].reshape(1).to(torch.float64)
+    best_idx = torch.tensor([index_offset + li], dtype=torch.int64, device=values.device)
+    best_cand = candidates[li].to(torch.float64).contiguous()
+    if ws == 1:
+        return candidates[li], values.view(-1)[li], int(best_idx)
+    vals = [torch.empty_like(best_val) for _ in range(ws)]
+    idxs = [torch.empty_like(best_idx) for _ in range(ws)]
+    cands = [torch.empty_like(best_cand) for _ in range(ws)]
+    dist.all_gather(vals, best_val)
+    dist.all_gather(idxs, best_idx)
+    dist.all_gather(cands, best_cand)
+    vals_t, idxs_t = torch.cat(vals), torch.cat(idxs)
+    top = vals_t.max()
+    tied = torch.nonzero(vals_t == top).view(-1)
+    win = int(tied[torch.argmin(idxs_t[tied])])
+    return cands[win].to(candidates.dtype), vals_t[win].to(values.dtype), int(idxs_t[win])
+
+
+def optimize_acqf_sharded(
+    acq_function,
+    bounds: Tensor,
+    q: int,
+    num_restarts: int,
+    raw_samples: int,
+    options: Optional[dict] = None,
+    gen_candidates: Optional[Callable] = None,
+) -> Tuple[Tensor, Tensor]:
+    """``optimize_acqf`` with raw samples and restarts sharded over the process group.
+
+    Equivalent to the reference run with ``options['batch_limit'] = ceil(num_restarts / world_size)``.
+    """
+    from .optim import gen_candidates_scipy, initialize_q_batch
+    from .sampling import draw_sobol_samples
+
+    options = dict(options or {})
+    rank, ws = world()
+    device = bounds.device
+    X_rnd = draw_sobol_samples(bounds=bounds.cpu(), n=raw_samples, q=q, seed=options.get("seed"))
+    Y_rnd = sharded_raw_sample_values(acq_function, X_rnd, device, options.get("init_batch_limit"))
+    # identical host RNG stream on every rank => identical initial conditions everywhere
+    gen = torch.random.get_rng_state()
+    torch.manual_seed(options.get("seed", 0) or 0)
+    ics = initialize_q_batch(X=X_rnd, Y=Y_rnd, n=num_restarts, **({"eta": options["eta"]} if "eta" in options else {}))
+    torch.random.set_rng_state(gen)
+    lo, hi = shard_range(num_restarts, rank, ws)
+    gen_candidates = gen_candidates or gen_candidates_scipy
+    gen_opts = {k: v for k, v in options.items() if k in ("maxiter", "method", "with_grad", "disp", "ftol", "gtol")}
+    cands, vals = gen_candidates(ics[lo:hi].to(device), acq_function, lower_bounds=bounds[0], upper_bounds=bounds[1],
+                                 options=gen_opts)  # fmt: skip
+    cand, val, _ = gather_best(vals, cands, lo)
+    return cand, val

@@ -58,6 +58,7 @@ class GPState:
         outputscale: Optional[Tensor] = None,
         y_mean: float = 0.0,
         y_std: float = 1.0,
+        setup: bool = True,
     ) -> None:
         dev = train_X.device
         self.device = dev
@@ -94,6 +95,9 @@ class GPState:
             aug_train=ptr(self.aug_train), linv_aug=ptr(self.linv_aug), linv_aug_t=ptr(self.linv_aug_t),
             chol=ptr(self.chol),
         )  # fmt: skip
+        self.jitter = torch.zeros(M, dtype=torch.float64, device=dev)
+        if not setup:  # factors arrive by broadcast from the rank that ran the setup (distributed.py)
+            return
         lib = _lib.lib()
         work = _lib.workspace(lib.bo_gp_setup_workspace_bytes(C.byref(self.c)), dev)
 
@@ -105,6 +109,10 @@ class GPState:
             return self.info.clone()
 
         self.jitter = _retry_with_jitter(run, M, dev, "K + noise*I")
+
+    def factor_buffers(self):
+        """Device buffers bo_gp_setup fills: what the setup rank broadcasts to its peers."""
+        return [self.aug_train, self.linv_aug, self.linv_aug_t, self.chol, self.jitter]
 
     # -- factors exposed for tests / callers ------------------------------------------------------
     @property
@@ -162,7 +170,7 @@ class GPState:
 class NEIState:
     """Baseline factors of qLogNEI (V_b, L_b and its inverse, base samples, best_f) and the fused fwd/bwd."""
 
-    def __init__(self, gp: GPState, X_baseline: Tensor, Z_b: Tensor) -> None:
+    def __init__(self, gp: GPState, X_baseline: Tensor, Z_b: Tensor, setup: bool = True) -> None:
         dev = gp.device
         self.gp = gp
         self.device = dev
@@ -193,6 +201,9 @@ class NEIState:
             lb_inv_t=ptr(self.lb_inv_t), zb_pad=ptr(self.zb_pad), zb_t=ptr(self.zb_t), mean_b=ptr(self.mean_b),
             best_f=ptr(self.best_f_pad),
         )  # fmt: skip
+        self.jitter = torch.zeros(M, dtype=torch.float64, device=dev)
+        if not setup:
+            return
         lib = _lib.lib()
         work = _lib.workspace(lib.bo_nei_setup_workspace_bytes(C.byref(gp.c), C.byref(self.c)), dev)
 
@@ -204,6 +215,12 @@ class NEIState:
             return self.info.clone()
 
         self.jitter = _retry_with_jitter(run, M, dev, "posterior covariance at X_baseline")
+
+    def factor_buffers(self):
+        """Device buffers bo_nei_setup fills (broadcast payload)."""
+        bufs = [self.vb, self.vb_t, self.lb, self.lb_inv, self.lb_inv_t, self.zb_pad, self.zb_t, self.mean_b,
+                self.best_f_pad, self.jitter]  # fmt: skip
+        return bufs + ([] if self.aug_b is None else [self.aug_b])
 
     @property
     def baseline_L(self) -> Tensor:
@@ -238,3 +255,101 @@ class NEIState:
                                         tau_relu, tau_max, ptr(grad_acq.contiguous()), ptr(grad_X), work.data_ptr(),
                                         work.numel(), _lib.stream_ptr(self.device)))  # fmt: skip
         return grad_X
+
+
+# -------------------------------------------------------------------------------------------------
+# dense MVN helpers for the posterior API (posteriors/gpytorch.py:85-149: root of Sigma, mu + root z)
+# -------------------------------------------------------------------------------------------------
+def mvn_root(cov: Tensor, what: str = "posterior covariance") -> Tensor:
+    """Lower Cholesky root of a batch of covariance matrices [... x r x r] with psd_safe_cholesky's
+    retry schedule; blocked right-looking factorisation inside libbotorch_b200 (bo_potrf)."""
+    dev = cov.device
+    r = cov.shape[-1]
+    batch_shape = cov.shape[:-2]
+    nb = max(int(torch.Size(batch_shape).numel()), 1)
+    if bool(torch.isnan(cov).any()):
+        raise NanError(f"cholesky: {int(torch.isnan(cov).sum())} of {cov.numel()} elements are NaN.")
+    rp = pad8(r)
+    src = _f64(cov, dev).reshape(nb, r, r)
+    lib = _lib.lib()
+    work = _lib.workspace(lib.bo_potrf_workspace_bytes(r, nb), dev)
+    info = torch.zeros(nb, dtype=torch.int32, device=dev)
+    A = torch.zeros(nb, r, rp, dtype=torch.float64, device=dev)
+
+    def run(jitter: Optional[Tensor]) -> Tensor:
+        A.zero_()
+        A[:, :, :r] = src
+        if jitter is not None:
+            A[:, :, :r].diagonal(dim1=-2, dim2=-1).add_(jitter.unsqueeze(-1))
+        check(lib.bo_potrf(_lib.ctx(dev), r, nb, ptr(A), rp, r * rp, None, work.data_ptr(), work.numel(), ptr(info),
+                           _lib.stream_ptr(dev)))  # fmt: skip
+        return info.clone()
+
+    _retry_with_jitter(run, nb, dev, what)
+    return A[:, :, :r].reshape(*batch_shape, r, r)
+
+
+def root_apply(L: Tensor, mean: Tensor, Z: Tensor) -> Tensor:
+    """samples[s, ..., i] = mean[..., i] + sum_j L[..., i, j] Z[s, ..., j].
+
+    L: [... x r x r] lower, mean: [... x r], Z: [S x ... x r] (batch dims may be broadcast views).
+    One triangular DMMA GEMM per batch member (bo_dgemm with BO_TRI_A_LOWER)."""
+    dev = L.device
+    r = L.shape[-1]
+    batch_shape = L.shape[:-2]
+    nb = max(int(torch.Size(batch_shape).numel()), 1)
+    S = Z.shape[0]
+    rp, Sp = pad8(r), pad8(S)
+    Lp = torch.zeros(nb, r, rp, dtype=torch.float64, device=dev)
+    Lp[:, :, :r] = L.reshape(nb, r, r)
+    shared = all(st == 0 or sz == 1 for st, sz in zip(Z.stride()[1:-1], Z.shape[1:-1]))
+    if shared:  # one base-sample set for every batch member (t-batch collapsed samplers)
+        Zt = torch.zeros(1, r, Sp, dtype=torch.float64, device=dev)
+        Zt[0, :, :S] = Z[(slice(None),) + (0,) * (Z.dim() - 2)].to(torch.float64).mT
+        strideZ = 0
+    else:
+        Zt = torch.zeros(nb, r, Sp, dtype=torch.float64, device=dev)
+        Zt[:, :, :S] = Z.expand(S, *batch_shape, r).reshape(S, nb, r).permute(1, 2, 0)
+        strideZ = r * Sp
+    out = torch.empty(nb, r, Sp, dtype=torch.float64, device=dev)
+    check(_lib.lib().bo_dgemm(_lib.ctx(dev), r, S, r, nb, 1.0, ptr(Lp), rp, r * rp, ptr(Zt), Sp, strideZ, 0.0, ptr(out),
+                              Sp, r * Sp, 1, _lib.stream_ptr(dev)))  # fmt: skip
+    samples = out[:, :, :S].permute(2, 0, 1).reshape(S, *batch_shape, r)
+    return samples + mean
+
+
+class _PosteriorJoint(torch.autograd.Function):
+    """mean/covariance blocks of B t-batches with the hand-written reverse pass (bo_posterior_joint_bwd)."""
+
+    @staticmethod
+    def forward(ctx, X: Tensor, st: GPState):
+        Xd = _f64(X.detach(), st.device)
+        mean, cov = st.posterior_joint(Xd)
+        ctx.st = st
+        ctx.save_for_backward(Xd)
+        ctx.in_dtype = X.dtype
+        return mean, cov
+
+    @staticmethod
+    def backward(ctx, mean_bar: Tensor, cov_bar: Tensor):
+        (Xd,) = ctx.saved_tensors
+        st: GPState = ctx.st
+        B, q, d = Xd.shape
+        lib = _lib.lib()
+        zeros = lambda *s: torch.zeros(*s, dtype=torch.float64, device=st.device)
+        mean_bar = zeros(st.M, B, q) if mean_bar is None else _f64(mean_bar, st.device)
+        cov_bar = zeros(st.M, B, q, q) if cov_bar is None else _f64(cov_bar, st.device)
+        grad = torch.empty(st.M, B, q, d, dtype=torch.float64, device=st.device)
+        work = _lib.workspace(lib.bo_posterior_bwd_workspace_bytes(C.byref(st.c), B, q), st.device)
+        check(lib.bo_posterior_joint_bwd(st.ctx, C.byref(st.c), B, q, ptr(Xd), ptr(mean_bar), ptr(cov_bar), ptr(grad),
+                                         work.data_ptr(), work.numel(), _lib.stream_ptr(st.device)))  # fmt: skip
+        return grad.sum(dim=0).to(ctx.in_dtype), None
+
+
+def posterior_joint(st: GPState, X: Tensor):
+    """X: B x q x d -> (mean [M x B x q], cov [M x B x q x q]); differentiable w.r.t. X."""
+    if X.device != st.device:
+        raise _lib.BoError(f"X is on {X.device} but the model factors live on {st.device}; there is no CPU path")
+    if torch.is_grad_enabled() and X.requires_grad:
+        return _PosteriorJoint.apply(X, st)
+    return st.posterior_joint(X.detach())

@@ -1,0 +1,354 @@
+"""Multi-start optimisation of an acquisition function (host control flow around the fused kernels).
+
+Contract mirrored from the reference:
+  * ``optimize_acqf`` / batch path          botorch/optim/optimize.py:246-394, 397-543
+  * ``gen_batch_initial_conditions``        botorch/optim/initializers.py:243-438
+  * ``initialize_q_batch``                  botorch/optim/initializers.py:893-965
+  * ``gen_candidates_scipy``                botorch/generation/gen.py:46-298 (L-BFGS-B over the flattened restarts,
+                                             value + ``torch.autograd.grad`` per function evaluation)
+  * ``get_best_candidates``                 botorch/generation/gen.py:427-455
+  * ``columnwise_clamp`` / scipy bounds     botorch/optim/utils/common.py, botorch/optim/parameter_constraints.py:53-96
+
+The SciPy L-BFGS-B driver stays on the host exactly as in the reference; every acquisition value and
+gradient it consumes comes from the CUDA path.  The raw-sample and restart batches are the sharding seams used by
+``botorch_b200.distributed`` (``init_batch_limit`` / ``batch_limit``, optimize.py:268-317).
+"""
+from __future__ import annotations
+
+import time
+import warnings
+from typing import Callable, Dict, Optional, Tuple, Union
+
+import numpy as np
+import torch
+from scipy import optimize as _sciopt
+from torch import Tensor
+from torch.quasirandom import SobolEngine
+
+from .exceptions import (
+    BadInitialCandidatesWarning,
+    OptimizationWarning,
+    UnsupportedError,
+)
+from .sampling import draw_sobol_samples, manual_seed
+
+INIT_OPTION_KEYS = {
+    "alpha", "batch_limit", "eta", "init_batch_limit", "nonnegative", "n_burnin", "sample_around_best",
+    "sample_around_best_sigma", "sample_around_best_prob_perturb", "sample_around_best_subset_sigma", "seed",
+    "thinning",
+}  # fmt: skip
+
+
+# -------------------------------------------------------------------------------------------------
+# initial conditions
+# -------------------------------------------------------------------------------------------------
+def initialize_q_batch(X: Tensor, Y: Tensor, n: int, eta: float = 1.0) -> Tensor:
+    """Pick ``n`` of the raw q-batches with probability ~ exp(eta * zscore(Y)); the best one is always kept.
+
+    The argmax over the raw samples is the index whose parity with the reference is bit-exact
+    (initializers.py:944); the multinomial draw uses torch's host RNG stream like the reference.
+    """
+    n_samples = X.shape[0]
+    if n > n_samples:
+        raise RuntimeError(f"n ({n}) cannot be larger than the number of provided samples ({n_samples})")
+    if n == n_samples:
+        return X
+    if X.dim() != 3:
+        raise UnsupportedError("initialize_q_batch on the fused path takes b x q x d raw samples (no extra batch dims)")
+    Ystd = Y.std(dim=0)
+    if bool(torch.any(Ystd == 0)):
+        warnings.warn(
+            "All acquisition values for raw samples points are the same for at least one batch. Choosing initial "
+            "conditions at random.",
+            BadInitialCandidatesWarning,
+        )
+        return X[torch.randperm(n=n_samples, device=X.device)][:n]
+    max_idx = torch.argmax(Y, dim=0)
+    etaZ = eta * (Y - Y.mean(dim=0)) / Ystd
+    weights = torch.exp(etaZ)
+    while bool(torch.isinf(weights).any()):
+        etaZ = etaZ * 0.5
+        weights = torch.exp(etaZ)
+    idcs = torch.multinomial(weights, n)
+    if max_idx not in idcs:
+        idcs[-1] = max_idx
+    return X[idcs]
+
+
+def gen_batch_initial_conditions(
+    acq_function,
+    bounds: Tensor,
+    q: int,
+    num_restarts: int,
+    raw_samples: int,
+    fixed_features: Optional[Dict[int, float]] = None,
+    options: Optional[Dict[str, Union[bool, float, int]]] = None,
+    inequality_constraints=None,
+    equality_constraints=None,
+    generator: Optional[Callable[[int, int, Optional[int]], Tensor]] = None,
+    fixed_X_fantasies: Optional[Tensor] = None,
+) -> Tensor:
+    """``num_restarts x q x d`` starting points chosen among ``raw_samples`` Sobol q-batches by acquisition value."""
+    if bool(bounds.isinf().any()):
+        raise NotImplementedError(
+            "Currently only finite values in `bounds` are supported for generating initial conditions for optimization."
+        )
+    if fixed_features or inequality_constraints or equality_constraints or fixed_X_fantasies is not None:
+        raise UnsupportedError("fixed features / linear constraints / fantasies are outside the fused path")
+    options = options or {}
+    if options.get("sample_around_best", False) or options.get("nonnegative", False):
+        raise UnsupportedError("sample_around_best / nonnegative initialisation are outside the fused path")
+    seed: Optional[int] = options.get("seed")
+    batch_limit: Optional[int] = options.get("init_batch_limit", options.get("batch_limit"))
+    init_kwargs = {"eta": options["eta"]} if "eta" in options else {}
+    device = bounds.device
+    bounds_cpu = bounds.cpu()
+    q = 1 if q is None else q
+    effective_dim = bounds.shape[-1] * q
+    factor, max_factor = 1, 5
+    while factor < max_factor:
+        with warnings.catch_warnings(record=True) as ws:
+            n = raw_samples * factor
+            if generator is not None:
+                X_rnd = generator(n, q, seed)
+            elif effective_dim <= SobolEngine.MAXDIM:
+                X_rnd = draw_sobol_samples(bounds=bounds_cpu, n=n, q=q, seed=seed)
+            else:
+                with manual_seed(seed):
+                    u = torch.rand(n, q, bounds_cpu.shape[-1], dtype=bounds.dtype)
+                X_rnd = bounds_cpu[0] + (bounds_cpu[1] - bounds_cpu[0]) * u
+            Y_rnd = evaluate_raw_samples(acq_function, X_rnd, device, batch_limit)
+            ics = initialize_q_batch(X=X_rnd, Y=Y_rnd, n=num_restarts, **init_kwargs).to(device=device)
+            if not any(issubclass(w.category, BadInitialCandidatesWarning) for w in ws):
+                return ics
+            if factor < max_factor:
+                factor += 1
+                if seed is not None:
+                    seed += 1
+    warnings.warn(
+        "Unable to find non-zero acquisition function values - initial conditions are being selected randomly.",
+        BadInitialCandidatesWarning,
+    )
+    return ics
+
+
+def evaluate_raw_samples(acq_function, X_rnd: Tensor, device, batch_limit: Optional[int] = None) -> Tensor:
+    """No-grad acquisition values of the raw q-batches in ``batch_limit`` chunks, returned on the host
+    (initializers.py:411-423)."""
+    with torch.no_grad():
+        step = X_rnd.shape[0] if batch_limit is None else batch_limit
+        out = [acq_function(X_rnd[i : i + step].to(device=device)).cpu() for i in range(0, X_rnd.shape[0], step)]
+    return torch.cat(out)
+
+
+# -------------------------------------------------------------------------------------------------
+# candidate generation (L-BFGS-B on the host, values/gradients from the GPU)
+# -------------------------------------------------------------------------------------------------
+def columnwise_clamp(X: Tensor, lower=None, upper=None, raise_on_violation: bool = False) -> Tensor:
+    out = X
+    if lower is not None:
+        out = torch.max(out, torch.as_tensor(lower, dtype=X.dtype, device=X.device).expand_as(out))
+    if upper is not None:
+        out = torch.min(out, torch.as_tensor(upper, dtype=X.dtype, device=X.device).expand_as(out))
+    if raise_on_violation and not bool(torch.allclose(X, out)):
+        raise RuntimeError("Original value(s) are out of bounds.")
+    return out
+
+
+def make_scipy_bounds(X: Tensor, lower_bounds=None, upper_bounds=None) -> Optional[_sciopt.Bounds]:
+    if lower_bounds is None and upper_bounds is None:
+        return None
+
+    def _expand(b, fill):
+        if b is None:
+            return np.full(X.numel(), fill)
+        return torch.as_tensor(b, dtype=X.dtype).expand_as(X.cpu()).reshape(-1).numpy().astype(np.float64)
+
+    return _sciopt.Bounds(lb=_expand(lower_bounds, -np.inf), ub=_expand(upper_bounds, np.inf), keep_feasible=True)
+
+
+class _Timeout(Exception):
+    def __init__(self, x):
+        self.x = x
+
+
+def gen_candidates_scipy(
+    initial_conditions: Tensor,
+    acquisition_function,
+    lower_bounds=None,
+    upper_bounds=None,
+    inequality_constraints=None,
+    equality_constraints=None,
+    nonlinear_inequality_constraints=None,
+    options: Optional[Dict] = None,
+    fixed_features: Optional[Dict[int, Optional[float]]] = None,
+    timeout_sec: Optional[float] = None,
+) -> Tuple[Tensor, Tensor]:
+    """Maximise the summed acquisition value of all restarts jointly with L-BFGS-B (gen.py:46-298).
+
+    Per function evaluation: host x -> device X, forward, ``torch.autograd.grad`` (the reverse CUDA kernels),
+    gradient -> host.  NaN in x or the gradient raises ``RuntimeError`` as in the reference.
+    """
+    if inequality_constraints or equality_constraints or nonlinear_inequality_constraints or fixed_features:
+        raise UnsupportedError("constraints / fixed features are outside the fused path")
+    options = dict(options or {})
+    options.setdefault("maxiter", 2000)
+    clamped = columnwise_clamp(initial_conditions, lower_bounds, upper_bounds)
+    shapeX = clamped.shape
+    x0 = clamped.reshape(-1).detach().cpu().numpy().astype(np.float64)
+    bounds = make_scipy_bounds(initial_conditions, lower_bounds, upper_bounds)
+    with_grad = options.get("with_grad", True)
+
+    def fun(x: np.ndarray):
+        if np.isnan(x).any():
+            raise RuntimeError(f"{np.isnan(x).sum()} elements of the {x.size} element array `x` are NaN.")
+        X = torch.from_numpy(x).to(initial_conditions).view(shapeX).contiguous()
+        if not with_grad:
+            with torch.no_grad():
+                return float((-acquisition_function(X)).sum())
+        X.requires_grad_(True)
+        loss = (-acquisition_function(X)).sum()
+        grad = torch.autograd.grad(loss, X)[0].contiguous().view(-1).cpu().numpy().astype(np.float64)
+        if np.isnan(grad).any():
+            msg = (f"{np.isnan(grad).sum()} elements of the {x.size} element gradient array `gradf` are NaN. "
+                   "This often indicates numerical issues.")  # fmt: skip
+            if initial_conditions.dtype != torch.double:
+                msg += " Consider using `dtype=torch.double`."
+            raise RuntimeError(msg)
+        return float(loss), grad
+
+    t0 = time.monotonic()
+    user_cb = options.get("callback")
+
+    def callback(xk):
+        if timeout_sec is not None and time.monotonic() - t0 > timeout_sec:
+            raise _Timeout(np.array(xk, copy=True))
+        if user_cb is not None:
+            user_cb(xk)
+
+    scipy_opts = {k: v for k, v in options.items() if k not in ("method", "callback", "with_grad")}
+    try:
+        res = _sciopt.minimize(fun=fun, x0=x0, method=options.get("method", "L-BFGS-B"), jac=with_grad, bounds=bounds,
+                               callback=callback, options=scipy_opts)  # fmt: skip
+        x_final, success, status, message = res.x, res.success, res.status, res.message
+    except _Timeout as e:
+        x_final, success, status = e.x, False, -1
+        message = f"Optimization timed out after {time.monotonic() - t0} seconds."
+    if not success and "disp" not in options:  # _process_scipy_result (gen.py:458-493)
+        msg = message if isinstance(message, str) else message.decode("ascii")
+        if status == -1:
+            warnings.warn(msg, OptimizationWarning)
+        elif "ITERATIONS REACHED LIMIT" in msg or "Iteration limit reached" in msg:
+            pass  # reaching maxiter is reported at INFO level only
+        else:
+            warnings.warn(
+                f"Optimization failed within `scipy.optimize.minimize` with status {status} and message {msg}.",
+                OptimizationWarning,
+            )
+    candidates = torch.from_numpy(x_final).to(initial_conditions).reshape(shapeX)
+    clamped = columnwise_clamp(candidates, lower_bounds, upper_bounds, raise_on_violation=True)
+    with torch.no_grad():
+        batch_acquisition = acquisition_function(clamped)
+    return clamped, batch_acquisition
+
+
+def get_best_candidates(batch_candidates: Tensor, batch_values: Tensor) -> Tensor:
+    best = torch.argmax(batch_values.view(-1), dim=0)
+    return batch_candidates[best]
+
+
+# -------------------------------------------------------------------------------------------------
+# optimize_acqf
+# -------------------------------------------------------------------------------------------------
+def optimize_acqf(
+    acq_function,
+    bounds: Tensor,
+    q: int,
+    num_restarts: int,
+    raw_samples: Optional[int] = None,
+    options: Optional[Dict[str, Union[bool, float, int, str]]] = None,
+    inequality_constraints=None,
+    equality_constraints=None,
+    nonlinear_inequality_constraints=None,
+    fixed_features: Optional[Dict[int, float]] = None,
+    post_processing_func: Optional[Callable[[Tensor], Tensor]] = None,
+    batch_initial_conditions: Optional[Tensor] = None,
+    return_best_only: bool = True,
+    gen_candidates: Optional[Callable] = None,
+    sequential: bool = False,
+    *,
+    ic_generator: Optional[Callable] = None,
+    timeout_sec: Optional[float] = None,
+    return_full_tree: bool = False,
+    retry_on_optimization_warning: bool = True,
+    **ic_gen_kwargs,
+) -> Tuple[Tensor, Tensor]:
+    """Multi-start maximisation of ``acq_function`` over the box ``bounds`` (optimize.py:397-543).
+
+    Joint (non-sequential) q-batch optimisation: raw samples -> initial conditions -> ``batch_limit`` chunks of
+    restarts, each optimised jointly by ``gen_candidates`` (default L-BFGS-B), one retry on an
+    ``OptimizationWarning``, best restart returned.
+    """
+    if inequality_constraints or equality_constraints or nonlinear_inequality_constraints or fixed_features:
+        raise UnsupportedError("constraints / fixed features are outside the fused path (SURVEY.md section 8)")
+    if sequential and q > 1:
+        raise UnsupportedError("sequential greedy optimisation is a 'next' row (SURVEY.md 8f N2); use sequential=False")
+    if not (bounds.ndim == 2 and bounds.shape[0] == 2):
+        raise ValueError(f"bounds should be a `2 x d` tensor, current shape: {list(bounds.shape)}.")
+    if batch_initial_conditions is None and raw_samples is None and ic_generator is None:
+        raise ValueError("Must specify `raw_samples` when `batch_initial_conditions` is None`.")
+    gen_candidates = gen_candidates or gen_candidates_scipy
+    ic_generator = ic_generator or gen_batch_initial_conditions
+    options = options or {}
+
+    def initial_conditions() -> Tensor:
+        return ic_generator(acq_function=acq_function, bounds=bounds, q=q, num_restarts=num_restarts,
+                            raw_samples=raw_samples, fixed_features=None,
+                            options={k: v for k, v in options.items() if k in INIT_OPTION_KEYS}, **ic_gen_kwargs)  # fmt: skip
+
+    provided_ics = batch_initial_conditions is not None
+    ics = batch_initial_conditions if provided_ics else initial_conditions()
+    batch_limit: int = options.get("batch_limit", num_restarts)
+    gen_options = {k: v for k, v in options.items() if k not in INIT_OPTION_KEYS}
+    start = time.monotonic()
+
+    def run(ics: Tensor):
+        cands, vals, ws_all = [], [], []
+        chunks = ics.split(batch_limit)
+        for chunk in chunks:
+            remaining = None if timeout_sec is None else max(timeout_sec - (time.monotonic() - start), 1e-3) / len(chunks)
+            with warnings.catch_warnings(record=True) as ws:
+                warnings.simplefilter("always", category=OptimizationWarning)
+                c, v = gen_candidates(chunk, acq_function, lower_bounds=bounds[0], upper_bounds=bounds[1],
+                                      options=gen_options, timeout_sec=remaining)  # fmt: skip
+            ws_all += [w for w in ws if issubclass(w.category, OptimizationWarning)]
+            for w in ws:
+                if not issubclass(w.category, OptimizationWarning):
+                    warnings.warn_explicit(w.message, w.category, w.filename, w.lineno)
+            cands.append(c)
+            vals.append(v)
+        return torch.cat(cands), torch.cat(vals), ws_all
+
+    batch_candidates, batch_acq_values, ws = run(ics)
+    if ws and retry_on_optimization_warning and not provided_ics:
+        warnings.warn(
+            "Optimization failed in `gen_candidates_scipy` with the following warning(s):\n"
+            f"{[w.message for w in ws]}\nTrying again with a new set of initial conditions.",
+            RuntimeWarning,
+        )
+        batch_candidates, batch_acq_values, ws = run(initial_conditions())
+        if ws:
+            warnings.warn("Optimization failed on the second try, after generating a new set of initial conditions.",
+                          RuntimeWarning)  # fmt: skip
+    elif ws:
+        for w in ws:
+            warnings.warn_explicit(w.message, w.category, w.filename, w.lineno)
+    if post_processing_func is not None:
+        batch_candidates = post_processing_func(batch_candidates)
+        with torch.no_grad():
+            batch_acq_values = acq_function(batch_candidates)
+    if return_best_only:
+        best = torch.argmax(batch_acq_values.view(-1), dim=0)
+        batch_candidates = batch_candidates[best]
+        batch_acq_values = batch_acq_values[best]
+    return batch_candidates, batch_acq_values

@@ -1,0 +1,209 @@
+"""Base-sample generation for the fused path (host side).
+
+Mirrors the reference's sampler contract so that base samples are bit-identical to BoTorch's:
+  * ``NormalQMCEngine``            botorch/sampling/qmc.py:25-101
+  * ``draw_sobol_samples`` /
+    ``draw_sobol_normal_samples``  botorch/utils/sampling.py:64-136
+  * ``manual_seed``                botorch/utils/sampling.py:40-61
+  * ``MCSampler``                  botorch/sampling/base.py:25-148
+  * ``NormalMCSampler`` & co       botorch/sampling/normal.py:25-209
+  * ``get_sampler`` (Sobol when the joint dimension fits SobolEngine.MAXDIM, else iid)
+                                    botorch/sampling/get_sampler.py
+
+The Sobol bits come from torch's own ``SobolEngine`` on the host, exactly as in the reference; the
+draw happens once per acquisition object and the result is copied to HBM, where the kernels stream
+it.  Applying the base samples (f = mu + L z) happens inside the CUDA kernels.
+"""
+from __future__ import annotations
+
+import math
+from contextlib import contextmanager
+from typing import Optional, Tuple
+
+import torch
+from torch import Tensor
+from torch.nn import Module
+from torch.quasirandom import SobolEngine
+
+from .exceptions import UnsupportedError
+
+
+@contextmanager
+def manual_seed(seed: Optional[int] = None):
+    """Seed torch's global RNG inside the block and restore its state afterwards."""
+    saved = None
+    if seed is not None:
+        saved = torch.random.get_rng_state()
+        torch.manual_seed(seed)
+    try:
+        yield
+    finally:
+        if saved is not None:
+            torch.random.set_rng_state(saved)
+
+
+class NormalQMCEngine:
+    """Quasi-random N(0, I_d) draws from a scrambled Sobol sequence.
+
+    ``inv_transform=True`` maps uniforms through the inverse normal CDF after shrinking them away
+    from {0, 1} by one ulp; otherwise consecutive pairs go through Box-Muller.
+    """
+
+    def __init__(self, d: int, seed: Optional[int] = None, inv_transform: bool = False) -> None:
+        self._d = d
+        self._seed = seed
+        self._inv_transform = inv_transform
+        sobol_dim = d if inv_transform else 2 * math.ceil(d / 2)
+        self._sobol_engine = SobolEngine(dimension=sobol_dim, scramble=True, seed=seed)
+
+    def draw(self, n: int = 1, out: Optional[Tensor] = None, dtype: Optional[torch.dtype] = None) -> Optional[Tensor]:
+        dtype = torch.get_default_dtype() if dtype is None else dtype
+        u = self._sobol_engine.draw(n, dtype=dtype)
+        if self._inv_transform:
+            v = 0.5 + (1 - torch.finfo(u.dtype).eps) * (u - 0.5)
+            z = torch.erfinv(2 * v - 1) * math.sqrt(2)
+        else:
+            even = torch.arange(0, u.shape[-1], 2)
+            radius = torch.sqrt(-2 * torch.log(u[:, even]))
+            angle = 2 * math.pi * u[:, 1 + even]
+            z = (radius.unsqueeze(-1) * torch.stack([torch.cos(angle), torch.sin(angle)], -1)).reshape(n, -1)
+            z = z[:, : self._d]
+        if out is None:
+            return z
+        out.copy_(z)
+        return None
+
+
+def draw_sobol_samples(
+    bounds: Tensor,
+    n: int,
+    q: int,
+    batch_shape: Optional[torch.Size] = None,
+    seed: Optional[int] = None,
+) -> Tensor:
+    """``n x batch_shape x q x d`` scrambled-Sobol points inside the box ``bounds`` (2 x d)."""
+    batch_shape = torch.Size(batch_shape or ())
+    d = bounds.shape[-1]
+    lower, width = bounds[0], bounds[1] - bounds[0]
+    engine = SobolEngine(q * d, scramble=True, seed=seed)
+    u = engine.draw(batch_shape.numel() * n, dtype=lower.dtype).view(*batch_shape, n, q, d).to(device=lower.device)
+    if len(batch_shape) > 0:  # the sample index leads
+        u = u.movedim(len(batch_shape), 0)
+    return lower + width * u
+
+
+def draw_sobol_normal_samples(
+    d: int,
+    n: int,
+    device: Optional[torch.device] = None,
+    dtype: Optional[torch.dtype] = None,
+    seed: Optional[int] = None,
+) -> Tensor:
+    """``n x d`` quasi-random standard normal draws (inverse-CDF Sobol)."""
+    engine = NormalQMCEngine(d=d, seed=seed, inv_transform=True)
+    return engine.draw(n, dtype=dtype).to(device=device)
+
+
+class MCSampler(Module):
+    """Holds the sample shape, the seed and the (t-batch collapsed) ``base_samples`` buffer."""
+
+    def __init__(self, sample_shape: torch.Size, seed: Optional[int] = None) -> None:
+        super().__init__()
+        if not isinstance(sample_shape, torch.Size):
+            raise ValueError(f"Expected `sample_shape` to be a `torch.Size` object, got {sample_shape}.")
+        self.sample_shape = sample_shape
+        self.seed = seed if seed is not None else int(torch.randint(0, 1000000, (1,)).item())
+        self.register_buffer("base_samples", None)
+
+    def forward(self, posterior) -> Tensor:  # pragma: no cover - abstract
+        raise NotImplementedError
+
+    def _get_batch_range(self, posterior) -> Tuple[int, int]:
+        return getattr(self, "batch_range_override", None) or posterior.batch_range
+
+    def _get_collapsed_shape(self, posterior) -> torch.Size:
+        """base-sample shape with every t-batch dimension set to 1 (one draw shared by all t-batches)."""
+        full = posterior.base_sample_shape
+        lo, hi = self._get_batch_range(posterior)
+        collapsed = full[:lo] + torch.Size([1] * len(full[lo:hi])) + full[hi:]
+        return self.sample_shape + collapsed
+
+    def _get_extended_base_sample_shape(self, posterior) -> torch.Size:
+        return self.sample_shape + posterior.base_sample_shape
+
+    def _instance_check(self, base_sampler) -> None:
+        if not isinstance(base_sampler, self.__class__):
+            raise RuntimeError(f"Expected `base_sampler` to be an instance of {self.__class__.__name__}.")
+
+
+class NormalMCSampler(MCSampler):
+    """Samplers whose base samples are standard normal."""
+
+    def forward(self, posterior) -> Tensor:
+        self._construct_base_samples(posterior=posterior)
+        return posterior.rsample_from_base_samples(
+            sample_shape=self.sample_shape,
+            base_samples=self.base_samples.expand(self._get_extended_base_sample_shape(posterior=posterior)),
+        )
+
+    def _construct_base_samples(self, posterior) -> None:  # pragma: no cover - abstract
+        raise NotImplementedError
+
+    def _update_base_samples(self, posterior, base_sampler: "NormalMCSampler") -> None:
+        """Redraw for ``posterior`` and overwrite the leading columns with ``base_sampler``'s draws.
+
+        This is what keeps the baseline points' base samples fixed when q new points are appended
+        (cached-Cholesky acquisition functions).  Single-output posteriors only: the points are the
+        last dimension of the base samples.
+        """
+        self._instance_check(base_sampler=base_sampler)
+        self._construct_base_samples(posterior=posterior)
+        prev = base_sampler.base_samples
+        if prev is None:
+            return
+        prev = prev.detach().clone()
+        target = self._get_collapsed_shape(posterior=posterior)
+        n_keep = prev.shape[-1]
+        ns = len(self.sample_shape)
+        lead = self.sample_shape + torch.Size([1] * (len(target) - prev.dim())) + prev.shape[ns:]
+        self.base_samples[..., :n_keep] = prev.reshape(lead).expand(target[:-1] + prev.shape[-1:])
+
+
+class IIDNormalSampler(NormalMCSampler):
+    """iid N(0,1) base samples (``torch.randn`` under a temporary seed)."""
+
+    def _construct_base_samples(self, posterior) -> None:
+        target = self._get_collapsed_shape(posterior=posterior)
+        if self.base_samples is None or self.base_samples.shape != target:
+            with manual_seed(seed=self.seed):
+                z = torch.randn(target, device=posterior.device, dtype=posterior.dtype)
+            self.register_buffer("base_samples", z)
+        if self.base_samples.device != posterior.device or self.base_samples.dtype != posterior.dtype:
+            self.to(device=posterior.device, dtype=posterior.dtype)
+
+
+class SobolQMCNormalSampler(NormalMCSampler):
+    """Scrambled-Sobol N(0,1) base samples through the inverse CDF."""
+
+    def _construct_base_samples(self, posterior) -> None:
+        target = self._get_collapsed_shape(posterior=posterior)
+        if self.base_samples is None or self.base_samples.shape != target:
+            dim = target[len(self.sample_shape) :].numel()
+            if dim > SobolEngine.MAXDIM:
+                raise UnsupportedError(
+                    f"SobolQMCSampler only supports dimensions `q * o <= {SobolEngine.MAXDIM}`. Requested: {dim}"
+                )
+            z = draw_sobol_normal_samples(
+                d=dim, n=self.sample_shape.numel(), device=posterior.device, dtype=posterior.dtype, seed=self.seed
+            )
+            self.register_buffer("base_samples", z.view(target))
+        self.to(device=posterior.device, dtype=posterior.dtype)
+
+
+def get_sampler(posterior, sample_shape: torch.Size, seed: Optional[int] = None) -> MCSampler:
+    """Sobol when the collapsed base-sample dimension fits ``SobolEngine.MAXDIM``, iid otherwise."""
+    lo, hi = posterior.batch_range
+    bss = posterior.base_sample_shape
+    dim = (bss[:lo] + bss[hi:]).numel()
+    cls = SobolQMCNormalSampler if dim <= SobolEngine.MAXDIM else IIDNormalSampler
+    return cls(sample_shape=sample_shape, seed=seed)

@@ -93,6 +93,11 @@ void bo_ctx_destroy(bo_ctx* ctx);
 long bo_launch_count(void);
 void bo_launch_count_reset(void);
 
+/* per-launch CUDA-event timing of the DMMA GEMM kernel (bench.py's roofline leg): enable, run, synchronise, read
+ * total milliseconds / launches / algorithmic flops (2MNK, halved for triangular operands) since enable. */
+void bo_prof_enable(int on);
+int bo_prof_read(double* ms, long* launches, double* flops);
+
 /* padded pitches used by every buffer of the ABI */
 long bo_pad8(long x);
 long bo_kp(int d);
@@ -135,6 +140,12 @@ size_t bo_posterior_workspace_bytes(const bo_gp* gp, long Nc);
  * Replaces BatchedMultiOutputGPyTorchModel.posterior (models/gpytorch.py:405-466). */
 int bo_posterior_joint(bo_ctx* ctx, const bo_gp* gp, int B, int q, const double* X, double* mean, double* cov,
                        void* work, size_t work_bytes, void* stream);
+/* grad_X[M x B x q x d] = d(sum mean_bar*mean + sum cov_bar*cov)/dX per model: the reverse pass torch.autograd
+ * runs through model.posterior when a caller differentiates posterior statistics (models/gpytorch.py:405-466
+ * with detached train caches, models/utils/assorted.py:294-296). */
+size_t bo_posterior_bwd_workspace_bytes(const bo_gp* gp, int B, int q);
+int bo_posterior_joint_bwd(bo_ctx* ctx, const bo_gp* gp, int B, int q, const double* X, const double* mean_bar,
+                           const double* cov_bar, double* grad_X, void* work, size_t work_bytes, void* stream);
 /* Marginal posterior at Nc points: mean, var [M x Nc].  The cross-covariance GEMM + triangular solve
  * of MaxPosteriorSampling at scale (generation/sampling.py:95-113, config C5). */
 int bo_posterior_mean_var(bo_ctx* ctx, const bo_gp* gp, long Nc, const double* Xc, double* mean, double* var,

@@ -1,0 +1,204 @@
+"""GPU parity of the reference-facing Python API (Model.posterior, posterior sampling, qLogNEI forward/backward via
+torch.autograd, optimize_acqf plumbing, Thompson sampling) against the CPU oracle."""
+import math
+import warnings
+
+import pytest
+import torch
+
+import botorch_b200 as bb
+from botorch_b200.synthetic import make_problem
+from oracle import qmc
+from tests.util import candidates, oracle_acq, oracle_gp, rel_err
+
+pytestmark = pytest.mark.gpu
+RTOL = 1e-9
+
+
+def _model(p, dev):
+    h = p.hypers
+    if p.kernel == "rbf":
+        return bb.SingleTaskGP(p.train_X.to(dev), p.train_Y.to(dev), lengthscale=h["lengthscale"], noise=h["noise"],
+                               mean_constant=h["mean"], outcome_transform="DEFAULT" if p.standardize else None)  # fmt: skip
+    m = bb.SaasFullyBayesianSingleTaskGP(p.train_X.to(dev), p.train_Y.to(dev))
+    m.load_mcmc_samples(h)
+    return m
+
+
+def _acqf(p, model, dev, **kw):
+    sampler = bb.SobolQMCNormalSampler(sample_shape=torch.Size([p.mc_samples]), seed=1234)
+    return bb.qLogNoisyExpectedImprovement(model, p.train_X.to(dev), sampler=sampler, **kw)
+
+
+@pytest.mark.parametrize("cfg,kw,bshape,q", [("C1", {}, (5,), 1), ("C2", {}, (3, 2), 4), ("C2", {"n": 77}, (), 3)])
+def test_posterior_mean_covariance_and_grad(cuda, cfg, kw, bshape, q):
+    p = make_problem(cfg, **kw)
+    ogp = oracle_gp(p)
+    model = _model(p, cuda)
+    X = candidates(p, max(math.prod(bshape), 1), q=q).reshape(*bshape, q, p.d)
+    Xd = X.to(cuda).requires_grad_(True)
+    post = model.posterior(Xd)
+    Xo = X.clone().requires_grad_(True)
+    m_ref, c_ref = ogp.posterior_direct(Xo)
+    assert post.mean.shape == (*bshape, q, 1) and post.variance.shape == (*bshape, q, 1)
+    assert rel_err(post.mean.squeeze(-1), m_ref) < RTOL
+    # variance tolerance relative to the prior scale: cancellation k** - |L^-1 k|^2
+    prior = float(ogp.y_std) ** 2
+    assert rel_err(post.distribution.covariance_matrix, c_ref, scale=prior) < RTOL
+    # gradient of a scalar functional of mean and covariance
+    w = torch.linspace(0.5, 1.5, q, dtype=torch.float64)
+    f = (post.mean.squeeze(-1) * w.to(cuda)).sum() + (post.distribution.covariance_matrix**2).sum()
+    (g,) = torch.autograd.grad(f, Xd)
+    f_ref = (m_ref * w).sum() + (c_ref**2).sum()
+    (g_ref,) = torch.autograd.grad(f_ref, Xo)
+    assert rel_err(g, g_ref) < 1e-8
+
+
+def test_posterior_observation_noise_and_errors(cuda):
+    p = make_problem("C1")
+    model = _model(p, cuda)
+    X = candidates(p, 4, q=2).to(cuda)
+    a, b = model.posterior(X), model.posterior(X, observation_noise=True)
+    ys2 = float(model.outcome_transform.stdvs) ** 2
+    assert torch.allclose(b.variance - a.variance, torch.full_like(a.variance, ys2 * float(p.hypers["noise"])))
+    with pytest.raises(bb.exceptions.BotorchTensorDimensionError):
+        model.posterior(torch.zeros(3, 5, device=cuda, dtype=torch.float64))
+    with pytest.raises(bb.exceptions.BotorchTensorDimensionError):
+        bb.SingleTaskGP(p.train_X, p.train_Y.squeeze(-1))
+    with pytest.warns(bb.exceptions.InputDataWarning):
+        bb.SingleTaskGP(p.train_X.float(), p.train_Y.float())
+
+
+def test_rsample_from_base_samples_is_mean_plus_chol_z(cuda):
+    """test/posteriors/test_gpytorch.py:28-96: samples == mean + chol(Sigma) z."""
+    p = make_problem("C2", n=50)
+    model = _model(p, cuda)
+    X = candidates(p, 6, q=5).to(cuda)
+    post = model.posterior(X)
+    S = 16
+    sampler = bb.SobolQMCNormalSampler(sample_shape=torch.Size([S]), seed=3)
+    samples = sampler(post)
+    assert samples.shape == (S, 6, 5, 1)
+    assert sampler.base_samples.shape == (S, 1, 5)  # collapsed over the t-batch
+    L = torch.linalg.cholesky(post.distribution.covariance_matrix.cpu())
+    z = sampler.base_samples.cpu().expand(S, 6, 5)
+    ref = post.mean.cpu().squeeze(-1) + torch.einsum("bij,sbj->sbi", L, z)
+    assert rel_err(samples.squeeze(-1), ref) < 1e-9
+    with pytest.raises(RuntimeError):
+        post.rsample_from_base_samples(torch.Size([S + 1]), sampler.base_samples.expand(S, 6, 5))
+    assert post.rsample(torch.Size([3])).shape == (3, 6, 5, 1)
+
+
+@pytest.mark.parametrize("cfg,kw,q,B", [("C1", {}, 1, 10), ("C2", {}, 4, 16), ("C3", {"n": 256}, 8, 6), ("C4", {"M": 5}, 4, 7)])
+def test_qlognei_forward_and_autograd_match_oracle(cuda, cfg, kw, q, B):
+    p = make_problem(cfg, **kw)
+    oacq = oracle_acq(p, oracle_gp(p))
+    model = _model(p, cuda)
+    acqf = _acqf(p, model, cuda)
+    X = candidates(p, B, q=q)
+    Xd = X.to(cuda).requires_grad_(True)
+    val = acqf(Xd)
+    assert val.shape == (B,)
+    (g,) = torch.autograd.grad((-val).sum(), Xd)  # the loss gen_candidates_scipy builds
+    a_ref, g_ref = oacq.value_and_grad(X, mode="faithful")
+    assert rel_err(val, a_ref, scale=0.0) < RTOL
+    scale = g_ref.flatten(1).abs().max(dim=1).values
+    assert float(((-g.cpu() - g_ref).flatten(1).abs().max(dim=1).values / scale).max()) < RTOL
+    # reference-named state
+    assert acqf._baseline_L.shape[-2:] == (p.n, p.n) and acqf.q_in == q
+    assert rel_err(acqf._baseline_best_f, oacq.best_f) < RTOL
+    assert rel_err(acqf.baseline_samples.squeeze(-1), oacq.baseline_samples) < 1e-8
+    with torch.no_grad():
+        assert torch.equal(acqf(X.to(cuda)), val.detach())
+    assert acqf(X[0].to(cuda)).shape == (1,)  # q x d input gains a t-batch dimension
+
+
+def test_qlognei_pending_points_and_errors(cuda):
+    p = make_problem("C2", n=60)
+    oacq = oracle_acq(p, oracle_gp(p))
+    model = _model(p, cuda)
+    X = candidates(p, 5, q=3)
+    pend = candidates(p, 1, q=1, seed=9)[0]
+    acqf = _acqf(p, model, cuda, X_pending=pend.to(cuda))
+    val = acqf(X.to(cuda))
+    ref = oacq.forward(torch.cat([X, pend.expand(5, 1, p.d)], dim=-2))
+    assert rel_err(val, ref, scale=0.0) < RTOL
+    with pytest.raises(ValueError):
+        acqf(torch.zeros(p.d, device=cuda, dtype=torch.float64))
+    with pytest.raises(bb.exceptions.UnsupportedError):
+        _acqf(p, model, cuda, objective=lambda s, X: s)
+    with pytest.raises(Exception):  # no CPU path
+        acqf(X)
+
+
+def test_optimize_acqf_improves_and_respects_bounds(cuda):
+    p = make_problem("C1")
+    model = _model(p, cuda)
+    acqf = _acqf(p, model, cuda)
+    bounds = torch.stack([torch.zeros(p.d), torch.ones(p.d)]).double().to(cuda)
+    cand, val = bb.optimize_acqf(acqf, bounds, q=2, num_restarts=4, raw_samples=64,
+                                 options={"seed": 0, "maxiter": 20, "batch_limit": 2, "init_batch_limit": 32})  # fmt: skip
+    assert cand.shape == (2, p.d) and val.shape == ()
+    assert bool(((cand >= 0) & (cand <= 1)).all())
+    X_rnd = bb.draw_sobol_samples(bounds.cpu(), n=64, q=2, seed=0)
+    with torch.no_grad():
+        y_raw = acqf(X_rnd.to(cuda))
+    assert float(val) >= float(y_raw.max()) - 1e-12  # the best raw sample is always among the restarts
+    assert float(acqf(cand)) == pytest.approx(float(val), rel=1e-12)
+
+
+def test_raw_sample_argmax_index_matches_oracle(cuda):
+    p = make_problem("C2")
+    oacq = oracle_acq(p, oracle_gp(p))
+    acqf = _acqf(p, _model(p, cuda), cuda)
+    bounds = torch.stack([torch.zeros(p.d), torch.ones(p.d)]).double()
+    X_rnd = bb.draw_sobol_samples(bounds, n=256, q=p.q, seed=5)
+    from botorch_b200.optim import evaluate_raw_samples
+
+    y = evaluate_raw_samples(acqf, X_rnd, cuda, batch_limit=100)
+    with torch.no_grad():
+        ref = torch.cat([oacq.forward(X_rnd[i : i + 64]) for i in range(0, 256, 64)])
+    assert int(torch.argmax(y)) == int(torch.argmax(ref))
+
+
+def test_thompson_sampling_marginal(cuda):
+    p = make_problem("C5", n=300)
+    ogp = oracle_gp(p)
+    model = _model(p, cuda)
+    Xc = qmc.sobol_box(torch.stack([torch.zeros(p.d), torch.ones(p.d)]).double(), 2000, 1, seed=1).squeeze(1)
+    ts = bb.MaxPosteriorSampling(model, replacement=False, chunk_size=512)
+    mean, var = ts.marginal_posterior(Xc.to(cuda))
+    m_ref, c_ref = ogp.posterior_direct(Xc.unsqueeze(1))
+    assert rel_err(mean[0], m_ref.squeeze(-1)) < RTOL
+    assert rel_err(var[0], c_ref.reshape(-1), scale=float(ogp.y_std) ** 2) < RTOL
+    g = torch.Generator(device=cuda).manual_seed(0)
+    picks = ts(Xc.to(cuda), num_samples=4, generator=g)
+    assert picks.shape == (4, p.d)
+    assert len({tuple(r.tolist()) for r in picks.cpu()}) == 4  # replacement=False
+    # a draw with zero noise is the posterior-mean maximiser
+    from botorch_b200 import _lib
+
+    val = torch.empty(1, dtype=torch.float64, device=cuda)
+    idx = torch.empty(1, dtype=torch.int64, device=cuda)
+    _lib.check(_lib.lib().bo_ts_argmax(_lib.ctx(cuda), 1, 2000, mean.data_ptr(), var.data_ptr(), None,
+                                       val.data_ptr(), idx.data_ptr(), _lib.stream_ptr(cuda)))  # fmt: skip
+    assert int(idx) == int(torch.argmax(m_ref.squeeze(-1)))
+
+
+def test_saas_posterior_mixture(cuda):
+    p = make_problem("C4", M=4)
+    ogp = oracle_gp(p)
+    model = _model(p, cuda)
+    X = candidates(p, 3, q=2)
+    post = model.posterior(X.to(cuda))
+    assert post.mean.shape == (3, 4, 2, 1)
+    m_ref, c_ref = ogp.posterior_direct(X)  # B x M x q
+    assert rel_err(post.mean.squeeze(-1), m_ref) < RTOL
+    assert rel_err(post.mixture_mean.squeeze(-1), m_ref.mean(dim=-2)) < RTOL
+    assert post.mixture_variance.shape == (3, 2, 1)
+    qv = post.quantile(torch.tensor(0.5, device=cuda, dtype=torch.float64))
+    assert qv.shape == (3, 2, 1)
+    sd = model.state_dict()
+    m2 = bb.SaasFullyBayesianSingleTaskGP(p.train_X.to(cuda), p.train_Y.to(cuda))
+    m2.load_state_dict(sd)
+    assert rel_err(m2.posterior(X.to(cuda)).mean, post.mean) < 1e-9
