@@ -114,10 +114,16 @@ def gather_best(values: Tensor, candidates: Tensor, index_offset: int) -> Tuple[
     on ties.  Returns (candidate q x d, value, global index) on every rank.
     """
     rank, ws = world()
-    li = int(torch.argmax(values.view(-1)))
-    best_val = values.view(-1)[li].reshape(1).to(torch.float64)
-    best_idx = torch.tensor([index_offset + li], dtype=torch.int64, device=values.device)
-    best_cand = candidates[li].to(torch.float64).contiguous()
+    if values.numel() == 0:  # a rank whose shard is empty (more ranks than restarts) never wins
+        best_val = torch.full((1,), -float("inf"), dtype=torch.float64, device=values.device)
+        best_idx = torch.full((1,), torch.iinfo(torch.int64).max, dtype=torch.int64, device=values.device)
+        best_cand = torch.zeros(candidates.shape[1:], dtype=torch.float64, device=values.device)
+        li = -1
+    else:
+        li = int(torch.argmax(values.view(-1)))
+        best_val = values.view(-1)[li].reshape(1).to(torch.float64)
+        best_idx = torch.tensor([index_offset + li], dtype=torch.int64, device=values.device)
+        best_cand = candidates[li].to(torch.float64).contiguous()
     if ws == 1:
         return candidates[li], values.view(-1)[li], int(best_idx)
     vals = [torch.empty_like(best_val) for _ in range(ws)]

@@ -162,7 +162,7 @@ def make_scipy_bounds(X: Tensor, lower_bounds=None, upper_bounds=None) -> Option
     def _expand(b, fill):
         if b is None:
             return np.full(X.numel(), fill)
-        return torch.as_tensor(b, dtype=X.dtype).expand_as(X.cpu()).reshape(-1).numpy().astype(np.float64)
+        return torch.as_tensor(b, dtype=X.dtype).cpu().expand(X.shape).reshape(-1).numpy().astype(np.float64)
 
     return _sciopt.Bounds(lb=_expand(lower_bounds, -np.inf), ub=_expand(upper_bounds, np.inf), keep_feasible=True)
 
@@ -215,7 +215,7 @@ def gen_candidates_scipy(
             if initial_conditions.dtype != torch.double:
                 msg += " Consider using `dtype=torch.double`."
             raise RuntimeError(msg)
-        return float(loss), grad
+        return float(loss.detach()), grad
 
     t0 = time.monotonic()
     user_cb = options.get("callback")

@@ -202,3 +202,36 @@ def test_saas_posterior_mixture(cuda):
     m2 = bb.SaasFullyBayesianSingleTaskGP(p.train_X.to(cuda), p.train_Y.to(cuda))
     m2.load_state_dict(sd)
     assert rel_err(m2.posterior(X.to(cuda)).mean, post.mean) < 1e-9
+
+
+def test_cuda_path_matches_committed_golden_fixtures(cuda):
+    """tests/golden/oracle_configs.pt (minted by tests/golden/make_golden.py): the CUDA path against committed numbers,
+    independent of the oracle code that travels with the repo."""
+    import os
+
+    gold = torch.load(os.path.join(os.path.dirname(__file__), "golden", "oracle_configs.pt"))
+    for tag in ("C1", "C2", "C3", "C4"):
+        c = gold[tag]
+        p = make_problem(c["cfg"], **c["kw"])
+        model = _model(p, cuda)
+        acqf = _acqf(p, model, cuda)
+        Xd = c["X"].to(cuda).requires_grad_(True)
+        val = acqf(Xd)
+        (g,) = torch.autograd.grad(val.sum(), Xd)
+        assert rel_err(val, c["acq"], scale=0.0) < RTOL, tag
+        scale = c["grad"].flatten(1).abs().max(dim=1).values
+        assert float(((g.cpu() - c["grad"]).flatten(1).abs().max(dim=1).values / scale).max()) < RTOL, tag
+        post = model.posterior(c["X"].to(cuda))
+        mean = post.mean.squeeze(-1)
+        assert rel_err(mean, c["mean"]) < RTOL, tag
+        raw = candidates(p, 128, q=c["q"], seed=c["raw_seed"])
+        with torch.no_grad():
+            y = acqf(raw.to(cuda))
+        assert int(torch.argmax(y)) == c["raw_argmax"], tag
+        assert float(y.max()) == pytest.approx(c["raw_max"], rel=1e-9)
+    c = gold["C5"]
+    p = make_problem("C5", **c["kw"])
+    ts = bb.MaxPosteriorSampling(_model(p, cuda))
+    mean, var = ts.marginal_posterior(c["X"].to(cuda))
+    assert rel_err(mean[0], c["mean"]) < RTOL
+    assert int(torch.argmax(mean[0])) == c["argmax_mean"]

@@ -1,0 +1,214 @@
+"""CPU tests of the host-side logic (no compute calls into the CUDA library): C-ABI symbols, samplers and their
+base-sample bookkeeping, initial-condition selection, shard arithmetic, error behaviour without a GPU."""
+import ctypes
+import os
+import re
+import warnings
+
+import pytest
+import torch
+
+import botorch_b200 as bb
+from botorch_b200 import distributed as bdist
+from botorch_b200 import exceptions as bex
+from botorch_b200 import optim as boptim
+from botorch_b200.acquisition import _ShapeOnlyPosterior
+from botorch_b200.build import LIB_PATH, build
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def test_library_builds_and_exports_every_declared_symbol():
+    path = build()
+    assert path == LIB_PATH and os.path.exists(path)
+    lib = ctypes.CDLL(path)
+    header = open(os.path.join(ROOT, "include", "botorch_b200.h")).read()
+    header = re.sub(r"/\*.*?\*/", "", header, flags=re.S)
+    names = set(re.findall(r"\b(bo_[a-z0-9_]+)\s*\(", header))
+    assert len(names) >= 25
+    missing = [n for n in sorted(names) if not hasattr(lib, n)]
+    assert not missing, missing
+    assert lib.bo_pad8(13) == 16 and lib.bo_kp(20) == 24
+    lib.bo_strerror.restype = ctypes.c_char_p
+    assert b"workspace" in lib.bo_strerror(3)
+
+
+def test_no_cpu_fallback():
+    if torch.cuda.is_available():
+        pytest.skip("GPU present")
+    X, Y = torch.rand(6, 2, dtype=torch.float64), torch.rand(6, 1, dtype=torch.float64)
+    model = bb.SingleTaskGP(X, Y)
+    with pytest.raises(Exception) as ei:
+        model.posterior(torch.rand(3, 1, 2, dtype=torch.float64))
+    assert "CPU" in str(ei.value) or "CUDA" in str(ei.value)
+    with pytest.raises(Exception):
+        bb.qLogNoisyExpectedImprovement(model, X)
+
+
+def test_product_package_never_imports_the_oracle():
+    pkg = os.path.join(ROOT, "botorch_b200")
+    for dirpath, _, files in os.walk(pkg):
+        for f in files:
+            if f.endswith(".py"):
+                src = open(os.path.join(dirpath, f)).read()
+                assert not re.search(r"^\s*(from|import)\s+oracle\b", src, flags=re.M), f
+
+
+def test_model_argument_validation_and_state_dict():
+    X, Y = torch.rand(5, 3, dtype=torch.float64), torch.rand(5, 1, dtype=torch.float64)
+    with pytest.raises(bex.BotorchTensorDimensionError):
+        bb.SingleTaskGP(X, Y.squeeze(-1))
+    with pytest.raises(bex.InputDataError):
+        bb.SingleTaskGP(X, Y.float())
+    with pytest.warns(bex.InputDataWarning):
+        bb.SingleTaskGP(X.float(), Y.float())
+    with pytest.raises(bex.UnsupportedError):
+        bb.SingleTaskGP(X, Y, train_Yvar=torch.ones_like(Y))
+    m = bb.SingleTaskGP(X, Y)
+    sd = m.state_dict()
+    for k in ("covar_module.raw_lengthscale", "likelihood.noise_covar.raw_noise", "mean_module.raw_constant",
+              "outcome_transform.means", "outcome_transform.stdvs"):  # fmt: skip
+        assert k in sd, k
+    assert sd["covar_module.raw_lengthscale"].shape == (1, 3)
+    assert torch.allclose(sd["outcome_transform.means"].reshape(()), Y.mean())
+    assert torch.allclose(m.train_targets.std(), torch.tensor(1.0, dtype=torch.float64))
+    sd2 = {k: v.clone() for k, v in sd.items()}
+    sd2["covar_module.raw_lengthscale"] = torch.full((1, 3), 0.7, dtype=torch.float64)
+    sd2["covar_module.raw_lengthscale_constraint.lower_bound"] = torch.tensor(0.025)  # extra reference key: ignored
+    m.load_state_dict(sd2)
+    assert torch.allclose(m._hypers()["lengthscale"], torch.full((3,), 0.7, dtype=torch.float64))
+    saas = bb.SaasFullyBayesianSingleTaskGP(X, Y)
+    with pytest.raises(RuntimeError):
+        saas.posterior(X)
+    saas.load_mcmc_samples({"mean": torch.zeros(4), "lengthscale": torch.ones(4, 3), "outputscale": torch.ones(4),
+                            "noise": torch.full((4,), 1e-6)})  # fmt: skip
+    assert saas.batch_shape == torch.Size([4]) and saas.num_mcmc_samples == 4
+    assert float(saas._hypers()["noise"].min()) == pytest.approx(1e-4)  # MIN_INFERRED_NOISE_LEVEL clamp
+    sd = saas.state_dict()
+    assert sd["covar_module.base_kernel.raw_lengthscale"].shape == (4, 1, 3)
+    saas2 = bb.SaasFullyBayesianSingleTaskGP(X, Y)
+    saas2.load_state_dict(sd)
+    assert torch.allclose(saas2._hypers()["lengthscale"], saas._hypers()["lengthscale"])
+    saas.train()
+    with pytest.raises(RuntimeError):
+        saas.num_mcmc_samples
+
+
+def test_sampler_shapes_seeding_and_baseline_columns():
+    """test/sampling/test_normal.py:75-116 + sampling/normal.py:68-131 on shape-only posteriors."""
+    S = torch.Size([8])
+    with pytest.raises(ValueError):
+        bb.SobolQMCNormalSampler(sample_shape=8)
+    post_b = _ShapeOnlyPosterior(torch.Size(), 5, torch.device("cpu"), torch.float64)
+    s1 = bb.SobolQMCNormalSampler(S, seed=1234)
+    s1._construct_base_samples(post_b)
+    assert s1.base_samples.shape == (8, 5)
+    first = s1.base_samples.clone()
+    s1._construct_base_samples(post_b)  # same shape: no redraw
+    assert torch.equal(s1.base_samples, first)
+    s2 = bb.SobolQMCNormalSampler(S, seed=1234)
+    s2._construct_base_samples(post_b)
+    assert torch.equal(s2.base_samples, first)  # seeded determinism
+    s3 = bb.SobolQMCNormalSampler(S, seed=1235)
+    s3._construct_base_samples(post_b)
+    assert not torch.equal(s3.base_samples, first)
+    # appending q = 3 points: t-batch collapsed, baseline columns preserved, same seed for the fresh draw
+    from copy import deepcopy
+
+    base = deepcopy(s1)
+    post_f = _ShapeOnlyPosterior(torch.Size([1]), 8, torch.device("cpu"), torch.float64)
+    s1._update_base_samples(post_f, base)
+    assert s1.base_samples.shape == (8, 1, 8)
+    assert torch.equal(s1.base_samples[:, 0, :5], first)
+    fresh = bb.draw_sobol_normal_samples(d=8, n=8, dtype=torch.float64, seed=1234)
+    assert torch.equal(s1.base_samples[:, 0, 5:], fresh[:, 5:])
+    # ensemble model: model batch dim collapsed too (posteriors/fully_bayesian.py:150-158)
+    e = bb.SobolQMCNormalSampler(S, seed=3)
+    e._construct_base_samples(_ShapeOnlyPosterior(torch.Size([6]), 5, torch.device("cpu"), torch.float64))
+    assert e.base_samples.shape == (8, 1, 5)
+    eb = deepcopy(e)
+    e._update_base_samples(_ShapeOnlyPosterior(torch.Size([1, 6]), 7, torch.device("cpu"), torch.float64), eb)
+    assert e.base_samples.shape == (8, 1, 1, 7) and torch.equal(e.base_samples[:, 0, 0, :5], eb.base_samples[:, 0])
+    with pytest.raises(RuntimeError):
+        e._update_base_samples(post_f, bb.IIDNormalSampler(S, seed=0))
+    iid = bb.IIDNormalSampler(S, seed=5)
+    iid._construct_base_samples(post_b)
+    iid2 = bb.IIDNormalSampler(S, seed=5)
+    iid2._construct_base_samples(post_b)
+    assert torch.equal(iid.base_samples, iid2.base_samples)
+    big = _ShapeOnlyPosterior(torch.Size(), 30000, torch.device("cpu"), torch.float64)
+    assert isinstance(bb.get_sampler(big, S), bb.IIDNormalSampler)
+    assert isinstance(bb.get_sampler(post_b, S), bb.SobolQMCNormalSampler)
+    with pytest.raises(bex.UnsupportedError):
+        bb.SobolQMCNormalSampler(S)._construct_base_samples(big)
+
+
+def test_initialize_q_batch_semantics():
+    """optim/initializers.py:893-965 and test/optim/test_initializers.py:131-243."""
+    torch.manual_seed(0)
+    X = torch.rand(40, 2, 3, dtype=torch.float64)
+    Y = torch.randn(40, dtype=torch.float64)
+    out = bb.initialize_q_batch(X, Y, n=5)
+    assert out.shape == (5, 2, 3)
+    best = X[int(torch.argmax(Y))]
+    assert any(torch.equal(o, best) for o in out)  # the argmax is always kept
+    assert bb.initialize_q_batch(X, Y, n=40) is X
+    with pytest.raises(RuntimeError):
+        bb.initialize_q_batch(X, Y, n=41)
+    with pytest.warns(bex.BadInitialCandidatesWarning):
+        r = bb.initialize_q_batch(X, torch.zeros(40, dtype=torch.float64), n=5)
+    assert r.shape == (5, 2, 3)
+    huge = torch.linspace(0, 1, 40, dtype=torch.float64)
+    huge[7] = 1e6  # exp overflow guard (eta halving)
+    out = bb.initialize_q_batch(X, huge, n=3, eta=1e3)
+    assert any(torch.equal(o, X[7]) for o in out)
+
+
+def test_optimize_acqf_plumbing_with_a_host_function():
+    """Control flow of optimize_acqf / gen_candidates_scipy on a closed-form acquisition (no GP)."""
+    target = torch.tensor([0.3, 0.7], dtype=torch.float64)
+
+    class Quad(torch.nn.Module):
+        calls = 0
+
+        def forward(self, X):
+            Quad.calls += 1
+            return -((X - target) ** 2).sum(dim=(-1, -2))
+
+    bounds = torch.stack([torch.zeros(2), torch.ones(2)]).double()
+    cand, val = bb.optimize_acqf(Quad(), bounds, q=1, num_restarts=6, raw_samples=32,
+                                 options={"seed": 1, "batch_limit": 4, "init_batch_limit": 10, "maxiter": 50})  # fmt: skip
+    assert cand.shape == (1, 2) and torch.allclose(cand[0], target, atol=1e-5) and float(val) > -1e-9
+    c_all, v_all = bb.optimize_acqf(Quad(), bounds, q=2, num_restarts=3, raw_samples=8, options={"seed": 1},
+                                    return_best_only=False)  # fmt: skip
+    assert c_all.shape == (3, 2, 2) and v_all.shape == (3,)
+    with pytest.raises(ValueError):
+        bb.optimize_acqf(Quad(), bounds, q=1, num_restarts=2)
+    with pytest.raises(bex.UnsupportedError):
+        bb.optimize_acqf(Quad(), bounds, q=1, num_restarts=2, raw_samples=4, fixed_features={0: 0.5})
+    # NaN from the acquisition function -> RuntimeError (gen.py:196-220)
+    nan_f = lambda X: (X * float("nan")).sum(dim=(-1, -2))  # noqa: E731
+    with pytest.raises(RuntimeError):
+        bb.gen_candidates_scipy(torch.rand(2, 1, 2, dtype=torch.float64), nan_f, bounds[0], bounds[1])
+    ics = torch.tensor([[[1.5, -0.2]]], dtype=torch.float64)  # out of bounds start is clamped
+    c, v = bb.gen_candidates_scipy(ics, Quad(), bounds[0], bounds[1], options={"maxiter": 5})
+    assert bool(((c >= 0) & (c <= 1)).all())
+    assert torch.equal(bb.get_best_candidates(c_all, v_all), c_all[int(torch.argmax(v_all))])
+    assert boptim.columnwise_clamp(ics, 0.0, 1.0).tolist() == [[[1.0, 0.0]]]
+    with pytest.raises(RuntimeError):
+        boptim.columnwise_clamp(ics, 0.0, 1.0, raise_on_violation=True)
+
+
+def test_shard_range_partitions_exactly():
+    for total in (0, 1, 7, 512, 32768, 1000003):
+        for ws in (1, 2, 3, 4, 8):
+            blocks = [bdist.shard_range(total, r, ws) for r in range(ws)]
+            assert blocks[0][0] == 0 and blocks[-1][1] == total
+            assert all(a[1] == b[0] for a, b in zip(blocks, blocks[1:]))
+            sizes = [hi - lo for lo, hi in blocks]
+            assert max(sizes) - min(sizes) <= 1
+    assert bdist.world() == (0, 1)
+    v = torch.tensor([1.0, 5.0, 5.0, 2.0], dtype=torch.float64)
+    c = torch.arange(4, dtype=torch.float64).reshape(4, 1, 1)
+    cand, val, idx = bdist.gather_best(v, c, index_offset=10)
+    assert idx == 11 and float(val) == 5.0 and float(cand) == 1.0  # first occurrence wins

@@ -1,0 +1,217 @@
+"""CPU tests: the oracle against the golden vectors recorded from the reference's own modules
+(tests/golden/reference_modules.pt, made by tests/golden/make_golden.py), its internal cross-checks, and the
+known-answer / property tests of the reference's suite (test/utils/test_safe_math.py, test/acquisition/test_logei.py)
+restated on the oracle."""
+import math
+import os
+
+import pytest
+import torch
+
+from botorch_b200 import sampling as bsampling
+from botorch_b200 import synthetic
+from botorch_b200.synthetic import make_problem
+from oracle import qmc, refstub, safe_math
+from oracle.qlognei import OracleQLogNEI
+from tests.util import candidates, oracle_acq, oracle_gp, rel_err
+
+GOLD = os.path.join(os.path.dirname(__file__), "golden")
+
+
+@pytest.fixture(scope="module")
+def ref_gold():
+    return torch.load(os.path.join(GOLD, "reference_modules.pt"))
+
+
+@pytest.fixture(scope="module")
+def cfg_gold():
+    return torch.load(os.path.join(GOLD, "oracle_configs.pt"))
+
+
+def _close(a, b, tol=1e-13):
+    a, b = torch.as_tensor(a), torch.as_tensor(b)
+    fin = torch.isfinite(b)
+    assert torch.equal(torch.isfinite(a), fin)
+    assert torch.equal(a[~fin], b[~fin]) or bool((torch.isnan(a[~fin]) == torch.isnan(b[~fin])).all())
+    if fin.any():
+        assert float(((a[fin] - b[fin]).abs() / b[fin].abs().clamp_min(1.0)).max()) <= tol
+
+
+# ---- reductions pinned to botorch/utils/safe_math.py ------------------------------------------------------------------------
+@pytest.mark.parametrize("tau", [1e-6, 1e-2, 1.0])
+def test_log_fatplus_matches_reference(ref_gold, tau):
+    c = ref_gold["safe_math"][f"log_fatplus_tau{tau:g}"]
+    x = c["x"].clone().requires_grad_(True)
+    v = safe_math.log_fatplus(x, tau=tau)
+    (g,) = torch.autograd.grad(v.sum(), x)
+    _close(v.detach(), c["value"])
+    _close(g, c["grad"], 1e-12)
+    _close(safe_math.fatplus(c["x"], tau=tau), ref_gold["safe_math"][f"fatplus_tau{tau:g}"]["value"])
+
+
+@pytest.mark.parametrize("tau", [1e-2, 1.0])
+def test_fatmax_matches_reference(ref_gold, tau):
+    c = ref_gold["safe_math"][f"fatmax_tau{tau:g}"]
+    x = c["x"].clone().requires_grad_(True)
+    v = safe_math.fatmax(x, dim=-1, tau=tau)
+    (g,) = torch.autograd.grad(v.sum(), x)
+    _close(v.detach(), c["value"])
+    _close(g, c["grad"], 1e-12)
+
+
+def test_logmeanexp_and_infinities_match_reference(ref_gold):
+    sm = ref_gold["safe_math"]
+    c = sm["logmeanexp_dim0"]
+    x = c["x"].clone().requires_grad_(True)
+    v = safe_math.logmeanexp(x, dim=0)
+    (g,) = torch.autograd.grad(v.sum(), x)
+    _close(v.detach(), c["value"])
+    _close(g, c["grad"], 1e-12)
+    for name, fn in (("fatmax_inf", lambda t: safe_math.fatmax(t, dim=-1, tau=1e-2)),
+                     ("logsumexp_inf", lambda t: safe_math.logsumexp(t, dim=-1)),
+                     ("logmeanexp_inf", lambda t: safe_math.logmeanexp(t, dim=-1))):  # fmt: skip
+        c = sm[name]
+        z = c["x"].clone().requires_grad_(True)
+        v = fn(z)
+        _close(v.detach(), c["value"])
+        (g,) = torch.autograd.grad(v[torch.isfinite(v)].sum(), z, allow_unused=True)
+        _close(g, c["grad"], 1e-12)
+
+
+def test_qlognei_reduction_chain_matches_reference(ref_gold):
+    c = ref_gold["safe_math"]["qlognei_chain"]
+    obj = c["obj"].clone().requires_grad_(True)
+    acq = safe_math.qlognei_reduction(obj, c["best_f"], 1e-6, 1e-2)
+    (g,) = torch.autograd.grad(acq.sum(), obj)
+    _close(acq.detach(), c["value"])
+    _close(g, c["grad"], 1e-12)
+
+
+def test_known_answers_of_test_logei(ref_gold):
+    """test_logei.py:324-395 / :429-501: baseline sample 0, new sample 1 -> exp(qLogNEI) == 1; batch -> [1, 0]."""
+    ka = ref_gold["known_answers"]
+    s = ka["single"]
+    best = s["baseline"].max(dim=-1).values.unsqueeze(-1)  # S x 1
+    acq = safe_math.qlognei_reduction(s["new"], best, 1e-6, 1e-2)
+    assert abs(float(acq.exp()) - s["exp_acq"]) < 1e-5
+    b = ka["batch"]
+    acq = safe_math.qlognei_reduction(b["new"], best, 1e-6, 1e-2)
+    assert torch.allclose(acq.exp(), torch.tensor(b["exp_acq"], dtype=torch.float64), atol=1e-6)
+
+
+# ---- closed-form properties of test/utils/test_safe_math.py --------------------------------------------------------------------
+def test_safe_math_properties():
+    torch.manual_seed(0)
+    x = torch.rand(50, 9, dtype=torch.float64) + 0.1
+    assert torch.allclose(safe_math.logmeanexp(x.log(), dim=0), x.mean(0).log(), atol=1e-14)  # :244-269
+    z = torch.zeros(1, dtype=torch.float64, requires_grad=True)  # :291-300 _pareto(0)=1, p'(0) = -1 convention
+    p = safe_math.pareto(z, alpha=2.0)
+    assert float(p) == 1.0
+    y = torch.randn(200, 6, dtype=torch.float64, requires_grad=True)
+    for tau in (1e-3, 1e-2, 1.0):
+        fm = safe_math.fatmax(y, dim=-1, tau=tau)
+        assert bool(((fm - y.amax(-1)).abs() <= math.log(6) * tau + 1e-12).all())  # :360-364
+        (g,) = torch.autograd.grad(fm.sum(), y)
+        assert torch.allclose(g.sum(-1), torch.ones(200, dtype=torch.float64), atol=1e-12)  # :390-391
+        assert bool((g >= 0).all())
+    t = torch.linspace(-5, 5, 101, dtype=torch.float64)
+    for tau in (1e-3, 1e-1):
+        assert bool(((safe_math.fatplus(t, tau) - t.clamp_min(0)).abs() <= tau).all())  # :308-342
+        assert bool((safe_math.fatplus(t, tau) > 0).all())
+
+
+# ---- Sobol draws pinned to botorch/sampling/qmc.py + botorch/utils/sampling.py ------------------------------------------------
+def test_sobol_draws_match_reference(ref_gold):
+    q = ref_gold["qmc"]
+    for d, n, seed in ((3, 8, 0), (21, 16, 1234), (204, 32, 1234), (108, 4, 7)):
+        want = q[f"normal_d{d}_n{n}_seed{seed}"]
+        assert torch.equal(qmc.sobol_normal(d, n, seed), want)  # oracle
+        assert torch.equal(bsampling.draw_sobol_normal_samples(d, n, dtype=torch.float64, seed=seed), want)  # product
+    bounds = torch.tensor([[0.0, -1.0, 2.0], [1.0, 1.0, 5.0]], dtype=torch.float64)
+    assert torch.equal(qmc.sobol_box(bounds, 8, 2, 0), q["box_n8_q2_seed0"])
+    assert torch.equal(bsampling.draw_sobol_samples(bounds, 8, 2, seed=0), q["box_n8_q2_seed0"])
+    got = bsampling.draw_sobol_samples(bounds, 4, 1, batch_shape=torch.Size([3]), seed=5)
+    assert torch.equal(got, q["box_n4_q1_batch3_seed5"])
+    eng = bsampling.NormalQMCEngine(d=5, seed=11, inv_transform=False)
+    assert torch.equal(eng.draw(6, dtype=torch.float64), q["boxmuller_d5_n6_seed11"])
+
+
+def test_synthetic_functions_match_reference(ref_gold):
+    s = ref_gold["synthetic"]
+    _close(synthetic.branin(s["branin"]["X"]), s["branin"]["f"], 1e-14)
+    _close(synthetic.hartmann6(s["hartmann6"]["X"]), s["hartmann6"]["f"], 1e-14)
+    _close(synthetic.ackley(s["ackley20"]["X"]), s["ackley20"]["f"], 1e-14)
+
+
+@pytest.mark.skipif(not refstub.available(), reason="/root/reference is not present on this machine")
+def test_golden_file_is_reproducible_from_the_live_reference(ref_gold):
+    ref = refstub.load()
+    want = ref_gold["qmc"]["normal_d21_n16_seed1234"]
+    assert torch.equal(ref.sampling.draw_sobol_normal_samples(d=21, n=16, dtype=torch.float64, seed=1234), want)
+    x = ref_gold["safe_math"]["fatmax_tau0.01"]["x"]
+    assert torch.equal(ref.safe_math.fatmax(x, dim=-1, tau=1e-2), ref_gold["safe_math"]["fatmax_tau0.01"]["value"])
+
+
+# ---- the GP part of the oracle: two independent formulations + the reference's self-consistency identities -----------------
+@pytest.mark.parametrize("cfg,kw,q", [("C1", {}, 2), ("C2", {"n": 80}, 4), ("C4", {"n": 40, "M": 3}, 3), ("C2", {"n": 50, "noise": 1e-4}, 4)])
+def test_posterior_formulations_agree(cfg, kw, q):
+    p = make_problem(cfg, **kw)
+    gp = oracle_gp(p)
+    X = candidates(p, 5, q=q)
+    m1, c1 = gp.posterior(X)  # L^-T GEMM form (fast_pred_var)
+    m2, c2 = gp.posterior_direct(X)  # cholesky_solve form
+    scale = float(gp.y_std) ** 2 * float(p.hypers.get("outputscale", torch.ones(1)).max() if p.hypers.get("outputscale") is not None else 1.0)
+    assert rel_err(m1, m2) < 1e-11
+    assert rel_err(c1, c2, scale=scale) < 1e-10
+    mq, Sqb, Sqq = gp.posterior_minimal_blocks(X, p.train_X)
+    assert rel_err(mq, m2) < 1e-11 and rel_err(Sqq, c2, scale=scale) < 1e-10
+
+
+@pytest.mark.parametrize("cfg,kw,q", [("C1", {}, 1), ("C1", {}, 3), ("C2", {"n": 40}, 4), ("C4", {"n": 30, "M": 2}, 2)])
+def test_cached_equals_uncached_and_minimal(cfg, kw, q):
+    """test_logei.py:559-676 (cache_root True == False, value and X-gradient) and test_low_rank.py:45-207."""
+    p = make_problem(cfg, **kw)
+    acq = oracle_acq(p, oracle_gp(p))
+    X = candidates(p, 4, q=q)
+    a1, g1 = acq.value_and_grad(X, "faithful")
+    a2, g2 = acq.value_and_grad(X, "minimal")
+    a3, g3 = acq.value_and_grad(X, "uncached")
+    assert rel_err(a2, a1, scale=0.0) < 1e-10 and rel_err(a3, a1, scale=0.0) < 1e-8
+    assert rel_err(g2, g1) < 1e-9 and rel_err(g3, g1) < 1e-6
+
+
+def test_oracle_outputs_match_committed_fixture(cfg_gold):
+    """The oracle itself is pinned: any change to oracle/ that moves a number fails here."""
+    for tag in ("C1", "C2", "C3", "C4"):
+        c = cfg_gold[tag]
+        p = make_problem(c["cfg"], **c["kw"])
+        gp = oracle_gp(p)
+        acq = oracle_acq(p, gp)
+        mean, cov = gp.posterior(c["X"])
+        val, grad = acq.value_and_grad(c["X"], "faithful")
+        assert rel_err(mean, c["mean"]) < 1e-12 and rel_err(cov, c["cov"]) < 1e-10
+        assert rel_err(val, c["acq"], scale=0.0) < 1e-10 and rel_err(grad, c["grad"]) < 1e-8
+        raw = candidates(p, 128, q=c["q"], seed=c["raw_seed"])
+        with torch.no_grad():
+            assert int(torch.argmax(acq.forward(raw))) == c["raw_argmax"]
+
+
+def test_psd_safe_cholesky_semantics():
+    from oracle.gp import NanError, NotPSDError, NumericalWarning, psd_safe_cholesky
+
+    A = torch.tensor([[1.0, 1.0], [1.0, 1.0 - 1e-12]], dtype=torch.float64)
+    with pytest.warns(NumericalWarning):
+        L = psd_safe_cholesky(A)
+    assert torch.allclose(L @ L.mT, A, atol=1e-7)
+    with pytest.raises(NanError):
+        psd_safe_cholesky(torch.full((2, 2), float("nan"), dtype=torch.float64))
+    with pytest.raises(NotPSDError), pytest.warns(NumericalWarning):
+        psd_safe_cholesky(-torch.eye(2, dtype=torch.float64))
+
+
+def test_base_sample_layout_of_qlognei():
+    """sampling/normal.py:68-131: appending q points keeps the baseline columns of the base samples."""
+    zb, zq = qmc.qlognei_base_samples(S=8, n_b=5, q=3, seed=1234)
+    assert zb.shape == (8, 5) and zq.shape == (8, 3)
+    assert torch.equal(zb, qmc.sobol_normal(5, 8, 1234))
+    assert torch.equal(zq, qmc.sobol_normal(8, 8, 1234)[:, 5:])
