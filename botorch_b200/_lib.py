@@ -36,6 +36,7 @@ class BoGP(C.Structure):
         ("linv_aug", C.c_void_p),
         ("linv_aug_t", C.c_void_p),
         ("chol", C.c_void_p),
+        ("xt_aug", C.c_void_p),
     ]
 
 
@@ -57,6 +58,8 @@ class BoNEI(C.Structure):
         ("zb_t", C.c_void_p),
         ("mean_b", C.c_void_p),
         ("best_f", C.c_void_p),
+        ("qmat", C.c_void_p),
+        ("qmat_t", C.c_void_p),
     ]
 
 

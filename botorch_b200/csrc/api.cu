@@ -78,7 +78,7 @@ BoKernelHyper hyper_of(const bo_gp* gp) {
 
 // covariance matrix from augmented operands: C[z] = k(A_aug[z] . B_aug[z])
 int kmat(const bo_gp* gp, const double* A_aug, int rows, const double* B_aug, long ldb, long cols, double* C, long ldc,
-         long strideC, int diag_exact, const double* diag_add, cudaStream_t st) {
+         long strideC, int diag_exact, const double* diag_add, cudaStream_t st, double* C2 = nullptr) {
     const long Kp = bo_kp(gp->d);
     BoGemm g{};
     g.A = A_aug; g.lda = Kp; g.strideA = (long)rows * Kp;
@@ -87,6 +87,7 @@ int kmat(const bo_gp* gp, const double* A_aug, int rows, const double* B_aug, lo
     g.M = rows; g.N = (int)cols; g.K = (int)Kp; g.batch = gp->M;
     g.epi = gp->kernel_id == BO_KERNEL_RBF ? BO_EPI_RBF : BO_EPI_MATERN52;
     g.os = gp->outputscale; g.diag_add = diag_add; g.diag_exact = diag_exact;
+    g.C2 = C2; g.ldc2 = ldc; g.strideC2 = strideC;
     return bo_gemm_launch(g, st);
 }
 
@@ -179,6 +180,11 @@ int bo_gp_setup(bo_ctx* ctx, const bo_gp* gp, void* work, size_t work_bytes, int
     BO_CUDA_TRY(cudaMemsetAsync(info, 0, sizeof(int32_t) * M, st));
     BO_TRY(bo_aug_rows(h, gp->train_X, n, gp->aug_train, Kp, n * Kp, st));
     BO_TRY(bo_aug_cols(h, gp->train_X, n, baug, Kp, np, Kp * np, st));
+    if (gp->xt_aug) {  // [train_X^T; 1]: operand of the gradient contraction (bo_qlognei_bwd step 6)
+        BO_TRY(bo_fill(gp->xt_aug, (long)(gp->d + 1) * np, 0.0, st));
+        BO_TRY(bo_transpose(gp->train_X, gp->d, 0, gp->xt_aug, np, 0, (int)n, gp->d, 1, st));
+        BO_TRY(bo_fill(gp->xt_aug + (long)gp->d * np, n, 1.0, st));
+    }
     vec_add_kernel<<<(unsigned)((M + 127) / 128), 128, 0, st>>>(gp->noise, gp->jitter, nz, (int)M);
     g_bo_launch_count++;
     // K + (s2 + jitter) I, unit diagonal of the kernel enforced exactly (x1_eq_x2 branch of gpytorch's sq_dist)
@@ -202,7 +208,7 @@ int bo_gp_setup(bo_ctx* ctx, const bo_gp* gp, void* work, size_t work_bytes, int
 }
 
 static size_t nei_setup_layout(const bo_gp* gp, const bo_nei* nei, void* work, size_t cap, double** baug_b,
-                               double** kb, double** fb, double** scratch, double** nz, bool* ok) {
+                               double** kb, double** fb, double** scratch, double** nz, double** khinv, bool* ok) {
     const long n = gp->n, M = gp->M, nb = nei->n_b, nbp = bo_pad8(nb), Sp = bo_pad8(nei->S), Kp = bo_kp(gp->d);
     Bump b(work, cap);
     *baug_b = b.doubles(M * Kp * nbp);
@@ -210,14 +216,15 @@ static size_t nei_setup_layout(const bo_gp* gp, const bo_nei* nei, void* work, s
     *fb = b.doubles(M * nb * Sp);
     *scratch = b.doubles(bo_linalg_scratch_doubles((int)nb, (int)M));
     *nz = b.doubles(M);
+    *khinv = nei->baseline_is_train ? b.doubles(M * n * bo_pad8(n)) : nullptr;  // (K + s2 I)^-1
     *ok = b.ok;
     return b.off;
 }
 
 size_t bo_nei_setup_workspace_bytes(const bo_gp* gp, const bo_nei* nei) {
-    double *a, *b, *c, *d, *e;
+    double *a, *b, *c, *d, *e, *f;
     bool ok;
-    return nei_setup_layout(gp, nei, nullptr, 0, &a, &b, &c, &d, &e, &ok);
+    return nei_setup_layout(gp, nei, nullptr, 0, &a, &b, &c, &d, &e, &f, &ok);
 }
 
 int bo_nei_setup(bo_ctx* ctx, const bo_gp* gp, const bo_nei* nei, void* work, size_t work_bytes, int32_t* info,
@@ -228,9 +235,9 @@ int bo_nei_setup(bo_ctx* ctx, const bo_gp* gp, const bo_nei* nei, void* work, si
     const long n = gp->n, M = gp->M, np = bo_pad8(n), nb = nei->n_b, nbp = bo_pad8(nb), S = nei->S, Sp = bo_pad8(S);
     const long Kp = bo_kp(gp->d);
     const double ys2 = gp->y_std * gp->y_std;
-    double *baug_b, *kb, *fb, *scratch, *nz;
+    double *baug_b, *kb, *fb, *scratch, *nz, *khinv;
     bool ok;
-    nei_setup_layout(gp, nei, work, work_bytes, &baug_b, &kb, &fb, &scratch, &nz, &ok);
+    nei_setup_layout(gp, nei, work, work_bytes, &baug_b, &kb, &fb, &scratch, &nz, &khinv, &ok);
     if (!ok) return BO_ERR_WORKSPACE;
     const BoKernelHyper h = hyper_of(gp);
     BO_CUDA_TRY(cudaMemsetAsync(info, 0, sizeof(int32_t) * M, st));
@@ -268,6 +275,24 @@ int bo_nei_setup(bo_ctx* ctx, const bo_gp* gp, const bo_nei* nei, void* work, si
     BO_TRY(gemm((int)nb, (int)S, (int)nb, (int)M, 1.0, nei->lb, nbp, nb * nbp, nei->zb_t, Sp, 0, 0.0, nullptr, 0, 0, fb, Sp,
                 nb * Sp, BO_TRI_A_LOWER, 0, st));
     BO_TRY(bo_col_max(fb, nb * Sp, Sp, nei->mean_b, nbp, (int)nb, (int)S, (int)M, nei->best_f, Sp, st));
+    if (nei->baseline_is_train && nei->qmat && nei->qmat_t) {
+        // X_baseline == train_X: Sigma(X_b, X) = ys^2 (K - K Khat^-1 K_x) = ys^2 s2 Khat^-1 K_x with Khat = K + s2 I,
+        // so bl_chol^T = inv(L_b) Sigma(X_b, X) = Q K(X_tr, X),  Q = ys^2 s2 inv(L_b) Khat^-1  (no cancellation).
+        vec_add_kernel<<<(unsigned)((M + 127) / 128), 128, 0, st>>>(gp->noise, gp->jitter, nz, (int)M);
+        g_bo_launch_count++;
+        const long n1p = bo_pad8(n + 1);
+        BO_TRY(gemm((int)n, (int)n, (int)n, (int)M, 1.0, gp->linv_aug_t, n1p, n * n1p, gp->linv_aug, np, (n + 1) * np, 0.0,
+                    nullptr, 0, 0, khinv, np, n * np, BO_TRI_A_UPPER, 0, st));
+        BoGemm g{};
+        g.A = nei->lb_inv; g.lda = nbp; g.strideA = nb * nbp;
+        g.B = khinv; g.ldb = np; g.strideB = n * np;
+        g.C = nei->qmat; g.ldc = np; g.strideC = nb * np;
+        g.CT = nei->qmat_t; g.ldct = nbp; g.strideCT = n * nbp;
+        g.alpha = ys2; g.alpha_vec = nz; g.M = (int)nb; g.N = (int)n; g.K = (int)nb; g.batch = (int)M;
+        g.tri = BO_TRI_A_LOWER; g.epi = BO_EPI_LINEAR;
+        BO_TRY(bo_fill(nei->qmat_t, M * n * nbp, 0.0, st));
+        BO_TRY(bo_gemm_launch(g, st));
+    }
     BO_CUDA_TRY(cudaGetLastError());
     return BO_OK;
 }
@@ -281,7 +306,9 @@ namespace {
 
 struct QWork {
     long ldn, R, regionStride;
-    double *baug, *W0, *W1, *W2, *W3, *F, *W5, *W6, *Lq, *lse, *Sbar;
+    double *baug, *W0, *W1, *W2, *W3, *F, *W5, *W6, *Lq, *lse, *Sbar, *Wd, *H;
+    long strideH;
+    bool qpath;  // X_baseline == train_X with a precomputed Q (bo_nei.qmat): bl_chol^T = Q K(X_tr, X)
     int32_t* info;
     bool ok;
     size_t bytes;
@@ -305,9 +332,15 @@ QWork qlayout(const bo_gp* gp, const bo_nei* nei, int B, int q, int with_grad, v
     w.lse = b.doubles(M * (long)B);
     w.info = reinterpret_cast<int32_t*>(b.doubles((M * (long)B + 1) / 2));
     w.W6 = nei->baseline_is_train ? nullptr : b.doubles(M * w.regionStride);
+    w.qpath = nei->baseline_is_train && nei->qmat && nei->qmat_t && gp->xt_aug;
     if (with_grad) {
         w.W5 = b.doubles(M * w.regionStride);
         w.Sbar = b.doubles(M * (long)B * q * q);
+        if (w.qpath) {
+            w.strideH = (long)(gp->d + 1) * w.ldn;
+            w.H = b.doubles(M * w.strideH);
+            if (gp->kernel_id != BO_KERNEL_RBF) w.Wd = b.doubles(M * w.regionStride);  // Matern derivative factor
+        }
     }
     w.ok = b.ok;
     w.bytes = b.off;
@@ -357,7 +390,8 @@ int bo_qlognei_fwd(bo_ctx* ctx, const bo_gp* gp, const bo_nei* nei, int B, int q
     const BoKernelHyper h = hyper_of(gp);
     // 1. K(X_tr, X) (and K(X_b, X)) through the augmented squared-distance contraction
     BO_TRY(bo_aug_cols(h, X, N, w.baug, Kp, w.ldn, Kp * w.ldn, st));
-    BO_TRY(kmat(gp, gp->aug_train, (int)n, w.baug, w.ldn, N, w.W0, w.ldn, w.regionStride, 0, nullptr, st));
+    BO_TRY(kmat(gp, gp->aug_train, (int)n, w.baug, w.ldn, N, w.W0, w.ldn, w.regionStride, 0, nullptr, st,
+                with_grad ? w.Wd : nullptr));
     const double* KB = w.W0;
     if (!nei->baseline_is_train) {
         BO_TRY(kmat(gp, nei->aug_b, (int)nb, w.baug, w.ldn, N, w.W6, w.ldn, w.regionStride, 0, nullptr, st));
@@ -366,12 +400,18 @@ int bo_qlognei_fwd(bo_ctx* ctx, const bo_gp* gp, const bo_nei* nei, int B, int q
     // 2. V = [inv(L); alpha^T] K(X_tr, X)           (n+1) x N
     BO_TRY(gemm((int)n + 1, (int)N, (int)n, (int)M, 1.0, gp->linv_aug, np, (n + 1) * np, w.W0, w.ldn, w.regionStride, 0.0,
                 nullptr, 0, 0, w.W1, w.ldn, w.regionStride, BO_TRI_A_LOWER, 0, st));
+    if (w.qpath) {
+        // 3+4. bl_chol^T = Q K(X_tr, X): one dense GEMM instead of the Schur GEMM + the triangular solve
+        BO_TRY(gemm((int)nb, (int)N, (int)n, (int)M, 1.0, nei->qmat, np, nb * np, w.W0, w.ldn, w.regionStride, 0.0, nullptr,
+                    0, 0, w.W3, w.ldn, w.regionStride, BO_TRI_NONE, 0, st));
+    } else {
     // 3. Sigma(X_b, X) = ys^2 (K(X_b, X) - V_b^T V)   n_b x N
     BO_TRY(gemm((int)nb, (int)N, (int)n, (int)M, -ys2, nei->vb_t, np, nb * np, w.W1, w.ldn, w.regionStride, ys2, KB, w.ldn,
                 w.regionStride, w.W2, w.ldn, w.regionStride, BO_TRI_NONE, 0, st));
     // 4. bl_chol^T = inv(L_b) Sigma(X_b, X)
     BO_TRY(gemm((int)nb, (int)N, (int)nb, (int)M, 1.0, nei->lb_inv, nbp, nb * nbp, w.W2, w.ldn, w.regionStride, 0.0,
                 nullptr, 0, 0, w.W3, w.ldn, w.regionStride, BO_TRI_A_LOWER, 0, st));
+    }
     // 5. baseline part of the samples: Z_b bl_chol^T    S x N
     BO_TRY(gemm((int)S, (int)N, (int)nb, (int)M, 1.0, nei->zb_pad, nbp, 0, w.W3, w.ldn, w.regionStride, 0.0, nullptr, 0, 0,
                 w.F, w.ldn, S * w.ldn, BO_TRI_NONE, 0, st));
@@ -408,7 +448,31 @@ int bo_qlognei_bwd(bo_ctx* ctx, const bo_gp* gp, const bo_nei* nei, int B, int q
     // 2. BLbar = Z_b^T dF - 2 BL Sbar                       (W2)
     BO_TRY(gemm((int)nb, (int)N, (int)S, (int)M, 1.0, nei->zb_t, Sp, 0, w.F, w.ldn, S * w.ldn, 0.0, nullptr, 0, 0, w.W2,
                 w.ldn, w.regionStride, BO_TRI_NONE, 0, st));
-    BO_TRY(bo_colblock_update(w.W2, w.regionStride, w.W3, w.regionStride, w.Sbar, (int)nb, B, q, (int)M, w.ldn, -2.0, st));
+    BO_TRY(bo_colblock_update(w.W2, w.regionStride, w.W3, w.regionStride, w.Sbar, (int)nb, B, q, (int)M, w.ldn, -2.0, 1, st));
+    if (w.qpath) {
+        const long np = bo_pad8(n);
+        (void)np;
+        // 3q. Vbar = -2 ys^2 V Sbar (rows 0..n-1 of W5; row n already holds y_std * mubar)
+        BO_TRY(bo_colblock_update(w.W5, w.regionStride, w.W1, w.regionStride, w.Sbar, (int)n, B, q, (int)M, w.ldn,
+                                  -2.0 * ys2, 0, st));
+        // 4q. T = Q^T BLbar                                  (W3; BL is dead from here on)
+        BO_TRY(gemm((int)n, (int)N, (int)nb, (int)M, 1.0, nei->qmat_t, nbp, n * nbp, w.W2, w.ldn, w.regionStride, 0.0, nullptr,
+                    0, 0, w.W3, w.ldn, w.regionStride, BO_TRI_NONE, 0, st));
+        // 5q. G = ([inv(L)^T | alpha] Vbar + T) .* g(r),  g = K for RBF, the stored derivative factor for Matern   (W2)
+        BoGemm g{};
+        g.A = gp->linv_aug_t; g.lda = n1p; g.strideA = n * n1p;
+        g.B = w.W5; g.ldb = w.ldn; g.strideB = w.regionStride;
+        g.C = w.W2; g.ldc = w.ldn; g.strideC = w.regionStride;
+        g.D = w.W3; g.ldd = w.ldn; g.strideD = w.regionStride;
+        g.E = w.Wd ? w.Wd : w.W0; g.lde = w.ldn; g.strideE = w.regionStride;
+        g.alpha = 1.0; g.beta = 1.0; g.M = (int)n; g.N = (int)N; g.K = (int)n + 1; g.batch = (int)M;
+        g.tri = BO_TRI_A_UPPER; g.epi = BO_EPI_LINEAR;
+        BO_TRY(bo_gemm_launch(g, st));
+        // 6q. H = [train_X^T; 1] G  ((d+1) x N), then gradX += (H_t - x_t H_d) / l_t^2
+        BO_TRY(gemm(gp->d + 1, (int)N, (int)n, (int)M, 1.0, gp->xt_aug, bo_pad8(n), 0, w.W2, w.ldn, w.regionStride, 0.0,
+                    nullptr, 0, 0, w.H, w.ldn, w.strideH, BO_TRI_NONE, 0, st));
+        return bo_kgrad_finalize(h, w.H, w.strideH, w.ldn, X, N, 1.0, grad_X, st);
+    }
     // 3. Cbar = inv(L_b)^T BLbar                            (W0)
     BO_TRY(gemm((int)nb, (int)N, (int)nb, (int)M, 1.0, nei->lb_inv_t, nbp, nb * nbp, w.W2, w.ldn, w.regionStride, 0.0,
                 nullptr, 0, 0, w.W0, w.ldn, w.regionStride, BO_TRI_A_UPPER, 0, st));
@@ -416,7 +480,7 @@ int bo_qlognei_bwd(bo_ctx* ctx, const bo_gp* gp, const bo_nei* nei, int B, int q
     BO_TRY(gemm((int)n, (int)N, (int)nb, (int)M, -ys2, nei->vb, nbp, (n + 1) * nbp, w.W0, w.ldn, w.regionStride, 0.0,
                 nullptr, 0, 0, w.W5, w.ldn, w.regionStride, BO_TRI_NONE, 0, st));
     BO_TRY(bo_colblock_update(w.W5, w.regionStride, w.W1, w.regionStride, w.Sbar, (int)n, B, q, (int)M, w.ldn, -2.0 * ys2,
-                              st));
+                              1, st));
     // 5. KXbar = [inv(L)^T | alpha] Vbar (+ ys^2 Cbar when X_baseline is train_X)      (W2)
     const bool shared = nei->baseline_is_train != 0;
     BO_TRY(gemm((int)n, (int)N, (int)n + 1, (int)M, 1.0, gp->linv_aug_t, n1p, n * n1p, w.W5, w.ldn, w.regionStride,
@@ -524,7 +588,7 @@ int bo_posterior_joint_bwd(bo_ctx* ctx, const bo_gp* gp, int B, int q, const dou
     BO_TRY(bo_fill(vbar, M * regionV, 0.0, st));
     BO_TRY(bo_cand_posterior_bwd(a, mean_bar, cov_bar, tbuf, st));
     // Vbar = -ys^2 V (cov_bar + cov_bar^T)
-    BO_TRY(bo_colblock_update(vbar, regionV, v, regionV, tbuf, (int)n, B, q, (int)M, ldn, -ys2, st));
+    BO_TRY(bo_colblock_update(vbar, regionV, v, regionV, tbuf, (int)n, B, q, (int)M, ldn, -ys2, 1, st));
     // KXbar = [inv(L)^T | alpha] Vbar     (into the kx region)
     BO_TRY(gemm((int)n, (int)Nc, (int)n + 1, (int)M, 1.0, gp->linv_aug_t, n1p, n * n1p, vbar, ldn, regionV, 0.0, nullptr, 0,
                 0, kx, ldn, n * ldn, BO_TRI_A_UPPER, 0, st));

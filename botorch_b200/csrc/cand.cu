@@ -460,7 +460,7 @@ __global__ void __launch_bounds__(CAND_THREADS) cand_bwd_kernel(const BoCandArgs
 size_t cand_bwd_smem_bytes(int q) { return sizeof(double) * (size_t)(4 * q * q + q); }
 
 __global__ void colblock_update_kernel(double* Y, long strideY, const double* Xm, long strideX, const double* Tm,
-                                       int rows, int B, int q, long ldn, double coef) {
+                                       int rows, int B, int q, long ldn, double coef, int accumulate) {
     extern __shared__ __align__(16) double st[];  // q*q block of T
     const int b = blockIdx.x, z = blockIdx.z;
     const double* T = Tm + ((long)z * B + b) * q * q;
@@ -475,7 +475,8 @@ __global__ void colblock_update_kernel(double* Y, long strideY, const double* Xm
         const int i = r_lo + idx / q, j = idx % q;
         double s = 0.0;
         for (int k = 0; k < q; k++) s += Xz[(long)i * ldn + c0 + k] * st[k * q + j];
-        Yz[(long)i * ldn + c0 + j] += coef * s;
+        double* y = Yz + (long)i * ldn + c0 + j;
+        *y = (accumulate ? *y : 0.0) + coef * s;
     }
 }
 
@@ -529,6 +530,18 @@ __global__ void __launch_bounds__(CAND_THREADS) kgrad_kernel(BoKernelHyper h, co
         for (int grp = 0; grp < ngroups; grp++) s += part[grp * QD + jt];
         gX[jt] += scale * s * il2[jt % d];
     }
+}
+// gradX[z][c][t] += scale * il2[z][t] * (H[z][t][c] - x_c[t] * H[z][d][c]),   H = [train_X^T; 1] (Kbar .* g)
+__global__ void kgrad_finalize_kernel(BoKernelHyper h, const double* H, long strideH, long ldn, const double* X, long N,
+                                      double scale, double* gradX) {
+    const int z = blockIdx.y, d = h.d;
+    const long idx = blockIdx.x * (long)blockDim.x + threadIdx.x;
+    if (idx >= N * d) return;
+    const long c = idx / d;
+    const int t = (int)(idx % d);
+    const double il = h.inv_ls[(long)z * d + t];
+    const double* Hz = H + (long)z * strideH;
+    gradX[(long)z * N * d + idx] += scale * il * il * (Hz[(long)t * ldn + c] - X[idx] * Hz[(long)d * ldn + c]);
 }
 size_t kgrad_smem_bytes(int q, int d, int T) {
     const int QD = q * d;
@@ -706,13 +719,13 @@ int bo_cand_bwd(const BoCandArgs& a, cudaStream_t stream) {
     return BO_OK;
 }
 int bo_colblock_update(double* Y, long strideY, const double* Xm, long strideX, const double* T, int rows, int B,
-                       int q, int M, long ldn, double coef, cudaStream_t stream) {
+                       int q, int M, long ldn, double coef, int accumulate, cudaStream_t stream) {
     if (rows <= 0 || B <= 0) return BO_OK;
     int ysplit = (rows + 255) / 256;  // ~256 rows per CTA
     if (ysplit > 65535) ysplit = 65535;
     dim3 grid(B, ysplit, M);
     colblock_update_kernel<<<grid, 256, sizeof(double) * q * q, stream>>>(Y, strideY, Xm, strideX, T, rows, B, q, ldn,
-                                                                         coef);
+                                                                         coef, accumulate);
     BO_LAUNCH_CHECK();
     return BO_OK;
 }
@@ -724,6 +737,14 @@ int bo_kgrad(const BoKernelHyper& h, const double* Xpts, int npts, const double*
     BO_TRY(set_smem_limit((const void*)kgrad_kernel, smem));
     dim3 grid(B, h.M);
     kgrad_kernel<<<grid, CAND_THREADS, smem, stream>>>(h, Xpts, npts, Kbar, strideK, ldn, X, B, q, scale, gradX);
+    BO_LAUNCH_CHECK();
+    return BO_OK;
+}
+int bo_kgrad_finalize(const BoKernelHyper& h, const double* H, long strideH, long ldn, const double* X, long N,
+                      double scale, double* gradX, cudaStream_t stream) {
+    if (N <= 0) return BO_OK;
+    dim3 grid((unsigned)((N * h.d + 255) / 256), h.M);
+    kgrad_finalize_kernel<<<grid, 256, 0, stream>>>(h, H, strideH, ldn, X, N, scale, gradX);
     BO_LAUNCH_CHECK();
     return BO_OK;
 }

@@ -47,9 +47,13 @@ struct BoCandArgs {
 int bo_cand_fwd(const BoCandArgs& a, cudaStream_t stream);
 int bo_cand_bwd(const BoCandArgs& a, cudaStream_t stream);
 
-// Y[z][i][b*q+j] += coef * sum_k Xm[z][i][b*q+k] * T[z][b][k][j]     (rows x (B*q) matrices, pitch ldn)
+// Y[z][i][b*q+j] (+)= coef * sum_k Xm[z][i][b*q+k] * T[z][b][k][j]     (rows x (B*q) matrices, pitch ldn)
 int bo_colblock_update(double* Y, long strideY, const double* Xm, long strideX, const double* T, int rows, int B,
-                       int q, int M, long ldn, double coef, cudaStream_t stream);
+                       int q, int M, long ldn, double coef, int accumulate, cudaStream_t stream);
+
+// last step of the GEMM-shaped kernel gradient: gradX[z][c][t] += scale/l_t^2 (H[t][c] - x_c[t] H[d][c])
+int bo_kgrad_finalize(const BoKernelHyper& h, const double* H, long strideH, long ldn, const double* X, long N,
+                      double scale, double* gradX, cudaStream_t stream);
 
 // gradX[z][b][j][:] (+)= scale * sum_i Kbar[z][i][b*q+j] * d k(x_i, x_bj) / d x_bj
 int bo_kgrad(const BoKernelHyper& h, const double* Xpts, int npts, const double* Kbar, long strideK, long ldn,

@@ -67,6 +67,9 @@ struct BoGemm {
     const double* diag_add;  // [batch] value added where row==col (noise), may be null
     int diag_exact;          // 1: squared distance forced to 0 where row==col (x1_eq_x2)
     int a_bcast, b_bcast;    // unused (strides of 0 already broadcast); kept for clarity
+    const double* alpha_vec; // [batch] optional per-member factor multiplying alpha (LINEAR only)
+    const double* E; long lde; long strideE;    // optional elementwise factor: C = (alpha*acc + beta*D) * E  (LINEAR only)
+    double* C2; long ldc2; long strideC2;       // kernel epilogues: optional second output g(r), d k/dx_a = -g (x_a-x_b)/l^2
 };
 
 int bo_gemm_launch(const BoGemm& g, cudaStream_t stream);

@@ -9,6 +9,7 @@
 //   torch.linalg.solve_triangular in low_rank.py:131  (as a multiply with the cached inverse factor)
 //   new_Lq.matmul(base_samples) in low_rank.py:156
 #include "common.cuh"
+#include <cstdlib>
 
 long g_bo_launch_count = 0;
 
@@ -74,8 +75,9 @@ struct Cfg {
 
 __device__ __forceinline__ double epilogue_value(const BoGemm& p, int z, double acc, int row, int col) {
     if (p.epi == BO_EPI_LINEAR) {
-        double v = p.alpha * acc;
+        double v = (p.alpha_vec ? p.alpha * p.alpha_vec[z] : p.alpha) * acc;
         if (p.D != nullptr) v += p.beta * p.D[(long)z * p.strideD + (long)row * p.ldd + col];
+        if (p.E != nullptr) v *= p.E[(long)z * p.strideE + (long)row * p.lde + col];
         return v;
     }
     double r2 = acc > 0.0 ? acc : 0.0;
@@ -88,7 +90,10 @@ __device__ __forceinline__ double epilogue_value(const BoGemm& p, int z, double 
     } else {
         const double sqrt5 = 2.23606797749978969641;
         double r = sqrt(r2 > 1e-30 ? r2 : 1e-30);
-        v = os * ((sqrt5 * r + 1.0) + (5.0 / 3.0) * (r * r)) * exp(-sqrt5 * r);
+        const double e = exp(-sqrt5 * r);
+        v = os * ((sqrt5 * r + 1.0) + (5.0 / 3.0) * (r * r)) * e;
+        if (p.C2)  // derivative factor of Matern-5/2 (zero below gpytorch's distance clamp)
+            p.C2[(long)z * p.strideC2 + (long)row * p.ldc2 + col] = r2 < 1e-30 ? 0.0 : os * (5.0 / 3.0) * (1.0 + sqrt5 * r) * e;
     }
     if (p.diag_add && on_diag) v += p.diag_add[z];
     return v;
@@ -214,6 +219,13 @@ __global__ void __launch_bounds__(C::THREADS) dgemm_dmma_kernel(const BoGemm p) 
 using CfgBig = Cfg<128, 128, 16, 64, 32, 4>;
 using CfgMid = Cfg<64, 64, 16, 32, 32, 4>;
 using CfgSmall = Cfg<32, 32, 16, 16, 16, 3>;
+// tuning candidates (selected with BO_GEMM_CFG=n for tools/gemm_bench.py)
+using CfgT2 = Cfg<64, 64, 16, 32, 32, 3>;     // 4 warps, 4 CTAs/SM
+using CfgT3 = Cfg<128, 64, 16, 32, 32, 3>;    // 8 warps of 32x32, 2 CTAs/SM
+using CfgT4 = Cfg<64, 128, 16, 32, 32, 3>;    // 8 warps of 32x32, 2 CTAs/SM
+using CfgT5 = Cfg<128, 128, 32, 64, 32, 3>;   // Big with BK=32: half the barriers
+using CfgT6 = Cfg<128, 128, 16, 32, 32, 3>;   // 16 warps of 32x32 in one CTA
+using CfgT7 = Cfg<64, 128, 16, 32, 64, 3>;    // 4 warps of 32x64
 
 template <class C>
 int launch_cfg(const BoGemm& g, cudaStream_t stream) {
@@ -255,9 +267,22 @@ int bo_gemm_launch(const BoGemm& g, cudaStream_t stream) {
         (reinterpret_cast<uintptr_t>(g.C) & 15))
         return BO_ERR_INVALID;
     if ((g.strideA & 1) || (g.strideB & 1) || (g.strideC & 1)) return BO_ERR_INVALID;
+    static const int forced = [] { const char* e = getenv("BO_GEMM_CFG"); return e ? atoi(e) : -1; }();
+    switch (forced) {
+        case 0: return launch_cfg<CfgBig>(g, stream);
+        case 1: return launch_cfg<CfgMid>(g, stream);
+        case 2: return launch_cfg<CfgT2>(g, stream);
+        case 3: return launch_cfg<CfgT3>(g, stream);
+        case 4: return launch_cfg<CfgT4>(g, stream);
+        case 5: return launch_cfg<CfgT5>(g, stream);
+        case 6: return launch_cfg<CfgT6>(g, stream);
+        case 7: return launch_cfg<CfgT7>(g, stream);
+        default: break;
+    }
     auto tiles = [&](int bm, int bn) { return (long)((g.M + bm - 1) / bm) * ((g.N + bn - 1) / bn) * g.batch; };
     // Pick the largest tile that still fills the 148 SMs; small problems trade tile efficiency for occupancy.
-    if (tiles(128, 128) >= 120) return launch_cfg<CfgBig>(g, stream);
+    // 64x64 tiles with 4 warps, 3 CTAs per SM: measured best on B200 (tools/gemm_bench.py) --
+    // co-resident small CTAs keep the DMMA pipe fed through each other's barriers and shrink the last wave.
     if (tiles(64, 64) >= 120 || (g.M >= 48 && g.N >= 48 && tiles(32, 32) > 2048)) return launch_cfg<CfgMid>(g, stream);
     return launch_cfg<CfgSmall>(g, stream);
 }

@@ -86,6 +86,7 @@ class GPState:
         self.linv_aug = z(M, n + 1, self.np_)
         self.linv_aug_t = z(M, n, self.n1p)
         self.chol = z(M, n, self.np_)
+        self.xt_aug = z(d + 1, self.np_)
         self.info = torch.zeros(M, dtype=torch.int32, device=dev)
         self.c = BoGP(
             kernel_id=KERNEL_IDS[kernel], n=n, d=d, M=M, y_mean=self.y_mean, y_std=self.y_std,
@@ -93,7 +94,7 @@ class GPState:
             outputscale=ptr(self.outputscale), noise=ptr(self.noise), mean=ptr(self.mean),
             targets=ptr(self.targets), jitter=None,
             aug_train=ptr(self.aug_train), linv_aug=ptr(self.linv_aug), linv_aug_t=ptr(self.linv_aug_t),
-            chol=ptr(self.chol),
+            chol=ptr(self.chol), xt_aug=ptr(self.xt_aug),
         )  # fmt: skip
         self.jitter = torch.zeros(M, dtype=torch.float64, device=dev)
         if not setup:  # factors arrive by broadcast from the rank that ran the setup (distributed.py)
@@ -112,7 +113,7 @@ class GPState:
 
     def factor_buffers(self):
         """Device buffers bo_gp_setup fills: what the setup rank broadcasts to its peers."""
-        return [self.aug_train, self.linv_aug, self.linv_aug_t, self.chol, self.jitter]
+        return [self.aug_train, self.linv_aug, self.linv_aug_t, self.chol, self.xt_aug, self.jitter]
 
     # -- factors exposed for tests / callers ------------------------------------------------------
     @property
@@ -194,12 +195,14 @@ class NEIState:
         self.zb_t = z(nb, Sp)
         self.mean_b = z(M, nbp)
         self.best_f_pad = z(M, Sp)
+        self.qmat = z(M, nb, gp.np_) if self.is_train else None
+        self.qmat_t = z(M, n, nbp) if self.is_train else None
         self.info = torch.zeros(M, dtype=torch.int32, device=dev)
         self.c = BoNEI(
             n_b=nb, S=S, baseline_is_train=int(self.is_train), X_b=ptr(self.X_b), Z_b=ptr(self.Z_b), jitter=None,
             aug_b=ptr(self.aug_b), vb=ptr(self.vb), vb_t=ptr(self.vb_t), lb=ptr(self.lb), lb_inv=ptr(self.lb_inv),
             lb_inv_t=ptr(self.lb_inv_t), zb_pad=ptr(self.zb_pad), zb_t=ptr(self.zb_t), mean_b=ptr(self.mean_b),
-            best_f=ptr(self.best_f_pad),
+            best_f=ptr(self.best_f_pad), qmat=ptr(self.qmat), qmat_t=ptr(self.qmat_t),
         )  # fmt: skip
         self.jitter = torch.zeros(M, dtype=torch.float64, device=dev)
         if not setup:
@@ -220,7 +223,8 @@ class NEIState:
         """Device buffers bo_nei_setup fills (broadcast payload)."""
         bufs = [self.vb, self.vb_t, self.lb, self.lb_inv, self.lb_inv_t, self.zb_pad, self.zb_t, self.mean_b,
                 self.best_f_pad, self.jitter]  # fmt: skip
-        return bufs + ([] if self.aug_b is None else [self.aug_b])
+        bufs += [] if self.aug_b is None else [self.aug_b]
+        return bufs + ([] if self.qmat is None else [self.qmat, self.qmat_t])
 
     @property
     def baseline_L(self) -> Tensor:

@@ -59,6 +59,7 @@ typedef struct bo_gp {
     double* linv_aug;          /* [M][(n+1) x np]    rows 0..n-1: inv(L); row n: alpha = (K+s2 I)^-1 (y-m) */
     double* linv_aug_t;        /* [M][n x n1p]       transpose of linv_aug */
     double* chol;              /* [M][n x np]        L, K + s2 I = L L^T */
+    double* xt_aug;            /* [(d+1) x np]       rows 0..d-1: train_X^T, row d: ones (gradient contraction operand) */
 } bo_gp;
 
 /* qLogNEI baseline state.  Replaces qLogNoisyExpectedImprovement._init_baseline
@@ -81,6 +82,9 @@ typedef struct bo_nei {
     double* zb_t;              /* [n_b x Sp]      */
     double* mean_b;            /* [M][nbp]        posterior mean at X_b (outcome scale) */
     double* best_f;            /* [M][Sp]         max_j baseline sample (acquisition/utils.py:125-129) */
+    /* only when baseline_is_train: Sigma(X_b, X) = ys^2 s2 (K+s2 I)^-1 K(X_tr, X), so bl_chol^T = Q K(X_tr, X) */
+    double* qmat;              /* [M][n_b x np]   Q = ys^2 (s2+jitter) inv(L_b) (K+s2 I)^-1 */
+    double* qmat_t;            /* [M][n x nbp]    Q^T */
 } bo_nei;
 
 typedef struct bo_ctx bo_ctx;
