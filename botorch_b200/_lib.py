@@ -60,6 +60,10 @@ class BoNEI(C.Structure):
         ("best_f", C.c_void_p),
         ("qmat", C.c_void_p),
         ("qmat_t", C.c_void_p),
+        ("lw", C.c_void_p),
+        ("lw_t", C.c_void_p),
+        ("zq_aug", C.c_void_p),
+        ("zq_aug_t", C.c_void_p),
     ]
 
 

@@ -292,6 +292,23 @@ int bo_nei_setup(bo_ctx* ctx, const bo_gp* gp, const bo_nei* nei, void* work, si
         g.tri = BO_TRI_A_LOWER; g.epi = BO_EPI_LINEAR;
         BO_TRY(bo_fill(nei->qmat_t, M * n * nbp, 0.0, st));
         BO_TRY(bo_gemm_launch(g, st));
+        if (nei->lw && nei->lw_t && nei->zq_aug && nei->zq_aug_t) {
+            // W = ys^2 Khat^-1 + Q^T Q (lower block triangle), W = L_W L_W^T
+            const long S1p = bo_pad8(S + 1);
+            BO_TRY(gemm((int)n, (int)n, (int)nb, (int)M, 1.0, nei->qmat_t, nbp, n * nbp, nei->qmat, np, nb * np, ys2, khinv, np,
+                        n * np, nei->lw, np, n * np, BO_TRI_NONE, 1, st));
+            BO_TRY(bo_potrf_blocked(nei->lw, np, n * np, (int)n, (int)M, nullptr, np, n * np, scratch, info, st));
+            BO_TRY(bo_fill(nei->lw_t, M * n * np, 0.0, st));
+            BO_TRY(bo_transpose(nei->lw, np, n * np, nei->lw_t, np, n * np, (int)n, (int)n, (int)M, st));
+            // [Z_b Q; alpha^T]  ((S+1) x n) and its transpose
+            BO_TRY(bo_fill(nei->zq_aug, M * (S + 1) * np, 0.0, st));
+            BO_TRY(gemm((int)S, (int)n, (int)nb, (int)M, 1.0, nei->zb_pad, nbp, 0, nei->qmat, np, nb * np, 0.0, nullptr, 0, 0,
+                        nei->zq_aug, np, (S + 1) * np, BO_TRI_NONE, 0, st));
+            BO_TRY(bo_copy2d(gp->linv_aug + n * np, np, (n + 1) * np, nei->zq_aug + S * np, np, (S + 1) * np, 1, (int)n,
+                             (int)M, st));
+            BO_TRY(bo_fill(nei->zq_aug_t, M * n * S1p, 0.0, st));
+            BO_TRY(bo_transpose(nei->zq_aug, np, (S + 1) * np, nei->zq_aug_t, S1p, n * S1p, (int)S + 1, (int)n, (int)M, st));
+        }
     }
     BO_CUDA_TRY(cudaGetLastError());
     return BO_OK;
@@ -308,7 +325,7 @@ struct QWork {
     long ldn, R, regionStride;
     double *baug, *W0, *W1, *W2, *W3, *F, *W5, *W6, *Lq, *lse, *Sbar, *Wd, *H;
     long strideH;
-    bool qpath;  // X_baseline == train_X with a precomputed Q (bo_nei.qmat): bl_chol^T = Q K(X_tr, X)
+    bool qpath;  // X_baseline == train_X with the combined root L_W (bo_nei.lw): Schur = ys^2 k - U^T U, U = L_W^T K(X_tr, X)
     int32_t* info;
     bool ok;
     size_t bytes;
@@ -327,12 +344,12 @@ QWork qlayout(const bo_gp* gp, const bo_nei* nei, int B, int q, int with_grad, v
     w.W1 = b.doubles(M * w.regionStride);
     w.W2 = b.doubles(M * w.regionStride);
     w.W3 = b.doubles(M * w.regionStride);
-    w.F = b.doubles(M * (long)nei->S * w.ldn);
+    w.F = b.doubles(M * (long)(nei->S + 1) * w.ldn);  // row S: alpha . K (mean) forward, y_std * mubar backward
     w.Lq = b.doubles(M * (long)B * q * q);
     w.lse = b.doubles(M * (long)B);
     w.info = reinterpret_cast<int32_t*>(b.doubles((M * (long)B + 1) / 2));
     w.W6 = nei->baseline_is_train ? nullptr : b.doubles(M * w.regionStride);
-    w.qpath = nei->baseline_is_train && nei->qmat && nei->qmat_t && gp->xt_aug;
+    w.qpath = nei->baseline_is_train && nei->lw && nei->lw_t && nei->zq_aug && nei->zq_aug_t && gp->xt_aug;
     if (with_grad) {
         w.W5 = b.doubles(M * w.regionStride);
         w.Sbar = b.doubles(M * (long)B * q * q);
@@ -361,7 +378,7 @@ BoCandArgs cand_args(const bo_gp* gp, const bo_nei* nei, int B, int q, const dou
     a.ldn = w.ldn;
     a.V = w.W1; a.strideV = w.regionStride;
     a.BL = w.W3; a.strideBL = w.regionStride;
-    a.F = w.F; a.strideF = nei ? (long)nei->S * w.ldn : 0;
+    a.F = w.F; a.strideF = nei ? (long)(nei->S + 1) * w.ldn : 0;
     a.Lq = w.Lq; a.lse = w.lse;
     return a;
 }
@@ -397,24 +414,35 @@ int bo_qlognei_fwd(bo_ctx* ctx, const bo_gp* gp, const bo_nei* nei, int B, int q
         BO_TRY(kmat(gp, nei->aug_b, (int)nb, w.baug, w.ldn, N, w.W6, w.ldn, w.regionStride, 0, nullptr, st));
         KB = w.W6;
     }
+    if (w.qpath) {
+        // 2r. U = L_W^T K(X_tr, X)  (n x N, the only n^2-sized product of the forward pass)
+        BO_TRY(gemm((int)n, (int)N, (int)n, (int)M, 1.0, nei->lw_t, np, n * np, w.W0, w.ldn, w.regionStride, 0.0, nullptr, 0, 0,
+                    w.W1, w.ldn, w.regionStride, BO_TRI_A_UPPER, 0, st));
+        // 3r. [Z_b Q; alpha^T] K(X_tr, X): baseline part of every sample and the mean row
+        BO_TRY(gemm((int)S + 1, (int)N, (int)n, (int)M, 1.0, nei->zq_aug, np, (S + 1) * np, w.W0, w.ldn, w.regionStride, 0.0,
+                    nullptr, 0, 0, w.F, w.ldn, (S + 1) * w.ldn, BO_TRI_NONE, 0, st));
+        BoCandArgs a = cand_args(gp, nei, B, q, X, Z_q, tau_relu, tau_max, w);
+        a.V = nullptr;
+        a.BL = w.W1; a.strideBL = w.regionStride; a.n_b = (int)n;
+        a.mu_row = w.F + S * w.ldn; a.strideMu = (S + 1) * w.ldn;
+        a.acq = acq;
+        a.info = w.info;
+        BO_TRY(bo_cand_fwd(a, st));
+        BO_CUDA_TRY(cudaMemcpyAsync(info, w.info, sizeof(int32_t) * M * B, cudaMemcpyDeviceToDevice, st));
+        return BO_OK;
+    }
     // 2. V = [inv(L); alpha^T] K(X_tr, X)           (n+1) x N
     BO_TRY(gemm((int)n + 1, (int)N, (int)n, (int)M, 1.0, gp->linv_aug, np, (n + 1) * np, w.W0, w.ldn, w.regionStride, 0.0,
                 nullptr, 0, 0, w.W1, w.ldn, w.regionStride, BO_TRI_A_LOWER, 0, st));
-    if (w.qpath) {
-        // 3+4. bl_chol^T = Q K(X_tr, X): one dense GEMM instead of the Schur GEMM + the triangular solve
-        BO_TRY(gemm((int)nb, (int)N, (int)n, (int)M, 1.0, nei->qmat, np, nb * np, w.W0, w.ldn, w.regionStride, 0.0, nullptr,
-                    0, 0, w.W3, w.ldn, w.regionStride, BO_TRI_NONE, 0, st));
-    } else {
     // 3. Sigma(X_b, X) = ys^2 (K(X_b, X) - V_b^T V)   n_b x N
     BO_TRY(gemm((int)nb, (int)N, (int)n, (int)M, -ys2, nei->vb_t, np, nb * np, w.W1, w.ldn, w.regionStride, ys2, KB, w.ldn,
                 w.regionStride, w.W2, w.ldn, w.regionStride, BO_TRI_NONE, 0, st));
     // 4. bl_chol^T = inv(L_b) Sigma(X_b, X)
     BO_TRY(gemm((int)nb, (int)N, (int)nb, (int)M, 1.0, nei->lb_inv, nbp, nb * nbp, w.W2, w.ldn, w.regionStride, 0.0,
                 nullptr, 0, 0, w.W3, w.ldn, w.regionStride, BO_TRI_A_LOWER, 0, st));
-    }
     // 5. baseline part of the samples: Z_b bl_chol^T    S x N
     BO_TRY(gemm((int)S, (int)N, (int)nb, (int)M, 1.0, nei->zb_pad, nbp, 0, w.W3, w.ldn, w.regionStride, 0.0, nullptr, 0, 0,
-                w.F, w.ldn, S * w.ldn, BO_TRI_NONE, 0, st));
+                w.F, w.ldn, (S + 1) * w.ldn, BO_TRI_NONE, 0, st));
     // 6. Schur block, q x q Cholesky, samples, log_fatplus / fatmax / logmeanexp
     BoCandArgs a = cand_args(gp, nei, B, q, X, Z_q, tau_relu, tau_max, w);
     a.acq = acq;
@@ -436,43 +464,45 @@ int bo_qlognei_bwd(bo_ctx* ctx, const bo_gp* gp, const bo_nei* nei, int B, int q
     const long S = nei->S, N = (long)B * q;
     const double ys2 = gp->y_std * gp->y_std;
     const BoKernelHyper h = hyper_of(gp);
-    // 1. reductions, samples and q x q Cholesky in reverse: F <- dF, Sbar, row n of Vbar, gradX <- k(X,X) part
+    // 1. reductions, samples and q x q Cholesky in reverse: F <- dF, Sbar, y_std * mubar, gradX <- k(X,X) part
     BoCandArgs a = cand_args(gp, nei, B, q, X, Z_q, tau_relu, tau_max, w);
     a.info = w.info;
     a.grad_acq = grad_acq;
     a.Sbar = w.Sbar;
-    a.Vbar_mu = w.W5 + n * w.ldn;
-    a.strideVbar = w.regionStride;
     a.gradX = grad_X;
-    BO_TRY(bo_cand_bwd(a, st));
-    // 2. BLbar = Z_b^T dF - 2 BL Sbar                       (W2)
-    BO_TRY(gemm((int)nb, (int)N, (int)S, (int)M, 1.0, nei->zb_t, Sp, 0, w.F, w.ldn, S * w.ldn, 0.0, nullptr, 0, 0, w.W2,
-                w.ldn, w.regionStride, BO_TRI_NONE, 0, st));
-    BO_TRY(bo_colblock_update(w.W2, w.regionStride, w.W3, w.regionStride, w.Sbar, (int)nb, B, q, (int)M, w.ldn, -2.0, 1, st));
     if (w.qpath) {
-        const long np = bo_pad8(n);
-        (void)np;
-        // 3q. Vbar = -2 ys^2 V Sbar (rows 0..n-1 of W5; row n already holds y_std * mubar)
-        BO_TRY(bo_colblock_update(w.W5, w.regionStride, w.W1, w.regionStride, w.Sbar, (int)n, B, q, (int)M, w.ldn,
-                                  -2.0 * ys2, 0, st));
-        // 4q. T = Q^T BLbar                                  (W3; BL is dead from here on)
-        BO_TRY(gemm((int)n, (int)N, (int)nb, (int)M, 1.0, nei->qmat_t, nbp, n * nbp, w.W2, w.ldn, w.regionStride, 0.0, nullptr,
-                    0, 0, w.W3, w.ldn, w.regionStride, BO_TRI_NONE, 0, st));
-        // 5q. G = ([inv(L)^T | alpha] Vbar + T) .* g(r),  g = K for RBF, the stored derivative factor for Matern   (W2)
+        const long np = bo_pad8(n), S1p = bo_pad8(S + 1);
+        a.Vbar_mu = w.F + S * w.ldn;  // row S of the sample matrix: [dF; y_std * mubar] is the operand of step 3r
+        a.strideVbar = (S + 1) * w.ldn;
+        BO_TRY(bo_cand_bwd(a, st));
+        // 2r. Ubar = -2 U Sbar                               (W5)
+        BO_TRY(bo_colblock_update(w.W5, w.regionStride, w.W1, w.regionStride, w.Sbar, (int)n, B, q, (int)M, w.ldn, -2.0, 0,
+                                  st));
+        // 3r. T = [Z_b Q; alpha^T]^T [dF; y_std mubar]       (W3)
+        BO_TRY(gemm((int)n, (int)N, (int)S + 1, (int)M, 1.0, nei->zq_aug_t, S1p, n * S1p, w.F, w.ldn, (S + 1) * w.ldn, 0.0,
+                    nullptr, 0, 0, w.W3, w.ldn, w.regionStride, BO_TRI_NONE, 0, st));
+        // 4r. G = (L_W Ubar + T) .* g(r),  g = K for RBF, the stored derivative factor for Matern   (W2)
         BoGemm g{};
-        g.A = gp->linv_aug_t; g.lda = n1p; g.strideA = n * n1p;
+        g.A = nei->lw; g.lda = np; g.strideA = n * np;
         g.B = w.W5; g.ldb = w.ldn; g.strideB = w.regionStride;
         g.C = w.W2; g.ldc = w.ldn; g.strideC = w.regionStride;
         g.D = w.W3; g.ldd = w.ldn; g.strideD = w.regionStride;
         g.E = w.Wd ? w.Wd : w.W0; g.lde = w.ldn; g.strideE = w.regionStride;
-        g.alpha = 1.0; g.beta = 1.0; g.M = (int)n; g.N = (int)N; g.K = (int)n + 1; g.batch = (int)M;
-        g.tri = BO_TRI_A_UPPER; g.epi = BO_EPI_LINEAR;
+        g.alpha = 1.0; g.beta = 1.0; g.M = (int)n; g.N = (int)N; g.K = (int)n; g.batch = (int)M;
+        g.tri = BO_TRI_A_LOWER; g.epi = BO_EPI_LINEAR;
         BO_TRY(bo_gemm_launch(g, st));
-        // 6q. H = [train_X^T; 1] G  ((d+1) x N), then gradX += (H_t - x_t H_d) / l_t^2
-        BO_TRY(gemm(gp->d + 1, (int)N, (int)n, (int)M, 1.0, gp->xt_aug, bo_pad8(n), 0, w.W2, w.ldn, w.regionStride, 0.0,
-                    nullptr, 0, 0, w.H, w.ldn, w.strideH, BO_TRI_NONE, 0, st));
+        // 5r. H = [train_X^T; 1] G  ((d+1) x N), then gradX += (H_t - x_t H_d) / l_t^2
+        BO_TRY(gemm(gp->d + 1, (int)N, (int)n, (int)M, 1.0, gp->xt_aug, np, 0, w.W2, w.ldn, w.regionStride, 0.0, nullptr, 0, 0,
+                    w.H, w.ldn, w.strideH, BO_TRI_NONE, 0, st));
         return bo_kgrad_finalize(h, w.H, w.strideH, w.ldn, X, N, 1.0, grad_X, st);
     }
+    a.Vbar_mu = w.W5 + n * w.ldn;
+    a.strideVbar = w.regionStride;
+    BO_TRY(bo_cand_bwd(a, st));
+    // 2. BLbar = Z_b^T dF - 2 BL Sbar                       (W2)
+    BO_TRY(gemm((int)nb, (int)N, (int)S, (int)M, 1.0, nei->zb_t, Sp, 0, w.F, w.ldn, (S + 1) * w.ldn, 0.0, nullptr, 0, 0, w.W2,
+                w.ldn, w.regionStride, BO_TRI_NONE, 0, st));
+    BO_TRY(bo_colblock_update(w.W2, w.regionStride, w.W3, w.regionStride, w.Sbar, (int)nb, B, q, (int)M, w.ldn, -2.0, 1, st));
     // 3. Cbar = inv(L_b)^T BLbar                            (W0)
     BO_TRY(gemm((int)nb, (int)N, (int)nb, (int)M, 1.0, nei->lb_inv_t, nbp, nb * nbp, w.W2, w.ldn, w.regionStride, 0.0,
                 nullptr, 0, 0, w.W0, w.ldn, w.regionStride, BO_TRI_A_UPPER, 0, st));

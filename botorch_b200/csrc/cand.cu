@@ -258,11 +258,17 @@ __global__ void __launch_bounds__(CAND_THREADS) cand_fwd_kernel(const BoCandArgs
     const int q = a.q, b = blockIdx.x, z = blockIdx.y, tid = threadIdx.x, T = blockDim.x;
     const CandSmem c = carve(sm, q, T, a.S);
     const int c0 = b * q;
-    const double* V = a.V + (long)z * a.strideV;
+    const double* V = a.V ? a.V + (long)z * a.strideV : nullptr;
     const double* BL = a.BL + (long)z * a.strideBL;
     double* F = a.F + (long)z * a.strideF;
+    // mean row: row n of V, or (combined-root path) its own row produced by the sample GEMM
+    const double* mu_row = a.mu_row ? a.mu_row + (long)z * a.strideMu : V + (long)a.n * a.ldn;
 
-    gram_block(V, a.ldn, a.n, c0, q, c.panel, c.part, c.GV);
+    if (V) gram_block(V, a.ldn, a.n, c0, q, c.panel, c.part, c.GV);
+    else {
+        for (int i = tid; i < q * q; i += T) c.GV[i] = 0.0;
+        __syncthreads();
+    }
     gram_block(BL, a.ldn, a.n_b, c0, q, c.panel, c.part, c.GB);
 
     const double ys2 = a.y_std * a.y_std;
@@ -273,7 +279,7 @@ __global__ void __launch_bounds__(CAND_THREADS) cand_fwd_kernel(const BoCandArgs
         const double kv = kern_value(a.h.kernel_id, pair_r2(a.X, a.h.d, il, c0 + j, c0 + k), os);
         c.Lq[idx] = ys2 * (kv - c.GV[idx]) - c.GB[idx];  // Schur block  br - bl_chol bl_chol^T
     }
-    if (tid < q) c.mu[tid] = a.y_mean + a.y_std * (a.mean_const[z] + V[(long)a.n * a.ldn + c0 + tid]);
+    if (tid < q) c.mu[tid] = a.y_mean + a.y_std * (a.mean_const[z] + mu_row[c0 + tid]);
     __syncthreads();
     if (tid == 0) {  // psd_safe_cholesky: plain attempt, then jitter 1e-8 * 10^i, i = 0..5
         double* Sq = c.GV;  // backup of the Schur block

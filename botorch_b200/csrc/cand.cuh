@@ -31,7 +31,8 @@ struct BoCandArgs {
     long ldn;                  // pitch of every [rows x N] workspace matrix (N = B*q padded)
     // per-model strides (doubles) of the workspace matrices
     const double* V;  long strideV;    // [(n+1) x ldn]  rows 0..n-1 inv(L) K(X_tr, X); row n: alpha . K
-    const double* BL; long strideBL;   // [n_b x ldn]    bl_chol^T
+    const double* BL; long strideBL;   // [n_b x ldn]    bl_chol^T  (combined-root path: U = L_W^T K(X_tr, X), n rows, V null)
+    const double* mu_row; long strideMu; // optional [ldn] row holding alpha . K(X_tr, x) (else row n of V)
     double* F;        long strideF;    // [S x ldn]      in: Z_b BL ; out: samples f (fwd) / df (bwd)
     double* Lq;                        // [M][B][q*q]    br_chol
     double* lse;                       // [M][B]         logsumexp over MC samples

@@ -85,6 +85,12 @@ typedef struct bo_nei {
     /* only when baseline_is_train: Sigma(X_b, X) = ys^2 s2 (K+s2 I)^-1 K(X_tr, X), so bl_chol^T = Q K(X_tr, X) */
     double* qmat;              /* [M][n_b x np]   Q = ys^2 (s2+jitter) inv(L_b) (K+s2 I)^-1 */
     double* qmat_t;            /* [M][n x nbp]    Q^T */
+    /* combined root: ys^2 (K+s2 I)^-1 + Q^T Q = L_W L_W^T, so the q x q Schur block of a candidate is
+     * ys^2 k(x,x') - U^T U with U = L_W^T K(X_tr, X): one triangular GEMM replaces V, Sigma(X_b,X) and bl_chol */
+    double* lw;                /* [M][n x np]     L_W (lower) */
+    double* lw_t;              /* [M][n x np]     L_W^T (upper) */
+    double* zq_aug;            /* [M][(S+1) x np] rows 0..S-1: Z_b Q (baseline part of the samples = (Z_b Q) K(X_tr,X)); row S: alpha */
+    double* zq_aug_t;          /* [M][n x pad8(S+1)] its transpose */
 } bo_nei;
 
 typedef struct bo_ctx bo_ctx;
