@@ -204,6 +204,65 @@ __device__ void gram_block(const double* __restrict__ Mtx, long ld, int rows, in
     __syncthreads();
 }
 
+// Register-blocked variant for q <= QT (QT in {4, 8}): every thread walks its own rows (r = tid, tid + T, ...), keeps all
+// QT(QT+1)/2 products in registers, then a fixed xor-shuffle tree and a fixed-order sum over warps: deterministic,
+// no shared-memory staging and ~10x fewer instructions than gram_block for the q = 8 case of config C3.
+template <int QT>
+__device__ void gram_block_reg(const double* __restrict__ Mtx, long ld, int rows, int c0, int q, double* red, double* G) {
+    constexpr int P = QT * (QT + 1) / 2;
+    const int T = blockDim.x, tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    double acc[P];
+#pragma unroll
+    for (int p = 0; p < P; p++) acc[p] = 0.0;
+    const bool vec = (q == QT) && ((QT & 1) == 0) && ((c0 & 1) == 0) && ((ld & 1) == 0);
+    for (int r = tid; r < rows; r += T) {
+        double v[QT];
+        const double* row = Mtx + (long)r * ld + c0;
+        if (vec) {
+#pragma unroll
+            for (int j = 0; j < QT; j += 2) {
+                const double2 t2 = *reinterpret_cast<const double2*>(row + j);
+                v[j] = t2.x;
+                v[j + 1] = t2.y;
+            }
+        } else {
+#pragma unroll
+            for (int j = 0; j < QT; j++) v[j] = (j < q) ? row[j] : 0.0;
+        }
+        int p = 0;
+#pragma unroll
+        for (int j = 0; j < QT; j++)
+#pragma unroll
+            for (int k = 0; k <= j; k++) acc[p++] += v[j] * v[k];
+    }
+#pragma unroll
+    for (int p = 0; p < P; p++) {
+        double a = acc[p];
+        for (int o = 16; o > 0; o >>= 1) a += __shfl_xor_sync(0xffffffffu, a, o);
+        if (lane == 0) red[warp * P + p] = a;
+    }
+    __syncthreads();
+    for (int p = tid; p < P; p += T) {
+        int j = 0;
+        while ((j + 1) * (j + 2) / 2 <= p) j++;
+        const int k = p - j * (j + 1) / 2;
+        double s_ = 0.0;
+        for (int w = 0; w < (T >> 5); w++) s_ += red[w * P + p];
+        if (j < q) {
+            G[j * q + k] = s_;
+            G[k * q + j] = s_;
+        }
+    }
+    __syncthreads();
+}
+
+__device__ __forceinline__ void gram_any(const double* Mtx, long ld, int rows, int c0, int q, double* panel, double* part,
+                                         double* G) {
+    if (q <= 4) gram_block_reg<4>(Mtx, ld, rows, c0, q, part, G);
+    else if (q <= 8) gram_block_reg<8>(Mtx, ld, rows, c0, q, part, G);
+    else gram_block(Mtx, ld, rows, c0, q, panel, part, G);
+}
+
 // in-place lower Cholesky of the q x q matrix A (row-major); returns false on a non-positive pivot
 __device__ bool chol_small(double* A, int q) {
     for (int j = 0; j < q; j++) {
@@ -221,6 +280,12 @@ __device__ bool chol_small(double* A, int q) {
     return true;
 }
 
+// scratch of the gram reductions: T (generic path, q > 8) or one 36-entry slot per warp (register-blocked path)
+__host__ __device__ inline int part_doubles(int q, int T) {
+    const int P = q * (q + 1) / 2;
+    const int a = T > P ? T : P, b = (T / 32) * 36;
+    return a > b ? a : b;
+}
 struct CandSmem {
     double *panel, *part, *GV, *GB, *Lq, *mu, *fm;
 };
@@ -229,7 +294,7 @@ __device__ __forceinline__ CandSmem carve(double* sm, int q, int T, int S) {
     CandSmem c;
     c.panel = sm;
     c.part = c.panel + PANEL_ROWS * q;
-    c.GV = c.part + (T > P ? T : P);
+    c.GV = c.part + part_doubles(q, T);
     c.GB = c.GV + q * q;
     c.Lq = c.GB + q * q;
     c.mu = c.Lq + q * q;
@@ -239,7 +304,8 @@ __device__ __forceinline__ CandSmem carve(double* sm, int q, int T, int S) {
 }
 size_t cand_smem_bytes(int q, int T, int S) {
     const int P = q * (q + 1) / 2;
-    return sizeof(double) * ((size_t)PANEL_ROWS * q + (T > P ? T : P) + 3 * q * q + q + S);
+    (void)P;
+    return sizeof(double) * ((size_t)PANEL_ROWS * q + part_doubles(q, T) + 3 * q * q + q + S);
 }
 
 __device__ __forceinline__ double pair_r2(const double* X, int d, const double* il, int a, int b) {
@@ -264,12 +330,12 @@ __global__ void __launch_bounds__(CAND_THREADS) cand_fwd_kernel(const BoCandArgs
     // mean row: row n of V, or (combined-root path) its own row produced by the sample GEMM
     const double* mu_row = a.mu_row ? a.mu_row + (long)z * a.strideMu : V + (long)a.n * a.ldn;
 
-    if (V) gram_block(V, a.ldn, a.n, c0, q, c.panel, c.part, c.GV);
+    if (V) gram_any(V, a.ldn, a.n, c0, q, c.panel, c.part, c.GV);
     else {
         for (int i = tid; i < q * q; i += T) c.GV[i] = 0.0;
         __syncthreads();
     }
-    gram_block(BL, a.ldn, a.n_b, c0, q, c.panel, c.part, c.GB);
+    gram_any(BL, a.ldn, a.n_b, c0, q, c.panel, c.part, c.GB);
 
     const double ys2 = a.y_std * a.y_std;
     const double os = a.h.outputscale ? a.h.outputscale[z] : 1.0;
@@ -566,7 +632,7 @@ __global__ void __launch_bounds__(CAND_THREADS) cand_posterior_kernel(const BoCa
     const CandSmem c = carve(sm, q, T, 0);
     const int c0 = b * q;
     const double* V = a.V + (long)z * a.strideV;
-    gram_block(V, a.ldn, a.n, c0, q, c.panel, c.part, c.GV);
+    gram_any(V, a.ldn, a.n, c0, q, c.panel, c.part, c.GV);
     const double ys2 = a.y_std * a.y_std;
     const double os = a.h.outputscale ? a.h.outputscale[z] : 1.0;
     const double* il = a.h.inv_ls + (long)z * a.h.d;

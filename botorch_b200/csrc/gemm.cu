@@ -112,9 +112,11 @@ __global__ void __launch_bounds__(C::THREADS) dgemm_dmma_kernel(const BoGemm p) 
     const int wn0 = (warp % C::WARPS_N) * C::WN;
     const int z = blockIdx.z;
     // heavy (large-m) row tiles first when A is lower triangular: better tail balance
-    const int mt = (p.tri == BO_TRI_A_LOWER) ? (gridDim.x - 1 - blockIdx.x) : blockIdx.x;
+    // grid = (column tiles, row tiles): CTAs are dispatched x-fastest, so all column tiles of the heaviest row tile go
+    // first and the last wave holds only the lightest tiles (longest-processing-time order for triangular A)
+    const int mt = (p.tri == BO_TRI_A_LOWER) ? (gridDim.y - 1 - blockIdx.y) : blockIdx.y;
     const int m0 = mt * C::BM;
-    const int n0 = blockIdx.y * C::BN;
+    const int n0 = blockIdx.x * C::BN;
     if (p.out_lower && n0 > m0 + C::BM - 1) return;
 
     const double* __restrict__ A = p.A + (long)z * p.strideA;
@@ -226,6 +228,8 @@ using CfgT4 = Cfg<64, 128, 16, 32, 32, 3>;    // 8 warps of 32x32, 2 CTAs/SM
 using CfgT5 = Cfg<128, 128, 32, 64, 32, 3>;   // Big with BK=32: half the barriers
 using CfgT6 = Cfg<128, 128, 16, 32, 32, 3>;   // 16 warps of 32x32 in one CTA
 using CfgT7 = Cfg<64, 128, 16, 32, 64, 3>;    // 4 warps of 32x64
+using CfgT8 = Cfg<64, 64, 32, 32, 32, 2>;     // BK=32, double buffered, 3 CTAs/SM
+using CfgT9 = Cfg<64, 64, 32, 32, 32, 3>;     // BK=32, 3 stages, 2 CTAs/SM
 
 template <class C>
 int launch_cfg(const BoGemm& g, cudaStream_t stream) {
@@ -235,7 +239,7 @@ int launch_cfg(const BoGemm& g, cudaStream_t stream) {
                                          (int)C::SMEM));
         attr_set = true;
     }
-    dim3 grid((g.M + C::BM - 1) / C::BM, (g.N + C::BN - 1) / C::BN, g.batch);
+    dim3 grid((g.N + C::BN - 1) / C::BN, (g.M + C::BM - 1) / C::BM, g.batch);
     if (grid.y > 65535u || grid.z > 65535u) return BO_ERR_UNSUPPORTED;
     ProfRec* rec = nullptr;
     if (g_prof_on) {
@@ -277,6 +281,8 @@ int bo_gemm_launch(const BoGemm& g, cudaStream_t stream) {
         case 5: return launch_cfg<CfgT5>(g, stream);
         case 6: return launch_cfg<CfgT6>(g, stream);
         case 7: return launch_cfg<CfgT7>(g, stream);
+        case 8: return launch_cfg<CfgT8>(g, stream);
+        case 9: return launch_cfg<CfgT9>(g, stream);
         default: break;
     }
     auto tiles = [&](int bm, int bn) { return (long)((g.M + bm - 1) / bm) * ((g.N + bn - 1) / bn) * g.batch; };

@@ -2,6 +2,7 @@
 import os, subprocess, sys, json
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT)
+KSWEEP = [("K%d" % k, 2000, 4096, k, 0) for k in (64, 128, 256, 512, 1024, 2000)]
 SHAPES = [("V tri", 2001, 4096, 2000, 1), ("Sigma", 2000, 4096, 2000, 0), ("F", 256, 4096, 2000, 0), ("Kbar upper", 2000, 4096, 2001, 2)]
 
 def child():
@@ -9,7 +10,7 @@ def child():
     from botorch_b200 import _lib
     dev = torch.device("cuda:0"); lib = _lib.lib(); ctx = _lib.ctx(dev)
     out = {}
-    for name, M, N, K, tri in SHAPES:
+    for name, M, N, K, tri in (KSWEEP if os.environ.get('BO_KSWEEP') else SHAPES):
         lda, ldb = _lib.pad8(K), _lib.pad8(N)
         A = torch.randn(M, lda, dtype=torch.float64, device=dev); B = torch.randn(K, ldb, dtype=torch.float64, device=dev)
         C = torch.empty(M, ldb, dtype=torch.float64, device=dev)
