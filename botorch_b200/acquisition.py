@@ -79,17 +79,28 @@ class _QLogNEIFunction(torch.autograd.Function):
     def forward(ctx, X: Tensor, nei: engine.NEIState, Zq: Tensor, tau_relu: float, tau_max: float):
         with_grad = ctx.needs_input_grad[0]
         Xd = X.detach().to(torch.float64).contiguous()
-        acq, info, work = nei.forward(Xd, Zq, tau_relu, tau_max, with_grad=with_grad)
-        if with_grad:
-            ctx.nei, ctx.work, ctx.taus, ctx.in_dtype = nei, work, (tau_relu, tau_max), X.dtype
-            ctx.save_for_backward(Xd, Zq)
+        B, q, d = Xd.shape
+        ge = nei.graphed(B, q, d, Zq, tau_relu, tau_max, with_grad)
+        if ge is not None and not ge.busy:  # replay the captured launch sequence
+            acq, info = ge.run_forward(Xd)
+            ctx.ge = ge if with_grad else None
+        else:
+            acq, info, work = nei.forward(Xd, Zq, tau_relu, tau_max, with_grad=with_grad)
+            ctx.ge = None
+            if with_grad:
+                ctx.nei, ctx.work, ctx.taus = nei, work, (tau_relu, tau_max)
+                ctx.save_for_backward(Xd, Zq)
+        ctx.in_dtype = X.dtype
         ctx.mark_non_differentiable(info)
         return acq.to(X.dtype), info
 
     @staticmethod
     def backward(ctx, grad_acq: Tensor, _grad_info):
+        if ctx.ge is not None:
+            g = ctx.ge.run_backward(grad_acq.to(torch.float64))
+            return g.to(ctx.in_dtype), None, None, None, None
         Xd, Zq = ctx.saved_tensors
-        g = ctx.nei.backward(Xd, Zq, ctx.taus[0], ctx.taus[1], grad_acq.to(torch.float64), ctx.work)
+        g = ctx.nei.backward(Xd, Zq, ctx.taus[0], ctx.taus[1], grad_acq.to(torch.float64).contiguous(), ctx.work)
         ctx.work = None  # the workspace may be recycled from here on
         return g.sum(dim=0).to(ctx.in_dtype), None, None, None, None
 

@@ -7,6 +7,7 @@ Every number is produced by the CUDA library.
 from __future__ import annotations
 
 import ctypes as C
+import os
 import warnings
 from typing import Optional, Tuple
 
@@ -239,6 +240,20 @@ class NEIState:
     def best_f(self) -> Tensor:
         return self.best_f_pad[:, : self.S]
 
+    # -- CUDA-graph replay of the fixed launch sequence (small configs are launch-bound) ---------------
+    def graphed(self, B: int, q: int, d: int, Z_q: Tensor, tau_relu: float, tau_max: float, with_grad: bool):
+        """Cached ``GraphedEval`` for this shape, or None when graphs are disabled (BOTORCH_B200_GRAPHS=0)."""
+        if os.environ.get("BOTORCH_B200_GRAPHS", "1") == "0":
+            return None
+        key = (B, q, bool(with_grad), Z_q.data_ptr(), float(tau_relu), float(tau_max))
+        cache = self.__dict__.setdefault("_graphs", {})
+        ge = cache.get(key)
+        if ge is None:
+            if len(cache) >= 6:  # each entry pins its workspace; keep the most recent shapes only
+                cache.pop(next(iter(cache)))
+            ge = cache[key] = GraphedEval(self, B, q, d, Z_q, tau_relu, tau_max, with_grad)
+        return ge
+
     def workspace_bytes(self, B: int, q: int, with_grad: bool) -> int:
         return _lib.lib().bo_qlognei_workspace_bytes(C.byref(self.gp.c), C.byref(self.c), B, q, int(with_grad))
 
@@ -264,6 +279,52 @@ class NEIState:
                                         tau_relu, tau_max, ptr(grad_acq.contiguous()), ptr(grad_X), work.data_ptr(),
                                         work.numel(), _lib.stream_ptr(self.device)))  # fmt: skip
         return grad_X
+
+
+class GraphedEval:
+    """bo_qlognei_fwd (+ bo_qlognei_bwd) for one (B, q) shape captured into CUDA graphs over static buffers.
+
+    The library never allocates or synchronises, so its launch sequence captures as-is; replay costs one graph launch
+    instead of ~11 kernel launches through ctypes.  ``busy`` marks a forward whose backward has not run yet: a second
+    gradient-carrying forward in that window must not reuse the workspace (the caller falls back to the eager path).
+    """
+
+    def __init__(self, nei: "NEIState", B: int, q: int, d: int, Z_q: Tensor, tau_relu: float, tau_max: float,
+                 with_grad: bool) -> None:  # fmt: skip
+        dev = nei.device
+        self.X = torch.zeros(B, q, d, dtype=torch.float64, device=dev)
+        self.busy = False
+        self.with_grad = with_grad
+        args = (self.X, Z_q, tau_relu, tau_max)
+        side = torch.cuda.Stream(device=dev)
+        side.wait_stream(torch.cuda.current_stream(dev))
+        with torch.cuda.stream(side):  # eager warm-up: one-time function attributes are set outside the capture
+            _, _, w = nei.forward(*args, with_grad=with_grad)
+            if with_grad:
+                nei.backward(*args, torch.zeros(nei.gp.M, B, dtype=torch.float64, device=dev), w)
+        torch.cuda.current_stream(dev).wait_stream(side)
+        torch.cuda.synchronize(dev)
+        self.fwd = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(self.fwd):
+            self.acq, self.info, self.work = nei.forward(*args, with_grad=with_grad)
+        self.bwd = None
+        if with_grad:
+            self.grad_in = torch.zeros(nei.gp.M, B, dtype=torch.float64, device=dev)
+            self.bwd = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(self.bwd, pool=self.fwd.pool()):
+                self.grad_X = nei.backward(*args, self.grad_in, self.work)
+
+    def run_forward(self, X: Tensor):
+        self.X.copy_(X)
+        self.fwd.replay()
+        self.busy = self.with_grad
+        return self.acq.clone(), self.info.clone()
+
+    def run_backward(self, grad_acq: Tensor) -> Tensor:
+        self.grad_in.copy_(grad_acq)
+        self.bwd.replay()
+        self.busy = False
+        return self.grad_X.sum(dim=0)
 
 
 # -------------------------------------------------------------------------------------------------
