@@ -60,10 +60,8 @@ class BoNEI(C.Structure):
         ("best_f", C.c_void_p),
         ("qmat", C.c_void_p),
         ("qmat_t", C.c_void_p),
-        ("lw", C.c_void_p),
-        ("lw_t", C.c_void_p),
-        ("zq_aug", C.c_void_p),
-        ("zq_aug_t", C.c_void_p),
+        ("fwd_cat", C.c_void_p),
+        ("bwd_cat", C.c_void_p),
     ]
 
 

@@ -292,22 +292,22 @@ int bo_nei_setup(bo_ctx* ctx, const bo_gp* gp, const bo_nei* nei, void* work, si
         g.tri = BO_TRI_A_LOWER; g.epi = BO_EPI_LINEAR;
         BO_TRY(bo_fill(nei->qmat_t, M * n * nbp, 0.0, st));
         BO_TRY(bo_gemm_launch(g, st));
-        if (nei->lw && nei->lw_t && nei->zq_aug && nei->zq_aug_t) {
-            // W = ys^2 Khat^-1 + Q^T Q (lower block triangle), W = L_W L_W^T
-            const long S1p = bo_pad8(S + 1);
+        if (nei->fwd_cat && nei->bwd_cat) {
+            // W = ys^2 Khat^-1 + Q^T Q = L_W L_W^T, factored in place inside the backward operand [ . | L_W ]
+            const long S1 = S + 1, S1p = bo_pad8(S1), ldk = S1p + np, rowsF = S1p + n;
+            double* lw = nei->bwd_cat + S1p;
+            BO_TRY(bo_fill(nei->bwd_cat, M * n * ldk, 0.0, st));
+            BO_TRY(bo_fill(nei->fwd_cat, M * rowsF * np, 0.0, st));
             BO_TRY(gemm((int)n, (int)n, (int)nb, (int)M, 1.0, nei->qmat_t, nbp, n * nbp, nei->qmat, np, nb * np, ys2, khinv, np,
-                        n * np, nei->lw, np, n * np, BO_TRI_NONE, 1, st));
-            BO_TRY(bo_potrf_blocked(nei->lw, np, n * np, (int)n, (int)M, nullptr, np, n * np, scratch, info, st));
-            BO_TRY(bo_fill(nei->lw_t, M * n * np, 0.0, st));
-            BO_TRY(bo_transpose(nei->lw, np, n * np, nei->lw_t, np, n * np, (int)n, (int)n, (int)M, st));
-            // [Z_b Q; alpha^T]  ((S+1) x n) and its transpose
-            BO_TRY(bo_fill(nei->zq_aug, M * (S + 1) * np, 0.0, st));
+                        n * np, lw, ldk, n * ldk, BO_TRI_NONE, 1, st));
+            BO_TRY(bo_potrf_blocked(lw, ldk, n * ldk, (int)n, (int)M, nullptr, np, n * np, scratch, info, st));
+            BO_TRY(bo_transpose(lw, ldk, n * ldk, nei->fwd_cat + S1p * np, np, rowsF * np, (int)n, (int)n, (int)M, st));
+            // rows 0..S-1: Z_b Q, row S: alpha; then their transpose into the leading columns of the backward operand
             BO_TRY(gemm((int)S, (int)n, (int)nb, (int)M, 1.0, nei->zb_pad, nbp, 0, nei->qmat, np, nb * np, 0.0, nullptr, 0, 0,
-                        nei->zq_aug, np, (S + 1) * np, BO_TRI_NONE, 0, st));
-            BO_TRY(bo_copy2d(gp->linv_aug + n * np, np, (n + 1) * np, nei->zq_aug + S * np, np, (S + 1) * np, 1, (int)n,
-                             (int)M, st));
-            BO_TRY(bo_fill(nei->zq_aug_t, M * n * S1p, 0.0, st));
-            BO_TRY(bo_transpose(nei->zq_aug, np, (S + 1) * np, nei->zq_aug_t, S1p, n * S1p, (int)S + 1, (int)n, (int)M, st));
+                        nei->fwd_cat, np, rowsF * np, BO_TRI_NONE, 0, st));
+            BO_TRY(bo_copy2d(gp->linv_aug + n * np, np, (n + 1) * np, nei->fwd_cat + S * np, np, rowsF * np, 1, (int)n, (int)M,
+                             st));
+            BO_TRY(bo_transpose(nei->fwd_cat, np, rowsF * np, nei->bwd_cat, ldk, n * ldk, (int)S1, (int)n, (int)M, st));
         }
     }
     BO_CUDA_TRY(cudaGetLastError());
@@ -336,27 +336,33 @@ QWork qlayout(const bo_gp* gp, const bo_nei* nei, int B, int q, int with_grad, v
     const long n = gp->n, nb = nei->n_b, M = gp->M, Kp = bo_kp(gp->d);
     const long N = (long)B * q;
     w.ldn = bo_pad8(N);
-    w.R = (n > nb ? n : nb) + 1;
+    w.qpath = nei->baseline_is_train && nei->fwd_cat && nei->bwd_cat && gp->xt_aug;
+    const long S1p = bo_pad8((long)nei->S + 1);
+    // rows of every [rows x N] region: the stacked forward output [samples; pad; U] on the shared-baseline path
+    w.R = w.qpath ? S1p + n : (n > nb ? n : nb) + 1;
     w.regionStride = w.R * w.ldn;
     Bump b(work, cap);
     w.baug = b.doubles(M * Kp * w.ldn);
     w.W0 = b.doubles(M * w.regionStride);
     w.W1 = b.doubles(M * w.regionStride);
-    w.W2 = b.doubles(M * w.regionStride);
-    w.W3 = b.doubles(M * w.regionStride);
-    w.F = b.doubles(M * (long)(nei->S + 1) * w.ldn);  // row S: alpha . K (mean) forward, y_std * mubar backward
     w.Lq = b.doubles(M * (long)B * q * q);
     w.lse = b.doubles(M * (long)B);
     w.info = reinterpret_cast<int32_t*>(b.doubles((M * (long)B + 1) / 2));
-    w.W6 = nei->baseline_is_train ? nullptr : b.doubles(M * w.regionStride);
-    w.qpath = nei->baseline_is_train && nei->lw && nei->lw_t && nei->zq_aug && nei->zq_aug_t && gp->xt_aug;
+    if (!w.qpath) {
+        w.W2 = b.doubles(M * w.regionStride);
+        w.W3 = b.doubles(M * w.regionStride);
+        w.F = b.doubles(M * (long)(nei->S + 1) * w.ldn);
+        w.W6 = nei->baseline_is_train ? nullptr : b.doubles(M * w.regionStride);
+    }
     if (with_grad) {
-        w.W5 = b.doubles(M * w.regionStride);
         w.Sbar = b.doubles(M * (long)B * q * q);
         if (w.qpath) {
+            w.W2 = b.doubles(M * w.regionStride);
             w.strideH = (long)(gp->d + 1) * w.ldn;
             w.H = b.doubles(M * w.strideH);
             if (gp->kernel_id != BO_KERNEL_RBF) w.Wd = b.doubles(M * w.regionStride);  // Matern derivative factor
+        } else {
+            w.W5 = b.doubles(M * w.regionStride);
         }
     }
     w.ok = b.ok;
@@ -415,16 +421,21 @@ int bo_qlognei_fwd(bo_ctx* ctx, const bo_gp* gp, const bo_nei* nei, int B, int q
         KB = w.W6;
     }
     if (w.qpath) {
-        // 2r. U = L_W^T K(X_tr, X)  (n x N, the only n^2-sized product of the forward pass)
-        BO_TRY(gemm((int)n, (int)N, (int)n, (int)M, 1.0, nei->lw_t, np, n * np, w.W0, w.ldn, w.regionStride, 0.0, nullptr, 0, 0,
-                    w.W1, w.ldn, w.regionStride, BO_TRI_A_UPPER, 0, st));
-        // 3r. [Z_b Q; alpha^T] K(X_tr, X): baseline part of every sample and the mean row
-        BO_TRY(gemm((int)S + 1, (int)N, (int)n, (int)M, 1.0, nei->zq_aug, np, (S + 1) * np, w.W0, w.ldn, w.regionStride, 0.0,
-                    nullptr, 0, 0, w.F, w.ldn, (S + 1) * w.ldn, BO_TRI_NONE, 0, st));
+        // 2r. [Z_b Q; alpha^T; 0; L_W^T] K(X_tr, X) in ONE launch: rows 0..S-1 baseline part of every sample, row S the mean,
+        //     rows S1p.. U = L_W^T K(X_tr, X) (upper-triangular part of the operand: k-range skipped per row tile)
+        const long S1p = bo_pad8(S + 1);
+        BoGemm g{};
+        g.A = nei->fwd_cat; g.lda = np; g.strideA = (S1p + n) * np;
+        g.B = w.W0; g.ldb = w.ldn; g.strideB = w.regionStride;
+        g.C = w.W1; g.ldc = w.ldn; g.strideC = w.regionStride;
+        g.alpha = 1.0; g.M = (int)(S1p + n); g.N = (int)N; g.K = (int)n; g.batch = (int)M;
+        g.tri = BO_TRI_A_UPPER; g.tri_off = (int)S1p; g.epi = BO_EPI_LINEAR;
+        BO_TRY(bo_gemm_launch(g, st));
         BoCandArgs a = cand_args(gp, nei, B, q, X, Z_q, tau_relu, tau_max, w);
         a.V = nullptr;
-        a.BL = w.W1; a.strideBL = w.regionStride; a.n_b = (int)n;
-        a.mu_row = w.F + S * w.ldn; a.strideMu = (S + 1) * w.ldn;
+        a.F = w.W1; a.strideF = w.regionStride;
+        a.BL = w.W1 + S1p * w.ldn; a.strideBL = w.regionStride; a.n_b = (int)n;
+        a.mu_row = w.W1 + S * w.ldn; a.strideMu = w.regionStride;
         a.acq = acq;
         a.info = w.info;
         BO_TRY(bo_cand_fwd(a, st));
@@ -471,27 +482,24 @@ int bo_qlognei_bwd(bo_ctx* ctx, const bo_gp* gp, const bo_nei* nei, int B, int q
     a.Sbar = w.Sbar;
     a.gradX = grad_X;
     if (w.qpath) {
-        const long np = bo_pad8(n), S1p = bo_pad8(S + 1);
-        a.Vbar_mu = w.F + S * w.ldn;  // row S of the sample matrix: [dF; y_std * mubar] is the operand of step 3r
-        a.strideVbar = (S + 1) * w.ldn;
+        const long np = bo_pad8(n), S1p = bo_pad8(S + 1), ldk = S1p + np;
+        a.F = w.W1; a.strideF = w.regionStride;  // samples live in rows 0..S-1 of the stacked forward output
+        a.Vbar_mu = w.W1 + S * w.ldn;             // row S <- y_std * mubar: rows 0..S become [dF; y_std mubar]
+        a.strideVbar = w.regionStride;
         BO_TRY(bo_cand_bwd(a, st));
-        // 2r. Ubar = -2 U Sbar                               (W5)
-        BO_TRY(bo_colblock_update(w.W5, w.regionStride, w.W1, w.regionStride, w.Sbar, (int)n, B, q, (int)M, w.ldn, -2.0, 0,
-                                  st));
-        // 3r. T = [Z_b Q; alpha^T]^T [dF; y_std mubar]       (W3)
-        BO_TRY(gemm((int)n, (int)N, (int)S + 1, (int)M, 1.0, nei->zq_aug_t, S1p, n * S1p, w.F, w.ldn, (S + 1) * w.ldn, 0.0,
-                    nullptr, 0, 0, w.W3, w.ldn, w.regionStride, BO_TRI_NONE, 0, st));
-        // 4r. G = (L_W Ubar + T) .* g(r),  g = K for RBF, the stored derivative factor for Matern   (W2)
+        // 2r. Ubar = -2 U Sbar, in place on rows S1p.. of the same region
+        BO_TRY(bo_colblock_inplace(w.W1 + S1p * w.ldn, w.regionStride, w.Sbar, (int)n, B, q, (int)M, w.ldn, -2.0, st));
+        // 3r. G = ([Z_b Q; alpha^T]^T [dF; y_std mubar] + L_W Ubar) .* g(r) in ONE launch over the stacked operand;
+        //     g = K for RBF, the stored derivative factor for Matern                                          (W2)
         BoGemm g{};
-        g.A = nei->lw; g.lda = np; g.strideA = n * np;
-        g.B = w.W5; g.ldb = w.ldn; g.strideB = w.regionStride;
+        g.A = nei->bwd_cat; g.lda = ldk; g.strideA = n * ldk;
+        g.B = w.W1; g.ldb = w.ldn; g.strideB = w.regionStride;
         g.C = w.W2; g.ldc = w.ldn; g.strideC = w.regionStride;
-        g.D = w.W3; g.ldd = w.ldn; g.strideD = w.regionStride;
         g.E = w.Wd ? w.Wd : w.W0; g.lde = w.ldn; g.strideE = w.regionStride;
-        g.alpha = 1.0; g.beta = 1.0; g.M = (int)n; g.N = (int)N; g.K = (int)n; g.batch = (int)M;
-        g.tri = BO_TRI_A_LOWER; g.epi = BO_EPI_LINEAR;
+        g.alpha = 1.0; g.M = (int)n; g.N = (int)N; g.K = (int)(S1p + n); g.batch = (int)M;
+        g.tri = BO_TRI_A_LOWER; g.tri_off = (int)S1p; g.epi = BO_EPI_LINEAR;
         BO_TRY(bo_gemm_launch(g, st));
-        // 5r. H = [train_X^T; 1] G  ((d+1) x N), then gradX += (H_t - x_t H_d) / l_t^2
+        // 4r. H = [train_X^T; 1] G  ((d+1) x N), then gradX += (H_t - x_t H_d) / l_t^2
         BO_TRY(gemm(gp->d + 1, (int)N, (int)n, (int)M, 1.0, gp->xt_aug, np, 0, w.W2, w.ldn, w.regionStride, 0.0, nullptr, 0, 0,
                     w.H, w.ldn, w.strideH, BO_TRI_NONE, 0, st));
         return bo_kgrad_finalize(h, w.H, w.strideH, w.ldn, X, N, 1.0, grad_X, st);

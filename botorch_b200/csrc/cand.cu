@@ -555,6 +555,36 @@ __global__ void colblock_update_kernel(double* Y, long strideY, const double* Xm
     }
 }
 
+// In-place variant: Y[z][i][b*q + :] <- coef * Y[z][i][b*q + :] * T[z][b]  (one thread owns a whole q-wide row block, so
+// the update is race free).  Used for Ubar = -2 U Sbar on the rows of the stacked forward output.
+template <int QT>
+__global__ void colblock_inplace_kernel(double* Y, long strideY, const double* Tm, int rows, int B, int q, long ldn,
+                                        double coef) {
+    extern __shared__ __align__(16) double st[];  // q*q block of T
+    const int b = blockIdx.x, z = blockIdx.z;
+    const double* T = Tm + ((long)z * B + b) * q * q;
+    for (int i = threadIdx.x; i < q * q; i += blockDim.x) st[i] = T[i];
+    __syncthreads();
+    double* Yz = Y + (long)z * strideY + (long)b * q;
+    for (int i = blockIdx.y * blockDim.x + threadIdx.x; i < rows; i += gridDim.y * blockDim.x) {
+        double* row = Yz + (long)i * ldn;
+        double u[QT], o[QT];
+#pragma unroll
+        for (int k = 0; k < QT; k++) u[k] = (k < q) ? row[k] : 0.0;
+#pragma unroll
+        for (int j = 0; j < QT; j++) {
+            double s_ = 0.0;
+#pragma unroll
+            for (int k = 0; k < QT; k++)
+                if (k < q && j < q) s_ += u[k] * st[k * q + j];
+            o[j] = coef * s_;
+        }
+#pragma unroll
+        for (int j = 0; j < QT; j++)
+            if (j < q) row[j] = o[j];
+    }
+}
+
 // gradX[z][b][j][t] += scale * sum_i Kbar[i][c] * g(r_ic) * (x_i[t] - xc[t]) / l_t^2
 __global__ void __launch_bounds__(CAND_THREADS) kgrad_kernel(BoKernelHyper h, const double* Xpts, int npts,
                                                              const double* Kbar, long strideK, long ldn,
@@ -801,6 +831,20 @@ int bo_colblock_update(double* Y, long strideY, const double* Xm, long strideX, 
     dim3 grid(B, ysplit, M);
     colblock_update_kernel<<<grid, 256, sizeof(double) * q * q, stream>>>(Y, strideY, Xm, strideX, T, rows, B, q, ldn,
                                                                          coef, accumulate);
+    BO_LAUNCH_CHECK();
+    return BO_OK;
+}
+int bo_colblock_inplace(double* Y, long strideY, const double* T, int rows, int B, int q, int M, long ldn, double coef,
+                        cudaStream_t stream) {
+    if (rows <= 0 || B <= 0) return BO_OK;
+    int ysplit = (rows + 511) / 512;
+    if (ysplit > 65535) ysplit = 65535;
+    dim3 grid(B, ysplit, M);
+    const size_t smem = sizeof(double) * q * q;
+    if (q <= 4) colblock_inplace_kernel<4><<<grid, 128, smem, stream>>>(Y, strideY, T, rows, B, q, ldn, coef);
+    else if (q <= 8) colblock_inplace_kernel<8><<<grid, 128, smem, stream>>>(Y, strideY, T, rows, B, q, ldn, coef);
+    else if (q <= 16) colblock_inplace_kernel<16><<<grid, 128, smem, stream>>>(Y, strideY, T, rows, B, q, ldn, coef);
+    else colblock_inplace_kernel<BO_MAX_Q><<<grid, 128, smem, stream>>>(Y, strideY, T, rows, B, q, ldn, coef);
     BO_LAUNCH_CHECK();
     return BO_OK;
 }

@@ -52,6 +52,10 @@ int bo_cand_bwd(const BoCandArgs& a, cudaStream_t stream);
 int bo_colblock_update(double* Y, long strideY, const double* Xm, long strideX, const double* T, int rows, int B,
                        int q, int M, long ldn, double coef, int accumulate, cudaStream_t stream);
 
+// Y[z][i][b*q+:] <- coef * Y[z][i][b*q+:] T[z][b]   (in place)
+int bo_colblock_inplace(double* Y, long strideY, const double* T, int rows, int B, int q, int M, long ldn, double coef,
+                        cudaStream_t stream);
+
 // last step of the GEMM-shaped kernel gradient: gradX[z][c][t] += scale/l_t^2 (H[t][c] - x_c[t] H[d][c])
 int bo_kgrad_finalize(const BoKernelHyper& h, const double* H, long strideH, long ldn, const double* X, long N,
                       double scale, double* gradX, cudaStream_t stream);

@@ -61,6 +61,8 @@ struct BoGemm {
     double alpha, beta;
     int M, N, K, batch;
     int tri;          // BoTri
+    int tri_off;      // A_LOWER: A[m][k] == 0 for k > m + tri_off (tri_off dense leading columns);
+                      // A_UPPER: rows < tri_off are dense, row m >= tri_off has A[m][k] == 0 for k < m - tri_off
     int out_lower;    // 1: skip output tiles strictly above the block diagonal (syrk-style)
     int epi;          // BoEpilogue
     const double* os;        // [batch] outputscale (kernel epilogues), may be null (=1)

@@ -123,8 +123,8 @@ __global__ void __launch_bounds__(C::THREADS) dgemm_dmma_kernel(const BoGemm p) 
     const double* __restrict__ B = p.B + (long)z * p.strideB;
 
     int kb = 0, ke = p.K;
-    if (p.tri == BO_TRI_A_LOWER) ke = min(p.K, m0 + C::BM);
-    else if (p.tri == BO_TRI_A_UPPER) kb = (m0 / C::BK) * C::BK;
+    if (p.tri == BO_TRI_A_LOWER) ke = min(p.K, m0 + C::BM + p.tri_off);
+    else if (p.tri == BO_TRI_A_UPPER) kb = m0 > p.tri_off ? ((m0 - p.tri_off) / C::BK) * C::BK : 0;
     else if (p.tri == BO_TRI_B_LOWER) kb = (n0 / C::BK) * C::BK;
     const int ntiles = ke > kb ? (ke - kb + C::BK - 1) / C::BK : 0;
 
@@ -230,6 +230,8 @@ using CfgT6 = Cfg<128, 128, 16, 32, 32, 3>;   // 16 warps of 32x32 in one CTA
 using CfgT7 = Cfg<64, 128, 16, 32, 64, 3>;    // 4 warps of 32x64
 using CfgT8 = Cfg<64, 64, 32, 32, 32, 2>;     // BK=32, double buffered, 3 CTAs/SM
 using CfgT9 = Cfg<64, 64, 32, 32, 32, 3>;     // BK=32, 3 stages, 2 CTAs/SM
+using CfgT10 = Cfg<64, 64, 16, 32, 32, 2>;    // double buffered, 4 CTAs/SM (16 warps)
+using CfgT11 = Cfg<64, 32, 16, 32, 32, 3>;    // 2 warps per CTA, up to 8 CTAs/SM
 
 template <class C>
 int launch_cfg(const BoGemm& g, cudaStream_t stream) {
@@ -250,9 +252,17 @@ int launch_cfg(const BoGemm& g, cudaStream_t stream) {
             g_prof_recs.push_back(r);
         }
         rec = &g_prof_recs[g_prof_used++];
-        double f = 2.0 * g.M * (double)g.N * g.K * g.batch;
-        if (g.tri != BO_TRI_NONE || g.out_lower) f *= 0.5;  // triangular operand / lower-only output
-        g_prof_flops += f;
+        double macs = (double)g.M * g.K;  // multiply-adds per output column: nonzero entries of A
+        if (g.tri == BO_TRI_A_LOWER) {
+            macs = 0.0;
+            for (int m = 0; m < g.M; m++) macs += (m + 1 + g.tri_off < g.K) ? m + 1 + g.tri_off : g.K;
+        } else if (g.tri == BO_TRI_A_UPPER) {
+            macs = 0.0;
+            for (int m = 0; m < g.M; m++) macs += (m < g.tri_off) ? g.K : ((g.K - (m - g.tri_off) > 0) ? g.K - (m - g.tri_off) : 0);
+        } else if (g.tri == BO_TRI_B_LOWER || g.out_lower) {
+            macs *= 0.5;
+        }
+        g_prof_flops += 2.0 * macs * g.N * g.batch;
         BO_CUDA_TRY(cudaEventRecord(rec->a, stream));
     }
     dgemm_dmma_kernel<C><<<grid, C::THREADS, C::SMEM, stream>>>(g);
@@ -283,12 +293,14 @@ int bo_gemm_launch(const BoGemm& g, cudaStream_t stream) {
         case 7: return launch_cfg<CfgT7>(g, stream);
         case 8: return launch_cfg<CfgT8>(g, stream);
         case 9: return launch_cfg<CfgT9>(g, stream);
+        case 10: return launch_cfg<CfgT10>(g, stream);
+        case 11: return launch_cfg<CfgT11>(g, stream);
         default: break;
     }
     auto tiles = [&](int bm, int bn) { return (long)((g.M + bm - 1) / bm) * ((g.N + bn - 1) / bn) * g.batch; };
     // Pick the largest tile that still fills the 148 SMs; small problems trade tile efficiency for occupancy.
     // 64x64 tiles with 4 warps, 3 CTAs per SM: measured best on B200 (tools/gemm_bench.py) --
     // co-resident small CTAs keep the DMMA pipe fed through each other's barriers and shrink the last wave.
-    if (tiles(64, 64) >= 120 || (g.M >= 48 && g.N >= 48 && tiles(32, 32) > 2048)) return launch_cfg<CfgMid>(g, stream);
+    if (tiles(64, 64) >= 120 || (g.M >= 48 && g.N >= 48 && tiles(32, 32) > 2048)) return launch_cfg<CfgT10>(g, stream);
     return launch_cfg<CfgSmall>(g, stream);
 }

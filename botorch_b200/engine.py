@@ -198,17 +198,16 @@ class NEIState:
         self.best_f_pad = z(M, Sp)
         self.qmat = z(M, nb, gp.np_) if self.is_train else None
         self.qmat_t = z(M, n, nbp) if self.is_train else None
-        self.lw = z(M, n, gp.np_) if self.is_train else None
-        self.lw_t = z(M, n, gp.np_) if self.is_train else None
-        self.zq_aug = z(M, S + 1, gp.np_) if self.is_train else None
-        self.zq_aug_t = z(M, n, pad8(S + 1)) if self.is_train else None
+        S1p = pad8(S + 1)
+        self.fwd_cat = z(M, S1p + n, gp.np_) if self.is_train else None
+        self.bwd_cat = z(M, n, S1p + gp.np_) if self.is_train else None
         self.info = torch.zeros(M, dtype=torch.int32, device=dev)
         self.c = BoNEI(
             n_b=nb, S=S, baseline_is_train=int(self.is_train), X_b=ptr(self.X_b), Z_b=ptr(self.Z_b), jitter=None,
             aug_b=ptr(self.aug_b), vb=ptr(self.vb), vb_t=ptr(self.vb_t), lb=ptr(self.lb), lb_inv=ptr(self.lb_inv),
             lb_inv_t=ptr(self.lb_inv_t), zb_pad=ptr(self.zb_pad), zb_t=ptr(self.zb_t), mean_b=ptr(self.mean_b),
             best_f=ptr(self.best_f_pad), qmat=ptr(self.qmat), qmat_t=ptr(self.qmat_t),
-            lw=ptr(self.lw), lw_t=ptr(self.lw_t), zq_aug=ptr(self.zq_aug), zq_aug_t=ptr(self.zq_aug_t),
+            fwd_cat=ptr(self.fwd_cat), bwd_cat=ptr(self.bwd_cat),
         )  # fmt: skip
         self.jitter = torch.zeros(M, dtype=torch.float64, device=dev)
         if not setup:
@@ -230,7 +229,7 @@ class NEIState:
         bufs = [self.vb, self.vb_t, self.lb, self.lb_inv, self.lb_inv_t, self.zb_pad, self.zb_t, self.mean_b,
                 self.best_f_pad, self.jitter]  # fmt: skip
         bufs += [] if self.aug_b is None else [self.aug_b]
-        return bufs + ([] if self.qmat is None else [self.qmat, self.qmat_t, self.lw, self.lw_t, self.zq_aug, self.zq_aug_t])
+        return bufs + ([] if self.qmat is None else [self.qmat, self.qmat_t, self.fwd_cat, self.bwd_cat])
 
     @property
     def baseline_L(self) -> Tensor:

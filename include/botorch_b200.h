@@ -87,10 +87,10 @@ typedef struct bo_nei {
     double* qmat_t;            /* [M][n x nbp]    Q^T */
     /* combined root: ys^2 (K+s2 I)^-1 + Q^T Q = L_W L_W^T, so the q x q Schur block of a candidate is
      * ys^2 k(x,x') - U^T U with U = L_W^T K(X_tr, X): one triangular GEMM replaces V, Sigma(X_b,X) and bl_chol */
-    double* lw;                /* [M][n x np]     L_W (lower) */
-    double* lw_t;              /* [M][n x np]     L_W^T (upper) */
-    double* zq_aug;            /* [M][(S+1) x np] rows 0..S-1: Z_b Q (baseline part of the samples = (Z_b Q) K(X_tr,X)); row S: alpha */
-    double* zq_aug_t;          /* [M][n x pad8(S+1)] its transpose */
+    /* stacked operands, S1p = pad8(S+1): */
+    double* fwd_cat;           /* [M][(S1p+n) x np]   rows 0..S-1: Z_b Q (baseline part of the samples = (Z_b Q) K(X_tr,X)); row S: alpha;
+                                *                      rows S+1..S1p-1: 0; rows S1p+i: row i of L_W^T  -> one forward GEMM */
+    double* bwd_cat;           /* [M][n x (S1p+np)]   [ fwd rows 0..S1p-1 transposed | L_W ]             -> one backward GEMM */
 } bo_nei;
 
 typedef struct bo_ctx bo_ctx;
