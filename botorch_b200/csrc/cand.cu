@@ -58,42 +58,62 @@ __device__ __forceinline__ double dlog_fatplus(double z, double tau) {
 }
 __device__ __forceinline__ double pareto2(double u) { return 2.0 / (2.0 + 2.0 * u + u * u); }
 
-// fatmax over x[0..q) (alpha = 2) with the infinity handling of _inf_max_helper
-__device__ __forceinline__ double fatmax_q(const double* x, int q, double tau) {
+// fatmax over x[0..q) (alpha = 2) with the infinity handling of _inf_max_helper.  QT >= q is a compile-time bound:
+// every loop is fully unrolled with a (j < q) guard so that the per-sample arrays stay in registers.
+template <int QT>
+__device__ __forceinline__ double fatmax_q(const double (&x)[QT], int q, double tau) {
     double M = x[0];
-    for (int j = 1; j < q; j++) M = fmax(M, x[j]);  // NaN-ignoring like amax is not needed: NaN flagged earlier
+#pragma unroll
+    for (int j = 1; j < QT; j++)
+        if (j < q) M = fmax(M, x[j]);  // NaN-ignoring like amax is not needed: NaN flagged earlier
     if (isinf(M)) {
         double s = 0.0;
-        for (int j = 0; j < q; j++) if (x[j] == M) s += x[j];
+#pragma unroll
+        for (int j = 0; j < QT; j++)
+            if (j < q && x[j] == M) s += x[j];
         return s;
     }
     double sum = 0.0;
-    for (int j = 0; j < q; j++) sum += pareto2(-(x[j] - M) / tau);
+#pragma unroll
+    for (int j = 0; j < QT; j++)
+        if (j < q) sum += pareto2(-(x[j] - M) / tau);
     return M + tau * log(sum);
 }
 // gradient of fatmax w.r.t. x (g[0..q))
-__device__ __forceinline__ void fatmax_q_grad(const double* x, int q, double tau, double* g) {
+template <int QT>
+__device__ __forceinline__ void fatmax_q_grad(const double (&x)[QT], int q, double tau, double (&g)[QT]) {
     double M = x[0];
-    for (int j = 1; j < q; j++) M = fmax(M, x[j]);
+#pragma unroll
+    for (int j = 1; j < QT; j++)
+        if (j < q) M = fmax(M, x[j]);
     if (isinf(M)) {
-        for (int j = 0; j < q; j++) g[j] = (x[j] == M) ? 1.0 : 0.0;
+#pragma unroll
+        for (int j = 0; j < QT; j++) g[j] = (j < q && x[j] == M) ? 1.0 : 0.0;
         return;
     }
     double sum = 0.0;
     int nties = 0;
-    for (int j = 0; j < q; j++) {
-        sum += pareto2(-(x[j] - M) / tau);
-        nties += (x[j] == M);
-    }
+#pragma unroll
+    for (int j = 0; j < QT; j++)
+        if (j < q) {
+            sum += pareto2(-(x[j] - M) / tau);
+            nties += (x[j] == M);
+        }
     double wsum = 0.0;
-    for (int j = 0; j < q; j++) {
-        const double u = -(x[j] - M) / tau;
-        const double p = pareto2(u);
-        g[j] = isinf(u) ? 0.0 : p * p * (1.0 + u) / sum;
-        wsum += g[j];
+#pragma unroll
+    for (int j = 0; j < QT; j++) {
+        g[j] = 0.0;
+        if (j < q) {
+            const double u = -(x[j] - M) / tau;
+            const double p = pareto2(u);
+            g[j] = isinf(u) ? 0.0 : p * p * (1.0 + u) / sum;
+            wsum += g[j];
+        }
     }
     const double rest = (1.0 - wsum) / nties;  // amax subgradient, split evenly among ties (torch.amax)
-    for (int j = 0; j < q; j++) if (x[j] == M) g[j] += rest;
+#pragma unroll
+    for (int j = 0; j < QT; j++)
+        if (j < q && x[j] == M) g[j] += rest;
 }
 
 __device__ __forceinline__ double block_reduce_max(double v, double* red) {
@@ -320,7 +340,8 @@ __device__ __forceinline__ double pair_r2(const double* X, int d, const double* 
     return r2;
 }
 
-__global__ void __launch_bounds__(CAND_THREADS) cand_fwd_kernel(const BoCandArgs a) {
+template <int QT>
+__global__ void __launch_bounds__(CAND_THREADS, (QT <= 4 ? 6 : (QT <= 8 ? 4 : 1))) cand_fwd_kernel(const BoCandArgs a) {
     extern __shared__ __align__(16) double sm[];
     __shared__ double red[CAND_THREADS / 32];
     __shared__ int s_info;
@@ -380,16 +401,24 @@ __global__ void __launch_bounds__(CAND_THREADS) cand_fwd_kernel(const BoCandArgs
     int bad = 0;
     double local_max = -INFINITY;
     for (int s = tid; s < a.S; s += T) {
-        double li[BO_MAX_Q];
+        double li[QT], zq[QT];
         const double bf = a.best_f[(long)z * a.Sp + s];
-        for (int j = 0; j < q; j++) {
-            double v = F[(long)s * a.ldn + c0 + j] + c.mu[j];
-            for (int k = 0; k <= j; k++) v += c.Lq[j * q + k] * a.Zq[(long)s * q + k];
-            F[(long)s * a.ldn + c0 + j] = v;
-            if (!isfinite(v)) bad = 1;
-            li[j] = log_fatplus(v - bf, a.tau_relu);
+#pragma unroll
+        for (int j = 0; j < QT; j++) zq[j] = (j < q) ? a.Zq[(long)s * q + j] : 0.0;
+#pragma unroll
+        for (int j = 0; j < QT; j++) {
+            li[j] = 0.0;
+            if (j < q) {
+                double v = F[(long)s * a.ldn + c0 + j] + c.mu[j];
+#pragma unroll
+                for (int k = 0; k < QT; k++)
+                    if (k <= j) v += c.Lq[j * q + k] * zq[k];
+                F[(long)s * a.ldn + c0 + j] = v;
+                if (!isfinite(v)) bad = 1;
+                li[j] = log_fatplus(v - bf, a.tau_relu);
+            }
         }
-        const double m = fatmax_q(li, q, a.tau_max);
+        const double m = fatmax_q<QT>(li, q, a.tau_max);
         c.fm[s] = m;
         local_max = fmax(local_max, m);
     }
@@ -420,7 +449,8 @@ namespace {
 //   in : F holds the samples f[s][j];  Lq = br_chol;  lse;  grad_acq
 //   out: F <- d loss / d f ;  Sbar = adjoint of the Schur block (symmetric);
 //        Vbar row n <- y_std * d loss / d mu ;  gradX <- contribution of k(X, X)
-__global__ void __launch_bounds__(CAND_THREADS) cand_bwd_kernel(const BoCandArgs a) {
+template <int QT>
+__global__ void __launch_bounds__(CAND_THREADS, (QT <= 4 ? 6 : (QT <= 8 ? 3 : 1))) cand_bwd_kernel(const BoCandArgs a) {
     extern __shared__ __align__(16) double sm[];
     const int q = a.q, b = blockIdx.x, z = blockIdx.y, tid = threadIdx.x, T = blockDim.x;
     const int c0 = b * q;
@@ -435,36 +465,71 @@ __global__ void __launch_bounds__(CAND_THREADS) cand_bwd_kernel(const BoCandArgs
     const double lse = a.lse[o];
     for (int idx = tid; idx < q * q; idx += T) L[idx] = a.Lq[o * q * q + idx];
 
-    // 1. d loss / d f, written in place
+    // 1+2. d loss / d f, written in place; mu_bar[j] = sum_s df[s][j] and Lbar[j][k] = sum_s df[s][j] Zq[s][k] (k <= j)
+    //      accumulated in registers on the fly, then a fixed shuffle tree + fixed-order sum over warps (deterministic)
+    constexpr int PT = QT * (QT + 1) / 2;
+    double* red = mubar + q;  // (T/32) x (QT + PT)
+    double am[QT], al[PT];
+#pragma unroll
+    for (int j = 0; j < QT; j++) am[j] = 0.0;
+#pragma unroll
+    for (int p = 0; p < PT; p++) al[p] = 0.0;
     for (int s = tid; s < a.S; s += T) {
-        double f[BO_MAX_Q], li[BO_MAX_Q], gm[BO_MAX_Q];
+        double f[QT], li[QT], gm[QT], zq[QT];
         const double bf = a.best_f[(long)z * a.Sp + s];
-        for (int j = 0; j < q; j++) {
-            f[j] = F[(long)s * a.ldn + c0 + j];
-            li[j] = log_fatplus(f[j] - bf, a.tau_relu);
+#pragma unroll
+        for (int j = 0; j < QT; j++) {
+            f[j] = 0.0; li[j] = 0.0; zq[j] = 0.0;
+            if (j < q) {
+                f[j] = F[(long)s * a.ldn + c0 + j];
+                li[j] = log_fatplus(f[j] - bf, a.tau_relu);
+                zq[j] = a.Zq[(long)s * q + j];
+            }
         }
-        const double m = fatmax_q(li, q, a.tau_max);
+        const double m = fatmax_q<QT>(li, q, a.tau_max);
         // logmeanexp over samples: softmax weight; +-inf maximum -> unit gradient on the infinite entries
         const double w = isinf(lse) ? ((m == lse) ? 1.0 : 0.0) : exp(m - lse);
-        fatmax_q_grad(li, q, a.tau_max, gm);
-        for (int j = 0; j < q; j++) {
-            const double dli = isinf(li[j]) ? 0.0 : dlog_fatplus(f[j] - bf, a.tau_relu);
-            F[(long)s * a.ldn + c0 + j] = g * w * gm[j] * dli;
+        fatmax_q_grad<QT>(li, q, a.tau_max, gm);
+        int p = 0;
+#pragma unroll
+        for (int j = 0; j < QT; j++) {
+            double df = 0.0;
+            if (j < q) {
+                const double dli = isinf(li[j]) ? 0.0 : dlog_fatplus(f[j] - bf, a.tau_relu);
+                df = g * w * gm[j] * dli;
+                F[(long)s * a.ldn + c0 + j] = df;
+            }
+            am[j] += df;
+#pragma unroll
+            for (int k = 0; k <= j; k++) al[p++] += df * zq[k];
         }
     }
-    __syncthreads();  // block-scope visibility of the in-place writes
-
-    // 2. mu_bar[j] = sum_s df[s][j];  Lbar[j][k] = sum_s df[s][j] Zq[s][k]  (k <= j) -- fixed order
+    {
+        const int warp = tid >> 5, lane = tid & 31;
+#pragma unroll
+        for (int j = 0; j < QT; j++) {
+            double v = am[j];
+            for (int o2 = 16; o2 > 0; o2 >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o2);
+            if (lane == 0) red[warp * (QT + PT) + j] = v;
+        }
+#pragma unroll
+        for (int p = 0; p < PT; p++) {
+            double v = al[p];
+            for (int o2 = 16; o2 > 0; o2 >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o2);
+            if (lane == 0) red[warp * (QT + PT) + QT + p] = v;
+        }
+    }
+    __syncthreads();
     for (int idx = tid; idx < q + q * q; idx += T) {
         if (idx < q) {
             double s_ = 0.0;
-            for (int s = 0; s < a.S; s++) s_ += F[(long)s * a.ldn + c0 + idx];
+            for (int w2 = 0; w2 < (T >> 5); w2++) s_ += red[w2 * (QT + PT) + idx];
             mubar[idx] = s_;
         } else {
             const int j = (idx - q) / q, k = (idx - q) % q;
             double s_ = 0.0;
             if (k <= j)
-                for (int s = 0; s < a.S; s++) s_ += F[(long)s * a.ldn + c0 + j] * a.Zq[(long)s * q + k];
+                for (int w2 = 0; w2 < (T >> 5); w2++) s_ += red[w2 * (QT + PT) + QT + j * (j + 1) / 2 + k];
             Lbar[j * q + k] = s_;
         }
     }
@@ -532,7 +597,9 @@ __global__ void __launch_bounds__(CAND_THREADS) cand_bwd_kernel(const BoCandArgs
         gX[idx] = acc;
     }
 }
-size_t cand_bwd_smem_bytes(int q) { return sizeof(double) * (size_t)(4 * q * q + q); }
+size_t cand_bwd_smem_bytes(int q, int QT) {
+    return sizeof(double) * (size_t)(4 * q * q + q + (CAND_THREADS / 32) * (QT + QT * (QT + 1) / 2));
+}
 
 __global__ void colblock_update_kernel(double* Y, long strideY, const double* Xm, long strideX, const double* Tm,
                                        int rows, int B, int q, long ldn, double coef, int accumulate) {
@@ -555,10 +622,10 @@ __global__ void colblock_update_kernel(double* Y, long strideY, const double* Xm
     }
 }
 
-// In-place variant: Y[z][i][b*q + :] <- coef * Y[z][i][b*q + :] * T[z][b]  (one thread owns a whole q-wide row block, so
-// the update is race free).  Used for Ubar = -2 U Sbar on the rows of the stacked forward output.
-template <int QT>
-__global__ void colblock_inplace_kernel(double* Y, long strideY, const double* Tm, int rows, int B, int q, long ldn,
+// In-place variant: Y[z][i][b*q + :] <- coef * Y[z][i][b*q + :] * T[z][b].  G = next power of two >= q lanes share one
+// row block (lane j of the group produces column j), so a warp touches 32/G rows per instruction with the same
+// coalescing as the out-of-place kernel; all loads of a group precede its stores (__syncwarp), groups never span warps.
+__global__ void colblock_inplace_kernel(double* Y, long strideY, const double* Tm, int rows, int B, int q, int G, long ldn,
                                         double coef) {
     extern __shared__ __align__(16) double st[];  // q*q block of T
     const int b = blockIdx.x, z = blockIdx.z;
@@ -566,22 +633,18 @@ __global__ void colblock_inplace_kernel(double* Y, long strideY, const double* T
     for (int i = threadIdx.x; i < q * q; i += blockDim.x) st[i] = T[i];
     __syncthreads();
     double* Yz = Y + (long)z * strideY + (long)b * q;
-    for (int i = blockIdx.y * blockDim.x + threadIdx.x; i < rows; i += gridDim.y * blockDim.x) {
+    const int j = threadIdx.x % G, sub = threadIdx.x / G, per = blockDim.x / G;
+    const int rows_per = (rows + gridDim.y - 1) / gridDim.y;
+    const int r_lo = blockIdx.y * rows_per, r_hi = min(rows, r_lo + rows_per);
+    for (int i0 = r_lo; i0 < r_hi; i0 += per) {  // uniform trip count per warp: __syncwarp below is safe
+        const int i = i0 + sub;
+        const bool live = i < r_hi && j < q;
+        double s_ = 0.0;
         double* row = Yz + (long)i * ldn;
-        double u[QT], o[QT];
-#pragma unroll
-        for (int k = 0; k < QT; k++) u[k] = (k < q) ? row[k] : 0.0;
-#pragma unroll
-        for (int j = 0; j < QT; j++) {
-            double s_ = 0.0;
-#pragma unroll
-            for (int k = 0; k < QT; k++)
-                if (k < q && j < q) s_ += u[k] * st[k * q + j];
-            o[j] = coef * s_;
-        }
-#pragma unroll
-        for (int j = 0; j < QT; j++)
-            if (j < q) row[j] = o[j];
+        if (live)
+            for (int k = 0; k < q; k++) s_ += row[k] * st[k * q + j];
+        __syncwarp();
+        if (live) row[j] = coef * s_;
     }
 }
 
@@ -809,9 +872,20 @@ int bo_cand_fwd(const BoCandArgs& a, cudaStream_t stream) {
     if (a.B <= 0) return BO_OK;
     const size_t smem = cand_smem_bytes(a.q, CAND_THREADS, a.S);
     if (smem > 200 * 1024) return BO_ERR_UNSUPPORTED;
-    BO_TRY(set_smem_limit((const void*)cand_fwd_kernel, smem));
     dim3 grid(a.B, a.h.M);
-    cand_fwd_kernel<<<grid, CAND_THREADS, smem, stream>>>(a);
+    if (a.q <= 4) {
+        BO_TRY(set_smem_limit((const void*)cand_fwd_kernel<4>, smem));
+        cand_fwd_kernel<4><<<grid, CAND_THREADS, smem, stream>>>(a);
+    } else if (a.q <= 8) {
+        BO_TRY(set_smem_limit((const void*)cand_fwd_kernel<8>, smem));
+        cand_fwd_kernel<8><<<grid, CAND_THREADS, smem, stream>>>(a);
+    } else if (a.q <= 16) {
+        BO_TRY(set_smem_limit((const void*)cand_fwd_kernel<16>, smem));
+        cand_fwd_kernel<16><<<grid, CAND_THREADS, smem, stream>>>(a);
+    } else {
+        BO_TRY(set_smem_limit((const void*)cand_fwd_kernel<BO_MAX_Q>, smem));
+        cand_fwd_kernel<BO_MAX_Q><<<grid, CAND_THREADS, smem, stream>>>(a);
+    }
     BO_LAUNCH_CHECK();
     return BO_OK;
 }
@@ -819,7 +893,14 @@ int bo_cand_bwd(const BoCandArgs& a, cudaStream_t stream) {
     if (a.q < 1 || a.q > BO_MAX_Q || a.h.d > BO_MAX_D) return BO_ERR_UNSUPPORTED;
     if (a.B <= 0) return BO_OK;
     dim3 grid(a.B, a.h.M);
-    cand_bwd_kernel<<<grid, CAND_THREADS, cand_bwd_smem_bytes(a.q), stream>>>(a);
+    if (a.q <= 4) cand_bwd_kernel<4><<<grid, CAND_THREADS, cand_bwd_smem_bytes(a.q, 4), stream>>>(a);
+    else if (a.q <= 8) cand_bwd_kernel<8><<<grid, CAND_THREADS, cand_bwd_smem_bytes(a.q, 8), stream>>>(a);
+    else if (a.q <= 12) cand_bwd_kernel<12><<<grid, CAND_THREADS, cand_bwd_smem_bytes(a.q, 12), stream>>>(a);
+    else {
+        const size_t smem = cand_bwd_smem_bytes(a.q, BO_MAX_Q);
+        BO_TRY(set_smem_limit((const void*)cand_bwd_kernel<BO_MAX_Q>, smem));
+        cand_bwd_kernel<BO_MAX_Q><<<grid, CAND_THREADS, smem, stream>>>(a);
+    }
     BO_LAUNCH_CHECK();
     return BO_OK;
 }
@@ -837,14 +918,12 @@ int bo_colblock_update(double* Y, long strideY, const double* Xm, long strideX, 
 int bo_colblock_inplace(double* Y, long strideY, const double* T, int rows, int B, int q, int M, long ldn, double coef,
                         cudaStream_t stream) {
     if (rows <= 0 || B <= 0) return BO_OK;
-    int ysplit = (rows + 511) / 512;
+    int ysplit = (rows + 255) / 256;
     if (ysplit > 65535) ysplit = 65535;
     dim3 grid(B, ysplit, M);
-    const size_t smem = sizeof(double) * q * q;
-    if (q <= 4) colblock_inplace_kernel<4><<<grid, 128, smem, stream>>>(Y, strideY, T, rows, B, q, ldn, coef);
-    else if (q <= 8) colblock_inplace_kernel<8><<<grid, 128, smem, stream>>>(Y, strideY, T, rows, B, q, ldn, coef);
-    else if (q <= 16) colblock_inplace_kernel<16><<<grid, 128, smem, stream>>>(Y, strideY, T, rows, B, q, ldn, coef);
-    else colblock_inplace_kernel<BO_MAX_Q><<<grid, 128, smem, stream>>>(Y, strideY, T, rows, B, q, ldn, coef);
+    int G = 1;
+    while (G < q) G <<= 1;
+    colblock_inplace_kernel<<<grid, 256, sizeof(double) * q * q, stream>>>(Y, strideY, T, rows, B, q, G, ldn, coef);
     BO_LAUNCH_CHECK();
     return BO_OK;
 }
