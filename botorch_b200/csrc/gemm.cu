@@ -128,29 +128,57 @@ __global__ void __launch_bounds__(C::THREADS) dgemm_dmma_kernel(const BoGemm p) 
     else if (p.tri == BO_TRI_B_LOWER) kb = (n0 / C::BK) * C::BK;
     const int ntiles = ke > kb ? (ke - kb + C::BK - 1) / C::BK : 0;
 
+    // Per-thread copy plan, fixed for the whole k loop: every thread moves NA 16-byte chunks of the A tile and NB of the B
+    // tile per stage.  Source pointers, validity and shared-memory addresses are computed once; a k-tile then costs one
+    // pointer add per chunk (the generic bounds logic only runs for the ragged last tile).
+    constexpr int ACH = C::BK / 2, BCH = C::BN / 2;  // 16-byte chunks per A row / B row
+    constexpr int NA = (C::BM * ACH) / C::THREADS, NB = (C::BK * BCH) / C::THREADS;
+    static_assert((C::BM * ACH) % C::THREADS == 0 && (C::BK * BCH) % C::THREADS == 0, "copy plan");
+    const double* a_src[NA];
+    const double* b_src[NB];
+    unsigned a_dst[NA], b_dst[NB];
+    int a_bytes[NA], b_bytes[NB];
+    const unsigned as0 = (unsigned)__cvta_generic_to_shared(As), bs0 = (unsigned)__cvta_generic_to_shared(Bs);
+#pragma unroll
+    for (int i = 0; i < NA; i++) {
+        const int id = tid + i * C::THREADS, r = id / ACH, cc = id % ACH, row = m0 + r;
+        a_bytes[i] = row < p.M ? 16 : 0;
+        a_src[i] = A + (long)(row < p.M ? row : 0) * p.lda + 2 * cc + kb;
+        a_dst[i] = as0 + (unsigned)((r * C::LDA_S + 2 * cc) * sizeof(double));
+    }
+#pragma unroll
+    for (int i = 0; i < NB; i++) {
+        const int id = tid + i * C::THREADS, r = id / BCH, cc = id % BCH, col = n0 + 2 * cc;
+        b_bytes[i] = max(0, min(16, (p.N - col) * 8));
+        b_src[i] = B + (long)(kb + r) * p.ldb + (b_bytes[i] > 0 ? col : 0);
+        b_dst[i] = bs0 + (unsigned)((r * C::LDB_S + 2 * cc) * sizeof(double));
+    }
+    const long b_step = (long)C::BK * p.ldb;
+    auto cp16 = [](unsigned dst, const void* src, int bytes) {
+        asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;\n" ::"r"(dst), "l"(src), "r"(bytes));
+    };
     auto load_tile = [&](int tile, int stage) {
         const int k0 = kb + tile * C::BK;
-        double* as = As + (size_t)stage * C::A_STAGE;
-        double* bs = Bs + (size_t)stage * C::B_STAGE;
-        constexpr int ACH = C::BK / 2;  // 16-byte chunks per A row
+        const unsigned a_off = (unsigned)(stage * C::A_STAGE * sizeof(double));
+        const unsigned b_off = (unsigned)(stage * C::B_STAGE * sizeof(double));
+        if (k0 + C::BK <= ke) {  // interior tile: no k bounds
 #pragma unroll
-        for (int id = tid; id < C::BM * ACH; id += C::THREADS) {
-            const int r = id / ACH, cc = id % ACH;
-            const int row = m0 + r, k = k0 + 2 * cc;
-            int bytes = 0;
-            if (row < p.M) bytes = max(0, min(16, (ke - k) * 8));
-            const double* src = bytes > 0 ? (A + (long)row * p.lda + k) : A;
-            cp_async16(as + r * C::LDA_S + 2 * cc, src, bytes);
-        }
-        constexpr int BCH = C::BN / 2;
+            for (int i = 0; i < NA; i++) cp16(a_dst[i] + a_off, a_src[i] + (long)tile * C::BK, a_bytes[i]);
 #pragma unroll
-        for (int id = tid; id < C::BK * BCH; id += C::THREADS) {
-            const int r = id / BCH, cc = id % BCH;
-            const int k = k0 + r, col = n0 + 2 * cc;
-            int bytes = 0;
-            if (k < ke) bytes = max(0, min(16, (p.N - col) * 8));
-            const double* src = bytes > 0 ? (B + (long)k * p.ldb + col) : B;
-            cp_async16(bs + r * C::LDB_S + 2 * cc, src, bytes);
+            for (int i = 0; i < NB; i++) cp16(b_dst[i] + b_off, b_src[i] + tile * b_step, b_bytes[i]);
+        } else {  // ragged last tile: clip (zero-fill) beyond ke
+#pragma unroll
+            for (int i = 0; i < NA; i++) {
+                const int id = tid + i * C::THREADS, cc = id % ACH, k = k0 + 2 * cc;
+                const int bytes = a_bytes[i] ? max(0, min(16, (ke - k) * 8)) : 0;
+                cp16(a_dst[i] + a_off, bytes > 0 ? a_src[i] + (long)tile * C::BK : A, bytes);
+            }
+#pragma unroll
+            for (int i = 0; i < NB; i++) {
+                const int id = tid + i * C::THREADS, r = id / BCH;
+                const int bytes = (k0 + r < ke) ? b_bytes[i] : 0;
+                cp16(b_dst[i] + b_off, bytes > 0 ? b_src[i] + tile * b_step : B, bytes);
+            }
         }
     };
 
