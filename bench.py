@@ -29,6 +29,10 @@ sys.path.insert(0, ROOT)
 
 METRIC = "qLogNEI fwd+bwd candidate evals/s"
 UNIT = "candidate_evals/s"
+# dram__bytes_read.sum + dram__bytes_write.sum of the four dgemm_dmma_kernel launches of one step, averaged per launch,
+# from the `ncu --set full` capture of this command at the default workload (profiles/r01_ncu_full_step_v3.csv:
+# 14.9 + 151.3 + 328.1 + 66.5 MB).  Algorithmic operand bytes of the same four launches: ~550 MB, i.e. no re-reads.
+NCU_GEMM_TRAFFIC_BYTES_PER_LAUNCH = {("C3", 512): 140.2e6}
 FP64_DMMA_PEAK_TFLOPS = 37.07  # measured on this pool's B200 with tools/fp64_peaks.cu (profiles/r01_fp64_peaks.txt)
 
 
@@ -333,7 +337,9 @@ def _run_ours(args):
         "tflops_fp64_executed_whole_step": value * executed_per_eval / 1e12,
         "roofline": {
             "bound": "tensor", "achieved": gemm_tflops, "peak": FP64_DMMA_PEAK_TFLOPS, "unit": "TFLOP/s",
-            "frac": gemm_tflops / FP64_DMMA_PEAK_TFLOPS, "traffic": None, "kernel": "dgemm_dmma_kernel",
+            "frac": gemm_tflops / FP64_DMMA_PEAK_TFLOPS, "traffic": NCU_GEMM_TRAFFIC_BYTES_PER_LAUNCH.get((args.config, B)), "kernel": "dgemm_dmma_kernel",
+            "traffic_note": "bytes per launch (mean over the step's GEMM launches) from profiles/r01_ncu_full_step_v3.csv; "
+                            "null for workloads without a committed capture",
             "peak_source": "FP64 DMMA peak measured on this pool (tools/fp64_peaks.cu, profiles/r01_fp64_peaks.txt); "
                            "MEASURED_PEAKS.json holds no FP64 figure",
             "launches_per_step": gemm_n.value / args.steps, "avg_launch_ms": gemm_ms.value / max(gemm_n.value, 1),
