@@ -5,7 +5,14 @@ the multi-start optimiser seam and its multi-GPU sharding.  Python is the host l
 Python; every number is produced by ``csrc/libbotorch_b200.so`` through the C ABI in ``include/botorch_b200.h``.
 There is no CPU fallback: importing is cheap, the first compute call raises if the library or a B200 is missing.
 """
-from .acquisition import AcquisitionFunction, qLogNoisyExpectedImprovement  # noqa: F401
+from .acquisition import (  # noqa: F401
+    AcquisitionFunction,
+    prune_inferior_points,
+    qExpectedImprovement,
+    qLogExpectedImprovement,
+    qLogNoisyExpectedImprovement,
+    qNoisyExpectedImprovement,
+)
 from .generation import MaxPosteriorSampling  # noqa: F401
 from .models import SaasFullyBayesianSingleTaskGP, SingleTaskGP, Standardize  # noqa: F401
 from .optim import (  # noqa: F401

@@ -62,6 +62,8 @@ class BoNEI(C.Structure):
         ("qmat_t", C.c_void_p),
         ("fwd_cat", C.c_void_p),
         ("bwd_cat", C.c_void_p),
+        ("reduction", C.c_int32),
+        ("no_baseline", C.c_int32),
     ]
 
 
@@ -98,6 +100,11 @@ def _declare(lib: C.CDLL) -> None:
     lib.bo_nei_setup_workspace_bytes.restype = sz
     lib.bo_nei_setup_workspace_bytes.argtypes = [gp, nei]
     lib.bo_nei_setup.argtypes = [vp, gp, nei, vp, sz, vp, vp]
+    lib.bo_nei_dense_rows.restype = i64
+    lib.bo_nei_dense_rows.argtypes = [nei]
+    lib.bo_ei_setup_workspace_bytes.restype = sz
+    lib.bo_ei_setup_workspace_bytes.argtypes = [gp, nei]
+    lib.bo_ei_setup.argtypes = [vp, gp, nei, vp, sz, vp, vp]
     lib.bo_qlognei_workspace_bytes.restype = sz
     lib.bo_qlognei_workspace_bytes.argtypes = [gp, nei, i32, i32, i32]
     lib.bo_qlognei_fwd.argtypes = [vp, gp, nei, i32, i32, vp, vp, dbl, dbl, vp, vp, vp, sz, i32, vp]
@@ -117,7 +124,7 @@ def _declare(lib: C.CDLL) -> None:
     lib.bo_potrf_workspace_bytes.argtypes = [i32, i32]
     lib.bo_potrf.argtypes = [vp, i32, i32, vp, i64, i64, vp, vp, sz, vp, vp]
     for name in (
-        "bo_ctx_create bo_gp_setup bo_nei_setup bo_qlognei_fwd bo_qlognei_bwd bo_posterior_joint bo_posterior_joint_bwd "
+        "bo_ctx_create bo_gp_setup bo_nei_setup bo_ei_setup bo_qlognei_fwd bo_qlognei_bwd bo_posterior_joint bo_posterior_joint_bwd "
         "bo_posterior_mean_var bo_ts_argmax bo_argmax bo_dgemm bo_kernel_matrix bo_potrf"
     ).split():
         getattr(lib, name).restype = i32

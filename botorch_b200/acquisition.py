@@ -26,7 +26,8 @@ from torch import Tensor
 from torch.nn import Module
 
 from . import engine
-from .exceptions import BotorchWarning, NumericalWarning, UnsupportedError
+from .exceptions import BotorchWarning, NumericalWarning, NumericsWarning, UnsupportedError
+from .posteriors import MCMC_DIM
 from .models import Model, _FusedExactGP
 from .sampling import MCSampler, SobolQMCNormalSampler, get_sampler
 
@@ -59,6 +60,66 @@ class AcquisitionFunction(Module):
 
     def forward(self, X: Tensor) -> Tensor:  # pragma: no cover - abstract
         raise NotImplementedError
+
+
+def legacy_ei_numerics_warning(legacy_name: str) -> None:
+    """NumericsWarning pointing from a legacy EI class to its LogEI counterpart (exceptions/warnings.py:67-99)."""
+    logei_name = {"qExpectedImprovement": "qLogExpectedImprovement",
+                  "qNoisyExpectedImprovement": "qLogNoisyExpectedImprovement"}.get(legacy_name)  # fmt: skip
+    if logei_name is not None:
+        warnings.warn(
+            f"{legacy_name} has known numerical issues that lead to suboptimal optimization performance. It is "
+            f"strongly recommended to simply replace\n\n\t {legacy_name} \t --> \t {logei_name} \n\n"
+            "instead, which fixes the issues and has the same API. See https://arxiv.org/abs/2310.20708 for details.",
+            NumericsWarning,
+            stacklevel=3,
+        )
+
+
+def prune_inferior_points(
+    model: Model,
+    X: Tensor,
+    objective=None,
+    posterior_transform=None,
+    constraints=None,
+    num_samples: int = 2048,
+    max_frac: float = 1.0,
+    sampler: Optional[MCSampler] = None,
+    marginalize_dim: Optional[int] = None,
+) -> Tensor:
+    """Keep the points of ``X`` (n x d) that are the best one in at least one joint posterior sample
+    (acquisition/utils.py:245-349).  The joint draw over the n points runs on the GPU (blocked Cholesky + GEMM)."""
+    for name, arg in (("objective", objective), ("posterior_transform", posterior_transform), ("constraints", constraints)):
+        if arg is not None:
+            raise UnsupportedError(f"`{name}` is not on the fused path yet (SURVEY.md section 8f): pass None")
+    if marginalize_dim is None and model._is_ensemble:
+        marginalize_dim = MCMC_DIM
+    if X.ndim > 2:
+        raise UnsupportedError("Batched inputs `X` are currently unsupported by prune_inferior_points")
+    if X.size(-2) == 0:
+        raise ValueError("X must have at least one point.")
+    if max_frac <= 0 or max_frac > 1.0:
+        raise ValueError(f"max_frac must take values in (0, 1], is {max_frac}")
+    max_points = math.ceil(max_frac * X.size(-2))
+    with torch.no_grad():
+        posterior = model.posterior(X=X)
+        if sampler is None:
+            sampler = get_sampler(posterior=posterior, sample_shape=torch.Size([num_samples]))
+        samples = sampler(posterior)
+    obj_vals = samples.squeeze(-1)  # IdentityMCObjective
+    if obj_vals.ndim > 2:
+        if obj_vals.ndim == 3 and marginalize_dim is not None:
+            if marginalize_dim < 0:  # MCMC_DIM counts from the end of the model's batch shape + (q, m)
+                marginalize_dim = 1 + (marginalize_dim % obj_vals.ndim)
+            obj_vals = obj_vals.mean(dim=marginalize_dim)
+        else:
+            raise UnsupportedError("Models with multiple batch dims are currently unsupported by prune_inferior_points.")
+    is_best = torch.argmax(obj_vals, dim=-1)
+    idcs, counts = torch.unique(is_best, return_counts=True)
+    if len(idcs) > max_points:  # (sic) the reference indexes by the sort order of the unique list here
+        counts, order_idcs = torch.sort(counts, descending=True)
+        idcs = order_idcs[:max_points]
+    return X[idcs]
 
 
 class _ShapeOnlyPosterior:
@@ -105,7 +166,90 @@ class _QLogNEIFunction(torch.autograd.Function):
         return g.sum(dim=0).to(ctx.in_dtype), None, None, None, None
 
 
-class qLogNoisyExpectedImprovement(AcquisitionFunction):
+class _FusedImprovementBase(AcquisitionFunction):
+    """Shared forward of the improvement-based MC acquisition functions (SampleReducingMCAcquisitionFunction.forward,
+    monte_carlo.py:253-289): subclasses provide ``self._nei`` (device state), ``self._set_sampler(q)`` (-> ``self._Zq``)
+    and the class attribute ``_log``."""
+
+    tau_relu, tau_max = TAU_RELU, TAU_MAX
+    _info_host, _info_event, _info_pending = None, None, False
+
+    def _check_fused_args(self, model, **unsupported) -> None:
+        if not isinstance(model, _FusedExactGP):
+            raise UnsupportedError(
+                f"the fused {type(self).__name__} needs a botorch_b200 exact GP model, got {type(model).__name__}; "
+                "no generic fallback"
+            )
+        for name, arg in unsupported.items():
+            if arg is not None:
+                raise UnsupportedError(f"`{name}` is not on the fused path yet (SURVEY.md section 8f): pass None")
+
+    # -- forward --------------------------------------------------------------------------------------
+    def forward(self, X: Tensor) -> Tensor:
+        """X: (b) x q x d  ->  (b) acquisition values (one per t-batch)."""
+        if X.dim() < 2:
+            raise ValueError(
+                f"{type(self).__name__} requires X to have at least 2 dimensions, but received X with only "
+                f"{X.dim()} dimensions."
+            )
+        if self.X_pending is not None:  # concatenate_pending_points
+            pend = self.X_pending.expand(*X.shape[:-2], *self.X_pending.shape[-2:]).to(X)
+            X = torch.cat([X, pend], dim=-2)
+        X = X if X.dim() > 2 else X.unsqueeze(0)  # add the t-batch dimension
+        batch_shape = X.shape[:-2]
+        q, d = X.shape[-2:]
+        Xf = X.reshape(-1, q, d)
+        if Xf.device != self._nei.device:
+            raise engine._lib.BoError(
+                f"X is on {Xf.device}; the acquisition function lives on {self._nei.device}. There is no CPU path."
+            )
+        self._set_sampler(q_in=q)
+        acq, info = _QLogNEIFunction.apply(Xf, self._nei, self._Zq, self.tau_relu, self.tau_max)  # taus unused when not _log
+        self._warn_on_failures(info)
+        if self.model._is_ensemble:  # t_batch_mode_transform: (log)mean over the hyperparameter samples
+            acq = torch.logsumexp(acq, dim=0) - math.log(acq.shape[0]) if self._log else acq.mean(dim=0)
+        else:
+            acq = acq[0]
+        return acq.reshape(batch_shape)
+
+    def _warn_on_failures(self, info: Tensor) -> None:
+        """Queue the failure flags of this call; report the flags of the previous one.
+
+        Reading ``info`` right away would stall the host on the forward kernels before it can enqueue the loss and the
+        backward (one idle gap per L-BFGS-B evaluation).  The (min, max) pair goes to pinned host memory behind an
+        event instead and is examined at the next call -- by then the caller has read the loss, so the event is
+        long complete -- or by ``check_numerics()``, which ``optimize_acqf`` calls before returning.
+        """
+        self.check_numerics()
+        if self._info_host is None:
+            self._info_host = torch.empty(2, dtype=torch.int32).pin_memory()
+            self._info_event = torch.cuda.Event()
+        lo, hi = torch.aminmax(info)
+        self._info_host.copy_(torch.stack([lo, hi]).to(torch.int32), non_blocking=True)
+        self._info_event.record()
+        self._info_pending = True
+
+    def check_numerics(self) -> None:
+        """Emit the warnings of the most recent evaluation (waits for it if it is still running)."""
+        if not self._info_pending:
+            return
+        self._info_event.synchronize()
+        self._info_pending = False
+        lo, hi = int(self._info_host[0]), int(self._info_host[1])
+        if hi > 0:
+            warnings.warn(
+                f"A not p.d., added jitter of {1e-8 * 10 ** (hi - 1):.1e} to the diagonal", NumericalWarning, stacklevel=3
+            )
+        if lo < 0:
+            warnings.warn(
+                "Low-rank cholesky updates failed due NaNs or due to an ill-conditioned covariance matrix. "
+                "The affected t-batches were evaluated without their q x q root.",
+                BotorchWarning,
+                stacklevel=3,
+            )
+
+
+class qLogNoisyExpectedImprovement(_FusedImprovementBase):
     """MC batch log noisy expected improvement, evaluated by one fused GPU pipeline per call.
 
     qLogNEI(X) ~ log E[ max(max_j f(x_j) - max f(X_baseline), 0) ] with the smooth fat-tailed approximations of
@@ -139,13 +283,11 @@ class qLogNoisyExpectedImprovement(AcquisitionFunction):
                 f"the fused qLogNEI needs a botorch_b200 exact GP model, got {type(model).__name__}; no generic fallback"
             )
         for name, arg in (("objective", objective), ("posterior_transform", posterior_transform),
-                          ("constraints", constraints), ("marginalize_dim", marginalize_dim)):  # fmt: skip
+                          ("constraints", constraints)):  # fmt: skip
             if arg is not None:
                 raise UnsupportedError(f"`{name}` is not on the fused path yet (SURVEY.md section 8f): pass None")
         if not fat:
             raise UnsupportedError("fat=False (plain softplus / logsumexp smoothing) is not on the fused path")
-        if prune_baseline:
-            raise UnsupportedError("prune_baseline=True is not on the fused path: prune X_baseline before constructing")
         if X_baseline.dim() != 2:
             raise UnsupportedError("X_baseline must be r x d (one baseline set shared by all t-batches)")
         self.tau_relu, self.tau_max = float(tau_relu), float(tau_max)
@@ -155,6 +297,8 @@ class qLogNoisyExpectedImprovement(AcquisitionFunction):
         self._cache_root = bool(cache_root)
         self.sample_shape = torch.Size([DEFAULT_MC_SAMPLES]) if sampler is None else sampler.sample_shape
         self.set_X_pending(X_pending)
+        if prune_baseline:  # logei.py:377-385
+            X_baseline = prune_inferior_points(model=model, X=X_baseline, marginalize_dim=marginalize_dim)
         self._init_baseline(X_baseline, sampler, _factor_setup)
 
     # -- one-time setup (logei.py:364-420) ------------------------------------------------------------
@@ -173,7 +317,8 @@ class qLogNoisyExpectedImprovement(AcquisitionFunction):
         S = self.sample_shape[0]
         Z_b = self.sampler.base_samples.reshape(S, n_b).to(device=gp.device, dtype=torch.float64).contiguous()
         # setup=False: allocate only; botorch_b200.distributed broadcasts the factors from the rank that computed them
-        self._nei = engine.NEIState(gp, self.X_baseline.to(gp.device), Z_b, setup=setup)
+        self._nei = engine.NEIState(gp, self.X_baseline.to(gp.device), Z_b, setup=setup,
+                                    reduction=engine.REDUCE_LOG if self._log else engine.REDUCE_PLAIN)
         self.q_in = -1
         self._Zq: Optional[Tensor] = None
         self.register_buffer("_baseline_best_f", None)
@@ -219,45 +364,97 @@ class qLogNoisyExpectedImprovement(AcquisitionFunction):
         self._Zq = Z[:, n_b:].to(device=gp.device, dtype=torch.float64).contiguous()
         self.q_in = q_in
 
-    # -- forward --------------------------------------------------------------------------------------
-    def forward(self, X: Tensor) -> Tensor:
-        """X: (b) x q x d  ->  (b) acquisition values (one per t-batch)."""
-        if X.dim() < 2:
-            raise ValueError(
-                f"{type(self).__name__} requires X to have at least 2 dimensions, but received X with only "
-                f"{X.dim()} dimensions."
-            )
-        if self.X_pending is not None:  # concatenate_pending_points
-            pend = self.X_pending.expand(*X.shape[:-2], *self.X_pending.shape[-2:]).to(X)
-            X = torch.cat([X, pend], dim=-2)
-        X = X if X.dim() > 2 else X.unsqueeze(0)  # add the t-batch dimension
-        batch_shape = X.shape[:-2]
-        q, d = X.shape[-2:]
-        Xf = X.reshape(-1, q, d)
-        if Xf.device != self._nei.device:
-            raise engine._lib.BoError(
-                f"X is on {Xf.device}; the acquisition function lives on {self._nei.device}. There is no CPU path."
-            )
-        self._set_sampler(q_in=q)
-        acq, info = _QLogNEIFunction.apply(Xf, self._nei, self._Zq, self.tau_relu, self.tau_max)
-        self._warn_on_failures(info)
-        if self.model._is_ensemble:  # t_batch_mode_transform: logmeanexp over the hyperparameter samples
-            acq = torch.logsumexp(acq, dim=0) - math.log(acq.shape[0])
-        else:
-            acq = acq[0]
-        return acq.reshape(batch_shape)
 
-    def _warn_on_failures(self, info: Tensor) -> None:
-        lo, hi = torch.aminmax(info)
-        lo, hi = int(lo), int(hi)
-        if hi > 0:
-            warnings.warn(
-                f"A not p.d., added jitter of {1e-8 * 10 ** (hi - 1):.1e} to the diagonal", NumericalWarning, stacklevel=3
-            )
-        if lo < 0:
-            warnings.warn(
-                "Low-rank cholesky updates failed due NaNs or due to an ill-conditioned covariance matrix. "
-                "The affected t-batches were evaluated without their q x q root.",
-                BotorchWarning,
-                stacklevel=3,
-            )
+class qNoisyExpectedImprovement(qLogNoisyExpectedImprovement):
+    """MC batch noisy expected improvement, qNEI(X) = E[max(max_j f(x_j) - max f(X_baseline), 0)]
+    (acquisition/monte_carlo.py:417-620): the sample path of qLogNEI with ``clamp_min(0)``, ``amax`` over q and the
+    plain mean over samples.  ``prune_baseline`` defaults to True as in the reference."""
+
+    _log = False
+
+    def __init__(
+        self,
+        model: Model,
+        X_baseline: Tensor,
+        sampler: Optional[MCSampler] = None,
+        objective=None,
+        posterior_transform=None,
+        X_pending: Optional[Tensor] = None,
+        prune_baseline: bool = True,
+        cache_root: bool = True,
+        constraints=None,
+        eta=1e-3,
+        marginalize_dim: Optional[int] = None,
+        *,
+        _factor_setup: bool = True,
+    ) -> None:
+        legacy_ei_numerics_warning(type(self).__name__)
+        super().__init__(model, X_baseline, sampler=sampler, objective=objective, posterior_transform=posterior_transform,
+                         X_pending=X_pending, constraints=constraints, eta=eta, prune_baseline=prune_baseline,
+                         cache_root=cache_root, marginalize_dim=marginalize_dim, _factor_setup=_factor_setup)  # fmt: skip
+
+
+class qLogExpectedImprovement(_FusedImprovementBase):
+    """MC batch log expected improvement over a fixed incumbent ``best_f`` (acquisition/logei.py:138-234):
+    joint posterior over the q points, log_fatplus(f - best_f), fatmax over q, logmeanexp over samples."""
+
+    _log = True
+
+    def __init__(
+        self,
+        model: Model,
+        best_f,
+        sampler: Optional[MCSampler] = None,
+        objective=None,
+        posterior_transform=None,
+        X_pending: Optional[Tensor] = None,
+        constraints=None,
+        eta=1e-3,
+        fat: bool = True,
+        tau_max: float = TAU_MAX,
+        tau_relu: float = TAU_RELU,
+    ) -> None:
+        AcquisitionFunction.__init__(self, model=model)
+        self._check_fused_args(model, objective=objective, posterior_transform=posterior_transform, constraints=constraints)
+        if not fat:
+            raise UnsupportedError("fat=False (plain softplus / logsumexp smoothing) is not on the fused path")
+        self.tau_relu, self.tau_max = float(tau_relu), float(tau_max)
+        self._init_fixed_incumbent(best_f, sampler, X_pending)
+
+    def _init_fixed_incumbent(self, best_f, sampler: Optional[MCSampler], X_pending: Optional[Tensor]) -> None:
+        gp: engine.GPState = self.model.gp_state
+        self.register_buffer("best_f", torch.as_tensor(best_f, dtype=torch.float64))
+        self.sample_shape = torch.Size([DEFAULT_MC_SAMPLES]) if sampler is None else sampler.sample_shape
+        if len(self.sample_shape) != 1:
+            raise UnsupportedError("the fused path takes a one-dimensional sample_shape")
+        self.sampler = sampler
+        self.set_X_pending(X_pending)
+        self._nei = engine.EIState(gp, self.best_f.to(gp.device), self.sample_shape[0],
+                                   reduction=engine.REDUCE_LOG if self._log else engine.REDUCE_PLAIN)  # fmt: skip
+        self.q_in, self._Zq = -1, None
+
+    def _set_sampler(self, q_in: int) -> None:
+        """Base samples S x 1 x q of the joint draw, shared by all t-batches and models (sampling/base.py:78-125)."""
+        if self.q_in == q_in and self._Zq is not None:
+            return
+        gp = self._nei.gp
+        post = _ShapeOnlyPosterior(torch.Size([1]) + self.model.batch_shape, q_in, gp.device, torch.float64)
+        if self.sampler is None:  # MCAcquisitionFunction.get_posterior_samples, monte_carlo.py:116-125
+            self.sampler = get_sampler(post, sample_shape=self.sample_shape)
+        self.sampler._construct_base_samples(post)
+        S = self.sample_shape[0]
+        self._Zq = self.sampler.base_samples.reshape(S, q_in).to(device=gp.device, dtype=torch.float64).contiguous()
+        self.q_in = q_in
+
+
+class qExpectedImprovement(qLogExpectedImprovement):
+    """MC batch expected improvement, qEI(X) = E[max(max_j f(x_j) - best_f, 0)] (acquisition/monte_carlo.py:333-414)."""
+
+    _log = False
+
+    def __init__(self, model: Model, best_f, sampler: Optional[MCSampler] = None, objective=None,
+                 posterior_transform=None, X_pending: Optional[Tensor] = None, constraints=None, eta=1e-3) -> None:  # fmt: skip
+        legacy_ei_numerics_warning(type(self).__name__)
+        AcquisitionFunction.__init__(self, model=model)
+        self._check_fused_args(model, objective=objective, posterior_transform=posterior_transform, constraints=constraints)
+        self._init_fixed_incumbent(best_f, sampler, X_pending)

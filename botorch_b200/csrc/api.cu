@@ -314,6 +314,51 @@ int bo_nei_setup(bo_ctx* ctx, const bo_gp* gp, const bo_nei* nei, void* work, si
     return BO_OK;
 }
 
+long bo_nei_dense_rows(const bo_nei* nei) { return bo_pad8((nei->no_baseline ? 0 : (long)nei->S) + 1); }
+
+static size_t ei_setup_layout(const bo_gp* gp, void* work, size_t cap, double** scratch, bool* ok) {
+    Bump b(work, cap);
+    *scratch = b.doubles(bo_linalg_scratch_doubles(gp->n, gp->M));
+    *ok = b.ok;
+    return b.off;
+}
+
+size_t bo_ei_setup_workspace_bytes(const bo_gp* gp, const bo_nei* nei) {
+    (void)nei;
+    double* a;
+    bool ok;
+    return ei_setup_layout(gp, nullptr, 0, &a, &ok);
+}
+
+int bo_ei_setup(bo_ctx* ctx, const bo_gp* gp, const bo_nei* nei, void* work, size_t work_bytes, int32_t* info,
+                void* stream) {
+    if (!ctx || !valid_gp(gp) || !nei || !nei->no_baseline || nei->S <= 0 || !nei->fwd_cat || !nei->bwd_cat ||
+        !nei->best_f || !work || !info)
+        return BO_ERR_INVALID;
+    cudaStream_t st = (cudaStream_t)stream;
+    const long n = gp->n, M = gp->M, np = bo_pad8(n), n1p = bo_pad8(n + 1);
+    const long S1p = bo_nei_dense_rows(nei), ldk = S1p + np, rowsF = S1p + n;
+    const double ys2 = gp->y_std * gp->y_std;
+    double* scratch;
+    bool ok;
+    ei_setup_layout(gp, work, work_bytes, &scratch, &ok);
+    if (!ok) return BO_ERR_WORKSPACE;
+    BO_CUDA_TRY(cudaMemsetAsync(info, 0, sizeof(int32_t) * M, st));
+    double* lw = nei->bwd_cat + S1p;
+    BO_TRY(bo_fill(nei->bwd_cat, M * n * ldk, 0.0, st));
+    BO_TRY(bo_fill(nei->fwd_cat, M * rowsF * np, 0.0, st));
+    // W = ys^2 (K + s2 I)^-1 = ys^2 L^-T L^-1 (lower block-triangle), factored in place inside the backward operand
+    BO_TRY(gemm((int)n, (int)n, (int)n, (int)M, ys2, gp->linv_aug_t, n1p, n * n1p, gp->linv_aug, np, (n + 1) * np, 0.0,
+                nullptr, 0, 0, lw, ldk, n * ldk, BO_TRI_A_UPPER, 1, st));
+    BO_TRY(bo_potrf_blocked(lw, ldk, n * ldk, (int)n, (int)M, nullptr, np, n * np, scratch, info, st));
+    BO_TRY(bo_transpose(lw, ldk, n * ldk, nei->fwd_cat + S1p * np, np, rowsF * np, (int)n, (int)n, (int)M, st));
+    // row 0: alpha, and its transpose as column 0 of the backward operand
+    BO_TRY(bo_copy2d(gp->linv_aug + n * np, np, (n + 1) * np, nei->fwd_cat, np, rowsF * np, 1, (int)n, (int)M, st));
+    BO_TRY(bo_transpose(nei->fwd_cat, np, rowsF * np, nei->bwd_cat, ldk, n * ldk, 1, (int)n, (int)M, st));
+    BO_CUDA_TRY(cudaGetLastError());
+    return BO_OK;
+}
+
 }  // extern "C"
 
 // ------------------------------------------------------------------------------------------------
@@ -336,8 +381,8 @@ QWork qlayout(const bo_gp* gp, const bo_nei* nei, int B, int q, int with_grad, v
     const long n = gp->n, nb = nei->n_b, M = gp->M, Kp = bo_kp(gp->d);
     const long N = (long)B * q;
     w.ldn = bo_pad8(N);
-    w.qpath = nei->baseline_is_train && nei->fwd_cat && nei->bwd_cat && gp->xt_aug;
-    const long S1p = bo_pad8((long)nei->S + 1);
+    w.qpath = (nei->baseline_is_train || nei->no_baseline) && nei->fwd_cat && nei->bwd_cat && gp->xt_aug;
+    const long S1p = bo_nei_dense_rows(nei);
     // rows of every [rows x N] region: the stacked forward output [samples; pad; U] on the shared-baseline path
     w.R = w.qpath ? S1p + n : (n > nb ? n : nb) + 1;
     w.regionStride = w.R * w.ldn;
@@ -353,6 +398,8 @@ QWork qlayout(const bo_gp* gp, const bo_nei* nei, int B, int q, int with_grad, v
         w.W3 = b.doubles(M * w.regionStride);
         w.F = b.doubles(M * (long)(nei->S + 1) * w.ldn);
         w.W6 = nei->baseline_is_train ? nullptr : b.doubles(M * w.regionStride);
+    } else if (nei->no_baseline) {
+        w.F = b.doubles(M * (long)nei->S * w.ldn);  // the samples (no baseline rows in the stacked output)
     }
     if (with_grad) {
         w.Sbar = b.doubles(M * (long)B * q * q);
@@ -381,6 +428,7 @@ BoCandArgs cand_args(const bo_gp* gp, const bo_nei* nei, int B, int q, const dou
     a.best_f = nei ? nei->best_f : nullptr;
     a.Sp = nei ? bo_pad8(nei->S) : 0;
     a.tau_relu = tau_relu; a.tau_max = tau_max;
+    a.reduction = nei ? nei->reduction : BO_REDUCE_LOG;
     a.ldn = w.ldn;
     a.V = w.W1; a.strideV = w.regionStride;
     a.BL = w.W3; a.strideBL = w.regionStride;
@@ -407,6 +455,7 @@ int bo_qlognei_fwd(bo_ctx* ctx, const bo_gp* gp, const bo_nei* nei, int B, int q
     cudaStream_t st = (cudaStream_t)stream;
     const QWork w = qlayout(gp, nei, B, q, with_grad, work, work_bytes);
     if (!w.ok) return BO_ERR_WORKSPACE;
+    if (nei->no_baseline && !w.qpath) return BO_ERR_INVALID;
     const long n = gp->n, nb = nei->n_b, M = gp->M, np = bo_pad8(n), nbp = bo_pad8(nb), Kp = bo_kp(gp->d);
     const long S = nei->S, N = (long)B * q;
     const double ys2 = gp->y_std * gp->y_std;
@@ -423,7 +472,7 @@ int bo_qlognei_fwd(bo_ctx* ctx, const bo_gp* gp, const bo_nei* nei, int B, int q
     if (w.qpath) {
         // 2r. [Z_b Q; alpha^T; 0; L_W^T] K(X_tr, X) in ONE launch: rows 0..S-1 baseline part of every sample, row S the mean,
         //     rows S1p.. U = L_W^T K(X_tr, X) (upper-triangular part of the operand: k-range skipped per row tile)
-        const long S1p = bo_pad8(S + 1);
+        const long S1p = bo_nei_dense_rows(nei), Sd = nei->no_baseline ? 0 : S;  // Sd sample rows, then the mean row
         BoGemm g{};
         g.A = nei->fwd_cat; g.lda = np; g.strideA = (S1p + n) * np;
         g.B = w.W0; g.ldb = w.ldn; g.strideB = w.regionStride;
@@ -433,9 +482,10 @@ int bo_qlognei_fwd(bo_ctx* ctx, const bo_gp* gp, const bo_nei* nei, int B, int q
         BO_TRY(bo_gemm_launch(g, st));
         BoCandArgs a = cand_args(gp, nei, B, q, X, Z_q, tau_relu, tau_max, w);
         a.V = nullptr;
-        a.F = w.W1; a.strideF = w.regionStride;
+        if (nei->no_baseline) { a.F = w.F; a.strideF = S * w.ldn; a.f_zero = 1; }
+        else { a.F = w.W1; a.strideF = w.regionStride; }
         a.BL = w.W1 + S1p * w.ldn; a.strideBL = w.regionStride; a.n_b = (int)n;
-        a.mu_row = w.W1 + S * w.ldn; a.strideMu = w.regionStride;
+        a.mu_row = w.W1 + Sd * w.ldn; a.strideMu = w.regionStride;
         a.acq = acq;
         a.info = w.info;
         BO_TRY(bo_cand_fwd(a, st));
@@ -471,6 +521,7 @@ int bo_qlognei_bwd(bo_ctx* ctx, const bo_gp* gp, const bo_nei* nei, int B, int q
     cudaStream_t st = (cudaStream_t)stream;
     const QWork w = qlayout(gp, nei, B, q, 1, work, work_bytes);
     if (!w.ok) return BO_ERR_WORKSPACE;
+    if (nei->no_baseline && !w.qpath) return BO_ERR_INVALID;
     const long n = gp->n, nb = nei->n_b, M = gp->M, n1p = bo_pad8(n + 1), nbp = bo_pad8(nb), Sp = bo_pad8(nei->S);
     const long S = nei->S, N = (long)B * q;
     const double ys2 = gp->y_std * gp->y_std;
@@ -482,9 +533,10 @@ int bo_qlognei_bwd(bo_ctx* ctx, const bo_gp* gp, const bo_nei* nei, int B, int q
     a.Sbar = w.Sbar;
     a.gradX = grad_X;
     if (w.qpath) {
-        const long np = bo_pad8(n), S1p = bo_pad8(S + 1), ldk = S1p + np;
-        a.F = w.W1; a.strideF = w.regionStride;  // samples live in rows 0..S-1 of the stacked forward output
-        a.Vbar_mu = w.W1 + S * w.ldn;             // row S <- y_std * mubar: rows 0..S become [dF; y_std mubar]
+        const long np = bo_pad8(n), S1p = bo_nei_dense_rows(nei), ldk = S1p + np, Sd = nei->no_baseline ? 0 : S;
+        if (nei->no_baseline) { a.F = w.F; a.strideF = S * w.ldn; }  // samples / dF in their own scratch
+        else { a.F = w.W1; a.strideF = w.regionStride; }  // samples live in rows 0..S-1 of the stacked forward output
+        a.Vbar_mu = w.W1 + Sd * w.ldn;            // row Sd <- y_std * mubar: rows 0..Sd become [dF; y_std mubar]
         a.strideVbar = w.regionStride;
         BO_TRY(bo_cand_bwd(a, st));
         // 2r. Ubar = -2 U Sbar, in place on rows S1p.. of the same region

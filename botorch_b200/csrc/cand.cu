@@ -400,6 +400,7 @@ __global__ void __launch_bounds__(CAND_THREADS, (QT <= 4 ? 6 : (QT <= 8 ? 4 : 1)
 
     int bad = 0;
     double local_max = -INFINITY;
+    const bool plain = (a.reduction == BO_REDUCE_PLAIN);
     for (int s = tid; s < a.S; s += T) {
         double li[QT], zq[QT];
         const double bf = a.best_f[(long)z * a.Sp + s];
@@ -409,32 +410,48 @@ __global__ void __launch_bounds__(CAND_THREADS, (QT <= 4 ? 6 : (QT <= 8 ? 4 : 1)
         for (int j = 0; j < QT; j++) {
             li[j] = 0.0;
             if (j < q) {
-                double v = F[(long)s * a.ldn + c0 + j] + c.mu[j];
+                double v = (a.f_zero ? 0.0 : F[(long)s * a.ldn + c0 + j]) + c.mu[j];
 #pragma unroll
                 for (int k = 0; k < QT; k++)
                     if (k <= j) v += c.Lq[j * q + k] * zq[k];
                 F[(long)s * a.ldn + c0 + j] = v;
                 if (!isfinite(v)) bad = 1;
-                li[j] = log_fatplus(v - bf, a.tau_relu);
+                li[j] = plain ? fmax(v - bf, 0.0) : log_fatplus(v - bf, a.tau_relu);
             }
         }
-        const double m = fatmax_q<QT>(li, q, a.tau_max);
+        double m;
+        if (plain) {  // (obj - best_f).clamp_min(0).amax(q)   (monte_carlo.py:410,536-547)
+            m = li[0];
+#pragma unroll
+            for (int j = 1; j < QT; j++)
+                if (j < q) m = fmax(m, li[j]);
+        } else {
+            m = fatmax_q<QT>(li, q, a.tau_max);
+        }
         c.fm[s] = m;
         local_max = fmax(local_max, m);
     }
     const int anybad = __syncthreads_or(bad);
-    const double Mx = block_reduce_max(local_max, red);
-    double lse;
-    if (isinf(Mx)) {
-        lse = Mx;
-    } else {
+    double lse, val;
+    if (plain) {  // mean over the MC samples; lse keeps the plain sum
         double part = 0.0;
-        for (int s = tid; s < a.S; s += T) part += exp(c.fm[s] - Mx);
-        lse = Mx + log(block_reduce_sum(part, red));
+        for (int s = tid; s < a.S; s += T) part += c.fm[s];
+        lse = block_reduce_sum(part, red);
+        val = lse / (double)a.S;
+    } else {
+        const double Mx = block_reduce_max(local_max, red);
+        if (isinf(Mx)) {
+            lse = Mx;
+        } else {
+            double part = 0.0;
+            for (int s = tid; s < a.S; s += T) part += exp(c.fm[s] - Mx);
+            lse = Mx + log(block_reduce_sum(part, red));
+        }
+        val = lse - log((double)a.S);
     }
     if (tid == 0) {
         const long o = (long)z * a.B + b;
-        a.acq[o] = lse - log((double)a.S);
+        a.acq[o] = val;
         a.lse[o] = lse;
         a.info[o] = anybad ? -1 : s_info;
     }
@@ -470,6 +487,7 @@ __global__ void __launch_bounds__(CAND_THREADS, (QT <= 4 ? 6 : (QT <= 8 ? 3 : 1)
     constexpr int PT = QT * (QT + 1) / 2;
     double* red = mubar + q;  // (T/32) x (QT + PT)
     double am[QT], al[PT];
+    const bool plain = (a.reduction == BO_REDUCE_PLAIN);
 #pragma unroll
     for (int j = 0; j < QT; j++) am[j] = 0.0;
 #pragma unroll
@@ -482,21 +500,38 @@ __global__ void __launch_bounds__(CAND_THREADS, (QT <= 4 ? 6 : (QT <= 8 ? 3 : 1)
             f[j] = 0.0; li[j] = 0.0; zq[j] = 0.0;
             if (j < q) {
                 f[j] = F[(long)s * a.ldn + c0 + j];
-                li[j] = log_fatplus(f[j] - bf, a.tau_relu);
+                li[j] = plain ? fmax(f[j] - bf, 0.0) : log_fatplus(f[j] - bf, a.tau_relu);
                 zq[j] = a.Zq[(long)s * q + j];
             }
         }
-        const double m = fatmax_q<QT>(li, q, a.tau_max);
-        // logmeanexp over samples: softmax weight; +-inf maximum -> unit gradient on the infinite entries
-        const double w = isinf(lse) ? ((m == lse) ? 1.0 : 0.0) : exp(m - lse);
-        fatmax_q_grad<QT>(li, q, a.tau_max, gm);
+        double m, w;
+        int ties = 0;
+        if (plain) {  // mean over samples; amax spreads its gradient evenly over tied maxima; clamp_min(0) passes x >= 0
+            m = li[0];
+#pragma unroll
+            for (int j = 1; j < QT; j++)
+                if (j < q) m = fmax(m, li[j]);
+#pragma unroll
+            for (int j = 0; j < QT; j++)
+                if (j < q && li[j] == m) ties++;
+            w = 1.0 / (double)a.S;
+        } else {
+            m = fatmax_q<QT>(li, q, a.tau_max);
+            // logmeanexp over samples: softmax weight; +-inf maximum -> unit gradient on the infinite entries
+            w = isinf(lse) ? ((m == lse) ? 1.0 : 0.0) : exp(m - lse);
+            fatmax_q_grad<QT>(li, q, a.tau_max, gm);
+        }
         int p = 0;
 #pragma unroll
         for (int j = 0; j < QT; j++) {
             double df = 0.0;
             if (j < q) {
-                const double dli = isinf(li[j]) ? 0.0 : dlog_fatplus(f[j] - bf, a.tau_relu);
-                df = g * w * gm[j] * dli;
+                if (plain) {
+                    df = (li[j] == m && f[j] - bf >= 0.0) ? g * w / (double)ties : 0.0;
+                } else {
+                    const double dli = isinf(li[j]) ? 0.0 : dlog_fatplus(f[j] - bf, a.tau_relu);
+                    df = g * w * gm[j] * dli;
+                }
                 F[(long)s * a.ldn + c0 + j] = df;
             }
             am[j] += df;

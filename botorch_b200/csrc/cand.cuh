@@ -34,6 +34,8 @@ struct BoCandArgs {
     const double* BL; long strideBL;   // [n_b x ldn]    bl_chol^T  (combined-root path: U = L_W^T K(X_tr, X), n rows, V null)
     const double* mu_row; long strideMu; // optional [ldn] row holding alpha . K(X_tr, x) (else row n of V)
     double* F;        long strideF;    // [S x ldn]      in: Z_b BL ; out: samples f (fwd) / df (bwd)
+    int f_zero;                        // 1: no baseline part (qEI / qLogEI): F is write-only scratch for the samples
+    int reduction;                     // BO_REDUCE_LOG: log_fatplus / fatmax / logmeanexp; BO_REDUCE_PLAIN: relu / amax / mean
     double* Lq;                        // [M][B][q*q]    br_chol
     double* lse;                       // [M][B]         logsumexp over MC samples
     double* acq;                       // [M][B]

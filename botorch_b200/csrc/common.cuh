@@ -15,6 +15,8 @@
 
 #define BO_KERNEL_RBF 0
 #define BO_KERNEL_MATERN52 1
+#define BO_REDUCE_LOG 0    // log_fatplus / fatmax / logmeanexp  (qLogNEI, qLogEI)
+#define BO_REDUCE_PLAIN 1  // clamp_min(0) / amax / mean           (qNEI, qEI)
 
 #define BO_CUDA_TRY(expr)                                                                    \
     do {                                                                                     \

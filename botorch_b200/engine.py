@@ -18,6 +18,8 @@ from . import _lib
 from ._lib import BoGP, BoNEI, check, kp, pad8, ptr
 from .exceptions import NanError, NotPSDError, NumericalWarning
 
+REDUCE_LOG, REDUCE_PLAIN = 0, 1  # BO_REDUCE_* of include/botorch_b200.h
+
 KERNEL_IDS = {"rbf": 0, "matern52": 1}
 CHOLESKY_MAX_TRIES = 6  # botorch/__init__.py:47
 CHOLESKY_JITTER = 1e-8  # linear_operator settings.cholesky_jitter for float64
@@ -172,7 +174,8 @@ class GPState:
 class NEIState:
     """Baseline factors of qLogNEI (V_b, L_b and its inverse, base samples, best_f) and the fused fwd/bwd."""
 
-    def __init__(self, gp: GPState, X_baseline: Tensor, Z_b: Tensor, setup: bool = True) -> None:
+    def __init__(self, gp: GPState, X_baseline: Tensor, Z_b: Tensor, setup: bool = True,
+                 reduction: int = REDUCE_LOG) -> None:  # fmt: skip
         dev = gp.device
         self.gp = gp
         self.device = dev
@@ -207,7 +210,7 @@ class NEIState:
             aug_b=ptr(self.aug_b), vb=ptr(self.vb), vb_t=ptr(self.vb_t), lb=ptr(self.lb), lb_inv=ptr(self.lb_inv),
             lb_inv_t=ptr(self.lb_inv_t), zb_pad=ptr(self.zb_pad), zb_t=ptr(self.zb_t), mean_b=ptr(self.mean_b),
             best_f=ptr(self.best_f_pad), qmat=ptr(self.qmat), qmat_t=ptr(self.qmat_t),
-            fwd_cat=ptr(self.fwd_cat), bwd_cat=ptr(self.bwd_cat),
+            fwd_cat=ptr(self.fwd_cat), bwd_cat=ptr(self.bwd_cat), reduction=int(reduction), no_baseline=0,
         )  # fmt: skip
         self.jitter = torch.zeros(M, dtype=torch.float64, device=dev)
         if not setup:
@@ -278,6 +281,43 @@ class NEIState:
                                         tau_relu, tau_max, ptr(grad_acq.contiguous()), ptr(grad_X), work.data_ptr(),
                                         work.numel(), _lib.stream_ptr(self.device)))  # fmt: skip
         return grad_X
+
+
+class EIState(NEIState):
+    """qEI / qLogEI: no baseline set, a fixed incumbent ``best_f`` ([M] or scalar) instead of per-sample baseline maxima.
+
+    Same forward / backward entry points; the stacked operands hold only the mean row and the root of
+    ys^2 (K + s2 I)^-1 (``bo_ei_setup``), so the q x q posterior covariance is ys^2 k(X,X) - U^T U.
+    """
+
+    def __init__(self, gp: GPState, best_f: Tensor, S: int, setup: bool = True, reduction: int = REDUCE_LOG) -> None:
+        dev = gp.device
+        self.gp, self.device = gp, dev
+        self.S, self.n_b, self.is_train = int(S), 0, False
+        n, M = gp.n, gp.M
+        self.Sp = pad8(self.S)
+        z = lambda *s: torch.zeros(*s, dtype=torch.float64, device=dev)
+        bf = torch.as_tensor(best_f, dtype=torch.float64, device=dev).reshape(-1)
+        if bf.numel() not in (1, M):
+            raise ValueError(f"best_f must be a scalar or one value per model ({M}), got {tuple(bf.shape)}")
+        self.best_f_pad = bf.expand(M).reshape(M, 1).expand(M, self.Sp).contiguous()
+        self.fwd_cat = z(M, 8 + n, gp.np_)
+        self.bwd_cat = z(M, n, 8 + gp.np_)
+        self.info = torch.zeros(M, dtype=torch.int32, device=dev)
+        self.c = BoNEI(n_b=0, S=self.S, baseline_is_train=0, best_f=ptr(self.best_f_pad), fwd_cat=ptr(self.fwd_cat),
+                       bwd_cat=ptr(self.bwd_cat), reduction=int(reduction), no_baseline=1)  # fmt: skip
+        if not setup:
+            return
+        lib = _lib.lib()
+        work = _lib.workspace(lib.bo_ei_setup_workspace_bytes(C.byref(gp.c), C.byref(self.c)), dev)
+        check(lib.bo_ei_setup(gp.ctx, C.byref(gp.c), C.byref(self.c), work.data_ptr(), work.numel(), ptr(self.info),
+                              _lib.stream_ptr(dev)))  # fmt: skip
+        bad = int(self.info.max())
+        if bad != 0:
+            raise NotPSDError(f"root of the train precision matrix: pivot {bad} not positive")
+
+    def factor_buffers(self):
+        return [self.best_f_pad, self.fwd_cat, self.bwd_cat]
 
 
 class GraphedEval:

@@ -21,6 +21,7 @@ try:  # pragma: no cover - botorch is not installed on the build image
         BadInitialCandidatesWarning,
         BotorchWarning,
         InputDataWarning,
+        NumericsWarning,
         OptimizationWarning,
         SamplingWarning,
     )
@@ -60,6 +61,9 @@ except Exception:
         pass
 
     class SamplingWarning(BotorchWarning):
+        pass
+
+    class NumericsWarning(BotorchWarning):
         pass
 
 

@@ -138,7 +138,15 @@ def evaluate_raw_samples(acq_function, X_rnd: Tensor, device, batch_limit: Optio
     with torch.no_grad():
         step = X_rnd.shape[0] if batch_limit is None else batch_limit
         out = [acq_function(X_rnd[i : i + step].to(device=device)).cpu() for i in range(0, X_rnd.shape[0], step)]
+    _flush_warnings(acq_function)
     return torch.cat(out)
+
+
+def _flush_warnings(acq_function) -> None:
+    """Numerical-failure flags are read back one call late (acquisition._warn_on_failures); drain the last one."""
+    check = getattr(acq_function, "check_numerics", None)
+    if check is not None:
+        check()
 
 
 # -------------------------------------------------------------------------------------------------
@@ -249,6 +257,7 @@ def gen_candidates_scipy(
     clamped = columnwise_clamp(candidates, lower_bounds, upper_bounds, raise_on_violation=True)
     with torch.no_grad():
         batch_acquisition = acquisition_function(clamped)
+    _flush_warnings(acquisition_function)
     return clamped, batch_acquisition
 
 

@@ -33,6 +33,10 @@ extern "C" {
 #define BO_KERNEL_RBF 0      /* gpytorch RBFKernel (ARD), models/utils/gpytorch_modules.py:100-127 */
 #define BO_KERNEL_MATERN52 1 /* gpytorch MaternKernel(nu=2.5, ARD), models/fully_bayesian.py:81-85,275-282 */
 
+/* sample / q reductions of SampleReducingMCAcquisitionFunction (acquisition/monte_carlo.py:180-252) */
+#define BO_REDUCE_LOG 0   /* log_fatplus, fatmax, logmeanexp: qLogNEI, qLogEI (acquisition/logei.py:73-135) */
+#define BO_REDUCE_PLAIN 1 /* clamp_min(0), amax, mean: qNEI, qEI (acquisition/monte_carlo.py:333-414,417-560) */
+
 /* info codes written per (model, t-batch element) by bo_qlognei_fwd */
 #define BO_INFO_OK 0
 #define BO_INFO_NAN (-1)      /* NaN/Inf in samples: low_rank.py:163-172 NanError */
@@ -91,6 +95,12 @@ typedef struct bo_nei {
     double* fwd_cat;           /* [M][(S1p+n) x np]   rows 0..S-1: Z_b Q (baseline part of the samples = (Z_b Q) K(X_tr,X)); row S: alpha;
                                 *                      rows S+1..S1p-1: 0; rows S1p+i: row i of L_W^T  -> one forward GEMM */
     double* bwd_cat;           /* [M][n x (S1p+np)]   [ fwd rows 0..S1p-1 transposed | L_W ]             -> one backward GEMM */
+    /* the other members of the family on the same kernels */
+    int32_t reduction;         /* BO_REDUCE_LOG (qLogNEI, qLogEI) or BO_REDUCE_PLAIN (qNEI, qEI) */
+    int32_t no_baseline;       /* 1: qEI / qLogEI (acquisition/logei.py:138-234, monte_carlo.py:333-414): posterior over the q
+                                *    new points only, best_f [M][Sp] supplied by the caller; n_b = 0, only S, best_f, fwd_cat,
+                                *    bwd_cat are used, with S1p = 8: fwd_cat = [alpha; 0 x 7; L_W^T], L_W L_W^T = ys^2 (K+s2 I)^-1
+                                *    (filled by bo_ei_setup) */
 } bo_nei;
 
 typedef struct bo_ctx bo_ctx;
@@ -113,6 +123,8 @@ long bo_pad8(long x);
 long bo_kp(int d);
 
 /* ---- setup -------------------------------------------------------------------------------- */
+/* stacked-operand geometry shared by setup, forward and backward: number of leading dense rows of fwd_cat */
+long bo_nei_dense_rows(const bo_nei* nei);
 size_t bo_gp_setup_workspace_bytes(const bo_gp* gp);
 /* K = k(X,X) + (noise+jitter) I; L = chol(K) (blocked right-looking, DMMA trailing updates);
  * inv(L); alpha.  info[M] (device int32): 0 or 1-based index of the first bad pivot. */
@@ -122,6 +134,14 @@ size_t bo_nei_setup_workspace_bytes(const bo_gp* gp, const bo_nei* nei);
 /* V_b, Sigma_bb, L_b (+inverse), baseline samples and best_f. info[M] as above for chol(Sigma_bb). */
 int bo_nei_setup(bo_ctx* ctx, const bo_gp* gp, const bo_nei* nei, void* work, size_t work_bytes, int32_t* info,
                  void* stream);
+
+/* qEI / qLogEI (nei->no_baseline = 1): fills fwd_cat = [alpha; 0; L_W^T] and bwd_cat = [alpha | 0 | L_W] with
+ * L_W L_W^T = ys^2 (K + s2 I)^-1, so that the q x q posterior covariance of a candidate set is ys^2 k(X,X) - U^T U,
+ * U = L_W^T K(X_tr, X) -- the joint posterior of model.posterior(X) (models/gpytorch.py:405-466) sampled as
+ * mean + chol(Sigma) z (posteriors/gpytorch.py:121-165).  best_f [M][Sp] is an INPUT here.  info[M] as above. */
+size_t bo_ei_setup_workspace_bytes(const bo_gp* gp, const bo_nei* nei);
+int bo_ei_setup(bo_ctx* ctx, const bo_gp* gp, const bo_nei* nei, void* work, size_t work_bytes, int32_t* info,
+                void* stream);
 
 /* ---- the hot path ------------------------------------------------------------------------- */
 /* workspace for B t-batch elements of q points; with_grad != 0 adds the backward regions.

@@ -131,6 +131,28 @@ def test_qlognei_pending_points_and_errors(cuda):
         acqf(X)
 
 
+def test_jitter_warning_is_reported_by_check_numerics(cuda):
+    """A candidate on a training point makes the q x q Schur block singular: the jitter schedule of psd_safe_cholesky
+    runs in the kernel and the host reports it as a NumericalWarning -- one call late, or on check_numerics()."""
+    p = make_problem("C1")
+    model = _model(p, cuda)
+    acqf = _acqf(p, model, cuda)
+    X = torch.stack([p.train_X[:2], p.train_X[2:4]]).to(cuda)  # 2 t-batches of q = 2 training points
+    with warnings.catch_warnings(record=True) as rec:
+        warnings.simplefilter("always")
+        val = acqf(X)
+        acqf.check_numerics()
+    assert bool(torch.isfinite(val).all())
+    kinds = {w.category for w in rec}
+    _, info, _ = acqf._nei.forward(X.contiguous(), acqf._Zq, acqf.tau_relu, acqf.tau_max, with_grad=False)
+    assert (bb.exceptions.NumericalWarning in kinds) == (int(info.max()) > 0)
+    assert (bb.exceptions.BotorchWarning in kinds) == (int(info.min()) < 0)
+    with warnings.catch_warnings(record=True) as rec:  # drained: nothing is reported twice
+        warnings.simplefilter("always")
+        acqf.check_numerics()
+    assert not rec
+
+
 def test_optimize_acqf_improves_and_respects_bounds(cuda):
     p = make_problem("C1")
     model = _model(p, cuda)

@@ -215,3 +215,37 @@ def test_base_sample_layout_of_qlognei():
     assert zb.shape == (8, 5) and zq.shape == (8, 3)
     assert torch.equal(zb, qmc.sobol_normal(5, 8, 1234))
     assert torch.equal(zq, qmc.sobol_normal(8, 8, 1234)[:, 5:])
+
+
+def test_plain_ei_reduction_known_answers():
+    """qEI / qNEI reductions (monte_carlo.py:410,180-252) on hand-made samples: the known answers of
+    test/acquisition/test_monte_carlo.py:112-136 (zero samples: 0 at best_f = 0, 1 at best_f = -1) and the
+    gradient conventions of torch (amax: even split over ties, clamp_min: passes x >= 0)."""
+    from oracle.qei import _plain_reduction
+
+    zeros = torch.zeros(2, 1, 1, dtype=torch.float64)  # S x B x q
+    assert float(_plain_reduction(zeros, torch.tensor(0.0))) == 0.0
+    assert float(_plain_reduction(zeros, torch.tensor(-1.0))) == 1.0
+    obj = torch.tensor([[[0.5, 2.0, 2.0]], [[-1.0, -3.0, -2.0]]], dtype=torch.float64, requires_grad=True)  # S=2, B=1, q=3
+    val = _plain_reduction(obj, torch.tensor(0.0))
+    assert float(val) == 1.0  # mean(2, 0)
+    (g,) = torch.autograd.grad(val.sum(), obj)
+    assert torch.equal(g, torch.tensor([[[0.0, 0.25, 0.25]], [[0.0, 0.0, 0.0]]], dtype=torch.float64))
+
+
+def test_oracle_ei_family_consistency():
+    """qNEI oracle == mean_s relu(max_j f_sj - best_f_s) on the qLogNEI sample path; qLogEI ~ log qEI up to the
+    smoothing (tau_relu = 1e-6, tau_max = 1e-2) where improvement is common."""
+    from oracle.qei import OracleQEI, OracleQLogEI, OracleQNEI
+
+    p = make_problem("C2", n=40)
+    ogp = oracle_gp(p)
+    X = candidates(p, 4, q=3)
+    nei, lognei = OracleQNEI(ogp, p.train_X, p.mc_samples), OracleQLogNEI(ogp, p.train_X, p.mc_samples)
+    f = lognei.samples_faithful(X)
+    manual = (f.amax(-1) - lognei.best_f.unsqueeze(1)).clamp_min(0).mean(0)
+    _close(nei.forward(X), manual)
+    with torch.no_grad():
+        best_f = ogp.posterior(p.train_X)[0].min()
+    ei, logei = OracleQEI(ogp, best_f, p.mc_samples), OracleQLogEI(ogp, best_f, p.mc_samples)
+    assert float((logei.forward(X) - ei.forward(X).log()).abs().max()) < 0.05
