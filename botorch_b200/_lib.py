@@ -112,6 +112,10 @@ def _declare(lib: C.CDLL) -> None:
     lib.bo_posterior_workspace_bytes.restype = sz
     lib.bo_posterior_workspace_bytes.argtypes = [gp, i64]
     lib.bo_posterior_joint.argtypes = [vp, gp, i32, i32, vp, vp, vp, vp, sz, vp]
+    lib.bo_posterior_joint_large_workspace_bytes.restype = sz
+    lib.bo_posterior_joint_large_workspace_bytes.argtypes = [gp, i64]
+    lib.bo_posterior_joint_large.argtypes = [vp, gp, i64, vp, vp, vp, vp, sz, vp]
+    lib.bo_posterior_joint_large.restype = i32
     lib.bo_posterior_bwd_workspace_bytes.restype = sz
     lib.bo_posterior_bwd_workspace_bytes.argtypes = [gp, i32, i32]
     lib.bo_posterior_joint_bwd.argtypes = [vp, gp, i32, i32, vp, vp, vp, vp, vp, sz, vp]

@@ -643,6 +643,56 @@ int bo_posterior_joint(bo_ctx* ctx, const bo_gp* gp, int B, int q, const double*
     return bo_cand_posterior(a, mean, cov, st);
 }
 
+// ---- joint posterior of ONE large point set (q up to n and beyond): all GEMM-shaped ------------------------------
+static size_t post_large_layout(const bo_gp* gp, long q, void* work, size_t cap, double** arows, double** vt,
+                                double** var, size_t* base_bytes, bool* ok) {
+    const long M = gp->M, Kp = bo_kp(gp->d), np = bo_pad8(gp->n), ldq = bo_pad8(q);
+    *base_bytes = bo_posterior_workspace_bytes(gp, q);
+    Bump b(work ? (char*)work + *base_bytes : nullptr, cap > *base_bytes ? cap - *base_bytes : 0);
+    *arows = b.doubles(M * q * Kp);
+    *vt = b.doubles(M * q * np);
+    *var = b.doubles(M * ldq);
+    *ok = b.ok && (!work || cap >= *base_bytes);
+    return *base_bytes + b.off;
+}
+
+size_t bo_posterior_joint_large_workspace_bytes(const bo_gp* gp, long q) {
+    double *a, *b, *c;
+    size_t base;
+    bool ok;
+    return post_large_layout(gp, q, nullptr, 0, &a, &b, &c, &base, &ok);
+}
+
+int bo_posterior_joint_large(bo_ctx* ctx, const bo_gp* gp, long q, const double* X, double* mean, double* cov,
+                             void* work, size_t work_bytes, void* stream) {
+    if (!ctx || !valid_gp(gp) || q <= 0 || !X || !mean || !cov || !work) return BO_ERR_INVALID;
+    if (q > 0x7fffffffL) return BO_ERR_UNSUPPORTED;
+    cudaStream_t st = (cudaStream_t)stream;
+    double *arows, *vt, *var, *v, *kx;
+    size_t base;
+    bool ok;
+    post_large_layout(gp, q, work, work_bytes, &arows, &vt, &var, &base, &ok);
+    if (!ok) return BO_ERR_WORKSPACE;
+    long ldn;
+    BO_TRY(posterior_v(gp, q, X, work, base, &v, &kx, &ldn, st));  // V = [inv(L); alpha^T] K(X_tr, X)
+    const long n = gp->n, M = gp->M, np = bo_pad8(n), Kp = bo_kp(gp->d);
+    const double ys2 = gp->y_std * gp->y_std;
+    const BoKernelHyper h = hyper_of(gp);
+    // mean (and a scratch marginal variance) from row n and the column norms of V
+    BO_TRY(bo_col_mean_var(v, (n + 1) * ldn, ldn, (int)n, q, (int)M, gp->y_mean, gp->y_std, gp->mean, gp->outputscale, mean,
+                           var, st));
+    // cov = ys^2 (k(X, X) - V^T V): the augmented operands of X on both sides, then one q x q x n GEMM
+    BO_TRY(bo_aug_rows(h, X, q, arows, Kp, q * Kp, st));
+    double* baug = reinterpret_cast<double*>(work);  // first region of the base layout: augmented columns of X
+    const long ldq = bo_pad8(q);  // pitch of cov: [M][q x ldq]
+    BO_TRY(kmat(gp, arows, (int)q, baug, ldn, q, cov, ldq, q * ldq, 1, nullptr, st));
+    BO_TRY(bo_fill(vt, M * q * np, 0.0, st));
+    BO_TRY(bo_transpose(v, ldn, (n + 1) * ldn, vt, np, q * np, (int)n, (int)q, (int)M, st));
+    BO_TRY(gemm((int)q, (int)q, (int)n, (int)M, -ys2, vt, np, q * np, v, ldn, (n + 1) * ldn, ys2, cov, ldq, q * ldq, cov, ldq,
+                q * ldq, BO_TRI_NONE, 0, st));
+    return BO_OK;
+}
+
 size_t bo_posterior_bwd_workspace_bytes(const bo_gp* gp, int B, int q) {
     const long Nc = (long)B * q, ldn = bo_pad8(Nc);
     Bump b(nullptr, 0);

@@ -19,6 +19,7 @@ from ._lib import BoGP, BoNEI, check, kp, pad8, ptr
 from .exceptions import NanError, NotPSDError, NumericalWarning
 
 REDUCE_LOG, REDUCE_PLAIN = 0, 1  # BO_REDUCE_* of include/botorch_b200.h
+MAX_Q = 32  # BO_MAX_Q: largest q-batch of the per-candidate kernels
 
 KERNEL_IDS = {"rbf": 0, "matern52": 1}
 CHOLESKY_MAX_TRIES = 6  # botorch/__init__.py:47
@@ -137,6 +138,15 @@ class GPState:
         X = _f64(X, self.device)
         B, q, _ = X.shape
         lib = _lib.lib()
+        if q > MAX_Q:  # large joint sets (e.g. all of X_baseline): GEMM-shaped, one t-batch at a time, no gradient
+            ldq = pad8(q)
+            mean = torch.empty(B, self.M, q, dtype=torch.float64, device=self.device)
+            cov = torch.empty(B, self.M, q, ldq, dtype=torch.float64, device=self.device)
+            work = _lib.workspace(lib.bo_posterior_joint_large_workspace_bytes(C.byref(self.c), q), self.device)
+            for b in range(B):
+                check(lib.bo_posterior_joint_large(self.ctx, C.byref(self.c), q, ptr(X[b]), ptr(mean[b]), ptr(cov[b]),
+                                                   work.data_ptr(), work.numel(), _lib.stream_ptr(self.device)))  # fmt: skip
+            return mean.transpose(0, 1), cov[..., :q].transpose(0, 1)
         mean = torch.empty(self.M, B, q, dtype=torch.float64, device=self.device)
         cov = torch.empty(self.M, B, q, q, dtype=torch.float64, device=self.device)
         work = _lib.workspace(lib.bo_posterior_workspace_bytes(C.byref(self.c), B * q), self.device)
@@ -460,5 +470,8 @@ def posterior_joint(st: GPState, X: Tensor):
     if X.device != st.device:
         raise _lib.BoError(f"X is on {X.device} but the model factors live on {st.device}; there is no CPU path")
     if torch.is_grad_enabled() and X.requires_grad:
+        if X.shape[-2] > MAX_Q:
+            raise _lib.BoError(f"the posterior of a {X.shape[-2]}-point joint set is not differentiable w.r.t. X on this "
+                               f"path (q <= {MAX_Q}); evaluate it under torch.no_grad()")
         return _PosteriorJoint.apply(X, st)
     return st.posterior_joint(X.detach())

@@ -173,6 +173,13 @@ int bo_posterior_joint(bo_ctx* ctx, const bo_gp* gp, int B, int q, const double*
 /* grad_X[M x B x q x d] = d(sum mean_bar*mean + sum cov_bar*cov)/dX per model: the reverse pass torch.autograd
  * runs through model.posterior when a caller differentiates posterior statistics (models/gpytorch.py:405-466
  * with detached train caches, models/utils/assorted.py:294-296). */
+/* Joint posterior of ONE large point set (q may exceed BO_MAX_Q; e.g. all of X_baseline for
+ * prune_inferior_points, acquisition/utils.py:245-349, or a joint Thompson draw over a candidate block,
+ * generation/sampling.py:95-155): mean [M x q], cov [M][q x ldq] with ldq = bo_pad8(q), all GEMM-shaped. */
+size_t bo_posterior_joint_large_workspace_bytes(const bo_gp* gp, long q);
+int bo_posterior_joint_large(bo_ctx* ctx, const bo_gp* gp, long q, const double* X, double* mean, double* cov,
+                             void* work, size_t work_bytes, void* stream);
+
 size_t bo_posterior_bwd_workspace_bytes(const bo_gp* gp, int B, int q);
 int bo_posterior_joint_bwd(bo_ctx* ctx, const bo_gp* gp, int B, int q, const double* X, const double* mean_bar,
                            const double* cov_bar, double* grad_X, void* work, size_t work_bytes, void* stream);

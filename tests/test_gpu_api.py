@@ -54,6 +54,27 @@ def test_posterior_mean_covariance_and_grad(cuda, cfg, kw, bshape, q):
     assert rel_err(g, g_ref) < 1e-8
 
 
+@pytest.mark.parametrize("cfg,kw,q", [("C2", {"n": 60}, 60), ("C3", {"n": 256}, 131), ("C4", {"M": 3}, 45)])
+def test_posterior_of_a_large_joint_set(cuda, cfg, kw, q):
+    """q beyond the per-candidate kernels' limit (prune_inferior_points evaluates the joint posterior of all of
+    X_baseline): the GEMM-shaped path gives the same mean / covariance, and sampling from it works."""
+    p = make_problem(cfg, **kw)
+    ogp = oracle_gp(p)
+    model = _model(p, cuda)
+    X = torch.cat([p.train_X[: q // 2], candidates(p, q - q // 2, q=1).reshape(-1, p.d)])
+    with torch.no_grad():
+        post = model.posterior(X.to(cuda))
+    m_ref, c_ref = ogp.posterior_direct(X)
+    prior = float(ogp.y_std) ** 2 * (float(p.hypers["outputscale"].max()) if p.hypers.get("outputscale") is not None else 1.0)
+    assert rel_err(post.mean.squeeze(-1), m_ref) < RTOL
+    assert rel_err(post.distribution.covariance_matrix, c_ref, scale=prior) < RTOL
+    sampler = bb.SobolQMCNormalSampler(sample_shape=torch.Size([16]), seed=3)
+    samples = sampler(post)
+    assert samples.shape[0] == 16 and samples.shape[-2:] == (q, 1) and bool(torch.isfinite(samples).all())
+    with pytest.raises(Exception):
+        model.posterior(X.to(cuda).requires_grad_(True))
+
+
 def test_posterior_observation_noise_and_errors(cuda):
     p = make_problem("C1")
     model = _model(p, cuda)
