@@ -403,14 +403,11 @@ QWork qlayout(const bo_gp* gp, const bo_nei* nei, int B, int q, int with_grad, v
     }
     if (with_grad) {
         w.Sbar = b.doubles(M * (long)B * q * q);
-        if (w.qpath) {
-            w.W2 = b.doubles(M * w.regionStride);
-            w.strideH = (long)(gp->d + 1) * w.ldn;
-            w.H = b.doubles(M * w.strideH);
-            if (gp->kernel_id != BO_KERNEL_RBF) w.Wd = b.doubles(M * w.regionStride);  // Matern derivative factor
-        } else {
-            w.W5 = b.doubles(M * w.regionStride);
-        }
+        w.strideH = (long)(gp->d + 1) * w.ldn;
+        w.H = gp->xt_aug ? b.doubles(M * w.strideH) : nullptr;
+        if (gp->kernel_id != BO_KERNEL_RBF) w.Wd = b.doubles(M * w.regionStride);  // Matern derivative factor
+        if (w.qpath) w.W2 = b.doubles(M * w.regionStride);
+        else w.W5 = b.doubles(M * w.regionStride);
     }
     w.ok = b.ok;
     w.bytes = b.off;
@@ -563,22 +560,39 @@ int bo_qlognei_bwd(bo_ctx* ctx, const bo_gp* gp, const bo_nei* nei, int B, int q
     BO_TRY(gemm((int)nb, (int)N, (int)S, (int)M, 1.0, nei->zb_t, Sp, 0, w.F, w.ldn, (S + 1) * w.ldn, 0.0, nullptr, 0, 0, w.W2,
                 w.ldn, w.regionStride, BO_TRI_NONE, 0, st));
     BO_TRY(bo_colblock_update(w.W2, w.regionStride, w.W3, w.regionStride, w.Sbar, (int)nb, B, q, (int)M, w.ldn, -2.0, 1, st));
-    // 3. Cbar = inv(L_b)^T BLbar                            (W0)
+    // 3. Cbar = inv(L_b)^T BLbar                            (W3: bl_chol^T is dead after step 2; W0 keeps K(X_tr, X))
     BO_TRY(gemm((int)nb, (int)N, (int)nb, (int)M, 1.0, nei->lb_inv_t, nbp, nb * nbp, w.W2, w.ldn, w.regionStride, 0.0,
-                nullptr, 0, 0, w.W0, w.ldn, w.regionStride, BO_TRI_A_UPPER, 0, st));
+                nullptr, 0, 0, w.W3, w.ldn, w.regionStride, BO_TRI_A_UPPER, 0, st));
     // 4. Vbar = -ys^2 V_b Cbar - 2 ys^2 V Sbar              (W5 rows 0..n-1; row n holds y_std * mubar)
-    BO_TRY(gemm((int)n, (int)N, (int)nb, (int)M, -ys2, nei->vb, nbp, (n + 1) * nbp, w.W0, w.ldn, w.regionStride, 0.0,
+    BO_TRY(gemm((int)n, (int)N, (int)nb, (int)M, -ys2, nei->vb, nbp, (n + 1) * nbp, w.W3, w.ldn, w.regionStride, 0.0,
                 nullptr, 0, 0, w.W5, w.ldn, w.regionStride, BO_TRI_NONE, 0, st));
     BO_TRY(bo_colblock_update(w.W5, w.regionStride, w.W1, w.regionStride, w.Sbar, (int)n, B, q, (int)M, w.ldn, -2.0 * ys2,
                               1, st));
-    // 5. KXbar = [inv(L)^T | alpha] Vbar (+ ys^2 Cbar when X_baseline is train_X)      (W2)
+    // 5. KXbar = [inv(L)^T | alpha] Vbar (+ ys^2 Cbar when X_baseline is train_X), and with the gradient contraction
+    //    operand available G = KXbar .* g(r) straight from the epilogue                                    (W2)
     const bool shared = nei->baseline_is_train != 0;
-    BO_TRY(gemm((int)n, (int)N, (int)n + 1, (int)M, 1.0, gp->linv_aug_t, n1p, n * n1p, w.W5, w.ldn, w.regionStride,
-                shared ? ys2 : 0.0, shared ? w.W0 : nullptr, w.ldn, w.regionStride, w.W2, w.ldn, w.regionStride,
-                BO_TRI_A_UPPER, 0, st));
-    // 6. chain through the covariance function to X
-    BO_TRY(bo_kgrad(h, gp->train_X, (int)n, w.W2, w.regionStride, w.ldn, X, B, q, 1.0, grad_X, st));
-    if (!shared) BO_TRY(bo_kgrad(h, nei->X_b, (int)nb, w.W0, w.regionStride, w.ldn, X, B, q, ys2, grad_X, st));
+    const bool gemm_grad = w.H != nullptr;
+    {
+        BoGemm g{};
+        g.A = gp->linv_aug_t; g.lda = n1p; g.strideA = n * n1p;
+        g.B = w.W5; g.ldb = w.ldn; g.strideB = w.regionStride;
+        g.C = w.W2; g.ldc = w.ldn; g.strideC = w.regionStride;
+        if (shared) { g.D = w.W3; g.ldd = w.ldn; g.strideD = w.regionStride; g.beta = ys2; }
+        if (gemm_grad) { g.E = w.Wd ? w.Wd : w.W0; g.lde = w.ldn; g.strideE = w.regionStride; }
+        g.alpha = 1.0; g.M = (int)n; g.N = (int)N; g.K = (int)n + 1; g.batch = (int)M;
+        g.tri = BO_TRI_A_UPPER; g.epi = BO_EPI_LINEAR;
+        BO_TRY(bo_gemm_launch(g, st));
+    }
+    // 6. chain through the covariance function to X: H = [train_X^T; 1] G, gradX += (H_t - x_t H_d) / l_t^2
+    if (gemm_grad) {
+        const long np = bo_pad8(n);
+        BO_TRY(gemm(gp->d + 1, (int)N, (int)n, (int)M, 1.0, gp->xt_aug, np, 0, w.W2, w.ldn, w.regionStride, 0.0, nullptr, 0, 0,
+                    w.H, w.ldn, w.strideH, BO_TRI_NONE, 0, st));
+        BO_TRY(bo_kgrad_finalize(h, w.H, w.strideH, w.ldn, X, N, 1.0, grad_X, st));
+    } else {
+        BO_TRY(bo_kgrad(h, gp->train_X, (int)n, w.W2, w.regionStride, w.ldn, X, B, q, 1.0, grad_X, st));
+    }
+    if (!shared) BO_TRY(bo_kgrad(h, nei->X_b, (int)nb, w.W3, w.regionStride, w.ldn, X, B, q, ys2, grad_X, st));
     return BO_OK;
 }
 

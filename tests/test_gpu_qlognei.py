@@ -93,18 +93,33 @@ def test_forward_no_grad_equals_with_grad_and_is_deterministic(cuda):
     assert torch.equal(a4, a1[:, perm])
 
 
-def test_separate_baseline_set(cuda):
-    """X_baseline != train_X (e.g. pruned baseline): extra cross-covariance and its gradient path."""
-    p = make_problem("C2")
+@pytest.mark.parametrize("cfg,kw,q,B,kind", [
+    ("C2", {}, 4, 9, "subset"), ("C3", {"n": 300}, 8, 5, "subset"), ("C2", {"n": 90}, 3, 6, "off-train"),
+    ("C4", {"M": 4}, 4, 6, "subset"), ("C4", {"M": 3}, 2, 5, "off-train"),
+])  # fmt: skip
+def test_separate_baseline_set(cuda, cfg, kw, q, B, kind):
+    """X_baseline != train_X (a pruned baseline, or points that were never observed): extra cross-covariance
+    K(X_b, X) and its gradient path, RBF and Matern, single- and multi-tile sizes."""
+    p = make_problem(cfg, **kw)
     Xb = p.train_X[::3].contiguous()
-    p, ogp, oacq, st, nei = _setup(cuda, "C2", {}, X_baseline=Xb)
+    if kind == "off-train":
+        Xb = torch.cat([Xb[:7], candidates(p, 6, q=1, seed=21).reshape(-1, p.d)])
+    p, ogp, oacq, st, nei = _setup(cuda, cfg, kw, X_baseline=Xb)
     assert not nei.is_train
-    X = candidates(p, 9)
-    Zq = oacq.Z_q(p.q).to(cuda).contiguous()
+    X = candidates(p, B, q=q)
+    Zq = oacq.Z_q(q).to(cuda).contiguous()
     acq, info, work = nei.forward(X.to(cuda), Zq, 1e-6, 1e-2, with_grad=True)
-    g = nei.backward(X.to(cuda), Zq, 1e-6, 1e-2, torch.ones_like(acq), work)[0]
     a_ref, g_ref = oacq.value_and_grad(X, mode="faithful")
-    assert rel_err(acq[0], a_ref, scale=0.0) < RTOL
+    if st.M == 1:
+        a = acq[0]
+        g = nei.backward(X.to(cuda), Zq, 1e-6, 1e-2, torch.ones_like(acq), work)[0]
+    else:
+        from oracle.safe_math import logmeanexp
+
+        a = logmeanexp(acq.mT.cpu(), dim=-1)
+        w = torch.softmax(acq.mT, dim=-1).mT.contiguous()
+        g = nei.backward(X.to(cuda), Zq, 1e-6, 1e-2, w, work).sum(0)
+    assert rel_err(a, a_ref, scale=0.0) < RTOL
     assert _grad_rel(g, g_ref) < RTOL
 
 
