@@ -370,11 +370,25 @@ struct QWork {
     long ldn, R, regionStride;
     double *baug, *W0, *W1, *W2, *W3, *F, *W5, *W6, *Lq, *lse, *Sbar, *Wd, *H;
     long strideH;
+    int ksplit;  // row slices of the [train_X^T; 1] G contraction (split-K), summed in order by the finalize kernel
     bool qpath;  // X_baseline == train_X with the combined root L_W (bo_nei.lw): Schur = ys^2 k - U^T U, U = L_W^T K(X_tr, X)
     int32_t* info;
     bool ok;
     size_t bytes;
 };
+
+// The (d+1) x N x n contraction H = [train_X^T; 1] G has one row tile only: split its n-long sum into slices that run as
+// separate batch members (single-model case), so the launch fills the SMs; slices must be equal and 16-byte aligned.
+int hsplit(const bo_gp* gp) {
+    if (gp->M != 1 || gp->n < 512) return 1;
+    for (int ks = 8; ks >= 2; ks--)
+        if (gp->n % ks == 0 && (gp->n / ks) % 2 == 0) return ks;
+    return 1;
+}
+
+// H slices <- [train_X^T; 1] G, then gradX += (H_t - x_t H_d) / l_t^2
+int kernel_gradient(const bo_gp* gp, const BoKernelHyper& h, const QWork& w, const double* G, const double* X, long N,
+                    double* grad_X, cudaStream_t st);
 
 QWork qlayout(const bo_gp* gp, const bo_nei* nei, int B, int q, int with_grad, void* work, size_t cap) {
     QWork w{};
@@ -404,7 +418,8 @@ QWork qlayout(const bo_gp* gp, const bo_nei* nei, int B, int q, int with_grad, v
     if (with_grad) {
         w.Sbar = b.doubles(M * (long)B * q * q);
         w.strideH = (long)(gp->d + 1) * w.ldn;
-        w.H = gp->xt_aug ? b.doubles(M * w.strideH) : nullptr;
+        w.ksplit = hsplit(gp);
+        w.H = gp->xt_aug ? b.doubles(M * w.strideH * w.ksplit) : nullptr;
         if (gp->kernel_id != BO_KERNEL_RBF) w.Wd = b.doubles(M * w.regionStride);  // Matern derivative factor
         if (w.qpath) w.W2 = b.doubles(M * w.regionStride);
         else w.W5 = b.doubles(M * w.regionStride);
@@ -412,6 +427,20 @@ QWork qlayout(const bo_gp* gp, const bo_nei* nei, int B, int q, int with_grad, v
     w.ok = b.ok;
     w.bytes = b.off;
     return w;
+}
+
+int kernel_gradient(const bo_gp* gp, const BoKernelHyper& h, const QWork& w, const double* G, const double* X, long N,
+                    double* grad_X, cudaStream_t st) {
+    const long n = gp->n, M = gp->M, np = bo_pad8(n);
+    if (w.ksplit > 1) {  // M == 1: batch index = slice
+        const long kc = n / w.ksplit;
+        BO_TRY(gemm(gp->d + 1, (int)N, (int)kc, w.ksplit, 1.0, gp->xt_aug, np, kc, G, w.ldn, kc * w.ldn, 0.0, nullptr, 0, 0,
+                    w.H, w.ldn, w.strideH, BO_TRI_NONE, 0, st));
+        return bo_kgrad_finalize(h, w.H, 0, w.ldn, X, N, 1.0, grad_X, w.ksplit, w.strideH, st);
+    }
+    BO_TRY(gemm(gp->d + 1, (int)N, (int)n, (int)M, 1.0, gp->xt_aug, np, 0, G, w.ldn, w.regionStride, 0.0, nullptr, 0, 0, w.H,
+                w.ldn, w.strideH, BO_TRI_NONE, 0, st));
+    return bo_kgrad_finalize(h, w.H, w.strideH, w.ldn, X, N, 1.0, grad_X, 1, 0, st);
 }
 
 BoCandArgs cand_args(const bo_gp* gp, const bo_nei* nei, int B, int q, const double* X, const double* Zq,
@@ -549,9 +578,7 @@ int bo_qlognei_bwd(bo_ctx* ctx, const bo_gp* gp, const bo_nei* nei, int B, int q
         g.tri = BO_TRI_A_LOWER; g.tri_off = (int)S1p; g.epi = BO_EPI_LINEAR;
         BO_TRY(bo_gemm_launch(g, st));
         // 4r. H = [train_X^T; 1] G  ((d+1) x N), then gradX += (H_t - x_t H_d) / l_t^2
-        BO_TRY(gemm(gp->d + 1, (int)N, (int)n, (int)M, 1.0, gp->xt_aug, np, 0, w.W2, w.ldn, w.regionStride, 0.0, nullptr, 0, 0,
-                    w.H, w.ldn, w.strideH, BO_TRI_NONE, 0, st));
-        return bo_kgrad_finalize(h, w.H, w.strideH, w.ldn, X, N, 1.0, grad_X, st);
+        return kernel_gradient(gp, h, w, w.W2, X, N, grad_X, st);
     }
     a.Vbar_mu = w.W5 + n * w.ldn;
     a.strideVbar = w.regionStride;
@@ -585,10 +612,7 @@ int bo_qlognei_bwd(bo_ctx* ctx, const bo_gp* gp, const bo_nei* nei, int B, int q
     }
     // 6. chain through the covariance function to X: H = [train_X^T; 1] G, gradX += (H_t - x_t H_d) / l_t^2
     if (gemm_grad) {
-        const long np = bo_pad8(n);
-        BO_TRY(gemm(gp->d + 1, (int)N, (int)n, (int)M, 1.0, gp->xt_aug, np, 0, w.W2, w.ldn, w.regionStride, 0.0, nullptr, 0, 0,
-                    w.H, w.ldn, w.strideH, BO_TRI_NONE, 0, st));
-        BO_TRY(bo_kgrad_finalize(h, w.H, w.strideH, w.ldn, X, N, 1.0, grad_X, st));
+        BO_TRY(kernel_gradient(gp, h, w, w.W2, X, N, grad_X, st));
     } else {
         BO_TRY(bo_kgrad(h, gp->train_X, (int)n, w.W2, w.regionStride, w.ldn, X, B, q, 1.0, grad_X, st));
     }

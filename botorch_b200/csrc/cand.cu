@@ -41,15 +41,16 @@ __device__ __forceinline__ double log_fatplus(double z, double tau) {
     const double u = z / tau;
     // exp(u) underflows to exactly 0 below -746: skipping exp/log1p there is bit-identical and removes two of the three
     // transcendentals for the bulk of the samples (tau = 1e-6 puts |u| in the 1e4..1e6 range)
-    const double sp = (u > 20.0) ? u : (u < -746.0 ? 0.0 : log1p(exp(u)));
+    if (u < -746.0) return log(0.1 * tau) - log(fma(u, u, 1.0));  // softplus == 0: log(tau * 0.1 / (1 + u^2)), no division
+    const double sp = (u > 20.0) ? u : log1p(exp(u));
     return log(tau * (sp + 0.1 * (1.0 / (1.0 + u * u))));
 }
 // d log_fatplus / dz
 __device__ __forceinline__ double dlog_fatplus(double z, double tau) {
     const double u = z / tau;
+    if (u < -746.0) return -2.0 * u / (fma(u, u, 1.0) * tau);  // softplus == sigmoid == 0: d/dz log(0.1 / (1 + u^2))
     double sp, sig;
     if (u > 20.0) { sp = u; sig = 1.0; }
-    else if (u < -746.0) { sp = 0.0; sig = 0.0; }
     else { const double e = exp(u); sp = log1p(e); sig = e / (e + 1.0); }
     const double c = 1.0 / (1.0 + u * u);
     const double val = sp + 0.1 * c;
@@ -115,6 +116,41 @@ __device__ __forceinline__ void fatmax_q_grad(const double (&x)[QT], int q, doub
     for (int j = 0; j < QT; j++)
         if (j < q && x[j] == M) g[j] += rest;
 }
+
+// Sum P per-lane values over the 32 lanes of a warp with ~P shuffles instead of 5 P: at every butterfly step each lane
+// keeps one half of its values and sends the other half to its partner, so the value count halves while the lane
+// groups that share a value shrink.  idx[] tracks which original value a slot holds.  The order of the additions is
+// fixed by the lane layout, so the result is deterministic.  After the five steps every lane owns NOUT slots.
+template <int N>
+__device__ __forceinline__ void halve_step(double* v, int* idx, int lane, int off) {
+    constexpr int H = (N + 1) / 2;
+    const bool hi = (lane & off) != 0;
+#pragma unroll
+    for (int i = 0; i < N - H; i++) {
+        const double send = hi ? v[i] : v[i + H];
+        const double keep = hi ? v[i + H] : v[i];
+        v[i] = keep + __shfl_xor_sync(0xffffffffu, send, off);
+        idx[i] = hi ? idx[i + H] : idx[i];
+    }
+    if constexpr (N & 1) v[H - 1] += __shfl_xor_sync(0xffffffffu, v[H - 1], off);
+}
+template <int P>
+struct WarpMultiReduce {
+    static constexpr int N1 = (P + 1) / 2, N2 = (N1 + 1) / 2, N3 = (N2 + 1) / 2, N4 = (N3 + 1) / 2, NOUT = (N4 + 1) / 2;
+    // v[P] in, out[idx] = warp sum for every value (each written by the lanes that end up owning it; duplicates agree)
+    static __device__ __forceinline__ void run(double* v, int lane, double* out) {
+        int idx[P];
+#pragma unroll
+        for (int i = 0; i < P; i++) idx[i] = i;
+        halve_step<P>(v, idx, lane, 16);
+        halve_step<N1>(v, idx, lane, 8);
+        halve_step<N2>(v, idx, lane, 4);
+        halve_step<N3>(v, idx, lane, 2);
+        halve_step<N4>(v, idx, lane, 1);
+#pragma unroll
+        for (int i = 0; i < NOUT; i++) out[idx[i]] = v[i];
+    }
+};
 
 __device__ __forceinline__ double block_reduce_max(double v, double* red) {
     for (int o = 16; o > 0; o >>= 1) v = fmax(v, __shfl_xor_sync(0xffffffffu, v, o));
@@ -238,6 +274,7 @@ __device__ void gram_block_reg(const double* __restrict__ Mtx, long ld, int rows
 #pragma unroll
     for (int p = 0; p < P; p++) acc[p] = 0.0;
     const bool vec = (q == QT) && ((QT & 1) == 0) && ((c0 & 1) == 0) && ((ld & 1) == 0);
+#pragma unroll 2
     for (int r = tid; r < rows; r += T) {
         double v[QT];
         const double* row = Mtx + (long)r * ld + c0;
@@ -258,12 +295,7 @@ __device__ void gram_block_reg(const double* __restrict__ Mtx, long ld, int rows
 #pragma unroll
             for (int k = 0; k <= j; k++) acc[p++] += v[j] * v[k];
     }
-#pragma unroll
-    for (int p = 0; p < P; p++) {
-        double a = acc[p];
-        for (int o = 16; o > 0; o >>= 1) a += __shfl_xor_sync(0xffffffffu, a, o);
-        if (lane == 0) red[warp * P + p] = a;
-    }
+    WarpMultiReduce<P>::run(acc, lane, red + warp * P);
     __syncthreads();
     for (int p = tid; p < P; p += T) {
         int j = 0;
@@ -298,6 +330,32 @@ __device__ bool chol_small(double* A, int q) {
             double s = A[i * q + j];
             for (int k = 0; k < j; k++) s -= A[i * q + k] * A[j * q + k];
             A[i * q + j] = s / d;
+        }
+    }
+    return true;
+}
+
+// Cholesky of the q x q matrix whose row `lane` sits in r[] (lanes >= q idle), right-looking, one pivot per step: the
+// pivot and the column entries travel by shuffle, so the q steps cost a few hundred cycles instead of a serial
+// O(q^3) chain through shared memory.  The subtraction order per entry (k ascending) is the one of chol_small.
+// Returns false (uniformly) on a non-positive pivot.  On success r[0..lane] is row `lane` of L.
+template <int QT>
+__device__ __forceinline__ bool chol_warp(double (&r)[QT], int q, int lane) {
+#pragma unroll
+    for (int j = 0; j < QT; j++) {
+        if (j < q) {
+            const double d = __shfl_sync(0xffffffffu, r[j], j);
+            if (!(d > 0.0)) return false;
+            const double sd = sqrt(d);
+            const double lij = (lane == j) ? sd : r[j] / sd;
+            r[j] = lij;
+#pragma unroll
+            for (int k = j + 1; k < QT; k++) {
+                if (k < q) {
+                    const double lkj = __shfl_sync(0xffffffffu, lij, k);
+                    if (lane >= k) r[k] -= lij * lkj;
+                }
+            }
         }
     }
     return true;
@@ -341,7 +399,7 @@ __device__ __forceinline__ double pair_r2(const double* X, int d, const double* 
 }
 
 template <int QT>
-__global__ void __launch_bounds__(CAND_THREADS, (QT <= 4 ? 6 : (QT <= 8 ? 4 : 1))) cand_fwd_kernel(const BoCandArgs a) {
+__global__ void __launch_bounds__(CAND_THREADS, (QT <= 8 ? 4 : 1)) cand_fwd_kernel(const BoCandArgs a) {
     extern __shared__ __align__(16) double sm[];
     __shared__ double red[CAND_THREADS / 32];
     __shared__ int s_info;
@@ -371,30 +429,34 @@ __global__ void __launch_bounds__(CAND_THREADS, (QT <= 4 ? 6 : (QT <= 8 ? 4 : 1)
     }
     if (tid < q) c.mu[tid] = a.y_mean + a.y_std * (a.mean_const[z] + mu_row[c0 + tid]);
     __syncthreads();
-    if (tid == 0) {  // psd_safe_cholesky: plain attempt, then jitter 1e-8 * 10^i, i = 0..5
-        double* Sq = c.GV;  // backup of the Schur block
+    if (tid < 32) {  // psd_safe_cholesky on warp 0: plain attempt, then jitter 1e-8 * 10^i, i = 0..5; lane i owns row i
+        const int lane = tid;
+        double row0[QT], r[QT];
         bool has_nan = false;
-        for (int i = 0; i < q * q; i++) {
-            Sq[i] = c.Lq[i];
-            has_nan |= isnan(Sq[i]);
+#pragma unroll
+        for (int k = 0; k < QT; k++) {
+            row0[k] = (lane < q && k < q) ? c.Lq[lane * q + k] : 0.0;
+            has_nan |= isnan(row0[k]);
         }
+        has_nan = __any_sync(0xffffffffu, has_nan);
         int code = -2;
         if (has_nan) {
             code = -1;
         } else {
             double jit = 0.0;
             for (int attempt = 0; attempt <= 6; attempt++) {
-                for (int i = 0; i < q * q; i++) c.Lq[i] = Sq[i];
-                for (int i = 0; i < q; i++) c.Lq[i * q + i] += jit;
-                if (chol_small(c.Lq, q)) { code = attempt; break; }
+#pragma unroll
+                for (int k = 0; k < QT; k++) r[k] = row0[k] + ((k == lane) ? jit : 0.0);
+                if (chol_warp<QT>(r, q, lane)) { code = attempt; break; }
                 jit = (attempt == 0) ? 1e-8 : jit * 10.0;
             }
         }
-        if (code < 0)
-            for (int i = 0; i < q * q; i++) c.Lq[i] = 0.0;
-        for (int j = 0; j < q; j++)
-            for (int k = j + 1; k < q; k++) c.Lq[j * q + k] = 0.0;
-        s_info = code;
+        if (lane < q) {
+#pragma unroll
+            for (int k = 0; k < QT; k++)
+                if (k < q) c.Lq[lane * q + k] = (code >= 0 && k <= lane) ? r[k] : 0.0;
+        }
+        if (lane == 0) s_info = code;
     }
     __syncthreads();
 
@@ -467,7 +529,7 @@ namespace {
 //   out: F <- d loss / d f ;  Sbar = adjoint of the Schur block (symmetric);
 //        Vbar row n <- y_std * d loss / d mu ;  gradX <- contribution of k(X, X)
 template <int QT>
-__global__ void __launch_bounds__(CAND_THREADS, (QT <= 4 ? 6 : (QT <= 8 ? 3 : 1))) cand_bwd_kernel(const BoCandArgs a) {
+__global__ void __launch_bounds__(CAND_THREADS, (QT <= 8 ? 4 : 1)) cand_bwd_kernel(const BoCandArgs a) {
     extern __shared__ __align__(16) double sm[];
     const int q = a.q, b = blockIdx.x, z = blockIdx.y, tid = threadIdx.x, T = blockDim.x;
     const int c0 = b * q;
@@ -541,18 +603,12 @@ __global__ void __launch_bounds__(CAND_THREADS, (QT <= 4 ? 6 : (QT <= 8 ? 3 : 1)
     }
     {
         const int warp = tid >> 5, lane = tid & 31;
+        double both[QT + PT];
 #pragma unroll
-        for (int j = 0; j < QT; j++) {
-            double v = am[j];
-            for (int o2 = 16; o2 > 0; o2 >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o2);
-            if (lane == 0) red[warp * (QT + PT) + j] = v;
-        }
+        for (int j = 0; j < QT; j++) both[j] = am[j];
 #pragma unroll
-        for (int p = 0; p < PT; p++) {
-            double v = al[p];
-            for (int o2 = 16; o2 > 0; o2 >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o2);
-            if (lane == 0) red[warp * (QT + PT) + QT + p] = v;
-        }
+        for (int p = 0; p < PT; p++) both[QT + p] = al[p];
+        WarpMultiReduce<QT + PT>::run(both, lane, red + warp * (QT + PT));
     }
     __syncthreads();
     for (int idx = tid; idx < q + q * q; idx += T) {
@@ -735,8 +791,10 @@ __global__ void __launch_bounds__(CAND_THREADS) kgrad_kernel(BoKernelHyper h, co
     }
 }
 // gradX[z][c][t] += scale * il2[z][t] * (H[z][t][c] - x_c[t] * H[z][d][c]),   H = [train_X^T; 1] (Kbar .* g)
+// H may come as `ksplit` partial sums over row ranges of the contraction (split-K, slice stride strideKs): they are
+// added here in slice order, so the result does not depend on scheduling.
 __global__ void kgrad_finalize_kernel(BoKernelHyper h, const double* H, long strideH, long ldn, const double* X, long N,
-                                      double scale, double* gradX) {
+                                      double scale, double* gradX, int ksplit, long strideKs) {
     const int z = blockIdx.y, d = h.d;
     const long idx = blockIdx.x * (long)blockDim.x + threadIdx.x;
     if (idx >= N * d) return;
@@ -744,7 +802,12 @@ __global__ void kgrad_finalize_kernel(BoKernelHyper h, const double* H, long str
     const int t = (int)(idx % d);
     const double il = h.inv_ls[(long)z * d + t];
     const double* Hz = H + (long)z * strideH;
-    gradX[(long)z * N * d + idx] += scale * il * il * (Hz[(long)t * ldn + c] - X[idx] * Hz[(long)d * ldn + c]);
+    double ht = 0.0, hd = 0.0;
+    for (int k = 0; k < ksplit; k++) {
+        ht += Hz[k * strideKs + (long)t * ldn + c];
+        hd += Hz[k * strideKs + (long)d * ldn + c];
+    }
+    gradX[(long)z * N * d + idx] += scale * il * il * (ht - X[idx] * hd);
 }
 size_t kgrad_smem_bytes(int q, int d, int T) {
     const int QD = q * d;
@@ -974,10 +1037,10 @@ int bo_kgrad(const BoKernelHyper& h, const double* Xpts, int npts, const double*
     return BO_OK;
 }
 int bo_kgrad_finalize(const BoKernelHyper& h, const double* H, long strideH, long ldn, const double* X, long N,
-                      double scale, double* gradX, cudaStream_t stream) {
+                      double scale, double* gradX, int ksplit, long strideKs, cudaStream_t stream) {
     if (N <= 0) return BO_OK;
     dim3 grid((unsigned)((N * h.d + 255) / 256), h.M);
-    kgrad_finalize_kernel<<<grid, 256, 0, stream>>>(h, H, strideH, ldn, X, N, scale, gradX);
+    kgrad_finalize_kernel<<<grid, 256, 0, stream>>>(h, H, strideH, ldn, X, N, scale, gradX, ksplit, strideKs);
     BO_LAUNCH_CHECK();
     return BO_OK;
 }

@@ -59,8 +59,9 @@ int bo_colblock_inplace(double* Y, long strideY, const double* T, int rows, int 
                         cudaStream_t stream);
 
 // last step of the GEMM-shaped kernel gradient: gradX[z][c][t] += scale/l_t^2 (H[t][c] - x_c[t] H[d][c])
+// H holds `ksplit` partial sums (slice stride strideKs) that are added in slice order
 int bo_kgrad_finalize(const BoKernelHyper& h, const double* H, long strideH, long ldn, const double* X, long N,
-                      double scale, double* gradX, cudaStream_t stream);
+                      double scale, double* gradX, int ksplit, long strideKs, cudaStream_t stream);
 
 // gradX[z][b][j][:] (+)= scale * sum_i Kbar[z][i][b*q+j] * d k(x_i, x_bj) / d x_bj
 int bo_kgrad(const BoKernelHyper& h, const double* Xpts, int npts, const double* Kbar, long strideK, long ldn,

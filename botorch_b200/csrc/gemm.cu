@@ -222,6 +222,32 @@ __global__ void __launch_bounds__(C::THREADS) dgemm_dmma_kernel(const BoGemm p) 
 
     double* __restrict__ Cz = p.C + (long)z * p.strideC;
     double* __restrict__ CTz = p.CT ? p.CT + (long)z * p.strideCT : nullptr;
+    constexpr bool kStageFits = (size_t)C::BM * (C::BN + 2) <= (size_t)C::STAGES * (C::A_STAGE + C::B_STAGE);
+    if constexpr (kStageFits) if (p.epi != BO_EPI_LINEAR) {
+        // Covariance epilogues (exp per element): stage the tile through shared memory and run ONE rolled copy of the
+        // transcendental code with row-contiguous stores.  The fully unrolled per-fragment form is ~32 inlined exp()
+        // bodies that each warp executes once -- ncu showed the K = d+2 launches stalled on instruction fetch.
+        constexpr int LDC_S = C::BN + 2;
+        __syncthreads();
+        double* Cs = smem;
+#pragma unroll
+        for (int i = 0; i < TM; i++)
+#pragma unroll
+            for (int j = 0; j < TN; j++)
+                *reinterpret_cast<double2*>(Cs + (wm0 + i * 8 + g) * LDC_S + wn0 + j * 8 + 2 * t) =
+                    make_double2(acc[i][j][0], acc[i][j][1]);
+        __syncthreads();
+#pragma unroll 2
+        for (int e = tid; e < C::BM * C::BN; e += C::THREADS) {
+            const int r = e / C::BN, c = e % C::BN;
+            const int row = m0 + r, col = n0 + c;
+            if (row >= p.M || col >= p.N) continue;
+            const double v = epilogue_value(p, z, Cs[r * LDC_S + c], row, col);
+            Cz[(long)row * p.ldc + col] = v;
+            if (CTz) CTz[(long)col * p.ldct + row] = v;
+        }
+        return;
+    }
 #pragma unroll
     for (int i = 0; i < TM; i++) {
         const int row = m0 + wm0 + i * 8 + g;
@@ -260,6 +286,7 @@ using CfgT8 = Cfg<64, 64, 32, 32, 32, 2>;     // BK=32, double buffered, 3 CTAs/
 using CfgT9 = Cfg<64, 64, 32, 32, 32, 3>;     // BK=32, 3 stages, 2 CTAs/SM
 using CfgT10 = Cfg<64, 64, 16, 32, 32, 2>;    // double buffered, 4 CTAs/SM (16 warps)
 using CfgT11 = Cfg<64, 32, 16, 32, 32, 3>;    // 2 warps per CTA, up to 8 CTAs/SM
+using CfgSkinny = Cfg<32, 128, 16, 32, 32, 2>; // M <= 32 (the (d+1)-row gradient contraction): one row tile, wide columns
 
 template <class C>
 int launch_cfg(const BoGemm& g, cudaStream_t stream) {
@@ -329,6 +356,8 @@ int bo_gemm_launch(const BoGemm& g, cudaStream_t stream) {
     // Pick the largest tile that still fills the 148 SMs; small problems trade tile efficiency for occupancy.
     // 64x64 tiles with 4 warps, 3 CTAs per SM: measured best on B200 (tools/gemm_bench.py) --
     // co-resident small CTAs keep the DMMA pipe fed through each other's barriers and shrink the last wave.
+    if (g.M <= 32 && g.N >= 1024 && g.K >= 64 && g.epi == BO_EPI_LINEAR && g.tri == BO_TRI_NONE)
+        return launch_cfg<CfgSkinny>(g, stream);
     if (tiles(64, 64) >= 120 || (g.M >= 48 && g.N >= 48 && tiles(32, 32) > 2048)) return launch_cfg<CfgT10>(g, stream);
     return launch_cfg<CfgSmall>(g, stream);
 }
