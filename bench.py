@@ -281,11 +281,13 @@ def _run_ours(args):
     ms_max = float(t)
 
     # ---- e2e: the user-facing call with HOST buffers (gen_candidates_scipy's f_np_wrapper, gen.py:194-222) -----------
+    from botorch_b200.optim import HostEvaluator
+
+    x_np = X_host.numpy().reshape(-1).copy()  # what SciPy hands to the objective: a plain float64 host array
+    evaluate = HostEvaluator(acqf, X_host.shape, torch.empty(0, dtype=torch.float64, device=dev))
+
     def e2e_step():
-        Xd = X_host.to(dev, non_blocking=True).requires_grad_(True)
-        loss = (-acqf(Xd)).sum()
-        grad = torch.autograd.grad(loss, Xd)[0]
-        return float(loss.detach()), grad.cpu()
+        return evaluate(x_np)  # H2D of x, forward, autograd backward, D2H of (gradient, loss), one host wait
 
     for _ in range(3):
         e2e_step()
@@ -354,7 +356,8 @@ def _run_ours(args):
         "e2e": {
             "value": ws * B * args.steps / e2e_s, "unit": UNIT, "h2d_bytes_per_step": X_host.numel() * 8,
             "d2h_bytes_per_step": X_host.numel() * 8 + 8,
-            "api": "qLogNoisyExpectedImprovement.forward + torch.autograd.grad, pinned host X in, gradient + loss out",
+            "api": "botorch_b200.optim.HostEvaluator (the objective gen_candidates_scipy hands to L-BFGS-B): host x in, "
+                   "qLogNoisyExpectedImprovement.forward + torch.autograd.grad, gradient + loss out",
         },
         "gpu_launches": launches,
         "posterior": {"tflops_fp64": post_flops / (post_ms * 1e-3) / 1e12, "frac_of_fp64_peak":

@@ -18,6 +18,7 @@ from .models import SaasFullyBayesianSingleTaskGP, SingleTaskGP, Standardize  # 
 from .optim import (  # noqa: F401
     gen_batch_initial_conditions,
     gen_candidates_scipy,
+    gen_candidates_torch,
     get_best_candidates,
     initialize_q_batch,
     optimize_acqf,

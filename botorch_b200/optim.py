@@ -180,6 +180,34 @@ class _Timeout(Exception):
         self.x = x
 
 
+class HostEvaluator:
+    """``f_np_wrapper`` of gen_candidates_scipy (gen.py:194-222) with the host round trip trimmed to the minimum:
+    x goes through a pinned staging buffer (asynchronous H2D), the gradient and the loss come back in ONE asynchronous
+    D2H into pinned memory, and the host waits once per evaluation."""
+
+    def __init__(self, acquisition_function, shapeX: torch.Size, like: Tensor) -> None:
+        self.acqf, self.shapeX, self.like = acquisition_function, torch.Size(shapeX), like
+        numel = self.shapeX.numel()
+        pin = like.is_cuda
+        self.x_host = torch.empty(numel, dtype=like.dtype, pin_memory=pin)
+        self.out_host = torch.empty(numel + 1, dtype=like.dtype, pin_memory=pin)
+
+    def __call__(self, x: np.ndarray, with_grad: bool = True):
+        self.x_host.copy_(torch.from_numpy(x))
+        X = self.x_host.to(self.like.device, non_blocking=True).view(self.shapeX)
+        if not with_grad:
+            with torch.no_grad():
+                return float((-self.acqf(X)).sum())
+        X.requires_grad_(True)
+        loss = (-self.acqf(X)).sum()
+        (grad,) = torch.autograd.grad(loss, X)
+        self.out_host.copy_(torch.cat([grad.reshape(-1), loss.detach().reshape(1)]), non_blocking=True)
+        if self.like.is_cuda:
+            torch.cuda.current_stream(self.like.device).synchronize()
+        out = self.out_host.numpy()
+        return float(out[-1]), out[:-1].astype(np.float64, copy=True)
+
+
 def gen_candidates_scipy(
     initial_conditions: Tensor,
     acquisition_function,
@@ -210,21 +238,18 @@ def gen_candidates_scipy(
     def fun(x: np.ndarray):
         if np.isnan(x).any():
             raise RuntimeError(f"{np.isnan(x).sum()} elements of the {x.size} element array `x` are NaN.")
-        X = torch.from_numpy(x).to(initial_conditions).view(shapeX).contiguous()
         if not with_grad:
-            with torch.no_grad():
-                return float((-acquisition_function(X)).sum())
-        X.requires_grad_(True)
-        loss = (-acquisition_function(X)).sum()
-        grad = torch.autograd.grad(loss, X)[0].contiguous().view(-1).cpu().numpy().astype(np.float64)
+            return evaluate(x, with_grad=False)
+        loss, grad = evaluate(x)
         if np.isnan(grad).any():
             msg = (f"{np.isnan(grad).sum()} elements of the {x.size} element gradient array `gradf` are NaN. "
                    "This often indicates numerical issues.")  # fmt: skip
             if initial_conditions.dtype != torch.double:
                 msg += " Consider using `dtype=torch.double`."
             raise RuntimeError(msg)
-        return float(loss.detach()), grad
+        return loss, grad
 
+    evaluate = HostEvaluator(acquisition_function, shapeX, initial_conditions)
     t0 = time.monotonic()
     user_cb = options.get("callback")
 
@@ -259,6 +284,88 @@ def gen_candidates_scipy(
         batch_acquisition = acquisition_function(clamped)
     _flush_warnings(acquisition_function)
     return clamped, batch_acquisition
+
+
+class ExpMAStoppingCriterion:
+    """Stop when the exponentially weighted moving average of the objective stalls (optim/stopping.py:30-127)."""
+
+    def __init__(self, maxiter: int = 10000, minimize: bool = True, n_window: int = 10, eta: float = 1.0,
+                 rel_tol: float = 1e-5) -> None:  # fmt: skip
+        self.maxiter, self.minimize, self.n_window, self.rel_tol = maxiter, minimize, n_window, rel_tol
+        self.iter = 0
+        weights = torch.exp(torch.linspace(-eta, 0, self.n_window))
+        self.weights = weights / weights.sum()
+        self._prev_fvals = None
+
+    def evaluate(self, fvals: Tensor) -> bool:
+        self.iter += 1
+        if self.iter == self.maxiter:
+            return True
+        if self._prev_fvals is None:
+            self._prev_fvals = fvals.unsqueeze(0)
+        else:
+            self._prev_fvals = torch.cat([self._prev_fvals[-self.n_window :], fvals.unsqueeze(0)])
+        if self._prev_fvals.size(0) < self.n_window + 1:
+            return False
+        weights = self.weights.to(fvals)
+        if self._prev_fvals.ndim > 1:
+            weights = weights.unsqueeze(-1)
+        prev_ma = (self._prev_fvals[:-1] * weights).sum(dim=0)
+        ma = (self._prev_fvals[1:] * weights).sum(dim=0)
+        rel_delta = (prev_ma - ma) / prev_ma.abs()
+        if not self.minimize:
+            rel_delta = -rel_delta
+        return bool(torch.max(rel_delta) < self.rel_tol)
+
+
+def gen_candidates_torch(
+    initial_conditions: Tensor,
+    acquisition_function,
+    lower_bounds=None,
+    upper_bounds=None,
+    optimizer=torch.optim.Adam,
+    options: Optional[Dict] = None,
+    callback: Optional[Callable] = None,
+    fixed_features: Optional[Dict[int, Optional[float]]] = None,
+    timeout_sec: Optional[float] = None,
+) -> Tuple[Tensor, Tensor]:
+    """Maximise the summed acquisition value with a ``torch.optim`` optimiser (gen.py:301-424).
+
+    The iterate never leaves the device: per iteration one fused forward, one fused backward and the optimiser's
+    elementwise update -- no SciPy round trip.  Stopping: ``ExpMAStoppingCriterion``.
+    """
+    if fixed_features:
+        raise UnsupportedError("fixed features are outside the fused path")
+    start_time = time.monotonic()
+    options = dict(options or {})
+    clamped_candidates = columnwise_clamp(initial_conditions, lower_bounds, upper_bounds).requires_grad_(True)
+    _optimizer = optimizer(params=[clamped_candidates], lr=options.get("lr", 0.025))
+    stop_keys = ("maxiter", "minimize", "n_window", "eta", "rel_tol")
+    stopping_criterion = ExpMAStoppingCriterion(**{k: v for k, v in options.items() if k in stop_keys})
+    i, stop = 0, False
+    while not stop:
+        i += 1
+        with torch.no_grad():
+            X = columnwise_clamp(clamped_candidates, lower_bounds, upper_bounds).requires_grad_(True)
+        loss = -acquisition_function(X).sum()
+        grad = torch.autograd.grad(loss, X)[0]
+        if callback:
+            callback(i, loss, grad)
+
+        def assign_grad():
+            _optimizer.zero_grad()
+            clamped_candidates.grad = grad
+            return loss
+
+        _optimizer.step(assign_grad)
+        stop = stopping_criterion.evaluate(fvals=loss.detach())
+        if timeout_sec is not None and time.monotonic() - start_time > timeout_sec:
+            stop = True
+    clamped_candidates = columnwise_clamp(clamped_candidates.detach(), lower_bounds, upper_bounds)
+    with torch.no_grad():
+        batch_acquisition = acquisition_function(clamped_candidates)
+    _flush_warnings(acquisition_function)
+    return clamped_candidates, batch_acquisition
 
 
 def get_best_candidates(batch_candidates: Tensor, batch_values: Tensor) -> Tensor:

@@ -212,3 +212,34 @@ def test_shard_range_partitions_exactly():
     c = torch.arange(4, dtype=torch.float64).reshape(4, 1, 1)
     cand, val, idx = bdist.gather_best(v, c, index_offset=10)
     assert idx == 11 and float(val) == 5.0 and float(cand) == 1.0  # first occurrence wins
+
+
+def test_expma_stopping_criterion():
+    """optim/stopping.py:83-127 / test/optim/test_stopping.py: stops at maxiter, not before the window is full, and
+    once the moving average of a flat objective stops decreasing."""
+    from botorch_b200.optim import ExpMAStoppingCriterion
+
+    sc = ExpMAStoppingCriterion(maxiter=2)
+    assert not sc.evaluate(torch.tensor(1.0)) and sc.evaluate(torch.tensor(1.0))
+    sc = ExpMAStoppingCriterion(n_window=4, rel_tol=0.0375)
+    stops = [sc.evaluate(torch.tensor(1.0 - 0.01 * i, dtype=torch.float64)) for i in range(6)]
+    assert stops[:4] == [False] * 4 and stops[4]  # relative decrease 0.01 per step < rel_tol
+    sc = ExpMAStoppingCriterion(n_window=3, rel_tol=1e-6)
+    vals = torch.tensor([[10.0, 5.0], [5.0, 4.0], [2.5, 3.9], [1.2, 3.9], [0.6, 3.9]], dtype=torch.float64)
+    assert not any(sc.evaluate(v) for v in vals)  # one element still improving => keep going
+
+
+def test_gen_candidates_torch_on_a_quadratic_and_host_evaluator_cpu():
+    """The torch-optimiser loop and the SciPy host bridge are generic over the acquisition callable: maximise
+    -(x - 0.3)^2 inside [0, 1] from several starts."""
+    from botorch_b200.optim import HostEvaluator, gen_candidates_torch
+
+    acq = lambda X: -((X - 0.3) ** 2).sum(dim=(-1, -2))
+    ics = torch.rand(5, 2, 3, dtype=torch.float64, generator=torch.Generator().manual_seed(0))
+    cands, vals = gen_candidates_torch(ics, acq, lower_bounds=0.0, upper_bounds=1.0, options={"maxiter": 400, "lr": 0.05})
+    assert cands.shape == ics.shape and vals.shape == (5,)
+    assert float((cands - 0.3).abs().max()) < 2e-2 and float(vals.min()) > -1e-2
+    ev = HostEvaluator(acq, ics.shape, ics)
+    loss, grad = ev(ics.reshape(-1).numpy())
+    assert abs(loss - float(-acq(ics).sum())) < 1e-12
+    assert torch.allclose(torch.from_numpy(grad).view_as(ics), 2 * (ics - 0.3))
