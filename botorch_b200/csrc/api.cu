@@ -564,9 +564,13 @@ int bo_qlognei_bwd(bo_ctx* ctx, const bo_gp* gp, const bo_nei* nei, int B, int q
         else { a.F = w.W1; a.strideF = w.regionStride; }  // samples live in rows 0..S-1 of the stacked forward output
         a.Vbar_mu = w.W1 + Sd * w.ldn;            // row Sd <- y_std * mubar: rows 0..Sd become [dF; y_std mubar]
         a.strideVbar = w.regionStride;
+        // 2r. Ubar = -2 U Sbar, in place on rows S1p.. of the same region: inside the reverse kernel for q <= 8 (the
+        //     q x q block lives in registers there), as a separate pass otherwise
+        const bool fuse_u = q <= 8;
+        if (fuse_u) { a.Uinplace = w.W1 + S1p * w.ldn; a.strideU = w.regionStride; a.u_coef = -2.0; a.n_b = (int)n; }
         BO_TRY(bo_cand_bwd(a, st));
-        // 2r. Ubar = -2 U Sbar, in place on rows S1p.. of the same region
-        BO_TRY(bo_colblock_inplace(w.W1 + S1p * w.ldn, w.regionStride, w.Sbar, (int)n, B, q, (int)M, w.ldn, -2.0, st));
+        if (!fuse_u)
+            BO_TRY(bo_colblock_inplace(w.W1 + S1p * w.ldn, w.regionStride, w.Sbar, (int)n, B, q, (int)M, w.ldn, -2.0, st));
         // 3r. G = ([Z_b Q; alpha^T]^T [dF; y_std mubar] + L_W Ubar) .* g(r) in ONE launch over the stacked operand;
         //     g = K for RBF, the stored derivative factor for Matern                                          (W2)
         BoGemm g{};

@@ -687,6 +687,46 @@ __global__ void __launch_bounds__(CAND_THREADS, (QT <= 8 ? 4 : 1)) cand_bwd_kern
         }
         gX[idx] = acc;
     }
+
+    // 5. combined-root path: Ubar = u_coef * U Sbar for this t-batch's q columns, in place over U (one row per thread and
+    //    iteration, 16-byte accesses); saves the separate pass and overlaps with the other CTAs' reduction phases
+    if constexpr (QT <= 8) if (a.Uinplace != nullptr) {
+        double* Ub = a.Uinplace + (long)z * a.strideU + c0;
+        const bool vec = (q == QT) && ((QT & 1) == 0) && ((c0 & 1) == 0) && ((a.ldn & 1) == 0);
+        __syncthreads();  // Y (the symmetric Sbar) is read below as a broadcast operand
+#pragma unroll 2
+        for (int r = tid; r < a.n_b; r += T) {
+            double* row = Ub + (long)r * a.ldn;
+            double v[QT], w[QT];
+            if (vec) {
+#pragma unroll
+                for (int j = 0; j < QT; j += 2) {
+                    const double2 t2 = *reinterpret_cast<const double2*>(row + j);
+                    v[j] = t2.x;
+                    v[j + 1] = t2.y;
+                }
+            } else {
+#pragma unroll
+                for (int j = 0; j < QT; j++) v[j] = (j < q) ? row[j] : 0.0;
+            }
+#pragma unroll
+            for (int j = 0; j < QT; j++) {
+                double s_ = 0.0;
+#pragma unroll
+                for (int k = 0; k < QT; k++)
+                    if (k < q && j < q) s_ += v[k] * Y[k * q + j];
+                w[j] = a.u_coef * s_;
+            }
+            if (vec) {
+#pragma unroll
+                for (int j = 0; j < QT; j += 2) *reinterpret_cast<double2*>(row + j) = make_double2(w[j], w[j + 1]);
+            } else {
+#pragma unroll
+                for (int j = 0; j < QT; j++)
+                    if (j < q) row[j] = w[j];
+            }
+        }
+    }
 }
 size_t cand_bwd_smem_bytes(int q, int QT) {
     return sizeof(double) * (size_t)(4 * q * q + q + (CAND_THREADS / 32) * (QT + QT * (QT + 1) / 2));

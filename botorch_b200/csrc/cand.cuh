@@ -45,6 +45,8 @@ struct BoCandArgs {
     double* Sbar;                      // [M][B][q*q]    adjoint of the q x q Schur block
     double* Vbar_mu; long strideVbar;  // row n of the adjoint of V (receives y_std * dmu)
     double* gradX;                     // [M][B][q][d]
+    double* Uinplace; long strideU;    // optional (QT <= 8 kernels): [n_b x ldn] block that receives u_coef * U Sbar in place
+    double u_coef;
 };
 
 int bo_cand_fwd(const BoCandArgs& a, cudaStream_t stream);
