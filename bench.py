@@ -30,9 +30,9 @@ sys.path.insert(0, ROOT)
 METRIC = "qLogNEI fwd+bwd candidate evals/s"
 UNIT = "candidate_evals/s"
 # dram__bytes_read.sum + dram__bytes_write.sum of the four dgemm_dmma_kernel launches of one step, averaged per launch,
-# from the `ncu --set full` capture of this command at the default workload (profiles/r01_ncu_full_step_v3.csv:
-# 14.9 + 151.3 + 328.1 + 66.5 MB).  Algorithmic operand bytes of the same four launches: ~550 MB, i.e. no re-reads.
-NCU_GEMM_TRAFFIC_BYTES_PER_LAUNCH = {("C3", 512): 140.2e6}
+# from the `ncu --set full` capture of this command at the default workload (profiles/r01_ncu_full_step_v4.csv:
+# 10.0 + 154.2 + 334.0 + 67.1 MB).  Algorithmic operand bytes of the same four launches: ~550 MB, i.e. no re-reads.
+NCU_GEMM_TRAFFIC_BYTES_PER_LAUNCH = {("C3", 512): 141.3e6}
 FP64_DMMA_PEAK_TFLOPS = 37.07  # measured on this pool's B200 with tools/fp64_peaks.cu (profiles/r01_fp64_peaks.txt)
 
 
@@ -346,7 +346,7 @@ def _run_ours(args):
         "roofline": {
             "bound": "tensor", "achieved": gemm_tflops, "peak": FP64_DMMA_PEAK_TFLOPS, "unit": "TFLOP/s",
             "frac": gemm_tflops / FP64_DMMA_PEAK_TFLOPS, "traffic": NCU_GEMM_TRAFFIC_BYTES_PER_LAUNCH.get((args.config, B)), "kernel": "dgemm_dmma_kernel",
-            "traffic_note": "bytes per launch (mean over the step's GEMM launches) from profiles/r01_ncu_full_step_v3.csv; "
+            "traffic_note": "bytes per launch (mean over the step's GEMM launches) from profiles/r01_ncu_full_step_v4.csv; "
                             "null for workloads without a committed capture",
             "peak_source": "FP64 DMMA peak measured on this pool (tools/fp64_peaks.cu, profiles/r01_fp64_peaks.txt); "
                            "MEASURED_PEAKS.json holds no FP64 figure",
