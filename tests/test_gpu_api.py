@@ -234,7 +234,7 @@ def test_thompson_sampling_marginal(cuda):
     assert rel_err(mean[0], m_ref.squeeze(-1)) < RTOL
     assert rel_err(var[0], c_ref.reshape(-1), scale=float(ogp.y_std) ** 2) < RTOL
     g = torch.Generator(device=cuda).manual_seed(0)
-    picks = ts(Xc.to(cuda), num_samples=4, generator=g)
+    picks = ts(Xc.to(cuda), num_samples=4, generator=g, joint=False)
     assert picks.shape == (4, p.d)
     assert len({tuple(r.tolist()) for r in picks.cpu()}) == 4  # replacement=False
     # a draw with zero noise is the posterior-mean maximiser
@@ -245,6 +245,36 @@ def test_thompson_sampling_marginal(cuda):
     _lib.check(_lib.lib().bo_ts_argmax(_lib.ctx(cuda), 1, 2000, mean.data_ptr(), var.data_ptr(), None,
                                        val.data_ptr(), idx.data_ptr(), _lib.stream_ptr(cuda)))  # fmt: skip
     assert int(idx) == int(torch.argmax(m_ref.squeeze(-1)))
+
+
+def test_thompson_sampling_joint(cuda):
+    """generation/sampling.py:95-155: joint posterior draws over the whole candidate set (N x N Cholesky on the GPU),
+    then the reference's maximize_samples index logic with and without replacement."""
+    p = make_problem("C5", n=200)
+    ogp = oracle_gp(p)
+    model = _model(p, cuda)
+    N = 700
+    Xc = qmc.sobol_box(torch.stack([torch.zeros(p.d), torch.ones(p.d)]).double(), N, 1, seed=2).squeeze(1).to(cuda)
+    ts = bb.MaxPosteriorSampling(model, replacement=True)
+    torch.manual_seed(11)
+    picks = ts(Xc, num_samples=5)
+    torch.manual_seed(11)
+    samples = model.posterior(Xc).rsample(sample_shape=torch.Size([5]))  # 5 x N x 1, same base draws
+    assert picks.shape == (5, p.d)
+    assert torch.equal(picks, Xc[samples.squeeze(-1).argmax(dim=-1)])
+    # the draws are joint: their empirical covariance between two nearby candidates follows the posterior covariance
+    torch.manual_seed(3)
+    big = model.posterior(Xc[:2]).rsample(sample_shape=torch.Size([4096])).squeeze(-1)
+    _, c_ref = ogp.posterior_direct(Xc[:2].cpu())
+    emp = torch.cov(big.T).cpu()
+    assert float((emp - c_ref).abs().max()) < 0.15 * float(c_ref.abs().max())
+    ts_nr = bb.MaxPosteriorSampling(model, replacement=False)
+    picks = ts_nr(Xc, num_samples=6)
+    assert picks.shape == (6, p.d) and len({tuple(r.tolist()) for r in picks.cpu()}) == 6
+    from botorch_b200.generation import _flip_sub_unique
+
+    x = torch.tensor([1, 6, 4, 3, 6, 3])  # generation/utils.py:62-66
+    assert _flip_sub_unique(x, 3).tolist() == [3, 6, 4] and _flip_sub_unique(x, 10).tolist() == [3, 6, 4, 1]
 
 
 def test_saas_posterior_mixture(cuda):
