@@ -37,8 +37,8 @@ __device__ __forceinline__ double kern_dfactor(int kernel_id, double r2, double 
 // reductions of safe_math.py
 // ---------------------------------------------------------------------------------------------
 // log(tau*(softplus(u) + 0.1/(1+u^2))), u = z/tau   (torch softplus: identity above threshold 20)
-__device__ __forceinline__ double log_fatplus(double z, double tau) {
-    const double u = z / tau;
+__device__ __forceinline__ double log_fatplus(double z, double tau, double inv_tau) {
+    const double u = z * inv_tau;
     // exp(u) underflows to exactly 0 below -746: skipping exp/log1p there is bit-identical and removes two of the three
     // transcendentals for the bulk of the samples (tau = 1e-6 puts |u| in the 1e4..1e6 range)
     if (u < -746.0) return log(0.1 * tau) - log(fma(u, u, 1.0));  // softplus == 0: log(tau * 0.1 / (1 + u^2)), no division
@@ -46,9 +46,9 @@ __device__ __forceinline__ double log_fatplus(double z, double tau) {
     return log(tau * (sp + 0.1 * (1.0 / (1.0 + u * u))));
 }
 // d log_fatplus / dz
-__device__ __forceinline__ double dlog_fatplus(double z, double tau) {
-    const double u = z / tau;
-    if (u < -746.0) return -2.0 * u / (fma(u, u, 1.0) * tau);  // softplus == sigmoid == 0: d/dz log(0.1 / (1 + u^2))
+__device__ __forceinline__ double dlog_fatplus(double z, double tau, double inv_tau) {
+    const double u = z * inv_tau;
+    if (u < -746.0) return -2.0 * u * inv_tau / fma(u, u, 1.0);  // softplus == sigmoid == 0: d/dz log(0.1 / (1 + u^2))
     double sp, sig;
     if (u > 20.0) { sp = u; sig = 1.0; }
     else { const double e = exp(u); sp = log1p(e); sig = e / (e + 1.0); }
@@ -61,6 +61,8 @@ __device__ __forceinline__ double pareto2(double u) { return 2.0 / (2.0 + 2.0 * 
 
 // fatmax over x[0..q) (alpha = 2) with the infinity handling of _inf_max_helper.  QT >= q is a compile-time bound:
 // every loop is fully unrolled with a (j < q) guard so that the per-sample arrays stay in registers.
+// The temperature enters as a multiplication by 1/tau (one rounding away from the reference's division: 1e-16 relative
+// on u, far inside the 1e-9 parity bar) -- an FP64 division costs as much as the rest of the per-element work.
 template <int QT>
 __device__ __forceinline__ double fatmax_q(const double (&x)[QT], int q, double tau) {
     double M = x[0];
@@ -74,47 +76,55 @@ __device__ __forceinline__ double fatmax_q(const double (&x)[QT], int q, double 
             if (j < q && x[j] == M) s += x[j];
         return s;
     }
+    const double inv_tau = 1.0 / tau;
     double sum = 0.0;
 #pragma unroll
     for (int j = 0; j < QT; j++)
-        if (j < q) sum += pareto2(-(x[j] - M) / tau);
+        if (j < q) sum += pareto2((M - x[j]) * inv_tau);
     return M + tau * log(sum);
 }
-// gradient of fatmax w.r.t. x (g[0..q))
+// fatmax value (returned) and its gradient w.r.t. x (g[0..q)) in one pass over the q Pareto terms
 template <int QT>
-__device__ __forceinline__ void fatmax_q_grad(const double (&x)[QT], int q, double tau, double (&g)[QT]) {
+__device__ __forceinline__ double fatmax_q_grad(const double (&x)[QT], int q, double tau, double (&g)[QT]) {
     double M = x[0];
 #pragma unroll
     for (int j = 1; j < QT; j++)
         if (j < q) M = fmax(M, x[j]);
     if (isinf(M)) {
+        double s = 0.0;
 #pragma unroll
-        for (int j = 0; j < QT; j++) g[j] = (j < q && x[j] == M) ? 1.0 : 0.0;
-        return;
+        for (int j = 0; j < QT; j++) {
+            g[j] = (j < q && x[j] == M) ? 1.0 : 0.0;
+            if (j < q && x[j] == M) s += x[j];
+        }
+        return s;
     }
+    const double inv_tau = 1.0 / tau;
     double sum = 0.0;
     int nties = 0;
-#pragma unroll
-    for (int j = 0; j < QT; j++)
-        if (j < q) {
-            sum += pareto2(-(x[j] - M) / tau);
-            nties += (x[j] == M);
-        }
-    double wsum = 0.0;
 #pragma unroll
     for (int j = 0; j < QT; j++) {
         g[j] = 0.0;
         if (j < q) {
-            const double u = -(x[j] - M) / tau;
+            const double u = (M - x[j]) * inv_tau;
             const double p = pareto2(u);
-            g[j] = isinf(u) ? 0.0 : p * p * (1.0 + u) / sum;
-            wsum += g[j];
+            sum += p;
+            nties += (x[j] == M);
+            g[j] = isinf(u) ? 0.0 : p * p * (1.0 + u);
         }
+    }
+    const double inv_sum = 1.0 / sum;
+    double wsum = 0.0;
+#pragma unroll
+    for (int j = 0; j < QT; j++) {
+        g[j] *= inv_sum;
+        wsum += g[j];
     }
     const double rest = (1.0 - wsum) / nties;  // amax subgradient, split evenly among ties (torch.amax)
 #pragma unroll
     for (int j = 0; j < QT; j++)
         if (j < q && x[j] == M) g[j] += rest;
+    return M + tau * log(sum);
 }
 
 // Sum P per-lane values over the 32 lanes of a warp with ~P shuffles instead of 5 P: at every butterfly step each lane
@@ -463,6 +473,7 @@ __global__ void __launch_bounds__(CAND_THREADS, (QT <= 8 ? 4 : 1)) cand_fwd_kern
     int bad = 0;
     double local_max = -INFINITY;
     const bool plain = (a.reduction == BO_REDUCE_PLAIN);
+    const double inv_tau_relu = 1.0 / a.tau_relu;
     for (int s = tid; s < a.S; s += T) {
         double li[QT], zq[QT];
         const double bf = a.best_f[(long)z * a.Sp + s];
@@ -478,7 +489,7 @@ __global__ void __launch_bounds__(CAND_THREADS, (QT <= 8 ? 4 : 1)) cand_fwd_kern
                     if (k <= j) v += c.Lq[j * q + k] * zq[k];
                 F[(long)s * a.ldn + c0 + j] = v;
                 if (!isfinite(v)) bad = 1;
-                li[j] = plain ? fmax(v - bf, 0.0) : log_fatplus(v - bf, a.tau_relu);
+                li[j] = plain ? fmax(v - bf, 0.0) : log_fatplus(v - bf, a.tau_relu, inv_tau_relu);
             }
         }
         double m;
@@ -550,6 +561,7 @@ __global__ void __launch_bounds__(CAND_THREADS, (QT <= 8 ? 4 : 1)) cand_bwd_kern
     double* red = mubar + q;  // (T/32) x (QT + PT)
     double am[QT], al[PT];
     const bool plain = (a.reduction == BO_REDUCE_PLAIN);
+    const double inv_tau_relu = 1.0 / a.tau_relu;
 #pragma unroll
     for (int j = 0; j < QT; j++) am[j] = 0.0;
 #pragma unroll
@@ -562,7 +574,7 @@ __global__ void __launch_bounds__(CAND_THREADS, (QT <= 8 ? 4 : 1)) cand_bwd_kern
             f[j] = 0.0; li[j] = 0.0; zq[j] = 0.0;
             if (j < q) {
                 f[j] = F[(long)s * a.ldn + c0 + j];
-                li[j] = plain ? fmax(f[j] - bf, 0.0) : log_fatplus(f[j] - bf, a.tau_relu);
+                li[j] = plain ? fmax(f[j] - bf, 0.0) : log_fatplus(f[j] - bf, a.tau_relu, inv_tau_relu);
                 zq[j] = a.Zq[(long)s * q + j];
             }
         }
@@ -578,10 +590,9 @@ __global__ void __launch_bounds__(CAND_THREADS, (QT <= 8 ? 4 : 1)) cand_bwd_kern
                 if (j < q && li[j] == m) ties++;
             w = 1.0 / (double)a.S;
         } else {
-            m = fatmax_q<QT>(li, q, a.tau_max);
+            m = fatmax_q_grad<QT>(li, q, a.tau_max, gm);
             // logmeanexp over samples: softmax weight; +-inf maximum -> unit gradient on the infinite entries
             w = isinf(lse) ? ((m == lse) ? 1.0 : 0.0) : exp(m - lse);
-            fatmax_q_grad<QT>(li, q, a.tau_max, gm);
         }
         int p = 0;
 #pragma unroll
@@ -591,7 +602,7 @@ __global__ void __launch_bounds__(CAND_THREADS, (QT <= 8 ? 4 : 1)) cand_bwd_kern
                 if (plain) {
                     df = (li[j] == m && f[j] - bf >= 0.0) ? g * w / (double)ties : 0.0;
                 } else {
-                    const double dli = isinf(li[j]) ? 0.0 : dlog_fatplus(f[j] - bf, a.tau_relu);
+                    const double dli = isinf(li[j]) ? 0.0 : dlog_fatplus(f[j] - bf, a.tau_relu, inv_tau_relu);
                     df = g * w * gm[j] * dli;
                 }
                 F[(long)s * a.ldn + c0 + j] = df;
@@ -676,16 +687,19 @@ __global__ void __launch_bounds__(CAND_THREADS, (QT <= 8 ? 4 : 1)) cand_bwd_kern
     const double* il = a.h.inv_ls + (long)z * a.h.d;
     const int d = a.h.d;
     double* gX = a.gradX + o * q * d;
+    // pair coefficients once (q^2 distance + transcendental evaluations), then the q*d gradient entries are plain sums
+    for (int idx = tid; idx < q * q; idx += T) {
+        const int j = idx / q, k = idx % q;
+        Pm[idx] = (j == k) ? 0.0
+                           : -2.0 * ys2 * Y[idx] * kern_dfactor(a.h.kernel_id, pair_r2(a.X, d, il, c0 + j, c0 + k), os);
+    }
+    __syncthreads();
     for (int idx = tid; idx < q * d; idx += T) {
         const int j = idx / d, t = idx % d;
+        const double xj = a.X[(long)(c0 + j) * d + t];
         double acc = 0.0;
-        for (int k = 0; k < q; k++) {
-            if (k == j) continue;
-            const double gf = kern_dfactor(a.h.kernel_id, pair_r2(a.X, d, il, c0 + j, c0 + k), os);
-            acc += 2.0 * ys2 * Y[j * q + k] * (-gf) * (a.X[(long)(c0 + j) * d + t] - a.X[(long)(c0 + k) * d + t]) *
-                   il[t] * il[t];
-        }
-        gX[idx] = acc;
+        for (int k = 0; k < q; k++) acc += Pm[j * q + k] * (xj - a.X[(long)(c0 + k) * d + t]);
+        gX[idx] = acc * il[t] * il[t];
     }
 
     // 5. combined-root path: Ubar = u_coef * U Sbar for this t-batch's q columns, in place over U (one row per thread and
