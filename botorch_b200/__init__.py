@@ -17,6 +17,7 @@ from .generation import MaxPosteriorSampling  # noqa: F401
 from .models import SaasFullyBayesianSingleTaskGP, SingleTaskGP, Standardize  # noqa: F401
 from .optim import (  # noqa: F401
     gen_batch_initial_conditions,
+    gen_candidates_lbfgs,
     gen_candidates_scipy,
     gen_candidates_torch,
     get_best_candidates,

@@ -67,6 +67,13 @@ class BoNEI(C.Structure):
     ]
 
 
+class BoLBFGS(C.Structure):
+    _fields_ = [("B", C.c_int32), ("D", C.c_int32), ("m", C.c_int32)] + [
+        (name, C.c_void_p)
+        for name in ("x g f x_prev g_prev S Y rho hist_count hist_head p alpha x_trial state lower upper n_iter").split()
+    ]
+
+
 class BoError(RuntimeError):
     pass
 
@@ -105,6 +112,12 @@ def _declare(lib: C.CDLL) -> None:
     lib.bo_ei_setup_workspace_bytes.restype = sz
     lib.bo_ei_setup_workspace_bytes.argtypes = [gp, nei]
     lib.bo_ei_setup.argtypes = [vp, gp, nei, vp, sz, vp, vp]
+    lb = C.POINTER(BoLBFGS)
+    lib.bo_lbfgs_init.argtypes = [vp, lb, vp, vp, vp]
+    lib.bo_lbfgs_propose.argtypes = [vp, lb, vp]
+    lib.bo_lbfgs_accept.argtypes = [vp, lb, vp, vp, dbl, dbl, dbl, i32, vp]
+    for name in ("bo_lbfgs_init", "bo_lbfgs_propose", "bo_lbfgs_accept"):
+        getattr(lib, name).restype = i32
     lib.bo_qlognei_workspace_bytes.restype = sz
     lib.bo_qlognei_workspace_bytes.argtypes = [gp, nei, i32, i32, i32]
     lib.bo_qlognei_fwd.argtypes = [vp, gp, nei, i32, i32, vp, vp, dbl, dbl, vp, vp, vp, sz, i32, vp]

@@ -224,8 +224,9 @@ class _FusedImprovementBase(AcquisitionFunction):
         if self._info_host is None:
             self._info_host = torch.empty(2, dtype=torch.int32).pin_memory()
             self._info_event = torch.cuda.Event()
-        lo, hi = torch.aminmax(info)
-        self._info_host.copy_(torch.stack([lo, hi]).to(torch.int32), non_blocking=True)
+        if info.numel() != 2 or info.dim() != 1:  # eager path: per-(model, t-batch) flags; graphs hand over (min, max)
+            info = torch.stack(torch.aminmax(info)).to(torch.int32)
+        self._info_host.copy_(info, non_blocking=True)
         self._info_event.record()
         self._info_pending = True
 

@@ -356,6 +356,8 @@ class GraphedEval:
         self.fwd = torch.cuda.CUDAGraph()
         with torch.cuda.graph(self.fwd):
             self.acq, self.info, self.work = nei.forward(*args, with_grad=with_grad)
+            # (min, max) of the failure flags, reduced inside the graph: the host reads two ints per call
+            self.info_minmax = torch.stack(torch.aminmax(self.info)).to(torch.int32)
         self.bwd = None
         if with_grad:
             self.grad_in = torch.zeros(nei.gp.M, B, dtype=torch.float64, device=dev)
@@ -367,7 +369,7 @@ class GraphedEval:
         self.X.copy_(X)
         self.fwd.replay()
         self.busy = self.with_grad
-        return self.acq.clone(), self.info.clone()
+        return self.acq.clone(), self.info_minmax.detach()  # alias of a static buffer: consumed (copied to the host) before the next replay
 
     def run_backward(self, grad_acq: Tensor) -> Tensor:
         self.grad_in.copy_(grad_acq)

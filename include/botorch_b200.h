@@ -204,6 +204,41 @@ int bo_potrf(bo_ctx* ctx, int n, int batch, double* A, long lda, long strideA, d
              void* work, size_t work_bytes, int32_t* info, void* stream);
 size_t bo_potrf_workspace_bytes(int n, int batch);
 
+/* ---- device-resident multi-start optimiser ---------------------------------------
+ * Replaces the SciPy L-BFGS-B round trip of gen_candidates_scipy (generation/gen.py:46-298) for the fused path: the
+ * objective is a sum over restarts (gen.py:209), so every restart is an independent box-constrained problem of
+ * D = q*d variables with its own limited-memory model.  State lives in caller-owned device buffers; a round is
+ * bo_lbfgs_propose -> (caller evaluates f = -acq and g = -d acq / dX at x_trial) -> bo_lbfgs_accept; no host sync.
+ * f is MINIMISED. */
+typedef struct bo_lbfgs {
+    int32_t B, D, m;           /* restarts, variables per restart, history length (<= 64) */
+    double* x;                 /* [B x D] current iterate (inside the bounds) */
+    double* g;                 /* [B x D] its gradient */
+    double* f;                 /* [B]     its objective */
+    double* x_prev;            /* [B x D] previous iterate / gradient (curvature pair) */
+    double* g_prev;
+    double* S;                 /* [B x m x D] steps */
+    double* Y;                 /* [B x m x D] gradient differences */
+    double* rho;               /* [B x m] */
+    int32_t* hist_count;       /* [B] */
+    int32_t* hist_head;        /* [B] */
+    double* p;                 /* [B x D] search direction (zero on the active set) */
+    double* alpha;             /* [B] step length of the next trial */
+    double* x_trial;           /* [B x D] out: clip(x + alpha p) */
+    int32_t* state;            /* [B] 0 new direction, 1 backtrack, 2 stopped, 3 restart from steepest descent */
+    const double* lower;       /* [D] */
+    const double* upper;       /* [D] */
+    int32_t* n_iter;           /* [B] accepted steps */
+} bo_lbfgs;
+
+/* x must be set by the caller; f0 [B], g0 [B x D] are the objective and gradient at x */
+int bo_lbfgs_init(bo_ctx* ctx, const bo_lbfgs* s, const double* f0, const double* g0, void* stream);
+int bo_lbfgs_propose(bo_ctx* ctx, const bo_lbfgs* s, void* stream);
+/* projected Armijo test f_trial <= f + c1 g.(x_trial - x); stops a restart when the projected gradient (sup norm) is
+ * <= pgtol, the decrease is <= ftol * max(|f|, |f_trial|, 1), or maxiter accepted steps were taken */
+int bo_lbfgs_accept(bo_ctx* ctx, const bo_lbfgs* s, const double* f_trial, const double* g_trial, double c1, double ftol,
+                    double pgtol, int maxiter, void* stream);
+
 #ifdef __cplusplus
 }
 #endif
