@@ -486,14 +486,37 @@ def optimize_acqf(
 ) -> Tuple[Tensor, Tensor]:
     """Multi-start maximisation of ``acq_function`` over the box ``bounds`` (optimize.py:397-543).
 
-    Joint (non-sequential) q-batch optimisation: raw samples -> initial conditions -> ``batch_limit`` chunks of
-    restarts, each optimised jointly by ``gen_candidates`` (default L-BFGS-B), one retry on an
-    ``OptimizationWarning``, best restart returned.
+Joint q-batch optimisation: raw samples -> initial conditions -> ``batch_limit`` chunks of restarts, each optimised
+    jointly by ``gen_candidates`` (default L-BFGS-B), one retry on an ``OptimizationWarning``, best restart returned.
+    ``sequential=True`` picks the q points greedily one at a time (optimize.py:202-243).
     """
     if inequality_constraints or equality_constraints or nonlinear_inequality_constraints or fixed_features:
         raise UnsupportedError("constraints / fixed features are outside the fused path (SURVEY.md section 8)")
     if sequential and q > 1:
-        raise UnsupportedError("sequential greedy optimisation is a 'next' row (SURVEY.md 8f N2); use sequential=False")
+        # _optimize_acqf_sequential_q (optimize.py:202-243): q greedy single-point optimisations, each conditioned on the
+        # points chosen so far through X_pending (they enter the fused kernels as extra columns of the q-batch)
+        if not return_best_only:
+            raise NotImplementedError("`return_best_only=False` only supported for joint optimization.")
+        if batch_initial_conditions is not None:
+            raise UnsupportedError("`batch_initial_conditions` is not supported for sequential optimization.")
+        candidate_list, acq_value_list = [], []
+        base_X_pending = acq_function.X_pending
+        step_timeout = timeout_sec / q if timeout_sec is not None else None
+        candidates = None
+        for _ in range(q):
+            candidate, acq_value = optimize_acqf(
+                acq_function, bounds, q=1, num_restarts=num_restarts, raw_samples=raw_samples, options=options,
+                post_processing_func=post_processing_func, return_best_only=True, gen_candidates=gen_candidates,
+                sequential=False, ic_generator=ic_generator, timeout_sec=step_timeout,
+                retry_on_optimization_warning=retry_on_optimization_warning, **ic_gen_kwargs)  # fmt: skip
+            candidate_list.append(candidate)
+            acq_value_list.append(acq_value)
+            candidates = torch.cat(candidate_list, dim=-2)
+            acq_function.set_X_pending(
+                torch.cat([base_X_pending, candidates], dim=-2) if base_X_pending is not None else candidates
+            )
+        acq_function.set_X_pending(base_X_pending)
+        return candidates, torch.stack(acq_value_list)
     if not (bounds.ndim == 2 and bounds.shape[0] == 2):
         raise ValueError(f"bounds should be a `2 x d` tensor, current shape: {list(bounds.shape)}.")
     if batch_initial_conditions is None and raw_samples is None and ic_generator is None:

@@ -209,6 +209,24 @@ def test_gen_candidates_torch_keeps_the_iterate_on_the_device(cuda):
     assert best.shape == (2, p.d) and bool(torch.isfinite(val))
 
 
+def test_sequential_greedy_optimize_acqf(cuda):
+    """optimize.py:202-243: q greedy single-point optimisations conditioned through X_pending; the i-th reported value is
+    the acquisition value of candidate i given the i-1 earlier ones, and X_pending is restored afterwards."""
+    p = make_problem("C2", n=50)
+    oacq = oracle_acq(p, oracle_gp(p))
+    model = _model(p, cuda)
+    acqf = _acqf(p, model, cuda)
+    bounds = torch.stack([torch.zeros(p.d), torch.ones(p.d)]).double().to(cuda)
+    cands, vals = bb.optimize_acqf(acqf, bounds, q=3, num_restarts=4, raw_samples=64, sequential=True,
+                                   options={"maxiter": 20, "seed": 0})  # fmt: skip
+    assert cands.shape == (3, p.d) and vals.shape == (3,) and acqf.X_pending is None
+    for i in range(3):
+        ref = oacq.forward(cands[: i + 1].cpu().unsqueeze(0)[:, [i] + list(range(i))])  # new point first, pending after
+        assert rel_err(vals[i], ref[0], scale=0.0) < 1e-8
+    with pytest.raises(NotImplementedError):
+        bb.optimize_acqf(acqf, bounds, q=2, num_restarts=2, raw_samples=8, sequential=True, return_best_only=False)
+
+
 def test_raw_sample_argmax_index_matches_oracle(cuda):
     p = make_problem("C2")
     oacq = oracle_acq(p, oracle_gp(p))
