@@ -139,6 +139,98 @@ def gather_best(values: Tensor, candidates: Tensor, index_offset: int) -> Tuple[
     return cands[win].to(candidates.dtype), vals_t[win].to(values.dtype), int(idxs_t[win])
 
 
+TS_NOISE_BLOCK = 16384  # candidates per base-sample block: the noise of candidate i depends on (seed, draw, i // block) only
+
+
+def ts_base_samples(lo: int, hi: int, draw: int, seed: int, device) -> Tensor:
+    """Standard-normal base samples of the candidates [lo, hi) for one Thompson draw, identical for every sharding:
+    block k of ``TS_NOISE_BLOCK`` candidates is generated from its own counter-derived seed."""
+    out = torch.empty(hi - lo, dtype=torch.float64, device=device)
+    gen = torch.Generator(device=device)
+    k0, k1 = lo // TS_NOISE_BLOCK, (hi - 1) // TS_NOISE_BLOCK
+    for k in range(k0, k1 + 1):
+        gen.manual_seed((int(seed) * 1_000_003 + draw) * 1_000_003 + k)
+        z = torch.randn(TS_NOISE_BLOCK, dtype=torch.float64, device=device, generator=gen)
+        a, b = max(lo, k * TS_NOISE_BLOCK), min(hi, (k + 1) * TS_NOISE_BLOCK)
+        out[a - lo : b - lo] = z[a - k * TS_NOISE_BLOCK : b - k * TS_NOISE_BLOCK]
+    return out
+
+
+class _ShardScorer:
+    """Marginal posterior of the shard [lo, hi) of a replicated candidate set, and per-draw Thompson picks inside it."""
+
+    def __init__(self, sampler, X: Tensor, lo: int, hi: int) -> None:
+        from . import _lib
+
+        st = sampler.model.gp_state
+        if st.M != 1:
+            raise NotImplementedError("sharded Thompson sampling is implemented for single (non-ensemble) models")
+        self.st, self.lo, self.hi, self.dev = st, lo, hi, st.device
+        self.lib = _lib
+        if hi > lo:
+            mean, var = sampler.marginal_posterior(X[lo:hi].to(torch.float64).contiguous())
+            self.mean, self.var = mean[0].clone().contiguous(), var[0].contiguous()
+        self.val = torch.empty(1, dtype=torch.float64, device=self.dev)
+        self.idx = torch.empty(1, dtype=torch.int64, device=self.dev)
+
+    def pick(self, draw: int, seed: int):
+        """(value [1], global index [1]) of the best candidate of this shard for one draw; (-inf, int64 max) if empty."""
+        if self.hi <= self.lo:
+            return (torch.full((1,), -float("inf"), dtype=torch.float64, device=self.dev),
+                    torch.full((1,), torch.iinfo(torch.int64).max, dtype=torch.int64, device=self.dev))  # fmt: skip
+        z = ts_base_samples(self.lo, self.hi, draw, seed, self.dev)
+        lib = self.lib
+        lib.check(lib.lib().bo_ts_argmax(self.st.ctx, 1, self.hi - self.lo, self.mean.data_ptr(), self.var.data_ptr(),
+                                         z.data_ptr(), self.val.data_ptr(), self.idx.data_ptr(),
+                                         lib.stream_ptr(self.dev)))  # fmt: skip
+        return self.val.clone(), self.idx + self.lo
+
+    def exclude(self, global_idx: int) -> None:
+        if self.lo <= global_idx < self.hi:
+            self.mean[global_idx - self.lo] = -float("inf")
+
+
+def _winner(vals: Tensor, idxs: Tensor) -> Tensor:
+    """Across ranks (dim 0): index of the largest value, lowest global index on ties (torch.argmax semantics)."""
+    top = vals.max(dim=0).values
+    masked = torch.where(vals == top, idxs, torch.full_like(idxs, torch.iinfo(torch.int64).max))
+    return masked.min(dim=0).values
+
+
+def thompson_sample_sharded(sampler, X: Tensor, num_samples: int = 1, seed: int = 0, shard=None) -> Tensor:
+    """``MaxPosteriorSampling`` (marginal form, SURVEY.md row T1 / 8e "C5: shard N") over a candidate set sharded across
+    the process group: rank r scores the contiguous block ``shard_range(N, r, G)``; (value, global index) pairs are
+    all-gathered -- once per call with replacement, once per draw without -- and the winner is the largest value,
+    lowest index on ties.  Base samples are keyed by global candidate position, so the picks do not depend on the
+    number of ranks.  ``X`` (N x d) is replicated; ``shard=(rank, world_size)`` overrides the process group (tests).
+    """
+    rank, ws = world() if shard is None else shard
+    gather = shard is None and ws > 1
+    lo, hi = shard_range(X.shape[0], rank, ws)
+    scorer = _ShardScorer(sampler, X, lo, hi)
+
+    def all_ranks(v: Tensor, i: Tensor):
+        if not gather:
+            return v.unsqueeze(0), i.unsqueeze(0)
+        gv = [torch.empty_like(v) for _ in range(ws)]
+        gi = [torch.empty_like(i) for _ in range(ws)]
+        dist.all_gather(gv, v)
+        dist.all_gather(gi, i)
+        return torch.stack(gv), torch.stack(gi)
+
+    if sampler.replacement:
+        picks = [scorer.pick(s, seed) for s in range(num_samples)]
+        V, I = all_ranks(torch.cat([p[0] for p in picks]), torch.cat([p[1] for p in picks]))
+        return X[_winner(V, I)]
+    chosen = []
+    for s in range(num_samples):  # sequential: the winner of draw s is excluded everywhere before draw s + 1
+        V, I = all_ranks(*scorer.pick(s, seed))
+        g = int(_winner(V, I))
+        scorer.exclude(g)
+        chosen.append(g)
+    return X[torch.tensor(chosen, dtype=torch.long, device=X.device)]
+
+
 def optimize_acqf_sharded(
     acq_function,
     bounds: Tensor,

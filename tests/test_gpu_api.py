@@ -295,6 +295,36 @@ def test_thompson_sampling_joint(cuda):
     assert _flip_sub_unique(x, 3).tolist() == [3, 6, 4] and _flip_sub_unique(x, 10).tolist() == [3, 6, 4, 1]
 
 
+def test_sharded_thompson_sampling_is_independent_of_the_sharding(cuda):
+    """SURVEY 8e "C5: shard N": per-shard marginal draws + (value, global index) reduction give the picks of the
+    unsharded run, for any number of shards, because the base samples are keyed by global candidate position."""
+    from botorch_b200 import distributed as bd
+
+    p = make_problem("C5", n=150)
+    model = _model(p, cuda)
+    N = 40000  # spans three base-sample blocks
+    Xc = qmc.sobol_box(torch.stack([torch.zeros(p.d), torch.ones(p.d)]).double(), N, 1, seed=4).squeeze(1).to(cuda)
+    for replacement in (True, False):
+        ts = bb.MaxPosteriorSampling(model, replacement=replacement, chunk_size=8192)
+        full = bd.thompson_sample_sharded(ts, Xc, num_samples=5, seed=7)
+        assert full.shape == (5, p.d)
+        if not replacement:
+            assert len({tuple(r.tolist()) for r in full.cpu()}) == 5
+        for ws in (2, 3):
+            scorers = [bd._ShardScorer(ts, Xc, *bd.shard_range(N, r, ws)) for r in range(ws)]
+            chosen = []
+            for s_ in range(5):
+                picks = [sc.pick(s_, 7) for sc in scorers]
+                g = int(bd._winner(torch.stack([v for v, _ in picks]), torch.stack([i for _, i in picks])))
+                chosen.append(g)
+                if not replacement:
+                    for sc in scorers:
+                        sc.exclude(g)
+            assert torch.equal(Xc[torch.tensor(chosen, device=cuda)], full)
+    z = bd.ts_base_samples(100, 40000, 2, 7, cuda)
+    assert torch.equal(z[16284:16294], bd.ts_base_samples(16384, 16394, 2, 7, cuda))  # block-keyed noise
+
+
 def test_saas_posterior_mixture(cuda):
     p = make_problem("C4", M=4)
     ogp = oracle_gp(p)
