@@ -243,3 +243,17 @@ def test_gen_candidates_torch_on_a_quadratic_and_host_evaluator_cpu():
     loss, grad = ev(ics.reshape(-1).numpy())
     assert abs(loss - float(-acq(ics).sum())) < 1e-12
     assert torch.allclose(torch.from_numpy(grad).view_as(ics), 2 * (ics - 0.3))
+
+
+def test_thompson_winner_reduction_and_block_keyed_noise():
+    """distributed._winner: across ranks the largest value wins, lowest global index on ties (torch.argmax semantics,
+    generation/sampling.py:117); base samples of a candidate depend on its global block only."""
+    from botorch_b200 import distributed as bd
+
+    vals = torch.tensor([[1.0, 5.0, 2.0], [3.0, 5.0, -float("inf")]], dtype=torch.float64)  # ranks x draws
+    idxs = torch.tensor([[10, 40, 7], [99, 12, torch.iinfo(torch.int64).max]])
+    assert bd._winner(vals, idxs).tolist() == [99, 12, 7]
+    z_all = bd.ts_base_samples(0, 40000, 1, 3, torch.device("cpu"))
+    z_mid = bd.ts_base_samples(16000, 33000, 1, 3, torch.device("cpu"))
+    assert torch.equal(z_all[16000:33000], z_mid)
+    assert not torch.equal(z_all[:100], bd.ts_base_samples(0, 100, 2, 3, torch.device("cpu")))
