@@ -37,6 +37,7 @@ class BoGP(C.Structure):
         ("linv_aug_t", C.c_void_p),
         ("chol", C.c_void_p),
         ("xt_aug", C.c_void_p),
+        ("noise_vec", C.c_void_p),
     ]
 
 

@@ -39,7 +39,7 @@ struct Bump {  // carve the caller's workspace; 256-byte aligned regions
 
 __global__ void vec_add_kernel(const double* a, const double* b, double* out, int n) {
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i < n) out[i] = a[i] + (b ? b[i] : 0.0);
+    if (i < n) out[i] = (a ? a[i] : 0.0) + (b ? b[i] : 0.0);
 }
 // r[z][i][0] = targets[i] - mean[z];  r[z][i][1] = 0
 __global__ void resid_kernel(const double* targets, const double* mean, double* r, int n) {
@@ -105,7 +105,7 @@ int gemm(int M, int N, int K, int batch, double alpha, const double* A, long lda
 }
 
 bool valid_gp(const bo_gp* gp) {
-    return gp && gp->n > 0 && gp->d > 0 && gp->d <= BO_MAX_D && gp->M > 0 &&
+    return gp && gp->n > 0 && gp->d > 0 && gp->d <= BO_MAX_D && gp->M > 0 && (gp->noise || gp->noise_vec) &&
            (gp->kernel_id == BO_KERNEL_RBF || gp->kernel_id == BO_KERNEL_MATERN52);
 }
 
@@ -185,10 +185,12 @@ int bo_gp_setup(bo_ctx* ctx, const bo_gp* gp, void* work, size_t work_bytes, int
         BO_TRY(bo_transpose(gp->train_X, gp->d, 0, gp->xt_aug, np, 0, (int)n, gp->d, 1, st));
         BO_TRY(bo_fill(gp->xt_aug + (long)gp->d * np, n, 1.0, st));
     }
-    vec_add_kernel<<<(unsigned)((M + 127) / 128), 128, 0, st>>>(gp->noise, gp->jitter, nz, (int)M);
+    vec_add_kernel<<<(unsigned)((M + 127) / 128), 128, 0, st>>>(gp->noise_vec ? nullptr : gp->noise, gp->jitter, nz, (int)M);
     g_bo_launch_count++;
-    // K + (s2 + jitter) I, unit diagonal of the kernel enforced exactly (x1_eq_x2 branch of gpytorch's sq_dist)
+    // K + (s2 + jitter) I, unit diagonal of the kernel enforced exactly (x1_eq_x2 branch of gpytorch's sq_dist);
+    // with fixed per-observation noise the diagonal gets noise_vec[i] + jitter instead
     BO_TRY(kmat(gp, gp->aug_train, (int)n, baug, np, n, gp->chol, np, n * np, 1, nz, st));
+    BO_TRY(bo_add_diag_vec(gp->chol, np, n * np, (int)n, (int)M, gp->noise_vec, n, st));
     BO_TRY(bo_potrf_blocked(gp->chol, np, n * np, (int)n, (int)M, gp->linv_aug, np, (n + 1) * np, scratch, info, st));
     BO_TRY(bo_trtri_blocked(gp->chol, np, n * np, (int)n, (int)M, gp->linv_aug, np, (n + 1) * np, scratch, st));
     BO_TRY(bo_fill(gp->linv_aug_t, M * n * n1p, 0.0, st));
@@ -208,7 +210,8 @@ int bo_gp_setup(bo_ctx* ctx, const bo_gp* gp, void* work, size_t work_bytes, int
 }
 
 static size_t nei_setup_layout(const bo_gp* gp, const bo_nei* nei, void* work, size_t cap, double** baug_b,
-                               double** kb, double** fb, double** scratch, double** nz, double** khinv, bool* ok) {
+                               double** kb, double** fb, double** scratch, double** nz, double** khinv, double** khs,
+                               bool* ok) {
     const long n = gp->n, M = gp->M, nb = nei->n_b, nbp = bo_pad8(nb), Sp = bo_pad8(nei->S), Kp = bo_kp(gp->d);
     Bump b(work, cap);
     *baug_b = b.doubles(M * Kp * nbp);
@@ -217,14 +220,15 @@ static size_t nei_setup_layout(const bo_gp* gp, const bo_nei* nei, void* work, s
     *scratch = b.doubles(bo_linalg_scratch_doubles((int)nb, (int)M));
     *nz = b.doubles(M);
     *khinv = nei->baseline_is_train ? b.doubles(M * n * bo_pad8(n)) : nullptr;  // (K + s2 I)^-1
+    *khs = (nei->baseline_is_train && gp->noise_vec) ? b.doubles(M * n * bo_pad8(n)) : nullptr;  // D (K + D)^-1
     *ok = b.ok;
     return b.off;
 }
 
 size_t bo_nei_setup_workspace_bytes(const bo_gp* gp, const bo_nei* nei) {
-    double *a, *b, *c, *d, *e, *f;
+    double *a, *b, *c, *d, *e, *f, *g;
     bool ok;
-    return nei_setup_layout(gp, nei, nullptr, 0, &a, &b, &c, &d, &e, &f, &ok);
+    return nei_setup_layout(gp, nei, nullptr, 0, &a, &b, &c, &d, &e, &f, &g, &ok);
 }
 
 int bo_nei_setup(bo_ctx* ctx, const bo_gp* gp, const bo_nei* nei, void* work, size_t work_bytes, int32_t* info,
@@ -235,9 +239,9 @@ int bo_nei_setup(bo_ctx* ctx, const bo_gp* gp, const bo_nei* nei, void* work, si
     const long n = gp->n, M = gp->M, np = bo_pad8(n), nb = nei->n_b, nbp = bo_pad8(nb), S = nei->S, Sp = bo_pad8(S);
     const long Kp = bo_kp(gp->d);
     const double ys2 = gp->y_std * gp->y_std;
-    double *baug_b, *kb, *fb, *scratch, *nz, *khinv;
+    double *baug_b, *kb, *fb, *scratch, *nz, *khinv, *khs;
     bool ok;
-    nei_setup_layout(gp, nei, work, work_bytes, &baug_b, &kb, &fb, &scratch, &nz, &khinv, &ok);
+    nei_setup_layout(gp, nei, work, work_bytes, &baug_b, &kb, &fb, &scratch, &nz, &khinv, &khs, &ok);
     if (!ok) return BO_ERR_WORKSPACE;
     const BoKernelHyper h = hyper_of(gp);
     BO_CUDA_TRY(cudaMemsetAsync(info, 0, sizeof(int32_t) * M, st));
@@ -283,12 +287,18 @@ int bo_nei_setup(bo_ctx* ctx, const bo_gp* gp, const bo_nei* nei, void* work, si
         const long n1p = bo_pad8(n + 1);
         BO_TRY(gemm((int)n, (int)n, (int)n, (int)M, 1.0, gp->linv_aug_t, n1p, n * n1p, gp->linv_aug, np, (n + 1) * np, 0.0,
                     nullptr, 0, 0, khinv, np, n * np, BO_TRI_A_UPPER, 0, st));
+        // Khat - K = D (s2 I, or diag(noise_vec) for fixed per-observation noise): Sigma(X_b, X) = ys^2 D Khat^-1 K_x
+        const double* qrhs = khinv;
+        if (gp->noise_vec) {
+            BO_TRY(bo_scale_rows(khinv, khs, np, n * np, (int)n, (int)n, (int)M, gp->noise_vec, n, gp->jitter, st));
+            qrhs = khs;
+        }
         BoGemm g{};
         g.A = nei->lb_inv; g.lda = nbp; g.strideA = nb * nbp;
-        g.B = khinv; g.ldb = np; g.strideB = n * np;
+        g.B = qrhs; g.ldb = np; g.strideB = n * np;
         g.C = nei->qmat; g.ldc = np; g.strideC = nb * np;
         g.CT = nei->qmat_t; g.ldct = nbp; g.strideCT = n * nbp;
-        g.alpha = ys2; g.alpha_vec = nz; g.M = (int)nb; g.N = (int)n; g.K = (int)nb; g.batch = (int)M;
+        g.alpha = ys2; g.alpha_vec = gp->noise_vec ? nullptr : nz; g.M = (int)nb; g.N = (int)n; g.K = (int)nb; g.batch = (int)M;
         g.tri = BO_TRI_A_LOWER; g.epi = BO_EPI_LINEAR;
         BO_TRY(bo_fill(nei->qmat_t, M * n * nbp, 0.0, st));
         BO_TRY(bo_gemm_launch(g, st));

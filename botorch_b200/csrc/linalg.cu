@@ -115,6 +115,21 @@ __global__ void add_diag_kernel(double* A, long lda, long strideA, int n, const 
     if (i < n) A[(long)z * strideA + (long)i * lda + i] += add[z];
 }
 
+// A[z][i][i] += vec[z][i]
+__global__ void add_diag_vec_kernel(double* A, long lda, long strideA, int n, const double* vec, long strideVec) {
+    const int z = blockIdx.y;
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) A[(long)z * strideA + (long)i * lda + i] += vec[(long)z * strideVec + i];
+}
+// dst[z][i][j] = (vec[z][i] + (add ? add[z] : 0)) * src[z][i][j]
+__global__ void scale_rows_kernel(const double* src, double* dst, long ld, long stride, int rows, int cols,
+                                  const double* vec, long strideVec, const double* add) {
+    const int z = blockIdx.z, i = blockIdx.y;
+    const double f = vec[(long)z * strideVec + i] + (add ? add[z] : 0.0);
+    const long base = (long)z * stride + (long)i * ld;
+    for (int j = blockIdx.x * blockDim.x + threadIdx.x; j < cols; j += gridDim.x * blockDim.x) dst[base + j] = f * src[base + j];
+}
+
 __global__ void fill_kernel(double* p, long count, double v) {
     for (long i = blockIdx.x * (long)blockDim.x + threadIdx.x; i < count; i += (long)gridDim.x * blockDim.x) p[i] = v;
 }
@@ -160,6 +175,27 @@ int bo_add_diag(double* A, long lda, long strideA, int n, int batch, const doubl
     if (!add || n <= 0) return BO_OK;
     dim3 grid((n + 127) / 128, batch);
     add_diag_kernel<<<grid, 128, 0, stream>>>(A, lda, strideA, n, add);
+    g_bo_launch_count++;
+    BO_CUDA_TRY(cudaGetLastError());
+    return BO_OK;
+}
+
+int bo_add_diag_vec(double* A, long lda, long strideA, int n, int batch, const double* vec, long strideVec,
+                    cudaStream_t stream) {
+    if (!vec || n <= 0) return BO_OK;
+    dim3 grid((n + 127) / 128, batch);
+    add_diag_vec_kernel<<<grid, 128, 0, stream>>>(A, lda, strideA, n, vec, strideVec);
+    g_bo_launch_count++;
+    BO_CUDA_TRY(cudaGetLastError());
+    return BO_OK;
+}
+
+int bo_scale_rows(const double* src, double* dst, long ld, long stride, int rows, int cols, int batch, const double* vec,
+                  long strideVec, const double* add, cudaStream_t stream) {
+    if (rows <= 0 || cols <= 0) return BO_OK;
+    if (rows > 65535 || batch > 65535) return BO_ERR_UNSUPPORTED;
+    dim3 grid((cols + 255) / 256 > 8 ? 8 : (cols + 255) / 256, rows, batch);
+    scale_rows_kernel<<<grid, 256, 0, stream>>>(src, dst, ld, stride, rows, cols, vec, strideVec, add);
     g_bo_launch_count++;
     BO_CUDA_TRY(cudaGetLastError());
     return BO_OK;

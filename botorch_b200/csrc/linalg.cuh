@@ -27,4 +27,10 @@ int bo_copy2d(const double* src, long lds, long strideS, double* dst, long ldd, 
               int batch, cudaStream_t stream);
 // A[z][i][i] += add[z]  (add may be null -> no-op)
 int bo_add_diag(double* A, long lda, long strideA, int n, int batch, const double* add, cudaStream_t stream);
+// A[z][i][i] += vec[z][i]  (vec may be null -> no-op)
+int bo_add_diag_vec(double* A, long lda, long strideA, int n, int batch, const double* vec, long strideVec,
+                    cudaStream_t stream);
+// dst[z][i][:] = (vec[z][i] + add[z]) * src[z][i][:]   (add may be null)
+int bo_scale_rows(const double* src, double* dst, long ld, long stride, int rows, int cols, int batch, const double* vec,
+                  long strideVec, const double* add, cudaStream_t stream);
 int bo_fill(double* p, long count, double v, cudaStream_t stream);

@@ -63,6 +63,7 @@ class GPState:
         y_mean: float = 0.0,
         y_std: float = 1.0,
         setup: bool = True,
+        noise_vec: Optional[Tensor] = None,
     ) -> None:
         dev = train_X.device
         self.device = dev
@@ -78,6 +79,11 @@ class GPState:
         self.mean = _f64(mean, dev).reshape(-1).expand(self.M).contiguous()
         self.outputscale = None if outputscale is None else _f64(outputscale, dev).reshape(-1).expand(self.M).contiguous()
         self.targets = _f64(targets, dev).reshape(-1)
+        # fixed per-observation noise [n] (shared by the M models): K + diag(noise_vec); `noise` stays the level that
+        # observation_noise=True adds at test points
+        self.noise_vec = None if noise_vec is None else _f64(noise_vec, dev).reshape(1, -1).expand(self.M, -1).contiguous()
+        if self.noise_vec is not None and self.noise_vec.shape[1] != self.train_X.shape[0]:
+            raise ValueError(f"noise_vec needs one entry per training point, got {tuple(self.noise_vec.shape)}")
         self.center = self.train_X.mean(dim=0).contiguous()
         self.y_mean, self.y_std = float(y_mean), float(y_std)
         for name, t in (("train_X", self.train_X), ("targets", self.targets), ("lengthscale", ls), ("noise", self.noise)):
@@ -98,7 +104,7 @@ class GPState:
             outputscale=ptr(self.outputscale), noise=ptr(self.noise), mean=ptr(self.mean),
             targets=ptr(self.targets), jitter=None,
             aug_train=ptr(self.aug_train), linv_aug=ptr(self.linv_aug), linv_aug_t=ptr(self.linv_aug_t),
-            chol=ptr(self.chol), xt_aug=ptr(self.xt_aug),
+            chol=ptr(self.chol), xt_aug=ptr(self.xt_aug), noise_vec=ptr(self.noise_vec),
         )  # fmt: skip
         self.jitter = torch.zeros(M, dtype=torch.float64, device=dev)
         if not setup:  # factors arrive by broadcast from the rank that ran the setup (distributed.py)

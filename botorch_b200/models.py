@@ -27,7 +27,13 @@ from torch import Tensor
 from torch.nn import Module
 
 from . import engine
-from .exceptions import BotorchTensorDimensionError, InputDataError, InputDataWarning, UnsupportedError
+from .exceptions import (
+    BotorchTensorDimensionError,
+    InputDataError,
+    InputDataWarning,
+    NumericalWarning,
+    UnsupportedError,
+)
 from .posteriors import MCMC_DIM, DenseMVN, FusedGPPosterior, GaussianMixturePosterior
 
 MIN_INFERRED_NOISE_LEVEL = 1e-4  # gpytorch_modules.py:29
@@ -121,17 +127,34 @@ class _FusedExactGP(Model):
 
     _kernel = "rbf"
 
-    def _init_data(self, train_X: Tensor, train_Y: Tensor, outcome_transform) -> None:
+    def _init_data(self, train_X: Tensor, train_Y: Tensor, outcome_transform, train_Yvar: Optional[Tensor] = None) -> None:
         _validate_tensor_args(train_X, train_Y)
         if train_X.dim() != 2 or train_Y.shape[-1] != 1:
             raise UnsupportedError("the fused path takes unbatched n x d inputs and n x 1 targets")
+        if train_Yvar is not None and train_Yvar.shape != train_Y.shape:
+            raise BotorchTensorDimensionError(
+                f"An explicit output dimension is required for observation noise. Expected Yvar with shape: "
+                f"{tuple(train_Y.shape)} (got {tuple(train_Yvar.shape)})."
+            )
         if outcome_transform is not None:
             outcome_transform.train()
-            train_Y, _ = outcome_transform(train_Y)
+            train_Y, train_Yvar = outcome_transform(train_Y, train_Yvar)  # Yvar / stdvs^2 (outcome.py:289-307)
             outcome_transform.eval()
             self.outcome_transform = outcome_transform
         self.train_inputs = (train_X,)
         self.train_targets = train_Y.squeeze(-1)
+        # fixed per-observation noise (FixedNoiseGaussianLikelihood, gp_regression.py:186-195), model space
+        self.train_Yvar = None
+        if train_Yvar is not None:  # gpytorch FixedGaussianNoise: settings.min_fixed_noise (1e-6 in double, 1e-4 in float)
+            floor = 1e-6 if train_Yvar.dtype == torch.float64 else 1e-4
+            if bool((train_Yvar < floor).any()):
+                warnings.warn(
+                    "Very small noise values detected. This will likely lead to numerical instabilities. Rounding "
+                    f"small noise values up to {floor}.",
+                    NumericalWarning,
+                    stacklevel=3,
+                )
+            self.train_Yvar = train_Yvar.detach().squeeze(-1).clamp_min(floor)
         self._state: Optional[engine.GPState] = None
 
     # -- hyperparameters (subclasses) -----------------------------------------------------------
@@ -159,6 +182,7 @@ class _FusedExactGP(Model):
             y_mean=float(ot.means) if ot is not None else 0.0,
             y_std=float(ot.stdvs) if ot is not None else 1.0,
             setup=setup,
+            noise_vec=getattr(self, "train_Yvar", None),
         )
 
     @property
@@ -212,7 +236,7 @@ class SingleTaskGP(_FusedExactGP):
         kernel: str = "rbf",
     ) -> None:
         super().__init__()
-        for name, arg in (("train_Yvar", train_Yvar), ("likelihood", likelihood), ("covar_module", covar_module),
+        for name, arg in (("likelihood", likelihood), ("covar_module", covar_module),
                           ("mean_module", mean_module), ("input_transform", input_transform)):  # fmt: skip
             if arg is not None:
                 raise UnsupportedError(f"`{name}` is outside the fused path (SURVEY.md section 8): pass None")
@@ -221,11 +245,15 @@ class SingleTaskGP(_FusedExactGP):
         if isinstance(outcome_transform, str):
             outcome_transform = Standardize(m=1)
         self._kernel = kernel
-        self._init_data(train_X, train_Y, outcome_transform)
+        if train_Yvar is not None and noise is not None:
+            raise ValueError("pass either `train_Yvar` (fixed per-observation noise) or `noise` (inferred homoskedastic level)")
+        self._init_data(train_X, train_Y, outcome_transform, train_Yvar)
         d = train_X.shape[-1]
         tk = {"dtype": train_X.dtype, "device": train_X.device}
         ls = torch.full((d,), default_lengthscale(d), **tk) if lengthscale is None else torch.as_tensor(lengthscale, **tk)
         nz = math.exp(-4.0 - 1.0) if noise is None else noise  # mode of LogNormal(-4, 1)
+        if self.train_Yvar is not None:  # observation_noise=True adds the mean training noise (models/gpytorch.py:393-400)
+            nz = float(self.train_Yvar.mean())
         self.covar_module = _Holder()
         self.covar_module.raw_lengthscale = torch.nn.Parameter(ls.reshape(1, d).clone())
         if outputscale is not None:

@@ -64,6 +64,9 @@ typedef struct bo_gp {
     double* linv_aug_t;        /* [M][n x n1p]       transpose of linv_aug */
     double* chol;              /* [M][n x np]        L, K + s2 I = L L^T */
     double* xt_aug;            /* [(d+1) x np]       rows 0..d-1: train_X^T, row d: ones (gradient contraction operand) */
+    /* optional: fixed per-observation noise (SingleTaskGP with train_Yvar -> FixedNoiseGaussianLikelihood,
+     * models/gp_regression.py:186-195): K + diag(noise_vec); `noise` is then ignored by the setup routines */
+    const double* noise_vec;   /* [M x n] or NULL */
 } bo_gp;
 
 /* qLogNEI baseline state.  Replaces qLogNoisyExpectedImprovement._init_baseline

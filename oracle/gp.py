@@ -123,6 +123,9 @@ class GPHyper:
     noise: Tensor
     mean: Tensor
     outputscale: Optional[Tensor] = None
+    # fixed per-observation noise (n,) in the model's (standardised) space: FixedNoiseGaussianLikelihood,
+    # /root/reference/botorch/models/gp_regression.py:186-195; the train covariance is then K + diag(noise_vec)
+    noise_vec: Optional[Tensor] = None
 
     @property
     def batch_shape(self) -> torch.Size:
@@ -165,7 +168,10 @@ class OracleGP:
     def caches(self) -> Tuple[Tensor, Tensor, Tensor]:
         if self._caches is None:
             K = self._kernel(self.train_X, self.train_X, x1_eq_x2=True)
-            Khat = K + self._noise() * torch.eye(self.n, dtype=K.dtype)
+            if self.hyper.noise_vec is not None:
+                Khat = K + torch.diag_embed(self.hyper.noise_vec)
+            else:
+                Khat = K + self._noise() * torch.eye(self.n, dtype=K.dtype)
             L = psd_safe_cholesky(Khat)
             resid = (self.train_targets - self.hyper.mean[..., None]).unsqueeze(-1)
             mean_cache = torch.cholesky_solve(resid.expand(*L.shape[:-1], 1), L).squeeze(-1)

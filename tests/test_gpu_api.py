@@ -375,3 +375,41 @@ def test_cuda_path_matches_committed_golden_fixtures(cuda):
     mean, var = ts.marginal_posterior(c["X"].to(cuda))
     assert rel_err(mean[0], c["mean"]) < RTOL
     assert int(torch.argmax(mean[0])) == c["argmax_mean"]
+
+
+def test_fixed_observation_noise_model(cuda):
+    """SingleTaskGP(train_X, train_Y, train_Yvar) (gp_regression.py:186-195): K + diag(Yvar / stdv^2); posterior,
+    qLogNEI value and gradient on the combined-root path (Sigma(X_b, X) = ys^2 D Khat^-1 K_x) against the oracle."""
+    from oracle.gp import GPHyper, OracleGP
+    from oracle.qlognei import OracleQLogNEI
+
+    p = make_problem("C2", n=90)
+    g = torch.Generator().manual_seed(3)
+    Yvar = (0.002 + 0.05 * torch.rand(p.train_Y.shape, generator=g, dtype=torch.float64)) * float(p.train_Y.var())
+    h = p.hypers
+    model = bb.SingleTaskGP(p.train_X.to(cuda), p.train_Y.to(cuda), Yvar.to(cuda), lengthscale=h["lengthscale"],
+                            mean_constant=h["mean"])  # fmt: skip
+    stdv = p.train_Y.std(dim=-2)
+    hyper = GPHyper("rbf", h["lengthscale"], torch.tensor(0.0, dtype=torch.float64), h["mean"],
+                    noise_vec=(Yvar / stdv**2).squeeze(-1))  # fmt: skip
+    ogp = OracleGP(p.train_X, p.train_Y, hyper, standardize=True)
+    X = candidates(p, 6, q=3)
+    Xd = X.to(cuda).requires_grad_(True)
+    post = model.posterior(Xd)
+    m_ref, c_ref = ogp.posterior_direct(X)
+    assert rel_err(post.mean.squeeze(-1), m_ref) < RTOL
+    assert rel_err(post.distribution.covariance_matrix, c_ref, scale=float(ogp.y_std) ** 2) < RTOL
+    # observation_noise=True adds the mean training noise (models/gpytorch.py:393-400)
+    noisy = model.posterior(X.to(cuda), observation_noise=True).variance.squeeze(-1)
+    expect = torch.diagonal(c_ref, dim1=-2, dim2=-1) + float(Yvar.mean())
+    assert rel_err(noisy, expect, scale=float(ogp.y_std) ** 2) < 1e-8
+    oacq = OracleQLogNEI(ogp, p.train_X, num_samples=p.mc_samples, seed=1234)
+    acqf = _acqf(p, model, cuda)
+    assert acqf._nei.is_train  # the shared-baseline (combined-root) path
+    val = acqf(Xd)
+    (grad,) = torch.autograd.grad(val.sum(), Xd)
+    a_ref, g_ref = oacq.value_and_grad(X)
+    assert rel_err(val, a_ref, scale=0.0) < RTOL
+    assert rel_err(grad, g_ref) < 1e-8
+    with pytest.raises(ValueError):
+        bb.SingleTaskGP(p.train_X.to(cuda), p.train_Y.to(cuda), Yvar.to(cuda), noise=0.1)
