@@ -63,7 +63,12 @@ def test_model_argument_validation_and_state_dict():
     with pytest.warns(bex.InputDataWarning):
         bb.SingleTaskGP(X.float(), Y.float())
     with pytest.raises(bex.UnsupportedError):
-        bb.SingleTaskGP(X, Y, train_Yvar=torch.ones_like(Y))
+        bb.SingleTaskGP(X, Y, covar_module=object())
+    with pytest.raises(bex.BotorchTensorDimensionError):  # Yvar needs the explicit output dimension (gpytorch.py:91-127)
+        bb.SingleTaskGP(X, Y, train_Yvar=torch.ones(5, dtype=torch.float64))
+    with pytest.warns(bex.NumericalWarning):  # gpytorch's min_fixed_noise floor
+        fixed = bb.SingleTaskGP(X, Y, train_Yvar=torch.full_like(Y, 1e-9))
+    assert float(fixed.train_Yvar.min()) == 1e-6
     m = bb.SingleTaskGP(X, Y)
     sd = m.state_dict()
     for k in ("covar_module.raw_lengthscale", "likelihood.noise_covar.raw_noise", "mean_module.raw_constant",
