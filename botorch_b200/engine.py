@@ -445,6 +445,37 @@ def root_apply(L: Tensor, mean: Tensor, Z: Tensor) -> Tensor:
     return samples + mean
 
 
+class _RootSample(torch.autograd.Function):
+    """samples = mean + chol(cov) z, differentiable w.r.t. mean and cov (``MultivariateNormal.rsample`` with base samples,
+    posteriors/gpytorch.py:121-165).  Forward: blocked Cholesky + triangular GEMM of libbotorch_b200.  Backward: the
+    Cholesky adjoint  cov_bar = sym(L^-T Phi(L^T L_bar) L^-1),  L_bar = sum_s samples_bar_s z_s^T  (small r x r algebra)."""
+
+    @staticmethod
+    def forward(ctx, mean: Tensor, cov: Tensor, Z: Tensor):
+        L = mvn_root(cov.detach())
+        ctx.save_for_backward(L, Z)
+        return root_apply(L, mean.detach(), Z)
+
+    @staticmethod
+    def backward(ctx, g: Tensor):
+        L, Z = ctx.saved_tensors
+        g = g.to(torch.float64)
+        mean_bar = g.sum(dim=0)
+        Lbar = torch.einsum("s...i,s...j->...ij", g, Z.to(torch.float64).expand_as(g)).tril()
+        P = (L.mT @ Lbar).tril()
+        P = P - 0.5 * torch.diag_embed(P.diagonal(dim1=-2, dim2=-1))
+        Sb = torch.linalg.solve_triangular(L.mT, P, upper=True)  # L^-T P
+        Sb = torch.linalg.solve_triangular(L, Sb, upper=False, left=False)  # (L^-T P) L^-1
+        return mean_bar, 0.5 * (Sb + Sb.mT), None
+
+
+def root_sample(mean: Tensor, cov: Tensor, Z: Tensor) -> Tensor:
+    """mean [... x r], cov [... x r x r], Z [S x ... x r] -> samples [S x ... x r]; carries gradients when its inputs do."""
+    if torch.is_grad_enabled() and (mean.requires_grad or cov.requires_grad):
+        return _RootSample.apply(mean, cov, Z)
+    return root_apply(mvn_root(cov.detach()), mean.detach(), Z)
+
+
 class _PosteriorJoint(torch.autograd.Function):
     """mean/covariance blocks of B t-batches with the hand-written reverse pass (bo_posterior_joint_bwd)."""
 

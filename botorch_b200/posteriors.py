@@ -56,7 +56,10 @@ class DenseMVN:
         if base_samples is None:
             base_samples = torch.randn(full, dtype=self.loc.dtype, device=self.loc.device)
         flat = base_samples.expand(full).reshape(max(sample_shape.numel(), 1), *self.loc.shape)
-        out = engine.root_apply(self.root(), self.loc.detach(), flat)
+        if torch.is_grad_enabled() and (self.loc.requires_grad or self.covariance_matrix.requires_grad):
+            out = engine.root_sample(self.loc, self.covariance_matrix, flat)  # differentiable w.r.t. X through mean / cov
+        else:
+            out = engine.root_apply(self.root(), self.loc.detach(), flat)
         return out.reshape(full).to(self.loc.dtype)
 
 

@@ -110,6 +110,30 @@ def test_rsample_from_base_samples_is_mean_plus_chol_z(cuda):
     assert post.rsample(torch.Size([3])).shape == (3, 6, 5, 1)
 
 
+@pytest.mark.parametrize("cfg,kw", [("C2", {"n": 50}), ("C4", {"M": 3})])
+def test_rsample_is_differentiable_through_the_cholesky(cuda, cfg, kw):
+    """Reparameterised samples carry gradients w.r.t. X (custom MC acquisition functions call
+    sampler(posterior) under autograd, acquisition/monte_carlo.py:116-125): compared with torch autograd through
+    mean + cholesky(cov) z on the oracle posterior."""
+    p = make_problem(cfg, **kw)
+    ogp = oracle_gp(p)
+    model = _model(p, cuda)
+    X = candidates(p, 4, q=3)
+    Xd = X.to(cuda).requires_grad_(True)
+    sampler = bb.SobolQMCNormalSampler(sample_shape=torch.Size([8]), seed=5)
+    samples = sampler(model.posterior(Xd)).squeeze(-1)  # 8 x 4 x (M) x 3
+    w = torch.linspace(0.5, 2.0, 3, dtype=torch.float64)
+    (g,) = torch.autograd.grad((samples**2 * w.to(cuda)).sum() + samples.sum(), Xd)
+    Xo = X.clone().requires_grad_(True)
+    m_ref, c_ref = ogp.posterior(Xo)
+    L = torch.linalg.cholesky(c_ref)
+    z = sampler.base_samples.cpu().reshape(8, *([1] * (m_ref.dim() - 1)), 3)
+    s_ref = m_ref + torch.einsum("...ij,s...j->s...i", L, z.expand(8, *m_ref.shape))
+    assert rel_err(samples, s_ref) < 1e-9
+    (g_ref,) = torch.autograd.grad((s_ref**2 * w).sum() + s_ref.sum(), Xo)
+    assert rel_err(g, g_ref) < 1e-8
+
+
 @pytest.mark.parametrize("cfg,kw,q,B", [("C1", {}, 1, 10), ("C2", {}, 4, 16), ("C3", {"n": 256}, 8, 6), ("C4", {"M": 5}, 4, 7)])
 def test_qlognei_forward_and_autograd_match_oracle(cuda, cfg, kw, q, B):
     p = make_problem(cfg, **kw)
