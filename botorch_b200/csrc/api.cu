@@ -211,7 +211,7 @@ int bo_gp_setup(bo_ctx* ctx, const bo_gp* gp, void* work, size_t work_bytes, int
 
 static size_t nei_setup_layout(const bo_gp* gp, const bo_nei* nei, void* work, size_t cap, double** baug_b,
                                double** kb, double** fb, double** scratch, double** nz, double** khinv, double** khs,
-                               bool* ok) {
+                               double** qr, bool* ok) {
     const long n = gp->n, M = gp->M, nb = nei->n_b, nbp = bo_pad8(nb), Sp = bo_pad8(nei->S), Kp = bo_kp(gp->d);
     Bump b(work, cap);
     *baug_b = b.doubles(M * Kp * nbp);
@@ -221,14 +221,16 @@ static size_t nei_setup_layout(const bo_gp* gp, const bo_nei* nei, void* work, s
     *nz = b.doubles(M);
     *khinv = nei->baseline_is_train ? b.doubles(M * n * bo_pad8(n)) : nullptr;  // (K + s2 I)^-1
     *khs = (nei->baseline_is_train && gp->noise_vec) ? b.doubles(M * n * bo_pad8(n)) : nullptr;  // D (K + D)^-1
+    // six n x n temporaries of the second Cholesky-QR pass over the stacked root [ys inv(L); Q]
+    *qr = (nei->baseline_is_train && nei->fwd_cat && nei->bwd_cat) ? b.doubles(6 * M * n * bo_pad8(n)) : nullptr;
     *ok = b.ok;
     return b.off;
 }
 
 size_t bo_nei_setup_workspace_bytes(const bo_gp* gp, const bo_nei* nei) {
-    double *a, *b, *c, *d, *e, *f, *g;
+    double *a, *b, *c, *d, *e, *f, *g, *h;
     bool ok;
-    return nei_setup_layout(gp, nei, nullptr, 0, &a, &b, &c, &d, &e, &f, &g, &ok);
+    return nei_setup_layout(gp, nei, nullptr, 0, &a, &b, &c, &d, &e, &f, &g, &h, &ok);
 }
 
 int bo_nei_setup(bo_ctx* ctx, const bo_gp* gp, const bo_nei* nei, void* work, size_t work_bytes, int32_t* info,
@@ -239,9 +241,9 @@ int bo_nei_setup(bo_ctx* ctx, const bo_gp* gp, const bo_nei* nei, void* work, si
     const long n = gp->n, M = gp->M, np = bo_pad8(n), nb = nei->n_b, nbp = bo_pad8(nb), S = nei->S, Sp = bo_pad8(S);
     const long Kp = bo_kp(gp->d);
     const double ys2 = gp->y_std * gp->y_std;
-    double *baug_b, *kb, *fb, *scratch, *nz, *khinv, *khs;
+    double *baug_b, *kb, *fb, *scratch, *nz, *khinv, *khs, *qr;
     bool ok;
-    nei_setup_layout(gp, nei, work, work_bytes, &baug_b, &kb, &fb, &scratch, &nz, &khinv, &khs, &ok);
+    nei_setup_layout(gp, nei, work, work_bytes, &baug_b, &kb, &fb, &scratch, &nz, &khinv, &khs, &qr, &ok);
     if (!ok) return BO_ERR_WORKSPACE;
     const BoKernelHyper h = hyper_of(gp);
     BO_CUDA_TRY(cudaMemsetAsync(info, 0, sizeof(int32_t) * M, st));
@@ -310,7 +312,32 @@ int bo_nei_setup(bo_ctx* ctx, const bo_gp* gp, const bo_nei* nei, void* work, si
             BO_TRY(bo_fill(nei->fwd_cat, M * rowsF * np, 0.0, st));
             BO_TRY(gemm((int)n, (int)n, (int)nb, (int)M, 1.0, nei->qmat_t, nbp, n * nbp, nei->qmat, np, nb * np, ys2, khinv, np,
                         n * np, lw, ldk, n * ldk, BO_TRI_NONE, 1, st));
-            BO_TRY(bo_potrf_blocked(lw, ldk, n * ldk, (int)n, (int)M, nullptr, np, n * np, scratch, info, st));
+            // W = A^T A with the stacked root A = [ys inv(L); Q] has the SQUARED condition number of A, and so does the
+            // error of its Cholesky factor (measured: 5e-7 relative on the Schur block of a densely sampled low-d
+            // problem).  Second pass of Cholesky-QR ("CholeskyQR2"): A1 = A inv(R1) is nearly orthonormal, R2 = chol(A1^T A1)^T,
+            // R = R2 R1, which is as accurate as a Householder QR of A for cond(A) < 1e8.  L_W = R^T = L_1 L_G.
+            const long sq = n * np;  // one n x n region per model
+            double *x1 = qr, *x1t = qr + M * sq, *a1 = qr + 2 * M * sq, *a2 = qr + 3 * M * sq, *at = qr + 4 * M * sq,
+                   *gm = qr + 5 * M * sq;
+            BO_TRY(bo_fill(qr, 6 * M * sq, 0.0, st));
+            BO_TRY(bo_potrf_blocked(lw, ldk, n * ldk, (int)n, (int)M, x1, np, sq, scratch, info, st));
+            BO_TRY(bo_trtri_blocked(lw, ldk, n * ldk, (int)n, (int)M, x1, np, sq, scratch, st));  // x1 = inv(L_1)
+            BO_TRY(bo_transpose(x1, np, sq, x1t, np, sq, (int)n, (int)n, (int)M, st));                 // inv(R1)
+            BO_TRY(gemm((int)n, (int)n, (int)n, (int)M, gp->y_std, gp->linv_aug, np, (n + 1) * np, x1t, np, sq, 0.0, nullptr,
+                        0, 0, a1, np, sq, BO_TRI_A_LOWER, 0, st));                                      // ys inv(L) inv(R1)
+            BO_TRY(gemm((int)nb, (int)n, (int)n, (int)M, 1.0, nei->qmat, np, nb * np, x1t, np, sq, 0.0, nullptr, 0, 0, a2, np,
+                        sq, BO_TRI_NONE, 0, st));                                                       // Q inv(R1)
+            BO_TRY(bo_transpose(a1, np, sq, at, np, sq, (int)n, (int)n, (int)M, st));
+            BO_TRY(gemm((int)n, (int)n, (int)n, (int)M, 1.0, at, np, sq, a1, np, sq, 0.0, nullptr, 0, 0, gm, np, sq, BO_TRI_NONE,
+                        1, st));
+            BO_TRY(bo_transpose(a2, np, sq, at, np, sq, (int)nb, (int)n, (int)M, st));
+            BO_TRY(gemm((int)n, (int)n, (int)nb, (int)M, 1.0, at, np, sq, a2, np, sq, 1.0, gm, np, sq, gm, np, sq, BO_TRI_NONE, 1,
+                        st));                                                                           // G = A1^T A1
+            BO_TRY(bo_potrf_blocked(gm, np, sq, (int)n, (int)M, nullptr, np, sq, scratch, info, st));      // L_G
+            // x1 (inv(L_1), no longer needed) has an all-zero strict upper part: the lower-tile product lands there
+            BO_TRY(gemm((int)n, (int)n, (int)n, (int)M, 1.0, lw, ldk, n * ldk, gm, np, sq, 0.0, nullptr, 0, 0, x1, np, sq,
+                        BO_TRI_A_LOWER, 1, st));                                                        // L_W = L_1 L_G
+            BO_TRY(bo_copy2d(x1, np, sq, lw, ldk, n * ldk, (int)n, (int)n, (int)M, st));
             BO_TRY(bo_transpose(lw, ldk, n * ldk, nei->fwd_cat + S1p * np, np, rowsF * np, (int)n, (int)n, (int)M, st));
             // rows 0..S-1: Z_b Q, row S: alpha; then their transpose into the leading columns of the backward operand
             BO_TRY(gemm((int)S, (int)n, (int)nb, (int)M, 1.0, nei->zb_pad, nbp, 0, nei->qmat, np, nb * np, 0.0, nullptr, 0, 0,

@@ -1,0 +1,90 @@
+"""Edge sizes of the fused path against the oracle: smallest and largest q the kernels accept, every q-templated kernel
+variant (4 / 8 / 12 / 16 / 32), the widest input dimension, sample counts that are not multiples of anything, a single
+training point, a single t-batch -- values and gradients through the C ABI (engine.NEIState)."""
+import math
+
+import pytest
+import torch
+
+from botorch_b200.synthetic import Problem, default_lengthscale
+from oracle import qmc
+from tests.test_gpu_qlognei import _grad_rel
+from tests.util import gp_state, oracle_acq, oracle_gp, rel_err
+
+pytestmark = pytest.mark.gpu
+RTOL = 1e-9
+
+
+def _problem(n, d, q, S, kernel="rbf", M=None, seed=0):
+    g = torch.Generator().manual_seed(seed)
+    X = torch.rand(n, d, generator=g, dtype=torch.float64)
+    Y = torch.sin(3.0 * X.sum(-1, keepdim=True) / math.sqrt(d)) + 0.05 * torch.randn(n, 1, generator=g, dtype=torch.float64)
+    if M is None:
+        hyp = {"lengthscale": torch.full((d,), default_lengthscale(d), dtype=torch.float64),
+               "noise": torch.tensor(1e-2, dtype=torch.float64), "mean": torch.tensor(0.0, dtype=torch.float64)}  # fmt: skip
+    else:
+        hyp = {"lengthscale": 0.3 + torch.rand(M, d, generator=g, dtype=torch.float64),
+               "noise": 1e-3 + 0.05 * torch.rand(M, generator=g, dtype=torch.float64),
+               "mean": 0.1 * torch.randn(M, generator=g, dtype=torch.float64),
+               "outputscale": 0.5 + torch.rand(M, generator=g, dtype=torch.float64)}  # fmt: skip
+    return Problem(f"edge-n{n}-d{d}-q{q}", X, Y, kernel, hyp, q, S, 4, 16, standardize=n > 1)
+
+
+EDGES = [
+    # n,   d,  q,  S,   B, kernel,     M
+    (1, 2, 1, 8, 3, "rbf", None),  # one training point, no standardisation
+    (7, 3, 17, 5, 2, "rbf", None),  # q above every register-blocked variant but 32 -> generic gram, QT = 32 kernels
+    (40, 4, 32, 33, 2, "rbf", None),  # BO_MAX_Q
+    (33, 128, 2, 64, 3, "rbf", None),  # BO_MAX_D
+    (300, 5, 12, 100, 4, "rbf", None),  # QT = 12 reverse kernel, multi-tile GEMMs
+    (65, 6, 16, 257, 1, "rbf", None),  # QT = 16 forward kernel, single t-batch, odd sample count
+    (50, 7, 5, 1000, 2, "matern52", 3),  # ensemble, odd q, many samples
+    (129, 3, 9, 31, 5, "matern52", 2),
+]
+
+
+@pytest.mark.parametrize("n,d,q,S,B,kernel,M", EDGES)
+def test_edge_sizes_match_oracle(cuda, n, d, q, S, B, kernel, M):
+    from botorch_b200.engine import NEIState
+
+    p = _problem(n, d, q, S, kernel, M)
+    ogp = oracle_gp(p)
+    oacq = oracle_acq(p, ogp)
+    st = gp_state(p, ogp, cuda)
+    nei = NEIState(st, p.train_X.to(cuda), oacq.Z_b.to(cuda))
+    bounds = torch.stack([torch.zeros(d), torch.ones(d)]).double()
+    X = qmc.sobol_box(bounds, B, q, seed=77) if q * d <= 21201 else torch.rand(B, q, d, dtype=torch.float64)
+    Zq = oacq.Z_q(q).to(cuda).contiguous()
+    acq, info, work = nei.forward(X.to(cuda), Zq, oacq.tau_relu, oacq.tau_max, with_grad=True)
+    assert int(info.min()) >= 0
+    a_ref, g_ref = oacq.value_and_grad(X, mode="faithful")
+    if st.M == 1:
+        a = acq[0]
+        g = nei.backward(X.to(cuda), Zq, oacq.tau_relu, oacq.tau_max, torch.ones_like(acq), work)[0]
+    else:
+        from oracle.safe_math import logmeanexp
+
+        a = logmeanexp(acq.mT.cpu(), dim=-1)
+        w = torch.softmax(acq.mT, dim=-1).mT.contiguous()
+        g = nei.backward(X.to(cuda), Zq, oacq.tau_relu, oacq.tau_max, w, work).sum(0)
+    assert rel_err(a, a_ref, scale=0.0) < RTOL
+    assert _grad_rel(g, g_ref) < 1e-8
+
+
+def test_size_limits_are_reported_not_crashed(cuda):
+    """q > 32 and d > 128 are outside the per-candidate kernels: the C ABI answers BO_ERR_UNSUPPORTED (a Python
+    exception with the library's message), it never launches out of bounds."""
+    from botorch_b200 import _lib
+    from botorch_b200.engine import NEIState
+
+    p = _problem(20, 3, 2, 16)
+    ogp = oracle_gp(p)
+    oacq = oracle_acq(p, ogp)
+    st = gp_state(p, ogp, cuda)
+    nei = NEIState(st, p.train_X.to(cuda), oacq.Z_b.to(cuda))
+    X = torch.rand(2, 33, 3, dtype=torch.float64, device=cuda)
+    Zq = torch.randn(16, 33, dtype=torch.float64, device=cuda)
+    with pytest.raises(_lib.BoError, match="unsupported"):
+        nei.forward(X, Zq, 1e-6, 1e-2, with_grad=False)
+    with pytest.raises(Exception):
+        gp_state(_problem(10, 129, 1, 8), oracle_gp(_problem(10, 129, 1, 8)), cuda)
