@@ -41,6 +41,11 @@ CASES = [
     ("C2", {"n": 131}, 2, 5),
     ("C3", {"n": 300}, 8, 12),
     ("C4", {"M": 6}, 4, 9),
+    # the inferred-noise floor 1e-4 (gpytorch_modules.py:29): SURVEY.md 8(d)'s ill-conditioned stress case
+    ("C1", {"noise": 1e-4}, 2, 6),
+    ("C2", {"noise": 1e-4}, 4, 8),
+    ("C2", {"n": 400, "noise": 1e-4}, 3, 6),
+    ("C3", {"n": 300, "noise": 1e-4}, 8, 6),
 ]
 
 
