@@ -209,6 +209,41 @@ int bo_gp_setup(bo_ctx* ctx, const bo_gp* gp, void* work, size_t work_bytes, int
     return BO_OK;
 }
 
+// lw holds W = A^T A (lower block-triangle, pitch ldk) for the stacked root A = [ys inv(L); Q] (Q [nb x n] may be null);
+// on return lw = L_W with L_W L_W^T = W to the accuracy of a QR of A.
+// W has the SQUARED condition number of A, and so does the error of its Cholesky factor (measured: 5e-7 relative on the
+// Schur block of a densely sampled low-d problem).  Second pass of Cholesky-QR ("CholeskyQR2"): A1 = A inv(R1) is nearly
+// orthonormal, R2 = chol(A1^T A1)^T, R = R2 R1, which is as accurate as a Householder QR of A for cond(A) < 1e8.
+// L_W = R^T = L_1 L_G.  qr: six n x n regions per model.
+static int cholqr2_root(const bo_gp* gp, const double* qmat, long nb, double* lw, long ldk, double* qr, double* scratch,
+                        int32_t* info, cudaStream_t st) {
+    const long n = gp->n, M = gp->M, np = bo_pad8(n);
+    const long sq = n * np;  // one n x n region per model
+    double *x1 = qr, *x1t = qr + M * sq, *a1 = qr + 2 * M * sq, *a2 = qr + 3 * M * sq, *at = qr + 4 * M * sq,
+           *gm = qr + 5 * M * sq;
+    BO_TRY(bo_fill(qr, 6 * M * sq, 0.0, st));
+    BO_TRY(bo_potrf_blocked(lw, ldk, n * ldk, (int)n, (int)M, x1, np, sq, scratch, info, st));
+    BO_TRY(bo_trtri_blocked(lw, ldk, n * ldk, (int)n, (int)M, x1, np, sq, scratch, st));  // x1 = inv(L_1)
+    BO_TRY(bo_transpose(x1, np, sq, x1t, np, sq, (int)n, (int)n, (int)M, st));                 // inv(R1)
+    BO_TRY(gemm((int)n, (int)n, (int)n, (int)M, gp->y_std, gp->linv_aug, np, (n + 1) * np, x1t, np, sq, 0.0, nullptr, 0, 0,
+                a1, np, sq, BO_TRI_A_LOWER, 0, st));                                            // ys inv(L) inv(R1)
+    BO_TRY(bo_transpose(a1, np, sq, at, np, sq, (int)n, (int)n, (int)M, st));
+    BO_TRY(gemm((int)n, (int)n, (int)n, (int)M, 1.0, at, np, sq, a1, np, sq, 0.0, nullptr, 0, 0, gm, np, sq, BO_TRI_NONE, 1,
+                st));
+    if (qmat) {
+        BO_TRY(gemm((int)nb, (int)n, (int)n, (int)M, 1.0, qmat, np, nb * np, x1t, np, sq, 0.0, nullptr, 0, 0, a2, np, sq,
+                    BO_TRI_NONE, 0, st));                                                       // Q inv(R1)
+        BO_TRY(bo_transpose(a2, np, sq, at, np, sq, (int)nb, (int)n, (int)M, st));
+        BO_TRY(gemm((int)n, (int)n, (int)nb, (int)M, 1.0, at, np, sq, a2, np, sq, 1.0, gm, np, sq, gm, np, sq, BO_TRI_NONE, 1,
+                    st));                                                                       // G = A1^T A1
+    }
+    BO_TRY(bo_potrf_blocked(gm, np, sq, (int)n, (int)M, nullptr, np, sq, scratch, info, st));      // L_G
+    // x1 (inv(L_1), no longer needed) has an all-zero strict upper part: the lower-tile product lands there
+    BO_TRY(gemm((int)n, (int)n, (int)n, (int)M, 1.0, lw, ldk, n * ldk, gm, np, sq, 0.0, nullptr, 0, 0, x1, np, sq,
+                BO_TRI_A_LOWER, 1, st));                                                        // L_W = L_1 L_G
+    return bo_copy2d(x1, np, sq, lw, ldk, n * ldk, (int)n, (int)n, (int)M, st);
+}
+
 static size_t nei_setup_layout(const bo_gp* gp, const bo_nei* nei, void* work, size_t cap, double** baug_b,
                                double** kb, double** fb, double** scratch, double** nz, double** khinv, double** khs,
                                double** qr, bool* ok) {
@@ -312,32 +347,7 @@ int bo_nei_setup(bo_ctx* ctx, const bo_gp* gp, const bo_nei* nei, void* work, si
             BO_TRY(bo_fill(nei->fwd_cat, M * rowsF * np, 0.0, st));
             BO_TRY(gemm((int)n, (int)n, (int)nb, (int)M, 1.0, nei->qmat_t, nbp, n * nbp, nei->qmat, np, nb * np, ys2, khinv, np,
                         n * np, lw, ldk, n * ldk, BO_TRI_NONE, 1, st));
-            // W = A^T A with the stacked root A = [ys inv(L); Q] has the SQUARED condition number of A, and so does the
-            // error of its Cholesky factor (measured: 5e-7 relative on the Schur block of a densely sampled low-d
-            // problem).  Second pass of Cholesky-QR ("CholeskyQR2"): A1 = A inv(R1) is nearly orthonormal, R2 = chol(A1^T A1)^T,
-            // R = R2 R1, which is as accurate as a Householder QR of A for cond(A) < 1e8.  L_W = R^T = L_1 L_G.
-            const long sq = n * np;  // one n x n region per model
-            double *x1 = qr, *x1t = qr + M * sq, *a1 = qr + 2 * M * sq, *a2 = qr + 3 * M * sq, *at = qr + 4 * M * sq,
-                   *gm = qr + 5 * M * sq;
-            BO_TRY(bo_fill(qr, 6 * M * sq, 0.0, st));
-            BO_TRY(bo_potrf_blocked(lw, ldk, n * ldk, (int)n, (int)M, x1, np, sq, scratch, info, st));
-            BO_TRY(bo_trtri_blocked(lw, ldk, n * ldk, (int)n, (int)M, x1, np, sq, scratch, st));  // x1 = inv(L_1)
-            BO_TRY(bo_transpose(x1, np, sq, x1t, np, sq, (int)n, (int)n, (int)M, st));                 // inv(R1)
-            BO_TRY(gemm((int)n, (int)n, (int)n, (int)M, gp->y_std, gp->linv_aug, np, (n + 1) * np, x1t, np, sq, 0.0, nullptr,
-                        0, 0, a1, np, sq, BO_TRI_A_LOWER, 0, st));                                      // ys inv(L) inv(R1)
-            BO_TRY(gemm((int)nb, (int)n, (int)n, (int)M, 1.0, nei->qmat, np, nb * np, x1t, np, sq, 0.0, nullptr, 0, 0, a2, np,
-                        sq, BO_TRI_NONE, 0, st));                                                       // Q inv(R1)
-            BO_TRY(bo_transpose(a1, np, sq, at, np, sq, (int)n, (int)n, (int)M, st));
-            BO_TRY(gemm((int)n, (int)n, (int)n, (int)M, 1.0, at, np, sq, a1, np, sq, 0.0, nullptr, 0, 0, gm, np, sq, BO_TRI_NONE,
-                        1, st));
-            BO_TRY(bo_transpose(a2, np, sq, at, np, sq, (int)nb, (int)n, (int)M, st));
-            BO_TRY(gemm((int)n, (int)n, (int)nb, (int)M, 1.0, at, np, sq, a2, np, sq, 1.0, gm, np, sq, gm, np, sq, BO_TRI_NONE, 1,
-                        st));                                                                           // G = A1^T A1
-            BO_TRY(bo_potrf_blocked(gm, np, sq, (int)n, (int)M, nullptr, np, sq, scratch, info, st));      // L_G
-            // x1 (inv(L_1), no longer needed) has an all-zero strict upper part: the lower-tile product lands there
-            BO_TRY(gemm((int)n, (int)n, (int)n, (int)M, 1.0, lw, ldk, n * ldk, gm, np, sq, 0.0, nullptr, 0, 0, x1, np, sq,
-                        BO_TRI_A_LOWER, 1, st));                                                        // L_W = L_1 L_G
-            BO_TRY(bo_copy2d(x1, np, sq, lw, ldk, n * ldk, (int)n, (int)n, (int)M, st));
+            BO_TRY(cholqr2_root(gp, nei->qmat, nb, lw, ldk, qr, scratch, info, st));
             BO_TRY(bo_transpose(lw, ldk, n * ldk, nei->fwd_cat + S1p * np, np, rowsF * np, (int)n, (int)n, (int)M, st));
             // rows 0..S-1: Z_b Q, row S: alpha; then their transpose into the leading columns of the backward operand
             BO_TRY(gemm((int)S, (int)n, (int)nb, (int)M, 1.0, nei->zb_pad, nbp, 0, nei->qmat, np, nb * np, 0.0, nullptr, 0, 0,
@@ -353,18 +363,19 @@ int bo_nei_setup(bo_ctx* ctx, const bo_gp* gp, const bo_nei* nei, void* work, si
 
 long bo_nei_dense_rows(const bo_nei* nei) { return bo_pad8((nei->no_baseline ? 0 : (long)nei->S) + 1); }
 
-static size_t ei_setup_layout(const bo_gp* gp, void* work, size_t cap, double** scratch, bool* ok) {
+static size_t ei_setup_layout(const bo_gp* gp, void* work, size_t cap, double** scratch, double** qr, bool* ok) {
     Bump b(work, cap);
     *scratch = b.doubles(bo_linalg_scratch_doubles(gp->n, gp->M));
+    *qr = b.doubles(6 * (long)gp->M * gp->n * bo_pad8(gp->n));
     *ok = b.ok;
     return b.off;
 }
 
 size_t bo_ei_setup_workspace_bytes(const bo_gp* gp, const bo_nei* nei) {
     (void)nei;
-    double* a;
+    double *a, *b;
     bool ok;
-    return ei_setup_layout(gp, nullptr, 0, &a, &ok);
+    return ei_setup_layout(gp, nullptr, 0, &a, &b, &ok);
 }
 
 int bo_ei_setup(bo_ctx* ctx, const bo_gp* gp, const bo_nei* nei, void* work, size_t work_bytes, int32_t* info,
@@ -376,9 +387,9 @@ int bo_ei_setup(bo_ctx* ctx, const bo_gp* gp, const bo_nei* nei, void* work, siz
     const long n = gp->n, M = gp->M, np = bo_pad8(n), n1p = bo_pad8(n + 1);
     const long S1p = bo_nei_dense_rows(nei), ldk = S1p + np, rowsF = S1p + n;
     const double ys2 = gp->y_std * gp->y_std;
-    double* scratch;
+    double *scratch, *qr;
     bool ok;
-    ei_setup_layout(gp, work, work_bytes, &scratch, &ok);
+    ei_setup_layout(gp, work, work_bytes, &scratch, &qr, &ok);
     if (!ok) return BO_ERR_WORKSPACE;
     BO_CUDA_TRY(cudaMemsetAsync(info, 0, sizeof(int32_t) * M, st));
     double* lw = nei->bwd_cat + S1p;
@@ -387,7 +398,7 @@ int bo_ei_setup(bo_ctx* ctx, const bo_gp* gp, const bo_nei* nei, void* work, siz
     // W = ys^2 (K + s2 I)^-1 = ys^2 L^-T L^-1 (lower block-triangle), factored in place inside the backward operand
     BO_TRY(gemm((int)n, (int)n, (int)n, (int)M, ys2, gp->linv_aug_t, n1p, n * n1p, gp->linv_aug, np, (n + 1) * np, 0.0,
                 nullptr, 0, 0, lw, ldk, n * ldk, BO_TRI_A_UPPER, 1, st));
-    BO_TRY(bo_potrf_blocked(lw, ldk, n * ldk, (int)n, (int)M, nullptr, np, n * np, scratch, info, st));
+    BO_TRY(cholqr2_root(gp, nullptr, 0, lw, ldk, qr, scratch, info, st));
     BO_TRY(bo_transpose(lw, ldk, n * ldk, nei->fwd_cat + S1p * np, np, rowsF * np, (int)n, (int)n, (int)M, st));
     // row 0: alpha, and its transpose as column 0 of the backward operand
     BO_TRY(bo_copy2d(gp->linv_aug + n * np, np, (n + 1) * np, nei->fwd_cat, np, rowsF * np, 1, (int)n, (int)M, st));

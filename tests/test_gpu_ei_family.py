@@ -13,7 +13,8 @@ from tests.util import candidates, oracle_gp, rel_err
 
 pytestmark = pytest.mark.gpu
 RTOL = 1e-9
-CASES = [("C1", {}, 1, 10), ("C2", {}, 4, 16), ("C3", {"n": 256}, 8, 6), ("C4", {"M": 5}, 4, 7)]
+CASES = [("C1", {}, 1, 10), ("C2", {}, 4, 16), ("C3", {"n": 256}, 8, 6), ("C4", {"M": 5}, 4, 7),
+         ("C1", {"n": 150, "noise": 1e-4}, 3, 6)]  # densely sampled, noise floor: the root must not square cond(K)
 # the noisy incumbent (max over n baseline draws) is out of reach of the plain qNEI at the bigger training sets: it is
 # identically 0 there -- the reason qLogNEI exists -- so its parity is checked where improvement is possible
 NEI_CASES = [("C1", {}, 1, 10), ("C2", {"n": 30}, 4, 16), ("C3", {"n": 100}, 8, 6), ("C4", {"M": 5}, 4, 7)]
