@@ -135,14 +135,19 @@ def _cpu_step(acq, X, mode="faithful"):
     return time.perf_counter() - t0
 
 
-def _cpu_baseline(p, sample: int, repeats: int = 1):
+def _cpu_baseline(p, chunk: int, budget_s: float = 10.0):
+    """Oracle timed on the host cores on a bounded sample of the workload: chunks of ``chunk`` restarts (the reference's
+    ``batch_limit``; its (n_b+q) x (2n+q) block per restart bounds the chunk by memory) until ~``budget_s`` seconds."""
     torch.set_num_threads(os.cpu_count() or 1)
     acq = _cpu_setup(p)
-    X = _restart_batch(p, sample, seed=1)
+    X = _restart_batch(p, p.num_restarts, seed=1)
     _cpu_step(acq, X[:1])  # warm the caches (train Cholesky, L^-T) outside the timing
-    best = min(_cpu_step(acq, X) for _ in range(repeats))
+    best, sample = 0.0, 0
+    while sample + chunk <= X.shape[0] and best < budget_s:
+        best += _cpu_step(acq, X[sample : sample + chunk])
+        sample += chunk
     # SURVEY.md 8(d) also asks for the minimal algorithm (only the q new rows, trsm order) on the same cores
-    n_min = min(8 * sample, p.num_restarts)
+    n_min = min(8 * chunk, p.num_restarts)
     Xm = _restart_batch(p, n_min, seed=1)
     _cpu_step(acq, Xm[:1], "minimal")
     t_min = _cpu_step(acq, Xm, "minimal")
@@ -152,8 +157,8 @@ def _cpu_baseline(p, sample: int, repeats: int = 1):
         "unit": UNIT,
         "cores": torch.get_num_threads(),
         "kind": "port",
-        "sample": f"{sample} of the config's restarts (B x q x d = {sample} x {p.q} x {p.d}), fwd + autograd bwd, "
-                  f"faithful reference order of operations, float64 torch CPU, {best:.2f} s",
+        "sample": f"{sample} of the config's restarts in chunks of {chunk} (q x d = {p.q} x {p.d} each), fwd + autograd "
+                  f"bwd, faithful reference order of operations, float64 torch CPU, {best:.2f} s",
     }
 
 
