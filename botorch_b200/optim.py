@@ -16,6 +16,7 @@ gradient it consumes comes from the CUDA path.  The raw-sample and restart batch
 from __future__ import annotations
 
 import ctypes as C
+import math
 import time
 import warnings
 from typing import Callable, Dict, Optional, Tuple, Union
@@ -389,7 +390,7 @@ def gen_candidates_lbfgs(
     own curvature model, and the iterate never leaves the GPU: per round one ``bo_lbfgs_propose``, one fused
     forward + backward of the acquisition function, one ``bo_lbfgs_accept`` -- no host synchronisation except a
     convergence poll every ``check_every`` rounds.  Options: maxiter (2000), maxcor (10), ftol (2.22e-9), gtol (1e-5)
-    as in SciPy's L-BFGS-B, c1 (1e-4), check_every (8).
+    as in SciPy's L-BFGS-B, c1 (1e-4), check_every (8), compact (True: shrink the batch as restarts stop).
     """
     from . import _lib  # deferred: importing the package must not need the library
 
@@ -407,6 +408,7 @@ def gen_candidates_lbfgs(
     maxiter = int(options.get("maxiter", 2000))
     ftol, gtol = float(options.get("ftol", 2.220446049250313e-09)), float(options.get("gtol", 1e-5))
     c1, check_every = float(options.get("c1", 1e-4)), int(options.get("check_every", 8))
+    compact = bool(options.get("compact", True))
 
     def bound(b, fill):
         t = torch.full(shapeX[1:], fill, dtype=torch.float64, device=dev)
@@ -420,18 +422,30 @@ def gen_candidates_lbfgs(
                 g_prev=f64(B, D), S=f64(B, m, D), Y=f64(B, m, D), rho=f64(B, m), hist_count=i32(B), hist_head=i32(B),
                 p=f64(B, D), alpha=f64(B), x_trial=f64(B, D), state=i32(B), lower=bound(lower_bounds, -float("inf")),
                 upper=bound(upper_bounds, float("inf")), n_iter=i32(B))  # fmt: skip
-    st = _lib.BoLBFGS(B=B, D=D, m=m, **{k: _lib.ptr(v) for k, v in bufs.items()})
     lib, ctx = _lib.lib(), _lib.ctx(dev)
+    shared = ("lower", "upper")  # not per restart
+
+    def bind(b: dict):
+        return _lib.BoLBFGS(B=b["x"].shape[0], D=D, m=m, **{k: _lib.ptr(v) for k, v in b.items()})
 
     def evaluate(x_flat: Tensor):
-        X = x_flat.view(shapeX).to(initial_conditions.dtype).requires_grad_(True)
+        Bc = x_flat.shape[0]
+        X = x_flat.view(Bc, *shapeX[1:]).to(initial_conditions.dtype).requires_grad_(True)
         acq = acquisition_function(X)
         (grad,) = torch.autograd.grad(acq.sum(), X)
-        return (-acq.detach()).to(torch.float64).contiguous(), (-grad).to(torch.float64).reshape(B, D).contiguous()
+        return (-acq.detach()).to(torch.float64).contiguous(), (-grad).to(torch.float64).reshape(Bc, D).contiguous()
 
+    st = bind(bufs)
     f0, g0 = evaluate(bufs["x"])
     _lib.check(lib.bo_lbfgs_init(ctx, C.byref(st), _lib.ptr(f0), _lib.ptr(g0), _lib.stream_ptr(dev)))
-    rounds = 0
+    # Restarts stop at very different times.  Every poll the batch is compacted to the next size of a fixed ladder
+    # (B, B/2, B/4, ...: few distinct shapes, so the captured graphs are reused) that still holds all running restarts;
+    # stopped ones leave with their final point.
+    ladder = sorted({max(int(math.ceil(B / 2**k)), min(B, 16)) for k in range(0, 12)}, reverse=True)
+    final_x = bufs["x"].clone()
+    final_iter = torch.zeros(B, dtype=torch.int32, device=dev)
+    rows = torch.arange(B, device=dev)  # global restart index of every row of the current batch
+    rounds, evals = 0, B
     max_rounds = maxiter * 4  # accepted steps are bounded per restart by maxiter; rounds include rejected trials
     while rounds < max_rounds:
         _lib.check(lib.bo_lbfgs_propose(ctx, C.byref(st), _lib.stream_ptr(dev)))
@@ -439,17 +453,32 @@ def gen_candidates_lbfgs(
         _lib.check(lib.bo_lbfgs_accept(ctx, C.byref(st), _lib.ptr(ft), _lib.ptr(gt), c1, ftol, gtol, maxiter,
                                        _lib.stream_ptr(dev)))  # fmt: skip
         rounds += 1
+        evals += rows.numel()
         if rounds % check_every == 0:
-            if bool((bufs["state"] == 2).all()):
+            running = bufs["state"] != 2
+            n_run = int(running.sum())  # the one host synchronisation per poll
+            if n_run == 0:
                 break
             if timeout_sec is not None and time.monotonic() - start_time > timeout_sec:
                 break
+            target = min(s_ for s_ in ladder if s_ >= n_run)
+            if compact and target < rows.numel():
+                final_x[rows] = bufs["x"]
+                final_iter[rows] = bufs["n_iter"]
+                keep = torch.cat([running.nonzero().view(-1), (~running).nonzero().view(-1)])[:target]
+                bufs = {k: (v if k in shared else v[keep].contiguous()) for k, v in bufs.items()}
+                rows = rows[keep]
+                st = bind(bufs)
+    final_x[rows] = bufs["x"]
+    final_iter[rows] = bufs["n_iter"]
+    bufs = {"x": final_x, "n_iter": final_iter}
     candidates = bufs["x"].view(shapeX).to(initial_conditions.dtype)
     candidates = columnwise_clamp(candidates, lower_bounds, upper_bounds, raise_on_violation=True)
     with torch.no_grad():
         batch_acquisition = acquisition_function(candidates)
     _flush_warnings(acquisition_function)
-    gen_candidates_lbfgs.last_stats = {"rounds": rounds, "accepted_steps": bufs["n_iter"].clone()}
+    gen_candidates_lbfgs.last_stats = {"rounds": rounds, "accepted_steps": bufs["n_iter"].clone(),
+                                       "restart_evaluations": evals}
     return candidates, batch_acquisition
 
 
