@@ -7,6 +7,8 @@ There is no CPU fallback: importing is cheap, the first compute call raises if t
 """
 from .acquisition import (  # noqa: F401
     AcquisitionFunction,
+    IdentityMCObjective,
+    LinearMCObjective,
     prune_inferior_points,
     qExpectedImprovement,
     qLogExpectedImprovement,

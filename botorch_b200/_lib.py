@@ -65,6 +65,7 @@ class BoNEI(C.Structure):
         ("bwd_cat", C.c_void_p),
         ("reduction", C.c_int32),
         ("no_baseline", C.c_int32),
+        ("obj_weight", C.c_double),
     ]
 
 

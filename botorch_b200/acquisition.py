@@ -62,6 +62,45 @@ class AcquisitionFunction(Module):
         raise NotImplementedError
 
 
+class IdentityMCObjective(Module):
+    """objective(samples) = samples[..., 0] for a single-outcome model (acquisition/objective.py:282-298)."""
+
+    def forward(self, samples: Tensor, X: Optional[Tensor] = None) -> Tensor:
+        return samples.squeeze(-1)
+
+
+class LinearMCObjective(Module):
+    """objective(samples) = sum_i weights[i] samples[..., i] (acquisition/objective.py:301-341).  The fused path takes
+    the single-outcome case: the weight is applied inside the kernels (``bo_nei.obj_weight``), e.g. ``weights=[-1.]``
+    turns the acquisition functions into their minimisation counterparts."""
+
+    def __init__(self, weights: Tensor) -> None:
+        super().__init__()
+        if weights.dim() != 1:
+            raise ValueError("weights must be a one-dimensional tensor.")
+        self.register_buffer("weights", weights)
+
+    def forward(self, samples: Tensor, X: Optional[Tensor] = None) -> Tensor:
+        if samples.shape[-1] != self.weights.shape[-1]:
+            raise RuntimeError("Output shape of samples not equal to that of weights")
+        return torch.einsum("...m, m", [samples, self.weights])
+
+
+def _objective_weight(objective) -> float:
+    """The scalar the kernels multiply the samples with; anything but identity / one-outcome linear is off the path."""
+    if objective is None or isinstance(objective, IdentityMCObjective):
+        return 1.0
+    if isinstance(objective, LinearMCObjective) and objective.weights.numel() == 1:
+        w = float(objective.weights[0])
+        if w == 0.0 or not math.isfinite(w):
+            raise ValueError("the objective weight must be finite and non-zero")
+        return w
+    raise UnsupportedError(
+        f"objective {type(objective).__name__} is not on the fused path (SURVEY.md section 8f): use None, "
+        "IdentityMCObjective or a one-outcome LinearMCObjective"
+    )
+
+
 def legacy_ei_numerics_warning(legacy_name: str) -> None:
     """NumericsWarning pointing from a legacy EI class to its LogEI counterpart (exceptions/warnings.py:67-99)."""
     logei_name = {"qExpectedImprovement": "qLogExpectedImprovement",
@@ -89,9 +128,10 @@ def prune_inferior_points(
 ) -> Tensor:
     """Keep the points of ``X`` (n x d) that are the best one in at least one joint posterior sample
     (acquisition/utils.py:245-349).  The joint draw over the n points runs on the GPU (blocked Cholesky + GEMM)."""
-    for name, arg in (("objective", objective), ("posterior_transform", posterior_transform), ("constraints", constraints)):
+    for name, arg in (("posterior_transform", posterior_transform), ("constraints", constraints)):
         if arg is not None:
             raise UnsupportedError(f"`{name}` is not on the fused path yet (SURVEY.md section 8f): pass None")
+    obj_w = _objective_weight(objective)
     if marginalize_dim is None and model._is_ensemble:
         marginalize_dim = MCMC_DIM
     if X.ndim > 2:
@@ -106,7 +146,7 @@ def prune_inferior_points(
         if sampler is None:
             sampler = get_sampler(posterior=posterior, sample_shape=torch.Size([num_samples]))
         samples = sampler(posterior)
-    obj_vals = samples.squeeze(-1)  # IdentityMCObjective
+    obj_vals = obj_w * samples.squeeze(-1)  # IdentityMCObjective / one-outcome LinearMCObjective
     if obj_vals.ndim > 2:
         if obj_vals.ndim == 3 and marginalize_dim is not None:
             if marginalize_dim < 0:  # MCMC_DIM counts from the end of the model's batch shape + (q, m)
@@ -283,10 +323,11 @@ class qLogNoisyExpectedImprovement(_FusedImprovementBase):
             raise UnsupportedError(
                 f"the fused qLogNEI needs a botorch_b200 exact GP model, got {type(model).__name__}; no generic fallback"
             )
-        for name, arg in (("objective", objective), ("posterior_transform", posterior_transform),
-                          ("constraints", constraints)):  # fmt: skip
+        for name, arg in (("posterior_transform", posterior_transform), ("constraints", constraints)):
             if arg is not None:
                 raise UnsupportedError(f"`{name}` is not on the fused path yet (SURVEY.md section 8f): pass None")
+        self._obj_weight = _objective_weight(objective)
+        self.objective = objective if objective is not None else IdentityMCObjective()
         if not fat:
             raise UnsupportedError("fat=False (plain softplus / logsumexp smoothing) is not on the fused path")
         if X_baseline.dim() != 2:
@@ -299,7 +340,8 @@ class qLogNoisyExpectedImprovement(_FusedImprovementBase):
         self.sample_shape = torch.Size([DEFAULT_MC_SAMPLES]) if sampler is None else sampler.sample_shape
         self.set_X_pending(X_pending)
         if prune_baseline:  # logei.py:377-385
-            X_baseline = prune_inferior_points(model=model, X=X_baseline, marginalize_dim=marginalize_dim)
+            X_baseline = prune_inferior_points(model=model, X=X_baseline, objective=objective,
+                                               marginalize_dim=marginalize_dim)
         self._init_baseline(X_baseline, sampler, _factor_setup)
 
     # -- one-time setup (logei.py:364-420) ------------------------------------------------------------
@@ -319,7 +361,8 @@ class qLogNoisyExpectedImprovement(_FusedImprovementBase):
         Z_b = self.sampler.base_samples.reshape(S, n_b).to(device=gp.device, dtype=torch.float64).contiguous()
         # setup=False: allocate only; botorch_b200.distributed broadcasts the factors from the rank that computed them
         self._nei = engine.NEIState(gp, self.X_baseline.to(gp.device), Z_b, setup=setup,
-                                    reduction=engine.REDUCE_LOG if self._log else engine.REDUCE_PLAIN)
+                                    reduction=engine.REDUCE_LOG if self._log else engine.REDUCE_PLAIN,
+                                    obj_weight=self._obj_weight)
         self.q_in = -1
         self._Zq: Optional[Tensor] = None
         self.register_buffer("_baseline_best_f", None)
@@ -344,7 +387,7 @@ class qLogNoisyExpectedImprovement(_FusedImprovementBase):
 
     @property
     def baseline_obj(self) -> Tensor:
-        return self.baseline_samples.squeeze(-1)
+        return self._obj_weight * self.baseline_samples.squeeze(-1)
 
     def compute_best_f(self, obj: Tensor) -> Tensor:
         val = self._baseline_best_f
@@ -416,10 +459,12 @@ class qLogExpectedImprovement(_FusedImprovementBase):
         tau_relu: float = TAU_RELU,
     ) -> None:
         AcquisitionFunction.__init__(self, model=model)
-        self._check_fused_args(model, objective=objective, posterior_transform=posterior_transform, constraints=constraints)
+        self._check_fused_args(model, posterior_transform=posterior_transform, constraints=constraints)
         if not fat:
             raise UnsupportedError("fat=False (plain softplus / logsumexp smoothing) is not on the fused path")
         self.tau_relu, self.tau_max = float(tau_relu), float(tau_max)
+        self._obj_weight = _objective_weight(objective)
+        self.objective = objective if objective is not None else IdentityMCObjective()
         self._init_fixed_incumbent(best_f, sampler, X_pending)
 
     def _init_fixed_incumbent(self, best_f, sampler: Optional[MCSampler], X_pending: Optional[Tensor]) -> None:
@@ -431,7 +476,8 @@ class qLogExpectedImprovement(_FusedImprovementBase):
         self.sampler = sampler
         self.set_X_pending(X_pending)
         self._nei = engine.EIState(gp, self.best_f.to(gp.device), self.sample_shape[0],
-                                   reduction=engine.REDUCE_LOG if self._log else engine.REDUCE_PLAIN)  # fmt: skip
+                                   reduction=engine.REDUCE_LOG if self._log else engine.REDUCE_PLAIN,
+                                   obj_weight=self._obj_weight)  # fmt: skip
         self.q_in, self._Zq = -1, None
 
     def _set_sampler(self, q_in: int) -> None:
@@ -457,5 +503,7 @@ class qExpectedImprovement(qLogExpectedImprovement):
                  posterior_transform=None, X_pending: Optional[Tensor] = None, constraints=None, eta=1e-3) -> None:  # fmt: skip
         legacy_ei_numerics_warning(type(self).__name__)
         AcquisitionFunction.__init__(self, model=model)
-        self._check_fused_args(model, objective=objective, posterior_transform=posterior_transform, constraints=constraints)
+        self._check_fused_args(model, posterior_transform=posterior_transform, constraints=constraints)
+        self._obj_weight = _objective_weight(objective)
+        self.objective = objective if objective is not None else IdentityMCObjective()
         self._init_fixed_incumbent(best_f, sampler, X_pending)

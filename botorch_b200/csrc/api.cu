@@ -315,7 +315,8 @@ int bo_nei_setup(bo_ctx* ctx, const bo_gp* gp, const bo_nei* nei, void* work, si
     // baseline samples f_b[s] = mean_b + L_b z_s and best_f[s] = max_i f_b[s][i]
     BO_TRY(gemm((int)nb, (int)S, (int)nb, (int)M, 1.0, nei->lb, nbp, nb * nbp, nei->zb_t, Sp, 0, 0.0, nullptr, 0, 0, fb, Sp,
                 nb * Sp, BO_TRI_A_LOWER, 0, st));
-    BO_TRY(bo_col_max(fb, nb * Sp, Sp, nei->mean_b, nbp, (int)nb, (int)S, (int)M, nei->best_f, Sp, st));
+    BO_TRY(bo_col_max(fb, nb * Sp, Sp, nei->mean_b, nbp, (int)nb, (int)S, (int)M, nei->best_f, Sp,
+                      nei->obj_weight != 0.0 ? nei->obj_weight : 1.0, st));
     if (nei->baseline_is_train && nei->qmat && nei->qmat_t) {
         // X_baseline == train_X: Sigma(X_b, X) = ys^2 (K - K Khat^-1 K_x) = ys^2 s2 Khat^-1 K_x with Khat = K + s2 I,
         // so bl_chol^T = inv(L_b) Sigma(X_b, X) = Q K(X_tr, X),  Q = ys^2 s2 inv(L_b) Khat^-1  (no cancellation).
@@ -503,6 +504,7 @@ BoCandArgs cand_args(const bo_gp* gp, const bo_nei* nei, int B, int q, const dou
     a.Sp = nei ? bo_pad8(nei->S) : 0;
     a.tau_relu = tau_relu; a.tau_max = tau_max;
     a.reduction = nei ? nei->reduction : BO_REDUCE_LOG;
+    a.obj_w = (nei && nei->obj_weight != 0.0) ? nei->obj_weight : 1.0;
     a.ldn = w.ldn;
     a.V = w.W1; a.strideV = w.regionStride;
     a.BL = w.W3; a.strideBL = w.regionStride;

@@ -489,7 +489,7 @@ __global__ void __launch_bounds__(CAND_THREADS, (QT <= 8 ? 4 : 1)) cand_fwd_kern
                     if (k <= j) v += c.Lq[j * q + k] * zq[k];
                 F[(long)s * a.ldn + c0 + j] = v;
                 if (!isfinite(v)) bad = 1;
-                li[j] = plain ? fmax(v - bf, 0.0) : log_fatplus(v - bf, a.tau_relu, inv_tau_relu);
+                li[j] = plain ? fmax(a.obj_w * v - bf, 0.0) : log_fatplus(a.obj_w * v - bf, a.tau_relu, inv_tau_relu);
             }
         }
         double m;
@@ -574,7 +574,7 @@ __global__ void __launch_bounds__(CAND_THREADS, (QT <= 8 ? 4 : 1)) cand_bwd_kern
             f[j] = 0.0; li[j] = 0.0; zq[j] = 0.0;
             if (j < q) {
                 f[j] = F[(long)s * a.ldn + c0 + j];
-                li[j] = plain ? fmax(f[j] - bf, 0.0) : log_fatplus(f[j] - bf, a.tau_relu, inv_tau_relu);
+                li[j] = plain ? fmax(a.obj_w * f[j] - bf, 0.0) : log_fatplus(a.obj_w * f[j] - bf, a.tau_relu, inv_tau_relu);
                 zq[j] = a.Zq[(long)s * q + j];
             }
         }
@@ -600,10 +600,10 @@ __global__ void __launch_bounds__(CAND_THREADS, (QT <= 8 ? 4 : 1)) cand_bwd_kern
             double df = 0.0;
             if (j < q) {
                 if (plain) {
-                    df = (li[j] == m && f[j] - bf >= 0.0) ? g * w / (double)ties : 0.0;
+                    df = (li[j] == m && a.obj_w * f[j] - bf >= 0.0) ? a.obj_w * g * w / (double)ties : 0.0;
                 } else {
-                    const double dli = isinf(li[j]) ? 0.0 : dlog_fatplus(f[j] - bf, a.tau_relu, inv_tau_relu);
-                    df = g * w * gm[j] * dli;
+                    const double dli = isinf(li[j]) ? 0.0 : dlog_fatplus(a.obj_w * f[j] - bf, a.tau_relu, inv_tau_relu);
+                    df = a.obj_w * g * w * gm[j] * dli;
                 }
                 F[(long)s * a.ldn + c0 + j] = df;
             }
@@ -949,14 +949,14 @@ __global__ void col_mean_var_kernel(const double* V, long strideV, long ldn, int
 }
 
 __global__ void col_max_kernel(const double* Fb, long strideF, long ldf, const double* mean_b, long strideMb,
-                               int rows, int cols, double* out, long strideOut) {
+                               int rows, int cols, double* out, long strideOut, double w) {
     const int z = blockIdx.y;
     const int s = blockIdx.x * blockDim.x + threadIdx.x;
     if (s >= cols) return;
     const double* Fz = Fb + (long)z * strideF;
     const double* mb = mean_b + (long)z * strideMb;
     double m = -INFINITY;
-    for (int i = 0; i < rows; i++) m = fmax(m, mb[i] + Fz[(long)i * ldf + s]);
+    for (int i = 0; i < rows; i++) m = fmax(m, w * (mb[i] + Fz[(long)i * ldf + s]));  // objective value w * f
     out[(long)z * strideOut + s] = m;
 }
 
@@ -1128,9 +1128,9 @@ int bo_col_mean_var(const double* V, long strideV, long ldn, int n, long Nc, int
     return BO_OK;
 }
 int bo_col_max(const double* Fb, long strideF, long ldf, const double* mean_b, long strideMb, int rows, int cols,
-               int M, double* out, long strideOut, cudaStream_t stream) {
+               int M, double* out, long strideOut, double obj_w, cudaStream_t stream) {
     dim3 grid((cols + 127) / 128, M);
-    col_max_kernel<<<grid, 128, 0, stream>>>(Fb, strideF, ldf, mean_b, strideMb, rows, cols, out, strideOut);
+    col_max_kernel<<<grid, 128, 0, stream>>>(Fb, strideF, ldf, mean_b, strideMb, rows, cols, out, strideOut, obj_w);
     BO_LAUNCH_CHECK();
     return BO_OK;
 }

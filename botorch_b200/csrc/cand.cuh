@@ -35,6 +35,7 @@ struct BoCandArgs {
     const double* mu_row; long strideMu; // optional [ldn] row holding alpha . K(X_tr, x) (else row n of V)
     double* F;        long strideF;    // [S x ldn]      in: Z_b BL ; out: samples f (fwd) / df (bwd)
     int f_zero;                        // 1: no baseline part (qEI / qLogEI): F is write-only scratch for the samples
+    double obj_w;                      // objective = obj_w * f (LinearMCObjective on the single outcome); best_f lives in objective space
     int reduction;                     // BO_REDUCE_LOG: log_fatplus / fatmax / logmeanexp; BO_REDUCE_PLAIN: relu / amax / mean
     double* Lq;                        // [M][B][q*q]    br_chol
     double* lse;                       // [M][B]         logsumexp over MC samples
@@ -81,9 +82,9 @@ int bo_col_mean_var(const double* V, long strideV, long ldn, int n, long Nc, int
                     const double* mean_const, const double* outputscale, double* mean, double* var,
                     cudaStream_t stream);
 
-// best_f[z][s] = max_i (mean_b[z][i] + Fb[z][i][s])
+// best_f[z][s] = max_i obj_w * (mean_b[z][i] + Fb[z][i][s])
 int bo_col_max(const double* Fb, long strideF, long ldf, const double* mean_b, long strideMb, int rows, int cols,
-               int M, double* out, long strideOut, cudaStream_t stream);
+               int M, double* out, long strideOut, double obj_w, cudaStream_t stream);
 
 int bo_ts_argmax_launch(int M, long Nc, const double* mean, const double* var, const double* z, double* out_val,
                         long long* out_idx, cudaStream_t stream);

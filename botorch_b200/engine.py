@@ -191,7 +191,7 @@ class NEIState:
     """Baseline factors of qLogNEI (V_b, L_b and its inverse, base samples, best_f) and the fused fwd/bwd."""
 
     def __init__(self, gp: GPState, X_baseline: Tensor, Z_b: Tensor, setup: bool = True,
-                 reduction: int = REDUCE_LOG) -> None:  # fmt: skip
+                 reduction: int = REDUCE_LOG, obj_weight: float = 1.0) -> None:  # fmt: skip
         dev = gp.device
         self.gp = gp
         self.device = dev
@@ -227,6 +227,7 @@ class NEIState:
             lb_inv_t=ptr(self.lb_inv_t), zb_pad=ptr(self.zb_pad), zb_t=ptr(self.zb_t), mean_b=ptr(self.mean_b),
             best_f=ptr(self.best_f_pad), qmat=ptr(self.qmat), qmat_t=ptr(self.qmat_t),
             fwd_cat=ptr(self.fwd_cat), bwd_cat=ptr(self.bwd_cat), reduction=int(reduction), no_baseline=0,
+            obj_weight=float(obj_weight),
         )  # fmt: skip
         self.jitter = torch.zeros(M, dtype=torch.float64, device=dev)
         if not setup:
@@ -306,7 +307,8 @@ class EIState(NEIState):
     ys^2 (K + s2 I)^-1 (``bo_ei_setup``), so the q x q posterior covariance is ys^2 k(X,X) - U^T U.
     """
 
-    def __init__(self, gp: GPState, best_f: Tensor, S: int, setup: bool = True, reduction: int = REDUCE_LOG) -> None:
+    def __init__(self, gp: GPState, best_f: Tensor, S: int, setup: bool = True, reduction: int = REDUCE_LOG,
+                 obj_weight: float = 1.0) -> None:  # fmt: skip
         dev = gp.device
         self.gp, self.device = gp, dev
         self.S, self.n_b, self.is_train = int(S), 0, False
@@ -321,7 +323,8 @@ class EIState(NEIState):
         self.bwd_cat = z(M, n, 8 + gp.np_)
         self.info = torch.zeros(M, dtype=torch.int32, device=dev)
         self.c = BoNEI(n_b=0, S=self.S, baseline_is_train=0, best_f=ptr(self.best_f_pad), fwd_cat=ptr(self.fwd_cat),
-                       bwd_cat=ptr(self.bwd_cat), reduction=int(reduction), no_baseline=1)  # fmt: skip
+                       bwd_cat=ptr(self.bwd_cat), reduction=int(reduction), no_baseline=1,
+                       obj_weight=float(obj_weight))  # fmt: skip
         if not setup:
             return
         lib = _lib.lib()

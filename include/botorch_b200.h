@@ -104,6 +104,8 @@ typedef struct bo_nei {
                                 *    new points only, best_f [M][Sp] supplied by the caller; n_b = 0, only S, best_f, fwd_cat,
                                 *    bwd_cat are used, with S1p = 8: fwd_cat = [alpha; 0 x 7; L_W^T], L_W L_W^T = ys^2 (K+s2 I)^-1
                                 *    (filled by bo_ei_setup) */
+    double obj_weight;         /* objective = obj_weight * f (LinearMCObjective with one outcome, acquisition/objective.py);
+                                * 0 means 1.  best_f (computed or supplied) is in objective space. */
 } bo_nei;
 
 typedef struct bo_ctx bo_ctx;

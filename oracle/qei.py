@@ -37,8 +37,9 @@ class _OracleEIBase:
     log = True
 
     def __init__(self, model: OracleGP, best_f, num_samples: int = 512, seed: int = 1234, tau_relu: float = TAU_RELU,
-                 tau_max: float = TAU_MAX):  # fmt: skip
+                 tau_max: float = TAU_MAX, obj_weight: float = 1.0):  # fmt: skip
         self.model = model
+        self.obj_weight = float(obj_weight)
         self.best_f = torch.as_tensor(best_f, dtype=torch.float64)
         self.S, self.seed = num_samples, seed
         self.tau_relu, self.tau_max = tau_relu, tau_max
@@ -56,7 +57,7 @@ class _OracleEIBase:
     def forward(self, X: Tensor) -> Tensor:
         if X.dim() == 2:
             X = X.unsqueeze(0)
-        obj = self.samples(X)  # S x B x (M?) x q
+        obj = self.obj_weight * self.samples(X)  # S x B x (M?) x q
         bf = self.best_f  # scalar or (M)
         if self.log:
             li = safe_math.log_improvement(obj, bf, tau=self.tau_relu)

@@ -30,8 +30,10 @@ class OracleQLogNEI:
         seed: int = 1234,
         tau_relu: float = TAU_RELU,
         tau_max: float = TAU_MAX,
+        obj_weight: float = 1.0,
     ):
         self.model = model
+        self.obj_weight = float(obj_weight)  # one-outcome LinearMCObjective (objective.py:217-256): obj = w * samples
         self.X_baseline = X_baseline
         self.S = num_samples
         self.seed = seed
@@ -46,7 +48,7 @@ class OracleQLogNEI:
             # MVN.rsample with base samples: root @ z + loc
             samples = torch.einsum("...ij,sj->s...i", self.baseline_L, self.Z_b) + mean_b
             self.baseline_samples = samples  # S x (M?) x n_b
-            self.best_f = samples.max(dim=-1).values  # S x (M?)   (acquisition/utils.py:125-129)
+            self.best_f = (self.obj_weight * samples).max(dim=-1).values  # S x (M?)   (acquisition/utils.py:125-129)
 
     # -- base samples ----------------------------------------------------------------------
     def Z_q(self, q: int) -> Tensor:
@@ -113,9 +115,10 @@ class OracleQLogNEI:
             return self._reduce_uncached(obj, base)
         else:
             raise ValueError(mode)
-        return self._reduce(obj, self.best_f)
+        return self._reduce(self.obj_weight * obj, self.best_f)
 
     def _reduce_uncached(self, obj: Tensor, base: Tensor) -> Tensor:
+        obj, base = self.obj_weight * obj, self.obj_weight * base
         best_f = base.max(dim=-1).values  # S x B x (M?)
         li = safe_math.log_improvement(obj, best_f, tau=self.tau_relu)
         acq = safe_math.logmeanexp(safe_math.fatmax(li, dim=-1, tau=self.tau_max), dim=0)

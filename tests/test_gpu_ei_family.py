@@ -130,3 +130,58 @@ def test_qnei_prunes_baseline_by_default(cuda):
     assert float(ref.max()) > 0.0
     assert rel_err(val, ref) < RTOL
     assert rel_err(g, g_ref) < 1e-8
+
+
+@pytest.mark.parametrize("kind", ["qlognei", "qnei", "qlogei", "qei"])
+def test_linear_objective_weight(cuda, kind):
+    """objective=LinearMCObjective(weights=[w]) on the one-outcome model (objective.py:217-256; w = -1 is how the
+    reference minimises): samples are scaled by w before the incumbent and the improvement are formed."""
+    w = -1.0 if kind != "qlogei" else -0.5
+    p = make_problem("C2", n=30)
+    ogp = oracle_gp(p)
+    model = _model(p, cuda)
+    objective = bb.LinearMCObjective(torch.tensor([w], dtype=torch.float64, device=cuda))
+    order = torch.argsort(p.train_Y.view(-1))  # candidates near the SMALLEST observations: w < 0 rewards those
+    gen = torch.Generator().manual_seed(11)
+    X = (p.train_X[order[torch.arange(12) % 6]] + 0.05 * torch.randn(12, p.d, generator=gen, dtype=torch.float64))
+    X = torch.cat([X.clamp(0, 1).reshape(4, 3, p.d), candidates(p, 2, q=3)])
+    with warnings.catch_warnings():
+        warnings.simplefilter("ignore", bb.exceptions.NumericsWarning)
+        if kind in ("qlognei", "qnei"):
+            ocls = OracleQNEI if kind == "qnei" else __import__("oracle.qlognei", fromlist=["x"]).OracleQLogNEI
+            oacq = ocls(ogp, p.train_X, num_samples=p.mc_samples, seed=1234, obj_weight=w)
+            cls = bb.qNoisyExpectedImprovement if kind == "qnei" else bb.qLogNoisyExpectedImprovement
+            acqf = cls(model, p.train_X.to(cuda), sampler=_sampler(p), objective=objective, prune_baseline=False)
+        else:
+            with torch.no_grad():
+                mean, _ = ogp.posterior(X)
+            best_f = (w * mean).amax(dim=-1).median(dim=0).values
+            ocls = OracleQEI if kind == "qei" else OracleQLogEI
+            oacq = ocls(ogp, best_f, num_samples=p.mc_samples, seed=1234, obj_weight=w)
+            cls = bb.qExpectedImprovement if kind == "qei" else bb.qLogExpectedImprovement
+            acqf = cls(model, best_f.to(cuda), sampler=_sampler(p), objective=objective)
+    val, g = _value_and_grad(acqf, X, cuda)
+    ref, g_ref = oacq.value_and_grad(X)
+    log = kind.startswith("qlog")
+    assert log or int((ref > 0).sum()) >= 2
+    assert rel_err(val, ref, scale=0.0 if log else None) < RTOL
+    assert rel_err(g, g_ref) < 1e-8
+    # the weight matters: the identity objective gives different numbers
+    if kind == "qlognei":
+        plain = bb.qLogNoisyExpectedImprovement(model, p.train_X.to(cuda), sampler=_sampler(p), prune_baseline=False)
+        with torch.no_grad():
+            assert not torch.allclose(plain(X.to(cuda)), val)
+
+
+def test_prune_inferior_points_with_objective(cuda):
+    """utils.py:252-341 with a negating objective keeps the points that are best under w * f."""
+    p = make_problem("C2", n=40)
+    model = _model(p, cuda)
+    obj = bb.LinearMCObjective(torch.tensor([-1.0], dtype=torch.float64, device=cuda))
+    keep_max = bb.prune_inferior_points(model, p.train_X.to(cuda))
+    keep_min = bb.prune_inferior_points(model, p.train_X.to(cuda), objective=obj)
+    y = p.train_Y.view(-1)
+    def _rows(K):
+        return [int((p.train_X == r).all(-1).nonzero()[0, 0]) for r in K.cpu()]
+    assert int(torch.argmax(y)) in _rows(keep_max) and int(torch.argmin(y)) in _rows(keep_min)
+    assert set(_rows(keep_max)) != set(_rows(keep_min))
