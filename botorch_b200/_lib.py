@@ -142,9 +142,12 @@ def _declare(lib: C.CDLL) -> None:
     lib.bo_potrf_workspace_bytes.restype = sz
     lib.bo_potrf_workspace_bytes.argtypes = [i32, i32]
     lib.bo_potrf.argtypes = [vp, i32, i32, vp, i64, i64, vp, vp, sz, vp, vp]
+    lib.bo_mll_workspace_bytes.restype = sz
+    lib.bo_mll_workspace_bytes.argtypes = [gp]
+    lib.bo_mll_value_grad.argtypes = [vp, gp, vp, sz, vp, vp, vp, vp]
     for name in (
         "bo_ctx_create bo_gp_setup bo_nei_setup bo_ei_setup bo_qlognei_fwd bo_qlognei_bwd bo_posterior_joint bo_posterior_joint_bwd "
-        "bo_posterior_mean_var bo_ts_argmax bo_argmax bo_dgemm bo_kernel_matrix bo_potrf"
+        "bo_posterior_mean_var bo_ts_argmax bo_argmax bo_dgemm bo_kernel_matrix bo_potrf bo_mll_value_grad"
     ).split():
         getattr(lib, name).restype = i32
 

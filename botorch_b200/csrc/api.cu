@@ -851,6 +851,203 @@ int bo_argmax(bo_ctx* ctx, long n, const double* v, double* out_val, int64_t* ou
 }
 
 // ------------------------------------------------------------------------------------------------
+// exact marginal log likelihood, value + gradient w.r.t. the hyperparameters
+// ------------------------------------------------------------------------------------------------
+}  // extern "C"
+
+namespace {
+
+constexpr int MLL_CHUNKS = 16;  // row chunks of the column sum-of-squares of inv(L) (summed in order)
+
+// Bn[z][k][j] = -inv(L)[z][k][j] (k < n), alpha[z][j] (k == n): [inv(L)^T | alpha] Bn = alpha alpha^T - (K + s2 I)^-1
+__global__ void mll_negate_kernel(const double* linv_aug, double* Bn, long np, int n) {
+    const long z = blockIdx.z, k = blockIdx.y;
+    const long base = z * (long)(n + 1) * np + k * np;
+    for (long j = blockIdx.x * (long)blockDim.x + threadIdx.x; j < np; j += (long)gridDim.x * blockDim.x)
+        Bn[base + j] = (k < n) ? -linv_aug[base + j] : linv_aug[base + j];
+}
+// xct[t][j] = train_X[j][t] - center[t] (t < d), 1 (t == d)
+__global__ void mll_xct_kernel(const double* X, const double* center, double* xct, long np, int n, int d) {
+    const int t = blockIdx.y;
+    const int j = blockIdx.x * blockDim.x + threadIdx.x;
+    if (j < np) xct[(long)t * np + j] = (j < n) ? (t < d ? X[(long)j * d + t] - center[t] : 1.0) : 0.0;
+}
+// part[z][c][j] = sum over the c-th row chunk of inv(L)[z][k][j]^2   (diag of (K + s2 I)^-1 = column norms of inv(L))
+__global__ void mll_colsq_kernel(const double* linv_aug, double* part, long np, int n) {
+    const long z = blockIdx.z;
+    const int c = blockIdx.y, j = blockIdx.x * blockDim.x + threadIdx.x;
+    if (j >= n) return;
+    const int rows = (n + MLL_CHUNKS - 1) / MLL_CHUNKS;
+    int k0 = c * rows, k1 = k0 + rows < n ? k0 + rows : n;
+    if (k0 < j) k0 = j;  // inv(L) is lower triangular
+    const double* L = linv_aug + z * (long)(n + 1) * np;
+    double s = 0.0;
+    for (int k = k0; k < k1; k++) { const double v = L[(long)k * np + j]; s += v * v; }
+    part[(z * MLL_CHUNKS + c) * np + j] = s;
+}
+
+__device__ double mll_block_sum(double v, double* sm) {  // fixed-order tree: deterministic
+    const int tid = threadIdx.x;
+    sm[tid] = v;
+    __syncthreads();
+    for (int s = blockDim.x / 2; s > 0; s >>= 1) {
+        if (tid < s) sm[tid] += sm[tid + s];
+        __syncthreads();
+    }
+    const double r = sm[0];
+    __syncthreads();
+    return r;
+}
+
+struct MllFin {
+    int n, d, ks;
+    long np, strideH, strideKs;
+    const double *H, *xct, *inv_ls, *outputscale, *noise, *noise_vec, *jitter, *mean, *targets, *linv_aug, *chol, *part;
+    double *value, *grad;
+};
+// grid (d+1, M): blocks 0..d-1 the lengthscale gradients, block d value + noise / mean / outputscale gradients
+__global__ void __launch_bounds__(256) mll_finalize_kernel(const MllFin a) {
+    __shared__ double sm[256];
+    const int z = blockIdx.y, t = blockIdx.x, tid = threadIdx.x, n = a.n, d = a.d;
+    double* g = a.grad + (long)z * (d + 3);
+    if (t < d) {
+        double s = 0.0;
+        for (int j = tid; j < n; j += blockDim.x) {
+            double hd = 0.0, ht = 0.0;
+            for (int k = 0; k < a.ks; k++) {
+                const double* Hk = a.H + (long)z * a.strideH + (long)k * a.strideKs;
+                hd += Hk[(long)d * a.np + j];
+                ht += Hk[(long)t * a.np + j];
+            }
+            const double x = a.xct[(long)t * a.np + j];
+            s += x * (x * hd - ht);
+        }
+        s = mll_block_sum(s, sm);
+        if (tid == 0) { const double il = a.inv_ls[(long)z * d + t]; g[t] = s * il * il * il; }
+        return;
+    }
+    const double* alpha = a.linv_aug + (long)z * (n + 1) * a.np + (long)n * a.np;
+    const double* L = a.chol + (long)z * n * a.np;
+    const double jit = a.jitter ? a.jitter[z] : 0.0;
+    double ra = 0.0, sa = 0.0, ld = 0.0, trw = 0.0, trwd = 0.0;
+    for (int i = tid; i < n; i += blockDim.x) {
+        const double al = alpha[i];
+        ra += (a.targets[i] - a.mean[z]) * al;
+        sa += al;
+        ld += log(L[(long)i * a.np + i]);
+        double kd = 0.0;
+        for (int c = 0; c < MLL_CHUNKS; c++) kd += a.part[((long)z * MLL_CHUNKS + c) * a.np + i];
+        const double w = al * al - kd;
+        trw += w;
+        trwd += w * ((a.noise_vec ? a.noise_vec[(long)z * n + i] : a.noise[z]) + jit);
+    }
+    ra = mll_block_sum(ra, sm); sa = mll_block_sum(sa, sm); ld = mll_block_sum(ld, sm);
+    trw = mll_block_sum(trw, sm); trwd = mll_block_sum(trwd, sm);
+    if (tid == 0) {
+        a.value[z] = -0.5 * ra - ld - 0.5 * n * 1.8378770664093454835606594728112;  // log(2 pi)
+        const double os = a.outputscale ? a.outputscale[z] : 1.0;
+        g[d] = (ra - n - trwd) / (2.0 * os);  // sum_ij W_ij K_ij = tr(W (Khat - D)) = r.alpha - n - tr(W D)
+        g[d + 1] = 0.5 * trw;
+        g[d + 2] = sa;
+    }
+}
+
+struct MllWork {
+    void* setup; size_t setup_bytes;
+    double *baug, *Kg, *Bn, *G, *xct, *H, *part;
+    int ks; bool ok; size_t bytes;
+};
+MllWork mll_layout(const bo_gp* gp, void* work, size_t cap) {
+    MllWork w{};
+    const long n = gp->n, M = gp->M, np = bo_pad8(n), Kp = bo_kp(gp->d);
+    w.setup_bytes = (size_t)bo_round_up((long)bo_gp_setup_workspace_bytes(gp), 256);
+    Bump b(work, cap);
+    w.setup = b.doubles((long)(w.setup_bytes / sizeof(double)));
+    w.baug = b.doubles(M * Kp * np);
+    w.Kg = b.doubles(M * n * np);
+    w.Bn = b.doubles(M * (n + 1) * np);
+    w.G = b.doubles(M * n * np);
+    w.xct = b.doubles((long)(gp->d + 1) * np);
+    w.ks = hsplit(gp);
+    w.H = b.doubles(M * w.ks * (long)(gp->d + 1) * np);
+    w.part = b.doubles(M * MLL_CHUNKS * np);
+    w.ok = b.ok;
+    w.bytes = b.off;
+    return w;
+}
+
+}  // namespace
+
+extern "C" {
+
+size_t bo_mll_workspace_bytes(const bo_gp* gp) { return mll_layout(gp, nullptr, 0).bytes; }
+
+int bo_mll_value_grad(bo_ctx* ctx, const bo_gp* gp, void* work, size_t work_bytes, double* value, double* grad,
+                      int32_t* info, void* stream) {
+    if (!ctx || !valid_gp(gp) || !work || !value || !grad || !info || !gp->xt_aug) return BO_ERR_INVALID;
+    cudaStream_t st = (cudaStream_t)stream;
+    const MllWork w = mll_layout(gp, work, work_bytes);
+    if (!w.ok) return BO_ERR_WORKSPACE;
+    const long n = gp->n, M = gp->M, np = bo_pad8(n), n1p = bo_pad8(n + 1), Kp = bo_kp(gp->d);
+    const int d = gp->d;
+    if (n + 1 > 65535 || M > 65535) return BO_ERR_UNSUPPORTED;
+    // 1. K + D = L L^T, inv(L), alpha: the prediction caches of these hyperparameters stay valid afterwards
+    BO_TRY(bo_gp_setup(ctx, gp, w.setup, w.setup_bytes, info, stream));
+    // 2. derivative factor g(r) of the covariance function (g = K for RBF)
+    const BoKernelHyper h = hyper_of(gp);
+    BO_TRY(bo_aug_cols(h, gp->train_X, n, w.baug, Kp, np, Kp * np, st));
+    if (gp->kernel_id == BO_KERNEL_RBF)
+        BO_TRY(kmat(gp, gp->aug_train, (int)n, w.baug, np, n, w.Kg, np, n * np, 1, nullptr, st));
+    else
+        BO_TRY(kmat(gp, gp->aug_train, (int)n, w.baug, np, n, w.G, np, n * np, 1, nullptr, st, w.Kg));
+    // 3. G = (alpha alpha^T - (K + D)^-1) .* g   in one GEMM over the augmented factors
+    {
+        dim3 grid((unsigned)((np + 255) / 256 > 8 ? 8 : (np + 255) / 256), (unsigned)(n + 1), (unsigned)M);
+        mll_negate_kernel<<<grid, 256, 0, st>>>(gp->linv_aug, w.Bn, np, (int)n);
+        g_bo_launch_count++;
+        BoGemm g{};
+        g.A = gp->linv_aug_t; g.lda = n1p; g.strideA = n * n1p;
+        g.B = w.Bn; g.ldb = np; g.strideB = (n + 1) * np;
+        g.C = w.G; g.ldc = np; g.strideC = n * np;
+        g.E = w.Kg; g.lde = np; g.strideE = n * np;
+        g.alpha = 1.0; g.M = (int)n; g.N = (int)n; g.K = (int)n + 1; g.batch = (int)M;
+        g.tri = BO_TRI_A_UPPER; g.epi = BO_EPI_LINEAR;
+        BO_TRY(bo_gemm_launch(g, st));
+    }
+    // 4. H = [x~^T; 1] G   ((d+1) x n), x~ = train_X - center
+    {
+        dim3 grid((unsigned)((np + 127) / 128), (unsigned)(d + 1));
+        mll_xct_kernel<<<grid, 128, 0, st>>>(gp->train_X, gp->center, w.xct, np, (int)n, d);
+        g_bo_launch_count++;
+    }
+    const long strideH = (long)(d + 1) * np;
+    if (w.ks > 1) {
+        const long kc = n / w.ks;
+        BO_TRY(gemm(d + 1, (int)n, (int)kc, w.ks, 1.0, w.xct, np, kc, w.G, np, kc * np, 0.0, nullptr, 0, 0, w.H, np, strideH,
+                    BO_TRI_NONE, 0, st));
+    } else {
+        BO_TRY(gemm(d + 1, (int)n, (int)n, (int)M, 1.0, w.xct, np, 0, w.G, np, n * np, 0.0, nullptr, 0, 0, w.H, np, strideH,
+                    BO_TRI_NONE, 0, st));
+    }
+    // 5. diag of (K + D)^-1 and the reductions
+    {
+        dim3 grid((unsigned)((n + 127) / 128), MLL_CHUNKS, (unsigned)M);
+        mll_colsq_kernel<<<grid, 128, 0, st>>>(gp->linv_aug, w.part, np, (int)n);
+        g_bo_launch_count++;
+    }
+    MllFin f{};
+    f.n = (int)n; f.d = d; f.ks = w.ks; f.np = np;
+    f.strideH = w.ks > 1 ? 0 : strideH; f.strideKs = w.ks > 1 ? strideH : 0;
+    f.H = w.H; f.xct = w.xct; f.inv_ls = gp->inv_ls; f.outputscale = gp->outputscale; f.noise = gp->noise;
+    f.noise_vec = gp->noise_vec; f.jitter = gp->jitter; f.mean = gp->mean; f.targets = gp->targets;
+    f.linv_aug = gp->linv_aug; f.chol = gp->chol; f.part = w.part; f.value = value; f.grad = grad;
+    mll_finalize_kernel<<<dim3((unsigned)(d + 1), (unsigned)M), 256, 0, st>>>(f);
+    g_bo_launch_count++;
+    BO_CUDA_TRY(cudaGetLastError());
+    return BO_OK;
+}
+
+// ------------------------------------------------------------------------------------------------
 // building blocks exported for the parity tests
 // ------------------------------------------------------------------------------------------------
 int bo_dgemm(bo_ctx* ctx, int M, int N, int K, int batch, double alpha, const double* A, long lda, long strideA,

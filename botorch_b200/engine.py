@@ -187,6 +187,50 @@ class GPState:
         return out[:, :, :Nc]
 
 
+class MLLState:
+    """Exact marginal log likelihood + hyperparameter gradient on the device (``bo_mll_value_grad``).
+
+    Owns one ``GPState`` whose hyperparameter buffers are overwritten in place per evaluation (no reallocation inside the
+    L-BFGS-B loop of ``fit_gpytorch_mll``); each evaluation leaves that state factored for its hyperparameters.
+    """
+
+    def __init__(self, train_X: Tensor, targets: Tensor, kernel: str, with_outputscale: bool, M: int = 1,
+                 noise_vec: Optional[Tensor] = None) -> None:  # fmt: skip
+        dev = train_X.device
+        d = train_X.shape[-1]
+        one = torch.ones(M, dtype=torch.float64, device=dev)
+        self.gp = GPState(train_X, targets, kernel, torch.ones(M, d, dtype=torch.float64, device=dev), one, 0.0 * one,
+                          one.clone() if with_outputscale else None, setup=False, noise_vec=noise_vec)  # fmt: skip
+        lib = _lib.lib()
+        self.work = _lib.workspace(lib.bo_mll_workspace_bytes(C.byref(self.gp.c)), dev)
+        self.value = torch.zeros(M, dtype=torch.float64, device=dev)
+        self.grad = torch.zeros(M, d + 3, dtype=torch.float64, device=dev)
+        self.evaluations = 0
+
+    def evaluate(self, lengthscale: Tensor, noise: Optional[Tensor], mean: Tensor, outputscale: Optional[Tensor] = None):
+        """-> (value [M], grad [M x (d+3)]: lengthscale (d), outputscale, noise, mean).  Raises NotPSDError after the
+        psd_safe_cholesky jitter schedule is exhausted."""
+        gp = self.gp
+        gp.inv_ls.copy_(1.0 / _f64(lengthscale, gp.device).reshape(gp.M, gp.d))
+        if noise is not None:
+            gp.noise.copy_(_f64(noise, gp.device).reshape(-1).expand(gp.M))
+        gp.mean.copy_(_f64(mean, gp.device).reshape(-1).expand(gp.M))
+        if gp.outputscale is not None and outputscale is not None:
+            gp.outputscale.copy_(_f64(outputscale, gp.device).reshape(-1).expand(gp.M))
+        lib = _lib.lib()
+
+        def run(jitter: Optional[Tensor]) -> Tensor:
+            gp.c.jitter = ptr(jitter)
+            self._jitter = jitter
+            check(lib.bo_mll_value_grad(gp.ctx, C.byref(gp.c), self.work.data_ptr(), self.work.numel(), ptr(self.value),
+                                        ptr(self.grad), ptr(gp.info), _lib.stream_ptr(gp.device)))  # fmt: skip
+            return gp.info.clone()
+
+        self.evaluations += 1
+        gp.jitter = _retry_with_jitter(run, gp.M, gp.device, "K + noise*I")
+        return self.value, self.grad
+
+
 class NEIState:
     """Baseline factors of qLogNEI (V_b, L_b and its inverse, base samples, best_f) and the fused fwd/bwd."""
 

@@ -199,6 +199,23 @@ int bo_ts_argmax(bo_ctx* ctx, int M, long Nc, const double* mean, const double* 
 /* first-occurrence argmax of a vector (optim/initializers.py:944, optim/optimize.py:385) */
 int bo_argmax(bo_ctx* ctx, long n, const double* v, double* out_val, int64_t* out_idx, void* stream);
 
+/* ---- hyperparameter side of the caller ----------------------------------------------
+ * Exact marginal log likelihood of the training data and its gradient w.r.t. the hyperparameters: what
+ * fit_gpytorch_mll's closure computes per L-BFGS-B evaluation (botorch/fit.py:117-259 ->
+ * optim/fit.py:47-110 -> optim/closures/model_closures.py:171-184: `-mll(model(*train_inputs), targets)` +
+ * autograd), i.e. gpytorch ExactMarginalLogLikelihood -> MultivariateNormal.log_prob with exact Cholesky
+ * (botorch/__init__.py:44-49).  Here:
+ *   value[z] = log N(targets | mean_z, K_z + D_z)                (NOT divided by n, no prior terms: host adds those)
+ *   grad[z]  = [ d/d lengthscale_0..d-1, d/d outputscale, d/d noise, d/d mean ]   ([M x (d+3)])
+ * with W = alpha alpha^T - (K + D)^-1:  d/d l_t = 1/2 sum_ij W_ij g_ij (x_it - x_jt)^2 / l_t^3  (g: derivative factor of
+ * the covariance function), evaluated as one triangular GEMM for W .* g, one (d+1)-row GEMM against [x~^T; 1] and
+ * deterministic reductions.  The d/d noise entry is meaningful for homoskedastic noise only (noise_vec == NULL).
+ * Runs bo_gp_setup first: on return the factor buffers of `gp` are the prediction caches of these hyperparameters.
+ * info[M]: as bo_gp_setup (first bad pivot; value/grad of that model are then meaningless). */
+size_t bo_mll_workspace_bytes(const bo_gp* gp);
+int bo_mll_value_grad(bo_ctx* ctx, const bo_gp* gp, void* work, size_t work_bytes, double* value, double* grad,
+                      int32_t* info, void* stream);
+
 /* ---- building blocks exported for the parity tests ------------------------------------------ */
 int bo_dgemm(bo_ctx* ctx, int M, int N, int K, int batch, double alpha, const double* A, long lda, long strideA,
              const double* B, long ldb, long strideB, double beta, double* C, long ldc, long strideC, int tri,

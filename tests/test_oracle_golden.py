@@ -249,3 +249,51 @@ def test_oracle_ei_family_consistency():
         best_f = ogp.posterior(p.train_X)[0].min()
     ei, logei = OracleQEI(ogp, best_f, p.mc_samples), OracleQLogEI(ogp, best_f, p.mc_samples)
     assert float((logei.forward(X) - ei.forward(X).log()).abs().max()) < 0.05
+
+
+# ---- exact marginal log likelihood oracle (oracle/mll.py) ---------------------------------------------------------------
+def test_mll_oracle_against_torch_distributions():
+    """The oracle's log_prob / prior restatements agree with torch.distributions (what gpytorch's MultivariateNormal,
+    LogNormalPrior and GammaPrior wrap) and its analytic pieces with autograd."""
+    import math
+
+    from oracle import mll as omll
+
+    g = torch.Generator().manual_seed(0)
+    n, d = 40, 3
+    X = torch.rand(n, d, generator=g, dtype=torch.float64)
+    y = torch.randn(n, generator=g, dtype=torch.float64)
+    ls = torch.tensor([0.4, 1.1, 0.7], dtype=torch.float64)
+    noise, mean, os = (torch.tensor(v, dtype=torch.float64) for v in (0.05, 0.3, 1.4))
+    for kernel in ("rbf", "matern52"):
+        K = omll.train_kernel(X, kernel, ls, os) + noise * torch.eye(n, dtype=torch.float64)
+        ref = torch.distributions.MultivariateNormal(mean.expand(n), covariance_matrix=K).log_prob(y)
+        got = omll.log_marginal(X, y, kernel, ls, noise, mean, os)
+        assert abs(float(got - ref)) < 1e-10 * abs(float(ref))
+    x = torch.tensor([0.03, 0.5, 2.0, 40.0], dtype=torch.float64)
+    assert torch.allclose(omll.lognormal_log_prob(x, 1.2, math.sqrt(3.0)),
+                          torch.distributions.LogNormal(torch.tensor(1.2, dtype=torch.float64), torch.tensor(3.0, dtype=torch.float64).sqrt()).log_prob(x), rtol=1e-13, atol=1e-13)  # fmt: skip
+    assert torch.allclose(omll.gamma_log_prob(x, 2.0, 0.15), torch.distributions.Gamma(torch.tensor(2.0, dtype=torch.float64), torch.tensor(0.15, dtype=torch.float64)).log_prob(x), rtol=1e-13, atol=1e-13)
+    # the full objective = (log_prob + priors) / n, finite-difference check of the autograd gradient
+    h = {"lengthscale": ls, "noise": noise, "mean": mean, "outputscale": None}
+    v, grads = omll.value_and_grad(omll.exact_mll, X, y, "rbf", h)
+    eps = 1e-6
+    hp = dict(h, noise=noise + eps)
+    hm = dict(h, noise=noise - eps)
+    fd = (omll.exact_mll(X, y, "rbf", hp["lengthscale"], hp["noise"], mean) - omll.exact_mll(X, y, "rbf", hm["lengthscale"], hm["noise"], mean)) / (2 * eps)
+    assert abs(float(fd - grads["noise"])) < 1e-6 * max(abs(float(fd)), 1.0)
+
+
+def test_fit_host_prior_terms_match_the_oracle():
+    """botorch_b200.fit's closed-form prior value/derivative (host-side plumbing) == oracle restatement + autograd."""
+    from botorch_b200 import fit as bfit
+    from oracle import mll as omll
+
+    x = torch.tensor([0.03, 0.5, 2.0, 40.0], dtype=torch.float64, requires_grad=True)
+    for (fn, ofn, args) in ((bfit._lognormal, omll.lognormal_log_prob, (-4.0, 1.0)), (bfit._gamma, omll.gamma_log_prob, (2.0, 0.15))):
+        lp, dlp = fn(x.detach(), *args)
+        ref = ofn(x, *args)
+        (gref,) = torch.autograd.grad(ref.sum(), x)
+        assert torch.allclose(lp, ref.detach(), rtol=1e-14, atol=1e-14)
+        assert torch.allclose(dlp, gref, rtol=1e-13, atol=1e-13)
+    assert bfit.lengthscale_prior_params(20) == (2.0**0.5 + 0.5 * __import__("math").log(20), 3.0**0.5)
