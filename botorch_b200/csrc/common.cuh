@@ -71,6 +71,8 @@ struct BoGemm {
     const double* diag_add;  // [batch] value added where row==col (noise), may be null
     int diag_exact;          // 1: squared distance forced to 0 where row==col (x1_eq_x2)
     int a_bcast, b_bcast;    // unused (strides of 0 already broadcast); kept for clarity
+    int tile64;              // 1: force the 64 x 64 tile configuration (lets C alias A when N <= 64: a CTA then reads exactly
+                             // the rows it writes, and all of its loads complete before its epilogue)
     const double* alpha_vec; // [batch] optional per-member factor multiplying alpha (LINEAR only)
     const double* E; long lde; long strideE;    // optional elementwise factor: C = (alpha*acc + beta*D) * E  (LINEAR only)
     double* C2; long ldc2; long strideC2;       // kernel epilogues: optional second output g(r), d k/dx_a = -g (x_a-x_b)/l^2

@@ -356,6 +356,7 @@ int bo_gemm_launch(const BoGemm& g, cudaStream_t stream) {
     // Pick the largest tile that still fills the 148 SMs; small problems trade tile efficiency for occupancy.
     // 64x64 tiles, 4 warps, double-buffered, 4 CTAs per SM: measured best on B200 (tools/gemm_bench.py) --
     // co-resident small CTAs keep the DMMA pipe fed through each other's barriers and shrink the last wave.
+    if (g.tile64) return launch_cfg<CfgT10>(g, stream);
     if (g.M <= 32 && g.N >= 1024 && g.K >= 64 && g.epi == BO_EPI_LINEAR && g.tri == BO_TRI_NONE)
         return launch_cfg<CfgSkinny>(g, stream);
     if (tiles(64, 64) >= 120 || (g.M >= 48 && g.N >= 48 && tiles(32, 32) > 2048)) return launch_cfg<CfgT10>(g, stream);

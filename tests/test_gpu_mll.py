@@ -179,3 +179,28 @@ def test_fit_retries_and_raises_model_fitting_error(cuda):
     assert len(calls) == 3 and not torch.equal(calls[0], calls[1])  # attempts 2.. start from prior samples
     assert mll.training
     assert torch.equal(model.covar_module.raw_lengthscale.detach().cpu(), calls[0])  # rolled back
+
+
+def test_mll_batched_hyperparameter_sets(cuda):
+    """M hyperparameter sets over one training set in a single call (the shape of a multi-chain NUTS potential for the
+    SAAS model, models/fully_bayesian.py:168-191): every member matches its own oracle evaluation."""
+    from botorch_b200.engine import MLLState
+
+    n, d, M = 100, 30, 5
+    X, y = _data(n, d, seed=21)
+    g = torch.Generator().manual_seed(4)
+    ls = 0.2 + 2.0 * torch.rand(M, d, generator=g, dtype=torch.float64)
+    noise = 1e-3 + 0.1 * torch.rand(M, generator=g, dtype=torch.float64)
+    mean = 0.3 * torch.randn(M, generator=g, dtype=torch.float64)
+    os_ = 0.5 + 1.5 * torch.rand(M, generator=g, dtype=torch.float64)
+    st = MLLState(X.to(cuda), y.to(cuda), "matern52", with_outputscale=True, M=M)
+    v, gr = st.evaluate(ls.to(cuda), noise.to(cuda), mean.to(cuda), os_.to(cuda))
+    v, gr = v.cpu(), gr.cpu()
+    for m in range(M):
+        h = {"lengthscale": ls[m], "noise": noise[m], "mean": mean[m], "outputscale": os_[m]}
+        ov, og = omll.value_and_grad(omll.log_marginal, X, y, "matern52", h)
+        assert abs(float(v[m]) - float(ov)) <= TOL * abs(float(ov))
+        assert rel_err(gr[m, :d], og["lengthscale"], scale=max(float(og["lengthscale"].abs().max()), 0.1)) < TOL
+        assert abs(float(gr[m, d]) - float(og["outputscale"])) <= TOL * n
+        assert abs(float(gr[m, d + 1]) - float(og["noise"])) <= TOL * max(abs(float(og["noise"])), float(n))
+        assert abs(float(gr[m, d + 2]) - float(og["mean"])) <= TOL * max(abs(float(og["mean"])), 1.0)
