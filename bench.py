@@ -192,6 +192,58 @@ def _run_reference(args):
     print(json.dumps(line), flush=True)
 
 
+def _mll_leg(p, dev, stream, cpu: bool):
+    """bo_mll_value_grad at the workload's training set: CUDA-event time per evaluation, FP64 rate on its algorithmic
+    flops (Cholesky n^3/3 + inverse factor n^3/3 + W = alpha alpha^T - Khat^-1 against the triangular factor n^3 +
+    covariance / gradient contractions), and the CPU oracle (torch float64 + autograd) on the same problem."""
+    import ctypes as C
+
+    from botorch_b200 import _lib, engine
+
+    y = ((p.train_Y - p.train_Y.mean()) / p.train_Y.std()).reshape(-1)
+    h = p.hypers
+    st = engine.MLLState(p.train_X.to(dev), y.to(dev), p.kernel, with_outputscale=h.get("outputscale") is not None)
+    hy = [h["lengthscale"].reshape(-1).to(dev), h["noise"].reshape(()).to(dev), h["mean"].reshape(()).to(dev),
+          None if h.get("outputscale") is None else h["outputscale"].reshape(()).to(dev)]  # fmt: skip
+    st.evaluate(*hy)
+    lib, gp = _lib.lib(), st.gp
+
+    def raw():
+        _lib.check(lib.bo_mll_value_grad(gp.ctx, C.byref(gp.c), st.work.data_ptr(), st.work.numel(), st.value.data_ptr(),
+                                         st.grad.data_ptr(), gp.info.data_ptr(), _lib.stream_ptr(dev)))  # fmt: skip
+
+    for _ in range(3):
+        raw()
+    torch.cuda.synchronize()
+    reps = 10
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record(stream)
+    for _ in range(reps):
+        raw()
+    e1.record(stream)
+    torch.cuda.synchronize()
+    ms = e0.elapsed_time(e1) / reps
+    n, d = p.n, p.d
+    flops = n**3 * (1 / 3 + 1 / 3 + 1.0) + 4 * (d + 2) * n * n + 2 * (d + 1) * n * n
+    leg = {"mll_evals_per_s": 1e3 / ms, "ms_per_eval": ms, "tflops_fp64": flops / (ms * 1e-3) / 1e12,
+           "frac_of_fp64_peak": flops / (ms * 1e-3) / 1e12 / FP64_DMMA_PEAK_TFLOPS, "n": n, "d": d,
+           "what": "bo_mll_value_grad: log N(y | m, K + s2 I) and its gradient w.r.t. lengthscales, noise, mean "
+                   "(one fit_gpytorch_mll closure evaluation), hyperparameters resident in HBM"}  # fmt: skip
+    if cpu:
+        from oracle import mll as omll  # CPU baseline leg only
+
+        hh = {"lengthscale": h["lengthscale"].reshape(-1), "noise": h["noise"].reshape(()), "mean": h["mean"].reshape(()),
+              "outputscale": None if h.get("outputscale") is None else h["outputscale"].reshape(())}  # fmt: skip
+        omll.value_and_grad(omll.log_marginal, p.train_X, y, p.kernel, hh)
+        creps = 3 if n >= 1000 else 20
+        t0 = time.perf_counter()
+        for _ in range(creps):
+            omll.value_and_grad(omll.log_marginal, p.train_X, y, p.kernel, hh)
+        leg["cpu_oracle_ms_per_eval"] = 1e3 * (time.perf_counter() - t0) / creps
+        leg["cpu_cores"] = os.cpu_count()
+    return leg
+
+
 def _workload_name(p, B):
     return (f"{p.name}: n={p.n} d={p.d} q={p.q} S={p.mc_samples} restarts/GPU={B} "
             f"(BASELINE.json configs[{'C1 C2 C3 C4 C5'.split().index(p.name[:2])}])")  # fmt: skip
@@ -352,6 +404,10 @@ def _run_ours(args):
         if ws > 1:
             dist.destroy_process_group()
         return
+    # ---- hyperparameter side: exact MLL value + gradient per L-BFGS-B evaluation of fit_gpytorch_mll ----
+    mll_leg = None
+    if ws == 1 and nei.gp.M == 1:
+        mll_leg = _mll_leg(p, dev, stream, cpu=not args.no_cpu_baseline)
     n_models = nei.gp.M
     fwd_f, bwd_f = _algorithmic_flops_per_eval(p.n, nei.n_b, p.d, p.q, p.mc_samples)
     survey_per_eval = 3 * fwd_f * n_models  # SURVEY.md 8(d) convention: fwd+bwd = 3 F_fwd of the trsm-based algorithm
@@ -397,6 +453,8 @@ def _run_ours(args):
                       "ms": post_ms},  # fmt: skip
         "setup_s": setup_s, "broadcast_bytes": bcast_bytes, "clocks": clk,
     }  # fmt: skip
+    if mll_leg is not None:
+        line["mll"] = mll_leg
     if not args.no_cpu_baseline and ws == 1:
         sample = args.cpu_sample or (4 if p.n >= 1000 else 32)
         line["cpu_baseline"] = _cpu_baseline(p, sample)

@@ -26,6 +26,8 @@ __global__ void __launch_bounds__(256) potrf_diag_kernel(double* A, long lda, lo
     double (*S)[NB + 1] = reinterpret_cast<double (*)[NB + 1]>(potrf_sm);
     double (*X)[NB + 1] = reinterpret_cast<double (*)[NB + 1]>(potrf_sm + NB * (NB + 1));
     __shared__ double colbuf[2][NB];
+    __shared__ double rdiag[NB];
+    __shared__ double Tbuf[32 * 32];
     const int z = blockIdx.x, tid = threadIdx.x;
     const int ty = tid >> 4, tx = tid & 15;
     double* Az = A + (long)z * strideA;
@@ -50,8 +52,9 @@ __global__ void __launch_bounds__(256) potrf_diag_kernel(double* A, long lda, lo
             __syncthreads();
             const double ajj = buf[j];
             if (!(ajj > 0.0) && j < kb) { fail = j + 1; break; }  // uniform: every thread reads the same pivot
-            const double d = sqrt(ajj);
-            const double rd = 1.0 / d;
+            const double rd = rsqrt(ajj);  // one MUFU + Newton chain instead of sqrt followed by a division
+            const double d = ajj * rd;
+            if (tid == 0) rdiag[j] = rd;
             double li[4], lk[4];
 #pragma unroll
             for (int q = 0; q < 4; q++) {
@@ -82,6 +85,7 @@ __global__ void __launch_bounds__(256) potrf_diag_kernel(double* A, long lda, lo
         for (int ai = 0; ai < 4; ai++)
 #pragma unroll
             for (int bi = 0; bi < 4; bi++) a[ai][bi] = (ty + 16 * ai == tx + 16 * bi) ? 1.0 : 0.0;
+        if (tid < NB) rdiag[tid] = 1.0;
     }
 #pragma unroll
     for (int ai = 0; ai < 4; ai++)
@@ -89,21 +93,44 @@ __global__ void __launch_bounds__(256) potrf_diag_kernel(double* A, long lda, lo
         for (int bi = 0; bi < 4; bi++) {
             const int i = ty + 16 * ai, j = tx + 16 * bi;
             S[i][j] = j <= i ? a[ai][bi] : 0.0;
+            X[i][j] = 0.0;
         }
     __syncthreads();
-    // inverse of the lower-triangular block: column c by lanes 4c..4c+3 of one warp (forward substitution, row by row)
-    {
-        const int c = tid >> 2, l = tid & 3;
-        for (int i = 0; i < NB; i++) {
-            double s = 0.0;
-            for (int k = c + l; k < i; k += 4) s += S[i][k] * X[k][c];
-            s += __shfl_xor_sync(0xffffffffu, s, 1);
-            s += __shfl_xor_sync(0xffffffffu, s, 2);
-            if (l == 0) X[i][c] = i < c ? 0.0 : ((i == c ? 1.0 : -s) / S[i][i]);
-            __syncwarp();
+    // inverse of the lower-triangular block, blocked 16 -> 32 -> 64:
+    // (1) the four 16 x 16 diagonal sub-blocks by forward substitution, one thread per column, fully unrolled in registers;
+    if (tid < NB) {
+        const int o = tid & ~15, c = tid & 15;
+        double x[16];
+#pragma unroll
+        for (int i = 0; i < 16; i++) {
+            double sacc = (i == c) ? 1.0 : 0.0;
+#pragma unroll
+            for (int k = 0; k < i; k++) sacc -= S[o + i][o + k] * x[k];
+            x[i] = sacc * rdiag[o + i];
         }
+#pragma unroll
+        for (int i = 0; i < 16; i++) X[o + i][o + c] = x[i];
     }
     __syncthreads();
+    // (2) merge adjacent blocks: X21 = -X22 (L21 X11), every output element on its own thread
+#pragma unroll
+    for (int sz = 16; sz < NB; sz *= 2) {
+        const int per = sz * sz, total = per * (NB / (2 * sz));
+        for (int e = tid; e < total; e += 256) {  // T = L21 X11
+            const int pr = e / per, r = (e % per) / sz, c = e % sz, o = pr * 2 * sz;
+            double acc = 0.0;
+            for (int k = c; k < sz; k++) acc += S[o + sz + r][o + k] * X[o + k][o + c];
+            Tbuf[e] = acc;
+        }
+        __syncthreads();
+        for (int e = tid; e < total; e += 256) {  // X21 = -X22 T
+            const int pr = e / per, r = (e % per) / sz, c = e % sz, o = pr * 2 * sz;
+            double acc = 0.0;
+            for (int k = 0; k <= r; k++) acc += X[o + sz + r][o + sz + k] * Tbuf[pr * per + k * sz + c];
+            X[o + sz + r][o + c] = -acc;
+        }
+        __syncthreads();
+    }
     double* Iz = inv ? inv + (long)z * strideI : nullptr;
     double* ITz = invT + (long)z * NB * NB;
     for (int idx = tid; idx < NB * NB; idx += blockDim.x) {
