@@ -286,6 +286,11 @@ using CfgT8 = Cfg<64, 64, 32, 32, 32, 2>;     // BK=32, double buffered, 3 CTAs/
 using CfgT9 = Cfg<64, 64, 32, 32, 32, 3>;     // BK=32, 3 stages, 2 CTAs/SM
 using CfgT10 = Cfg<64, 64, 16, 32, 32, 2>;    // double buffered, 4 CTAs/SM (16 warps)
 using CfgT11 = Cfg<64, 32, 16, 32, 32, 3>;    // 2 warps per CTA, up to 8 CTAs/SM
+// latency-bound panel products of the blocked Cholesky (M x 64 x K <= 128, a few dozen 64-row tiles at most): a lone CTA
+// per SM is bound by its own SM's DMMA issue rate and by one global round trip per k-tile (graph-replayed 64 x 64 tiles:
+// 10.8 us per launch even for a single tile).  16-row tiles spread the panel over four times as many SMs and BK = 32 with
+// three stages keeps most of the k-range in flight; BN = 64 keeps the in-place form legal (see BoGemm::tile64).
+using CfgPanel = Cfg<16, 64, 32, 16, 16, 3>;
 using CfgSkinny = Cfg<32, 128, 16, 32, 32, 2>; // M <= 32 (the (d+1)-row gradient contraction): one row tile, wide columns
 
 template <class C>
@@ -350,13 +355,14 @@ int bo_gemm_launch(const BoGemm& g, cudaStream_t stream) {
         case 9: return launch_cfg<CfgT9>(g, stream);
         case 10: return launch_cfg<CfgT10>(g, stream);
         case 11: return launch_cfg<CfgT11>(g, stream);
+        case 12: return launch_cfg<CfgPanel>(g, stream);
         default: break;
     }
     auto tiles = [&](int bm, int bn) { return (long)((g.M + bm - 1) / bm) * ((g.N + bn - 1) / bn) * g.batch; };
     // Pick the largest tile that still fills the 148 SMs; small problems trade tile efficiency for occupancy.
     // 64x64 tiles, 4 warps, double-buffered, 4 CTAs per SM: measured best on B200 (tools/gemm_bench.py) --
     // co-resident small CTAs keep the DMMA pipe fed through each other's barriers and shrink the last wave.
-    if (g.tile64) return launch_cfg<CfgT10>(g, stream);
+    if (g.tile64) return launch_cfg<CfgPanel>(g, stream);
     if (g.M <= 32 && g.N >= 1024 && g.K >= 64 && g.epi == BO_EPI_LINEAR && g.tri == BO_TRI_NONE)
         return launch_cfg<CfgSkinny>(g, stream);
     if (tiles(64, 64) >= 120 || (g.M >= 48 && g.N >= 48 && tiles(32, 32) > 2048)) return launch_cfg<CfgT10>(g, stream);
