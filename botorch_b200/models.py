@@ -13,8 +13,9 @@ Drop-in for the reference's model contract on this path:
                                         (botorch/models/utils/assorted.py:287-297: train caches detached, so
                                         gradients flow to X only)
 
-Hyperparameter inference (fit_gpytorch_mll / NUTS) is outside the path: hyperparameters are given, or loaded
-from a reference ``state_dict()`` (same keys).  All arithmetic happens in libbotorch_b200; there is no CPU path.
+Hyperparameters are given, loaded from a reference ``state_dict()`` (same keys), or fitted with
+``botorch_b200.fit.fit_gpytorch_mll`` (exact MLL value + gradient on the device); NUTS is outside the path.
+All arithmetic happens in libbotorch_b200; there is no CPU path.
 """
 from __future__ import annotations
 
