@@ -69,6 +69,10 @@ class BoNEI(C.Structure):
     ]
 
 
+class BoPaths(C.Structure):
+    _fields_ = [("S", C.c_int32), ("F", C.c_int32)] + [(name, C.c_void_p) for name in "W w eps w_aug w_pad v".split()]
+
+
 class BoLBFGS(C.Structure):
     _fields_ = [("B", C.c_int32), ("D", C.c_int32), ("m", C.c_int32)] + [
         (name, C.c_void_p)
@@ -142,12 +146,19 @@ def _declare(lib: C.CDLL) -> None:
     lib.bo_potrf_workspace_bytes.restype = sz
     lib.bo_potrf_workspace_bytes.argtypes = [i32, i32]
     lib.bo_potrf.argtypes = [vp, i32, i32, vp, i64, i64, vp, vp, sz, vp, vp]
+    pt = C.POINTER(BoPaths)
+    lib.bo_paths_setup_workspace_bytes.restype = sz
+    lib.bo_paths_setup_workspace_bytes.argtypes = [gp, pt]
+    lib.bo_paths_setup.argtypes = [vp, gp, pt, vp, sz, vp]
+    lib.bo_paths_eval_workspace_bytes.restype = sz
+    lib.bo_paths_eval_workspace_bytes.argtypes = [gp, pt, i64]
+    lib.bo_paths_eval.argtypes = [vp, gp, pt, i64, vp, vp, vp, sz, vp]
     lib.bo_mll_workspace_bytes.restype = sz
     lib.bo_mll_workspace_bytes.argtypes = [gp]
     lib.bo_mll_value_grad.argtypes = [vp, gp, vp, sz, vp, vp, vp, vp]
     for name in (
         "bo_ctx_create bo_gp_setup bo_nei_setup bo_ei_setup bo_qlognei_fwd bo_qlognei_bwd bo_posterior_joint bo_posterior_joint_bwd "
-        "bo_posterior_mean_var bo_ts_argmax bo_argmax bo_dgemm bo_kernel_matrix bo_potrf bo_mll_value_grad"
+        "bo_posterior_mean_var bo_ts_argmax bo_argmax bo_dgemm bo_kernel_matrix bo_potrf bo_mll_value_grad bo_paths_setup bo_paths_eval"
     ).split():
         getattr(lib, name).restype = i32
 

@@ -1048,6 +1048,157 @@ int bo_mll_value_grad(bo_ctx* ctx, const bo_gp* gp, void* work, size_t work_byte
 }
 
 // ------------------------------------------------------------------------------------------------
+// pathwise (Matheron) posterior samples
+// ------------------------------------------------------------------------------------------------
+}  // extern "C"
+
+namespace {
+
+// w_aug[f] = [W[f][0..d-1], sum_t W[f][t] center[t] / l[t], 0, ...]: against the column operand [(x-c)/l; 1; |.|^2] of
+// bo_aug_cols the contraction is W[f] . x / l  (InverseLengthscaleTransform, sampling/pathwise/utils.py:101-117)
+__global__ void paths_waug_kernel(const double* W, const double* inv_ls, const double* center, double* w_aug, int half,
+                                  int d, long Kp) {
+    const int f = blockIdx.x * blockDim.x + threadIdx.x;
+    if (f >= half) return;
+    double off = 0.0;
+    for (int t = 0; t < d; t++) {
+        const double wv = W[(long)f * d + t];
+        w_aug[(long)f * Kp + t] = wv;
+        off += wv * center[t] * inv_ls[t];
+    }
+    w_aug[(long)f * Kp + d] = off;
+    for (long k = d + 1; k < Kp; k++) w_aug[(long)f * Kp + k] = 0.0;
+}
+// r[s][i] = targets[i] - mean - f0[s][i] - sqrt(D_i) eps[s][i]      (update_strategies.py:82-91)
+__global__ void paths_resid_kernel(const double* targets, const double* mean, const double* noise, const double* noise_vec,
+                                   const double* f0, const double* eps, double* r, int n, long np) {
+    const int s = blockIdx.y, i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= np) return;
+    double v = 0.0;
+    if (i < n) {
+        const double dn = noise_vec ? noise_vec[i] : noise[0];
+        v = targets[i] - mean[0] - f0[(long)s * np + i] - sqrt(dn) * eps[(long)s * n + i];
+    }
+    r[(long)s * np + i] = v;
+}
+// out = y_mean + y_std * (mean + out)
+__global__ void paths_affine_kernel(double* out, long count, double y_mean, double y_std, const double* mean) {
+    const double b = y_mean + y_std * mean[0];
+    for (long i = blockIdx.x * (long)blockDim.x + threadIdx.x; i < count; i += (long)gridDim.x * blockDim.x)
+        out[i] = b + y_std * out[i];
+}
+
+bool valid_paths(const bo_gp* gp, const bo_paths* p) {
+    return p && gp->M == 1 && p->S > 0 && p->F >= 2 && (p->F % 2) == 0 && p->W && p->w && p->eps && p->w_aug && p->w_pad && p->v;
+}
+
+// PhiT[F x ldn] = features of the points whose column operand is baug; then C[S x ldn] = alpha * w_pad PhiT (+ beta D)
+int paths_features(const bo_gp* gp, const bo_paths* p, const double* baug, long npts, long ldn, double* PhiT,
+                   cudaStream_t st) {
+    const long Kp = bo_kp(gp->d), half = p->F / 2;
+    BoGemm g{};
+    g.A = p->w_aug; g.lda = Kp; g.strideA = 0;
+    g.B = baug; g.ldb = ldn; g.strideB = 0;
+    g.C = PhiT; g.ldc = ldn; g.strideC = 0;
+    g.C2 = PhiT + half * ldn; g.ldc2 = ldn; g.strideC2 = 0;
+    g.alpha = sqrt(2.0 / (double)p->F); g.os = gp->outputscale;
+    g.M = (int)half; g.N = (int)npts; g.K = (int)Kp; g.batch = 1; g.epi = BO_EPI_SINCOS;
+    return bo_gemm_launch(g, st);
+}
+
+struct PathsSetupWork { double *baug, *PhiT, *f0, *r, *t; bool ok; size_t bytes; };
+PathsSetupWork paths_setup_layout(const bo_gp* gp, const bo_paths* p, void* work, size_t cap) {
+    PathsSetupWork w{};
+    const long n = gp->n, np = bo_pad8(n), Kp = bo_kp(gp->d), Sp = bo_pad8(p->S);
+    Bump b(work, cap);
+    w.baug = b.doubles(Kp * np);
+    w.PhiT = b.doubles((long)p->F * np);
+    w.f0 = b.doubles(Sp * np);
+    w.r = b.doubles(Sp * np);
+    w.t = b.doubles(Sp * np);
+    w.ok = b.ok; w.bytes = b.off;
+    return w;
+}
+struct PathsEvalWork { double *baug, *PhiT, *kx; long ldn; bool ok; size_t bytes; };
+PathsEvalWork paths_eval_layout(const bo_gp* gp, const bo_paths* p, long Nc, void* work, size_t cap) {
+    PathsEvalWork w{};
+    const long Kp = bo_kp(gp->d);
+    w.ldn = bo_pad8(Nc);
+    Bump b(work, cap);
+    w.baug = b.doubles(Kp * w.ldn);
+    w.PhiT = b.doubles((long)p->F * w.ldn);
+    w.kx = b.doubles((long)gp->n * w.ldn);
+    w.ok = b.ok; w.bytes = b.off;
+    return w;
+}
+
+}  // namespace
+
+extern "C" {
+
+size_t bo_paths_setup_workspace_bytes(const bo_gp* gp, const bo_paths* paths) {
+    return paths_setup_layout(gp, paths, nullptr, 0).bytes;
+}
+
+int bo_paths_setup(bo_ctx* ctx, const bo_gp* gp, const bo_paths* paths, void* work, size_t work_bytes, void* stream) {
+    if (!ctx || !valid_gp(gp) || !valid_paths(gp, paths) || !work) return BO_ERR_INVALID;
+    cudaStream_t st = (cudaStream_t)stream;
+    const PathsSetupWork w = paths_setup_layout(gp, paths, work, work_bytes);
+    if (!w.ok) return BO_ERR_WORKSPACE;
+    const long n = gp->n, np = bo_pad8(n), n1p = bo_pad8(n + 1), Kp = bo_kp(gp->d), S = paths->S, F = paths->F, Fp = bo_pad8(F);
+    const BoKernelHyper h = hyper_of(gp);
+    paths_waug_kernel<<<(unsigned)((F / 2 + 127) / 128), 128, 0, st>>>(paths->W, gp->inv_ls, gp->center, paths->w_aug,
+                                                                       (int)(F / 2), gp->d, Kp);
+    g_bo_launch_count++;
+    BO_TRY(bo_fill(paths->w_pad, S * Fp, 0.0, st));
+    BO_TRY(bo_copy2d(paths->w, F, 0, paths->w_pad, Fp, 0, (int)S, (int)F, 1, st));
+    // prior paths at the training inputs: f0(X) - m = w Phi(X)^T
+    BO_TRY(bo_aug_cols(h, gp->train_X, n, w.baug, Kp, np, Kp * np, st));
+    BO_TRY(paths_features(gp, paths, w.baug, n, np, w.PhiT, st));
+    BO_TRY(gemm((int)S, (int)n, (int)F, 1, 1.0, paths->w_pad, Fp, 0, w.PhiT, np, 0, 0.0, nullptr, 0, 0, w.f0, np, 0,
+                BO_TRI_NONE, 0, st));
+    dim3 grid((unsigned)((np + 127) / 128), (unsigned)S);
+    paths_resid_kernel<<<grid, 128, 0, st>>>(gp->targets, gp->mean, gp->noise, gp->noise_vec, w.f0, paths->eps, w.r, (int)n, np);
+    g_bo_launch_count++;
+    // v = r (K + D)^-1 = (r inv(L)^T) inv(L), paths as rows
+    BO_TRY(gemm((int)S, (int)n, (int)n, 1, 1.0, w.r, np, 0, gp->linv_aug_t, n1p, 0, 0.0, nullptr, 0, 0, w.t, np, 0, BO_TRI_NONE,
+                0, st));
+    BO_TRY(bo_fill(paths->v, S * np, 0.0, st));
+    BO_TRY(gemm((int)S, (int)n, (int)n, 1, 1.0, w.t, np, 0, gp->linv_aug, np, 0, 0.0, nullptr, 0, 0, paths->v, np, 0,
+                BO_TRI_B_LOWER, 0, st));
+    BO_CUDA_TRY(cudaGetLastError());
+    return BO_OK;
+}
+
+size_t bo_paths_eval_workspace_bytes(const bo_gp* gp, const bo_paths* paths, long Nc) {
+    return paths_eval_layout(gp, paths, Nc, nullptr, 0).bytes;
+}
+
+int bo_paths_eval(bo_ctx* ctx, const bo_gp* gp, const bo_paths* paths, long Nc, const double* Xc, double* out, void* work,
+                  size_t work_bytes, void* stream) {
+    if (!ctx || !valid_gp(gp) || !valid_paths(gp, paths) || Nc <= 0 || !Xc || !out || !work) return BO_ERR_INVALID;
+    cudaStream_t st = (cudaStream_t)stream;
+    const PathsEvalWork w = paths_eval_layout(gp, paths, Nc, work, work_bytes);
+    if (!w.ok) return BO_ERR_WORKSPACE;
+    const long n = gp->n, np = bo_pad8(n), Kp = bo_kp(gp->d), S = paths->S, F = paths->F, Fp = bo_pad8(F), ldn = w.ldn;
+    const BoKernelHyper h = hyper_of(gp);
+    BO_TRY(bo_aug_cols(h, Xc, Nc, w.baug, Kp, ldn, Kp * ldn, st));
+    BO_TRY(paths_features(gp, paths, w.baug, Nc, ldn, w.PhiT, st));
+    BO_TRY(kmat(gp, gp->aug_train, (int)n, w.baug, ldn, Nc, w.kx, ldn, n * ldn, 0, nullptr, st));
+    // out = w Phi(x)^T + v k(X, x), then the mean and the outcome transform
+    BO_TRY(gemm((int)S, (int)Nc, (int)F, 1, 1.0, paths->w_pad, Fp, 0, w.PhiT, ldn, 0, 0.0, nullptr, 0, 0, out, ldn, 0,
+                BO_TRI_NONE, 0, st));
+    BO_TRY(gemm((int)S, (int)Nc, (int)n, 1, 1.0, paths->v, np, 0, w.kx, ldn, 0, 1.0, out, ldn, 0, out, ldn, 0, BO_TRI_NONE, 0,
+                st));
+    long blocks = (S * ldn + 255) / 256;
+    if (blocks > 148 * 16) blocks = 148 * 16;
+    paths_affine_kernel<<<(unsigned)blocks, 256, 0, st>>>(out, S * ldn, gp->y_mean, gp->y_std, gp->mean);
+    g_bo_launch_count++;
+    BO_CUDA_TRY(cudaGetLastError());
+    return BO_OK;
+}
+
+// ------------------------------------------------------------------------------------------------
 // building blocks exported for the parity tests
 // ------------------------------------------------------------------------------------------------
 int bo_dgemm(bo_ctx* ctx, int M, int N, int K, int batch, double alpha, const double* A, long lda, long strideA,

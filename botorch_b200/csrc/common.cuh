@@ -44,7 +44,8 @@ static inline long bo_round_up(long x, long m) { return (x + m - 1) / m * m; }
 enum BoEpilogue : int {
     BO_EPI_LINEAR = 0,  // C = alpha*acc + beta*D
     BO_EPI_RBF = 1,     // acc is a squared distance: C = os[z]*exp(-0.5*max(acc,0))   (+ diag options)
-    BO_EPI_MATERN52 = 2 // C = os[z]*(1+sqrt5 r+5/3 r^2) exp(-sqrt5 r), r = sqrt(max(acc,1e-30))
+    BO_EPI_MATERN52 = 2,// C = os[z]*(1+sqrt5 r+5/3 r^2) exp(-sqrt5 r), r = sqrt(max(acc,1e-30))
+    BO_EPI_SINCOS = 3   // random Fourier features: C = alpha*sqrt(os[z])*sin(acc), C2 = alpha*sqrt(os[z])*cos(acc)
 };
 
 enum BoTri : int {

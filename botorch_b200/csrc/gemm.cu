@@ -80,6 +80,13 @@ __device__ __forceinline__ double epilogue_value(const BoGemm& p, int z, double 
         if (p.E != nullptr) v *= p.E[(long)z * p.strideE + (long)row * p.lde + col];
         return v;
     }
+    if (p.epi == BO_EPI_SINCOS) {
+        double sn, cs;
+        sincos(acc, &sn, &cs);
+        const double sc = p.os ? p.alpha * sqrt(p.os[z]) : p.alpha;
+        p.C2[(long)z * p.strideC2 + (long)row * p.ldc2 + col] = sc * cs;
+        return sc * sn;
+    }
     double r2 = acc > 0.0 ? acc : 0.0;
     const bool on_diag = (row == col);
     if (p.diag_exact && on_diag) r2 = 0.0;

@@ -15,7 +15,7 @@ import torch
 from torch import Tensor
 
 from . import _lib
-from ._lib import BoGP, BoNEI, check, kp, pad8, ptr
+from ._lib import BoGP, BoNEI, BoPaths, check, kp, pad8, ptr
 from .exceptions import NanError, NotPSDError, NumericalWarning
 
 REDUCE_LOG, REDUCE_PLAIN = 0, 1  # BO_REDUCE_* of include/botorch_b200.h
@@ -229,6 +229,45 @@ class MLLState:
         self.evaluations += 1
         gp.jitter = _retry_with_jitter(run, gp.M, gp.device, "K + noise*I")
         return self.value, self.grad
+
+
+class PathState:
+    """S pathwise (Matheron) posterior samples of a single-model GP: random-feature prior paths + the exact data update
+    (``bo_paths_setup``), evaluated at any number of points with ``bo_paths_eval``.  The random draws are inputs."""
+
+    def __init__(self, gp: GPState, W: Tensor, w: Tensor, eps: Tensor) -> None:
+        if gp.M != 1:
+            raise ValueError("pathwise samples are defined for single-model GPs (M = 1)")
+        dev = gp.device
+        self.gp = gp
+        self.W, self.w, self.eps = _f64(W, dev), _f64(w, dev), _f64(eps, dev)
+        half, d = self.W.shape
+        self.S, self.F = self.w.shape
+        if d != gp.d or self.F != 2 * half or self.eps.shape != (self.S, gp.n):
+            raise ValueError(f"inconsistent draws: W {tuple(self.W.shape)}, w {tuple(self.w.shape)}, eps {tuple(self.eps.shape)}")
+        z = lambda *s: torch.zeros(*s, dtype=torch.float64, device=dev)
+        self.w_aug, self.w_pad, self.v = z(half, gp.Kp), z(self.S, pad8(self.F)), z(self.S, gp.np_)
+        self.c = BoPaths(S=self.S, F=self.F, W=ptr(self.W), w=ptr(self.w), eps=ptr(self.eps), w_aug=ptr(self.w_aug),
+                         w_pad=ptr(self.w_pad), v=ptr(self.v))  # fmt: skip
+        lib = _lib.lib()
+        work = _lib.workspace(lib.bo_paths_setup_workspace_bytes(C.byref(gp.c), C.byref(self.c)), dev)
+        check(lib.bo_paths_setup(gp.ctx, C.byref(gp.c), C.byref(self.c), work.data_ptr(), work.numel(), _lib.stream_ptr(dev)))
+        self._work: Optional[Tensor] = None
+        self._work_n = 0
+
+    def evaluate(self, Xc: Tensor) -> Tensor:
+        """Xc: Nc x d -> path values [S x Nc] on the outcome scale."""
+        gp = self.gp
+        Xc = _f64(Xc, gp.device)
+        Nc = Xc.shape[0]
+        lib = _lib.lib()
+        if self._work is None or self._work_n < Nc:
+            self._work = _lib.workspace(lib.bo_paths_eval_workspace_bytes(C.byref(gp.c), C.byref(self.c), Nc), gp.device)
+            self._work_n = Nc
+        out = torch.empty(self.S, pad8(Nc), dtype=torch.float64, device=gp.device)
+        check(lib.bo_paths_eval(gp.ctx, C.byref(gp.c), C.byref(self.c), Nc, ptr(Xc), ptr(out), self._work.data_ptr(),
+                                self._work.numel(), _lib.stream_ptr(gp.device)))  # fmt: skip
+        return out[:, :Nc]
 
 
 class NEIState:

@@ -10,6 +10,12 @@ The reference draws from the JOINT posterior over all N candidates (an N x N Cho
 exists: each candidate is its own t-batch (``X.unsqueeze(-2)``, q = 1), i.e. mean_i + sqrt(var_i) z_i -- the
 cross-covariance GEMM + triangular-solve path of SURVEY.md row T1; there ``replacement=False`` removes already picked
 candidates draw by draw.
+
+``pathwise=True`` (or ``draw_matheron_paths``) gives JOINT draws at any N: Matheron's rule over random-Fourier-feature
+prior paths (botorch/sampling/pathwise/: prior_samplers.py:51-91, update_strategies.py:72-103,
+posterior_samplers.py:143-199; acquisition/thompson_sampling.py evaluates such a path on a candidate set).  Each draw
+is a function, so the argmax over 1e6 candidates is consistent across them, and a chunk costs one covariance GEMM
+k(X, x) plus two skinny GEMMs instead of the n^2-per-candidate triangular product of the marginal variance.
 """
 from __future__ import annotations
 
@@ -23,6 +29,7 @@ from torch.nn import Module
 from . import _lib
 from .exceptions import UnsupportedError
 from .models import _FusedExactGP
+from .sampling import draw_sobol_normal_samples
 
 
 def _flip_sub_unique(x: Tensor, k: int) -> Tensor:
@@ -38,9 +45,58 @@ def _flip_sub_unique(x: Tensor, k: int) -> Tensor:
     return x[torch.tensor(keep, dtype=torch.long, device=x.device)]
 
 
+class MatheronPath:
+    """Sample paths f_s(.) of the GP posterior: ``path(X)`` with X ``(...) x d`` returns ``sample_shape x (...)`` values on
+    the outcome scale.  Prior part: F random Fourier features; update part: exact (uses the model's Cholesky factor)."""
+
+    def __init__(self, model: _FusedExactGP, sample_shape: torch.Size, num_features: int = 1024,
+                 chunk_size: int = 16384) -> None:  # fmt: skip
+        from . import engine
+
+        if model._is_fully_bayesian:
+            raise NotImplementedError("PathwiseThompsonSampling is not supported for fully Bayesian models")
+        if num_features % 2:
+            raise UnsupportedError(f"Expected an even number of output features, but received {num_features=}.")
+        model.eval()
+        st = model.gp_state
+        self.sample_shape = torch.Size(sample_shape)
+        S = max(int(self.sample_shape.numel()), 1)
+        d, n, half = st.d, st.n, num_features // 2
+        # the reference's generators, in its order of draws (features/generators.py:114-155, prior_samplers.py:74-80,
+        # update_strategies.py:83): Sobol-normal frequencies and weights, iid normal noise; torch's global generator
+        W = draw_sobol_normal_samples(d=d, n=half, dtype=torch.float64)
+        if st.kernel == "matern52":
+            nu = torch.tensor(2.5, dtype=torch.float64)
+            W = torch.distributions.Gamma(nu, nu).rsample((half, 1)).rsqrt() * W
+        w = draw_sobol_normal_samples(d=num_features, n=S, dtype=torch.float64)
+        eps = torch.randn(S, n, dtype=torch.float64)
+        self.state = engine.PathState(st, W.to(st.device), w.to(st.device), eps.to(st.device))
+        self.chunk_size = int(chunk_size)
+
+    @torch.no_grad()
+    def __call__(self, X: Tensor) -> Tensor:
+        st = self.state.gp
+        if X.device != st.device:
+            raise _lib.BoError(f"X is on {X.device}; the model lives on {st.device}. There is no CPU path.")
+        lead = X.shape[:-1]
+        Xf = X.reshape(-1, X.shape[-1]).to(torch.float64).contiguous()
+        out = torch.empty(self.state.S, Xf.shape[0], dtype=torch.float64, device=st.device)
+        for i in range(0, Xf.shape[0], self.chunk_size):
+            out[:, i : i + self.chunk_size] = self.state.evaluate(Xf[i : i + self.chunk_size])
+        return out.reshape(*self.sample_shape, *lead)
+
+
+def draw_matheron_paths(model: _FusedExactGP, sample_shape: torch.Size, num_features: int = 1024) -> MatheronPath:
+    """botorch/sampling/pathwise/posterior_samplers.py:143-169 for the fused exact GP."""
+    if not isinstance(model, _FusedExactGP):
+        raise UnsupportedError("draw_matheron_paths on the fused path needs a botorch_b200 exact GP model")
+    return MatheronPath(model, sample_shape, num_features=num_features)
+
+
 class MaxPosteriorSampling(Module):
     def __init__(self, model, objective=None, posterior_transform=None, replacement: bool = True,
-                 chunk_size: int = 16384, joint_max: int = 16384) -> None:  # fmt: skip
+                 chunk_size: int = 16384, joint_max: int = 16384, pathwise: bool = False,
+                 num_features: int = 1024) -> None:  # fmt: skip
         super().__init__()
         if objective is not None or posterior_transform is not None:
             raise UnsupportedError("objective / posterior_transform are outside the fused path")
@@ -50,6 +106,7 @@ class MaxPosteriorSampling(Module):
         self.replacement = replacement
         self.chunk_size = int(chunk_size)
         self.joint_max = int(joint_max)  # largest N sampled jointly (N x N covariance: 2 GiB at 16384)
+        self.pathwise, self.num_features = bool(pathwise), int(num_features)
 
     def marginal_posterior(self, X: Tensor):
         """mean, var [M x N] of N candidates, streamed through the GEMM pipeline in chunks."""
@@ -96,6 +153,11 @@ class MaxPosteriorSampling(Module):
         st = self.model.gp_state
         if X.device != st.device:
             raise _lib.BoError(f"X is on {X.device}; the model lives on {st.device}. There is no CPU path.")
+        if self.pathwise:  # joint draws as sample paths (Matheron's rule): any N
+            if observation_noise:
+                raise UnsupportedError("pathwise draws are draws of the latent function (no observation noise)")
+            paths = MatheronPath(self.model, torch.Size([num_samples]), self.num_features, self.chunk_size)
+            return self.maximize_samples(X, paths(X).unsqueeze(-1), num_samples)
         if joint is None:
             joint = X.shape[0] <= self.joint_max
         if joint:

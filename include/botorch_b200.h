@@ -216,6 +216,35 @@ size_t bo_mll_workspace_bytes(const bo_gp* gp);
 int bo_mll_value_grad(bo_ctx* ctx, const bo_gp* gp, void* work, size_t work_bytes, double* value, double* grad,
                       int32_t* info, void* stream);
 
+/* ---- pathwise (Matheron) posterior samples (second half) -----------------------------------------
+ * Replaces draw_matheron_paths (sampling/pathwise/posterior_samplers.py:143-199) for the exact single-model GP:
+ *   prior path   f0(x) = m + phi(x) . w,  phi(x) = sqrt(os) sqrt(2/F) [sin(W x/l), cos(W x/l)]      (random Fourier features:
+ *                sampling/pathwise/features/generators.py:66-110, prior_samplers.py:51-91, utils.py:84-117)
+ *   update       v = (K + D)^-1 (y - f0(X) - sqrt(D) eps),  path(x) = f0(x) + k(x, X) v          (update_strategies.py:72-103)
+ *   output       y_mean + y_std * path(x)                                                       (Standardize.untransform)
+ * The random draws are INPUTS (the host makes them with the reference's generators: draw_sobol_normal_samples for W and w,
+ * randn for eps), so a path is a deterministic function of them.  Unlike the marginal form of bo_posterior_mean_var, the
+ * S paths are JOINT draws over any number of candidates: Thompson sampling over 1e6 points costs one covariance GEMM
+ * k(X, x) and two skinny GEMMs per candidate chunk, no n^2-per-candidate triangular product.  M = 1 models only
+ * (the reference rejects fully Bayesian models, acquisition/thompson_sampling.py:47-50). */
+typedef struct bo_paths {
+    int32_t S, F;          /* sample paths; Fourier features (even): F/2 frequencies */
+    const double* W;       /* [F/2 x d]  frequencies (standard normal for RBF; the host scales them for Matern) */
+    const double* w;       /* [S x F]    feature weights */
+    const double* eps;     /* [S x n]    standard-normal noise draws (scaled by sqrt(noise) inside) */
+    /* state filled by bo_paths_setup (caller allocated) */
+    double* w_aug;         /* [F/2 x Kp]     frequencies as a distance-contraction operand: [W, W.(center/l), 0] */
+    double* w_pad;         /* [S x pad8(F)]  */
+    double* v;             /* [S x pad8(n)]  update weights */
+} bo_paths;
+size_t bo_paths_setup_workspace_bytes(const bo_gp* gp, const bo_paths* paths);
+/* needs the factors of bo_gp_setup */
+int bo_paths_setup(bo_ctx* ctx, const bo_gp* gp, const bo_paths* paths, void* work, size_t work_bytes, void* stream);
+size_t bo_paths_eval_workspace_bytes(const bo_gp* gp, const bo_paths* paths, long Nc);
+/* out [S x pad8(Nc)]: every path at Nc points Xc [Nc x d] (outcome scale) */
+int bo_paths_eval(bo_ctx* ctx, const bo_gp* gp, const bo_paths* paths, long Nc, const double* Xc, double* out, void* work,
+                  size_t work_bytes, void* stream);
+
 /* ---- building blocks exported for the parity tests ------------------------------------------ */
 int bo_dgemm(bo_ctx* ctx, int M, int N, int K, int batch, double alpha, const double* A, long lda, long strideA,
              const double* B, long ldb, long strideB, double beta, double* C, long ldc, long strideC, int tri,

@@ -1,0 +1,108 @@
+"""GPU parity of pathwise (Matheron) posterior samples (bo_paths_setup / bo_paths_eval) against the
+oracle restatement, plus the properties that pin the construction: interpolation of the data as the noise vanishes,
+agreement of the path ensemble with the exact posterior, and the Thompson argmax over a candidate set."""
+import pytest
+import torch
+
+from oracle import pathwise as opw
+from tests.util import rel_err
+
+pytestmark = pytest.mark.gpu
+
+TOL = 1e-9
+
+
+def _problem(n, d, kernel, seed, noise=0.02):
+    g = torch.Generator().manual_seed(seed)
+    X = torch.rand(n, d, generator=g, dtype=torch.float64)
+    y = torch.sin(5.0 * X[:, 0]) + X[:, -1] ** 2 + 0.05 * torch.randn(n, generator=g, dtype=torch.float64)
+    ls = 0.3 + torch.rand(d, generator=g, dtype=torch.float64)
+    h = {"lengthscale": ls, "noise": torch.tensor(noise, dtype=torch.float64), "mean": torch.tensor(0.1, dtype=torch.float64),
+         "outputscale": torch.tensor(1.3, dtype=torch.float64) if kernel == "matern52" else None}  # fmt: skip
+    return X, y, h
+
+
+def _draws(S, F, d, n, seed):
+    g = torch.Generator().manual_seed(seed)
+    return (torch.randn(F // 2, d, generator=g, dtype=torch.float64), torch.randn(S, F, generator=g, dtype=torch.float64),
+            torch.randn(S, n, generator=g, dtype=torch.float64))  # fmt: skip
+
+
+@pytest.mark.parametrize("n,d,kernel,S,F,N", [(40, 3, "rbf", 4, 64, 50), (150, 6, "matern52", 3, 256, 1000),
+                                             (300, 12, "rbf", 1, 1024, 777), (65, 2, "rbf", 16, 128, 9)])  # fmt: skip
+def test_paths_match_oracle(cuda, n, d, kernel, S, F, N):
+    from botorch_b200.engine import GPState, PathState
+
+    X, y, h = _problem(n, d, kernel, seed=n)
+    ymean, ystd = float(y.mean()), float(y.std())
+    t = (y - ymean) / ystd
+    W, w, eps = _draws(S, F, d, n, seed=n + 1)
+    Xc = torch.rand(N, d, dtype=torch.float64, generator=torch.Generator().manual_seed(3))
+    gp = GPState(X.to(cuda), t.to(cuda), kernel, h["lengthscale"].to(cuda), h["noise"].to(cuda), h["mean"].to(cuda),
+                 None if h["outputscale"] is None else h["outputscale"].to(cuda), y_mean=ymean, y_std=ystd)  # fmt: skip
+    ps = PathState(gp, W.to(cuda), w.to(cuda), eps.to(cuda))
+    got = ps.evaluate(Xc.to(cuda)).cpu()
+    ref = opw.matheron_paths(Xc, X, t, kernel, h["lengthscale"], h["noise"], h["mean"], h["outputscale"], W, w, eps, ymean, ystd)
+    assert got.shape == (S, N)
+    assert rel_err(got, ref, scale=float(ref.abs().max())) < TOL
+    # Thompson pick per path: same argmax index
+    assert torch.equal(got.argmax(dim=-1), ref.argmax(dim=-1))
+
+
+def test_zero_draws_give_the_posterior_mean(cuda):
+    """With w = 0 and eps = 0 a path is m + k(x, X) (K + s2 I)^-1 (y - m): exactly the posterior mean of the model."""
+    from botorch_b200 import SingleTaskGP, draw_matheron_paths
+    from botorch_b200.engine import PathState
+
+    X, y, h = _problem(60, 2, "rbf", seed=8)
+    model = SingleTaskGP(X.to(cuda), y.unsqueeze(-1).to(cuda), lengthscale=h["lengthscale"], noise=1e-2)
+    st = model.gp_state
+    F = 32
+    ps = PathState(st, torch.randn(F // 2, 2, dtype=torch.float64).to(cuda), torch.zeros(2, F, dtype=torch.float64).to(cuda),
+                   torch.zeros(2, 60, dtype=torch.float64).to(cuda))  # fmt: skip
+    Xc = torch.rand(33, 2, dtype=torch.float64, generator=torch.Generator().manual_seed(4)).to(cuda)
+    mean = model.posterior(Xc.unsqueeze(0)).mean.reshape(-1)
+    vals = ps.evaluate(Xc)
+    assert rel_err(vals[0], mean) < TOL and rel_err(vals[1], mean) < TOL
+    # the public constructor: sample_shape leads, the input's leading dims follow
+    torch.manual_seed(0)
+    paths = draw_matheron_paths(model, torch.Size([5]), num_features=512)
+    assert paths(X.to(cuda)).shape == (5, 60)
+    assert paths(X.to(cuda).reshape(6, 10, 2)).shape == (5, 6, 10)
+    with pytest.raises(Exception):
+        draw_matheron_paths(model, torch.Size([2]), num_features=33)
+
+
+def test_path_ensemble_matches_exact_posterior_moments(cuda):
+    from botorch_b200 import SingleTaskGP, draw_matheron_paths
+
+    X, y, h = _problem(80, 3, "rbf", seed=5, noise=0.05)
+    model = SingleTaskGP(X.to(cuda), y.unsqueeze(-1).to(cuda), lengthscale=h["lengthscale"], noise=0.05)
+    Xc = torch.rand(40, 3, dtype=torch.float64, generator=torch.Generator().manual_seed(1)).to(cuda)
+    torch.manual_seed(1)
+    vals = draw_matheron_paths(model, torch.Size([2048]), num_features=2048)(Xc)
+    post = model.posterior(Xc.unsqueeze(0))
+    mean, var = post.mean.reshape(-1), post.variance.reshape(-1)
+    sd = var.sqrt().clamp_min(1e-3)
+    assert float(((vals.mean(0) - mean).abs() / sd).max()) < 0.15  # ~ 6 / sqrt(2048) standard errors
+    assert float((vals.var(0) / var.clamp_min(1e-6) - 1.0).abs().median()) < 0.15  # RFF prior + Monte-Carlo error
+
+
+def test_pathwise_thompson_sampling_over_a_candidate_set(cuda):
+    from botorch_b200 import MaxPosteriorSampling, SingleTaskGP
+
+    X, y, h = _problem(100, 4, "rbf", seed=12)
+    model = SingleTaskGP(X.to(cuda), y.unsqueeze(-1).to(cuda), lengthscale=h["lengthscale"], noise=0.01)
+    cand = torch.rand(50000, 4, dtype=torch.float64, generator=torch.Generator().manual_seed(2)).to(cuda)
+    ts = MaxPosteriorSampling(model, pathwise=True, num_features=256, chunk_size=8192)
+    torch.manual_seed(3)
+    picks = ts(cand, num_samples=4)
+    assert picks.shape == (4, 4)
+    # every pick is a row of the candidate set, and good picks beat the average candidate under the posterior mean
+    assert all(bool((cand == p).all(dim=-1).any()) for p in picks)
+    mean_all = model.posterior(cand[:4096].unsqueeze(0)).mean.mean()
+    assert float(model.posterior(picks.unsqueeze(0)).mean.mean()) > float(mean_all)
+    ts_nr = MaxPosteriorSampling(model, pathwise=True, num_features=256, replacement=False)
+    torch.manual_seed(3)
+    picks_nr = ts_nr(cand[:2000], num_samples=3)
+    assert len({tuple(p.tolist()) for p in picks_nr}) == 3

@@ -297,3 +297,34 @@ def test_fit_host_prior_terms_match_the_oracle():
         assert torch.allclose(lp, ref.detach(), rtol=1e-14, atol=1e-14)
         assert torch.allclose(dlp, gref, rtol=1e-13, atol=1e-13)
     assert bfit.lengthscale_prior_params(20) == (2.0**0.5 + 0.5 * __import__("math").log(20), 3.0**0.5)
+
+
+# ---- pathwise (Matheron) sampling oracle (oracle/pathwise.py) ----------------------------------------------------------
+def test_pathwise_oracle_is_consistent_with_the_exact_posterior():
+    """No reference fixture exists for sample paths; the restatement is pinned by its defining properties against the
+    posterior oracle: zero draws give the posterior mean, and the path ensemble reproduces the posterior moments (the
+    covariance up to the random-feature approximation of the prior)."""
+    from oracle import pathwise as opw
+    from oracle.gp import GPHyper, OracleGP
+
+    g = torch.Generator().manual_seed(0)
+    n, d, F, S = 30, 2, 4096, 3000
+    X = torch.rand(n, d, generator=g, dtype=torch.float64)
+    y = torch.sin(4 * X[:, :1]) + 0.1 * torch.randn(n, 1, generator=g, dtype=torch.float64)
+    h = GPHyper("rbf", torch.tensor([0.4, 0.7], dtype=torch.float64), torch.tensor(0.05, dtype=torch.float64),
+                torch.tensor(0.1, dtype=torch.float64), None)
+    gp = OracleGP(X, y, h, standardize=True)
+    Xc = torch.rand(12, d, generator=g, dtype=torch.float64)
+    mean, cov = gp.posterior(Xc)
+    args = (Xc, X, gp.train_targets, "rbf", h.lengthscale, h.noise, h.mean, None)
+    W = torch.randn(F // 2, d, generator=g, dtype=torch.float64)
+    zero = opw.matheron_paths(*args, W, torch.zeros(1, F, dtype=torch.float64), torch.zeros(1, n, dtype=torch.float64),
+                              float(gp.y_mean), float(gp.y_std))
+    assert torch.allclose(zero[0], mean.reshape(-1), rtol=1e-10, atol=1e-12)
+    w = torch.randn(S, F, generator=g, dtype=torch.float64)
+    eps = torch.randn(S, n, generator=g, dtype=torch.float64)
+    vals = opw.matheron_paths(*args, W, w, eps, float(gp.y_mean), float(gp.y_std))
+    sd = cov.diagonal(dim1=-2, dim2=-1).reshape(-1).sqrt()
+    assert float(((vals.mean(0) - mean.reshape(-1)).abs() / sd).max()) < 0.12
+    emp = torch.cov(vals.T)
+    assert float((emp - cov.reshape(12, 12)).abs().max() / cov.abs().max()) < 0.15
