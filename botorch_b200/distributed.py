@@ -197,6 +197,23 @@ def _winner(vals: Tensor, idxs: Tensor) -> Tensor:
     return masked.min(dim=0).values
 
 
+def pathwise_shard_scores(sampler, X: Tensor, num_samples: int, seed: int, lo: int, hi: int):
+    """(best value, global index) per sample path over the candidate block [lo, hi).  Every rank draws the SAME paths: the
+    host generators run from ``seed`` (state restored afterwards), so the S functions are identical everywhere and only
+    the candidates are sharded."""
+    from .generation import MatheronPath
+
+    state = torch.random.get_rng_state()
+    torch.manual_seed(seed)
+    try:
+        paths = MatheronPath(sampler.model, torch.Size([num_samples]), sampler.num_features, sampler.chunk_size)
+    finally:
+        torch.random.set_rng_state(state)
+    vals = paths(X[lo:hi])
+    v, i = vals.max(dim=-1)  # first occurrence on ties
+    return v, i + lo
+
+
 def thompson_sample_sharded(sampler, X: Tensor, num_samples: int = 1, seed: int = 0, shard=None) -> Tensor:
     """``MaxPosteriorSampling`` (marginal form, SURVEY.md row T1 / 8e "C5: shard N") over a candidate set sharded across
     the process group: rank r scores the contiguous block ``shard_range(N, r, G)``; (value, global index) pairs are
@@ -207,7 +224,6 @@ def thompson_sample_sharded(sampler, X: Tensor, num_samples: int = 1, seed: int 
     rank, ws = world() if shard is None else shard
     gather = shard is None and ws > 1
     lo, hi = shard_range(X.shape[0], rank, ws)
-    scorer = _ShardScorer(sampler, X, lo, hi)
 
     def all_ranks(v: Tensor, i: Tensor):
         if not gather:
@@ -218,6 +234,14 @@ def thompson_sample_sharded(sampler, X: Tensor, num_samples: int = 1, seed: int 
         dist.all_gather(gi, i)
         return torch.stack(gv), torch.stack(gi)
 
+    if getattr(sampler, "pathwise", False):  # joint draws: one function per sample, argmax over all shards
+        if not sampler.replacement:
+            from .exceptions import UnsupportedError
+
+            raise UnsupportedError("sharded pathwise Thompson sampling draws with replacement")
+        V, I = all_ranks(*pathwise_shard_scores(sampler, X, num_samples, seed, lo, hi))
+        return X[_winner(V, I)]
+    scorer = _ShardScorer(sampler, X, lo, hi)
     if sampler.replacement:
         picks = [scorer.pick(s, seed) for s in range(num_samples)]
         V, I = all_ranks(torch.cat([p[0] for p in picks]), torch.cat([p[1] for p in picks]))

@@ -106,3 +106,21 @@ def test_pathwise_thompson_sampling_over_a_candidate_set(cuda):
     torch.manual_seed(3)
     picks_nr = ts_nr(cand[:2000], num_samples=3)
     assert len({tuple(p.tolist()) for p in picks_nr}) == 3
+
+
+def test_sharded_pathwise_thompson_is_sharding_invariant(cuda):
+    """Every shard draws the same paths (same host seed); winners over 1 and over 3 shards coincide."""
+    from botorch_b200 import MaxPosteriorSampling, SingleTaskGP
+    from botorch_b200.distributed import _winner, pathwise_shard_scores, shard_range, thompson_sample_sharded
+
+    X, y, h = _problem(80, 3, "rbf", seed=14)
+    model = SingleTaskGP(X.to(cuda), y.unsqueeze(-1).to(cuda), lengthscale=h["lengthscale"], noise=0.01)
+    cand = torch.rand(10001, 3, dtype=torch.float64, generator=torch.Generator().manual_seed(6)).to(cuda)
+    ts = MaxPosteriorSampling(model, pathwise=True, num_features=128, chunk_size=4096)
+    single = thompson_sample_sharded(ts, cand, num_samples=5, seed=11, shard=(0, 1))
+    parts = [pathwise_shard_scores(ts, cand, 5, 11, *shard_range(cand.shape[0], r, 3)) for r in range(3)]
+    win = _winner(torch.stack([p[0] for p in parts]), torch.stack([p[1] for p in parts]))
+    assert torch.equal(cand[win], single)
+    state = torch.random.get_rng_state()
+    thompson_sample_sharded(ts, cand, num_samples=2, seed=3, shard=(0, 1))
+    assert torch.equal(state, torch.random.get_rng_state())  # the caller's host RNG stream is left untouched
