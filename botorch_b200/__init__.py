@@ -16,7 +16,7 @@ from .acquisition import (  # noqa: F401
     qNoisyExpectedImprovement,
 )
 from .fit import ExactMarginalLogLikelihood, fit_gpytorch_mll, fit_gpytorch_mll_scipy  # noqa: F401
-from .generation import MatheronPath, MaxPosteriorSampling, draw_matheron_paths  # noqa: F401
+from .generation import MatheronPath, MaxPosteriorSampling, PathwiseThompsonSampling, draw_matheron_paths  # noqa: F401
 from .models import SaasFullyBayesianSingleTaskGP, SingleTaskGP, Standardize  # noqa: F401
 from .optim import (  # noqa: F401
     gen_batch_initial_conditions,

@@ -70,7 +70,7 @@ class BoNEI(C.Structure):
 
 
 class BoPaths(C.Structure):
-    _fields_ = [("S", C.c_int32), ("F", C.c_int32)] + [(name, C.c_void_p) for name in "W w eps w_aug w_pad v".split()]
+    _fields_ = [("S", C.c_int32), ("F", C.c_int32)] + [(name, C.c_void_p) for name in "W w eps w_aug w_pad v w_t v_t".split()]
 
 
 class BoLBFGS(C.Structure):
@@ -153,12 +153,15 @@ def _declare(lib: C.CDLL) -> None:
     lib.bo_paths_eval_workspace_bytes.restype = sz
     lib.bo_paths_eval_workspace_bytes.argtypes = [gp, pt, i64]
     lib.bo_paths_eval.argtypes = [vp, gp, pt, i64, vp, vp, vp, sz, vp]
+    lib.bo_paths_grad_workspace_bytes.restype = sz
+    lib.bo_paths_grad_workspace_bytes.argtypes = [gp, pt, i64]
+    lib.bo_paths_grad.argtypes = [vp, gp, pt, i64, vp, vp, vp, vp, sz, vp]
     lib.bo_mll_workspace_bytes.restype = sz
     lib.bo_mll_workspace_bytes.argtypes = [gp]
     lib.bo_mll_value_grad.argtypes = [vp, gp, vp, sz, vp, vp, vp, vp]
     for name in (
         "bo_ctx_create bo_gp_setup bo_nei_setup bo_ei_setup bo_qlognei_fwd bo_qlognei_bwd bo_posterior_joint bo_posterior_joint_bwd "
-        "bo_posterior_mean_var bo_ts_argmax bo_argmax bo_dgemm bo_kernel_matrix bo_potrf bo_mll_value_grad bo_paths_setup bo_paths_eval"
+        "bo_posterior_mean_var bo_ts_argmax bo_argmax bo_dgemm bo_kernel_matrix bo_potrf bo_mll_value_grad bo_paths_setup bo_paths_eval bo_paths_grad"
     ).split():
         getattr(lib, name).restype = i32
 

@@ -1166,6 +1166,13 @@ int bo_paths_setup(bo_ctx* ctx, const bo_gp* gp, const bo_paths* paths, void* wo
     BO_TRY(bo_fill(paths->v, S * np, 0.0, st));
     BO_TRY(gemm((int)S, (int)n, (int)n, 1, 1.0, w.t, np, 0, gp->linv_aug, np, 0, 0.0, nullptr, 0, 0, paths->v, np, 0,
                 BO_TRI_B_LOWER, 0, st));
+    if (paths->w_t && paths->v_t) {  // transposed copies for the gradient path
+        const long Sp = bo_pad8(S);
+        BO_TRY(bo_fill(paths->w_t, F * Sp, 0.0, st));
+        BO_TRY(bo_transpose(paths->w, F, 0, paths->w_t, Sp, 0, (int)S, (int)F, 1, st));
+        BO_TRY(bo_fill(paths->v_t, n * Sp, 0.0, st));
+        BO_TRY(bo_transpose(paths->v, np, 0, paths->v_t, Sp, 0, (int)S, (int)n, 1, st));
+    }
     BO_CUDA_TRY(cudaGetLastError());
     return BO_OK;
 }
@@ -1196,6 +1203,106 @@ int bo_paths_eval(bo_ctx* ctx, const bo_gp* gp, const bo_paths* paths, long Nc, 
     g_bo_launch_count++;
     BO_CUDA_TRY(cudaGetLastError());
     return BO_OK;
+}
+
+}  // extern "C"
+
+namespace {
+
+// wlsT[t][f] = W[f % half][t] / l[t]   ([d x pad8(F)]: the frequency matrix stacked twice, transposed, in input units)
+__global__ void paths_wlsT_kernel(const double* W, const double* inv_ls, double* wlsT, int half, int d, long Fp) {
+    const int t = blockIdx.y;
+    const long f = blockIdx.x * (long)blockDim.x + threadIdx.x;
+    if (f < Fp) wlsT[(long)t * Fp + f] = f < 2 * half ? W[(f % half) * d + t] * inv_ls[t] : 0.0;
+}
+
+struct PathsGradWork { double *baug, *PhiT, *kx, *wd, *R, *H, *gT, *wlsT; long ldn; int ks; bool ok; size_t bytes; };
+PathsGradWork paths_grad_layout(const bo_gp* gp, const bo_paths* p, long Nc, void* work, size_t cap) {
+    PathsGradWork w{};
+    const long Kp = bo_kp(gp->d);
+    w.ldn = bo_pad8(Nc);
+    Bump b(work, cap);
+    w.baug = b.doubles(Kp * w.ldn);
+    w.PhiT = b.doubles((long)p->F * w.ldn);
+    w.kx = b.doubles((long)gp->n * w.ldn);
+    w.wd = gp->kernel_id != BO_KERNEL_RBF ? b.doubles((long)gp->n * w.ldn) : nullptr;
+    w.R = b.doubles((long)p->F * w.ldn);
+    w.ks = hsplit(gp);
+    w.H = b.doubles((long)w.ks * (gp->d + 1) * w.ldn);
+    w.gT = b.doubles((long)gp->d * w.ldn);
+    w.wlsT = b.doubles((long)gp->d * bo_pad8(p->F));
+    w.ok = b.ok; w.bytes = b.off;
+    return w;
+}
+
+}  // namespace
+
+extern "C" {
+
+size_t bo_paths_grad_workspace_bytes(const bo_gp* gp, const bo_paths* paths, long Nc) {
+    return paths_grad_layout(gp, paths, Nc, nullptr, 0).bytes;
+}
+
+int bo_paths_grad(bo_ctx* ctx, const bo_gp* gp, const bo_paths* paths, long Nc, const double* Xc, const double* out_bar,
+                  double* grad_X, void* work, size_t work_bytes, void* stream) {
+    if (!ctx || !valid_gp(gp) || !valid_paths(gp, paths) || !paths->w_t || !paths->v_t || !gp->xt_aug || Nc <= 0 || !Xc ||
+        !out_bar || !grad_X || !work)
+        return BO_ERR_INVALID;
+    cudaStream_t st = (cudaStream_t)stream;
+    const PathsGradWork w = paths_grad_layout(gp, paths, Nc, work, work_bytes);
+    if (!w.ok) return BO_ERR_WORKSPACE;
+    const long n = gp->n, np = bo_pad8(n), Kp = bo_kp(gp->d), S = paths->S, F = paths->F, half = F / 2, Sp = bo_pad8(S);
+    const long ldn = w.ldn, Fp = bo_pad8(F);
+    const int d = gp->d;
+    const BoKernelHyper h = hyper_of(gp);
+    BO_TRY(bo_aug_cols(h, Xc, Nc, w.baug, Kp, ldn, Kp * ldn, st));
+    BO_TRY(paths_features(gp, paths, w.baug, Nc, ldn, w.PhiT, st));
+    BO_TRY(kmat(gp, gp->aug_train, (int)n, w.baug, ldn, Nc, w.kx, ldn, n * ldn, 0, nullptr, st, w.wd));
+    // feature part: R = ys (w^T out_bar) .* d phi / dz = [ (w_lo^T out_bar) .* cos ; -(w_hi^T out_bar) .* sin ]
+    for (int part = 0; part < 2; part++) {
+        BoGemm g{};
+        g.A = paths->w_t + (long)part * half * Sp; g.lda = Sp; g.strideA = 0;
+        g.B = out_bar; g.ldb = ldn; g.strideB = 0;
+        g.C = w.R + (long)part * half * ldn; g.ldc = ldn; g.strideC = 0;
+        g.E = w.PhiT + (long)(1 - part) * half * ldn; g.lde = ldn; g.strideE = 0;
+        g.alpha = part == 0 ? gp->y_std : -gp->y_std; g.M = (int)half; g.N = (int)Nc; g.K = (int)S; g.batch = 1;
+        g.epi = BO_EPI_LINEAR;
+        BO_TRY(bo_gemm_launch(g, st));
+    }
+    // grad^T [d x N] = [W / l stacked twice]^T R; its transposed copy IS grad_X [N x d]
+    {
+        dim3 grid((unsigned)((Fp + 127) / 128), (unsigned)d);
+        paths_wlsT_kernel<<<grid, 128, 0, st>>>(paths->W, gp->inv_ls, w.wlsT, (int)half, d, Fp);
+        g_bo_launch_count++;
+        BoGemm g{};
+        g.A = w.wlsT; g.lda = Fp; g.strideA = 0;
+        g.B = w.R; g.ldb = ldn; g.strideB = 0;
+        g.C = w.gT; g.ldc = ldn; g.strideC = 0;
+        g.CT = grad_X; g.ldct = d; g.strideCT = 0;
+        g.alpha = 1.0; g.M = d; g.N = (int)Nc; g.K = (int)F; g.batch = 1; g.epi = BO_EPI_LINEAR;
+        BO_TRY(bo_gemm_launch(g, st));
+    }
+    // data part: G = ys (v^T out_bar) .* g(r) (in place over the derivative factor), H = [X^T; 1] G, grad += (H_t - x_t H_d) / l_t^2
+    double* G = w.wd ? w.wd : w.kx;
+    {
+        BoGemm g{};
+        g.A = paths->v_t; g.lda = Sp; g.strideA = 0;
+        g.B = out_bar; g.ldb = ldn; g.strideB = 0;
+        g.C = G; g.ldc = ldn; g.strideC = 0;
+        g.E = G; g.lde = ldn; g.strideE = 0;
+        g.alpha = gp->y_std; g.M = (int)n; g.N = (int)Nc; g.K = (int)S; g.batch = 1; g.epi = BO_EPI_LINEAR;
+        BO_TRY(bo_gemm_launch(g, st));
+    }
+    const long strideH = (long)(d + 1) * ldn;
+    if (w.ks > 1) {
+        const long kc = n / w.ks;
+        BO_TRY(gemm(d + 1, (int)Nc, (int)kc, w.ks, 1.0, gp->xt_aug, np, kc, G, ldn, kc * ldn, 0.0, nullptr, 0, 0, w.H, ldn,
+                    strideH, BO_TRI_NONE, 0, st));
+        return bo_kgrad_finalize(h, w.H, 0, ldn, Xc, Nc, 1.0, grad_X, w.ks, strideH, st);
+    }
+    BO_TRY(gemm(d + 1, (int)Nc, (int)n, 1, 1.0, gp->xt_aug, np, 0, G, ldn, 0, 0.0, nullptr, 0, 0, w.H, ldn, strideH, BO_TRI_NONE,
+                0, st));
+    return bo_kgrad_finalize(h, w.H, strideH, ldn, Xc, Nc, 1.0, grad_X, 1, 0, st);
 }
 
 // ------------------------------------------------------------------------------------------------

@@ -247,8 +247,9 @@ class PathState:
             raise ValueError(f"inconsistent draws: W {tuple(self.W.shape)}, w {tuple(self.w.shape)}, eps {tuple(self.eps.shape)}")
         z = lambda *s: torch.zeros(*s, dtype=torch.float64, device=dev)
         self.w_aug, self.w_pad, self.v = z(half, gp.Kp), z(self.S, pad8(self.F)), z(self.S, gp.np_)
+        self.w_t, self.v_t = z(self.F, pad8(self.S)), z(gp.n, pad8(self.S))
         self.c = BoPaths(S=self.S, F=self.F, W=ptr(self.W), w=ptr(self.w), eps=ptr(self.eps), w_aug=ptr(self.w_aug),
-                         w_pad=ptr(self.w_pad), v=ptr(self.v))  # fmt: skip
+                         w_pad=ptr(self.w_pad), v=ptr(self.v), w_t=ptr(self.w_t), v_t=ptr(self.v_t))  # fmt: skip
         lib = _lib.lib()
         work = _lib.workspace(lib.bo_paths_setup_workspace_bytes(C.byref(gp.c), C.byref(self.c)), dev)
         check(lib.bo_paths_setup(gp.ctx, C.byref(gp.c), C.byref(self.c), work.data_ptr(), work.numel(), _lib.stream_ptr(dev)))
@@ -268,6 +269,43 @@ class PathState:
         check(lib.bo_paths_eval(gp.ctx, C.byref(gp.c), C.byref(self.c), Nc, ptr(Xc), ptr(out), self._work.data_ptr(),
                                 self._work.numel(), _lib.stream_ptr(gp.device)))  # fmt: skip
         return out[:, :Nc]
+
+    def gradient(self, Xc: Tensor, out_bar: Tensor) -> Tensor:
+        """d(sum out_bar * paths(Xc)) / dXc: Xc [Nc x d], out_bar [S x Nc] -> [Nc x d] (``bo_paths_grad``)."""
+        gp = self.gp
+        Xc = _f64(Xc, gp.device)
+        Nc = Xc.shape[0]
+        lib = _lib.lib()
+        bar = torch.zeros(self.S, pad8(Nc), dtype=torch.float64, device=gp.device)
+        bar[:, :Nc] = out_bar
+        work = _lib.workspace(lib.bo_paths_grad_workspace_bytes(C.byref(gp.c), C.byref(self.c), Nc), gp.device)
+        grad = torch.empty(Nc, gp.d, dtype=torch.float64, device=gp.device)
+        check(lib.bo_paths_grad(gp.ctx, C.byref(gp.c), C.byref(self.c), Nc, ptr(Xc), ptr(bar), ptr(grad), work.data_ptr(),
+                                work.numel(), _lib.stream_ptr(gp.device)))  # fmt: skip
+        return grad
+
+
+class _PathEval(torch.autograd.Function):
+    """paths(X) with the hand-written reverse pass (features and covariance are recomputed, nothing but X is saved)."""
+
+    @staticmethod
+    def forward(ctx, X: Tensor, ps: "PathState"):
+        Xd = _f64(X.detach(), ps.gp.device)
+        ctx.ps, ctx.in_dtype = ps, X.dtype
+        ctx.save_for_backward(Xd)
+        return ps.evaluate(Xd)
+
+    @staticmethod
+    def backward(ctx, out_bar: Tensor):
+        (Xd,) = ctx.saved_tensors
+        return ctx.ps.gradient(Xd, out_bar.to(torch.float64)).to(ctx.in_dtype), None
+
+
+def path_values(ps: "PathState", X: Tensor) -> Tensor:
+    """X: N x d -> [S x N]; differentiable w.r.t. X."""
+    if torch.is_grad_enabled() and X.requires_grad:
+        return _PathEval.apply(X, ps)
+    return ps.evaluate(X.detach())
 
 
 class NEIState:

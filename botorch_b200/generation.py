@@ -73,16 +73,16 @@ class MatheronPath:
         self.state = engine.PathState(st, W.to(st.device), w.to(st.device), eps.to(st.device))
         self.chunk_size = int(chunk_size)
 
-    @torch.no_grad()
     def __call__(self, X: Tensor) -> Tensor:
+        from .engine import path_values
+
         st = self.state.gp
         if X.device != st.device:
             raise _lib.BoError(f"X is on {X.device}; the model lives on {st.device}. There is no CPU path.")
         lead = X.shape[:-1]
-        Xf = X.reshape(-1, X.shape[-1]).to(torch.float64).contiguous()
-        out = torch.empty(self.state.S, Xf.shape[0], dtype=torch.float64, device=st.device)
-        for i in range(0, Xf.shape[0], self.chunk_size):
-            out[:, i : i + self.chunk_size] = self.state.evaluate(Xf[i : i + self.chunk_size])
+        Xf = X.reshape(-1, X.shape[-1])
+        chunks = [path_values(self.state, Xf[i : i + self.chunk_size]) for i in range(0, Xf.shape[0], self.chunk_size)]
+        out = chunks[0] if len(chunks) == 1 else torch.cat(chunks, dim=-1)
         return out.reshape(*self.sample_shape, *lead)
 
 
@@ -91,6 +91,50 @@ def draw_matheron_paths(model: _FusedExactGP, sample_shape: torch.Size, num_feat
     if not isinstance(model, _FusedExactGP):
         raise UnsupportedError("draw_matheron_paths on the fused path needs a botorch_b200 exact GP model")
     return MatheronPath(model, sample_shape, num_features=num_features)
+
+
+class PathwiseThompsonSampling(Module):
+    """Single-outcome Thompson sampling via sample paths (botorch/acquisition/thompson_sampling.py:30-87): the q points of a
+    candidate batch are scored by q independent posterior function draws, ``forward(X: b x q x d) -> b`` sums
+    ``f_j(x_j)`` over the batch, differentiable w.r.t. X so ``optimize_acqf`` can maximise it.  The paths are drawn on the
+    first call (for that q) and kept until ``redraw()``."""
+
+    def __init__(self, model: _FusedExactGP, posterior_transform=None, num_features: int = 1024) -> None:
+        super().__init__()
+        if posterior_transform is not None:
+            raise UnsupportedError("posterior_transform is outside the fused path")
+        if model._is_fully_bayesian:
+            raise NotImplementedError("PathwiseThompsonSampling is not supported for fully Bayesian models")
+        if not isinstance(model, _FusedExactGP):
+            raise UnsupportedError("PathwiseThompsonSampling on the fused path needs a botorch_b200 exact GP model")
+        self.model = model
+        self.num_features = int(num_features)
+        self.batch_size: Optional[int] = None
+        self.samples: Optional[MatheronPath] = None
+
+    def set_X_pending(self, X_pending=None) -> None:
+        if X_pending is not None:
+            raise UnsupportedError("X_pending is not used by pathwise Thompson sampling")
+
+    def redraw(self) -> None:
+        self.samples = MatheronPath(self.model, torch.Size([self.batch_size]), self.num_features)
+
+    def forward(self, X: Tensor) -> Tensor:
+        if X.dim() < 2:
+            raise ValueError(f"Expected X to be `(b) x q x d`, got {tuple(X.shape)}")
+        X3 = X if X.dim() > 2 else X.unsqueeze(0)
+        q = X3.shape[-2]
+        if self.batch_size is None:
+            self.batch_size = q
+            self.redraw()
+        elif self.batch_size != q:
+            raise ValueError(
+                f"The batch size of PathwiseThompsonSampling should not change during a forward pass - was {self.batch_size}, "
+                f"now {q}. Please re-initialize the acquisition if you want to change the batch size."
+            )
+        vals = self.samples(X3)  # [q paths] x batch_shape x [q points]
+        own = torch.diagonal(vals.movedim(0, -2), dim1=-2, dim2=-1)  # path j at point j
+        return own.sum(dim=-1)
 
 
 class MaxPosteriorSampling(Module):

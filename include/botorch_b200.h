@@ -236,6 +236,8 @@ typedef struct bo_paths {
     double* w_aug;         /* [F/2 x Kp]     frequencies as a distance-contraction operand: [W, W.(center/l), 0] */
     double* w_pad;         /* [S x pad8(F)]  */
     double* v;             /* [S x pad8(n)]  update weights */
+    double* w_t;           /* [F x pad8(S)]  w^T  (gradient path) */
+    double* v_t;           /* [n x pad8(S)]  v^T  (gradient path) */
 } bo_paths;
 size_t bo_paths_setup_workspace_bytes(const bo_gp* gp, const bo_paths* paths);
 /* needs the factors of bo_gp_setup */
@@ -244,6 +246,13 @@ size_t bo_paths_eval_workspace_bytes(const bo_gp* gp, const bo_paths* paths, lon
 /* out [S x pad8(Nc)]: every path at Nc points Xc [Nc x d] (outcome scale) */
 int bo_paths_eval(bo_ctx* ctx, const bo_gp* gp, const bo_paths* paths, long Nc, const double* Xc, double* out, void* work,
                   size_t work_bytes, void* stream);
+/* grad_X[Nc x d] = d(sum_{s,c} out_bar[s][c] * path_s(x_c)) / dX: the reverse pass autograd runs through a path when
+ * PathwiseThompsonSampling is maximised with optimize_acqf (acquisition/thompson_sampling.py:60-87, generation/gen.py:211).
+ * out_bar [S x pad8(Nc)].  Feature part: ((w^T out_bar) .* [cos; -sin]) contracted with W / l; data part: the same
+ * fused-epilogue GEMM + [X^T; 1] contraction as the acquisition backward. */
+size_t bo_paths_grad_workspace_bytes(const bo_gp* gp, const bo_paths* paths, long Nc);
+int bo_paths_grad(bo_ctx* ctx, const bo_gp* gp, const bo_paths* paths, long Nc, const double* Xc, const double* out_bar,
+                  double* grad_X, void* work, size_t work_bytes, void* stream);
 
 /* ---- building blocks exported for the parity tests ------------------------------------------ */
 int bo_dgemm(bo_ctx* ctx, int M, int N, int K, int batch, double alpha, const double* A, long lda, long strideA,

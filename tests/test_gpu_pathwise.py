@@ -124,3 +124,50 @@ def test_sharded_pathwise_thompson_is_sharding_invariant(cuda):
     state = torch.random.get_rng_state()
     thompson_sample_sharded(ts, cand, num_samples=2, seed=3, shard=(0, 1))
     assert torch.equal(state, torch.random.get_rng_state())  # the caller's host RNG stream is left untouched
+
+
+@pytest.mark.parametrize("n,d,kernel,S,F,N", [(40, 3, "rbf", 4, 64, 50), (150, 6, "matern52", 3, 256, 300),
+                                             (600, 5, "rbf", 2, 128, 1100), (65, 1, "rbf", 8, 32, 9)])  # fmt: skip
+def test_path_gradient_matches_oracle_autograd(cuda, n, d, kernel, S, F, N):
+    from botorch_b200.engine import GPState, PathState, path_values
+
+    X, y, h = _problem(n, d, kernel, seed=n + 3)
+    ymean, ystd = float(y.mean()), float(y.std())
+    t = (y - ymean) / ystd
+    W, w, eps = _draws(S, F, d, n, seed=n + 5)
+    g = torch.Generator().manual_seed(9)
+    Xc = torch.rand(N, d, dtype=torch.float64, generator=g)
+    coef = torch.randn(S, N, dtype=torch.float64, generator=g)
+    gp = GPState(X.to(cuda), t.to(cuda), kernel, h["lengthscale"].to(cuda), h["noise"].to(cuda), h["mean"].to(cuda),
+                 None if h["outputscale"] is None else h["outputscale"].to(cuda), y_mean=ymean, y_std=ystd)  # fmt: skip
+    ps = PathState(gp, W.to(cuda), w.to(cuda), eps.to(cuda))
+    Xg = Xc.to(cuda).requires_grad_(True)
+    vals = path_values(ps, Xg)
+    (grad,) = torch.autograd.grad((vals * coef.to(cuda)).sum(), Xg)
+    Xr = Xc.clone().requires_grad_(True)
+    ref = opw.matheron_paths(Xr, X, t, kernel, h["lengthscale"], h["noise"], h["mean"], h["outputscale"], W, w, eps, ymean, ystd)
+    (gref,) = torch.autograd.grad((ref * coef).sum(), Xr)
+    assert rel_err(grad, gref, scale=float(gref.abs().max())) < TOL
+
+
+def test_pathwise_thompson_sampling_acquisition_under_optimize_acqf(cuda):
+    from botorch_b200 import PathwiseThompsonSampling, SingleTaskGP, gen_candidates_torch, optimize_acqf
+
+    X, y, h = _problem(50, 2, "rbf", seed=17)
+    model = SingleTaskGP(X.to(cuda), y.unsqueeze(-1).to(cuda), lengthscale=h["lengthscale"], noise=0.01)
+    torch.manual_seed(5)
+    ts = PathwiseThompsonSampling(model, num_features=256)
+    Xq = torch.rand(7, 3, 2, dtype=torch.float64, generator=torch.Generator().manual_seed(1)).to(cuda)
+    v = ts(Xq)
+    assert v.shape == (7,) and ts.batch_size == 3
+    # path j scores point j: the value is the sum of the three paths on their own points
+    vals = ts.samples(Xq)  # [3 x 7 x 3]
+    assert torch.allclose(v, sum(vals[j, :, j] for j in range(3)), rtol=1e-12, atol=1e-12)
+    with pytest.raises(ValueError):
+        ts(Xq[:, :2])
+    bounds = torch.stack([torch.zeros(2), torch.ones(2)]).double().to(cuda)
+    cand, val = optimize_acqf(ts, bounds, q=3, num_restarts=4, raw_samples=64, gen_candidates=gen_candidates_torch,
+                              options={"maxiter": 40, "seed": 0})  # fmt: skip
+    assert cand.shape == (3, 2) and bool(((cand >= 0) & (cand <= 1)).all())
+    raw_best = float(ts(torch.rand(64, 3, 2, dtype=torch.float64, device=cuda)).max())
+    assert float(val) >= raw_best - 1e-6 or float(val) > float(v.max())
