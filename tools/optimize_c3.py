@@ -1,5 +1,6 @@
 """Full-size optimize_acqf at config C3 (n=2000, d=20, q=8, 512 restarts, 32768 raw samples) with the device-resident
-L-BFGS, timed phase by phase.  Usage: python tools/optimize_c3.py [maxiter]"""
+L-BFGS, timed phase by phase; with --fit the hyperparameters are fitted first (fit_gpytorch_mll on the device MLL), i.e. the
+whole fit -> acquire iteration of a BO loop runs on the GPU.  Usage: python tools/optimize_c3.py [maxiter] [--fit]"""
 import json
 import sys
 import time
@@ -10,13 +11,27 @@ sys.path.insert(0, ".")
 import botorch_b200 as bb  # noqa: E402
 from botorch_b200.synthetic import make_problem  # noqa: E402
 
-maxiter = int(sys.argv[1]) if len(sys.argv) > 1 else 50
+args = [a for a in sys.argv[1:] if not a.startswith("--")]
+maxiter = int(args[0]) if args else 50
 dev = torch.device("cuda:0")
 p = make_problem("C3")
 h = p.hypers
-t0 = time.perf_counter()
-model = bb.SingleTaskGP(p.train_X.to(dev), p.train_Y.to(dev), lengthscale=h["lengthscale"], noise=h["noise"],
-                        mean_constant=h["mean"])  # fmt: skip
+fit = {}
+if "--fit" in sys.argv:
+    for rep in range(2):
+        model = bb.SingleTaskGP(p.train_X.to(dev), p.train_Y.to(dev))
+        mll = bb.ExactMarginalLogLikelihood(model.likelihood, model)
+        torch.cuda.synchronize()
+        tf = time.perf_counter()
+        bb.fit_gpytorch_mll(mll)
+        torch.cuda.synchronize()
+        fit[f"rep{rep}"] = {"fit_s": time.perf_counter() - tf, "mll_evaluations": mll.evaluations,
+                            "final_mll": float(mll.value_and_grads()[0])}
+    t0 = time.perf_counter()
+else:
+    t0 = time.perf_counter()
+    model = bb.SingleTaskGP(p.train_X.to(dev), p.train_Y.to(dev), lengthscale=h["lengthscale"], noise=h["noise"],
+                            mean_constant=h["mean"])  # fmt: skip
 acqf = bb.qLogNoisyExpectedImprovement(model, p.train_X.to(dev),
                                        sampler=bb.SobolQMCNormalSampler(torch.Size([p.mc_samples]), seed=1234))
 torch.cuda.synchronize()
@@ -44,4 +59,4 @@ for rep in range(2):  # second repetition: graphs, pinned buffers and allocator 
         "mean_final": float(vals.mean()), "improved_restarts": int((vals > start_vals).sum()),
         "gpu_mem_peak_gb": torch.cuda.max_memory_allocated() / 2**30,
     }
-print(json.dumps({"config": "C3 full size", "maxiter": maxiter, "setup_s": t_setup, **out}))
+print(json.dumps({"config": "C3 full size", "maxiter": maxiter, "fit": fit, "setup_s": t_setup, **out}))
