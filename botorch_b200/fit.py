@@ -36,7 +36,8 @@ from .models import MIN_INFERRED_NOISE_LEVEL, MIN_LENGTHSCALE, SingleTaskGP
 
 LOG_2PI = math.log(2.0 * math.pi)
 MIN_OUTPUTSCALE = 1e-6
-_LBFGSB_MAXITER_MAXFUN_REGEX = re.compile("TOTAL NO. of (ITERATIONS REACHED LIMIT|f AND g EVALUATIONS EXCEEDS LIMIT)")
+# optim/core.py:34-36; SciPy >= 1.15 prints the same messages in upper case ("TOTAL NO. OF ...")
+_LBFGSB_MAXITER_MAXFUN_REGEX = re.compile("TOTAL NO. of (ITERATIONS REACHED LIMIT|f AND g EVALUATIONS EXCEEDS LIMIT)", re.IGNORECASE)
 
 
 class ModelFittingError(BotorchError):

@@ -262,3 +262,88 @@ def test_thompson_winner_reduction_and_block_keyed_noise():
     z_mid = bd.ts_base_samples(16000, 33000, 1, 3, torch.device("cpu"))
     assert torch.equal(z_all[16000:33000], z_mid)
     assert not torch.equal(z_all[:100], bd.ts_base_samples(0, 100, 2, 3, torch.device("cpu")))
+
+
+# ---- fit.py host logic (no compute calls into the CUDA library) -----------------------------------------------------------
+def _cpu_model(n=12, d=3):
+    from botorch_b200 import SingleTaskGP
+
+    g = torch.Generator().manual_seed(0)
+    X = torch.rand(n, d, generator=g, dtype=torch.float64)
+    return SingleTaskGP(X, torch.randn(n, 1, generator=g, dtype=torch.float64))
+
+
+def test_fit_parameter_names_bounds_and_prior_resampling():
+    from botorch_b200.fit import ExactMarginalLogLikelihood, get_parameters_and_bounds, sample_all_priors
+
+    model = _cpu_model()
+    mll = ExactMarginalLogLikelihood(model.likelihood, model)
+    assert [k for k, _ in mll.named_parameters()] == [
+        "likelihood.noise_covar.raw_noise", "model.covar_module.raw_lengthscale", "model.mean_module.raw_constant"]  # fmt: skip
+    params, bounds = get_parameters_and_bounds(mll)
+    assert set(params) == {"likelihood.noise_covar.raw_noise", "model.covar_module.raw_lengthscale", "model.mean_module.raw_constant"}
+    assert bounds["model.covar_module.raw_lengthscale"] == (2.5e-2, float("inf"))
+    assert bounds["likelihood.noise_covar.raw_noise"] == (1e-4, float("inf"))
+    assert "model.mean_module.raw_constant" not in bounds  # ConstantMean carries no constraint
+    before = model.covar_module.raw_lengthscale.detach().clone()
+    torch.manual_seed(1)
+    sample_all_priors(model)
+    after = model.covar_module.raw_lengthscale.detach()
+    assert not torch.equal(before, after) and bool((after >= 2.5e-2).all())
+    assert float(model.likelihood.noise_covar.raw_noise) >= 1e-4
+
+
+def test_scipy_minimize_drives_a_closure_over_named_tensors():
+    from botorch_b200.fit import OptimizationStatus, scipy_minimize
+
+    params = {"a": torch.nn.Parameter(torch.tensor([3.0, -2.0], dtype=torch.float64)),
+              "b": torch.nn.Parameter(torch.tensor(5.0, dtype=torch.float64))}  # fmt: skip
+    target = {"a": torch.tensor([1.0, 0.5], dtype=torch.float64), "b": torch.tensor(-1.0, dtype=torch.float64)}
+
+    def closure():
+        loss = sum(((p - target[k]) ** 2).sum() for k, p in params.items())
+        grads = torch.autograd.grad(loss, list(params.values()))
+        return loss.detach(), grads
+
+    seen = []
+    res = scipy_minimize(closure, params, bounds={"b": (0.0, None)}, callback=lambda p, r: seen.append(r.step))
+    assert res.status == OptimizationStatus.SUCCESS and res.step >= 1 and seen == list(range(1, len(seen) + 1))
+    assert torch.allclose(params["a"].detach(), target["a"], atol=1e-6)
+    assert abs(float(params["b"])) < 1e-8  # the bound is active: optimum at the lower bound 0, not at -1
+    with torch.no_grad():
+        params["a"].copy_(torch.tensor([30.0, -20.0], dtype=torch.float64))
+    stopped = scipy_minimize(closure, params, options={"maxiter": 1})  # iteration limit: STOPPED, not FAILURE
+    assert stopped.status == OptimizationStatus.STOPPED and "ITERATIONS REACHED LIMIT" in stopped.message.upper()
+
+
+def test_fit_gpytorch_mll_retry_policy_on_the_host():
+    import warnings
+
+    from botorch_b200.exceptions import OptimizationWarning
+    from botorch_b200.fit import (ExactMarginalLogLikelihood, ModelFittingError, OptimizationResult, OptimizationStatus,
+                                  fit_gpytorch_mll)  # fmt: skip
+
+    model = _cpu_model()
+    mll = ExactMarginalLogLikelihood(model.likelihood, model)
+    start = model.covar_module.raw_lengthscale.detach().clone()
+    calls = []
+
+    def flaky(mll_, closure=None, **kw):  # warns on the first two attempts, succeeds on the third
+        calls.append(model.covar_module.raw_lengthscale.detach().clone())
+        if len(calls) < 3:
+            warnings.warn("line search failed", OptimizationWarning)
+        return OptimizationResult(step=1, fval=1.0, status=OptimizationStatus.SUCCESS)
+
+    with pytest.warns(OptimizationWarning):
+        out = fit_gpytorch_mll(mll, optimizer=flaky, closure=lambda: None, max_attempts=5)
+    assert out is mll and not mll.training and len(calls) == 3
+    assert torch.equal(calls[0], start) and not torch.equal(calls[1], start)  # attempts 2.. restart from prior samples
+
+    def failing(mll_, closure=None, **kw):
+        warnings.warn("did not converge", OptimizationWarning)
+        return OptimizationResult(step=0, fval=float("nan"), status=OptimizationStatus.FAILURE)
+
+    now = model.covar_module.raw_lengthscale.detach().clone()
+    with pytest.raises(ModelFittingError), pytest.warns(OptimizationWarning):
+        fit_gpytorch_mll(mll, optimizer=failing, closure=lambda: None, max_attempts=2)
+    assert mll.training and torch.equal(model.covar_module.raw_lengthscale.detach(), now)  # rolled back
