@@ -66,6 +66,7 @@ class BoNEI(C.Structure):
         ("reduction", C.c_int32),
         ("no_baseline", C.c_int32),
         ("obj_weight", C.c_double),
+        ("external_df", C.c_int32),
     ]
 
 
@@ -156,12 +157,15 @@ def _declare(lib: C.CDLL) -> None:
     lib.bo_paths_grad_workspace_bytes.restype = sz
     lib.bo_paths_grad_workspace_bytes.argtypes = [gp, pt, i64]
     lib.bo_paths_grad.argtypes = [vp, gp, pt, i64, vp, vp, vp, vp, sz, vp]
+    lib.bo_qlognei_samples_view.argtypes = [gp, nei, i32, i32, C.POINTER(i64), C.POINTER(i64)]
+    lib.bo_mc_reduce_fwd.argtypes = [vp, i32, i32, i32, i64, vp, vp, vp, dbl, dbl, dbl, i32, vp, vp, vp]
+    lib.bo_mc_reduce_bwd.argtypes = [vp, i32, i32, i32, i64, vp, vp, vp, dbl, dbl, dbl, i32, vp, vp, vp, vp, vp]
     lib.bo_mll_workspace_bytes.restype = sz
     lib.bo_mll_workspace_bytes.argtypes = [gp]
     lib.bo_mll_value_grad.argtypes = [vp, gp, vp, sz, vp, vp, vp, vp]
     for name in (
         "bo_ctx_create bo_gp_setup bo_nei_setup bo_ei_setup bo_qlognei_fwd bo_qlognei_bwd bo_posterior_joint bo_posterior_joint_bwd "
-        "bo_posterior_mean_var bo_ts_argmax bo_argmax bo_dgemm bo_kernel_matrix bo_potrf bo_mll_value_grad bo_paths_setup bo_paths_eval bo_paths_grad"
+        "bo_posterior_mean_var bo_ts_argmax bo_argmax bo_dgemm bo_kernel_matrix bo_potrf bo_mll_value_grad bo_paths_setup bo_paths_eval bo_paths_grad bo_qlognei_samples_view bo_mc_reduce_fwd bo_mc_reduce_bwd"
     ).split():
         getattr(lib, name).restype = i32
 

@@ -299,6 +299,14 @@ class qLogNoisyExpectedImprovement(_FusedImprovementBase):
 
     _log = True
 
+    def __new__(cls, model=None, *args, **kwargs):
+        if cls is qLogNoisyExpectedImprovement:  # several outcomes / outcome constraints: botorch_b200/constrained.py
+            from .constrained import ModelListGP, qLogNEIModelList
+
+            if isinstance(model, ModelListGP):
+                return qLogNEIModelList(model, *args, **kwargs)
+        return super().__new__(cls)
+
     def __init__(
         self,
         model: Model,

@@ -592,7 +592,7 @@ int bo_qlognei_fwd(bo_ctx* ctx, const bo_gp* gp, const bo_nei* nei, int B, int q
 int bo_qlognei_bwd(bo_ctx* ctx, const bo_gp* gp, const bo_nei* nei, int B, int q, const double* X,
                    const double* Z_q, double tau_relu, double tau_max, const double* grad_acq, double* grad_X,
                    void* work, size_t work_bytes, void* stream) {
-    if (!ctx || !valid_gp(gp) || !nei || B <= 0 || q <= 0 || !X || !Z_q || !grad_acq || !grad_X || !work)
+    if (!ctx || !valid_gp(gp) || !nei || B <= 0 || q <= 0 || !X || !Z_q || (!grad_acq && !nei->external_df) || !grad_X || !work)
         return BO_ERR_INVALID;
     cudaStream_t st = (cudaStream_t)stream;
     const QWork w = qlayout(gp, nei, B, q, 1, work, work_bytes);
@@ -606,6 +606,7 @@ int bo_qlognei_bwd(bo_ctx* ctx, const bo_gp* gp, const bo_nei* nei, int B, int q
     BoCandArgs a = cand_args(gp, nei, B, q, X, Z_q, tau_relu, tau_max, w);
     a.info = w.info;
     a.grad_acq = grad_acq;
+    a.df_external = nei->external_df;
     a.Sbar = w.Sbar;
     a.gradX = grad_X;
     if (w.qpath) {
@@ -672,6 +673,48 @@ int bo_qlognei_bwd(bo_ctx* ctx, const bo_gp* gp, const bo_nei* nei, int B, int q
     }
     if (!shared) BO_TRY(bo_kgrad(h, nei->X_b, (int)nb, w.W3, w.regionStride, w.ldn, X, B, q, ys2, grad_X, st));
     return BO_OK;
+}
+
+// ------------------------------------------------------------------------------------------------
+// outcome constraints across several models
+// ------------------------------------------------------------------------------------------------
+int bo_qlognei_samples_view(const bo_gp* gp, const bo_nei* nei, int B, int q, long* offset, long* pitch) {
+    if (!valid_gp(gp) || !nei || B <= 0 || q <= 0 || !offset || !pitch || gp->M != 1) return BO_ERR_INVALID;
+    char base[1];
+    const QWork w = qlayout(gp, nei, B, q, 1, base, (size_t)1 << 62);
+    // combined-root path with a baseline: the samples are rows 0..S-1 of the stacked forward output W1; otherwise F
+    const double* rows = (w.qpath && !nei->no_baseline) ? w.W1 : w.F;
+    *offset = (long)(rows - reinterpret_cast<const double*>(base));
+    *pitch = w.ldn;
+    return BO_OK;
+}
+
+static BoReduceArgs reduce_args(int S, int B, int q, long ldn, const double* F, const double* lw, const double* best_f,
+                                double obj_weight, double tau_relu, double tau_max, int reduction) {
+    BoReduceArgs a{};
+    a.S = S; a.B = B; a.q = q; a.reduction = reduction; a.ldn = ldn;
+    a.F = F; a.lw = lw; a.best_f = best_f;
+    a.obj_w = obj_weight != 0.0 ? obj_weight : 1.0; a.tau_relu = tau_relu; a.tau_max = tau_max;
+    return a;
+}
+
+int bo_mc_reduce_fwd(bo_ctx* ctx, int S, int B, int q, long ldn, const double* F, const double* lw, const double* best_f,
+                     double obj_weight, double tau_relu, double tau_max, int reduction, double* acq, double* lse,
+                     void* stream) {
+    if (!ctx || S <= 0 || B <= 0 || q <= 0 || !F || !best_f || !acq || !lse || !(tau_relu > 0.0) || !(tau_max > 0.0))
+        return BO_ERR_INVALID;
+    BoReduceArgs a = reduce_args(S, B, q, ldn, F, lw, best_f, obj_weight, tau_relu, tau_max, reduction);
+    a.acq = acq; a.lse = lse;
+    return bo_mc_reduce_fwd_launch(a, (cudaStream_t)stream);
+}
+
+int bo_mc_reduce_bwd(bo_ctx* ctx, int S, int B, int q, long ldn, const double* F, const double* lw, const double* best_f,
+                     double obj_weight, double tau_relu, double tau_max, int reduction, const double* lse,
+                     const double* grad_acq, double* dF, double* lw_bar, void* stream) {
+    if (!ctx || S <= 0 || B <= 0 || q <= 0 || !F || !best_f || !lse || !grad_acq || !dF) return BO_ERR_INVALID;
+    BoReduceArgs a = reduce_args(S, B, q, ldn, F, lw, best_f, obj_weight, tau_relu, tau_max, reduction);
+    a.lse = const_cast<double*>(lse); a.grad_acq = grad_acq; a.dF = dF; a.lw_bar = lw_bar;
+    return bo_mc_reduce_bwd_launch(a, (cudaStream_t)stream);
 }
 
 // ------------------------------------------------------------------------------------------------

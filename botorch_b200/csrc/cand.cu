@@ -551,7 +551,7 @@ __global__ void __launch_bounds__(CAND_THREADS, (QT <= 8 ? 4 : 1)) cand_bwd_kern
     double* Y = Pm + q * q;    // q*q
     double* mubar = Y + q * q; // q
     double* F = a.F + (long)z * a.strideF;
-    const double g = a.grad_acq[o];
+    const double g = a.df_external ? 0.0 : a.grad_acq[o];
     const double lse = a.lse[o];
     for (int idx = tid; idx < q * q; idx += T) L[idx] = a.Lq[o * q * q + idx];
 
@@ -568,6 +568,17 @@ __global__ void __launch_bounds__(CAND_THREADS, (QT <= 8 ? 4 : 1)) cand_bwd_kern
     for (int p = 0; p < PT; p++) al[p] = 0.0;
     for (int s = tid; s < a.S; s += T) {
         double f[QT], li[QT], gm[QT], zq[QT];
+        if (a.df_external) {  // F already holds d loss / d f: only the accumulations below
+            int p2 = 0;
+#pragma unroll
+            for (int j = 0; j < QT; j++) {
+                const double df = (j < q) ? F[(long)s * a.ldn + c0 + j] : 0.0;
+                am[j] += df;
+#pragma unroll
+                for (int k = 0; k <= j; k++) al[p2++] += df * ((k < q) ? a.Zq[(long)s * q + k] : 0.0);
+            }
+            continue;
+        }
         const double bf = a.best_f[(long)z * a.Sp + s];
 #pragma unroll
         for (int j = 0; j < QT; j++) {
@@ -1016,6 +1027,148 @@ int bo_aug_cols(const BoKernelHyper& h, const double* X, long npts, double* out,
 
 static int set_smem_limit(const void* fn, size_t bytes) {
     if (bytes > 48 * 1024) BO_CUDA_TRY(cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes));
+    return BO_OK;
+}
+
+namespace {
+
+// One CTA per t-batch element: per-sample log improvement (+ log feasibility weight), q-reduction, sample reduction.
+template <int QT>
+__global__ void __launch_bounds__(CAND_THREADS) mc_reduce_fwd_kernel(const BoReduceArgs a) {
+    extern __shared__ __align__(16) double sm[];  // fm[S]
+    __shared__ double red[CAND_THREADS / 32];
+    const int q = a.q, b = blockIdx.x, tid = threadIdx.x, T = blockDim.x, c0 = b * q;
+    const bool plain = (a.reduction == BO_REDUCE_PLAIN);
+    const double inv_tau_relu = 1.0 / a.tau_relu;
+    double local_max = -INFINITY;
+    for (int s = tid; s < a.S; s += T) {
+        double li[QT];
+        const double bf = a.best_f[s];
+#pragma unroll
+        for (int j = 0; j < QT; j++) {
+            li[j] = 0.0;
+            if (j < q) {
+                const double v = a.F[(long)s * a.ldn + c0 + j];
+                const double lw = a.lw ? a.lw[(long)s * a.ldn + c0 + j] : 0.0;
+                li[j] = plain ? fmax(a.obj_w * v - bf, 0.0) * (a.lw ? exp(lw) : 1.0)
+                              : log_fatplus(a.obj_w * v - bf, a.tau_relu, inv_tau_relu) + lw;
+            }
+        }
+        double m;
+        if (plain) {
+            m = li[0];
+#pragma unroll
+            for (int j = 1; j < QT; j++)
+                if (j < q) m = fmax(m, li[j]);
+        } else {
+            m = fatmax_q<QT>(li, q, a.tau_max);
+        }
+        sm[s] = m;
+        local_max = fmax(local_max, m);
+    }
+    __syncthreads();
+    double lse, val;
+    if (plain) {
+        double part = 0.0;
+        for (int s = tid; s < a.S; s += T) part += sm[s];
+        lse = block_reduce_sum(part, red);
+        val = lse / (double)a.S;
+    } else {
+        const double Mx = block_reduce_max(local_max, red);
+        if (isinf(Mx)) {
+            lse = Mx;
+        } else {
+            double part = 0.0;
+            for (int s = tid; s < a.S; s += T) part += exp(sm[s] - Mx);
+            lse = Mx + log(block_reduce_sum(part, red));
+        }
+        val = lse - log((double)a.S);
+    }
+    if (tid == 0) { a.acq[b] = val; a.lse[b] = lse; }
+}
+
+// Reverse of mc_reduce_fwd_kernel: dF[s][c] = d loss / d f, lw_bar[s][c] = d loss / d lw
+template <int QT>
+__global__ void __launch_bounds__(CAND_THREADS) mc_reduce_bwd_kernel(const BoReduceArgs a) {
+    const int q = a.q, b = blockIdx.x, tid = threadIdx.x, T = blockDim.x, c0 = b * q;
+    const bool plain = (a.reduction == BO_REDUCE_PLAIN);
+    const double inv_tau_relu = 1.0 / a.tau_relu;
+    const double g = a.grad_acq[b], lse = a.lse[b];
+    for (int s = tid; s < a.S; s += T) {
+        double f[QT], li[QT], lwv[QT], gm[QT];
+        const double bf = a.best_f[s];
+#pragma unroll
+        for (int j = 0; j < QT; j++) {
+            f[j] = 0.0; li[j] = 0.0; lwv[j] = 0.0; gm[j] = 0.0;
+            if (j < q) {
+                f[j] = a.F[(long)s * a.ldn + c0 + j];
+                lwv[j] = a.lw ? a.lw[(long)s * a.ldn + c0 + j] : 0.0;
+                li[j] = plain ? fmax(a.obj_w * f[j] - bf, 0.0) * (a.lw ? exp(lwv[j]) : 1.0)
+                              : log_fatplus(a.obj_w * f[j] - bf, a.tau_relu, inv_tau_relu) + lwv[j];
+            }
+        }
+        double m, w;
+        int ties = 0;
+        if (plain) {
+            m = li[0];
+#pragma unroll
+            for (int j = 1; j < QT; j++)
+                if (j < q) m = fmax(m, li[j]);
+#pragma unroll
+            for (int j = 0; j < QT; j++)
+                if (j < q && li[j] == m) ties++;
+            w = 1.0 / (double)a.S;
+        } else {
+            m = fatmax_q_grad<QT>(li, q, a.tau_max, gm);
+            w = isinf(lse) ? ((m == lse) ? 1.0 : 0.0) : exp(m - lse);
+        }
+#pragma unroll
+        for (int j = 0; j < QT; j++) {
+            if (j >= q) continue;
+            double df, dl;
+            if (plain) {  // value = relu(obj - bf) * exp(lw); amax spreads its gradient evenly over ties
+                const double hit = (li[j] == m) ? g * w / (double)ties : 0.0;
+                const double ind = a.lw ? exp(lwv[j]) : 1.0;
+                df = (a.obj_w * f[j] - bf >= 0.0) ? hit * a.obj_w * ind : 0.0;
+                dl = hit * li[j];
+            } else {
+                const double dli = isinf(li[j]) ? 0.0 : dlog_fatplus(a.obj_w * f[j] - bf, a.tau_relu, inv_tau_relu);
+                dl = isinf(li[j]) ? 0.0 : g * w * gm[j];
+                df = a.obj_w * dl * dli;
+            }
+            a.dF[(long)s * a.ldn + c0 + j] = df;
+            if (a.lw_bar) a.lw_bar[(long)s * a.ldn + c0 + j] = dl;
+        }
+    }
+}
+
+}  // namespace
+
+int bo_mc_reduce_fwd_launch(const BoReduceArgs& a, cudaStream_t stream) {
+    if (a.q < 1 || a.q > BO_MAX_Q) return BO_ERR_UNSUPPORTED;
+    if (a.B <= 0) return BO_OK;
+    const size_t smem = sizeof(double) * (size_t)a.S;
+    if (smem > 200 * 1024) return BO_ERR_UNSUPPORTED;
+    if (a.q <= 4) {
+        BO_TRY(set_smem_limit((const void*)mc_reduce_fwd_kernel<4>, smem));
+        mc_reduce_fwd_kernel<4><<<a.B, CAND_THREADS, smem, stream>>>(a);
+    } else if (a.q <= 8) {
+        BO_TRY(set_smem_limit((const void*)mc_reduce_fwd_kernel<8>, smem));
+        mc_reduce_fwd_kernel<8><<<a.B, CAND_THREADS, smem, stream>>>(a);
+    } else {
+        BO_TRY(set_smem_limit((const void*)mc_reduce_fwd_kernel<BO_MAX_Q>, smem));
+        mc_reduce_fwd_kernel<BO_MAX_Q><<<a.B, CAND_THREADS, smem, stream>>>(a);
+    }
+    BO_LAUNCH_CHECK();
+    return BO_OK;
+}
+int bo_mc_reduce_bwd_launch(const BoReduceArgs& a, cudaStream_t stream) {
+    if (a.q < 1 || a.q > BO_MAX_Q) return BO_ERR_UNSUPPORTED;
+    if (a.B <= 0) return BO_OK;
+    if (a.q <= 4) mc_reduce_bwd_kernel<4><<<a.B, CAND_THREADS, 0, stream>>>(a);
+    else if (a.q <= 8) mc_reduce_bwd_kernel<8><<<a.B, CAND_THREADS, 0, stream>>>(a);
+    else mc_reduce_bwd_kernel<BO_MAX_Q><<<a.B, CAND_THREADS, 0, stream>>>(a);
+    BO_LAUNCH_CHECK();
     return BO_OK;
 }
 

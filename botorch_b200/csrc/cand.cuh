@@ -46,11 +46,32 @@ struct BoCandArgs {
     double* Sbar;                      // [M][B][q*q]    adjoint of the q x q Schur block
     double* Vbar_mu; long strideVbar;  // row n of the adjoint of V (receives y_std * dmu)
     double* gradX;                     // [M][B][q][d]
+    int df_external;                   // 1: F already holds d loss / d f (constraint-weighted path: the reductions ran outside)
     double* Uinplace; long strideU;    // optional (QT <= 8 kernels): [n_b x ldn] block that receives u_coef * U Sbar in place
     double u_coef;
 };
 
 int bo_cand_fwd(const BoCandArgs& a, cudaStream_t stream);
+
+// Sample / q reductions of SampleReducingMCAcquisitionFunction on a materialised sample matrix (monte_carlo.py:253-330):
+// F [S x ldn] objective-output samples of B t-batches of q points, lw [S x ldn] optional per-sample log feasibility weights
+// (added to the log improvement before the q-reduction: _apply_constraints with log=True), best_f [S].
+struct BoReduceArgs {
+    int S, B, q, reduction;
+    long ldn;
+    const double* F;
+    const double* lw;        // or null
+    const double* best_f;    // [S]
+    double obj_w, tau_relu, tau_max;
+    double* acq;             // [B]
+    double* lse;             // [B]
+    // backward only
+    const double* grad_acq;  // [B]
+    double* dF;              // [S x ldn]  d loss / d f
+    double* lw_bar;          // [S x ldn]  d loss / d lw (or null)
+};
+int bo_mc_reduce_fwd_launch(const BoReduceArgs& a, cudaStream_t stream);
+int bo_mc_reduce_bwd_launch(const BoReduceArgs& a, cudaStream_t stream);
 int bo_cand_bwd(const BoCandArgs& a, cudaStream_t stream);
 
 // Y[z][i][b*q+j] (+)= coef * sum_k Xm[z][i][b*q+k] * T[z][b][k][j]     (rows x (B*q) matrices, pitch ldn)

@@ -421,6 +421,28 @@ class NEIState:
         return grad_X
 
 
+    # -- outcome constraints across several models (SURVEY 8f N2): sample rows of the workspace, external sample adjoints --
+    def samples_view(self, work: Tensor, B: int, q: int) -> Tensor:
+        """[S x pitch] view of the cached-Cholesky samples a gradient-carrying forward left in ``work`` (M = 1)."""
+        off, pitch = C.c_int64(), C.c_int64()
+        check(_lib.lib().bo_qlognei_samples_view(C.byref(self.gp.c), C.byref(self.c), B, q, C.byref(off), C.byref(pitch)))
+        flat = work[off.value * 8 : (off.value + self.S * pitch.value) * 8].view(torch.float64)
+        return flat.view(self.S, pitch.value)
+
+    def backward_external(self, X: Tensor, Z_q: Tensor, tau_relu: float, tau_max: float, work: Tensor) -> Tensor:
+        """Reverse pass with d loss / d f supplied in the sample rows of ``work`` -> grad_X [M x B x q x d]."""
+        B, q, d = X.shape
+        grad_X = torch.empty(self.gp.M, B, q, d, dtype=torch.float64, device=self.device)
+        self.c.external_df = 1
+        try:
+            check(_lib.lib().bo_qlognei_bwd(self.gp.ctx, C.byref(self.gp.c), C.byref(self.c), B, q, ptr(X), ptr(Z_q),
+                                            tau_relu, tau_max, None, ptr(grad_X), work.data_ptr(), work.numel(),
+                                            _lib.stream_ptr(self.device)))  # fmt: skip
+        finally:
+            self.c.external_df = 0
+        return grad_X
+
+
 class EIState(NEIState):
     """qEI / qLogEI: no baseline set, a fixed incumbent ``best_f`` ([M] or scalar) instead of per-sample baseline maxima.
 

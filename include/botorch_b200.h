@@ -106,6 +106,9 @@ typedef struct bo_nei {
                                 *    (filled by bo_ei_setup) */
     double obj_weight;         /* objective = obj_weight * f (LinearMCObjective with one outcome, acquisition/objective.py);
                                 * 0 means 1.  best_f (computed or supplied) is in objective space. */
+    int32_t external_df;       /* bo_qlognei_bwd only.  1: the sample rows of the workspace (bo_qlognei_samples_view) already hold
+                                * d loss / d f, written by the caller -- the reductions ran outside (bo_mc_reduce_*: outcome
+                                * constraints couple the outputs of several models per sample); grad_acq is ignored. */
 } bo_nei;
 
 typedef struct bo_ctx bo_ctx;
@@ -168,6 +171,26 @@ int bo_qlognei_fwd(bo_ctx* ctx, const bo_gp* gp, const bo_nei* nei, int B, int q
 int bo_qlognei_bwd(bo_ctx* ctx, const bo_gp* gp, const bo_nei* nei, int B, int q, const double* X,
                    const double* Z_q, double tau_relu, double tau_max, const double* grad_acq, double* grad_X,
                    void* work, size_t work_bytes, void* stream);
+
+/* ---- outcome constraints across several single-output models --------------------------------------
+ * SampleReducingMCAcquisitionFunction with `constraints` (acquisition/monte_carlo.py:253-330, utils/objective.py:134-180):
+ * the feasibility weight of a sample couples the outputs of all models, so the per-sample work splits into
+ *   1. bo_qlognei_fwd per model (with_grad = 1): the cached-Cholesky samples land in its workspace (bo_qlognei_samples_view);
+ *   2. the caller forms log weights lw[s][c] = sum_k log sigmoid(-constraint_k(samples) / eta_k) from those samples;
+ *   3. bo_mc_reduce_fwd on the objective model's samples: log improvement + lw -> fatmax over q -> logmeanexp over samples;
+ *   4. bo_mc_reduce_bwd: d loss / d f of the objective output and d loss / d lw; the caller chains d lw through its
+ *      constraints into per-model sample adjoints, writes them into the sample rows and calls bo_qlognei_bwd with
+ *      nei->external_df = 1 for every model.
+ * Offset (in doubles, from the workspace base) and pitch of the [S x pitch] sample rows of one model (M = 1). */
+int bo_qlognei_samples_view(const bo_gp* gp, const bo_nei* nei, int B, int q, long* offset, long* pitch);
+/* F, lw (or NULL), dF, lw_bar (or NULL): [S x ldn]; best_f [S]; acq, lse, grad_acq: [B].  reduction: BO_REDUCE_*;
+ * with BO_REDUCE_PLAIN the weight multiplies the improvement (acqval.mul(ind), monte_carlo.py:328). */
+int bo_mc_reduce_fwd(bo_ctx* ctx, int S, int B, int q, long ldn, const double* F, const double* lw, const double* best_f,
+                     double obj_weight, double tau_relu, double tau_max, int reduction, double* acq, double* lse,
+                     void* stream);
+int bo_mc_reduce_bwd(bo_ctx* ctx, int S, int B, int q, long ldn, const double* F, const double* lw, const double* best_f,
+                     double obj_weight, double tau_relu, double tau_max, int reduction, const double* lse,
+                     const double* grad_acq, double* dF, double* lw_bar, void* stream);
 
 /* ---- posterior API ------------------------------------------------------------------------- */
 size_t bo_posterior_workspace_bytes(const bo_gp* gp, long Nc);

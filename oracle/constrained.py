@@ -1,0 +1,113 @@
+"""Oracle restatement of constrained qLogNEI over independent single-output models (TEST INFRASTRUCTURE, float64 CPU).
+
+  reference                                                        restated here
+  ---------------------------------------------------------------  ----------------------------------------------
+  acquisition/monte_carlo.py:253-330 (forward, _apply_constraints)   ``OracleConstrainedQLogNEI.forward``
+  utils/objective.py:101-180                                         ``feasibility`` / ``smoothed_log_feasibility``
+  utils/safe_math.py:97-99, 422-451                                  ``logexpit``, ``fatmoid``, ``log_fatmoid``
+  acquisition/utils.py:90-163                                        ``best_feasible_objective`` (no-fallback branch: the
+                                                                      tests construct baselines with a feasible point per sample)
+  sampling/normal.py:88-131, 178-209; utils/low_rank.py:43-82        base samples S x 1 x (n_b+q) x m, outcome k reads [..., k]
+  acquisition/logei.py:364-481                                       per-outcome cached-Cholesky samples (oracle/qlognei.py)
+
+``utils/objective.py`` and ``utils/safe_math.py`` import verbatim from /root/reference: tests/test_oracle_golden.py pins the
+restatements against them (and against literals minted from them, for machines without the reference tree).
+"""
+from __future__ import annotations
+
+import math
+from typing import Callable, List, Sequence
+
+import torch
+from torch import Tensor
+
+from . import qmc, safe_math
+from .gp import OracleGP
+from .qlognei import TAU_MAX, TAU_RELU, OracleQLogNEI
+
+_INV_SQRT_3 = math.sqrt(1 / 3)
+
+
+def logexpit(X: Tensor) -> Tensor:
+    return -torch.nn.functional.softplus(-X, threshold=math.log(torch.finfo(X.dtype).max) / 2)
+
+
+def fatmoid(X: Tensor, tau: float = 1.0) -> Tensor:
+    X = X / tau
+    cauchy = lambda x: 1 / (1 + x.square())
+    return torch.where(X < 0, 2 / 3 * cauchy(X - _INV_SQRT_3), 1 - 2 / 3 * cauchy(X + _INV_SQRT_3))
+
+
+def log_fatmoid(X: Tensor, tau: float = 1.0) -> Tensor:
+    return fatmoid(X, tau=tau).log()
+
+
+def feasibility(constraints, samples: Tensor) -> Tensor:
+    ind = torch.ones(samples.shape[:-1], dtype=torch.bool)
+    for c in constraints:
+        ind = ind.logical_and(c(samples) <= 0)
+    return ind
+
+
+def smoothed_log_feasibility(constraints, samples: Tensor, eta: Sequence[float], fat: bool = True) -> Tensor:
+    out = torch.zeros_like(samples[..., 0])
+    f = log_fatmoid if fat else logexpit
+    for c, e in zip(constraints, eta):
+        out = out + f(-c(samples) / e)
+    return out
+
+
+class OracleConstrainedQLogNEI:
+    """m independent OracleGPs; objective = obj_weight * outcome obj_idx; constraints: callables on (..., m) samples."""
+
+    def __init__(self, models: List[OracleGP], X_baseline: Tensor, constraints: List[Callable[[Tensor], Tensor]], eta,
+                 obj_idx: int = 0, obj_weight: float = 1.0, num_samples: int = 64, seed: int = 1234, fat: bool = True,
+                 tau_relu: float = TAU_RELU, tau_max: float = TAU_MAX):  # fmt: skip
+        self.m, self.S, self.seed = len(models), num_samples, seed
+        self.constraints = constraints
+        # utils/objective.py:167-168: a float eta becomes torch.full((n,), eta) in the DEFAULT dtype (float32 unless the caller
+        # changed it), so 0.05 enters the division as float32(0.05); a tensor eta is used as given
+        self.eta = list(torch.full((len(constraints),), eta)) if not isinstance(eta, Tensor) else list(eta)
+        self.fat, self.obj_idx, self.obj_w = fat, obj_idx, float(obj_weight)
+        self.tau_relu, self.tau_max = tau_relu, tau_max
+        self.X_baseline = X_baseline
+        self.n_b = n_b = X_baseline.shape[0]
+        Zb = qmc.sobol_normal(d=n_b * self.m, n=self.S, seed=seed).view(self.S, n_b, self.m)
+        self.parts = []
+        for k, gp in enumerate(models):
+            o = OracleQLogNEI(gp, X_baseline, num_samples=self.S, seed=seed, tau_relu=tau_relu, tau_max=tau_max)
+            o.Z_b = Zb[:, :, k].contiguous()
+            with torch.no_grad():
+                mean_b, _ = gp.posterior(X_baseline)
+                o.baseline_samples = torch.einsum("ij,sj->si", o.baseline_L, o.Z_b) + mean_b
+            self.parts.append(o)
+        base = torch.stack([o.baseline_samples for o in self.parts], dim=-1)  # S x n_b x m
+        obj_b = self.obj_w * base[..., obj_idx]
+        feas = feasibility(constraints, base)
+        assert bool(feas.any(dim=-1).all()), "oracle covers the branch with a feasible baseline point per sample"
+        self.best_f = torch.where(feas, obj_b, torch.full_like(obj_b, -float("inf"))).amax(dim=-1)  # S
+
+    def _set_q(self, q: int) -> None:
+        full = qmc.sobol_normal(d=(self.n_b + q) * self.m, n=self.S, seed=self.seed).view(self.S, self.n_b + q, self.m)
+        for k, o in enumerate(self.parts):
+            o._Zq_cache[q] = full[:, self.n_b :, k].contiguous()
+
+    def samples(self, X: Tensor) -> Tensor:
+        """S x B x q x m."""
+        self._set_q(X.shape[-2])
+        return torch.stack([o.samples_faithful(X) for o in self.parts], dim=-1)
+
+    def forward(self, X: Tensor) -> Tensor:
+        if X.dim() == 2:
+            X = X.unsqueeze(0)
+        smp = self.samples(X)
+        obj = self.obj_w * smp[..., self.obj_idx]
+        li = safe_math.log_improvement(obj, self.best_f.view(self.S, 1), tau=self.tau_relu)
+        li = li + smoothed_log_feasibility(self.constraints, smp, self.eta, self.fat)
+        return safe_math.logmeanexp(safe_math.fatmax(li, dim=-1, tau=self.tau_max), dim=0)
+
+    def value_and_grad(self, X: Tensor):
+        Xg = X.detach().clone().requires_grad_(True)
+        acq = self.forward(Xg)
+        (g,) = torch.autograd.grad(acq.sum(), Xg)
+        return acq.detach(), g

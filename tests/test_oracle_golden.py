@@ -328,3 +328,95 @@ def test_pathwise_oracle_is_consistent_with_the_exact_posterior():
     assert float(((vals.mean(0) - mean.reshape(-1)).abs() / sd).max()) < 0.12
     emp = torch.cov(vals.T)
     assert float((emp - cov.reshape(12, 12)).abs().max() / cov.abs().max()) < 0.15
+
+
+# ---- outcome constraints: feasibility weights of the product (botorch_b200/constrained.py) and of the
+# oracle (oracle/constrained.py) against literals minted from the reference's utils/safe_math.py + utils/objective.py
+_FEAS_X = [-30.0, -2.5, -0.3, 0.0, 0.4, 3.0, 50.0]
+_LOG_FATMOID = [-7.247053179813573, -2.7539872207593805, -0.976299726026775, -0.6931471805599453, -0.4169842841295436,
+                -0.04952450151883789, -0.0002605454114726355]  # fmt: skip
+_LOG_FATMOID_TAU_HALF = [-8.613579709661215, -3.874534075858838, -1.2751478288557359, -0.6931471805599453,
+                         -0.2615149935538013, -0.015176570258031662, -6.58991390632818e-05]  # fmt: skip
+_LOGEXPIT = [-30.000000000000092, -2.5788897342925496, -0.8543552444685272, -0.6931471805599453, -0.5130152523999526,
+             -0.04858735157374206, -1.9287498479639178e-22]  # fmt: skip
+
+
+def _feasibility_impls():
+    from botorch_b200 import constrained as prod
+    from oracle import constrained as orc
+
+    return [prod, orc]
+
+
+def test_feasibility_weights_match_reference_literals():
+    x = torch.tensor(_FEAS_X, dtype=torch.float64)
+    for impl in _feasibility_impls():
+        assert rel_err(impl.log_fatmoid(x), torch.tensor(_LOG_FATMOID, dtype=torch.float64), scale=1.0) < 1e-14
+        assert rel_err(impl.log_fatmoid(x, tau=0.5), torch.tensor(_LOG_FATMOID_TAU_HALF, dtype=torch.float64), scale=1.0) < 1e-14
+        got, want = impl.logexpit(x), torch.tensor(_LOGEXPIT, dtype=torch.float64)
+        assert bool(((got - want).abs() <= 1e-14 * want.abs().clamp_min(1e-300) + 1e-36).all())
+        assert rel_err(impl.fatmoid(x).log(), impl.log_fatmoid(x), scale=1.0) < 1e-13
+
+
+def test_smoothed_feasibility_indicator_semantics():
+    """utils/objective.py:131-185: product over constraints of sigmoid(-c/eta) (sum of logs), one eta per constraint;
+    the hard indicator is c <= 0 for every constraint."""
+    from botorch_b200 import constrained as prod
+    from oracle import constrained as orc
+
+    g = torch.Generator().manual_seed(0)
+    Z = torch.randn(5, 3, 4, 2, generator=g, dtype=torch.float64)
+    cons = [lambda s: s[..., 1] - 0.2, lambda s: 0.5 * s[..., 0] + s[..., 1]]
+    eta = torch.tensor([1e-2, 0.3], dtype=torch.float64)
+    for fat in (True, False):
+        f = prod.log_fatmoid if fat else prod.logexpit
+        want = f(-cons[0](Z) / eta[0]) + f(-cons[1](Z) / eta[1])
+        got = prod.compute_smoothed_feasibility_indicator(cons, Z, eta, log=True, fat=fat)
+        assert got.shape == Z.shape[:-1] and torch.equal(got, want)
+        assert rel_err(orc.smoothed_log_feasibility(cons, Z, eta, fat), want, scale=1.0) < 1e-15
+        lin = prod.compute_smoothed_feasibility_indicator(cons, Z, eta, log=False, fat=fat)
+        assert rel_err(lin, want.exp(), scale=1.0) < 1e-14
+    hard = (cons[0](Z) <= 0) & (cons[1](Z) <= 0)
+    assert torch.equal(prod.compute_feasibility_indicator(cons, Z), hard)
+    assert torch.equal(orc.feasibility(cons, Z), hard)
+    assert torch.equal(prod.compute_feasibility_indicator(None, Z), torch.ones(5, 3, 4, dtype=torch.bool))
+    with pytest.raises(ValueError):
+        prod.compute_smoothed_feasibility_indicator(cons, Z, torch.ones(3), log=True)
+    # a scalar eta is broadcast as torch.full((n,), eta) in the default dtype, exactly as the reference does (:167-168)
+    a = prod.compute_smoothed_feasibility_indicator(cons, Z, 0.1, log=True)
+    b = prod.compute_smoothed_feasibility_indicator(cons, Z, torch.full((2,), 0.1), log=True)
+    assert torch.equal(a, b) and a.dtype == torch.float64
+
+
+@pytest.mark.skipif(not refstub.available(), reason="/root/reference is not present on this machine")
+def test_feasibility_weights_match_the_live_reference():
+    refstub.load()
+    from botorch.utils.objective import compute_feasibility_indicator, compute_smoothed_feasibility_indicator
+
+    from botorch_b200 import constrained as prod
+
+    g = torch.Generator().manual_seed(1)
+    Z = torch.randn(7, 2, 3, 3, generator=g, dtype=torch.float64)
+    cons = [lambda s: s[..., 1] - 0.2, lambda s: s[..., 2] * s[..., 0] - 0.1]
+    for eta in (1e-3, torch.tensor([1e-2, 0.5], dtype=torch.float64)):
+        for fat in (True, False):
+            want = compute_smoothed_feasibility_indicator(cons, Z, eta, log=True, fat=fat)
+            got = prod.compute_smoothed_feasibility_indicator(cons, Z, eta, log=True, fat=fat)
+            assert rel_err(got, want, scale=1.0) < 1e-13
+    assert torch.equal(prod.compute_feasibility_indicator(cons, Z), compute_feasibility_indicator(cons, Z))
+
+
+def test_constrained_oracle_reduces_to_the_plain_oracle_without_constraints():
+    """One outcome, no constraints: oracle/constrained.py must reproduce oracle/qlognei.py (pinned against the reference's
+    golden vectors above) -- same Sobol dimensions, same incumbent, same reductions."""
+    from oracle.constrained import OracleConstrainedQLogNEI
+
+    p = make_problem("C1")
+    gp = oracle_gp(p)
+    plain = OracleQLogNEI(gp, p.train_X, num_samples=32, seed=5)
+    split = OracleConstrainedQLogNEI([gp], p.train_X, [], 1e-3, obj_idx=0, obj_weight=1.0, num_samples=32, seed=5)
+    X = candidates(p, 4, 2, seed=1)
+    assert rel_err(split.forward(X), plain.forward(X), scale=1.0) < 1e-12
+    v1, g1 = split.value_and_grad(X)
+    v2, g2 = plain.value_and_grad(X)
+    assert rel_err(g1, g2, scale=float(g2.abs().max())) < 1e-11
