@@ -17,6 +17,7 @@ from .acquisition import (  # noqa: F401
 )
 from .constrained import ModelListGP  # noqa: F401
 from .fit import ExactMarginalLogLikelihood, fit_gpytorch_mll, fit_gpytorch_mll_scipy  # noqa: F401
+from .fully_bayesian import SaasPotential, fit_fully_bayesian_model_nuts, nuts_sample  # noqa: F401
 from .generation import MatheronPath, MaxPosteriorSampling, PathwiseThompsonSampling, draw_matheron_paths  # noqa: F401
 from .models import SaasFullyBayesianSingleTaskGP, SingleTaskGP, Standardize  # noqa: F401
 from .optim import (  # noqa: F401

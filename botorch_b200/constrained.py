@@ -89,6 +89,35 @@ class ModelListGP(Model):
                 raise UnsupportedError("ModelListGP on the fused path takes single-output botorch_b200 exact GPs")
         self.models = torch.nn.ModuleList(gp_models)
 
+    @classmethod
+    def from_batched(cls, train_X: Tensor, train_Y: Tensor, train_Yvar: Optional[Tensor] = None, likelihood=None,
+                     covar_module=None, mean_module=None, outcome_transform="DEFAULT", input_transform=None, *,
+                     lengthscale=None, noise=None, mean_constant=0.0, outputscale=None, kernel: str = "rbf") -> "ModelListGP":  # fmt: skip
+        """What ``SingleTaskGP(train_X, train_Y)`` means for ``train_Y`` of shape n x m, m > 1: the reference turns the
+        outputs into a batch of m independent GPs over the same inputs with per-output hyperparameters and per-output
+        standardisation (models/gpytorch.py:405-466, models/gp_regression.py:164-254, Standardize(m=m)) -- exactly m
+        single-output models.  Per-output hyperparameters: ``lengthscale`` m x d (or d, shared), ``noise`` /
+        ``mean_constant`` / ``outputscale`` of length m (or scalars)."""
+        from .models import SingleTaskGP
+
+        m = train_Y.shape[-1]
+        if not (outcome_transform is None or isinstance(outcome_transform, str)):
+            raise UnsupportedError("pass outcome_transform='DEFAULT' (per-output Standardize) or None for multi-output data")
+
+        def col(v, k, per_output_dim):
+            if v is None or isinstance(v, (int, float)):
+                return v
+            t = torch.as_tensor(v)
+            return t[k] if t.dim() > per_output_dim else t
+
+        return cls(*[
+            SingleTaskGP(train_X, train_Y[:, k : k + 1], None if train_Yvar is None else train_Yvar[:, k : k + 1], likelihood,
+                         covar_module, mean_module, outcome_transform, input_transform, lengthscale=col(lengthscale, k, 1),
+                         noise=col(noise, k, 0), mean_constant=col(mean_constant, k, 0), outputscale=col(outputscale, k, 0),
+                         kernel=kernel)
+            for k in range(m)
+        ])  # fmt: skip
+
     @property
     def num_outputs(self) -> int:
         return len(self.models)

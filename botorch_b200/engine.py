@@ -207,9 +207,11 @@ class MLLState:
         self.grad = torch.zeros(M, d + 3, dtype=torch.float64, device=dev)
         self.evaluations = 0
 
-    def evaluate(self, lengthscale: Tensor, noise: Optional[Tensor], mean: Tensor, outputscale: Optional[Tensor] = None):
+    def evaluate(self, lengthscale: Tensor, noise: Optional[Tensor], mean: Tensor, outputscale: Optional[Tensor] = None,
+                 retry: bool = True):
         """-> (value [M], grad [M x (d+3)]: lengthscale (d), outputscale, noise, mean).  Raises NotPSDError after the
-        psd_safe_cholesky jitter schedule is exhausted."""
+        psd_safe_cholesky jitter schedule is exhausted; with ``retry=False`` there is one plain attempt and the per-member
+        outcome is left in ``self.info`` (0 ok, >0 first bad pivot, <0 NaN/Inf) for the caller to act on."""
         gp = self.gp
         gp.inv_ls.copy_(1.0 / _f64(lengthscale, gp.device).reshape(gp.M, gp.d))
         if noise is not None:
@@ -227,6 +229,9 @@ class MLLState:
             return gp.info.clone()
 
         self.evaluations += 1
+        if not retry:
+            self.info = run(None)
+            return self.value, self.grad
         gp.jitter = _retry_with_jitter(run, gp.M, gp.device, "K + noise*I")
         return self.value, self.grad
 

@@ -1,0 +1,385 @@
+"""Fully Bayesian (SAAS) fit on the device potential.
+
+What ``fit_fully_bayesian_model_nuts`` (botorch/fit.py:335-396) does is run pyro's NUTS on the potential energy of
+``SaasPyroModel.sample`` (models/fully_bayesian.py:167-246) and load the thinned draws into the model.  The expensive part of
+every leapfrog step is that potential: the log density of the training targets under ``outputscale * matern52 + noise I`` and
+its gradient w.r.t. every hyperparameter.  Here that is ``bo_mll_value_grad`` (one blocked Cholesky + the ``W .* g`` GEMMs,
+include/botorch_b200.h), evaluated for C chains as ONE batched call, and the sampler around it is a host-side NUTS that keeps
+all state on the device (no host synchronisation except the tree-building decisions).
+
+  * ``SaasPotential``                      -- pyro's ``potential_fn`` for the SAAS model, batched over chains
+  * ``nuts_sample``                        -- multinomial NUTS with dual-averaging step size and diagonal mass adaptation
+  * ``fit_fully_bayesian_model_nuts``      -- the reference's entry point and argument list
+
+pyro is not in this image, so the SAMPLER cannot be pinned against the reference's draws (different RNG consumption even
+with the same algorithm); the POTENTIAL is pinned at 1e-9 against oracle/saas.py (torch.distributions + autograd).
+
+Flat layout of the unconstrained vector (length d + 4):  [ kernel_tausq, _kernel_inv_length_sq (d), mean, noise, outputscale ]
+with the exp transform on every positive site (``biject_to(support)``) and its log-Jacobian in the energy.
+"""
+from __future__ import annotations
+
+import math
+from typing import Callable, Dict, Optional, Tuple
+
+import torch
+from torch import Tensor
+
+from . import engine
+from .models import MIN_INFERRED_NOISE_LEVEL, SaasFullyBayesianSingleTaskGP
+
+_LOG_2_OVER_PI = math.log(2.0 / math.pi)
+
+
+def _gamma_lp(x: Tensor, log_x: Tensor, a: float, b: float) -> Tensor:
+    return a * math.log(b) + (a - 1.0) * log_x - b * x - math.lgamma(a)
+
+
+def _half_cauchy_lp(x: Tensor, scale: float) -> Tensor:
+    return _LOG_2_OVER_PI - math.log(scale) - torch.log1p((x / scale) ** 2)
+
+
+class _LogLikelihood(torch.autograd.Function):
+    """log N(y | mean, outputscale * matern52(X / lengthscale) + noise I) for C hyperparameter sets: one bo_mll_value_grad."""
+
+    @staticmethod
+    def forward(ctx, lengthscale: Tensor, outputscale: Tensor, noise: Tensor, mean: Tensor, state: engine.MLLState):
+        # one plain factorisation, no jitter: a covariance that cannot be factored is a divergent transition, not a warning
+        value, grad = state.evaluate(lengthscale.detach(), noise.detach(), mean.detach(), outputscale.detach(), retry=False)
+        ctx.save_for_backward(grad.clone())
+        ctx.d = lengthscale.shape[-1]
+        return value.clone()
+
+    @staticmethod
+    def backward(ctx, g: Tensor):
+        (grad,) = ctx.saved_tensors  # [C x (d+3)]: lengthscale (d), outputscale, noise, mean
+        d = ctx.d
+        return g[:, None] * grad[:, :d], g * grad[:, d], g * grad[:, d + 1], g * grad[:, d + 2], None
+
+
+class SaasPotential:
+    """Potential energy (negative log joint in unconstrained space) of the SAAS model for ``num_chains`` parameter vectors."""
+
+    def __init__(self, train_X: Tensor, train_Y: Tensor, num_chains: int = 1, graph: bool = True) -> None:
+        if not train_X.is_cuda:
+            raise RuntimeError("SaasPotential lives on the GPU (no CPU path); move train_X / train_Y to a cuda device")
+        self.X = train_X.detach().to(torch.float64).contiguous()
+        self.y = train_Y.detach().to(torch.float64).reshape(-1).contiguous()
+        self.d = self.X.shape[-1]
+        self.dim = self.d + 4
+        self.num_chains = int(num_chains)
+        self._state = engine.MLLState(self.X, self.y, "matern52", with_outputscale=True, M=self.num_chains)
+        self.evaluations = 0
+        # The whole evaluation (transforms, bo_mll_value_grad, prior terms, chain rule) is a fixed launch sequence without
+        # host synchronisation: after two eager calls it is captured once and replayed as one CUDA graph per leapfrog step.
+        self._use_graph, self._graph, self._eager_calls = bool(graph), None, 0
+
+    def constrain(self, u: Tensor) -> Dict[str, Tensor]:
+        """Unconstrained [C x (d+4)] -> the dict ``postprocess_mcmc_samples`` produces (fully_bayesian.py:248-265)."""
+        d = self.d
+        tausq, ils = u[:, 0].exp(), u[:, 1 : 1 + d].exp()
+        return {"mean": u[:, 1 + d], "noise": MIN_INFERRED_NOISE_LEVEL + u[:, 2 + d].exp(), "outputscale": u[:, 3 + d].exp(),
+                "lengthscale": (tausq.unsqueeze(-1) * ils).rsqrt()}  # fmt: skip
+
+    def __call__(self, u: Tensor) -> Tuple[Tensor, Tensor]:
+        """u: [C x (d+4)] -> (energy [C], d energy / d u [C x (d+4)]).  A chain whose covariance cannot be factored or whose
+        energy is not finite gets energy +inf and a zero gradient -- a divergent transition for the sampler, which is how
+        pyro treats the LinAlgError / PositiveDefinite exceptions the reference registers (fully_bayesian.py:67-78).  The
+        other chains of the batch are unaffected."""
+        if u.shape != (self.num_chains, self.dim):
+            raise ValueError(f"expected u of shape {(self.num_chains, self.dim)}, got {tuple(u.shape)}")
+        self.evaluations += 1
+        u = u.detach().to(torch.float64)
+        if not self._use_graph:
+            return self._evaluate(u)
+        if self._graph is None:
+            if self._eager_calls < 2:  # warm-up: one-time kernel attributes and allocator pools settle outside the capture
+                self._eager_calls += 1
+                return self._evaluate(u)
+            self._u = u.clone()
+            torch.cuda.synchronize(u.device)
+            self._graph = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(self._graph):
+                self._out = self._evaluate(self._u)
+        self._u.copy_(u)
+        self._graph.replay()
+        return self._out[0].clone(), self._out[1].clone()
+
+    def _evaluate(self, u: Tensor) -> Tuple[Tensor, Tensor]:
+        d = self.d
+        wild = ~(torch.isfinite(u).all(-1) & (u.abs().amax(-1) < 80.0))  # exp() of the row would leave the float64 range
+        with torch.enable_grad():
+            v = torch.where(wild.unsqueeze(-1), torch.zeros_like(u), u).requires_grad_(True)
+            log_tausq, log_ils, mean, log_nr, log_os = v[:, 0], v[:, 1 : 1 + d], v[:, 1 + d], v[:, 2 + d], v[:, 3 + d]
+            tausq, ils, nr, os_ = log_tausq.exp(), log_ils.exp(), log_nr.exp(), log_os.exp()
+            lengthscale = torch.exp(-0.5 * (log_tausq.unsqueeze(-1) + log_ils))
+            ll = _LogLikelihood.apply(lengthscale, os_, MIN_INFERRED_NOISE_LEVEL + nr, mean, self._state)
+            logp = (ll + _gamma_lp(os_, log_os, 2.0, 0.15) + (-0.5 * mean * mean - 0.5 * math.log(2.0 * math.pi))
+                    + _gamma_lp(nr, log_nr, 0.9, 10.0) + _half_cauchy_lp(tausq, 0.1) + _half_cauchy_lp(ils, 1.0).sum(-1)
+                    + log_os + log_nr + log_tausq + log_ils.sum(-1))  # last line: log|dx/du| of the exp transforms
+            energy = -logp
+            (grad,) = torch.autograd.grad(energy.sum(), v)
+        bad = wild | (self._state.info != 0) | ~(torch.isfinite(energy) & torch.isfinite(grad).all(-1))
+        energy = torch.where(bad, torch.full_like(energy, float("inf")), energy.detach())
+        grad = torch.where(bad.unsqueeze(-1), torch.zeros_like(grad), grad)
+        return energy, grad
+
+
+# ---- NUTS over a batch of chains ---------------------------------------------------------------------------------------------
+# Multinomial NUTS (Hoffman & Gelman 2014 with Betancourt's multinomial sampling and the generalised U-turn criterion, the
+# variant pyro and Stan run), written for C chains in LOCKSTEP: every chain doubles its tree at the same time, a chain whose
+# tree has terminated rides along masked out, so each leapfrog step of all chains is one batched potential call.
+PotentialFn = Callable[[Tensor], Tuple[Tensor, Tensor]]
+_MAX_DELTA_ENERGY = 1000.0  # divergence threshold (pyro's NUTS._max_sliced_energy)
+
+
+class _Tree:
+    """Per-chain subtree summary.  `in` is the end the subtree was grown from, `out` the far end; momenta keep their
+    absolute orientation (backward growth integrates with a negative step), so the U-turn test is symmetric in the two ends."""
+
+    __slots__ = ("z_in", "r_in", "g_in", "z_out", "r_out", "g_out", "z_prop", "u_prop", "g_prop", "log_w", "rho", "stop",
+                 "diverged", "sum_accept", "leaves")  # fmt: skip
+
+    def select(self, keep_self: Tensor, other: "_Tree") -> "_Tree":
+        out = _Tree()
+        for name in self.__slots__:
+            a, b = getattr(self, name), getattr(other, name)
+            m = keep_self if a.dim() == 1 else keep_self.unsqueeze(-1)
+            setattr(out, name, torch.where(m, a, b))
+        return out
+
+
+def _kinetic(r: Tensor, minv: Tensor) -> Tensor:
+    return 0.5 * (r * r * minv).sum(-1)
+
+
+def _leaf(potential: PotentialFn, z, r, g, step, minv, h0) -> _Tree:
+    s = step.unsqueeze(-1)
+    r_half = r - 0.5 * s * g
+    z_new = z + s * minv * r_half
+    u_new, g_new = potential(z_new)
+    r_new = r_half - 0.5 * s * g_new
+    delta = u_new + _kinetic(r_new, minv) - h0
+    delta = torch.where(torch.isfinite(delta), delta, torch.full_like(delta, float("inf")))
+    t = _Tree()
+    t.z_in = t.z_out = t.z_prop = z_new
+    t.r_in = t.r_out = r_new
+    t.g_in = t.g_out = t.g_prop = g_new
+    t.u_prop = u_new
+    t.log_w = -delta
+    t.rho = r_new
+    t.diverged = delta > _MAX_DELTA_ENERGY
+    t.stop = t.diverged.clone()
+    t.sum_accept = torch.exp(torch.clamp(-delta, max=0.0))
+    t.leaves = torch.ones_like(delta)
+    return t
+
+
+def _turning(rho: Tensor, r_a: Tensor, r_b: Tensor, minv: Tensor) -> Tensor:
+    return ((rho * minv * r_a).sum(-1) <= 0) | ((rho * minv * r_b).sum(-1) <= 0)
+
+
+def _build(potential: PotentialFn, depth: int, z, r, g, step, minv, h0, gen) -> _Tree:
+    if depth == 0:
+        return _leaf(potential, z, r, g, step, minv, h0)
+    first = _build(potential, depth - 1, z, r, g, step, minv, h0, gen)
+    second = _build(potential, depth - 1, first.z_out, first.r_out, first.g_out, step, minv, h0, gen)
+    both = _Tree()
+    both.z_in, both.r_in, both.g_in = first.z_in, first.r_in, first.g_in
+    both.z_out, both.r_out, both.g_out = second.z_out, second.r_out, second.g_out
+    both.log_w = torch.logaddexp(first.log_w, second.log_w)
+    take2 = torch.rand(first.log_w.shape, generator=gen, device=z.device, dtype=z.dtype) < torch.exp(second.log_w - both.log_w)
+    both.z_prop = torch.where(take2.unsqueeze(-1), second.z_prop, first.z_prop)
+    both.g_prop = torch.where(take2.unsqueeze(-1), second.g_prop, first.g_prop)
+    both.u_prop = torch.where(take2, second.u_prop, first.u_prop)
+    both.rho = first.rho + second.rho
+    both.diverged = second.diverged
+    both.stop = second.stop | _turning(both.rho, both.r_in, both.r_out, minv)
+    both.sum_accept = first.sum_accept + second.sum_accept
+    both.leaves = first.leaves + second.leaves
+    return first.select(first.stop, both)  # a subtree that already stopped ignores everything grown after it
+
+
+class _DualAveraging:
+    """Nesterov dual averaging of log step size per chain (Hoffman & Gelman 2014, section 3.2; pyro's constants)."""
+
+    def __init__(self, eps0: Tensor, target: float = 0.8, gamma: float = 0.05, t0: float = 10.0, kappa: float = 0.75):
+        self.target, self.gamma, self.t0, self.kappa = target, gamma, t0, kappa
+        self.restart(eps0)
+
+    def restart(self, eps0: Tensor) -> None:
+        self.mu = torch.log(10.0 * eps0)
+        self.h_bar = torch.zeros_like(eps0)
+        self.log_eps_bar = torch.zeros_like(eps0)
+        self.t = 0
+
+    def update(self, accept: Tensor) -> Tensor:
+        self.t += 1
+        w = 1.0 / (self.t + self.t0)
+        self.h_bar = (1.0 - w) * self.h_bar + w * (self.target - accept)
+        log_eps = self.mu - math.sqrt(self.t) / self.gamma * self.h_bar
+        eta = self.t ** (-self.kappa)
+        self.log_eps_bar = eta * log_eps + (1.0 - eta) * self.log_eps_bar
+        return torch.exp(log_eps)
+
+    def final(self) -> Tensor:
+        return torch.exp(self.log_eps_bar)
+
+
+def _reasonable_step(potential: PotentialFn, z, u, g, minv, gen, eps0: float = 0.1, tries: int = 24) -> Tensor:
+    """Per chain: double / halve the step until the one-step acceptance probability crosses 1/2 (H&G Algorithm 4)."""
+    C = z.shape[0]
+    eps = torch.full((C,), eps0, dtype=z.dtype, device=z.device)
+    r = torch.randn(z.shape, generator=gen, device=z.device, dtype=z.dtype) / minv.sqrt()
+    h0 = u + _kinetic(r, minv)
+    direction = None
+    done = torch.zeros(C, dtype=torch.bool, device=z.device)
+    for _ in range(tries):
+        leaf = _leaf(potential, z, r, g, eps, minv, h0)
+        up = leaf.log_w > math.log(0.5)  # acceptance above 1/2: the step can grow
+        if direction is None:
+            direction = up
+        done = done | (up != direction)
+        if bool(done.all()):
+            break
+        eps = torch.where(done, eps, torch.where(direction, eps * 2.0, eps * 0.5))
+    return eps
+
+
+class _Welford:
+    def __init__(self, like: Tensor) -> None:
+        self.n, self.mean, self.m2 = 0, torch.zeros_like(like), torch.zeros_like(like)
+
+    def add(self, x: Tensor) -> None:
+        self.n += 1
+        delta = x - self.mean
+        self.mean = self.mean + delta / self.n
+        self.m2 = self.m2 + delta * (x - self.mean)
+
+    def variance(self) -> Tensor:  # Stan's regularisation towards the unit metric
+        var = self.m2 / max(self.n - 1, 1)
+        return (self.n / (self.n + 5.0)) * var + 1e-3 * (5.0 / (self.n + 5.0))
+
+
+def _adaptation_windows(warmup: int) -> Tuple[int, list]:
+    """(start of the metric phase, ends of its doubling windows); the last 10% adapt the step size only (Stan's schedule)."""
+    if warmup < 40:
+        return warmup, []
+    start, end = int(0.15 * warmup), int(0.9 * warmup)
+    ends, size, pos = [], 25, start
+    while pos + 2 * size + size <= end:
+        pos += size
+        ends.append(pos)
+        size *= 2
+    ends.append(end)
+    return start, ends
+
+
+def nuts_sample(potential: PotentialFn, init: Tensor, num_samples: int, warmup_steps: int, max_tree_depth: int = 6,
+                target_accept: float = 0.8, seed: Optional[int] = None, adapt_mass: bool = True):  # fmt: skip
+    """Run C chains of NUTS in lockstep.  init: [C x D] -> (samples [num_samples x C x D], stats).  ``potential`` maps
+    [C x D] to (energy [C], gradient [C x D]); +inf energy marks a divergent point."""
+    z = init.detach().clone()
+    dev, dt = z.device, z.dtype
+    C = z.shape[0]
+    gen = torch.Generator(device=dev)
+    gen.manual_seed(torch.seed() % (2**31) if seed is None else int(seed))
+    u, g = potential(z)
+    if not bool(torch.isfinite(u).all()):
+        raise RuntimeError("NUTS needs a finite potential energy at every initial point")
+    minv = torch.ones_like(z)
+    eps = _reasonable_step(potential, z, u, g, minv, gen)
+    averaging = _DualAveraging(eps, target=target_accept)
+    metric_start, window_ends = _adaptation_windows(warmup_steps) if adapt_mass else (warmup_steps, [])
+    welford = _Welford(z)
+    samples = torch.empty(num_samples, C, z.shape[1], dtype=dt, device=dev)
+    stats = {"accept_prob": [], "tree_depth": [], "divergent": torch.zeros(C, dtype=torch.long, device=dev), "leapfrogs": 0}
+    for it in range(warmup_steps + num_samples):
+        r0 = torch.randn(z.shape, generator=gen, device=dev, dtype=dt) / minv.sqrt()
+        h0 = u + _kinetic(r0, minv)
+        z_minus = z_plus = z
+        r_minus = r_plus = r0
+        g_minus = g_plus = g
+        rho, log_w = r0.clone(), torch.zeros_like(u)
+        active = torch.ones(C, dtype=torch.bool, device=dev)
+        sum_accept, leaves = torch.zeros_like(u), torch.zeros_like(u)
+        depth_reached = torch.zeros(C, dtype=torch.long, device=dev)
+        for depth in range(max_tree_depth):
+            fwd = torch.rand(C, generator=gen, device=dev, dtype=dt) < 0.5
+            f2 = fwd.unsqueeze(-1)
+            tree = _build(potential, depth, torch.where(f2, z_plus, z_minus), torch.where(f2, r_plus, r_minus),
+                          torch.where(f2, g_plus, g_minus), torch.where(fwd, eps, -eps), minv, h0, gen)  # fmt: skip
+            stats["leapfrogs"] += 2**depth
+            sum_accept = sum_accept + torch.where(active, tree.sum_accept, torch.zeros_like(u))
+            leaves = leaves + torch.where(active, tree.leaves, torch.zeros_like(u))
+            depth_reached = depth_reached + active.long()
+            if it >= warmup_steps:
+                stats["divergent"] += (active & tree.diverged).long()
+            valid = active & ~tree.stop
+            # biased progressive sampling between the old tree and the new subtree (Betancourt 2017, A.3.2)
+            take = valid & (torch.rand(C, generator=gen, device=dev, dtype=dt) < torch.exp(tree.log_w - log_w))
+            t2 = take.unsqueeze(-1)
+            z, g, u = torch.where(t2, tree.z_prop, z), torch.where(t2, tree.g_prop, g), torch.where(take, tree.u_prop, u)
+            grow_f, grow_b = (valid & fwd).unsqueeze(-1), (valid & ~fwd).unsqueeze(-1)
+            z_plus, r_plus, g_plus = (torch.where(grow_f, tree.z_out, z_plus), torch.where(grow_f, tree.r_out, r_plus),
+                                      torch.where(grow_f, tree.g_out, g_plus))  # fmt: skip
+            z_minus, r_minus, g_minus = (torch.where(grow_b, tree.z_out, z_minus), torch.where(grow_b, tree.r_out, r_minus),
+                                         torch.where(grow_b, tree.g_out, g_minus))  # fmt: skip
+            log_w = torch.where(valid, torch.logaddexp(log_w, tree.log_w), log_w)
+            rho = torch.where(valid.unsqueeze(-1), rho + tree.rho, rho)
+            active = valid & ~_turning(rho, r_minus, r_plus, minv)
+            if not bool(active.any()):
+                break
+        accept = sum_accept / leaves.clamp_min(1.0)
+        if it < warmup_steps:
+            eps = averaging.update(accept)
+            if window_ends and it >= metric_start:
+                welford.add(z)
+                if it + 1 == window_ends[0]:
+                    window_ends.pop(0)
+                    minv = welford.variance()
+                    welford = _Welford(z)
+                    eps = _reasonable_step(potential, z, u, g, minv, gen, eps0=1.0)
+                    averaging.restart(eps)
+            if it + 1 == warmup_steps:
+                eps = averaging.final()
+        else:
+            samples[it - warmup_steps] = z
+            stats["accept_prob"].append(accept)
+            stats["tree_depth"].append(depth_reached)
+    stats["step_size"], stats["inverse_mass"] = eps, minv
+    if stats["accept_prob"]:
+        stats["accept_prob"] = torch.stack(stats["accept_prob"]).mean(0)
+        stats["tree_depth"] = torch.stack(stats["tree_depth"]).double().mean(0)
+    return samples, stats
+
+
+def fit_fully_bayesian_model_nuts(model: SaasFullyBayesianSingleTaskGP, max_tree_depth: int = 6, warmup_steps: int = 512,
+                                  num_samples: int = 256, thinning: int = 16, disable_progbar: bool = False,
+                                  jit_compile: bool = False, num_chains: int = 1, seed: Optional[int] = None) -> None:  # fmt: skip
+    """botorch/fit.py:335-396: NUTS on the SAAS potential, every ``thinning``-th draw loaded into ``model``.
+
+    ``num_chains`` (not in the reference, which runs one chain) runs that many chains as ONE batched potential; each
+    contributes ``num_samples // num_chains`` draws, so the retained count stays ``num_samples / thinning``.  Initial points
+    are uniform in (-2, 2) in the unconstrained space (pyro's ``init_to_uniform`` default).  ``disable_progbar`` and
+    ``jit_compile`` are accepted for signature compatibility and have no effect."""
+    if not isinstance(model, SaasFullyBayesianSingleTaskGP):
+        raise TypeError("fit_fully_bayesian_model_nuts fits a SaasFullyBayesianSingleTaskGP")
+    model.train()
+    X = model.train_inputs[0]
+    potential = SaasPotential(X, model.train_targets, num_chains=num_chains)
+    gen = torch.Generator(device=X.device)
+    gen.manual_seed(torch.seed() % (2**31) if seed is None else int(seed))
+    init = None
+    for _ in range(20):  # redraw the starting points whose energy is not finite
+        trial = 4.0 * torch.rand(num_chains, potential.dim, generator=gen, device=X.device, dtype=torch.float64) - 2.0
+        init = trial if init is None else torch.where(torch.isfinite(potential(init)[0]).unsqueeze(-1), init, trial)
+        if bool(torch.isfinite(potential(init)[0]).all()):
+            break
+    per_chain = max(num_samples // num_chains, 1)
+    samples, stats = nuts_sample(potential, init, per_chain, warmup_steps, max_tree_depth=max_tree_depth,
+                                 seed=None if seed is None else seed + 1)  # fmt: skip
+    kept = samples.transpose(0, 1).reshape(-1, potential.dim)[::thinning]  # chain-major, then thinned like the reference
+    model.load_mcmc_samples(potential.constrain(kept))
+    model.eval()
+    model.nuts_stats = {**stats, "potential_evaluations": potential.evaluations}

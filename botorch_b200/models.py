@@ -219,6 +219,13 @@ class SingleTaskGP(_FusedExactGP):
     raw values are the values).
     """
 
+    def __new__(cls, train_X=None, train_Y=None, *args, **kwargs):
+        if cls is SingleTaskGP and isinstance(train_Y, Tensor) and train_Y.dim() == 2 and train_Y.shape[-1] > 1:
+            from .constrained import ModelListGP  # n x m targets: m independent outputs (models/gpytorch.py:405-466)
+
+            return ModelListGP.from_batched(train_X, train_Y, *args, **kwargs)
+        return super().__new__(cls)
+
     def __init__(
         self,
         train_X: Tensor,

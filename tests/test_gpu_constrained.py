@@ -119,3 +119,35 @@ def test_constrained_acquisition_under_optimize_acqf(cuda):
     assert cand.shape == (2, 2) and bool(torch.isfinite(val))
     with pytest.raises(bb.exceptions.UnsupportedError):
         bb.qLogNoisyExpectedImprovement(acqf.model, X.to(cuda), constraints=cons)  # no single-outcome objective given
+
+
+def test_multi_output_single_task_gp_is_the_list_of_its_outputs(cuda):
+    """SingleTaskGP(train_X, train_Y[n x m]) == m independent single-output models (models/gpytorch.py:405-466): same
+    posterior, and the constrained acquisition built on it equals the one built on the explicit list."""
+    import botorch_b200 as bb
+
+    X, ys, hy = _data(40, 3, seed=12)
+    Y = torch.stack(ys[:2], dim=-1)
+    ls = torch.stack([hy[0]["ls"], hy[1]["ls"]])
+    noise = torch.tensor([hy[0]["noise"], hy[1]["noise"]], dtype=torch.float64)
+    mean = torch.tensor([hy[0]["mean"], hy[1]["mean"]], dtype=torch.float64)
+    multi = bb.SingleTaskGP(X.to(cuda), Y.to(cuda), lengthscale=ls, noise=noise, mean_constant=mean)
+    assert isinstance(multi, bb.ModelListGP) and multi.num_outputs == 2
+    singles = [bb.SingleTaskGP(X.to(cuda), Y[:, k : k + 1].to(cuda), lengthscale=ls[k], noise=float(noise[k]),
+                               mean_constant=float(mean[k])) for k in range(2)]  # fmt: skip
+    Xt = torch.rand(4, 2, 3, dtype=torch.float64, generator=torch.Generator().manual_seed(1)).to(cuda)
+    pm = multi.posterior(Xt)
+    assert pm.mean.shape == (4, 2, 2) and pm.variance.shape == (4, 2, 2)
+    for k in range(2):
+        pk = singles[k].posterior(Xt)
+        assert torch.equal(pm.mean[..., k : k + 1], pk.mean) and torch.equal(pm.variance[..., k : k + 1], pk.variance)
+    cons = [lambda Z: Z[..., 1] - 0.6]
+    kw = dict(objective=bb.LinearMCObjective(torch.tensor([1.0, 0.0], dtype=torch.float64, device=cuda)), constraints=cons, eta=1e-2)
+    a = bb.qLogNoisyExpectedImprovement(multi, X.to(cuda), sampler=bb.SobolQMCNormalSampler(torch.Size([32]), seed=2), **kw)
+    b = bb.qLogNoisyExpectedImprovement(bb.ModelListGP(*singles), X.to(cuda),
+                                        sampler=bb.SobolQMCNormalSampler(torch.Size([32]), seed=2), **kw)  # fmt: skip
+    assert torch.equal(a(Xt), b(Xt))
+    oracle_models = [OracleGP(X, Y[:, k : k + 1], GPHyper("rbf", ls[k], noise[k], mean[k], None), standardize=True)
+                     for k in range(2)]  # fmt: skip
+    oracle = OracleConstrainedQLogNEI(oracle_models, X, cons, 1e-2, obj_idx=0, obj_weight=1.0, num_samples=32, seed=2)
+    _check(cuda, a, oracle, Xt.cpu())

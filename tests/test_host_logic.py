@@ -347,3 +347,60 @@ def test_fit_gpytorch_mll_retry_policy_on_the_host():
     with pytest.raises(ModelFittingError), pytest.warns(OptimizationWarning):
         fit_gpytorch_mll(mll, optimizer=failing, closure=lambda: None, max_attempts=2)
     assert mll.training and torch.equal(model.covar_module.raw_lengthscale.detach(), now)  # rolled back
+
+
+# ---- NUTS host logic (botorch_b200/fully_bayesian.py): the sampler is device-agnostic, the potential is not ----------------
+def test_nuts_recovers_a_gaussian_target():
+    from botorch_b200.fully_bayesian import nuts_sample
+
+    mu = torch.tensor([0.0, 1.0, -2.0], dtype=torch.float64)
+    sd = torch.tensor([0.2, 1.0, 4.0], dtype=torch.float64)
+    calls = []
+
+    def potential(z):
+        calls.append(z.shape)
+        return 0.5 * (((z - mu) / sd) ** 2).sum(-1), (z - mu) / sd**2
+
+    samples, stats = nuts_sample(potential, torch.zeros(6, 3, dtype=torch.float64), num_samples=250, warmup_steps=200, seed=3)
+    flat = samples.reshape(-1, 3)
+    assert samples.shape == (250, 6, 3) and all(s == (6, 3) for s in calls)
+    assert bool(((flat.mean(0) - mu).abs() < 0.15 * sd).all())
+    assert bool(((flat.std(0) / sd - 1.0).abs() < 0.12).all())
+    assert 0.6 < float(stats["accept_prob"].mean()) < 0.99 and int(stats["divergent"].sum()) == 0
+    # the adapted metric follows the target's scales (per chain, regularised variance of the warm-up windows)
+    assert bool(((stats["inverse_mass"].sqrt() / sd).log().abs() < 0.7).all())
+    again, _ = nuts_sample(potential, torch.zeros(6, 3, dtype=torch.float64), num_samples=5, warmup_steps=20, seed=3)
+    again2, _ = nuts_sample(potential, torch.zeros(6, 3, dtype=torch.float64), num_samples=5, warmup_steps=20, seed=3)
+    assert torch.equal(again, again2)
+
+
+def test_nuts_treats_infinite_energy_as_divergence_and_keeps_the_chain():
+    from botorch_b200.fully_bayesian import nuts_sample
+
+    def potential(z):  # standard normal restricted to z > -1: a wall of infinite energy
+        e = 0.5 * (z * z).sum(-1)
+        bad = (z < -1.0).any(-1)
+        return torch.where(bad, torch.full_like(e, float("inf")), e), torch.where(bad.unsqueeze(-1), torch.zeros_like(z), z)
+
+    samples, stats = nuts_sample(potential, torch.zeros(4, 2, dtype=torch.float64), num_samples=150, warmup_steps=100, seed=0)
+    assert bool((samples >= -1.0).all()) and bool(torch.isfinite(samples).all())
+    assert int(stats["divergent"].sum()) > 0
+    with pytest.raises(RuntimeError):
+        nuts_sample(potential, torch.full((4, 2), -3.0, dtype=torch.float64), num_samples=2, warmup_steps=2)
+
+
+def test_saas_prior_terms_and_adaptation_schedule():
+    from torch.distributions import Gamma, HalfCauchy
+
+    from botorch_b200 import fully_bayesian as fb
+
+    x = torch.tensor([1e-3, 0.2, 1.0, 7.5], dtype=torch.float64)
+    t = lambda v: torch.tensor(v, dtype=torch.float64)
+    assert torch.allclose(fb._gamma_lp(x, x.log(), 2.0, 0.15), Gamma(t(2.0), t(0.15)).log_prob(x), rtol=1e-13, atol=0)
+    assert torch.allclose(fb._gamma_lp(x, x.log(), 0.9, 10.0), Gamma(t(0.9), t(10.0)).log_prob(x), rtol=1e-13, atol=0)
+    assert torch.allclose(fb._half_cauchy_lp(x, 0.1), HalfCauchy(t(0.1)).log_prob(x), rtol=1e-13, atol=0)
+    start, ends = fb._adaptation_windows(512)
+    assert start == 76 and ends[-1] == 460 and ends == sorted(ends) and ends[0] - start == 25
+    assert fb._adaptation_windows(20) == (20, [])
+    with pytest.raises(RuntimeError):
+        fb.SaasPotential(torch.rand(5, 2, dtype=torch.float64), torch.rand(5, dtype=torch.float64))
