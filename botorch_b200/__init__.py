@@ -16,7 +16,7 @@ from .acquisition import (  # noqa: F401
     qNoisyExpectedImprovement,
 )
 from .constrained import ModelListGP  # noqa: F401
-from .fit import ExactMarginalLogLikelihood, fit_gpytorch_mll, fit_gpytorch_mll_scipy  # noqa: F401
+from .fit import ExactMarginalLogLikelihood, SumMarginalLogLikelihood, fit_gpytorch_mll, fit_gpytorch_mll_scipy  # noqa: F401
 from .fully_bayesian import SaasPotential, fit_fully_bayesian_model_nuts, nuts_sample  # noqa: F401
 from .generation import MatheronPath, MaxPosteriorSampling, PathwiseThompsonSampling, draw_matheron_paths  # noqa: F401
 from .models import SaasFullyBayesianSingleTaskGP, SingleTaskGP, Standardize  # noqa: F401

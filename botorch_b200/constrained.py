@@ -88,6 +88,7 @@ class ModelListGP(Model):
             if not isinstance(m, _FusedExactGP) or m._is_fully_bayesian:
                 raise UnsupportedError("ModelListGP on the fused path takes single-output botorch_b200 exact GPs")
         self.models = torch.nn.ModuleList(gp_models)
+        self.likelihood = torch.nn.ModuleList([m.likelihood for m in gp_models])  # LikelihoodList of the reference
 
     @classmethod
     def from_batched(cls, train_X: Tensor, train_Y: Tensor, train_Yvar: Optional[Tensor] = None, likelihood=None,

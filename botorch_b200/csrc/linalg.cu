@@ -294,6 +294,12 @@ __global__ void fill_kernel(double* p, long count, double v) {
     for (long i = blockIdx.x * (long)blockDim.x + threadIdx.x; i < count; i += (long)gridDim.x * blockDim.x) p[i] = v;
 }
 
+// `count` doubles at the start of each of gridDim.y batch members `stride` apart (augmented layouts: one launch, not one per member)
+__global__ void fill_strided_kernel(double* p, long stride, long count, double v) {
+    double* q = p + (long)blockIdx.y * stride;
+    for (long i = blockIdx.x * (long)blockDim.x + threadIdx.x; i < count; i += (long)gridDim.x * blockDim.x) q[i] = v;
+}
+
 }  // namespace
 
 long bo_linalg_scratch_doubles(int n, int batch) {
@@ -411,8 +417,17 @@ int bo_potrf_blocked(double* A, long lda, long strideA, int n, int batch, double
         if (strideX == (long)n * ldx) {
             BO_TRY(bo_fill(Xinv, (long)batch * n * ldx, 0.0, stream));
         } else {
-            for (int z = 0; z < batch; z++)  // zero n rows of ldx (strideX exceeds n*ldx: augmented layouts)
-                BO_TRY(bo_fill(Xinv + (long)z * strideX, (long)n * ldx, 0.0, stream));
+            // zero n rows of ldx per member (strideX exceeds n*ldx: augmented layouts); gridDim.y <= 65535
+            const long count = (long)n * ldx;
+            long blocks = (count + 255) / 256;
+            if (blocks > 148 * 4) blocks = 148 * 4;
+            for (int z0 = 0; z0 < batch; z0 += 65535) {
+                const int nz = (batch - z0 < 65535) ? batch - z0 : 65535;
+                fill_strided_kernel<<<dim3((unsigned)blocks, (unsigned)nz), 256, 0, stream>>>(Xinv + (long)z0 * strideX,
+                                                                                              strideX, count, 0.0);
+                g_bo_launch_count++;
+                BO_CUDA_TRY(cudaGetLastError());
+            }
         }
     }
     bool pending[2] = {false, false};

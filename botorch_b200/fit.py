@@ -166,6 +166,23 @@ _PART_OF = {
 }
 
 
+class SumMarginalLogLikelihood(Module):
+    """Sum of the exact MLLs of the independent outcomes of a ``ModelListGP`` (gpytorch ``SumMarginalLogLikelihood`` as the
+    reference uses it, fit.py:262-285): one ``ExactMarginalLogLikelihood`` per outcome in ``mlls``."""
+
+    def __init__(self, likelihood: Optional[Module], model) -> None:
+        super().__init__()
+        from .constrained import ModelListGP
+
+        if not isinstance(model, ModelListGP):
+            raise UnsupportedError("SumMarginalLogLikelihood takes a botorch_b200 ModelListGP")
+        self.model, self.likelihood = model, likelihood
+        self.mlls = torch.nn.ModuleList([ExactMarginalLogLikelihood(m.likelihood, m) for m in model.models])
+
+    def forward(self, *args: Any, **kwargs: Any) -> Tensor:
+        return sum(mll.forward() for mll in self.mlls)
+
+
 def get_parameters_and_bounds(mll: ExactMarginalLogLikelihood, requires_grad: Optional[bool] = None):
     """Named parameters and their box bounds (``GreaterThan`` constraints with ``transform=None``: raw == value)."""
     params: Dict[str, Tensor] = {}
@@ -359,8 +376,18 @@ def fit_gpytorch_mll(mll: ExactMarginalLogLikelihood, closure=None, optimizer: O
                      caught_exception_types: Tuple[type, ...] = (NotPSDError,), **ignore: Any) -> ExactMarginalLogLikelihood:  # fmt: skip
     """Maximise the exact MLL over the hyperparameters with L-BFGS-B; retry from prior samples on optimiser warnings.
 
-    Returns ``mll`` in eval mode on success; raises ``ModelFittingError`` when every attempt failed."""
+    Returns ``mll`` in eval mode on success; raises ``ModelFittingError`` when every attempt failed.  A
+    ``SumMarginalLogLikelihood`` over a ``ModelListGP`` is fitted one outcome at a time (``_fit_list``, fit.py:262-285)."""
     import copy
+
+    if isinstance(mll, SumMarginalLogLikelihood):
+        mll.train()
+        for sub_mll in mll.mlls:
+            fit_gpytorch_mll(sub_mll, closure=closure, optimizer=optimizer, closure_kwargs=closure_kwargs,
+                             optimizer_kwargs=optimizer_kwargs, max_attempts=max_attempts,
+                             pick_best_of_all_attempts=pick_best_of_all_attempts, warning_handler=warning_handler,
+                             caught_exception_types=caught_exception_types, **ignore)  # fmt: skip
+        return mll.eval() if not any(sub_mll.training for sub_mll in mll.mlls) else mll
 
     optimizer = fit_gpytorch_mll_scipy if optimizer is None else optimizer
     optimizer_kwargs = {} if optimizer_kwargs is None else optimizer_kwargs

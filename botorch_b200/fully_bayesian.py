@@ -39,24 +39,6 @@ def _half_cauchy_lp(x: Tensor, scale: float) -> Tensor:
     return _LOG_2_OVER_PI - math.log(scale) - torch.log1p((x / scale) ** 2)
 
 
-class _LogLikelihood(torch.autograd.Function):
-    """log N(y | mean, outputscale * matern52(X / lengthscale) + noise I) for C hyperparameter sets: one bo_mll_value_grad."""
-
-    @staticmethod
-    def forward(ctx, lengthscale: Tensor, outputscale: Tensor, noise: Tensor, mean: Tensor, state: engine.MLLState):
-        # one plain factorisation, no jitter: a covariance that cannot be factored is a divergent transition, not a warning
-        value, grad = state.evaluate(lengthscale.detach(), noise.detach(), mean.detach(), outputscale.detach(), retry=False)
-        ctx.save_for_backward(grad.clone())
-        ctx.d = lengthscale.shape[-1]
-        return value.clone()
-
-    @staticmethod
-    def backward(ctx, g: Tensor):
-        (grad,) = ctx.saved_tensors  # [C x (d+3)]: lengthscale (d), outputscale, noise, mean
-        d = ctx.d
-        return g[:, None] * grad[:, :d], g * grad[:, d], g * grad[:, d + 1], g * grad[:, d + 2], None
-
-
 class SaasPotential:
     """Potential energy (negative log joint in unconstrained space) of the SAAS model for ``num_chains`` parameter vectors."""
 
@@ -106,21 +88,34 @@ class SaasPotential:
         return self._out[0].clone(), self._out[1].clone()
 
     def _evaluate(self, u: Tensor) -> Tuple[Tensor, Tensor]:
+        """Closed-form chain rule around bo_mll_value_grad (few fused elementwise launches; the whole thing is graph-captured).
+        With x = exp(u) on the positive sites: d/du of a log density term is x * d/dx, the log-Jacobian contributes +1, and
+        lengthscale_i = exp(-(u_tausq + u_ils_i) / 2) gives d lengthscale_i / d u_tausq = d lengthscale_i / d u_ils_i = -l_i / 2."""
         d = self.d
         wild = ~(torch.isfinite(u).all(-1) & (u.abs().amax(-1) < 80.0))  # exp() of the row would leave the float64 range
-        with torch.enable_grad():
-            v = torch.where(wild.unsqueeze(-1), torch.zeros_like(u), u).requires_grad_(True)
-            log_tausq, log_ils, mean, log_nr, log_os = v[:, 0], v[:, 1 : 1 + d], v[:, 1 + d], v[:, 2 + d], v[:, 3 + d]
-            tausq, ils, nr, os_ = log_tausq.exp(), log_ils.exp(), log_nr.exp(), log_os.exp()
-            lengthscale = torch.exp(-0.5 * (log_tausq.unsqueeze(-1) + log_ils))
-            ll = _LogLikelihood.apply(lengthscale, os_, MIN_INFERRED_NOISE_LEVEL + nr, mean, self._state)
-            logp = (ll + _gamma_lp(os_, log_os, 2.0, 0.15) + (-0.5 * mean * mean - 0.5 * math.log(2.0 * math.pi))
-                    + _gamma_lp(nr, log_nr, 0.9, 10.0) + _half_cauchy_lp(tausq, 0.1) + _half_cauchy_lp(ils, 1.0).sum(-1)
-                    + log_os + log_nr + log_tausq + log_ils.sum(-1))  # last line: log|dx/du| of the exp transforms
-            energy = -logp
-            (grad,) = torch.autograd.grad(energy.sum(), v)
+        v = torch.where(wild.unsqueeze(-1), torch.zeros_like(u), u)
+        x = v.exp()
+        mean, nr, os_ = v[:, 1 + d], x[:, 2 + d], x[:, 3 + d]
+        lengthscale = torch.exp(-0.5 * (v[:, :1] + v[:, 1 : 1 + d]))
+        # one plain factorisation, no jitter: a covariance that cannot be factored is a divergent transition, not a warning
+        ll, gl = self._state.evaluate(lengthscale, MIN_INFERRED_NOISE_LEVEL + nr, mean, os_, retry=False)
+        # half-Cauchy sites (tausq: scale 0.1, inv_length_sq: scale 1), columns 0 .. d
+        r2 = x[:, : 1 + d] ** 2
+        r2[:, 0] *= 100.0
+        lp_hc = _LOG_2_OVER_PI - torch.log1p(r2)
+        logp = (ll + lp_hc.sum(-1) - math.log(0.1) + _gamma_lp(os_, v[:, 3 + d], 2.0, 0.15) + _gamma_lp(nr, v[:, 2 + d], 0.9, 10.0)
+                - 0.5 * mean * mean - 0.5 * math.log(2.0 * math.pi) + v[:, : 1 + d].sum(-1) + v[:, 2 + d] + v[:, 3 + d])
+        half_l_g = -0.5 * lengthscale * gl[:, :d]  # d ll / d u_ils_i
+        grad_logp = torch.empty_like(v)
+        grad_logp[:, : 1 + d] = 1.0 - 2.0 * r2 / (1.0 + r2)
+        grad_logp[:, 0] += half_l_g.sum(-1)
+        grad_logp[:, 1 : 1 + d] += half_l_g
+        grad_logp[:, 1 + d] = gl[:, d + 2] - mean
+        grad_logp[:, 2 + d] = gl[:, d + 1] * nr + (0.9 - 1.0) - 10.0 * nr + 1.0
+        grad_logp[:, 3 + d] = gl[:, d] * os_ + (2.0 - 1.0) - 0.15 * os_ + 1.0
+        energy, grad = -logp, -grad_logp
         bad = wild | (self._state.info != 0) | ~(torch.isfinite(energy) & torch.isfinite(grad).all(-1))
-        energy = torch.where(bad, torch.full_like(energy, float("inf")), energy.detach())
+        energy = torch.where(bad, torch.full_like(energy, float("inf")), energy)
         grad = torch.where(bad.unsqueeze(-1), torch.zeros_like(grad), grad)
         return energy, grad
 
@@ -134,10 +129,10 @@ _MAX_DELTA_ENERGY = 1000.0  # divergence threshold (pyro's NUTS._max_sliced_ener
 
 
 class _Tree:
-    """Per-chain subtree summary.  `in` is the end the subtree was grown from, `out` the far end; momenta keep their
-    absolute orientation (backward growth integrates with a negative step), so the U-turn test is symmetric in the two ends."""
+    """Per-chain subtree summary.  `in` is the end the subtree was grown from (only its momentum is needed: growth continues
+    from the far end `out`); momenta keep their absolute orientation (backward growth integrates with a negative step), so the U-turn test is symmetric in the two ends."""
 
-    __slots__ = ("z_in", "r_in", "g_in", "z_out", "r_out", "g_out", "z_prop", "u_prop", "g_prop", "log_w", "rho", "stop",
+    __slots__ = ("r_in", "z_out", "r_out", "g_out", "z_prop", "u_prop", "g_prop", "log_w", "rho", "stop",
                  "diverged", "sum_accept", "leaves")  # fmt: skip
 
     def select(self, keep_self: Tensor, other: "_Tree") -> "_Tree":
@@ -162,9 +157,9 @@ def _leaf(potential: PotentialFn, z, r, g, step, minv, h0) -> _Tree:
     delta = u_new + _kinetic(r_new, minv) - h0
     delta = torch.where(torch.isfinite(delta), delta, torch.full_like(delta, float("inf")))
     t = _Tree()
-    t.z_in = t.z_out = t.z_prop = z_new
+    t.z_out = t.z_prop = z_new
     t.r_in = t.r_out = r_new
-    t.g_in = t.g_out = t.g_prop = g_new
+    t.g_out = t.g_prop = g_new
     t.u_prop = u_new
     t.log_w = -delta
     t.rho = r_new
@@ -185,7 +180,7 @@ def _build(potential: PotentialFn, depth: int, z, r, g, step, minv, h0, gen) -> 
     first = _build(potential, depth - 1, z, r, g, step, minv, h0, gen)
     second = _build(potential, depth - 1, first.z_out, first.r_out, first.g_out, step, minv, h0, gen)
     both = _Tree()
-    both.z_in, both.r_in, both.g_in = first.z_in, first.r_in, first.g_in
+    both.r_in = first.r_in
     both.z_out, both.r_out, both.g_out = second.z_out, second.r_out, second.g_out
     both.log_w = torch.logaddexp(first.log_w, second.log_w)
     take2 = torch.rand(first.log_w.shape, generator=gen, device=z.device, dtype=z.dtype) < torch.exp(second.log_w - both.log_w)

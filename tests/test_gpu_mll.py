@@ -204,3 +204,27 @@ def test_mll_batched_hyperparameter_sets(cuda):
         assert abs(float(gr[m, d]) - float(og["outputscale"])) <= TOL * n
         assert abs(float(gr[m, d + 1]) - float(og["noise"])) <= TOL * max(abs(float(og["noise"])), float(n))
         assert abs(float(gr[m, d + 2]) - float(og["mean"])) <= TOL * max(abs(float(og["mean"])), 1.0)
+
+
+def test_sum_mll_fits_every_outcome_of_a_model_list(cuda):
+    """fit_gpytorch_mll(SumMarginalLogLikelihood(model.likelihood, model)) == fitting each outcome on its own (_fit_list,
+    fit.py:262-285), also for a SingleTaskGP built on n x m targets."""
+    import botorch_b200 as bb
+
+    n, d = 50, 3
+    X, y0 = _data(n, d, seed=3, noise=0.1)
+    y1 = torch.cos(4.0 * X[:, 1]) + 0.2 * torch.randn(n, generator=torch.Generator().manual_seed(4), dtype=torch.float64)
+    Y = torch.stack([y0.reshape(-1), y1.reshape(-1)], dim=-1)
+    multi = bb.SingleTaskGP(X.to(cuda), Y.to(cuda))
+    assert isinstance(multi, bb.ModelListGP)
+    mll = bb.SumMarginalLogLikelihood(multi.likelihood, multi)
+    before = float(mll.forward())
+    out = bb.fit_gpytorch_mll(mll)
+    assert out is mll and not mll.training and float(mll.forward()) > before
+    for k in range(2):
+        single = bb.SingleTaskGP(X.to(cuda), Y[:, k : k + 1].to(cuda))
+        bb.fit_gpytorch_mll(bb.ExactMarginalLogLikelihood(single.likelihood, single))
+        a, b = multi.models[k].state_dict(), single.state_dict()
+        assert a.keys() == b.keys() and all(torch.equal(a[key], b[key]) for key in a)
+    post = multi.posterior(X[:4].to(cuda).unsqueeze(0))
+    assert post.mean.shape == (1, 4, 2) and bool(torch.isfinite(post.variance).all())
