@@ -244,6 +244,75 @@ def _mll_leg(p, dev, stream, cpu: bool):
     return leg
 
 
+def _constrained_leg(p, dev, B):
+    """SURVEY 8f N2 at the workload's shape: qLogNEI over two outcomes (the workload's objective + one constrained outcome on
+    the same inputs) with one smoothed constraint, forward + backward through the public API, CUDA-event timed."""
+    import botorch_b200 as bb
+
+    h = p.hypers
+    g = torch.Generator().manual_seed(0)
+    X = p.train_X
+    y_con = (X[:, : min(4, p.d)].sum(-1) - 0.5 * min(4, p.d) + 0.05 * torch.randn(p.n, generator=g, dtype=torch.float64)).unsqueeze(-1)
+    kw = {"lengthscale": h["lengthscale"], "noise": h["noise"], "mean_constant": h["mean"], "kernel": p.kernel}
+    if h.get("outputscale") is not None:
+        kw["outputscale"] = h["outputscale"]
+    gps = [bb.SingleTaskGP(X.to(dev), y.to(dev), **kw) for y in (p.train_Y, y_con)]
+    acqf = bb.qLogNoisyExpectedImprovement(
+        bb.ModelListGP(*gps), X.to(dev), sampler=bb.SobolQMCNormalSampler(torch.Size([p.mc_samples]), seed=1234),
+        objective=bb.LinearMCObjective(torch.tensor([1.0, 0.0], dtype=torch.float64, device=dev)),
+        constraints=[lambda Z: Z[..., 1] - 0.25], eta=1e-2)  # fmt: skip
+    Xc = torch.rand(B, p.q, p.d, dtype=torch.float64, generator=g).to(dev)
+
+    def step():
+        Xg = Xc.detach().requires_grad_(True)
+        v = acqf(Xg)
+        return v, torch.autograd.grad(v.sum(), Xg)[0]
+
+    for _ in range(3):
+        v, gr = step()
+    reps = 10
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    torch.cuda.synchronize()
+    e0.record()
+    for _ in range(reps):
+        v, gr = step()
+    e1.record()
+    torch.cuda.synchronize()
+    ms = e0.elapsed_time(e1) / reps
+    return {"candidate_evals_per_s": B / (ms * 1e-3), "ms_per_step": ms, "outcomes": 2, "constraints": 1, "restarts": B,
+            "finite": bool(torch.isfinite(v).all() and torch.isfinite(gr).all()),
+            "what": "qLogNoisyExpectedImprovement(ModelListGP, constraints=[...]) forward + autograd backward: two fused "
+                    "pipelines, bo_mc_reduce_fwd/_bwd, external sample adjoints (profiles/r01_constrained_c3.json)"}  # fmt: skip
+
+
+def _saas_leg(dev, chains: int = 64):
+    """the SAAS potential energy + gradient NUTS evaluates per leapfrog step, C4's training shape
+    (n=100, d=30), `chains` chains per call as one CUDA-graph replay of bo_mll_value_grad + the prior terms."""
+    from botorch_b200.fully_bayesian import SaasPotential
+
+    g = torch.Generator().manual_seed(0)
+    n, d = 100, 30
+    X = torch.rand(n, d, generator=g, dtype=torch.float64)
+    y = torch.sin(2 * torch.pi * X[:, 0]) + 0.1 * torch.randn(n, generator=g, dtype=torch.float64)
+    pot = SaasPotential(X.to(dev), ((y - y.mean()) / y.std()).to(dev), num_chains=chains)
+    U = (torch.rand(chains, d + 4, generator=g, dtype=torch.float64) - 0.5).to(dev)
+    for _ in range(5):
+        e, _ = pot(U)
+    reps = 30
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    torch.cuda.synchronize()
+    e0.record()
+    for _ in range(reps):
+        pot(U)
+    e1.record()
+    torch.cuda.synchronize()
+    ms = e0.elapsed_time(e1) / reps
+    return {"chain_evals_per_s": chains / (ms * 1e-3), "ms_per_call": ms, "chains": chains, "n": n, "d": d,
+            "finite": bool(torch.isfinite(e).all()),
+            "what": "SaasPotential: potential energy + gradient of SaasPyroModel for all chains in one call "
+                    "(profiles/r01_saas_potential_nuts.json)"}  # fmt: skip
+
+
 def _workload_name(p, B):
     return (f"{p.name}: n={p.n} d={p.d} q={p.q} S={p.mc_samples} restarts/GPU={B} "
             f"(BASELINE.json configs[{'C1 C2 C3 C4 C5'.split().index(p.name[:2])}])")  # fmt: skip
@@ -455,6 +524,8 @@ def _run_ours(args):
     }  # fmt: skip
     if mll_leg is not None:
         line["mll"] = mll_leg
+        line["constrained"] = _constrained_leg(p, dev, B)
+        line["saas_potential"] = _saas_leg(dev)
     if not args.no_cpu_baseline and ws == 1:
         sample = args.cpu_sample or (4 if p.n >= 1000 else 32)
         line["cpu_baseline"] = _cpu_baseline(p, sample)
