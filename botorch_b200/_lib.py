@@ -163,9 +163,10 @@ def _declare(lib: C.CDLL) -> None:
     lib.bo_mll_workspace_bytes.restype = sz
     lib.bo_mll_workspace_bytes.argtypes = [gp]
     lib.bo_mll_value_grad.argtypes = [vp, gp, vp, sz, vp, vp, vp, vp]
+    lib.bo_saas_potential.argtypes = [vp, gp, vp, vp, sz, vp, vp, vp, vp, vp, vp, vp]
     for name in (
         "bo_ctx_create bo_gp_setup bo_nei_setup bo_ei_setup bo_qlognei_fwd bo_qlognei_bwd bo_posterior_joint bo_posterior_joint_bwd "
-        "bo_posterior_mean_var bo_ts_argmax bo_argmax bo_dgemm bo_kernel_matrix bo_potrf bo_mll_value_grad bo_paths_setup bo_paths_eval bo_paths_grad bo_qlognei_samples_view bo_mc_reduce_fwd bo_mc_reduce_bwd"
+        "bo_posterior_mean_var bo_ts_argmax bo_argmax bo_dgemm bo_kernel_matrix bo_potrf bo_mll_value_grad bo_saas_potential bo_paths_setup bo_paths_eval bo_paths_grad bo_qlognei_samples_view bo_mc_reduce_fwd bo_mc_reduce_bwd"
     ).split():
         getattr(lib, name).restype = i32
 

@@ -1091,6 +1091,125 @@ int bo_mll_value_grad(bo_ctx* ctx, const bo_gp* gp, void* work, size_t work_byte
 }
 
 // ------------------------------------------------------------------------------------------------
+// SAAS potential energy: what pyro's NUTS evaluates per leapfrog step inside
+// fit_fully_bayesian_model_nuts (fit.py:335-396 over SaasPyroModel.sample, models/fully_bayesian.py:167-246)
+// ------------------------------------------------------------------------------------------------
+}  // extern "C"
+
+namespace {
+
+constexpr double SAAS_MIN_NOISE = 1e-4;  // MIN_INFERRED_NOISE_LEVEL (models/utils/gpytorch_modules.py:29)
+constexpr double SAAS_U_MAX = 80.0;      // |u| beyond this: exp() leaves the useful float64 range -> divergent
+
+// u [C x (d+4)] = [log tausq, log inv_length_sq (d), mean, log noise_raw, log outputscale] -> the hyperparameter buffers of gp
+__global__ void saas_transform_kernel(const double* u, int d, double* inv_ls, double* outputscale, double* noise,
+                                      double* mean, int* wild) {
+    const int c = blockIdx.x, D = d + 4;
+    const double* uc = u + (long)c * D;
+    __shared__ int bad;
+    if (threadIdx.x == 0) bad = 0;
+    __syncthreads();
+    for (int i = threadIdx.x; i < D; i += blockDim.x)
+        if (!(fabs(uc[i]) < SAAS_U_MAX)) bad = 1;  // also catches NaN
+    __syncthreads();
+    const int b = bad;
+    for (int i = threadIdx.x; i < d; i += blockDim.x)
+        inv_ls[(long)c * d + i] = b ? 1.0 : exp(0.5 * (uc[0] + uc[1 + i]));  // 1 / lengthscale = sqrt(tausq * inv_length_sq)
+    if (threadIdx.x == 0) {
+        mean[c] = b ? 0.0 : uc[1 + d];
+        noise[c] = SAAS_MIN_NOISE + (b ? 1.0 : exp(uc[2 + d]));
+        outputscale[c] = b ? 1.0 : exp(uc[3 + d]);
+        wild[c] = b;
+    }
+}
+
+// energy = -(log lik + log priors + log|dx/du|), gradient by the closed-form chain rule (x = exp(u): d/du = x d/dx;
+// lengthscale_i = exp(-(u_0 + u_{1+i}) / 2)  =>  d lengthscale_i / d u_0 = d lengthscale_i / d u_{1+i} = -lengthscale_i / 2)
+__global__ void __launch_bounds__(128) saas_finalize_kernel(const double* u, int d, const double* value, const double* grad,
+                                                            const int* info, const int* wild, double* energy,
+                                                            double* grad_u) {
+    __shared__ double sm[128];
+    const int c = blockIdx.x, D = d + 4, tid = threadIdx.x;
+    const double* uc = u + (long)c * D;
+    const double* g = grad + (long)c * (d + 3);  // [d lengthscale (d), outputscale, noise, mean]
+    double* gu = grad_u + (long)c * D;
+    const bool bad = wild[c] || info[c] != 0;
+    const double u0 = bad ? 0.0 : uc[0];
+    double lp = 0.0, gsum = 0.0;  // half-Cauchy(1) sites + their Jacobians; sum_i d ll / d u_{1+i}
+    for (int i = tid; i < d; i += blockDim.x) {
+        const double ui = bad ? 0.0 : uc[1 + i];
+        const double x = exp(ui), r2 = x * x;
+        const double hl = -0.5 * exp(-0.5 * (u0 + ui)) * g[i];
+        lp += -0.4515827052894548647 - log1p(r2) + ui;  // log(2/pi)
+        gsum += hl;
+        gu[1 + i] = -(hl + 1.0 - 2.0 * r2 / (1.0 + r2));
+    }
+    sm[tid] = lp;
+    __syncthreads();
+    for (int s_ = 64; s_ > 0; s_ >>= 1) { if (tid < s_) sm[tid] += sm[tid + s_]; __syncthreads(); }
+    lp = sm[0];
+    __syncthreads();
+    sm[tid] = gsum;
+    __syncthreads();
+    for (int s_ = 64; s_ > 0; s_ >>= 1) { if (tid < s_) sm[tid] += sm[tid + s_]; __syncthreads(); }
+    gsum = sm[0];
+    if (tid == 0) {
+        const double mean = bad ? 0.0 : uc[1 + d], unr = bad ? 0.0 : uc[2 + d], uos = bad ? 0.0 : uc[3 + d];
+        const double t = exp(u0), nr = exp(unr), os = exp(uos), r2 = 100.0 * t * t;  // tausq ~ HalfCauchy(0.1)
+        // Gamma(a, b): a log b + (a-1) log x - b x - lgamma(a); lgamma(2) = 0, lgamma(0.9) = 0.06637623973474297
+        const double lp_os = 2.0 * log(0.15) + uos - 0.15 * os;
+        const double lp_nr = 0.9 * log(10.0) - 0.1 * unr - 10.0 * nr - 0.066376239734742966;
+        const double lp_t = -0.4515827052894548647 - log(0.1) - log1p(r2);
+        const double lp_m = -0.5 * mean * mean - 0.91893853320467274178;
+        const double logp = value[c] + lp + lp_t + lp_os + lp_nr + lp_m + u0 + unr + uos;
+        double e = -logp;
+        double g0 = -(gsum + 1.0 - 2.0 * r2 / (1.0 + r2));
+        double gm = -(g[d + 2] - mean);
+        double gn = -(g[d + 1] * nr - 0.1 - 10.0 * nr + 1.0);
+        double go = -(g[d] * os + 1.0 - 0.15 * os + 1.0);
+        bool fail = bad || !isfinite(e) || !isfinite(g0) || !isfinite(gm) || !isfinite(gn) || !isfinite(go);
+        sm[0] = fail ? 1.0 : 0.0;
+        energy[c] = e; gu[0] = g0; gu[1 + d] = gm; gu[2 + d] = gn; gu[3 + d] = go;
+    }
+    __syncthreads();
+    bool fail = sm[0] != 0.0;
+    __syncthreads();
+    // a non-finite lengthscale gradient entry also marks the chain as failed
+    int nf = 0;
+    for (int i = tid; i < d; i += blockDim.x) nf |= !isfinite(gu[1 + i]);
+    sm[tid] = (double)nf;
+    __syncthreads();
+    for (int s_ = 64; s_ > 0; s_ >>= 1) { if (tid < s_) sm[tid] += sm[tid + s_]; __syncthreads(); }
+    fail = fail || sm[0] != 0.0;
+    if (fail) {
+        for (int i = tid; i < D; i += blockDim.x) gu[i] = 0.0;
+        if (tid == 0) energy[c] = INFINITY;
+    }
+}
+
+}  // namespace
+
+extern "C" {
+
+// gp: Matern-5/2 with outputscale, M = number of chains, hyperparameter buffers (inv_ls, outputscale, noise, mean) writable.
+int bo_saas_potential(bo_ctx* ctx, const bo_gp* gp, const double* u, void* work, size_t work_bytes, double* value,
+                      double* grad, int32_t* wild, double* energy, double* grad_u, int32_t* info, void* stream) {
+    if (!ctx || !gp || !u || !value || !grad || !wild || !energy || !grad_u || !info) return BO_ERR_INVALID;
+    if (!gp->outputscale || gp->noise_vec) return BO_ERR_UNSUPPORTED;
+    cudaStream_t st = (cudaStream_t)stream;
+    const int C = (int)gp->M, d = (int)gp->d;
+    saas_transform_kernel<<<C, 64, 0, st>>>(u, d, const_cast<double*>(gp->inv_ls), const_cast<double*>(gp->outputscale),
+                                            const_cast<double*>(gp->noise), const_cast<double*>(gp->mean), wild);
+    g_bo_launch_count++;
+    BO_CUDA_TRY(cudaGetLastError());
+    BO_TRY(bo_mll_value_grad(ctx, gp, work, work_bytes, value, grad, info, stream));
+    saas_finalize_kernel<<<C, 128, 0, st>>>(u, d, value, grad, info, wild, energy, grad_u);
+    g_bo_launch_count++;
+    BO_CUDA_TRY(cudaGetLastError());
+    return BO_OK;
+}
+
+// ------------------------------------------------------------------------------------------------
 // pathwise (Matheron) posterior samples
 // ------------------------------------------------------------------------------------------------
 }  // extern "C"

@@ -19,18 +19,21 @@ with the exp transform on every positive site (``biject_to(support)``) and its l
 """
 from __future__ import annotations
 
+import ctypes
 import math
 from typing import Callable, Dict, Optional, Tuple
 
 import torch
 from torch import Tensor
 
-from . import engine
+from . import _lib, engine
+from ._lib import check, ptr
 from .models import MIN_INFERRED_NOISE_LEVEL, SaasFullyBayesianSingleTaskGP
 
 _LOG_2_OVER_PI = math.log(2.0 / math.pi)
 
 
+# Host mirrors of the prior terms inside saas_finalize_kernel (csrc/api.cu), pinned against torch.distributions by the CPU tests.
 def _gamma_lp(x: Tensor, log_x: Tensor, a: float, b: float) -> Tensor:
     return a * math.log(b) + (a - 1.0) * log_x - b * x - math.lgamma(a)
 
@@ -51,8 +54,9 @@ class SaasPotential:
         self.dim = self.d + 4
         self.num_chains = int(num_chains)
         self._state = engine.MLLState(self.X, self.y, "matern52", with_outputscale=True, M=self.num_chains)
+        self._wild = torch.zeros(self.num_chains, dtype=torch.int32, device=self.X.device)
         self.evaluations = 0
-        # The whole evaluation (transforms, bo_mll_value_grad, prior terms, chain rule) is a fixed launch sequence without
+        # The whole evaluation (bo_saas_potential: transforms, bo_mll_value_grad, prior terms, chain rule) is a fixed launch sequence without
         # host synchronisation: after two eager calls it is captured once and replayed as one CUDA graph per leapfrog step.
         self._use_graph, self._graph, self._eager_calls = bool(graph), None, 0
 
@@ -87,37 +91,24 @@ class SaasPotential:
         self._graph.replay()
         return self._out[0].clone(), self._out[1].clone()
 
+    @property
+    def capture_safe_evaluate(self) -> PotentialFn:
+        """The evaluation as a plain launch sequence (no replay of this object's own graph): what `nuts_sample` captures
+        inside its per-depth subtree graphs."""
+        return self._evaluate
+
     def _evaluate(self, u: Tensor) -> Tuple[Tensor, Tensor]:
-        """Closed-form chain rule around bo_mll_value_grad (few fused elementwise launches; the whole thing is graph-captured).
-        With x = exp(u) on the positive sites: d/du of a log density term is x * d/dx, the log-Jacobian contributes +1, and
-        lengthscale_i = exp(-(u_tausq + u_ils_i) / 2) gives d lengthscale_i / d u_tausq = d lengthscale_i / d u_ils_i = -l_i / 2."""
-        d = self.d
-        wild = ~(torch.isfinite(u).all(-1) & (u.abs().amax(-1) < 80.0))  # exp() of the row would leave the float64 range
-        v = torch.where(wild.unsqueeze(-1), torch.zeros_like(u), u)
-        x = v.exp()
-        mean, nr, os_ = v[:, 1 + d], x[:, 2 + d], x[:, 3 + d]
-        lengthscale = torch.exp(-0.5 * (v[:, :1] + v[:, 1 : 1 + d]))
-        # one plain factorisation, no jitter: a covariance that cannot be factored is a divergent transition, not a warning
-        ll, gl = self._state.evaluate(lengthscale, MIN_INFERRED_NOISE_LEVEL + nr, mean, os_, retry=False)
-        # half-Cauchy sites (tausq: scale 0.1, inv_length_sq: scale 1), columns 0 .. d
-        r2 = x[:, : 1 + d] ** 2
-        r2[:, 0] *= 100.0
-        lp_hc = _LOG_2_OVER_PI - torch.log1p(r2)
-        logp = (ll + lp_hc.sum(-1) - math.log(0.1) + _gamma_lp(os_, v[:, 3 + d], 2.0, 0.15) + _gamma_lp(nr, v[:, 2 + d], 0.9, 10.0)
-                - 0.5 * mean * mean - 0.5 * math.log(2.0 * math.pi) + v[:, : 1 + d].sum(-1) + v[:, 2 + d] + v[:, 3 + d])
-        half_l_g = -0.5 * lengthscale * gl[:, :d]  # d ll / d u_ils_i
-        grad_logp = torch.empty_like(v)
-        grad_logp[:, : 1 + d] = 1.0 - 2.0 * r2 / (1.0 + r2)
-        grad_logp[:, 0] += half_l_g.sum(-1)
-        grad_logp[:, 1 : 1 + d] += half_l_g
-        grad_logp[:, 1 + d] = gl[:, d + 2] - mean
-        grad_logp[:, 2 + d] = gl[:, d + 1] * nr + (0.9 - 1.0) - 10.0 * nr + 1.0
-        grad_logp[:, 3 + d] = gl[:, d] * os_ + (2.0 - 1.0) - 0.15 * os_ + 1.0
-        energy, grad = -logp, -grad_logp
-        bad = wild | (self._state.info != 0) | ~(torch.isfinite(energy) & torch.isfinite(grad).all(-1))
-        energy = torch.where(bad, torch.full_like(energy, float("inf")), energy)
-        grad = torch.where(bad.unsqueeze(-1), torch.zeros_like(grad), grad)
-        return energy, grad
+        """One ``bo_saas_potential``: transform kernel -> bo_mll_value_grad -> closed-form chain-rule kernel.  No host
+        synchronisation, no allocation inside the library: the launch sequence is graph-capturable as it is."""
+        st, gp = self._state, self._state.gp
+        energy = torch.empty(self.num_chains, dtype=torch.float64, device=u.device)
+        grad_u = torch.empty(self.num_chains, self.dim, dtype=torch.float64, device=u.device)
+        u = u.contiguous()
+        gp.c.jitter = None  # one plain factorisation: a covariance that cannot be factored is a divergent transition
+        check(_lib.lib().bo_saas_potential(gp.ctx, ctypes.byref(gp.c), ptr(u), st.work.data_ptr(), st.work.numel(), ptr(st.value),
+                                           ptr(st.grad), ptr(self._wild), ptr(energy), ptr(grad_u), ptr(gp.info),
+                                           _lib.stream_ptr(u.device)))  # fmt: skip
+        return energy, grad_u
 
 
 # ---- NUTS over a batch of chains ---------------------------------------------------------------------------------------------
@@ -174,16 +165,19 @@ def _turning(rho: Tensor, r_a: Tensor, r_b: Tensor, minv: Tensor) -> Tensor:
     return ((rho * minv * r_a).sum(-1) <= 0) | ((rho * minv * r_b).sum(-1) <= 0)
 
 
-def _build(potential: PotentialFn, depth: int, z, r, g, step, minv, h0, gen) -> _Tree:
+def _build(potential: PotentialFn, depth: int, z, r, g, step, minv, h0, R: Tensor, base: int = 0) -> _Tree:
+    """Subtree of 2**depth leapfrog steps.  R [2**depth x C]: uniform draws, one row per merge (2**depth - 1 of them: row
+    `base` for this node, the next 2**(depth-1) - 1 for the first half, the rest for the second)."""
     if depth == 0:
         return _leaf(potential, z, r, g, step, minv, h0)
-    first = _build(potential, depth - 1, z, r, g, step, minv, h0, gen)
-    second = _build(potential, depth - 1, first.z_out, first.r_out, first.g_out, step, minv, h0, gen)
+    half = 2 ** (depth - 1)
+    first = _build(potential, depth - 1, z, r, g, step, minv, h0, R, base + 1)
+    second = _build(potential, depth - 1, first.z_out, first.r_out, first.g_out, step, minv, h0, R, base + half)
     both = _Tree()
     both.r_in = first.r_in
     both.z_out, both.r_out, both.g_out = second.z_out, second.r_out, second.g_out
     both.log_w = torch.logaddexp(first.log_w, second.log_w)
-    take2 = torch.rand(first.log_w.shape, generator=gen, device=z.device, dtype=z.dtype) < torch.exp(second.log_w - both.log_w)
+    take2 = R[base] < torch.exp(second.log_w - both.log_w)
     both.z_prop = torch.where(take2.unsqueeze(-1), second.z_prop, first.z_prop)
     both.g_prop = torch.where(take2.unsqueeze(-1), second.g_prop, first.g_prop)
     both.u_prop = torch.where(take2, second.u_prop, first.u_prop)
@@ -193,6 +187,32 @@ def _build(potential: PotentialFn, depth: int, z, r, g, step, minv, h0, gen) -> 
     both.sum_accept = first.sum_accept + second.sum_accept
     both.leaves = first.leaves + second.leaves
     return first.select(first.stop, both)  # a subtree that already stopped ignores everything grown after it
+
+
+class _GraphedTrees:
+    """`_build` for each depth captured once into a CUDA graph over static buffers (CUDA tensors and a potential that offers
+    a capture-safe evaluation): growing a subtree of 2**depth leapfrog steps is then ONE graph launch instead of
+    ~100 * 2**depth kernel launches issued from Python."""
+
+    def __init__(self, evaluate: PotentialFn, like: Tensor) -> None:
+        self.evaluate, self.graphs = evaluate, {}
+        self.z, self.r, self.g, self.minv = (torch.zeros_like(like) for _ in range(4))
+        self.step, self.h0 = torch.zeros_like(like[:, 0]), torch.zeros_like(like[:, 0])
+
+    def build(self, depth: int, z, r, g, step, minv, h0, R: Tensor) -> _Tree:
+        for dst, src in ((self.z, z), (self.r, r), (self.g, g), (self.step, step), (self.minv, minv), (self.h0, h0)):
+            dst.copy_(src)
+        if depth not in self.graphs:
+            R_static = R.clone()
+            torch.cuda.synchronize(z.device)
+            graph = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(graph):
+                tree = _build(self.evaluate, depth, self.z, self.r, self.g, self.step, self.minv, self.h0, R_static)
+            self.graphs[depth] = (graph, R_static, tree)
+        graph, R_static, tree = self.graphs[depth]
+        R_static.copy_(R)
+        graph.replay()
+        return tree  # fields alias the graph's output buffers: consumed (torch.where into new tensors) before the next replay
 
 
 class _DualAveraging:
@@ -271,9 +291,12 @@ def _adaptation_windows(warmup: int) -> Tuple[int, list]:
 
 
 def nuts_sample(potential: PotentialFn, init: Tensor, num_samples: int, warmup_steps: int, max_tree_depth: int = 6,
-                target_accept: float = 0.8, seed: Optional[int] = None, adapt_mass: bool = True):  # fmt: skip
+                target_accept: float = 0.8, seed: Optional[int] = None, adapt_mass: bool = True,
+                graph: Optional[bool] = None):  # fmt: skip
     """Run C chains of NUTS in lockstep.  init: [C x D] -> (samples [num_samples x C x D], stats).  ``potential`` maps
-    [C x D] to (energy [C], gradient [C x D]); +inf energy marks a divergent point."""
+    [C x D] to (energy [C], gradient [C x D]); +inf energy marks a divergent point.  With ``graph`` (default: whenever the
+    potential offers ``capture_safe_evaluate`` and lives on a CUDA device) each subtree is one CUDA-graph launch; the draws
+    are the same with and without graphs."""
     z = init.detach().clone()
     dev, dt = z.device, z.dtype
     C = z.shape[0]
@@ -282,6 +305,12 @@ def nuts_sample(potential: PotentialFn, init: Tensor, num_samples: int, warmup_s
     u, g = potential(z)
     if not bool(torch.isfinite(u).all()):
         raise RuntimeError("NUTS needs a finite potential energy at every initial point")
+    capture_safe = getattr(potential, "capture_safe_evaluate", None)
+    if graph is None:
+        graph = capture_safe is not None and z.is_cuda
+    if graph and (capture_safe is None or not z.is_cuda):
+        raise ValueError("graph=True needs CUDA tensors and a potential with `capture_safe_evaluate`")
+    trees = _GraphedTrees(capture_safe, z) if graph else None
     minv = torch.ones_like(z)
     eps = _reasonable_step(potential, z, u, g, minv, gen)
     averaging = _DualAveraging(eps, target=target_accept)
@@ -302,8 +331,15 @@ def nuts_sample(potential: PotentialFn, init: Tensor, num_samples: int, warmup_s
         for depth in range(max_tree_depth):
             fwd = torch.rand(C, generator=gen, device=dev, dtype=dt) < 0.5
             f2 = fwd.unsqueeze(-1)
-            tree = _build(potential, depth, torch.where(f2, z_plus, z_minus), torch.where(f2, r_plus, r_minus),
-                          torch.where(f2, g_plus, g_minus), torch.where(fwd, eps, -eps), minv, h0, gen)  # fmt: skip
+            R = torch.rand(2**depth, C, generator=gen, device=dev, dtype=dt)
+            edge = (torch.where(f2, z_plus, z_minus), torch.where(f2, r_plus, r_minus), torch.where(f2, g_plus, g_minus),
+                    torch.where(fwd, eps, -eps), minv, h0, R)  # fmt: skip
+            if trees is not None:
+                tree = trees.build(depth, *edge)
+                if hasattr(potential, "evaluations"):
+                    potential.evaluations += 2**depth
+            else:
+                tree = _build(potential, depth, *edge)
             stats["leapfrogs"] += 2**depth
             sum_accept = sum_accept + torch.where(active, tree.sum_accept, torch.zeros_like(u))
             leaves = leaves + torch.where(active, tree.leaves, torch.zeros_like(u))

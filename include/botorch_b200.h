@@ -239,6 +239,22 @@ size_t bo_mll_workspace_bytes(const bo_gp* gp);
 int bo_mll_value_grad(bo_ctx* ctx, const bo_gp* gp, void* work, size_t work_bytes, double* value, double* grad,
                       int32_t* info, void* stream);
 
+/* Potential energy of the reference's SAAS model in the unconstrained space pyro's NUTS works in, for M = gp->M chains at
+ * once: what fit_fully_bayesian_model_nuts (botorch/fit.py:335-396) evaluates per leapfrog step through
+ * SaasPyroModel.sample (models/fully_bayesian.py:167-246) + autograd.
+ *   u [M x (d+4)] = [ log kernel_tausq, log _kernel_inv_length_sq (d), mean, log (noise - 1e-4), log outputscale ]
+ *   energy[z] = -( log N(targets | mean, outputscale * matern52(X / lengthscale) + noise I) + log priors + log|dx/du| )
+ *   with outputscale ~ Gamma(2, 0.15), mean ~ N(0, 1), noise - 1e-4 ~ Gamma(0.9, 10), tausq ~ HalfCauchy(0.1),
+ *   inv_length_sq ~ HalfCauchy(1)^d, lengthscale = (tausq * inv_length_sq)^-1/2;   grad_u [M x (d+4)] = d energy / d u.
+ * The call writes the hyperparameter buffers of `gp` (inv_ls, outputscale, noise, mean: must be writable, kernel
+ * BO_KERNEL_MATERN52 with outputscale, no noise_vec), runs bo_mll_value_grad (value [M], grad [M x (d+3)] are its
+ * outputs, kept for the caller) and finishes with the closed-form chain rule.  A chain with a non-finite / out-of-range u
+ * (wild[z] = 1), a failed factorisation (info[z] != 0; no jitter is added) or a non-finite result gets energy = +inf and
+ * a zero gradient -- a divergent transition, as pyro's registered exception handlers make it (fully_bayesian.py:67-78);
+ * the other chains are unaffected.  Workspace: bo_mll_workspace_bytes. */
+int bo_saas_potential(bo_ctx* ctx, const bo_gp* gp, const double* u, void* work, size_t work_bytes, double* value,
+                      double* grad, int32_t* wild, double* energy, double* grad_u, int32_t* info, void* stream);
+
 /* ---- pathwise (Matheron) posterior samples (second half) -----------------------------------------
  * Replaces draw_matheron_paths (sampling/pathwise/posterior_samplers.py:143-199) for the exact single-model GP:
  *   prior path   f0(x) = m + phi(x) . w,  phi(x) = sqrt(os) sqrt(2/F) [sin(W x/l), cos(W x/l)]      (random Fourier features:

@@ -69,13 +69,22 @@ def potential(u: Tensor, X: Tensor, y: Tensor) -> Tensor:
     return -logp
 
 
-def potential_and_grad(U: Tensor, X: Tensor, y: Tensor) -> Tuple[Tensor, Tensor]:
-    """U: [M x (d+4)] -> (energy [M], gradient [M x (d+4)]) by autograd, one chain at a time."""
+def potential_and_grad(U: Tensor, X: Tensor, y: Tensor, divergent_as_inf: bool = False) -> Tuple[Tensor, Tensor]:
+    """U: [M x (d+4)] -> (energy [M], gradient [M x (d+4)]) by autograd, one chain at a time.  With ``divergent_as_inf`` a
+    chain whose evaluation raises (LinAlgError / "PositiveDefinite" ValueError: the exceptions the reference registers with
+    pyro's integrator, fully_bayesian.py:67-78) or is not finite gets energy +inf and a zero gradient."""
     vals, grads = [], []
     for u in U:
         ug = u.detach().clone().requires_grad_(True)
-        e = potential(ug, X, y)
-        (g,) = torch.autograd.grad(e, ug)
+        try:
+            e = potential(ug, X, y)
+            (g,) = torch.autograd.grad(e, ug)
+            if divergent_as_inf and not (torch.isfinite(e) and torch.isfinite(g).all()):
+                raise ValueError("not finite")
+        except (ValueError, torch.linalg.LinAlgError):
+            if not divergent_as_inf:
+                raise
+            e, g = torch.tensor(float("inf"), dtype=u.dtype), torch.zeros_like(u)
         vals.append(e.detach())
         grads.append(g)
     return torch.stack(vals), torch.stack(grads)

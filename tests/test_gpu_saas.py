@@ -86,7 +86,7 @@ def test_nuts_on_the_device_potential_follows_the_oracle_potential(cuda):
     pot = SaasPotential(X.to(cuda), y.to(cuda), num_chains=C)
 
     def oracle_pot(u):
-        e, gr = osaas.potential_and_grad(u.cpu(), X, y)
+        e, gr = osaas.potential_and_grad(u.cpu(), X, y, divergent_as_inf=True)
         return e.to(cuda), gr.to(cuda)
 
     a, sa = nuts_sample(pot, init, num_samples=4, warmup_steps=3, max_tree_depth=4, seed=11, adapt_mass=False)
@@ -94,6 +94,22 @@ def test_nuts_on_the_device_potential_follows_the_oracle_potential(cuda):
     assert sa["leapfrogs"] == sb["leapfrogs"]
     assert rel_err(a, b, scale=1.0) < 1e-6
     assert not torch.equal(a[0], a[-1])
+
+
+def test_graphed_subtrees_draw_what_the_eager_sampler_draws(cuda):
+    """Each subtree of 2**depth leapfrog steps as one CUDA-graph launch: bit-identical draws and statistics."""
+    from botorch_b200.fully_bayesian import SaasPotential, nuts_sample
+
+    X, y, g = _problem(40, 5, seed=8)
+    C = 4
+    init = (torch.rand(C, 9, generator=g, dtype=torch.float64) - 0.5).to(cuda)
+    runs = []
+    for graph in (False, True):
+        pot = SaasPotential(X.to(cuda), y.to(cuda), num_chains=C)
+        runs.append(nuts_sample(pot, init, num_samples=6, warmup_steps=45, max_tree_depth=4, seed=2, graph=graph) + (pot,))
+    (a, sa, pa), (b, sb, pb) = runs
+    assert torch.equal(a, b) and sa["leapfrogs"] == sb["leapfrogs"] and pa.evaluations == pb.evaluations
+    assert torch.equal(sa["step_size"], sb["step_size"]) and torch.equal(sa["inverse_mass"], sb["inverse_mass"])
 
 
 def test_fit_fully_bayesian_model_nuts_end_to_end(cuda):
