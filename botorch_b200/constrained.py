@@ -205,7 +205,10 @@ class _ConstrainedFn(torch.autograd.Function):
             with torch.enable_grad():
                 s = samples.detach().requires_grad_(True)
                 lw = compute_smoothed_feasibility_indicator(acqf._constraints, s, acqf._eta, log=True, fat=acqf._fat)
-                (gs,) = torch.autograd.grad(lw, s, grad_outputs=lw_bar[:, :N].reshape(S, B, q))
+                if lw.requires_grad:
+                    (gs,) = torch.autograd.grad(lw, s, grad_outputs=lw_bar[:, :N].reshape(S, B, q), allow_unused=True)
+                else:  # constraints that do not read the samples differentiably (constants, hard thresholds)
+                    gs = None
         grad = None
         for k, nei in enumerate(acqf._neis):
             dFk = torch.zeros(S, N, dtype=torch.float64, device=dev) if gs is None else gs[..., k].reshape(S, N).clone()

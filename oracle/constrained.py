@@ -16,7 +16,7 @@ restatements against them (and against literals minted from them, for machines w
 from __future__ import annotations
 
 import math
-from typing import Callable, List, Sequence
+from typing import Optional, Callable, List, Sequence
 
 import torch
 from torch import Tensor
@@ -57,12 +57,24 @@ def smoothed_log_feasibility(constraints, samples: Tensor, eta: Sequence[float],
     return out
 
 
+def objective_lower_bound(models, X: Tensor, convex_weights: Tensor, obj_idx: int, obj_w: float) -> float:
+    """``_estimate_objective_lower_bound`` + ``get_infeasible_cost`` (acquisition/utils.py:166-242): the objective of the
+    6-sigma lower posterior bound at convex combinations of the baseline points (``convex_weights``: the 32 x n uniform
+    draws, normalised over dim 0 as the reference does), minimum over points, clamped at 0.  Returns -M."""
+    w = convex_weights / convex_weights.sum(dim=0, keepdim=True)
+    Xc = w @ X
+    mean, cov = models[obj_idx].posterior(Xc.unsqueeze(0))  # 1 x 32 joint block; only its diagonal is used
+    var = torch.diagonal(cov, dim1=-2, dim2=-1).clamp_min(0)
+    lb = obj_w * (mean - 6.0 * var.sqrt())
+    return float(lb.min().clamp_max(0.0))
+
+
 class OracleConstrainedQLogNEI:
     """m independent OracleGPs; objective = obj_weight * outcome obj_idx; constraints: callables on (..., m) samples."""
 
     def __init__(self, models: List[OracleGP], X_baseline: Tensor, constraints: List[Callable[[Tensor], Tensor]], eta,
                  obj_idx: int = 0, obj_weight: float = 1.0, num_samples: int = 64, seed: int = 1234, fat: bool = True,
-                 tau_relu: float = TAU_RELU, tau_max: float = TAU_MAX):  # fmt: skip
+                 tau_relu: float = TAU_RELU, tau_max: float = TAU_MAX, convex_weights: Optional[Tensor] = None):  # fmt: skip
         self.m, self.S, self.seed = len(models), num_samples, seed
         self.constraints = constraints
         # utils/objective.py:167-168: a float eta becomes torch.full((n,), eta) in the DEFAULT dtype (float32 unless the caller
@@ -84,8 +96,12 @@ class OracleConstrainedQLogNEI:
         base = torch.stack([o.baseline_samples for o in self.parts], dim=-1)  # S x n_b x m
         obj_b = self.obj_w * base[..., obj_idx]
         feas = feasibility(constraints, base)
-        assert bool(feas.any(dim=-1).all()), "oracle covers the branch with a feasible baseline point per sample"
-        self.best_f = torch.where(feas, obj_b, torch.full_like(obj_b, -float("inf"))).amax(dim=-1)  # S
+        if bool(feas.any(dim=-1).all()):
+            infeasible_value = -float("inf")
+        else:  # acquisition/utils.py:137-152: no feasible baseline point in some sample -> 6-sigma lower bound
+            assert convex_weights is not None, "pass the 32 x n_b uniform draws of _estimate_objective_lower_bound"
+            infeasible_value = objective_lower_bound(models, X_baseline, convex_weights, obj_idx, self.obj_w)
+        self.best_f = torch.where(feas, obj_b, torch.full_like(obj_b, infeasible_value)).amax(dim=-1)  # S
 
     def _set_q(self, q: int) -> None:
         full = qmc.sobol_normal(d=(self.n_b + q) * self.m, n=self.S, seed=self.seed).view(self.S, self.n_b + q, self.m)

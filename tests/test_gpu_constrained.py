@@ -151,3 +151,38 @@ def test_multi_output_single_task_gp_is_the_list_of_its_outputs(cuda):
                      for k in range(2)]  # fmt: skip
     oracle = OracleConstrainedQLogNEI(oracle_models, X, cons, 1e-2, obj_idx=0, obj_weight=1.0, num_samples=32, seed=2)
     _check(cuda, a, oracle, Xt.cpu())
+
+
+def test_incumbent_with_and_without_feasible_baseline_points(cuda):
+    """test/acquisition/test_logei.py:701-727: with an always-feasible constraint the incumbent is the unconstrained best
+    objective; with a never-feasible one it is the 6-sigma lower bound of acquisition/utils.py:137-199 for every sample."""
+    import botorch_b200 as bb
+
+    X, ys, hy = _data(30, 3, seed=17)
+    feasible_con = lambda Z: -torch.ones_like(Z[..., 0])
+    infeasible_con = lambda Z: torch.ones_like(Z[..., 0])
+    acqf, oracle = _build(cuda, X, ys[:2], hy[:2], 32, seed=4, constraints=[feasible_con], eta=1e-2)
+    assert torch.equal(acqf._best_f, acqf.baseline_obj.amax(dim=-1))
+    assert rel_err(acqf._best_f, oracle.best_f, scale=1.0) < TOL
+
+    torch.cuda.manual_seed(123)
+    weights = torch.rand(32, 30, dtype=torch.float64, device=cuda).cpu()  # the draw _estimate_objective_lower_bound makes
+    torch.cuda.manual_seed(123)
+    import botorch_b200.constrained  # noqa: F401
+
+    gms = [bb.SingleTaskGP(X.to(cuda), y.unsqueeze(-1).to(cuda), lengthscale=h["ls"], noise=h["noise"], mean_constant=h["mean"])
+           for y, h in zip(ys[:2], hy[:2])]  # fmt: skip
+    torch.cuda.manual_seed(123)
+    acqf = bb.qLogNoisyExpectedImprovement(
+        bb.ModelListGP(*gms), X.to(cuda), sampler=bb.SobolQMCNormalSampler(torch.Size([32]), seed=4),
+        objective=bb.LinearMCObjective(torch.tensor([1.0, 0.0], dtype=torch.float64, device=cuda)),
+        constraints=[infeasible_con], eta=1e-2)  # fmt: skip
+    ogps = [OracleGP(X, y.unsqueeze(-1), GPHyper("rbf", h["ls"], torch.tensor(h["noise"], dtype=torch.float64),
+                                                 torch.tensor(h["mean"], dtype=torch.float64), None), standardize=True)
+            for y, h in zip(ys[:2], hy[:2])]  # fmt: skip
+    oracle = OracleConstrainedQLogNEI(ogps, X, [infeasible_con], 1e-2, obj_idx=0, obj_weight=1.0, num_samples=32, seed=4,
+                                      convex_weights=weights)  # fmt: skip
+    assert bool((acqf._best_f == acqf._best_f[0]).all()) and float(acqf._best_f[0]) <= 0.0
+    assert rel_err(acqf._best_f, oracle.best_f, scale=1.0) < TOL
+    Xc = torch.rand(4, 2, 3, dtype=torch.float64, generator=torch.Generator().manual_seed(3))
+    _check(cuda, acqf, oracle, Xc)
