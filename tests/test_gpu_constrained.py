@@ -186,3 +186,18 @@ def test_incumbent_with_and_without_feasible_baseline_points(cuda):
     assert rel_err(acqf._best_f, oracle.best_f, scale=1.0) < TOL
     Xc = torch.rand(4, 2, 3, dtype=torch.float64, generator=torch.Generator().manual_seed(3))
     _check(cuda, acqf, oracle, Xc)
+
+
+@pytest.mark.parametrize("q,B,S", [(12, 1, 7), (32, 2, 8), (1, 1, 1)])
+def test_constrained_edge_shapes(cuda, q, B, S):
+    """Wide q-batches (the QT = 16 / 32 instantiations of the reduction kernels), odd sample counts, a single sample, and
+    an input that is neither contiguous nor requires grad."""
+    X, ys, hy = _data(40, 3, seed=5)
+    cons = [lambda Z: Z[..., 1] - 0.9]
+    acqf, oracle = _build(cuda, X, ys[:2], hy[:2], S, seed=2, constraints=cons, eta=0.1)
+    Xc = torch.rand(B, q, 3, dtype=torch.float64, generator=torch.Generator().manual_seed(q))
+    _check(cuda, acqf, oracle, Xc)
+    wide = torch.rand(B, q, 6, dtype=torch.float64, generator=torch.Generator().manual_seed(1)).to(cuda)
+    view = wide[..., ::2]  # non-contiguous
+    with torch.no_grad():
+        assert rel_err(acqf(view), oracle.forward(view.cpu().contiguous()), scale=1.0) < TOL
