@@ -288,3 +288,57 @@ def optimize_acqf_sharded(
                                  options=gen_opts)  # fmt: skip
     cand, val, _ = gather_best(vals, cands, lo)
     return cand, val
+
+
+# ---- fully Bayesian fit: independent chains per rank (units that never interact) ------------------------------
+def nuts_sample_sharded(make_potential, dim: int, chains_per_rank: int, num_samples: int, warmup_steps: int, device,
+                        max_tree_depth: int = 6, seed: int = 0, init_radius: float = 2.0):
+    """Every rank runs ``chains_per_rank`` lockstep NUTS chains on its own device (seed offset by the rank, so the chains of
+    the job are distinct) and the draws are all-gathered: -> samples [num_samples x (world * chains_per_rank) x dim], chains
+    in rank order, identical on every rank.  ``make_potential(num_chains)`` builds the rank-local potential.  One collective
+    after the last draw; none inside the sampler."""
+    from .fully_bayesian import nuts_sample
+
+    rank, ws = world()
+    potential = make_potential(chains_per_rank)
+    gen = torch.Generator(device=device)
+    gen.manual_seed(int(seed) + 7919 * rank)
+    init = None
+    for _ in range(20):  # redraw the starting points whose energy is not finite (init_to_uniform, radius 2)
+        trial = 2.0 * init_radius * torch.rand(chains_per_rank, dim, generator=gen, device=device, dtype=torch.float64) - init_radius
+        init = trial if init is None else torch.where(torch.isfinite(potential(init)[0]).unsqueeze(-1), init, trial)
+        if bool(torch.isfinite(potential(init)[0]).all()):
+            break
+    samples, stats = nuts_sample(potential, init, num_samples, warmup_steps, max_tree_depth=max_tree_depth,
+                                 seed=int(seed) + 7919 * rank + 1)  # fmt: skip
+    if ws == 1:
+        return samples, stats
+    local = samples.transpose(0, 1).contiguous()  # chains x draws x dim: rank blocks concatenate along the chain axis
+    out = [torch.empty_like(local) for _ in range(ws)]
+    dist.all_gather(out, local)
+    return torch.cat(out, dim=0).transpose(0, 1).contiguous(), stats
+
+
+def fit_fully_bayesian_model_nuts_sharded(model, max_tree_depth: int = 6, warmup_steps: int = 512, num_samples: int = 256,
+                                          thinning: int = 16, chains_per_rank: int = 1, seed: int = 0) -> None:
+    """``fit_fully_bayesian_model_nuts`` with the chains spread over the ranks: each rank draws
+    ``num_samples // (world * chains_per_rank)`` samples per chain after its own warm-up, every rank loads the same thinned
+    ensemble (chain-major, rank order)."""
+    from .fully_bayesian import SaasPotential
+
+    _, ws = world()
+    X = model.train_inputs[0]
+    model.train()
+    holder = {}
+
+    def make(num_chains):
+        holder["p"] = SaasPotential(X, model.train_targets, num_chains=num_chains)
+        return holder["p"]
+
+    per_chain = max(num_samples // (ws * chains_per_rank), 1)
+    samples, stats = nuts_sample_sharded(make, X.shape[-1] + 4, chains_per_rank, per_chain, warmup_steps, X.device,
+                                         max_tree_depth=max_tree_depth, seed=seed)  # fmt: skip
+    kept = samples.transpose(0, 1).reshape(-1, samples.shape[-1])[::thinning]
+    model.load_mcmc_samples(holder["p"].constrain(kept))
+    model.eval()
+    model.nuts_stats = {**stats, "potential_evaluations": holder["p"].evaluations}

@@ -51,7 +51,16 @@ def _worker(rank: int, ws: int, port: int, outdir: str) -> None:
         # sharded optimize_acqf: both ranks return the same winner, close to the optimum
         cand, val = bdist.optimize_acqf_sharded(acq, bounds, q=2, num_restarts=6, raw_samples=32,
                                                 options={"seed": 0, "maxiter": 100})  # fmt: skip
-        torch.save({"cand": cand, "val": val}, os.path.join(outdir, f"r{rank}.pt"))
+        # NUTS chains sharded over the ranks: distinct chains per rank, one all-gather, same ensemble everywhere
+        mu = torch.tensor([1.0, -1.0], dtype=torch.float64)
+
+        def make_potential(num_chains):
+            return lambda z: (0.5 * ((z - mu) ** 2).sum(-1), z - mu)
+
+        draws, _ = bdist.nuts_sample_sharded(make_potential, 2, 3, num_samples=40, warmup_steps=60, device=torch.device("cpu"),
+                                             seed=5)  # fmt: skip
+        assert draws.shape == (40, 6, 2)
+        torch.save({"cand": cand, "val": val, "draws": draws}, os.path.join(outdir, f"r{rank}.pt"))
     finally:
         dist.destroy_process_group()
 
@@ -63,3 +72,7 @@ def test_world_size_2_gloo():
         a, b = torch.load(os.path.join(d, "r0.pt")), torch.load(os.path.join(d, "r1.pt"))
     assert torch.equal(a["cand"], b["cand"]) and torch.equal(a["val"], b["val"])
     assert torch.allclose(a["cand"], torch.tensor([0.25, 0.6, 0.9], dtype=torch.float64).expand(2, 3), atol=1e-4)
+    assert torch.equal(a["draws"], b["draws"])  # every rank holds the same gathered chains ...
+    chains = a["draws"].transpose(0, 1)
+    assert all(not torch.equal(chains[i], chains[j]) for i in range(6) for j in range(i))  # ... and the chains are distinct
+    assert float((a["draws"].reshape(-1, 2).mean(0) - torch.tensor([1.0, -1.0])).abs().max()) < 0.3
