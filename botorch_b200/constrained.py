@@ -156,9 +156,10 @@ class _ConstrainedFn(torch.autograd.Function):
         B, q, _ = Xd.shape
         N, S = B * q, acqf.S
         Zq = acqf._base_samples_q(q)
+        need_grad = bool(ctx.needs_input_grad[0])  # no-grad calls (raw samples) skip the backward's workspace regions
         works, views = [], []
         for k, nei in enumerate(acqf._neis):  # 1. cached-Cholesky samples of every output (fused pipeline, reductions ignored)
-            _, info, work = nei.forward(Xd, Zq[k], acqf.tau_relu, acqf.tau_max, with_grad=True)
+            _, info, work = nei.forward(Xd, Zq[k], acqf.tau_relu, acqf.tau_max, with_grad=need_grad)
             works.append(work)
             views.append(nei.samples_view(work, B, q))
         samples = torch.stack([v[:, :N] for v in views], dim=-1).reshape(S, B, q, len(views))
