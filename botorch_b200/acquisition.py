@@ -29,7 +29,7 @@ from . import engine
 from .exceptions import BotorchWarning, NumericalWarning, NumericsWarning, UnsupportedError
 from .posteriors import MCMC_DIM
 from .models import Model, _FusedExactGP
-from .sampling import MCSampler, SobolQMCNormalSampler, get_sampler
+from .sampling import MCSampler, get_sampler
 
 TAU_RELU = 1e-6  # logei.py:66
 TAU_MAX = 1e-2  # logei.py:67

@@ -16,7 +16,6 @@ by torch on the device between ``bo_mc_reduce_fwd`` / ``bo_mc_reduce_bwd``, whic
 """
 from __future__ import annotations
 
-import ctypes as C
 import math
 from typing import Callable, List, Optional, Sequence, Tuple, Union
 

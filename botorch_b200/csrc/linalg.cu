@@ -7,7 +7,6 @@
 // trailing updates are DMMA GEMMs (gemm.cu).
 #include "linalg.cuh"
 
-#include <cstdlib>
 
 namespace {
 

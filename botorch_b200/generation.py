@@ -19,7 +19,6 @@ k(X, x) plus two skinny GEMMs instead of the n^2-per-candidate triangular produc
 """
 from __future__ import annotations
 
-import ctypes as C
 from typing import Optional
 
 import torch

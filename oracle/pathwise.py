@@ -15,7 +15,6 @@ The random draws (W, w, eps) are inputs, produced by the reference's own generat
 """
 from __future__ import annotations
 
-import math
 from typing import Optional
 
 import torch
