@@ -21,6 +21,7 @@ from typing import Callable, List, Optional, Sequence, Tuple, Union
 
 import torch
 from torch import Tensor
+from torch.quasirandom import SobolEngine
 
 from . import _lib, engine
 from ._lib import check, pad8, ptr
@@ -148,6 +149,50 @@ def _one_outcome(objective, m: int) -> Tuple[int, float]:
     return int(nz[0]), float(w[nz[0]])
 
 
+def prune_inferior_points_list(model: ModelListGP, X: Tensor, objective, constraints=None, num_samples: int = 2048,
+                               max_frac: float = 1.0, sampler: Optional[MCSampler] = None) -> Tensor:  # fmt: skip
+    """``prune_inferior_points`` (acquisition/utils.py:245-349) over several independent outcomes: keep the points of ``X``
+    that are the best FEASIBLE one in at least one joint posterior sample.  One joint draw over the (points x outcomes)
+    block as the reference's sampler makes it; per outcome the n x n posterior covariance, its blocked Cholesky and the
+    root-times-base-samples GEMM run on the GPU; infeasible entries are set below the worst objective (:336-340)."""
+    if X.ndim > 2:
+        raise UnsupportedError("Batched inputs `X` are currently unsupported by prune_inferior_points")
+    if X.size(-2) == 0:
+        raise ValueError("X must have at least one point.")
+    if max_frac <= 0 or max_frac > 1.0:
+        raise ValueError(f"max_frac must take values in (0, 1], is {max_frac}")
+    m, n = model.num_outputs, X.size(-2)
+    obj_idx, obj_w = _one_outcome(objective, m)
+    max_points = math.ceil(max_frac * n)
+    if sampler is None:
+        cls = SobolQMCNormalSampler if n * m <= SobolEngine.MAXDIM else IIDNormalSampler
+        sampler = cls(sample_shape=torch.Size([num_samples]))
+    S = int(sampler.sample_shape[0])
+    if isinstance(sampler, SobolQMCNormalSampler):
+        z = draw_sobol_normal_samples(d=n * m, n=S, dtype=torch.float64, seed=sampler.seed)
+    else:
+        with manual_seed(seed=sampler.seed):
+            z = torch.randn(S, n * m, dtype=torch.float64)
+    z = z.view(S, n, m).to(X.device)
+    with torch.no_grad():
+        cols = []
+        for k, mod in enumerate(model.models):
+            post = mod.posterior(X)
+            base = z[..., k].reshape(torch.Size([S]) + post.base_sample_shape)
+            cols.append(post.rsample_from_base_samples(torch.Size([S]), base).reshape(S, n))
+        samples = torch.stack(cols, dim=-1)  # S x n x m
+        obj_vals = obj_w * samples[..., obj_idx]
+        infeas = ~compute_feasibility_indicator(constraints, samples)
+        if bool(infeas.any()):
+            obj_vals[infeas] = obj_vals.min() - 1
+        is_best = torch.argmax(obj_vals, dim=-1)
+    idcs, counts = torch.unique(is_best, return_counts=True)
+    if len(idcs) > max_points:  # (sic) the reference indexes by the sort order of the unique list here
+        counts, order_idcs = torch.sort(counts, descending=True)
+        idcs = order_idcs[:max_points]
+    return X[idcs]
+
+
 class _ConstrainedFn(torch.autograd.Function):
     @staticmethod
     def forward(ctx, X: Tensor, acqf: "qLogNEIModelList"):
@@ -241,12 +286,14 @@ class qLogNEIModelList(AcquisitionFunction):
                  fat: bool = True, prune_baseline: bool = False, cache_root: bool = True, tau_max: float = TAU_MAX,
                  tau_relu: float = TAU_RELU, marginalize_dim: Optional[int] = None) -> None:  # fmt: skip
         super().__init__(model=model)
-        if posterior_transform is not None or prune_baseline or marginalize_dim is not None:
-            raise UnsupportedError("posterior_transform / prune_baseline / marginalize_dim are not on the constrained fused path")
+        if posterior_transform is not None or marginalize_dim is not None:
+            raise UnsupportedError("posterior_transform / marginalize_dim are not on the constrained fused path")
         if X_baseline.dim() != 2:
             raise UnsupportedError("X_baseline must be r x d (one baseline set shared by all t-batches)")
         m = model.num_outputs
         self._obj_idx, self._obj_w = _one_outcome(objective, m)
+        if prune_baseline:  # logei.py:377-385
+            X_baseline = prune_inferior_points_list(model, X_baseline, objective, constraints=constraints)
         self.objective = objective
         self._constraints = list(constraints) if constraints else None
         self._eta, self._fat = eta, bool(fat)

@@ -16,13 +16,13 @@ restatements against them (and against literals minted from them, for machines w
 from __future__ import annotations
 
 import math
-from typing import Optional, Callable, List, Sequence
+from typing import Callable, List, Optional, Sequence
 
 import torch
 from torch import Tensor
 
 from . import qmc, safe_math
-from .gp import OracleGP
+from .gp import OracleGP, psd_safe_cholesky
 from .qlognei import TAU_MAX, TAU_RELU, OracleQLogNEI
 
 _INV_SQRT_3 = math.sqrt(1 / 3)
@@ -55,6 +55,29 @@ def smoothed_log_feasibility(constraints, samples: Tensor, eta: Sequence[float],
     for c, e in zip(constraints, eta):
         out = out + f(-c(samples) / e)
     return out
+
+
+def prune_inferior_points(models, X: Tensor, constraints, obj_idx: int, obj_w: float, num_samples: int, seed: int,
+                          max_frac: float = 1.0) -> Tensor:
+    """acquisition/utils.py:245-349 for m independent outcomes: indices (into X) of the points that are the best feasible
+    one in at least one joint posterior sample; Sobol base samples over the (points x outcomes) block."""
+    n, m = X.shape[0], len(models)
+    z = qmc.sobol_normal(d=n * m, n=num_samples, seed=seed).view(num_samples, n, m)
+    cols = []
+    for k, gp in enumerate(models):
+        mean, cov = gp.posterior(X)
+        root = psd_safe_cholesky(cov)
+        cols.append(mean + torch.einsum("ij,sj->si", root, z[..., k]))
+    samples = torch.stack(cols, dim=-1)
+    obj = obj_w * samples[..., obj_idx]
+    infeas = ~feasibility(constraints, samples)
+    if bool(infeas.any()):
+        obj[infeas] = obj.min() - 1
+    idcs, counts = torch.unique(torch.argmax(obj, dim=-1), return_counts=True)
+    if len(idcs) > math.ceil(max_frac * n):
+        counts, order = torch.sort(counts, descending=True)
+        idcs = order[: math.ceil(max_frac * n)]
+    return idcs
 
 
 def objective_lower_bound(models, X: Tensor, convex_weights: Tensor, obj_idx: int, obj_w: float) -> float:

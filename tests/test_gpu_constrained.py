@@ -201,3 +201,35 @@ def test_constrained_edge_shapes(cuda, q, B, S):
     view = wide[..., ::2]  # non-contiguous
     with torch.no_grad():
         assert rel_err(acqf(view), oracle.forward(view.cpu().contiguous()), scale=1.0) < TOL
+
+
+def test_prune_baseline_over_several_outcomes(cuda):
+    """prune_inferior_points with constraints over a model list: the kept index set equals the oracle's (same Sobol draw over
+    the points x outcomes block), and `prune_baseline=True` builds the acquisition on the pruned set."""
+    import botorch_b200 as bb
+    from botorch_b200.constrained import prune_inferior_points_list
+    from oracle.constrained import prune_inferior_points as oracle_prune
+
+    X, ys, hy = _data(60, 3, seed=23)
+    cons = [lambda Z: Z[..., 1] - 0.3]
+    gms = [bb.SingleTaskGP(X.to(cuda), y.unsqueeze(-1).to(cuda), lengthscale=h["ls"], noise=h["noise"], mean_constant=h["mean"])
+           for y, h in zip(ys[:2], hy[:2])]  # fmt: skip
+    ogps = [OracleGP(X, y.unsqueeze(-1), GPHyper("rbf", h["ls"], torch.tensor(h["noise"], dtype=torch.float64),
+                                                 torch.tensor(h["mean"], dtype=torch.float64), None), standardize=True)
+            for y, h in zip(ys[:2], hy[:2])]  # fmt: skip
+    model = bb.ModelListGP(*gms)
+    obj = bb.LinearMCObjective(torch.tensor([1.0, 0.0], dtype=torch.float64, device=cuda))
+    for max_frac in (1.0, 0.05):
+        kept = prune_inferior_points_list(model, X.to(cuda), obj, constraints=cons, max_frac=max_frac,
+                                          sampler=bb.SobolQMCNormalSampler(torch.Size([256]), seed=9))  # fmt: skip
+        idx = oracle_prune(ogps, X, cons, 0, 1.0, num_samples=256, seed=9, max_frac=max_frac)
+        assert torch.equal(kept.cpu(), X[idx]) and 0 < kept.shape[0] < 60
+    with pytest.raises(ValueError):
+        prune_inferior_points_list(model, X.to(cuda), obj, max_frac=0.0)
+    acqf = bb.qLogNoisyExpectedImprovement(model, X.to(cuda), sampler=bb.SobolQMCNormalSampler(torch.Size([32]), seed=1),
+                                           objective=obj, constraints=cons, eta=1e-2, prune_baseline=True)  # fmt: skip
+    assert acqf.X_baseline.shape[0] < 60
+    pruned = acqf.X_baseline.cpu()
+    oracle = OracleConstrainedQLogNEI(ogps, pruned, cons, 1e-2, obj_idx=0, obj_weight=1.0, num_samples=32, seed=1)
+    Xc = torch.rand(3, 2, 3, dtype=torch.float64, generator=torch.Generator().manual_seed(8))
+    _check(cuda, acqf, oracle, Xc)
