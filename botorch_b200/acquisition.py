@@ -424,6 +424,14 @@ class qNoisyExpectedImprovement(qLogNoisyExpectedImprovement):
 
     _log = False
 
+    def __new__(cls, model=None, *args, **kwargs):
+        if cls is qNoisyExpectedImprovement:
+            from .constrained import ModelListGP, qNEIModelList
+
+            if isinstance(model, ModelListGP):
+                return qNEIModelList(model, *args, **kwargs)
+        return object.__new__(cls)
+
     def __init__(
         self,
         model: Model,

@@ -219,7 +219,7 @@ class _ConstrainedFn(torch.autograd.Function):
         Fobj = views[acqf._obj_idx]
         lib = _lib.lib()
         check(lib.bo_mc_reduce_fwd(acqf._ctx, S, B, q, Fobj.stride(0), ptr_view(Fobj), ptr(lw), ptr(acqf._best_f),
-                                   acqf._obj_w, acqf.tau_relu, acqf.tau_max, engine.REDUCE_LOG, ptr(acq), ptr(lse),
+                                   acqf._obj_w, acqf.tau_relu, acqf.tau_max, acqf._reduction, ptr(acq), ptr(lse),
                                    _lib.stream_ptr(Xd.device)))  # fmt: skip
         ctx.acqf, ctx.works, ctx.views, ctx.Zq = acqf, works, views, Zq
         ctx.lw, ctx.lse, ctx.in_dtype = lw, lse, X.dtype
@@ -242,7 +242,7 @@ class _ConstrainedFn(torch.autograd.Function):
             lw_arg = ctx.lw if ldn == Fobj.stride(0) else torch.nn.functional.pad(ctx.lw, (0, Fobj.stride(0) - ldn))
         lib = _lib.lib()
         check(lib.bo_mc_reduce_bwd(acqf._ctx, S, B, q, Fobj.stride(0), ptr_view(Fobj), ptr(lw_arg), ptr(acqf._best_f),
-                                   acqf._obj_w, acqf.tau_relu, acqf.tau_max, engine.REDUCE_LOG, ptr(ctx.lse),
+                                   acqf._obj_w, acqf.tau_relu, acqf.tau_max, acqf._reduction, ptr(ctx.lse),
                                    ptr(grad_acq.to(torch.float64).contiguous()), ptr(dF), ptr(lw_bar),
                                    _lib.stream_ptr(dev)))  # fmt: skip
         gs = None
@@ -279,6 +279,7 @@ class qLogNEIModelList(AcquisitionFunction):
     ``qLogNoisyExpectedImprovement(model_list, X_baseline, objective=..., constraints=[...])`` constructs)."""
 
     _log = True
+    _reduction = engine.REDUCE_LOG
 
     def __init__(self, model: ModelListGP, X_baseline: Tensor, sampler: Optional[MCSampler] = None, objective=None,
                  posterior_transform=None, X_pending: Optional[Tensor] = None,
@@ -310,7 +311,7 @@ class qLogNEIModelList(AcquisitionFunction):
         n_b = X_baseline.shape[0]
         self._Zb = self._draw(n_b, m)  # S x n_b x m: one draw over the (points x outcomes) block, like the reference
         Xb = self.X_baseline.to(dev)
-        self._neis = [engine.NEIState(gp, Xb, self._Zb[:, :, k].to(dev).contiguous(), reduction=engine.REDUCE_LOG,
+        self._neis = [engine.NEIState(gp, Xb, self._Zb[:, :, k].to(dev).contiguous(), reduction=self._reduction,
                                       obj_weight=(self._obj_w if k == self._obj_idx else 1.0)) for k, gp in enumerate(gps)]  # fmt: skip
         self._Zq_cache = {}
         # incumbent: best FEASIBLE objective over the baseline samples of all outcomes (acquisition/utils.py:90-163)
@@ -368,3 +369,24 @@ class qLogNEIModelList(AcquisitionFunction):
         if Xf.device != self._neis[0].device:
             raise _lib.BoError(f"X is on {Xf.device}; the acquisition function lives on {self._neis[0].device}. No CPU path.")
         return _ConstrainedFn.apply(Xf, self).reshape(batch_shape)
+
+
+class qNEIModelList(qLogNEIModelList):
+    """``qNoisyExpectedImprovement(model_list, X_baseline, objective=..., constraints=[...])`` (acquisition/monte_carlo.py:
+    417-620 with ``_apply_constraints`` :305-330): relu improvement times the sigmoid feasibility weights, ``amax`` over q,
+    plain mean over the samples -- the BO_REDUCE_PLAIN branch of the same reduction kernels.  ``prune_baseline`` defaults to
+    True and the weights are plain sigmoids (``fat=False``) as in the reference."""
+
+    _log = False
+    _reduction = engine.REDUCE_PLAIN
+
+    def __init__(self, model: ModelListGP, X_baseline: Tensor, sampler: Optional[MCSampler] = None, objective=None,
+                 posterior_transform=None, X_pending: Optional[Tensor] = None, prune_baseline: bool = True,
+                 cache_root: bool = True, constraints=None, eta: Union[Tensor, float] = 1e-3,
+                 marginalize_dim: Optional[int] = None) -> None:  # fmt: skip
+        from .acquisition import legacy_ei_numerics_warning
+
+        legacy_ei_numerics_warning("qNoisyExpectedImprovement")
+        super().__init__(model, X_baseline, sampler=sampler, objective=objective, posterior_transform=posterior_transform,
+                         X_pending=X_pending, constraints=constraints, eta=eta, fat=False, prune_baseline=prune_baseline,
+                         cache_root=cache_root, marginalize_dim=marginalize_dim)  # fmt: skip

@@ -97,7 +97,8 @@ class OracleConstrainedQLogNEI:
 
     def __init__(self, models: List[OracleGP], X_baseline: Tensor, constraints: List[Callable[[Tensor], Tensor]], eta,
                  obj_idx: int = 0, obj_weight: float = 1.0, num_samples: int = 64, seed: int = 1234, fat: bool = True,
-                 tau_relu: float = TAU_RELU, tau_max: float = TAU_MAX, convex_weights: Optional[Tensor] = None):  # fmt: skip
+                 tau_relu: float = TAU_RELU, tau_max: float = TAU_MAX, convex_weights: Optional[Tensor] = None, plain: bool = False):  # fmt: skip
+        self.plain = plain
         self.m, self.S, self.seed = len(models), num_samples, seed
         self.constraints = constraints
         # utils/objective.py:167-168: a float eta becomes torch.full((n,), eta) in the DEFAULT dtype (float32 unless the caller
@@ -141,6 +142,10 @@ class OracleConstrainedQLogNEI:
             X = X.unsqueeze(0)
         smp = self.samples(X)
         obj = self.obj_w * smp[..., self.obj_idx]
+        if self.plain:  # qNEI (monte_carlo.py:305-330, 417-620): relu improvement times the feasibility weights, amax, mean
+            imp = (obj - self.best_f.view(self.S, 1, 1)).clamp_min(0)
+            imp = imp * smoothed_log_feasibility(self.constraints, smp, self.eta, self.fat).exp()
+            return imp.amax(dim=-1).mean(dim=0)
         li = safe_math.log_improvement(obj, self.best_f.view(self.S, 1), tau=self.tau_relu)
         li = li + smoothed_log_feasibility(self.constraints, smp, self.eta, self.fat)
         return safe_math.logmeanexp(safe_math.fatmax(li, dim=-1, tau=self.tau_max), dim=0)

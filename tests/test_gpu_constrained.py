@@ -233,3 +233,38 @@ def test_prune_baseline_over_several_outcomes(cuda):
     oracle = OracleConstrainedQLogNEI(ogps, pruned, cons, 1e-2, obj_idx=0, obj_weight=1.0, num_samples=32, seed=1)
     Xc = torch.rand(3, 2, 3, dtype=torch.float64, generator=torch.Generator().manual_seed(8))
     _check(cuda, acqf, oracle, Xc)
+
+
+def test_constrained_qnei_matches_oracle(cuda):
+    """qNoisyExpectedImprovement over a model list with constraints: relu improvement x sigmoid weights, amax, mean.  The
+    baseline is a small subset of the training inputs, so that candidates do improve on the incumbent."""
+    import warnings
+
+    import botorch_b200 as bb
+
+    X, ys, hy = _data(50, 3, seed=31)
+    cons = [lambda Z: Z[..., 1] - 0.7]
+    eta = torch.tensor([0.2], dtype=torch.float64)
+    Xb = X[ys[0].argsort()[:8]]  # the eight worst observed points
+    gms = [bb.SingleTaskGP(X.to(cuda), y.unsqueeze(-1).to(cuda), lengthscale=h["ls"], noise=h["noise"], mean_constant=h["mean"])
+           for y, h in zip(ys[:2], hy[:2])]  # fmt: skip
+    with warnings.catch_warnings():
+        warnings.simplefilter("ignore")
+        acqf = bb.qNoisyExpectedImprovement(
+            bb.ModelListGP(*gms), Xb.to(cuda), sampler=bb.SobolQMCNormalSampler(torch.Size([64]), seed=6),
+            objective=bb.LinearMCObjective(torch.tensor([1.0, 0.0], dtype=torch.float64, device=cuda)), constraints=cons,
+            eta=eta, prune_baseline=False)  # fmt: skip
+    assert type(acqf).__name__ == "qNEIModelList" and not acqf._log
+    ogps = [OracleGP(X, y.unsqueeze(-1), GPHyper("rbf", h["ls"], torch.tensor(h["noise"], dtype=torch.float64),
+                                                 torch.tensor(h["mean"], dtype=torch.float64), None), standardize=True)
+            for y, h in zip(ys[:2], hy[:2])]  # fmt: skip
+    oracle = OracleConstrainedQLogNEI(ogps, Xb, cons, eta, obj_idx=0, obj_weight=1.0, num_samples=64, seed=6, fat=False,
+                                      plain=True)  # fmt: skip
+    Xc = torch.rand(6, 3, 3, dtype=torch.float64, generator=torch.Generator().manual_seed(4))
+    Xg = Xc.to(cuda).requires_grad_(True)
+    val = acqf(Xg)
+    (grad,) = torch.autograd.grad(val.sum(), Xg)
+    oval, ograd = oracle.value_and_grad(Xc)
+    assert bool((oval > 0).any())  # a non-trivial case: some candidates improve
+    assert rel_err(val, oval, scale=float(oval.abs().max())) < TOL
+    assert rel_err(grad, ograd, scale=float(ograd.abs().max())) < TOL
