@@ -25,7 +25,7 @@ from torch.quasirandom import SobolEngine
 
 from . import _lib, engine
 from ._lib import check, pad8, ptr
-from .acquisition import DEFAULT_MC_SAMPLES, TAU_MAX, TAU_RELU, AcquisitionFunction, LinearMCObjective
+from .acquisition import DEFAULT_MC_SAMPLES, TAU_MAX, TAU_RELU, AcquisitionFunction, LinearMCObjective, _FusedImprovementBase
 from .exceptions import UnsupportedError
 from .models import Model, _FusedExactGP
 from .sampling import IIDNormalSampler, MCSampler, SobolQMCNormalSampler, draw_sobol_normal_samples, manual_seed
@@ -201,11 +201,14 @@ class _ConstrainedFn(torch.autograd.Function):
         N, S = B * q, acqf.S
         Zq = acqf._base_samples_q(q)
         need_grad = bool(ctx.needs_input_grad[0])  # no-grad calls (raw samples) skip the backward's workspace regions
-        works, views = [], []
+        works, views, infos = [], [], []
         for k, nei in enumerate(acqf._neis):  # 1. cached-Cholesky samples of every output (fused pipeline, reductions ignored)
             _, info, work = nei.forward(Xd, Zq[k], acqf.tau_relu, acqf.tau_max, with_grad=need_grad)
             works.append(work)
+            infos.append(info.reshape(-1))
             views.append(nei.samples_view(work, B, q))
+        # jitter / failed q x q roots of any outcome are reported like the fused path does: (min, max) of the flags, deferred
+        acqf._warn_on_failures(torch.stack(torch.aminmax(torch.cat(infos))).to(torch.int32))
         samples = torch.stack([v[:, :N] for v in views], dim=-1).reshape(S, B, q, len(views))
         ldn = pad8(N)
         lw = None
@@ -280,6 +283,9 @@ class qLogNEIModelList(AcquisitionFunction):
 
     _log = True
     _reduction = engine.REDUCE_LOG
+    _info_host, _info_event, _info_pending = None, None, False
+    _warn_on_failures = _FusedImprovementBase._warn_on_failures
+    check_numerics = _FusedImprovementBase.check_numerics
 
     def __init__(self, model: ModelListGP, X_baseline: Tensor, sampler: Optional[MCSampler] = None, objective=None,
                  posterior_transform=None, X_pending: Optional[Tensor] = None,

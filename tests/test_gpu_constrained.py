@@ -268,3 +268,27 @@ def test_constrained_qnei_matches_oracle(cuda):
     assert bool((oval > 0).any())  # a non-trivial case: some candidates improve
     assert rel_err(val, oval, scale=float(oval.abs().max())) < TOL
     assert rel_err(grad, ograd, scale=float(ograd.abs().max())) < TOL
+
+
+def test_constrained_path_reports_the_jitter_warning(cuda):
+    """A candidate on a training point makes the q x q Schur block of every outcome singular: the jitter schedule runs in the
+    kernels and check_numerics() reports it, as on the single-model path."""
+    import warnings
+
+    import botorch_b200 as bb
+
+    X, ys, hy = _data(30, 3, seed=2)
+    gms = [bb.SingleTaskGP(X.to(cuda), y.unsqueeze(-1).to(cuda), lengthscale=h["ls"], noise=1e-4, mean_constant=h["mean"])
+           for y, h in zip(ys[:2], hy[:2])]  # fmt: skip
+    acqf = bb.qLogNoisyExpectedImprovement(
+        bb.ModelListGP(*gms), X.to(cuda), sampler=bb.SobolQMCNormalSampler(torch.Size([16]), seed=0),
+        objective=bb.LinearMCObjective(torch.tensor([1.0, 0.0], dtype=torch.float64, device=cuda)),
+        constraints=[lambda Z: Z[..., 1] - 0.9], eta=0.1)  # fmt: skip
+    Xc = X[:2].clone().unsqueeze(0).to(cuda)  # two candidates sitting on training points
+    Xc[0, 1] = Xc[0, 0]  # ... and on each other
+    with warnings.catch_warnings(record=True) as caught:
+        warnings.simplefilter("always")
+        val = acqf(Xc)
+        acqf.check_numerics()
+    assert bool(torch.isfinite(val).all()) or bool(torch.isneginf(val).all())
+    assert any(issubclass(w.category, (bb.exceptions.NumericalWarning, bb.exceptions.BotorchWarning)) for w in caught)
