@@ -241,6 +241,7 @@ def test_sequential_greedy_optimize_acqf(cuda):
     model = _model(p, cuda)
     acqf = _acqf(p, model, cuda)
     bounds = torch.stack([torch.zeros(p.d), torch.ones(p.d)]).double().to(cuda)
+    torch.manual_seed(0)  # initialize_q_batch selects restarts with torch.multinomial on the global RNG (initializers.py:946)
     cands, vals = bb.optimize_acqf(acqf, bounds, q=3, num_restarts=4, raw_samples=64, sequential=True,
                                    options={"maxiter": 20, "seed": 0})  # fmt: skip
     assert cands.shape == (3, p.d) and vals.shape == (3,) and acqf.X_pending is None
