@@ -144,6 +144,8 @@ def _declare(lib: C.CDLL) -> None:
     lib.bo_argmax.argtypes = [vp, i64, vp, vp, vp, vp]
     lib.bo_dgemm.argtypes = [vp, i32, i32, i32, i32, dbl, vp, i64, i64, vp, i64, i64, dbl, vp, i64, i64, i32, vp]
     lib.bo_kernel_matrix.argtypes = [vp, gp, i64, vp, vp, vp, sz, vp]
+    lib.bo_kernel_matrix_static.argtypes = [vp, gp, i64, vp, vp, vp]
+    lib.bo_kernel_matrix_static.restype = i32
     lib.bo_potrf_workspace_bytes.restype = sz
     lib.bo_potrf_workspace_bytes.argtypes = [i32, i32]
     lib.bo_potrf.argtypes = [vp, i32, i32, vp, i64, i64, vp, vp, sz, vp, vp]

@@ -14,7 +14,7 @@ import sys
 
 CSRC = os.path.join(os.path.dirname(os.path.abspath(__file__)), "csrc")
 LIB_PATH = os.path.join(CSRC, "libbotorch_b200.so")
-SOURCES = ["gemm.cu", "linalg.cu", "cand.cu", "api.cu", "lbfgs.cu"]
+SOURCES = ["gemm.cu", "linalg.cu", "cand.cu", "api.cu", "lbfgs.cu", "noalloc.cu"]
 HEADERS = ["common.cuh", "linalg.cuh", "cand.cuh", os.path.join("..", "..", "include", "botorch_b200.h")]
 NVCC_FLAGS = [
     "-gencode",

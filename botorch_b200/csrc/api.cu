@@ -120,6 +120,9 @@ const char* bo_strerror(int code) {
         case BO_ERR_CUDA: return "CUDA runtime error (see bo_last_cuda_error)";
         case BO_ERR_WORKSPACE: return "workspace too small";
         case BO_ERR_UNSUPPORTED: return "unsupported size (q > 32, d > 128 or grid limit)";
+        case BO_ERR_STATIC_SCRATCH:
+            return "problem exceeds the built-in scratch of the *_static entry point (M * kp(d) * pad8(Nc) > "
+                   "BO_STATIC_SCRATCH_DOUBLES = 65536 doubles); use the workspace-taking entry point";
         default: return "unknown error";
     }
 }

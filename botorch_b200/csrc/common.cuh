@@ -9,6 +9,7 @@
 #define BO_ERR_CUDA 2
 #define BO_ERR_WORKSPACE 3
 #define BO_ERR_UNSUPPORTED 4
+#define BO_ERR_STATIC_SCRATCH 5
 
 #define BO_MAX_Q 32   // largest q-batch (incl. pending points) the per-candidate kernels accept
 #define BO_MAX_D 128  // largest input dimension

@@ -29,6 +29,7 @@ extern "C" {
 #define BO_ERR_CUDA 2
 #define BO_ERR_WORKSPACE 3
 #define BO_ERR_UNSUPPORTED 4
+#define BO_ERR_STATIC_SCRATCH 5 /* problem larger than the built-in scratch of a *_static entry point */
 
 #define BO_KERNEL_RBF 0      /* gpytorch RBFKernel (ARD), models/utils/gpytorch_modules.py:100-127 */
 #define BO_KERNEL_MATERN52 1 /* gpytorch MaternKernel(nu=2.5, ARD), models/fully_bayesian.py:81-85,275-282 */
@@ -302,6 +303,21 @@ int bo_kernel_matrix(bo_ctx* ctx, const bo_gp* gp, long Nc, const double* Xc, do
 int bo_potrf(bo_ctx* ctx, int n, int batch, double* A, long lda, long strideA, double* inv /* or NULL */,
              void* work, size_t work_bytes, int32_t* info, void* stream);
 size_t bo_potrf_workspace_bytes(int n, int batch);
+
+/* bo_kernel_matrix without a workspace argument.  NO COUNTERPART IN THE REFERENCE: added
+ * for callers that cannot allocate (code under CUDA-graph capture, tight serving loops, harnesses that forbid
+ * cudaMalloc).  Same kernels and bit-identical output to bo_kernel_matrix; the augmented candidate operand
+ * [M][bo_kp(d) x bo_pad8(Nc)] lives in a file-scope device array of BO_STATIC_SCRATCH_DOUBLES doubles (512 KiB, held by
+ * every GPU that loads the library until the process exits) instead of caller memory.  The call allocates nothing
+ * (no cudaMalloc / cudaFree / allocating library routine).  Limits and rules:
+ *   - M * bo_kp(d) * bo_pad8(Nc) <= BO_STATIC_SCRATCH_DOUBLES, else BO_ERR_STATIC_SCRATCH (e.g. d = 20, M = 1: Nc <= 2728);
+ *   - the device that owns `out` must be the current device (its copy of the array is used), else BO_ERR_INVALID;
+ *   - every call on a device shares the one array: calls that overlap on the GPU (different streams, or graph branches
+ *     without a dependency) RACE -- serialise them.  The array keeps the previous call's contents; the call overwrites all
+ *     of the region it uses, so nothing needs clearing in between.
+ * out [M][n x bo_pad8(Nc)] as for bo_kernel_matrix. */
+#define BO_STATIC_SCRATCH_DOUBLES (64 * 1024)
+int bo_kernel_matrix_static(bo_ctx* ctx, const bo_gp* gp, long Nc, const double* Xc, double* out, void* stream);
 
 /* ---- device-resident multi-start optimiser ---------------------------------------
  * Replaces the SciPy L-BFGS-B round trip of gen_candidates_scipy (generation/gen.py:46-298) for the fused path: the
