@@ -25,11 +25,43 @@ import torch.distributed as dist
 from torch import Tensor
 
 
+_GROUP = None  # process group the sharding functions run over (None: the default group)
+
+
+class use_group:
+    """Context manager: run the sharding functions of this module over a sub-group of the job's ranks (e.g. the first N
+    GPUs of the box).  Only the members may call them inside the context; ``src`` arguments are ranks WITHIN the group."""
+
+    def __init__(self, group) -> None:
+        self.group, self.prev = group, None
+
+    def __enter__(self):
+        global _GROUP
+        self.prev, _GROUP = _GROUP, self.group
+        return self.group
+
+    def __exit__(self, *exc) -> None:
+        global _GROUP
+        _GROUP = self.prev
+
+
 def world() -> Tuple[int, int]:
-    """(rank, world_size); (0, 1) without an initialised process group."""
+    """(rank, world_size) in the active group; (0, 1) without an initialised process group."""
     if dist.is_available() and dist.is_initialized():
-        return dist.get_rank(), dist.get_world_size()
+        return dist.get_rank(_GROUP), dist.get_world_size(_GROUP)
     return 0, 1
+
+
+def _backend() -> str:
+    return dist.get_backend(_GROUP)
+
+
+def _bcast(t: Tensor, src: int) -> None:
+    dist.broadcast(t, src=src if _GROUP is None else dist.get_global_rank(_GROUP, src), group=_GROUP)
+
+
+def _all_gather(out: List[Tensor], t: Tensor) -> None:
+    dist.all_gather(out, t, group=_GROUP)
 
 
 def shard_range(total: int, rank: int, world_size: int) -> Tuple[int, int]:
@@ -39,21 +71,69 @@ def shard_range(total: int, rank: int, world_size: int) -> Tuple[int, int]:
     return lo, lo + base + (1 if rank < extra else 0)
 
 
-def broadcast_buffers(buffers: List[Tensor], src: int = 0) -> int:
-    """Broadcast every buffer in place from ``src``; returns the payload in bytes."""
-    nbytes = 0
+def warm_up(device=None) -> None:
+    """Bring the communicator up (NCCL creates its channels lazily on the first collective: ~1 s on an 8-GPU box) so that
+    the first acquisition does not pay for it.  Call once after ``init_process_group``."""
     _, ws = world()
+    if ws == 1:
+        return
+    t = torch.zeros(1, dtype=torch.float64, device=device if _backend() == "nccl" else "cpu")
+    dist.all_reduce(t, group=_GROUP)
+    _bcast(t, 0)
+    if t.is_cuda:
+        torch.cuda.synchronize(t.device)
+
+
+def shared_seed(seed: Optional[int], device=None) -> Optional[int]:
+    """The seed every rank must agree on.  A given seed is returned as is; ``None`` means "draw one", which has to happen on
+    ONE rank (rank 0, from its global RNG like the reference's samplers do) and be broadcast -- otherwise every rank would
+    scramble its own Sobol sequence and the gathered values would belong to different points."""
+    rank, ws = world()
+    if seed is not None or ws == 1:
+        return seed
+    t = torch.randint(0, 2**31 - 1, (1,), dtype=torch.int64)
+    if _backend() == "nccl":
+        t = t.to(device if device is not None else torch.device("cuda", torch.cuda.current_device()))
+    _bcast(t, 0)
+    return int(t.item())
+
+
+def broadcast_buffers(buffers: List[Tensor], src: int = 0) -> int:
+    """Broadcast every buffer in place from ``src``; returns the payload in bytes.
+
+    The buffers are packed into ONE contiguous allocation per dtype and sent with a single collective (one NCCL launch
+    instead of ~25 blocking ones; the two extra device copies cost 2 x payload / HBM bandwidth, ~0.15 ms for the 0.4 GB of
+    config C3)."""
+    nbytes = sum(b.numel() * b.element_size() for b in buffers)
+    rank, ws = world()
+    if ws == 1 or not buffers:
+        return nbytes
+    by_dtype = {}
     for b in buffers:
-        nbytes += b.numel() * b.element_size()
-        if ws > 1:
-            dist.broadcast(b, src=src)
+        by_dtype.setdefault(b.dtype, []).append(b)
+    for group in by_dtype.values():
+        if len(group) == 1:
+            _bcast(group[0], src)
+            continue
+        total = sum(b.numel() for b in group)
+        flat = torch.empty(total, dtype=group[0].dtype, device=group[0].device)
+        if rank == src:
+            torch.cat([b.reshape(-1) for b in group], out=flat)
+        _bcast(flat, src)
+        if rank != src:
+            off = 0
+            for b in group:
+                b.copy_(flat[off : off + b.numel()].view_as(b))
+                off += b.numel()
     return nbytes
 
 
-def replicate_model(model, src: int = 0) -> int:
-    """Factor the training set on ``src`` only and broadcast the factors (K2 of SURVEY.md: once per model)."""
+def replicate_model(model, src: int = 0, factor_mode: str = "broadcast") -> int:
+    """Factor the training set on ``src`` only and broadcast the factors (K2 of SURVEY.md: once per model).
+    ``factor_mode="recompute"``: every rank factors its own copy instead (the kernels are deterministic, so the factors
+    are bit-identical on every rank; no transfer at all -- cheaper than any broadcast while n is a few thousand)."""
     rank, ws = world()
-    if ws == 1:
+    if ws == 1 or factor_mode == "recompute":
         model.gp_state
         return 0
     model.eval()
@@ -61,19 +141,30 @@ def replicate_model(model, src: int = 0) -> int:
     return broadcast_buffers(model._state.factor_buffers(), src)
 
 
-def make_qlognei(model, X_baseline: Tensor, sampler=None, src: int = 0, **kwargs):
+def make_qlognei(model, X_baseline: Tensor, sampler=None, src: int = 0, factor_mode: str = "broadcast", **kwargs):
     """qLogNoisyExpectedImprovement whose baseline state is computed on ``src`` and broadcast.
 
     Returns (acquisition function, broadcast bytes).  Base samples are drawn on every rank from the same seed
-    (host SobolEngine), so only factors travel.
+    (host SobolEngine), so only factors travel; with ``sampler=None`` the seed is drawn on rank 0 and broadcast.
     """
-    from .acquisition import qLogNoisyExpectedImprovement
+    from .acquisition import DEFAULT_MC_SAMPLES, qLogNoisyExpectedImprovement
+    from .sampling import SobolQMCNormalSampler
 
     rank, ws = world()
-    nbytes = replicate_model(model, src)
-    acqf = qLogNoisyExpectedImprovement(model, X_baseline, sampler=sampler, _factor_setup=(ws == 1 or rank == src),
-                                        **kwargs)  # fmt: skip
-    if ws > 1:
+    nbytes = replicate_model(model, src, factor_mode)
+    if ws > 1 and sampler is None:
+        sampler = SobolQMCNormalSampler(sample_shape=torch.Size([DEFAULT_MC_SAMPLES]),
+                                        seed=shared_seed(None, X_baseline.device))  # fmt: skip
+    elif ws > 1 and getattr(sampler, "seed", None) is not None:
+        # a sampler constructed without a seed drew its own on every rank: adopt rank 0's
+        t = torch.tensor([int(sampler.seed)], dtype=torch.int64)
+        if _backend() == "nccl":
+            t = t.to(X_baseline.device)
+        _bcast(t, src)
+        sampler.seed = int(t.item())
+    local_setup = ws == 1 or rank == src or factor_mode == "recompute"
+    acqf = qLogNoisyExpectedImprovement(model, X_baseline, sampler=sampler, _factor_setup=local_setup, **kwargs)
+    if ws > 1 and factor_mode != "recompute":
         nbytes += broadcast_buffers(acqf._nei.factor_buffers(), src)
         acqf._refresh_baseline_views()
     return acqf, nbytes
@@ -89,7 +180,7 @@ def all_gather_blocks(local: Tensor, total: int) -> Tensor:
     pad = torch.zeros(width, *local.shape[1:], dtype=local.dtype, device=local.device)
     pad[: local.shape[0]] = local
     out = [torch.empty_like(pad) for _ in range(ws)]
-    dist.all_gather(out, pad)
+    _all_gather(out, pad)
     return torch.cat([o[: hi - lo] for o, (lo, hi) in zip(out, sizes)], dim=0)
 
 
@@ -102,7 +193,7 @@ def sharded_raw_sample_values(acq_function, X_rnd: Tensor, device, batch_limit: 
     y_local = evaluate_raw_samples(acq_function, X_rnd[lo:hi], device, batch_limit)
     if ws == 1:
         return y_local
-    backend = dist.get_backend()
+    backend = _backend()
     y_dev = y_local.to(device) if backend == "nccl" else y_local
     return all_gather_blocks(y_dev, X_rnd.shape[0]).cpu()
 
@@ -129,9 +220,9 @@ def gather_best(values: Tensor, candidates: Tensor, index_offset: int) -> Tuple[
     vals = [torch.empty_like(best_val) for _ in range(ws)]
     idxs = [torch.empty_like(best_idx) for _ in range(ws)]
     cands = [torch.empty_like(best_cand) for _ in range(ws)]
-    dist.all_gather(vals, best_val)
-    dist.all_gather(idxs, best_idx)
-    dist.all_gather(cands, best_cand)
+    _all_gather(vals, best_val)
+    _all_gather(idxs, best_idx)
+    _all_gather(cands, best_cand)
     vals_t, idxs_t = torch.cat(vals), torch.cat(idxs)
     top = vals_t.max()
     tied = torch.nonzero(vals_t == top).view(-1)
@@ -230,8 +321,8 @@ def thompson_sample_sharded(sampler, X: Tensor, num_samples: int = 1, seed: int 
             return v.unsqueeze(0), i.unsqueeze(0)
         gv = [torch.empty_like(v) for _ in range(ws)]
         gi = [torch.empty_like(i) for _ in range(ws)]
-        dist.all_gather(gv, v)
-        dist.all_gather(gi, i)
+        _all_gather(gv, v)
+        _all_gather(gi, i)
         return torch.stack(gv), torch.stack(gi)
 
     if getattr(sampler, "pathwise", False):  # joint draws: one function per sample, argmax over all shards
@@ -263,30 +354,56 @@ def optimize_acqf_sharded(
     raw_samples: int,
     options: Optional[dict] = None,
     gen_candidates: Optional[Callable] = None,
+    timings: Optional[dict] = None,
 ) -> Tuple[Tensor, Tensor]:
     """``optimize_acqf`` with raw samples and restarts sharded over the process group.
 
-    Equivalent to the reference run with ``options['batch_limit'] = ceil(num_restarts / world_size)``.
+    Equivalent to the reference run with ``options['batch_limit'] = ceil(num_restarts / world_size)``.  Without
+    ``options['seed']`` rank 0 draws the seed and broadcasts it, so every rank holds the same raw samples and makes the
+    same host-side selection.  ``timings`` (optional dict) receives the wall time of each phase, device-synchronised.
     """
+    from time import perf_counter
+
     from .optim import gen_candidates_scipy, initialize_q_batch
     from .sampling import draw_sobol_samples
 
     options = dict(options or {})
     rank, ws = world()
     device = bounds.device
-    X_rnd = draw_sobol_samples(bounds=bounds.cpu(), n=raw_samples, q=q, seed=options.get("seed"))
+
+    def mark(name: str, t0: float) -> float:
+        if timings is None:
+            return t0
+        if device.type == "cuda":
+            torch.cuda.synchronize(device)
+        t1 = perf_counter()
+        timings[name] = timings.get(name, 0.0) + (t1 - t0)
+        return t1
+
+    t = perf_counter()
+    seed = shared_seed(options.get("seed"), device)
+    # the base samples of the q new points are drawn on a host thread while this one draws the raw samples
+    pending = acq_function.prefetch_base_samples(q) if hasattr(acq_function, "prefetch_base_samples") else None
+    X_rnd = draw_sobol_samples(bounds=bounds.cpu(), n=raw_samples, q=q, seed=seed)
+    if pending is not None:
+        pending.join()
+    t = mark("raw_sample_draw_s", t)
     Y_rnd = sharded_raw_sample_values(acq_function, X_rnd, device, options.get("init_batch_limit"))
+    t = mark("raw_sample_eval_and_allgather_s", t)
     # identical host RNG stream on every rank => identical initial conditions everywhere
     gen = torch.random.get_rng_state()
-    torch.manual_seed(options.get("seed", 0) or 0)
+    torch.manual_seed(seed or 0)
     ics = initialize_q_batch(X=X_rnd, Y=Y_rnd, n=num_restarts, **({"eta": options["eta"]} if "eta" in options else {}))
     torch.random.set_rng_state(gen)
+    t = mark("initial_condition_selection_s", t)
     lo, hi = shard_range(num_restarts, rank, ws)
     gen_candidates = gen_candidates or gen_candidates_scipy
     gen_opts = {k: v for k, v in options.items() if k in ("maxiter", "method", "with_grad", "disp", "ftol", "gtol")}
     cands, vals = gen_candidates(ics[lo:hi].to(device), acq_function, lower_bounds=bounds[0], upper_bounds=bounds[1],
                                  options=gen_opts)  # fmt: skip
+    t = mark("restart_optimisation_s", t)
     cand, val, _ = gather_best(vals, cands, lo)
+    mark("best_gather_s", t)
     return cand, val
 
 
@@ -315,7 +432,7 @@ def nuts_sample_sharded(make_potential, dim: int, chains_per_rank: int, num_samp
         return samples, stats
     local = samples.transpose(0, 1).contiguous()  # chains x draws x dim: rank blocks concatenate along the chain axis
     out = [torch.empty_like(local) for _ in range(ws)]
-    dist.all_gather(out, local)
+    _all_gather(out, local)
     return torch.cat(out, dim=0).transpose(0, 1).contiguous(), stats
 
 

@@ -313,6 +313,12 @@ def path_values(ps: "PathState", X: Tensor) -> Tensor:
     return ps.evaluate(X.detach())
 
 
+# CUDA graphs pay only where a step is launch-bound (C1 / C2: 0.1 ms for ~11 launches).  Capturing one shape costs ~25 ms
+# (profiles/r02_strong_c3_host_profile.txt); at C3 a step is 1.6 ms of kernels that the host enqueues well ahead of the
+# GPU, so shapes whose workspace exceeds this stay eager.
+GRAPH_MAX_WORKSPACE_BYTES = 16 << 20
+
+
 class NEIState:
     """Baseline factors of qLogNEI (V_b, L_b and its inverse, base samples, best_f) and the fused fwd/bwd."""
 
@@ -394,6 +400,14 @@ class NEIState:
         cache = self.__dict__.setdefault("_graphs", {})
         ge = cache.get(key)
         if ge is None:
+            # Capture pays for itself only when a shape recurs (the L-BFGS loop): a capture runs the launch sequence three
+            # times and pins a private workspace.  One-shot shapes -- the raw-sample sweep of gen_batch_initial_conditions
+            # (32 768 t-batches, ~9 GB of workspace at C3), the final evaluation -- stay eager: first use of a key only
+            # counts it.  Shapes whose kernels run for milliseconds gain nothing from saving ~10 launch latencies either.
+            seen = self.__dict__.setdefault("_graph_seen", {})
+            seen[key] = seen.get(key, 0) + 1
+            if seen[key] < 2 or self.workspace_bytes(B, q, with_grad) > GRAPH_MAX_WORKSPACE_BYTES:
+                return None
             if len(cache) >= 6:  # each entry pins its workspace; keep the most recent shapes only
                 cache.pop(next(iter(cache)))
             ge = cache[key] = GraphedEval(self, B, q, d, Z_q, tau_relu, tau_max, with_grad)

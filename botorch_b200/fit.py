@@ -18,6 +18,7 @@ There is no CPU path for the likelihood.
 from __future__ import annotations
 
 import math
+import logging
 import re
 import warnings
 from dataclasses import dataclass
@@ -363,10 +364,21 @@ def sample_all_priors(model: SingleTaskGP, max_retries: int = 100) -> None:
 
 
 def _default_warning_handler(w: warnings.WarningMessage) -> bool:
-    """fit.py:51-73 DEFAULT_WARNING_HANDLER: True = the warning does not trigger a retry."""
-    if not issubclass(w.category, OptimizationWarning):
+    """fit.py:51-73 DEFAULT_WARNING_HANDLER over optim/utils/common.py:35-60: True = resolved (no retry).
+
+    * the L-BFGS-B "iteration / evaluation limit reached" message is resolved at DEBUG level: a fit that merely hit
+      ``maxiter`` is returned as is, not retried (``_debug_warn``);
+    * anything that is not an ``OptimizationWarning`` (e.g. a ``NumericalWarning`` from a jitter retry) and the
+      optimiser's time-out message are re-emitted to the caller and resolved (``_rethrow_warn``);
+    * every other ``OptimizationWarning`` is unresolved: the attempt failed and the fit is retried from prior samples."""
+    message = str(w.message)
+    if _LBFGSB_MAXITER_MAXFUN_REGEX.search(message):
+        logging.getLogger("botorch").debug(message)
         return True
-    return "Optimization timed out after" in str(w.message)
+    if not issubclass(w.category, OptimizationWarning) or "Optimization timed out after" in message:
+        warnings.warn_explicit(message, w.category, w.filename, w.lineno)
+        return True
+    return False
 
 
 def fit_gpytorch_mll(mll: ExactMarginalLogLikelihood, closure=None, optimizer: Optional[Callable] = None,

@@ -108,6 +108,9 @@ def gen_batch_initial_conditions(
     q = 1 if q is None else q
     effective_dim = bounds.shape[-1] * q
     factor, max_factor = 1, 5
+    # base samples of the q new points: drawn on a host thread while this one draws the raw samples (both are scrambled
+    # Sobol engines whose construction is independent host work)
+    pending = acq_function.prefetch_base_samples(q) if hasattr(acq_function, "prefetch_base_samples") else None
     while factor < max_factor:
         with warnings.catch_warnings(record=True) as ws:
             n = raw_samples * factor
@@ -119,6 +122,9 @@ def gen_batch_initial_conditions(
                 with manual_seed(seed):
                     u = torch.rand(n, q, bounds_cpu.shape[-1], dtype=bounds.dtype)
                 X_rnd = bounds_cpu[0] + (bounds_cpu[1] - bounds_cpu[0]) * u
+            if pending is not None:
+                pending.join()
+                pending = None
             Y_rnd = evaluate_raw_samples(acq_function, X_rnd, device, batch_limit)
             ics = initialize_q_batch(X=X_rnd, Y=Y_rnd, n=num_restarts, **init_kwargs).to(device=device)
             if not any(issubclass(w.category, BadInitialCandidatesWarning) for w in ws):

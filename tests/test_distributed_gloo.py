@@ -51,6 +51,22 @@ def _worker(rank: int, ws: int, port: int, outdir: str) -> None:
         # sharded optimize_acqf: both ranks return the same winner, close to the optimum
         cand, val = bdist.optimize_acqf_sharded(acq, bounds, q=2, num_restarts=6, raw_samples=32,
                                                 options={"seed": 0, "maxiter": 100})  # fmt: skip
+        # no seed given: rank 0 draws it and broadcasts it, although the ranks' global RNGs differ (every rank used
+        # to scramble its own Sobol sequence, so the gathered values belonged to other ranks' points)
+        torch.manual_seed(100 + rank)
+        seeds = [bdist.shared_seed(None) for _ in range(2)]
+        assert bdist.shared_seed(17) == 17
+        timings = {}
+        cand_u, val_u = bdist.optimize_acqf_sharded(acq, bounds, q=2, num_restarts=6, raw_samples=32,
+                                                    options={"maxiter": 100}, timings=timings)  # fmt: skip
+        assert set(timings) == {"raw_sample_draw_s", "raw_sample_eval_and_allgather_s", "initial_condition_selection_s",
+                                "restart_optimisation_s", "best_gather_s"}  # fmt: skip
+        bdist.warm_up()
+        # mixed dtypes travel as one packed buffer per dtype
+        mixed = [torch.full((5,), float(rank), dtype=torch.float64), torch.full((3,), rank + 7, dtype=torch.int32),
+                 torch.full((2, 2), float(rank) - 1.0, dtype=torch.float64)]  # fmt: skip
+        bdist.broadcast_buffers(mixed, src=0)
+        assert float(mixed[0][4]) == 0.0 and int(mixed[1][0]) == 7 and float(mixed[2][1, 1]) == -1.0
         # NUTS chains sharded over the ranks: distinct chains per rank, one all-gather, same ensemble everywhere
         mu = torch.tensor([1.0, -1.0], dtype=torch.float64)
 
@@ -60,7 +76,7 @@ def _worker(rank: int, ws: int, port: int, outdir: str) -> None:
         draws, _ = bdist.nuts_sample_sharded(make_potential, 2, 3, num_samples=40, warmup_steps=60, device=torch.device("cpu"),
                                              seed=5)  # fmt: skip
         assert draws.shape == (40, 6, 2)
-        torch.save({"cand": cand, "val": val, "draws": draws}, os.path.join(outdir, f"r{rank}.pt"))
+        torch.save({"cand": cand, "val": val, "draws": draws, "cand_u": cand_u, "val_u": val_u, "seeds": seeds}, os.path.join(outdir, f"r{rank}.pt"))
     finally:
         dist.destroy_process_group()
 
@@ -72,6 +88,9 @@ def test_world_size_2_gloo():
         a, b = torch.load(os.path.join(d, "r0.pt")), torch.load(os.path.join(d, "r1.pt"))
     assert torch.equal(a["cand"], b["cand"]) and torch.equal(a["val"], b["val"])
     assert torch.allclose(a["cand"], torch.tensor([0.25, 0.6, 0.9], dtype=torch.float64).expand(2, 3), atol=1e-4)
+    assert a["seeds"] == b["seeds"] and a["seeds"][0] != a["seeds"][1]
+    assert torch.equal(a["cand_u"], b["cand_u"]) and torch.equal(a["val_u"], b["val_u"])
+    assert torch.allclose(a["cand_u"], torch.tensor([0.25, 0.6, 0.9], dtype=torch.float64).expand(2, 3), atol=1e-4)
     assert torch.equal(a["draws"], b["draws"])  # every rank holds the same gathered chains ...
     chains = a["draws"].transpose(0, 1)
     assert all(not torch.equal(chains[i], chains[j]) for i in range(6) for j in range(i))  # ... and the chains are distinct

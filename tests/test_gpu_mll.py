@@ -158,6 +158,27 @@ def test_fit_gpytorch_mll_reaches_the_oracle_optimum(cuda):
     assert post.mean.shape == (1, 5, 1) and bool(torch.isfinite(post.variance).all())
 
 
+def test_fit_that_hits_maxiter_is_returned_not_retried(cuda):
+    """fit.py:51-70 (`_debug_warn`): L-BFGS-B stopping at its iteration limit is not a failed attempt -- the reference returns
+    the partially fitted model; no ModelFittingError, no restart from prior samples."""
+    import warnings
+
+    from botorch_b200.fit import ExactMarginalLogLikelihood, fit_gpytorch_mll
+
+    X, y = _data(40, 3, seed=5, noise=0.1)
+    model = _model(cuda, X, y)
+    mll = ExactMarginalLogLikelihood(model.likelihood, model)
+    start = float(mll.value_and_grads()[0])
+    evals0 = mll._state.evaluations if getattr(mll, "_state", None) is not None else None
+    with warnings.catch_warnings():
+        warnings.simplefilter("error")
+        out = fit_gpytorch_mll(mll, optimizer_kwargs={"options": {"maxiter": 1}})
+    assert out is mll and not mll.training
+    assert float(mll.value_and_grads()[0]) > start  # one accepted step
+    if evals0 is not None:
+        assert mll._state.evaluations - evals0 < 25  # a single attempt, not five
+
+
 def test_fit_retries_and_raises_model_fitting_error(cuda):
     from botorch_b200.exceptions import OptimizationWarning
     from botorch_b200.fit import ExactMarginalLogLikelihood, ModelFittingError, OptimizationResult, OptimizationStatus, fit_gpytorch_mll

@@ -349,6 +349,57 @@ def test_fit_gpytorch_mll_retry_policy_on_the_host():
     assert mll.training and torch.equal(model.covar_module.raw_lengthscale.detach(), now)  # rolled back
 
 
+def test_fit_warning_handler_follows_the_reference_policy():
+    """fit.py:51-70 + optim/utils/common.py:35-60: an L-BFGS-B iteration-limit message is resolved quietly (no retry, no
+    ModelFittingError), a non-optimisation warning and the time-out message are re-emitted without a retry."""
+    import warnings
+
+    from botorch_b200.exceptions import OptimizationWarning
+    from botorch_b200.fit import ExactMarginalLogLikelihood, OptimizationResult, OptimizationStatus, fit_gpytorch_mll
+
+    model = _cpu_model()
+    mll = ExactMarginalLogLikelihood(model.likelihood, model)
+    calls = []
+
+    def hits_maxiter(mll_, closure=None, **kw):
+        calls.append(1)
+        warnings.warn("`scipy_minimize` terminated with status OptimizationStatus.STOPPED, displaying original message "
+                      "from `scipy.optimize.minimize`: STOP: TOTAL NO. of ITERATIONS REACHED LIMIT", OptimizationWarning)  # fmt: skip
+        return OptimizationResult(step=1, fval=1.0, status=OptimizationStatus.STOPPED)
+
+    with warnings.catch_warnings():
+        warnings.simplefilter("error")  # nothing may be re-emitted
+        out = fit_gpytorch_mll(mll, optimizer=hits_maxiter, closure=lambda: None, max_attempts=5)
+    assert out is mll and not mll.training and len(calls) == 1
+    calls.clear()
+
+    def newer_scipy_wording(mll_, closure=None, **kw):
+        calls.append(1)
+        warnings.warn("STOP: TOTAL NO. OF F,G EVALUATIONS EXCEEDS LIMIT".replace("F,G", "f AND g"), OptimizationWarning)
+        return OptimizationResult(step=1, fval=1.0, status=OptimizationStatus.STOPPED)
+
+    with warnings.catch_warnings():
+        warnings.simplefilter("error")
+        fit_gpytorch_mll(mll, optimizer=newer_scipy_wording, closure=lambda: None, max_attempts=5)
+    assert len(calls) == 1
+    calls.clear()
+
+    class NumericalWarning(RuntimeWarning):
+        pass
+
+    def jittered_and_timed_out(mll_, closure=None, **kw):
+        calls.append(1)
+        warnings.warn("A not p.d., added jitter of 1.0e-08 to the diagonal", NumericalWarning)
+        warnings.warn("Optimization timed out after 1.0 seconds.", OptimizationWarning)
+        return OptimizationResult(step=1, fval=1.0, status=OptimizationStatus.STOPPED)
+
+    with pytest.warns() as rec:
+        out = fit_gpytorch_mll(mll, optimizer=jittered_and_timed_out, closure=lambda: None, max_attempts=5)
+    assert out is mll and len(calls) == 1  # both resolved: no retry
+    cats = {r.category for r in rec}
+    assert NumericalWarning in cats and OptimizationWarning in cats
+
+
 # ---- NUTS host logic (botorch_b200/fully_bayesian.py): the sampler is device-agnostic, the potential is not ----------------
 def test_nuts_recovers_a_gaussian_target():
     from botorch_b200.fully_bayesian import nuts_sample

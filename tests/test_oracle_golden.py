@@ -420,3 +420,42 @@ def test_constrained_oracle_reduces_to_the_plain_oracle_without_constraints():
     v1, g1 = split.value_and_grad(X)
     v2, g2 = plain.value_and_grad(X)
     assert rel_err(g1, g2, scale=float(g2.abs().max())) < 1e-11
+
+
+# ---- the GP algebra against 50-digit mpmath vectors (independent of torch: tests/golden/make_mpmath_golden.py) -------
+def _mp_cases():
+    from tests.util import mpmath_cases
+
+    return mpmath_cases()
+
+
+@pytest.mark.parametrize("case,p", _mp_cases(), ids=lambda v: v["name"] if isinstance(v, dict) else "")
+def test_oracle_gp_algebra_matches_mpmath(case, p):
+    """oracle/gp.py + oracle/qlognei.py (the restatement of gpytorch 1.12 / linear_operator 0.5.2 behind
+    models/gpytorch.py:446, utils/low_rank.py:118-162, acquisition/logei.py:391-481) against the published formulas
+    evaluated in 50-digit arithmetic without torch.  This is the pin SURVEY.md 8(c) says the reference cannot give."""
+    from tests.util import oracle_acq, oracle_gp
+
+    t = lambda v: torch.tensor(v, dtype=torch.float64)  # noqa: E731
+    ogp = oracle_gp(p)
+    assert abs(float(ogp.y_mean) - case["y_mean"]) <= 1e-14 * max(1.0, abs(case["y_mean"]))
+    assert abs(float(ogp.y_std) - case["y_std"]) <= 1e-14 * case["y_std"]
+    X = t(case["X"])  # B x q x d
+    prior = float(ogp.y_std**2 * (case["outputscale"] or 1.0))
+    for form in (ogp.posterior, ogp.posterior_direct):
+        mean, cov = form(X)
+        assert rel_err(mean, t(case["post_mean"])) < 1e-13  # measured over the 48 cases: 1.2e-15
+        assert rel_err(cov, t(case["post_cov"]), scale=prior) < 1e-13  # measured 8e-16;  # cancellation k** - |L^-1 k|^2: prior-scale form (H1)
+    oacq = oracle_acq(p, ogp, seed=case["seed"])
+    assert torch.equal(oacq.Z_b, t(case["Z_b"])) and torch.equal(oacq.Z_q(p.q), t(case["Z_q"]))
+    assert rel_err(oacq.baseline_L, t(case["baseline_L"]), scale=prior**0.5) < 1e-12  # measured 6e-14
+    assert rel_err(oacq.best_f, t(case["best_f"])) < 1e-12  # measured 4e-14
+    ref_samples = t(case["samples"]).permute(1, 0, 2)  # S x B x q
+    for sampler in (oacq.samples_faithful, oacq.samples_minimal):
+        assert rel_err(sampler(X), ref_samples) < 1e-11  # measured 1.1e-13
+    for mode in ("faithful", "minimal"):
+        val, grad = oacq.value_and_grad(X, mode=mode)
+        assert rel_err(val, t(case["acq"]), scale=0.0) < 1e-11, mode  # measured 9e-14
+        gref = t(case["grad"])
+        gerr = ((grad - gref).flatten(1).abs().max(1).values / gref.flatten(1).abs().max(1).values).max()
+        assert float(gerr) < 1e-10, mode  # measured 1.2e-12

@@ -50,3 +50,23 @@ def rel_err(a: torch.Tensor, b: torch.Tensor, scale=None) -> float:
     a, b = a.detach().cpu().double(), b.detach().cpu().double()
     s = b.abs().max() if scale is None else torch.as_tensor(scale)
     return float(((a - b).abs() / torch.maximum(b.abs(), s.expand_as(b))).max())
+
+
+def mpmath_cases():
+    """The 50-digit golden vectors of tests/golden/make_mpmath_golden.py as (case dict, Problem) pairs."""
+    import json
+    import os
+
+    path = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "mpmath_gp.json")
+    with open(path) as fh:
+        data = json.load(fh)
+    out = []
+    for c in data["cases"]:
+        t = lambda v: torch.tensor(v, dtype=torch.float64)  # noqa: E731
+        hypers = {"lengthscale": t(c["lengthscale"]), "noise": t(c["noise"]), "mean": t(c["mean_const"])}
+        if c["outputscale"] is not None:
+            hypers["outputscale"] = t(c["outputscale"])
+        p = Problem(c["name"], t(c["train_X"]), t(c["train_Y"]).unsqueeze(-1), c["kernel"], hypers, c["q"], c["S"], 0, 0,
+                    standardize=c["standardize"])  # fmt: skip
+        out.append((c, p))
+    return out

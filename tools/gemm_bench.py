@@ -10,7 +10,10 @@ def child():
     from botorch_b200 import _lib
     dev = torch.device("cuda:0"); lib = _lib.lib(); ctx = _lib.ctx(dev)
     out = {}
-    for name, M, N, K, tri in (KSWEEP if os.environ.get('BO_KSWEEP') else SHAPES):
+    shapes = KSWEEP if os.environ.get('BO_KSWEEP') else SHAPES
+    if os.environ.get('BO_SHAPES'):  # "M,N,K,tri;M,N,K,tri"
+        shapes = [("%sx%sx%s t%s" % tuple(t.split(",")), *map(int, t.split(","))) for t in os.environ['BO_SHAPES'].split(";")]
+    for name, M, N, K, tri in shapes:
         lda, ldb = _lib.pad8(K), _lib.pad8(N)
         A = torch.randn(M, lda, dtype=torch.float64, device=dev); B = torch.randn(K, ldb, dtype=torch.float64, device=dev)
         C = torch.empty(M, ldb, dtype=torch.float64, device=dev)
