@@ -10,6 +10,7 @@
 //   new_Lq.matmul(base_samples) in low_rank.py:156
 #include "common.cuh"
 #include <cstdlib>
+#include <cuda.h>  // CUtensorMap (types only: the encoder is fetched through cudaGetDriverEntryPoint, libcuda is not linked)
 
 long g_bo_launch_count = 0;
 
@@ -279,6 +280,196 @@ __global__ void __launch_bounds__(C::THREADS) dgemm_dmma_kernel(const BoGemm p) 
     }
 }
 
+// ------------------------------------------------------------------------------------------------------------------
+// TMA-staged variant: operand tiles are moved by the tensor memory accelerator (cp.async.bulk.tensor + mbarrier
+// full/empty pairs) issued by ONE producer warp; the consumer warps only wait on a stage's `full` barrier, run their
+// DMMA.8x8x4 sequence out of shared memory and release the stage -- no CTA-wide barrier and no address arithmetic in the
+// main loop.  FP64 has no tcgen05 kind, so the math stays on mma.sync m8n8k4; only the data movement changes.
+//
+// Shared-memory layout (dense, no padding, no swizzle) chosen so that every fragment load of a warp is ONE contiguous
+// 256-byte segment (conflict-free): the tensor maps present the operands as rank-4 tensors
+//   A: {4 (k within a k4 group), M rows, K/4 groups, batch}   box {4, BM, BK/4, 1}  -> As[k4][row][4]
+//   B: {8 (column within an 8-column group), K rows, N/8 groups, batch}   box {8, BK, BN/8, 1}  -> Bs[n8][k][8]
+// so lane (g, t) of a warp reads A[row0 + g][k4*4 + t] at ((k4*BM + row0 + g)*4 + t) and B[k + t][col0 + g] at
+// ((n8*BK + k + t)*8 + g).  Out-of-range rows / k rows / batch are zero-filled by the TMA unit itself.
+// ------------------------------------------------------------------------------------------------------------------
+template <int BM_, int BN_, int BK_, int WM_, int WN_, int STAGES_, int MINB_>
+struct TCfg {
+    static constexpr int BM = BM_, BN = BN_, BK = BK_, WM = WM_, WN = WN_, STAGES = STAGES_, MINB = MINB_;
+    static constexpr int WARPS_M = BM / WM, WARPS_N = BN / WN;
+    static constexpr int CONSUMERS = WARPS_M * WARPS_N;
+    static constexpr int THREADS = (CONSUMERS + 1) * 32;  // + the producer warp
+    static constexpr int A_STAGE = BM * BK, B_STAGE = BK * BN;  // doubles
+    static constexpr unsigned STAGE_BYTES = (unsigned)((A_STAGE + B_STAGE) * sizeof(double));
+    static constexpr size_t SMEM = (size_t)STAGES * STAGE_BYTES + 2 * STAGES * sizeof(unsigned long long) + 128;
+    static_assert(BK % 4 == 0 && BN % 8 == 0 && BM <= 256 && BK <= 256 && BN / 8 <= 256, "TMA box limits");
+};
+
+__device__ __forceinline__ void mbar_init(unsigned bar, unsigned count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;\n" ::"r"(bar), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(unsigned bar, unsigned parity) {
+    asm volatile(
+        "{\n\t.reg .pred P1;\n\t"
+        "WAIT_%=:\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 P1, [%0], %1;\n\t"
+        "@P1 bra DONE_%=;\n\t"
+        "bra WAIT_%=;\n\t"
+        "DONE_%=:\n\t}\n" ::"r"(bar), "r"(parity)
+        : "memory");
+}
+__device__ __forceinline__ void mbar_arrive(unsigned bar) {
+    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];\n" ::"r"(bar) : "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(unsigned bar, unsigned bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;\n" ::"r"(bar), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void tma_load_4d(unsigned dst, const CUtensorMap* map, unsigned bar, int c0, int c1, int c2,
+                                            int c3) {
+    asm volatile(
+        "cp.async.bulk.tensor.4d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5, %6}], [%2];\n" ::
+            "r"(dst), "l"(reinterpret_cast<unsigned long long>(map)), "r"(bar), "r"(c0), "r"(c1), "r"(c2), "r"(c3)
+        : "memory");
+}
+
+template <class C>
+__global__ void __launch_bounds__(C::THREADS, C::MINB)
+dgemm_dmma_tma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, const BoGemm p,
+                      const int za_step, const int zb_step) {
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    // 128-byte aligned tile area (TMA destination alignment), then the barriers
+    const unsigned raw = (unsigned)__cvta_generic_to_shared(smem_raw);
+    const unsigned pad = (128u - (raw & 127u)) & 127u;
+    double* tiles = reinterpret_cast<double*>(smem_raw + pad);
+    const unsigned tiles_s = raw + pad;
+    const unsigned bars_s = tiles_s + (unsigned)C::STAGES * C::STAGE_BYTES;  // full[STAGES], empty[STAGES]
+
+    const int tid = threadIdx.x;
+    const int warp = tid >> 5, lane = tid & 31;
+    const int g = lane >> 2, t = lane & 3;
+    const int z = blockIdx.z;
+    const int mt = (p.tri == BO_TRI_A_LOWER) ? (gridDim.y - 1 - blockIdx.y) : blockIdx.y;
+    const int m0 = mt * C::BM;
+    const int n0 = blockIdx.x * C::BN;
+    if (p.out_lower && n0 > m0 + C::BM - 1) return;
+
+    int kb = 0, ke = p.K;
+    if (p.tri == BO_TRI_A_LOWER) ke = min(p.K, m0 + C::BM + p.tri_off);
+    else if (p.tri == BO_TRI_A_UPPER) kb = m0 > p.tri_off ? ((m0 - p.tri_off) / C::BK) * C::BK : 0;
+    else if (p.tri == BO_TRI_B_LOWER) kb = (n0 / C::BK) * C::BK;
+    const int ntiles = ke > kb ? (ke - kb + C::BK - 1) / C::BK : 0;
+
+    if (tid == 0) {
+#pragma unroll
+        for (int s = 0; s < C::STAGES; s++) {
+            mbar_init(bars_s + 8u * s, 1);                          // full: the producer's expect_tx arrival
+            mbar_init(bars_s + 8u * (C::STAGES + s), C::CONSUMERS);  // empty: one arrival per consumer warp
+        }
+        asm volatile("fence.mbarrier_init.release.cluster;\n" ::: "memory");
+    }
+    __syncthreads();
+
+    constexpr int TM = C::WM / 8, TN = C::WN / 8;
+    double acc[TM][TN][2];
+    const int wm0 = (warp / C::WARPS_N) * C::WM;
+    const int wn0 = (warp % C::WARPS_N) * C::WN;
+
+    if (warp == C::CONSUMERS) {
+        // ---- producer: one lane streams the k-tiles of this CTA's (row tile, column tile) through the ring ----
+        if (lane == 0) {
+            for (int kt = 0; kt < ntiles; kt++) {
+                const int s = kt % C::STAGES;
+                if (kt >= C::STAGES) mbar_wait(bars_s + 8u * (C::STAGES + s), ((kt / C::STAGES) - 1) & 1);
+                const unsigned full = bars_s + 8u * s;
+                mbar_expect_tx(full, C::STAGE_BYTES);
+                const unsigned a_dst = tiles_s + (unsigned)s * C::STAGE_BYTES;
+                const unsigned b_dst = a_dst + (unsigned)(C::A_STAGE * sizeof(double));
+                const int k0 = kb + kt * C::BK;
+                tma_load_4d(a_dst, &tmA, full, 0, m0, k0 / 4, z * za_step);
+                tma_load_4d(b_dst, &tmB, full, 0, k0, n0 / 8, z * zb_step);
+            }
+        }
+    } else {
+#pragma unroll
+        for (int i = 0; i < TM; i++)
+#pragma unroll
+            for (int j = 0; j < TN; j++) acc[i][j][0] = acc[i][j][1] = 0.0;
+        for (int kt = 0; kt < ntiles; kt++) {
+            const int s = kt % C::STAGES;
+            mbar_wait(bars_s + 8u * s, (kt / C::STAGES) & 1);
+            const double* as = tiles + (size_t)s * (C::A_STAGE + C::B_STAGE) + (wm0 + g) * 4 + t;
+            const double* bs = tiles + (size_t)s * (C::A_STAGE + C::B_STAGE) + C::A_STAGE + ((wn0 / 8) * C::BK + t) * 8 + g;
+#pragma unroll
+            for (int kk = 0; kk < C::BK; kk += 4) {
+                double a[TM], b[TN];
+#pragma unroll
+                for (int i = 0; i < TM; i++) a[i] = as[(kk / 4) * C::BM * 4 + i * 32];
+#pragma unroll
+                for (int j = 0; j < TN; j++) b[j] = bs[(j * C::BK + kk) * 8];
+#pragma unroll
+                for (int i = 0; i < TM; i++)
+#pragma unroll
+                    for (int j = 0; j < TN; j++) dmma884(acc[i][j][0], acc[i][j][1], a[i], b[j]);
+            }
+            __syncwarp();
+            if (lane == 0) mbar_arrive(bars_s + 8u * (C::STAGES + s));
+        }
+    }
+
+    double* __restrict__ Cz = p.C + (long)z * p.strideC;
+    double* __restrict__ CTz = p.CT ? p.CT + (long)z * p.strideCT : nullptr;
+    constexpr bool kStageFits = (size_t)C::BM * (C::BN + 2) * sizeof(double) <= (size_t)C::STAGES * C::STAGE_BYTES;
+    if constexpr (kStageFits) if (p.epi != BO_EPI_LINEAR) {
+        // covariance epilogues: staged through shared memory, one rolled copy of the transcendental code (see above).
+        // Every TMA write has landed (each consumer waited on every `full` phase), so the ring can be reused.
+        constexpr int LDC_S = C::BN + 2;
+        __syncthreads();
+        double* Cs = tiles;
+        if (warp < C::CONSUMERS) {
+#pragma unroll
+            for (int i = 0; i < TM; i++)
+#pragma unroll
+                for (int j = 0; j < TN; j++)
+                    *reinterpret_cast<double2*>(Cs + (wm0 + i * 8 + g) * LDC_S + wn0 + j * 8 + 2 * t) =
+                        make_double2(acc[i][j][0], acc[i][j][1]);
+        }
+        __syncthreads();
+#pragma unroll 2
+        for (int e = tid; e < C::BM * C::BN; e += C::THREADS) {
+            const int r = e / C::BN, c = e % C::BN;
+            const int row = m0 + r, col = n0 + c;
+            if (row >= p.M || col >= p.N) continue;
+            const double v = epilogue_value(p, z, Cs[r * LDC_S + c], row, col);
+            Cz[(long)row * p.ldc + col] = v;
+            if (CTz) CTz[(long)col * p.ldct + row] = v;
+        }
+        return;
+    }
+    if (warp >= C::CONSUMERS) return;
+#pragma unroll
+    for (int i = 0; i < TM; i++) {
+        const int row = m0 + wm0 + i * 8 + g;
+        if (row >= p.M) continue;
+#pragma unroll
+        for (int j = 0; j < TN; j++) {
+            const int col = n0 + wn0 + j * 8 + 2 * t;
+            if (col >= p.N) continue;
+            const double v0 = epilogue_value(p, z, acc[i][j][0], row, col);
+            if (col + 1 < p.N) {
+                const double v1 = epilogue_value(p, z, acc[i][j][1], row, col + 1);
+                *reinterpret_cast<double2*>(Cz + (long)row * p.ldc + col) = make_double2(v0, v1);
+                if (CTz) {
+                    CTz[(long)col * p.ldct + row] = v0;
+                    CTz[(long)(col + 1) * p.ldct + row] = v1;
+                }
+            } else {
+                Cz[(long)row * p.ldc + col] = v0;
+                if (CTz) CTz[(long)col * p.ldct + row] = v0;
+            }
+        }
+    }
+}
+
 using CfgBig = Cfg<128, 128, 16, 64, 32, 4>;
 using CfgMid = Cfg<64, 64, 16, 32, 32, 4>;
 using CfgSmall = Cfg<32, 32, 16, 16, 16, 3>;
@@ -300,6 +491,21 @@ using CfgT11 = Cfg<64, 32, 16, 32, 32, 3>;    // 2 warps per CTA, up to 8 CTAs/S
 using CfgPanel = Cfg<16, 64, 32, 16, 16, 3>;
 using CfgSkinny = Cfg<32, 128, 16, 32, 32, 2>; // M <= 32 (the (d+1)-row gradient contraction): one row tile, wide columns
 
+// multiply-adds per output column: nonzero entries of A (algorithmic count; triangular operands count their nonzeros only)
+double gemm_macs(const BoGemm& g) {
+    double macs = (double)g.M * g.K;
+    if (g.tri == BO_TRI_A_LOWER) {
+        macs = 0.0;
+        for (int m = 0; m < g.M; m++) macs += (m + 1 + g.tri_off < g.K) ? m + 1 + g.tri_off : g.K;
+    } else if (g.tri == BO_TRI_A_UPPER) {
+        macs = 0.0;
+        for (int m = 0; m < g.M; m++) macs += (m < g.tri_off) ? g.K : ((g.K - (m - g.tri_off) > 0) ? g.K - (m - g.tri_off) : 0);
+    } else if (g.tri == BO_TRI_B_LOWER || g.out_lower) {
+        macs *= 0.5;
+    }
+    return macs;
+}
+
 template <class C>
 int launch_cfg(const BoGemm& g, cudaStream_t stream) {
     static bool attr_set = false;
@@ -319,17 +525,7 @@ int launch_cfg(const BoGemm& g, cudaStream_t stream) {
             g_prof_recs.push_back(r);
         }
         rec = &g_prof_recs[g_prof_used++];
-        double macs = (double)g.M * g.K;  // multiply-adds per output column: nonzero entries of A
-        if (g.tri == BO_TRI_A_LOWER) {
-            macs = 0.0;
-            for (int m = 0; m < g.M; m++) macs += (m + 1 + g.tri_off < g.K) ? m + 1 + g.tri_off : g.K;
-        } else if (g.tri == BO_TRI_A_UPPER) {
-            macs = 0.0;
-            for (int m = 0; m < g.M; m++) macs += (m < g.tri_off) ? g.K : ((g.K - (m - g.tri_off) > 0) ? g.K - (m - g.tri_off) : 0);
-        } else if (g.tri == BO_TRI_B_LOWER || g.out_lower) {
-            macs *= 0.5;
-        }
-        g_prof_flops += 2.0 * macs * g.N * g.batch;
+        g_prof_flops += 2.0 * gemm_macs(g) * g.N * g.batch;
         BO_CUDA_TRY(cudaEventRecord(rec->a, stream));
     }
     dgemm_dmma_kernel<C><<<grid, C::THREADS, C::SMEM, stream>>>(g);
@@ -338,6 +534,93 @@ int launch_cfg(const BoGemm& g, cudaStream_t stream) {
     BO_CUDA_TRY(cudaGetLastError());
     return BO_OK;
 }
+
+// ---- host side of the TMA variant -------------------------------------------------------------------------------
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
+                                  const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                  CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+EncodeTiledFn encode_tiled_fn() {
+    static EncodeTiledFn fn = [] {
+        void* f = nullptr;
+        cudaDriverEntryPointQueryResult q;
+        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &f, cudaEnableDefault, &q) != cudaSuccess ||
+            q != cudaDriverEntryPointSuccess)
+            f = nullptr;
+        return (EncodeTiledFn)f;
+    }();
+    return fn;
+}
+
+// rank-4 view {inner (4 or 8 doubles), rows, groups, batch} of a row-major matrix batch
+bool make_map(CUtensorMap* m, const double* base, unsigned inner, long rows, long groups, long ld, int batch, long stride,
+              unsigned box_rows, unsigned box_groups) {
+    EncodeTiledFn enc = encode_tiled_fn();
+    if (!enc) return false;
+    const bool bcast = (batch > 1 && stride == 0);
+    cuuint64_t dims[4] = {inner, (cuuint64_t)rows, (cuuint64_t)groups, (cuuint64_t)(bcast ? 1 : batch)};
+    cuuint64_t strides[3] = {(cuuint64_t)ld * 8, (cuuint64_t)inner * 8,
+                             (cuuint64_t)((batch > 1 && !bcast) ? stride * 8 : (long)inner * 8)};
+    cuuint32_t box[4] = {inner, box_rows, box_groups, 1};
+    cuuint32_t estr[4] = {1, 1, 1, 1};
+    return enc(m, CU_TENSOR_MAP_DATA_TYPE_FLOAT64, 4, const_cast<double*>(base), dims, strides, box, estr,
+               CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+               CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
+}
+
+// operands the rank-4 views can describe: K a multiple of 4 (an A k4 group never straddles the row end), B rows padded to
+// whole 8-column groups, 16-byte aligned batch strides
+bool tma_eligible(const BoGemm& g) {
+    if (g.K % 4 != 0 || g.ldb < bo_round_up(g.N, 8) || g.lda < g.K) return false;
+    if (g.batch > 1 && ((g.strideA & 1) || (g.strideB & 1))) return false;
+    if ((long)g.lda * 8 >= (1L << 40) || (long)g.ldb * 8 >= (1L << 40)) return false;
+    return encode_tiled_fn() != nullptr;
+}
+
+template <class C>
+int launch_tma(const BoGemm& g, cudaStream_t stream) {
+    static bool attr_set = false;
+    if (!attr_set) {
+        BO_CUDA_TRY(cudaFuncSetAttribute(dgemm_dmma_tma_kernel<C>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                         (int)C::SMEM));
+        attr_set = true;
+    }
+    dim3 grid((g.N + C::BN - 1) / C::BN, (g.M + C::BM - 1) / C::BM, g.batch);
+    if (grid.y > 65535u || grid.z > 65535u) return BO_ERR_UNSUPPORTED;
+    CUtensorMap tmA, tmB;
+    if (!make_map(&tmA, g.A, 4, g.M, g.K / 4, g.lda, g.batch, g.strideA, C::BM, C::BK / 4) ||
+        !make_map(&tmB, g.B, 8, g.K, (g.N + 7) / 8, g.ldb, g.batch, g.strideB, C::BK, C::BN / 8))
+        return BO_ERR_INVALID;
+    ProfRec* rec = nullptr;
+    if (g_prof_on) {
+        if (g_prof_used == g_prof_recs.size()) {
+            ProfRec r;
+            BO_CUDA_TRY(cudaEventCreate(&r.a));
+            BO_CUDA_TRY(cudaEventCreate(&r.b));
+            g_prof_recs.push_back(r);
+        }
+        rec = &g_prof_recs[g_prof_used++];
+        g_prof_flops += 2.0 * gemm_macs(g) * g.N * g.batch;
+        BO_CUDA_TRY(cudaEventRecord(rec->a, stream));
+    }
+    dgemm_dmma_tma_kernel<C><<<grid, C::THREADS, C::SMEM, stream>>>(tmA, tmB, g, (g.batch > 1 && g.strideA == 0) ? 0 : 1,
+                                                                  (g.batch > 1 && g.strideB == 0) ? 0 : 1);
+    if (rec) BO_CUDA_TRY(cudaEventRecord(rec->b, stream));
+    g_bo_launch_count++;
+    BO_CUDA_TRY(cudaGetLastError());
+    return BO_OK;
+}
+
+using TCfgBig = TCfg<128, 128, 16, 64, 32, 4, 1>;    // 8 consumer warps of 64 x 32, 1 CTA/SM, 128 KB ring
+using TCfgWide = TCfg<128, 64, 16, 32, 32, 4, 2>;    // 8 consumer warps of 32 x 32, 2 CTAs/SM
+using TCfgMid = TCfg<64, 64, 16, 32, 32, 4, 3>;      // 4 consumer warps of 32 x 32, 3 CTAs/SM
+using TCfgBig32 = TCfg<128, 128, 32, 64, 32, 3, 1>;  // BK = 32: half the barrier traffic, 192 KB ring
+using TCfgTall = TCfg<256, 64, 16, 64, 32, 4, 1>;    // 8 consumer warps of 64 x 32, B tile re-read less often
+using TCfgMid4 = TCfg<64, 64, 16, 32, 32, 3, 4>;     // 3 stages, 4 CTAs/SM
+using TCfgMid32 = TCfg<64, 64, 32, 32, 32, 3, 2>;    // BK = 32
+using TCfgRow = TCfg<64, 128, 16, 32, 32, 4, 2>;     // 8 consumer warps of 32 x 32 side by side
+using TCfgCol = TCfg<128, 64, 16, 64, 32, 4, 2>;     // 4 consumer warps of 64 x 32
+using TCfgMid6 = TCfg<64, 64, 16, 32, 32, 6, 2>;     // deeper ring
 
 }  // namespace
 
@@ -365,6 +648,20 @@ int bo_gemm_launch(const BoGemm& g, cudaStream_t stream) {
         case 12: return launch_cfg<CfgPanel>(g, stream);
         default: break;
     }
+    if (forced >= 20 && forced <= 29 && tma_eligible(g)) {  // TMA-staged variants (tools/gemm_bench.py)
+        switch (forced) {
+            case 20: return launch_tma<TCfgBig>(g, stream);
+            case 21: return launch_tma<TCfgWide>(g, stream);
+            case 22: return launch_tma<TCfgMid>(g, stream);
+            case 23: return launch_tma<TCfgBig32>(g, stream);
+            case 24: return launch_tma<TCfgTall>(g, stream);
+            case 25: return launch_tma<TCfgMid4>(g, stream);
+            case 26: return launch_tma<TCfgMid32>(g, stream);
+            case 27: return launch_tma<TCfgRow>(g, stream);
+            case 28: return launch_tma<TCfgCol>(g, stream);
+            default: return launch_tma<TCfgMid6>(g, stream);
+        }
+    }
     auto tiles = [&](int bm, int bn) { return (long)((g.M + bm - 1) / bm) * ((g.N + bn - 1) / bn) * g.batch; };
     // Pick the largest tile that still fills the 148 SMs; small problems trade tile efficiency for occupancy.
     // 64x64 tiles, 4 warps, double-buffered, 4 CTAs per SM: measured best on B200 (tools/gemm_bench.py) --
@@ -372,6 +669,11 @@ int bo_gemm_launch(const BoGemm& g, cudaStream_t stream) {
     if (g.tile64) return launch_cfg<CfgPanel>(g, stream);
     if (g.M <= 32 && g.N >= 1024 && g.K >= 64 && g.epi == BO_EPI_LINEAR && g.tri == BO_TRI_NONE)
         return launch_cfg<CfgSkinny>(g, stream);
+    // TMA-staged 64 x 64 tiles (one producer warp + 4 DMMA warps, 3 CTAs/SM) wherever the tensor maps can describe the
+    // operands: measured 36.4 TF dense against 34.8 for the cp.async form and 35.4 for cuBLAS (tools/gemm_bench.py,
+    // profiles/r02_gemm_tma_sweep.txt).  BO_GEMM_TMA=0 switches back for A/B comparisons.
+    static const bool use_tma = [] { const char* e = getenv("BO_GEMM_TMA"); return !e || atoi(e) != 0; }();
+    if (use_tma && tiles(64, 64) >= 120 && g.K >= 64 && tma_eligible(g)) return launch_tma<TCfgMid>(g, stream);
     if (tiles(64, 64) >= 120 || (g.M >= 48 && g.N >= 48 && tiles(32, 32) > 2048)) return launch_cfg<CfgT10>(g, stream);
     return launch_cfg<CfgSmall>(g, stream);
 }
