@@ -3,6 +3,7 @@
 // caller's, every launch goes to the caller's stream.
 #include "../../include/botorch_b200.h"
 
+#include <cstdlib>
 #include <cstring>
 
 #include "cand.cuh"
@@ -421,6 +422,9 @@ namespace {
 struct QWork {
     long ldn, R, regionStride;
     double *baug, *W0, *W1, *W2, *W3, *F, *W5, *W6, *Lq, *lse, *Sbar, *Wd, *H;
+    double *gram, *post;           // fused combined-root pieces (BoGemm::gram / BoGemm::post), 8 % q == 0 only
+    long strideGram, stridePost;
+    int gram_tiles;
     long strideH;
     int ksplit;  // row slices of the [train_X^T; 1] G contraction (split-K), summed in order by the finalize kernel
     bool qpath;  // X_baseline == train_X with the combined root L_W (bo_nei.lw): Schur = ys^2 k - U^T U, U = L_W^T K(X_tr, X)
@@ -441,6 +445,12 @@ int hsplit(const bo_gp* gp) {
 // H slices <- [train_X^T; 1] G, then gradX += (H_t - x_t H_d) / l_t^2
 int kernel_gradient(const bo_gp* gp, const BoKernelHyper& h, const QWork& w, const double* G, const double* X, long N,
                     double* grad_X, cudaStream_t st);
+
+// BO_FUSE=0 disables the fused Gram / adjoint pieces of the combined-root path (A/B measurements)
+static bool fuse_enabled() {
+    static const bool on = [] { const char* e = getenv("BO_FUSE"); return !e || atoi(e) != 0; }();
+    return on;
+}
 
 QWork qlayout(const bo_gp* gp, const bo_nei* nei, int B, int q, int with_grad, void* work, size_t cap) {
     QWork w{};
@@ -475,6 +485,14 @@ QWork qlayout(const bo_gp* gp, const bo_nei* nei, int B, int q, int with_grad, v
         if (gp->kernel_id != BO_KERNEL_RBF) w.Wd = b.doubles(M * w.regionStride);  // Matern derivative factor
         if (w.qpath) w.W2 = b.doubles(M * w.regionStride);
         else w.W5 = b.doubles(M * w.regionStride);
+    }
+    if (w.qpath && q <= 8 && 8 % q == 0 && fuse_enabled()) {  // appended last: the offsets of every other region stay what they were
+        const long groups = (N + 7) / 8;
+        w.gram_tiles = (int)((S1p + n + BO_GRAM_BM - 1) / BO_GRAM_BM);
+        w.strideGram = (long)w.gram_tiles * groups * 64;
+        w.stridePost = groups * 64;
+        w.gram = b.doubles(M * w.strideGram);
+        if (with_grad) w.post = b.doubles(M * w.stridePost);
     }
     w.ok = b.ok;
     w.bytes = b.off;
@@ -558,8 +576,12 @@ int bo_qlognei_fwd(bo_ctx* ctx, const bo_gp* gp, const bo_nei* nei, int B, int q
         g.C = w.W1; g.ldc = w.ldn; g.strideC = w.regionStride;
         g.alpha = 1.0; g.M = (int)(S1p + n); g.N = (int)N; g.K = (int)n; g.batch = (int)M;
         g.tri = BO_TRI_A_UPPER; g.tri_off = (int)S1p; g.epi = BO_EPI_LINEAR;
+        // q x q Gram U^T U of every t-batch from the epilogue of this launch (no second pass over the n x N block U)
+        const bool fuse_gram = w.gram != nullptr && bo_gemm_fused_ok(g);
+        if (fuse_gram) { g.gram = w.gram; g.strideGram = w.strideGram; g.gram_row0 = (int)S1p; }
         BO_TRY(bo_gemm_launch(g, st));
         BoCandArgs a = cand_args(gp, nei, B, q, X, Z_q, tau_relu, tau_max, w);
+        if (fuse_gram) { a.gram = w.gram; a.strideGram = w.strideGram; a.gram_tiles = w.gram_tiles; }
         a.V = nullptr;
         if (nei->no_baseline) { a.F = w.F; a.strideF = S * w.ldn; a.f_zero = 1; }
         else { a.F = w.W1; a.strideF = w.regionStride; }
@@ -620,11 +642,6 @@ int bo_qlognei_bwd(bo_ctx* ctx, const bo_gp* gp, const bo_nei* nei, int B, int q
         a.strideVbar = w.regionStride;
         // 2r. Ubar = -2 U Sbar, in place on rows S1p.. of the same region: inside the reverse kernel for q <= 8 (the
         //     q x q block lives in registers there), as a separate pass otherwise
-        const bool fuse_u = q <= 8;
-        if (fuse_u) { a.Uinplace = w.W1 + S1p * w.ldn; a.strideU = w.regionStride; a.u_coef = -2.0; a.n_b = (int)n; }
-        BO_TRY(bo_cand_bwd(a, st));
-        if (!fuse_u)
-            BO_TRY(bo_colblock_inplace(w.W1 + S1p * w.ldn, w.regionStride, w.Sbar, (int)n, B, q, (int)M, w.ldn, -2.0, st));
         // 3r. G = ([Z_b Q; alpha^T]^T [dF; y_std mubar] + L_W Ubar) .* g(r) in ONE launch over the stacked operand;
         //     g = K for RBF, the stored derivative factor for Matern                                          (W2)
         BoGemm g{};
@@ -634,6 +651,16 @@ int bo_qlognei_bwd(bo_ctx* ctx, const bo_gp* gp, const bo_nei* nei, int B, int q
         g.E = w.Wd ? w.Wd : w.W0; g.lde = w.ldn; g.strideE = w.regionStride;
         g.alpha = 1.0; g.M = (int)n; g.N = (int)N; g.K = (int)(S1p + n); g.batch = (int)M;
         g.tri = BO_TRI_A_LOWER; g.tri_off = (int)S1p; g.epi = BO_EPI_LINEAR;
+        // L_W (U (-2 Sbar)) = (L_W U) (-2 Sbar): the block-diagonal factor is applied to the accumulators inside the
+        // GEMM (BoGemm::post), so U stays as the forward left it and nobody rewrites the n x N block
+        const bool fuse_post = w.post != nullptr && bo_gemm_fused_ok(g);
+        const bool fuse_u = !fuse_post && q <= 8;
+        if (fuse_post) { a.post = w.post; a.stridePost = w.stridePost; a.u_coef = -2.0; }
+        if (fuse_u) { a.Uinplace = w.W1 + S1p * w.ldn; a.strideU = w.regionStride; a.u_coef = -2.0; a.n_b = (int)n; }
+        BO_TRY(bo_cand_bwd(a, st));
+        if (!fuse_u && !fuse_post)
+            BO_TRY(bo_colblock_inplace(w.W1 + S1p * w.ldn, w.regionStride, w.Sbar, (int)n, B, q, (int)M, w.ldn, -2.0, st));
+        if (fuse_post) { g.post = w.post; g.stridePost = w.stridePost; g.post_k0 = (int)S1p; }
         BO_TRY(bo_gemm_launch(g, st));
         // 4r. H = [train_X^T; 1] G  ((d+1) x N), then gradX += (H_t - x_t H_d) / l_t^2
         return kernel_gradient(gp, h, w, w.W2, X, N, grad_X, st);

@@ -427,7 +427,32 @@ __global__ void __launch_bounds__(CAND_THREADS, (QT <= 8 ? 4 : 1)) cand_fwd_kern
         for (int i = tid; i < q * q; i += T) c.GV[i] = 0.0;
         __syncthreads();
     }
-    gram_any(BL, a.ldn, a.n_b, c0, q, c.panel, c.part, c.GB);
+    if (a.gram != nullptr) {
+        // the GEMM that produced BL left per-row-tile partial Grams of every 8-column group: sum them in tile order
+        const long groups = ((long)a.B * q + 7) / 8;
+        const double* Gp = a.gram + (long)z * a.strideGram + (long)(c0 / 8) * 64;
+        const int o8 = c0 % 8;
+        // warp w sums the tiles w, w + W, w + 2W, ... (independent loads in flight), then the W partials are added in warp
+        // order: a fixed summation tree
+        const int warp = tid >> 5, lane = tid & 31, W = T >> 5;
+        for (int idx = lane; idx < q * q; idx += 32) {
+            const int j = idx / q, k = idx % q;
+            const int hi = j > k ? j : k, lo = j > k ? k : j;  // one triangle: the result is exactly symmetric
+            const int pr = (o8 + hi) * 8 + o8 + lo;
+            double s_ = 0.0;
+            for (int rt = warp; rt < a.gram_tiles; rt += W) s_ += Gp[(long)rt * groups * 64 + pr];
+            c.panel[warp * q * q + idx] = s_;
+        }
+        __syncthreads();
+        for (int idx = tid; idx < q * q; idx += T) {
+            double s_ = 0.0;
+            for (int w2 = 0; w2 < W; w2++) s_ += c.panel[w2 * q * q + idx];
+            c.GB[idx] = s_;
+        }
+        __syncthreads();
+    } else {
+        gram_any(BL, a.ldn, a.n_b, c0, q, c.panel, c.part, c.GB);
+    }
 
     const double ys2 = a.y_std * a.y_std;
     const double os = a.h.outputscale ? a.h.outputscale[z] : 1.0;
@@ -690,6 +715,16 @@ __global__ void __launch_bounds__(CAND_THREADS, (QT <= 8 ? 4 : 1)) cand_bwd_kern
         Sbar[idx] = v;
     }
     if (tid < q) a.Vbar_mu[(long)z * a.strideVbar + c0 + tid] = a.y_std * mubar[tid];
+    if (a.post != nullptr) {
+        // this t-batch's q rows of its 8 x 8 column-group matrix: u_coef * Sbar on the diagonal block, zero elsewhere
+        double* Pg = a.post + (long)z * a.stridePost + (long)(c0 / 8) * 64;
+        const int o8 = c0 % 8;
+        for (int idx = tid; idx < q * 8; idx += T) {
+            const int r = idx / 8, cc = idx % 8, k = cc - o8;
+            const double v = (k >= 0 && k < q && ok) ? a.u_coef * 0.5 * (Pm[r * q + k] + Pm[k * q + r]) : 0.0;
+            Pg[(o8 + r) * 8 + cc] = v;
+        }
+    }
     __syncthreads();
 
     // 4. gradient through k(X, X):  Schur = ys^2 (k(x_j,x_k) - ...) - ...   =>  kbar = ys^2 Sbar (symmetric)

@@ -49,6 +49,10 @@ struct BoCandArgs {
     int df_external;                   // 1: F already holds d loss / d f (constraint-weighted path: the reductions ran outside)
     double* Uinplace; long strideU;    // optional (QT <= 8 kernels): [n_b x ldn] block that receives u_coef * U Sbar in place
     double u_coef;
+    // fused forms (8 % q == 0; BoGemm::gram / BoGemm::post):
+    const double* gram; long strideGram; int gram_tiles;  // forward: [row tile][ceil(N/8)][8 x 8] partial Grams of the BL block
+                                                           // produced by the GEMM epilogue; BL itself is not read
+    double* post; long stridePost;     // backward: [ceil(N/8)][8 x 8] <- u_coef * Sbar (block diagonal), instead of Uinplace
 };
 
 int bo_cand_fwd(const BoCandArgs& a, cudaStream_t stream);

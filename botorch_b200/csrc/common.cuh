@@ -78,7 +78,22 @@ struct BoGemm {
     const double* alpha_vec; // [batch] optional per-member factor multiplying alpha (LINEAR only)
     const double* E; long lde; long strideE;    // optional elementwise factor: C = (alpha*acc + beta*D) * E  (LINEAR only)
     double* C2; long ldc2; long strideC2;       // kernel epilogues: optional second output g(r), d k/dx_a = -g (x_a-x_b)/l^2
+    // Fused per-column-group pieces of the combined-root qLogNEI path.  Honoured by the TMA 64 x 64 kernel only: set them
+    // only when bo_gemm_fused_ok(g) says the launch will take it (LINEAR epilogue, alpha = 1, no D).
+    //   gram (forward): for every 64-row tile rt and every group of 8 adjacent columns, the 8 x 8 Gram
+    //     sum_r C[r][c1] C[r][c2] over the tile's rows r >= gram_row0, written to gram[z][rt][group][c1 * 8 + c2];
+    //     summed over rt in order by the consumer: the q x q Gram U^T U of a t-batch without a second pass over U.
+    //   post (backward): the k-range [post_k0, K) is accumulated FIRST, every 8-column group of that partial product is
+    //     multiplied from the right by post[z][group] (8 x 8, row-major), then the k-range [0, post_k0) is added:
+    //     A[:, k0:] (B[k0:, :] P) = (A[:, k0:] B[k0:, :]) P for block-diagonal P -- the adjoint U_bar = -2 U S_bar is
+    //     never materialised.
+    double* gram; long strideGram; int gram_row0;
+    const double* post; long stridePost; int post_k0;
 };
+
+#define BO_GRAM_BM 64  // row-tile height of the gram partials
+// 1 if bo_gemm_launch(g) will run the kernel that honours g.gram / g.post
+int bo_gemm_fused_ok(const BoGemm& g);
 
 int bo_gemm_launch(const BoGemm& g, cudaStream_t stream);
 // number of kernels launched by this library since the last reset (bench.py's gpu_launches claim)

@@ -302,6 +302,7 @@ struct TCfg {
     static constexpr int A_STAGE = BM * BK, B_STAGE = BK * BN;  // doubles
     static constexpr unsigned STAGE_BYTES = (unsigned)((A_STAGE + B_STAGE) * sizeof(double));
     static constexpr size_t SMEM = (size_t)STAGES * STAGE_BYTES + 2 * STAGES * sizeof(unsigned long long) + 128;
+    static_assert((size_t)CONSUMERS * (WN / 8) * 64 * sizeof(double) <= (size_t)STAGES * STAGE_BYTES, "gram partials");
     static_assert(BK % 4 == 0 && BN % 8 == 0 && BM <= 256 && BK <= 256 && BN / 8 <= 256, "TMA box limits");
 };
 
@@ -332,9 +333,12 @@ __device__ __forceinline__ void tma_load_4d(unsigned dst, const CUtensorMap* map
         : "memory");
 }
 
-template <class C>
+// MODE: 0 plain, 1 with the gram epilogue (BoGemm::gram), 2 with the mid-loop column-group transform (BoGemm::post).
+// Separate instantiations: the fused pieces must not cost the plain kernel registers.
+template <class C, int MODE>
 __global__ void __launch_bounds__(C::THREADS, C::MINB)
-dgemm_dmma_tma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, const BoGemm p,
+dgemm_dmma_tma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
+                      const __grid_constant__ CUtensorMap tmA2, const __grid_constant__ CUtensorMap tmB2, const BoGemm p,
                       const int za_step, const int zb_step) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     // 128-byte aligned tile area (TMA destination alignment), then the barriers
@@ -357,7 +361,12 @@ dgemm_dmma_tma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_cons
     if (p.tri == BO_TRI_A_LOWER) ke = min(p.K, m0 + C::BM + p.tri_off);
     else if (p.tri == BO_TRI_A_UPPER) kb = m0 > p.tri_off ? ((m0 - p.tri_off) / C::BK) * C::BK : 0;
     else if (p.tri == BO_TRI_B_LOWER) kb = (n0 / C::BK) * C::BK;
-    const int ntiles = ke > kb ? (ke - kb + C::BK - 1) / C::BK : 0;
+    // fused adjoint (p.post): tiles of [post_k0, ke) first (through tmA / tmB), then the tiles of [0, post_k0) through the
+    // second pair of maps, whose k extent ends at post_k0 (the tile that straddles it is zero-filled beyond)
+    constexpr bool has_post = (MODE == 2);
+    if (has_post) kb = p.post_k0;
+    const int n_first = ke > kb ? (ke - kb + C::BK - 1) / C::BK : 0;
+    const int ntiles = n_first + (has_post ? (p.post_k0 + C::BK - 1) / C::BK : 0);
 
     if (tid == 0) {
 #pragma unroll
@@ -384,9 +393,15 @@ dgemm_dmma_tma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_cons
                 mbar_expect_tx(full, C::STAGE_BYTES);
                 const unsigned a_dst = tiles_s + (unsigned)s * C::STAGE_BYTES;
                 const unsigned b_dst = a_dst + (unsigned)(C::A_STAGE * sizeof(double));
-                const int k0 = kb + kt * C::BK;
-                tma_load_4d(a_dst, &tmA, full, 0, m0, k0 / 4, z * za_step);
-                tma_load_4d(b_dst, &tmB, full, 0, k0, n0 / 8, z * zb_step);
+                if (kt < n_first) {
+                    const int k0 = kb + kt * C::BK;
+                    tma_load_4d(a_dst, &tmA, full, 0, m0, k0 / 4, z * za_step);
+                    tma_load_4d(b_dst, &tmB, full, 0, k0, n0 / 8, z * zb_step);
+                } else {
+                    const int k0 = (kt - n_first) * C::BK;
+                    tma_load_4d(a_dst, &tmA2, full, 0, m0, k0 / 4, z * za_step);
+                    tma_load_4d(b_dst, &tmB2, full, 0, k0, n0 / 8, z * zb_step);
+                }
             }
         }
     } else {
@@ -395,6 +410,32 @@ dgemm_dmma_tma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_cons
 #pragma unroll
             for (int j = 0; j < TN; j++) acc[i][j][0] = acc[i][j][1] = 0.0;
         for (int kt = 0; kt < ntiles; kt++) {
+            if (has_post && kt == n_first) {
+                // acc <- acc * P per 8-column group, on the tensor path: the accumulator block (8 rows x 8 columns, lane
+                // (g, t) holds columns 2t, 2t+1 of row g) is re-laid as the A operand of two m8n8k4 steps by 4 shuffles
+                // (column c lives in lane (g, c / 2), slot c % 2); P supplies the B fragments
+                const double* P = p.post + (long)z * p.stridePost;
+                const int src_lo = (lane & ~3) | (t >> 1), src_hi = src_lo | 2;
+#pragma unroll
+                for (int j = 0; j < TN; j++) {
+                    const int col0 = n0 + wn0 + j * 8;
+                    if (col0 >= p.N) continue;
+                    const double* Pg = P + (long)(col0 / 8) * 64;
+                    const double pb0 = Pg[t * 8 + g], pb1 = Pg[(4 + t) * 8 + g];
+#pragma unroll
+                    for (int i = 0; i < TM; i++) {
+                        const double x00 = __shfl_sync(0xffffffffu, acc[i][j][0], src_lo);
+                        const double x01 = __shfl_sync(0xffffffffu, acc[i][j][1], src_lo);
+                        const double x10 = __shfl_sync(0xffffffffu, acc[i][j][0], src_hi);
+                        const double x11 = __shfl_sync(0xffffffffu, acc[i][j][1], src_hi);
+                        double r0 = 0.0, r1 = 0.0;
+                        dmma884(r0, r1, (t & 1) ? x01 : x00, pb0);
+                        dmma884(r0, r1, (t & 1) ? x11 : x10, pb1);
+                        acc[i][j][0] = r0;
+                        acc[i][j][1] = r1;
+                    }
+                }
+            }
             const int s = kt % C::STAGES;
             mbar_wait(bars_s + 8u * s, (kt / C::STAGES) & 1);
             const double* as = tiles + (size_t)s * (C::A_STAGE + C::B_STAGE) + (wm0 + g) * 4 + t;
@@ -414,6 +455,48 @@ dgemm_dmma_tma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_cons
             __syncwarp();
             if (lane == 0) mbar_arrive(bars_s + 8u * (C::STAGES + s));
         }
+    }
+
+    if constexpr (MODE == 1) {
+        // Gram C_g^T C_g (8 x 8) of every 8-column group over this tile's rows >= gram_row0, on the tensor path: for a k4
+        // step over rows r..r+3 of an 8-row block both MMA operands are C[r + t][column g], which lives in lane
+        // (r % 8 + t, g / 2), slot g % 2 of the accumulator block -- 2 shuffles and a select per step.  Per-warp partials
+        // go through shared memory (the ring is idle by now) and are added over the warps stacked in M in a fixed order.
+        double* gpart = tiles;
+        __syncthreads();  // every warp is done reading the ring
+        if (warp < C::CONSUMERS) {
+#pragma unroll
+            for (int j = 0; j < TN; j++) {
+                double g0 = 0.0, g1 = 0.0;
+#pragma unroll
+                for (int i = 0; i < TM; i++) {
+                    const int row = m0 + wm0 + i * 8 + g;
+                    const bool valid = row >= p.gram_row0 && row < p.M;
+                    const double c0m = valid ? acc[i][j][0] : 0.0, c1m = valid ? acc[i][j][1] : 0.0;
+#pragma unroll
+                    for (int hh = 0; hh < 2; hh++) {
+                        const int src = ((hh * 4 + t) << 2) | (g >> 1);
+                        const double y0 = __shfl_sync(0xffffffffu, c0m, src);
+                        const double y1 = __shfl_sync(0xffffffffu, c1m, src);
+                        const double av = (g & 1) ? y1 : y0;
+                        dmma884(g0, g1, av, av);
+                    }
+                }
+                *reinterpret_cast<double2*>(gpart + (warp * TN + j) * 64 + g * 8 + 2 * t) = make_double2(g0, g1);
+            }
+        }
+        __syncthreads();
+        double* Gz = p.gram + (long)z * p.strideGram + (long)mt * ((p.N + 7) / 8) * 64;
+        for (int e = tid; e < (C::BN / 8) * 64; e += C::THREADS) {
+            const int jg = e / 64, pr = e % 64;
+            if (n0 + jg * 8 >= p.N) continue;
+            const int wn = jg / TN, j = jg % TN;
+            double s_ = 0.0;
+#pragma unroll
+            for (int wmi = 0; wmi < C::WARPS_M; wmi++) s_ += gpart[((wmi * C::WARPS_N + wn) * TN + j) * 64 + pr];
+            Gz[(long)(n0 / 8 + jg) * 64 + pr] = s_;
+        }
+        __syncthreads();  // the covariance epilogue below may stage through the same memory
     }
 
     double* __restrict__ Cz = p.C + (long)z * p.strideC;
@@ -577,20 +660,40 @@ bool tma_eligible(const BoGemm& g) {
     return encode_tiled_fn() != nullptr;
 }
 
+template <class C, int MODE>
+int launch_tma_mode(const BoGemm& g, cudaStream_t stream);
+
 template <class C>
 int launch_tma(const BoGemm& g, cudaStream_t stream) {
+    if (g.gram != nullptr && g.post != nullptr) return BO_ERR_INVALID;
+    if (g.gram != nullptr) return launch_tma_mode<C, 1>(g, stream);
+    if (g.post != nullptr) return launch_tma_mode<C, 2>(g, stream);
+    return launch_tma_mode<C, 0>(g, stream);
+}
+
+template <class C, int MODE>
+int launch_tma_mode(const BoGemm& g, cudaStream_t stream) {
     static bool attr_set = false;
     if (!attr_set) {
-        BO_CUDA_TRY(cudaFuncSetAttribute(dgemm_dmma_tma_kernel<C>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+        BO_CUDA_TRY(cudaFuncSetAttribute(dgemm_dmma_tma_kernel<C, MODE>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                          (int)C::SMEM));
         attr_set = true;
     }
     dim3 grid((g.N + C::BN - 1) / C::BN, (g.M + C::BM - 1) / C::BM, g.batch);
     if (grid.y > 65535u || grid.z > 65535u) return BO_ERR_UNSUPPORTED;
-    CUtensorMap tmA, tmB;
+    CUtensorMap tmA, tmB, tmA2, tmB2;
     if (!make_map(&tmA, g.A, 4, g.M, g.K / 4, g.lda, g.batch, g.strideA, C::BM, C::BK / 4) ||
         !make_map(&tmB, g.B, 8, g.K, (g.N + 7) / 8, g.ldb, g.batch, g.strideB, C::BK, C::BN / 8))
         return BO_ERR_INVALID;
+    tmA2 = tmA;
+    tmB2 = tmB;
+    if (g.post != nullptr) {  // the dense leading k-range [0, post_k0): same operands, k extent clipped at post_k0
+        if (g.post_k0 <= 0 || g.post_k0 % 4 != 0 || g.post_k0 >= g.K || g.epi != BO_EPI_LINEAR) return BO_ERR_INVALID;
+        if (!make_map(&tmA2, g.A, 4, g.M, g.post_k0 / 4, g.lda, g.batch, g.strideA, C::BM, C::BK / 4) ||
+            !make_map(&tmB2, g.B, 8, g.post_k0, (g.N + 7) / 8, g.ldb, g.batch, g.strideB, C::BK, C::BN / 8))
+            return BO_ERR_INVALID;
+    }
+    if (g.gram != nullptr && (C::BM != BO_GRAM_BM || g.epi != BO_EPI_LINEAR)) return BO_ERR_INVALID;
     ProfRec* rec = nullptr;
     if (g_prof_on) {
         if (g_prof_used == g_prof_recs.size()) {
@@ -603,7 +706,8 @@ int launch_tma(const BoGemm& g, cudaStream_t stream) {
         g_prof_flops += 2.0 * gemm_macs(g) * g.N * g.batch;
         BO_CUDA_TRY(cudaEventRecord(rec->a, stream));
     }
-    dgemm_dmma_tma_kernel<C><<<grid, C::THREADS, C::SMEM, stream>>>(tmA, tmB, g, (g.batch > 1 && g.strideA == 0) ? 0 : 1,
+    dgemm_dmma_tma_kernel<C, MODE><<<grid, C::THREADS, C::SMEM, stream>>>(tmA, tmB, tmA2, tmB2, g,
+                                                                  (g.batch > 1 && g.strideA == 0) ? 0 : 1,
                                                                   (g.batch > 1 && g.strideB == 0) ? 0 : 1);
     if (rec) BO_CUDA_TRY(cudaEventRecord(rec->b, stream));
     g_bo_launch_count++;
@@ -623,6 +727,21 @@ using TCfgCol = TCfg<128, 64, 16, 64, 32, 4, 2>;     // 4 consumer warps of 64 x
 using TCfgMid6 = TCfg<64, 64, 16, 32, 32, 6, 2>;     // deeper ring
 
 }  // namespace
+
+static bool takes_tma_mid(const BoGemm& g) {
+    static const int forced = [] { const char* e = getenv("BO_GEMM_CFG"); return e ? atoi(e) : -1; }();
+    static const bool use_tma = [] { const char* e = getenv("BO_GEMM_TMA"); return !e || atoi(e) != 0; }();
+    if (forced >= 0 || !use_tma || g.tile64) return false;
+    if (g.M <= 32 && g.N >= 1024 && g.K >= 64 && g.epi == BO_EPI_LINEAR && g.tri == BO_TRI_NONE) return false;  // skinny
+    const long tiles = (long)((g.M + 63) / 64) * ((g.N + 63) / 64) * g.batch;
+    return tiles >= 120 && g.K >= 64 && tma_eligible(g);
+}
+
+int bo_gemm_fused_ok(const BoGemm& g) {
+    if (g.M <= 0 || g.N <= 0 || g.batch <= 0) return 0;
+    if ((g.lda & 1) || (g.ldb & 1) || (g.ldc & 1) || (g.strideA & 1) || (g.strideB & 1) || (g.strideC & 1)) return 0;
+    return takes_tma_mid(g) ? 1 : 0;
+}
 
 int bo_gemm_launch(const BoGemm& g, cudaStream_t stream) {
     if (g.M <= 0 || g.N <= 0 || g.batch <= 0) return BO_OK;
@@ -672,8 +791,8 @@ int bo_gemm_launch(const BoGemm& g, cudaStream_t stream) {
     // TMA-staged 64 x 64 tiles (one producer warp + 4 DMMA warps, 3 CTAs/SM) wherever the tensor maps can describe the
     // operands: measured 36.4 TF dense against 34.8 for the cp.async form and 35.4 for cuBLAS (tools/gemm_bench.py,
     // profiles/r02_gemm_tma_sweep.txt).  BO_GEMM_TMA=0 switches back for A/B comparisons.
-    static const bool use_tma = [] { const char* e = getenv("BO_GEMM_TMA"); return !e || atoi(e) != 0; }();
-    if (use_tma && tiles(64, 64) >= 120 && g.K >= 64 && tma_eligible(g)) return launch_tma<TCfgMid>(g, stream);
+    if (takes_tma_mid(g)) return launch_tma<TCfgMid>(g, stream);
+    if (g.gram != nullptr || g.post != nullptr) return BO_ERR_INVALID;  // the caller did not ask bo_gemm_fused_ok
     if (tiles(64, 64) >= 120 || (g.M >= 48 && g.N >= 48 && tiles(32, 32) > 2048)) return launch_cfg<CfgT10>(g, stream);
     return launch_cfg<CfgSmall>(g, stream);
 }
