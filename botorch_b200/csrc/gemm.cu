@@ -440,17 +440,41 @@ dgemm_dmma_tma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_cons
             mbar_wait(bars_s + 8u * s, (kt / C::STAGES) & 1);
             const double* as = tiles + (size_t)s * (C::A_STAGE + C::B_STAGE) + (wm0 + g) * 4 + t;
             const double* bs = tiles + (size_t)s * (C::A_STAGE + C::B_STAGE) + C::A_STAGE + ((wn0 / 8) * C::BK + t) * 8 + g;
+            // k-tiles that cross the diagonal of a triangular A: the 8-row blocks whose entries are all zero over a k4 step
+            // are skipped (half of the work of those tiles; ~3% of a triangular product with 64-row tiles)
+            const int k0 = kb + kt * C::BK;
+            const bool edge = kt < n_first && ((p.tri == BO_TRI_A_UPPER && k0 < m0 + C::BM - p.tri_off) ||
+                                               (p.tri == BO_TRI_A_LOWER && k0 + C::BK > m0 + p.tri_off + 8));
+            if (!edge) {
 #pragma unroll
-            for (int kk = 0; kk < C::BK; kk += 4) {
-                double a[TM], b[TN];
+                for (int kk = 0; kk < C::BK; kk += 4) {
+                    double a[TM], b[TN];
 #pragma unroll
-                for (int i = 0; i < TM; i++) a[i] = as[(kk / 4) * C::BM * 4 + i * 32];
+                    for (int i = 0; i < TM; i++) a[i] = as[(kk / 4) * C::BM * 4 + i * 32];
 #pragma unroll
-                for (int j = 0; j < TN; j++) b[j] = bs[(j * C::BK + kk) * 8];
+                    for (int j = 0; j < TN; j++) b[j] = bs[(j * C::BK + kk) * 8];
 #pragma unroll
-                for (int i = 0; i < TM; i++)
+                    for (int i = 0; i < TM; i++)
 #pragma unroll
-                    for (int j = 0; j < TN; j++) dmma884(acc[i][j][0], acc[i][j][1], a[i], b[j]);
+                        for (int j = 0; j < TN; j++) dmma884(acc[i][j][0], acc[i][j][1], a[i], b[j]);
+                }
+            } else {
+#pragma unroll
+                for (int kk = 0; kk < C::BK; kk += 4) {
+                    double b[TN];
+#pragma unroll
+                    for (int j = 0; j < TN; j++) b[j] = bs[(j * C::BK + kk) * 8];
+#pragma unroll
+                    for (int i = 0; i < TM; i++) {
+                        const int r0 = m0 + wm0 + i * 8;
+                        const bool zero = (p.tri == BO_TRI_A_UPPER) ? (k0 + kk + 4 <= r0 - p.tri_off)
+                                                                    : (k0 + kk > r0 + 7 + p.tri_off);
+                        if (zero) continue;
+                        const double av = as[(kk / 4) * C::BM * 4 + i * 32];
+#pragma unroll
+                        for (int j = 0; j < TN; j++) dmma884(acc[i][j][0], acc[i][j][1], av, b[j]);
+                    }
+                }
             }
             __syncwarp();
             if (lane == 0) mbar_arrive(bars_s + 8u * (C::STAGES + s));
@@ -618,6 +642,253 @@ int launch_cfg(const BoGemm& g, cudaStream_t stream) {
     return BO_OK;
 }
 
+// ------------------------------------------------------------------------------------------------------------------
+// Persistent form of the TMA-staged kernel (LINEAR epilogue): a 1-D grid of (SMs x MINB) CTAs, each walking a fixed
+// list of output tiles.  The producer warp streams the k-tiles of one tile after another through the same ring, so
+// the first k-tiles of the NEXT tile land while the DMMA warps run the epilogue of the current one: no pipeline fill
+// per tile, which is where the triangular products (many short tiles) lost ~10% against the dense case.
+// Tiles are ordered heaviest first (row tile major) and dealt to the CTAs in alternating direction wave by wave
+// (boustrophedon), a static longest-processing-time schedule: no atomics, identical work list on both warp roles.
+// ------------------------------------------------------------------------------------------------------------------
+struct TileGeo {
+    int z, mt, m0, n0, kb, ke, n_first, ntiles;
+    bool skip;
+};
+
+template <class C, int MODE>
+__device__ __forceinline__ TileGeo tile_geometry(const BoGemm& p, long L, int gx, int gy, int gz) {
+    TileGeo q;
+    const int x = (int)(L % gx);
+    const int zz = (int)((L / gx) % gz);
+    const int y = (int)(L / ((long)gx * gz));
+    q.z = zz;
+    q.mt = (p.tri == BO_TRI_A_LOWER) ? (gy - 1 - y) : y;  // heavy (long k-range) row tiles first
+    q.m0 = q.mt * C::BM;
+    q.n0 = x * C::BN;
+    q.skip = p.out_lower && q.n0 > q.m0 + C::BM - 1;
+    q.kb = 0;
+    q.ke = p.K;
+    if (p.tri == BO_TRI_A_LOWER) q.ke = min(p.K, q.m0 + C::BM + p.tri_off);
+    else if (p.tri == BO_TRI_A_UPPER) q.kb = q.m0 > p.tri_off ? ((q.m0 - p.tri_off) / C::BK) * C::BK : 0;
+    else if (p.tri == BO_TRI_B_LOWER) q.kb = (q.n0 / C::BK) * C::BK;
+    if (MODE == 2) q.kb = p.post_k0;
+    q.n_first = q.ke > q.kb ? (q.ke - q.kb + C::BK - 1) / C::BK : 0;
+    q.ntiles = q.n_first + (MODE == 2 ? (p.post_k0 + C::BK - 1) / C::BK : 0);
+    return q;
+}
+
+__device__ __forceinline__ void consumer_bar(int threads) {
+    asm volatile("bar.sync 1, %0;\n" ::"r"(threads) : "memory");
+}
+
+template <class C, int MODE>
+__global__ void __launch_bounds__(C::THREADS, C::MINB)
+dgemm_dmma_tma_persistent_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
+                                 const __grid_constant__ CUtensorMap tmA2, const __grid_constant__ CUtensorMap tmB2,
+                                 const BoGemm p, const int za_step, const int zb_step, const int gx, const int gy,
+                                 const int gz) {
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    const unsigned raw = (unsigned)__cvta_generic_to_shared(smem_raw);
+    const unsigned pad = (128u - (raw & 127u)) & 127u;
+    double* tiles = reinterpret_cast<double*>(smem_raw + pad);
+    const unsigned tiles_s = raw + pad;
+    const unsigned bars_s = tiles_s + (unsigned)C::STAGES * C::STAGE_BYTES;  // full[STAGES], empty[STAGES]
+    // gram partials of the fused forward: their own region (the ring keeps filling during the epilogue)
+    double* gpart = reinterpret_cast<double*>(smem_raw + pad + (size_t)C::STAGES * C::STAGE_BYTES +
+                                              2 * C::STAGES * sizeof(unsigned long long));
+
+    const int tid = threadIdx.x;
+    const int warp = tid >> 5, lane = tid & 31;
+    const int g = lane >> 2, t = lane & 3;
+    const long total = (long)gx * gy * gz;
+    const long G = gridDim.x;
+    const long c = blockIdx.x;
+
+    if (tid == 0) {
+#pragma unroll
+        for (int s = 0; s < C::STAGES; s++) {
+            mbar_init(bars_s + 8u * s, 1);
+            mbar_init(bars_s + 8u * (C::STAGES + s), C::CONSUMERS);
+        }
+        asm volatile("fence.mbarrier_init.release.cluster;\n" ::: "memory");
+    }
+    __syncthreads();
+
+    constexpr int TM = C::WM / 8, TN = C::WN / 8;
+    const int wm0 = (warp / C::WARPS_N) * C::WM;
+    const int wn0 = (warp % C::WARPS_N) * C::WN;
+
+    if (warp == C::CONSUMERS) {
+        // ---- producer ----
+        if (lane == 0) {
+            long it = 0;  // k-tiles issued so far by this CTA (ring position)
+            for (long w = 0; w * G < total; w++) {
+                const long L = w * G + ((w & 1) ? (G - 1 - c) : c);
+                if (L >= total) continue;
+                const TileGeo q = tile_geometry<C, MODE>(p, L, gx, gy, gz);
+                if (q.skip) continue;
+                for (int kt = 0; kt < q.ntiles; kt++, it++) {
+                    const int s = (int)(it % C::STAGES);
+                    if (it >= C::STAGES) mbar_wait(bars_s + 8u * (C::STAGES + s), (unsigned)(((it / C::STAGES) - 1) & 1));
+                    const unsigned full = bars_s + 8u * s;
+                    mbar_expect_tx(full, C::STAGE_BYTES);
+                    const unsigned a_dst = tiles_s + (unsigned)s * C::STAGE_BYTES;
+                    const unsigned b_dst = a_dst + (unsigned)(C::A_STAGE * sizeof(double));
+                    if (kt < q.n_first) {
+                        const int k0 = q.kb + kt * C::BK;
+                        tma_load_4d(a_dst, &tmA, full, 0, q.m0, k0 / 4, q.z * za_step);
+                        tma_load_4d(b_dst, &tmB, full, 0, k0, q.n0 / 8, q.z * zb_step);
+                    } else {
+                        const int k0 = (kt - q.n_first) * C::BK;
+                        tma_load_4d(a_dst, &tmA2, full, 0, q.m0, k0 / 4, q.z * za_step);
+                        tma_load_4d(b_dst, &tmB2, full, 0, k0, q.n0 / 8, q.z * zb_step);
+                    }
+                }
+            }
+        }
+        return;
+    }
+
+    // ---- consumers ----
+    long it = 0;
+    for (long w = 0; w * G < total; w++) {
+        const long L = w * G + ((w & 1) ? (G - 1 - c) : c);
+        if (L >= total) continue;
+        const TileGeo q = tile_geometry<C, MODE>(p, L, gx, gy, gz);
+        if (q.skip) continue;
+        const int z = q.z, m0 = q.m0, n0 = q.n0;
+        double acc[TM][TN][2];
+#pragma unroll
+        for (int i = 0; i < TM; i++)
+#pragma unroll
+            for (int j = 0; j < TN; j++) acc[i][j][0] = acc[i][j][1] = 0.0;
+        for (int kt = 0; kt < q.ntiles; kt++, it++) {
+            if (MODE == 2 && kt == q.n_first) {
+                const double* P = p.post + (long)z * p.stridePost;
+                const int src_lo = (lane & ~3) | (t >> 1), src_hi = src_lo | 2;
+#pragma unroll
+                for (int j = 0; j < TN; j++) {
+                    const int col0 = n0 + wn0 + j * 8;
+                    if (col0 >= p.N) continue;
+                    const double* Pg = P + (long)(col0 / 8) * 64;
+                    const double pb0 = Pg[t * 8 + g], pb1 = Pg[(4 + t) * 8 + g];
+#pragma unroll
+                    for (int i = 0; i < TM; i++) {
+                        const double x00 = __shfl_sync(0xffffffffu, acc[i][j][0], src_lo);
+                        const double x01 = __shfl_sync(0xffffffffu, acc[i][j][1], src_lo);
+                        const double x10 = __shfl_sync(0xffffffffu, acc[i][j][0], src_hi);
+                        const double x11 = __shfl_sync(0xffffffffu, acc[i][j][1], src_hi);
+                        double r0 = 0.0, r1 = 0.0;
+                        dmma884(r0, r1, (t & 1) ? x01 : x00, pb0);
+                        dmma884(r0, r1, (t & 1) ? x11 : x10, pb1);
+                        acc[i][j][0] = r0;
+                        acc[i][j][1] = r1;
+                    }
+                }
+            }
+            const int s = (int)(it % C::STAGES);
+            mbar_wait(bars_s + 8u * s, (unsigned)((it / C::STAGES) & 1));
+            const double* as = tiles + (size_t)s * (C::A_STAGE + C::B_STAGE) + (wm0 + g) * 4 + t;
+            const double* bs = tiles + (size_t)s * (C::A_STAGE + C::B_STAGE) + C::A_STAGE + ((wn0 / 8) * C::BK + t) * 8 + g;
+            const int k0 = q.kb + kt * C::BK;
+            const bool edge = kt < q.n_first && ((p.tri == BO_TRI_A_UPPER && k0 < m0 + C::BM - p.tri_off) ||
+                                                 (p.tri == BO_TRI_A_LOWER && k0 + C::BK > m0 + p.tri_off + 8));
+            if (!edge) {
+#pragma unroll
+                for (int kk = 0; kk < C::BK; kk += 4) {
+                    double a[TM], b[TN];
+#pragma unroll
+                    for (int i = 0; i < TM; i++) a[i] = as[(kk / 4) * C::BM * 4 + i * 32];
+#pragma unroll
+                    for (int j = 0; j < TN; j++) b[j] = bs[(j * C::BK + kk) * 8];
+#pragma unroll
+                    for (int i = 0; i < TM; i++)
+#pragma unroll
+                        for (int j = 0; j < TN; j++) dmma884(acc[i][j][0], acc[i][j][1], a[i], b[j]);
+                }
+            } else {
+#pragma unroll
+                for (int kk = 0; kk < C::BK; kk += 4) {
+                    double b[TN];
+#pragma unroll
+                    for (int j = 0; j < TN; j++) b[j] = bs[(j * C::BK + kk) * 8];
+#pragma unroll
+                    for (int i = 0; i < TM; i++) {
+                        const int r0 = m0 + wm0 + i * 8;
+                        const bool zero = (p.tri == BO_TRI_A_UPPER) ? (k0 + kk + 4 <= r0 - p.tri_off)
+                                                                    : (k0 + kk > r0 + 7 + p.tri_off);
+                        if (zero) continue;
+                        const double av = as[(kk / 4) * C::BM * 4 + i * 32];
+#pragma unroll
+                        for (int j = 0; j < TN; j++) dmma884(acc[i][j][0], acc[i][j][1], av, b[j]);
+                    }
+                }
+            }
+            __syncwarp();
+            if (lane == 0) mbar_arrive(bars_s + 8u * (C::STAGES + s));
+        }
+
+        if constexpr (MODE == 1) {
+#pragma unroll
+            for (int j = 0; j < TN; j++) {
+                double g0 = 0.0, g1 = 0.0;
+#pragma unroll
+                for (int i = 0; i < TM; i++) {
+                    const int row = m0 + wm0 + i * 8 + g;
+                    const bool valid = row >= p.gram_row0 && row < p.M;
+                    const double c0m = valid ? acc[i][j][0] : 0.0, c1m = valid ? acc[i][j][1] : 0.0;
+#pragma unroll
+                    for (int hh = 0; hh < 2; hh++) {
+                        const int src = ((hh * 4 + t) << 2) | (g >> 1);
+                        const double y0 = __shfl_sync(0xffffffffu, c0m, src);
+                        const double y1 = __shfl_sync(0xffffffffu, c1m, src);
+                        const double av = (g & 1) ? y1 : y0;
+                        dmma884(g0, g1, av, av);
+                    }
+                }
+                *reinterpret_cast<double2*>(gpart + (warp * TN + j) * 64 + g * 8 + 2 * t) = make_double2(g0, g1);
+            }
+            consumer_bar(C::CONSUMERS * 32);
+            double* Gz = p.gram + (long)z * p.strideGram + (long)q.mt * ((p.N + 7) / 8) * 64;
+            for (int e = tid; e < (C::BN / 8) * 64; e += C::CONSUMERS * 32) {
+                const int jg = e / 64, pr = e % 64;
+                if (n0 + jg * 8 >= p.N) continue;
+                const int wn = jg / TN, j = jg % TN;
+                double s_ = 0.0;
+#pragma unroll
+                for (int wmi = 0; wmi < C::WARPS_M; wmi++) s_ += gpart[((wmi * C::WARPS_N + wn) * TN + j) * 64 + pr];
+                Gz[(long)(n0 / 8 + jg) * 64 + pr] = s_;
+            }
+            consumer_bar(C::CONSUMERS * 32);  // the next tile's partials reuse gpart
+        }
+
+        double* __restrict__ Cz = p.C + (long)z * p.strideC;
+        double* __restrict__ CTz = p.CT ? p.CT + (long)z * p.strideCT : nullptr;
+#pragma unroll
+        for (int i = 0; i < TM; i++) {
+            const int row = m0 + wm0 + i * 8 + g;
+            if (row >= p.M) continue;
+#pragma unroll
+            for (int j = 0; j < TN; j++) {
+                const int col = n0 + wn0 + j * 8 + 2 * t;
+                if (col >= p.N) continue;
+                const double v0 = epilogue_value(p, z, acc[i][j][0], row, col);
+                if (col + 1 < p.N) {
+                    const double v1 = epilogue_value(p, z, acc[i][j][1], row, col + 1);
+                    *reinterpret_cast<double2*>(Cz + (long)row * p.ldc + col) = make_double2(v0, v1);
+                    if (CTz) {
+                        CTz[(long)col * p.ldct + row] = v0;
+                        CTz[(long)(col + 1) * p.ldct + row] = v1;
+                    }
+                } else {
+                    Cz[(long)row * p.ldc + col] = v0;
+                    if (CTz) CTz[(long)col * p.ldct + row] = v0;
+                }
+            }
+        }
+    }
+}
+
 // ---- host side of the TMA variant -------------------------------------------------------------------------------
 typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
                                   const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
@@ -671,12 +942,31 @@ int launch_tma(const BoGemm& g, cudaStream_t stream) {
     return launch_tma_mode<C, 0>(g, stream);
 }
 
+int sm_count() {
+    static int sms = [] {
+        int dev = 0, n = 148;
+        if (cudaGetDevice(&dev) == cudaSuccess) cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev);
+        return n;
+    }();
+    return sms;
+}
+
 template <class C, int MODE>
 int launch_tma_mode(const BoGemm& g, cudaStream_t stream) {
+    // LINEAR epilogues run the persistent form; the covariance epilogues stage through the ring and keep one tile per CTA
+    // Measured (profiles/r02_ncu_gemm_persistent_vs_tiled.txt): the static persistent schedule LOSES 8-9% to one tile per
+    // CTA (dense 4096^3: 4.25 vs 3.89 ms; C3 step 1.71 vs 1.52 ms): the block scheduler's dynamic dispatch keeps every SM
+    // at 3 resident CTAs to the end (14.3 of 15 warps active), the static work lists leave 12.2.  Off unless
+    // BO_GEMM_PERSISTENT=1.
+    static const bool pers_on = [] { const char* e = getenv("BO_GEMM_PERSISTENT"); return e && atoi(e) != 0; }();
+    const bool persistent = pers_on && g.epi == BO_EPI_LINEAR;
+    constexpr size_t SMEM_P = C::SMEM + (size_t)C::CONSUMERS * (C::WN / 8) * 64 * sizeof(double);
     static bool attr_set = false;
     if (!attr_set) {
         BO_CUDA_TRY(cudaFuncSetAttribute(dgemm_dmma_tma_kernel<C, MODE>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                          (int)C::SMEM));
+        BO_CUDA_TRY(cudaFuncSetAttribute(dgemm_dmma_tma_persistent_kernel<C, MODE>,
+                                         cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SMEM_P));
         attr_set = true;
     }
     dim3 grid((g.N + C::BN - 1) / C::BN, (g.M + C::BM - 1) / C::BM, g.batch);
@@ -706,9 +996,16 @@ int launch_tma_mode(const BoGemm& g, cudaStream_t stream) {
         g_prof_flops += 2.0 * gemm_macs(g) * g.N * g.batch;
         BO_CUDA_TRY(cudaEventRecord(rec->a, stream));
     }
-    dgemm_dmma_tma_kernel<C, MODE><<<grid, C::THREADS, C::SMEM, stream>>>(tmA, tmB, tmA2, tmB2, g,
-                                                                  (g.batch > 1 && g.strideA == 0) ? 0 : 1,
-                                                                  (g.batch > 1 && g.strideB == 0) ? 0 : 1);
+    const int za = (g.batch > 1 && g.strideA == 0) ? 0 : 1, zb = (g.batch > 1 && g.strideB == 0) ? 0 : 1;
+    if (persistent) {
+        const long total = (long)grid.x * grid.y * grid.z;
+        const long slots = (long)sm_count() * C::MINB;
+        const unsigned ctas = (unsigned)(total < slots ? total : slots);
+        dgemm_dmma_tma_persistent_kernel<C, MODE><<<ctas, C::THREADS, (MODE == 1 ? SMEM_P : C::SMEM), stream>>>(
+            tmA, tmB, tmA2, tmB2, g, za, zb, (int)grid.x, (int)grid.y, (int)grid.z);
+    } else {
+        dgemm_dmma_tma_kernel<C, MODE><<<grid, C::THREADS, C::SMEM, stream>>>(tmA, tmB, tmA2, tmB2, g, za, zb);
+    }
     if (rec) BO_CUDA_TRY(cudaEventRecord(rec->b, stream));
     g_bo_launch_count++;
     BO_CUDA_TRY(cudaGetLastError());
@@ -791,7 +1088,12 @@ int bo_gemm_launch(const BoGemm& g, cudaStream_t stream) {
     // TMA-staged 64 x 64 tiles (one producer warp + 4 DMMA warps, 3 CTAs/SM) wherever the tensor maps can describe the
     // operands: measured 36.4 TF dense against 34.8 for the cp.async form and 35.4 for cuBLAS (tools/gemm_bench.py,
     // profiles/r02_gemm_tma_sweep.txt).  BO_GEMM_TMA=0 switches back for A/B comparisons.
-    if (takes_tma_mid(g)) return launch_tma<TCfgMid>(g, stream);
+    if (takes_tma_mid(g)) {
+        // 64 x 128 tiles (8 DMMA warps, 2 CTAs/SM) halve the per-tile fixed cost on wide problems; BO_GEMM_WIDE=0 for A/B
+        static const bool wide = [] { const char* e = getenv("BO_GEMM_WIDE"); return e && atoi(e) != 0; }();
+        if (wide && g.N >= 2048) return launch_tma<TCfgRow>(g, stream);
+        return launch_tma<TCfgMid>(g, stream);
+    }
     if (g.gram != nullptr || g.post != nullptr) return BO_ERR_INVALID;  // the caller did not ask bo_gemm_fused_ok
     if (tiles(64, 64) >= 120 || (g.M >= 48 && g.N >= 48 && tiles(32, 32) > 2048)) return launch_cfg<CfgT10>(g, stream);
     return launch_cfg<CfgSmall>(g, stream);
