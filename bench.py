@@ -481,13 +481,14 @@ def _run_ours(args):
         torch.set_num_threads(max(1, (os.cpu_count() or 1) // ws))  # torchrun exports OMP_NUM_THREADS=1
         bdist.warm_up(dev)
         world_group = dist.group.WORLD if ws > 1 else None
-        r_n = strong_c3(dev, world_group, maxiter=20, factor_mode="broadcast")
-        r_1 = r_n
-        if ws > 1:
+        r_1 = None
+        if ws > 1:  # the single-GPU time of the same job first, on rank 0 alone (the other ranks wait at the barrier)
             if rank == 0:
                 with _Solo(bdist, True):
                     r_1 = strong_c3(dev, None, maxiter=20, factor_mode="recompute")
             barrier()
+        r_n = strong_c3(dev, world_group, maxiter=20, factor_mode="broadcast")
+        r_1 = r_n if r_1 is None else r_1
         strong = {"scaling": "strong", "what": "one optimize_acqf: 512 restarts + 32768 raw samples in total over N GPUs, "
                   "timed from the model's factorisation to the gathered best candidate (device L-BFGS, maxiter 20)",
                   "n_gpus": ws, "total_ms": r_n["total_ms"], "single_gpu_total_ms": r_1["total_ms"],
