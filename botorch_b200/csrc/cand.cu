@@ -39,65 +39,29 @@ __device__ __forceinline__ double kern_dfactor(int kernel_id, double r2, double 
 // log(tau*(softplus(u) + 0.1/(1+u^2))), u = z/tau   (torch softplus: identity above threshold 20)
 __device__ __forceinline__ double log_fatplus(double z, double tau, double inv_tau) {
     const double u = z * inv_tau;
-    // exp(u) underflows to exactly 0 below -746: skipping exp/log1p there is bit-identical and removes two of the three
-    // transcendentals for the bulk of the samples (tau = 1e-6 puts |u| in the 1e4..1e6 range)
-    if (u < -746.0) return log(0.1 * tau) - log(fma(u, u, 1.0));  // softplus == 0: log(tau * 0.1 / (1 + u^2)), no division
-    const double sp = (u > 20.0) ? u : log1p(exp(u));
-    return log(tau * (sp + 0.1 * (1.0 / (1.0 + u * u))));
+    // log(tau * (softplus(u) + 0.1 / (1 + u^2))) as the reference evaluates it.  tau = 1e-6 puts |u| in the 1e4..1e6 range
+    // for the bulk of the samples: softplus is u above torch's threshold 20 and exp(u) underflows to exactly 0 below
+    // -746, so both tails share ONE division and ONE log -- a warp whose lanes sit on both sides of zero executes this
+    // code once instead of one tail after the other; only -746 <= u <= 20 pays for exp and log1p.
+    double sp = (u > 20.0) ? u : 0.0;
+    if (u >= -746.0 && u <= 20.0) sp = log1p(exp(u));
+    return log(tau * (sp + 0.1 * (1.0 / fma(u, u, 1.0))));
 }
 // d log_fatplus / dz
 __device__ __forceinline__ double dlog_fatplus(double z, double tau, double inv_tau) {
     const double u = z * inv_tau;
-    if (u < -746.0) return -2.0 * u * inv_tau / fma(u, u, 1.0);  // softplus == sigmoid == 0: d/dz log(0.1 / (1 + u^2))
-    double sp, sig;
-    if (u > 20.0) { sp = u; sig = 1.0; }
-    else { const double e = exp(u); sp = log1p(e); sig = e / (e + 1.0); }
-    const double c = 1.0 / (1.0 + u * u);
+    double sp = (u > 20.0) ? u : 0.0, sig = (u > 20.0) ? 1.0 : 0.0;
+    if (u >= -746.0 && u <= 20.0) {
+        const double e = exp(u);
+        sp = log1p(e);
+        sig = e / (e + 1.0);
+    }
+    const double c = 1.0 / fma(u, u, 1.0);
     const double val = sp + 0.1 * c;
     if (!(val > 0.0)) return 0.0;
     return (sig - 0.2 * u * c * c) / (val * tau);
 }
 __device__ __forceinline__ double pareto2(double u) { return 2.0 / (2.0 + 2.0 * u + u * u); }
-
-// Reductions over a group of W adjacent lanes (W a power of two <= 32): fixed xor-shuffle trees, every lane gets the result.
-template <int W>
-__device__ __forceinline__ double group_max(double v) {
-#pragma unroll
-    for (int o = W / 2; o > 0; o >>= 1) v = fmax(v, __shfl_xor_sync(0xffffffffu, v, o));
-    return v;
-}
-template <int W>
-__device__ __forceinline__ double group_sum(double v) {
-#pragma unroll
-    for (int o = W / 2; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
-    return v;
-}
-// fatmax over the W lanes of a group (lane j holds x_j, -inf on the lanes j >= q): the cooperative form of fatmax_q
-template <int W>
-__device__ __forceinline__ double fatmax_group(double x, double tau) {
-    const double M = group_max<W>(x);
-    if (isinf(M)) return group_sum<W>(x == M ? x : 0.0);  // group-uniform branch
-    const double sum = group_sum<W>(pareto2((M - x) * (1.0 / tau)));
-    return M + tau * log(sum);
-}
-// ... and of fatmax_q_grad: returns the value, g = d fatmax / d x_j of this lane (`valid`: j < q)
-template <int W>
-__device__ __forceinline__ double fatmax_group_grad(double x, bool valid, double tau, double& g) {
-    const double M = group_max<W>(x);
-    if (isinf(M)) {
-        g = (valid && x == M) ? 1.0 : 0.0;
-        return group_sum<W>(x == M ? x : 0.0);
-    }
-    const double u = (M - x) * (1.0 / tau);
-    const double pr = pareto2(u);
-    const double sum = group_sum<W>(pr);
-    const double nties = group_sum<W>((valid && x == M) ? 1.0 : 0.0);
-    g = (!valid || isinf(u)) ? 0.0 : pr * pr * (1.0 + u);
-    g *= 1.0 / sum;
-    const double rest = (1.0 - group_sum<W>(g)) / nties;  // amax subgradient, split evenly among ties (torch.amax)
-    if (valid && x == M) g += rest;
-    return M + tau * log(sum);
-}
 
 // fatmax over x[0..q) (alpha = 2) with the infinity handling of _inf_max_helper.  QT >= q is a compile-time bound:
 // every loop is fully unrolled with a (j < q) guard so that the per-sample arrays stay in registers.
@@ -449,7 +413,7 @@ __device__ __forceinline__ double pair_r2(const double* X, int d, const double* 
 }
 
 template <int QT>
-__global__ void __launch_bounds__(CAND_THREADS, (QT <= 8 ? 4 : 1)) cand_fwd_kernel(const BoCandArgs a) {
+__global__ void __launch_bounds__(CAND_THREADS, (QT <= 4 ? 6 : (QT <= 8 ? 4 : 1))) cand_fwd_kernel(const BoCandArgs a) {
     extern __shared__ __align__(16) double sm[];
     __shared__ double red[CAND_THREADS / 32];
     __shared__ int s_info;
@@ -540,49 +504,6 @@ __global__ void __launch_bounds__(CAND_THREADS, (QT <= 8 ? 4 : 1)) cand_fwd_kern
     double local_max = -INFINITY;
     const bool plain = (a.reduction == BO_REDUCE_PLAIN);
     const double inv_tau_relu = 1.0 / a.tau_relu;
-    if constexpr (QT <= 8) {
-        // one thread per (sample, point): QT adjacent lanes share a sample, so the row segment F[s][c0..c0+q) is one
-        // contiguous read, the transcendental code exists once (the per-sample form inlined it QT times and the kernel
-        // stalled on instruction fetch), and the q-reduction is a shuffle tree inside the lane group
-        const int j = tid % QT;
-        const bool jv = j < q;
-        double lrow[QT];
-#pragma unroll
-        for (int k = 0; k < QT; k++) lrow[k] = (jv && k <= j) ? c.Lq[j * q + k] : 0.0;
-        const double muj = jv ? c.mu[j] : 0.0;
-        constexpr int U = 4;  // samples in flight per thread: their loads are issued together (the rows come from DRAM)
-        for (int base = 0; base < a.S * QT; base += U * T) {
-            double fv[U], bfv[U];
-#pragma unroll
-            for (int u = 0; u < U; u++) {
-                const int s = (base + u * T + tid) / QT;
-                const bool v = s < a.S && jv;
-                fv[u] = (v && !a.f_zero) ? F[(long)s * a.ldn + c0 + j] : 0.0;
-                bfv[u] = v ? a.best_f[(long)z * a.Sp + s] : 0.0;
-            }
-#pragma unroll
-            for (int u = 0; u < U; u++) {
-                const int s = (base + u * T + tid) / QT;
-                const bool sv = s < a.S;
-                double li = -INFINITY;
-                if (sv && jv) {
-                    double v = fv[u] + muj;
-                    const double* zrow = a.Zq + (long)s * q;
-#pragma unroll
-                    for (int k = 0; k < QT; k++)
-                        if (k <= j) v += lrow[k] * zrow[k];
-                    F[(long)s * a.ldn + c0 + j] = v;
-                    if (!isfinite(v)) bad = 1;
-                    li = plain ? fmax(a.obj_w * v - bfv[u], 0.0) : log_fatplus(a.obj_w * v - bfv[u], a.tau_relu, inv_tau_relu);
-                }
-                const double m = plain ? group_max<QT>(li) : fatmax_group<QT>(li, a.tau_max);
-                if (sv && j == 0) {
-                    c.fm[s] = m;
-                    local_max = fmax(local_max, m);
-                }
-            }
-        }
-    } else
     for (int s = tid; s < a.S; s += T) {
         double li[QT], zq[QT];
         const double bf = a.best_f[(long)z * a.Sp + s];
@@ -649,7 +570,7 @@ namespace {
 //   out: F <- d loss / d f ;  Sbar = adjoint of the Schur block (symmetric);
 //        Vbar row n <- y_std * d loss / d mu ;  gradX <- contribution of k(X, X)
 template <int QT>
-__global__ void __launch_bounds__(CAND_THREADS, (QT <= 8 ? 4 : 1)) cand_bwd_kernel(const BoCandArgs a) {
+__global__ void __launch_bounds__(CAND_THREADS, (QT <= 4 ? 6 : (QT <= 8 ? 4 : 1))) cand_bwd_kernel(const BoCandArgs a) {
     extern __shared__ __align__(16) double sm[];
     const int q = a.q, b = blockIdx.x, z = blockIdx.y, tid = threadIdx.x, T = blockDim.x;
     const int c0 = b * q;
@@ -675,66 +596,6 @@ __global__ void __launch_bounds__(CAND_THREADS, (QT <= 8 ? 4 : 1)) cand_bwd_kern
     for (int j = 0; j < QT; j++) am[j] = 0.0;
 #pragma unroll
     for (int p = 0; p < PT; p++) al[p] = 0.0;
-    if constexpr (QT <= 8) {
-        // one thread per (sample, point), as in the forward kernel: lane j of a group of QT owns point j of its sample and
-        // accumulates mu_bar[j] and row j of Lbar over its samples; equal-j lanes are then added by a fixed shuffle tree
-        const int j = tid % QT, lane = tid & 31, warp = tid >> 5;
-        const bool jv = j < q;
-        double amj = 0.0, alj[QT];
-#pragma unroll
-        for (int k = 0; k < QT; k++) alj[k] = 0.0;
-        for (int base = 0; base < a.S * QT; base += T) {
-            const int s = (base + tid) / QT;
-            const bool v = (s < a.S) && jv;
-            double df = 0.0;
-            if (a.df_external) {  // F already holds d loss / d f: only the accumulations below
-                if (v) df = F[(long)s * a.ldn + c0 + j];
-            } else {
-                const double f = v ? F[(long)s * a.ldn + c0 + j] : 0.0;
-                const double bf = v ? a.best_f[(long)z * a.Sp + s] : 0.0;
-                const double li = !v ? -INFINITY
-                                     : (plain ? fmax(a.obj_w * f - bf, 0.0)
-                                              : log_fatplus(a.obj_w * f - bf, a.tau_relu, inv_tau_relu));
-                if (plain) {  // mean over samples; amax spreads its gradient evenly over tied maxima
-                    const double m = group_max<QT>(li);
-                    const double ties = group_sum<QT>((v && li == m) ? 1.0 : 0.0);
-                    if (v && li == m && a.obj_w * f - bf >= 0.0) df = a.obj_w * g / ((double)a.S * ties);
-                } else {
-                    double gm;
-                    const double m = fatmax_group_grad<QT>(li, v, a.tau_max, gm);
-                    // logmeanexp over samples: softmax weight; +-inf maximum -> unit gradient on the infinite entries
-                    double w = 0.0;
-                    if (j == 0) w = isinf(lse) ? ((m == lse) ? 1.0 : 0.0) : exp(m - lse);
-                    w = __shfl_sync(0xffffffffu, w, lane & ~(QT - 1));
-                    if (v) {
-                        const double dli = isinf(li) ? 0.0 : dlog_fatplus(a.obj_w * f - bf, a.tau_relu, inv_tau_relu);
-                        df = a.obj_w * g * w * gm * dli;
-                    }
-                }
-                if (v) F[(long)s * a.ldn + c0 + j] = df;
-            }
-            if (v) {
-                amj += df;
-                const double* zrow = a.Zq + (long)s * q;
-#pragma unroll
-                for (int k = 0; k < QT; k++)
-                    if (k <= j) alj[k] += df * zrow[k];
-            }
-        }
-#pragma unroll
-        for (int o = QT; o < 32; o <<= 1) {
-            amj += __shfl_xor_sync(0xffffffffu, amj, o);
-#pragma unroll
-            for (int k = 0; k < QT; k++) alj[k] += __shfl_xor_sync(0xffffffffu, alj[k], o);
-        }
-        if (lane < QT) {
-            double* rw = red + warp * (QT + PT);
-            rw[j] = amj;
-#pragma unroll
-            for (int k = 0; k < QT; k++)
-                if (k <= j) rw[QT + j * (j + 1) / 2 + k] = alj[k];
-        }
-    } else
     for (int s = tid; s < a.S; s += T) {
         double f[QT], li[QT], gm[QT], zq[QT];
         if (a.df_external) {  // F already holds d loss / d f: only the accumulations below
@@ -792,7 +653,7 @@ __global__ void __launch_bounds__(CAND_THREADS, (QT <= 8 ? 4 : 1)) cand_bwd_kern
             for (int k = 0; k <= j; k++) al[p++] += df * zq[k];
         }
     }
-    if constexpr (QT > 8) {
+    {
         const int warp = tid >> 5, lane = tid & 31;
         double both[QT + PT];
 #pragma unroll
