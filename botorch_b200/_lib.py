@@ -67,6 +67,8 @@ class BoNEI(C.Structure):
         ("no_baseline", C.c_int32),
         ("obj_weight", C.c_double),
         ("external_df", C.c_int32),
+        ("schur_jitter", C.c_double),
+        ("schur_fixed", C.c_int32),
     ]
 
 

@@ -26,7 +26,7 @@ from torch import Tensor
 from torch.nn import Module
 
 from . import engine
-from .exceptions import BotorchWarning, NumericalWarning, NumericsWarning, UnsupportedError
+from .exceptions import BotorchWarning, NanError, NotPSDError, NumericalWarning, NumericsWarning, UnsupportedError
 from .posteriors import MCMC_DIM
 from .models import Model, _FusedExactGP
 from .sampling import MCSampler, get_sampler
@@ -245,12 +245,105 @@ class _FusedImprovementBase(AcquisitionFunction):
             )
         self._set_sampler(q_in=q)
         acq, info = _QLogNEIFunction.apply(Xf, self._nei, self._Zq, self.tau_relu, self.tau_max)  # taus unused when not _log
-        self._warn_on_failures(info)
+        if self._strict_numerics or not (torch.is_grad_enabled() and Xf.requires_grad):
+            # no gradient is being recorded (raw-sample sweeps, final evaluations: the caller reads the values next anyway),
+            # or a caller asked for it: look at the failure flags of THIS call now and resolve them before returning
+            failed = self._failed_tbatches(info)
+            if failed is not None and not self._nei.c.no_baseline:
+                acq = self._forward_resolved(Xf, failed, acq)
+            elif failed is not None:  # fixed-incumbent family: no cached baseline root to fall back from
+                warnings.warn("The q x q posterior covariance could not be factored; the affected t-batches were "
+                              "evaluated without their root.", BotorchWarning, stacklevel=3)  # fmt: skip
+        else:
+            self._warn_on_failures(info)
         if self.model._is_ensemble:  # t_batch_mode_transform: (log)mean over the hyperparameter samples
             acq = torch.logsumexp(acq, dim=0) - math.log(acq.shape[0]) if self._log else acq.mean(dim=0)
         else:
             acq = acq[0]
         return acq.reshape(batch_shape)
+
+    # -- numerical failures: the reference's fallback to standard sampling (cached_cholesky.py:139-165) ---------------------
+    _strict_numerics = False
+    last_call_failed = False
+
+    def strict_numerics(self, on: bool = True) -> None:
+        """Check the failure flags of every call before it returns, also while a gradient is recorded (one host wait per
+        forward).  ``optim.HostEvaluator`` switches it on to redo an evaluation whose deferred check failed."""
+        self._strict_numerics = bool(on)
+
+    def _failed_tbatches(self, info: Tensor) -> Optional[Tensor]:
+        """Indices of the t-batches whose cached update failed in the call that produced ``info`` (waits for it), or None.
+        Jitter retries that succeeded (info > 0) only warn, as psd_safe_cholesky does."""
+        if info.numel() == 2 and info.dim() == 1:  # graph replay: (min, max) of the flags; the full array is static
+            lo, hi = (int(v) for v in info.tolist())
+            full = None
+        else:
+            lo, hi = int(info.min()), int(info.max())
+            full = info
+        if hi > 0:
+            warnings.warn(
+                f"A not p.d., added jitter of {1e-8 * 10 ** (hi - 1):.1e} to the diagonal", NumericalWarning, stacklevel=4
+            )
+        if lo >= 0:
+            return None
+        if full is None:
+            full = self._nei.last_graph_info
+        return torch.nonzero((full < 0).any(dim=0)).view(-1)
+
+    def _forward_resolved(self, Xf: Tensor, failed: Tensor, acq: Tensor) -> Tensor:
+        """Re-evaluate the t-batches ``failed`` the way the reference does when ``sample_cached_cholesky`` raises
+        ``NanError`` / ``NotPSDError``: warn, then sample from the JOINT posterior over [X_baseline; X]
+        (``get_posterior_samples`` -> ``psd_safe_cholesky`` of the (n_b+q) covariance) and keep the last q rows.
+
+        The joint factor with jitter delta on its diagonal is [[L_b', 0], [Sigma_qb L_b'^-T, chol(Schur' + delta I)]] with
+        L_b' = chol(Sigma_bb + delta I): the cached update with the baseline block re-factored under delta and the q x q
+        block under the same delta.  So each delta of psd_safe_cholesky's schedule (0, 1e-8 ... 1e-3) gets a temporary
+        baseline state and the SAME fused kernels (values and gradients); ``best_f`` stays the cached one, as in the
+        reference (``_baseline_best_f`` is not recomputed on this path).  A t-batch that fails every delta raises
+        ``NotPSDError`` (``NanError`` for NaN inputs) like ``psd_safe_cholesky``.  The reference falls back for the whole
+        call; the t-batches that did not fail are identical on both routes (delta = 0), so only the failed ones move."""
+        warnings.warn(
+            "Low-rank cholesky updates failed due NaNs or due to an ill-conditioned covariance matrix. "
+            "Falling back to standard sampling.",
+            BotorchWarning,
+            stacklevel=4,
+        )
+        if bool(torch.isnan(Xf[failed]).any()):
+            raise NanError(f"cholesky: {int(torch.isnan(Xf[failed]).sum())} of {Xf[failed].numel()} elements are NaN.")
+        nei = self._nei
+        for ge in nei.__dict__.get("_graphs", {}).values():
+            ge.busy = False  # the failed forward is dropped below: its backward will never run
+        # the call that failed leaves the autograd graph altogether (its backward would push NaNs through the broken state):
+        # the t-batches that were fine are evaluated again on their own
+        B = Xf.shape[0]
+        ok_mask = torch.ones(B, dtype=torch.bool, device=Xf.device)
+        ok_mask[failed] = False
+        ok = torch.nonzero(ok_mask).view(-1)
+        out = torch.zeros_like(acq.detach())
+        if ok.numel():
+            a_ok, _ = _QLogNEIFunction.apply(Xf[ok].contiguous(), nei, self._Zq, self.tau_relu, self.tau_max)
+            out = out.index_copy(1, ok, a_ok)
+        todo = failed
+        for i in range(-1, engine.CHOLESKY_MAX_TRIES):
+            delta = 0.0 if i < 0 else engine.CHOLESKY_JITTER * (10**i)
+            if i >= 0:
+                warnings.warn(f"A not p.d., added jitter of {delta:.1e} to the diagonal", NumericalWarning, stacklevel=4)
+            tmp = engine.NEIState(nei.gp, nei.X_b, nei.Z_b, reduction=nei.c.reduction, obj_weight=nei.c.obj_weight,
+                                  forced_jitter=delta)  # fmt: skip
+            if tmp.setup_failed:
+                continue
+            tmp.best_f_pad.copy_(nei.best_f_pad)
+            a, info = _QLogNEIFunction.apply(Xf[todo].contiguous(), tmp, self._Zq, self.tau_relu, self.tau_max)
+            if info.numel() != a.numel():  # graph replay hands over (min, max) only: read the static array
+                info = tmp.last_graph_info
+            good = (info.reshape(a.shape) >= 0).all(dim=0)
+            idx = todo[good]
+            if idx.numel():
+                out = out.index_copy(1, idx, a[:, good])
+            todo = todo[~good]
+            if todo.numel() == 0:
+                return out
+        raise NotPSDError(f"Matrix not positive definite after repeatedly adding jitter up to {delta:.1e}.")
 
     def _warn_on_failures(self, info: Tensor) -> None:
         """Queue the failure flags of this call; report the flags of the previous one.
@@ -270,21 +363,27 @@ class _FusedImprovementBase(AcquisitionFunction):
         self._info_event.record()
         self._info_pending = True
 
-    def check_numerics(self) -> None:
-        """Emit the warnings of the most recent evaluation (waits for it if it is still running)."""
+    def check_numerics(self, quiet: bool = False) -> None:
+        """Emit the warnings of the most recent evaluation (waits for it if it is still running); ``last_call_failed`` tells
+        whether its cached update failed (``quiet``: only set the flag)."""
         if not self._info_pending:
             return
         self._info_event.synchronize()
         self._info_pending = False
         lo, hi = int(self._info_host[0]), int(self._info_host[1])
+        self.last_call_failed = lo < 0
+        if quiet:
+            return
         if hi > 0:
             warnings.warn(
                 f"A not p.d., added jitter of {1e-8 * 10 ** (hi - 1):.1e} to the diagonal", NumericalWarning, stacklevel=3
             )
         if lo < 0:
             warnings.warn(
-                "Low-rank cholesky updates failed due NaNs or due to an ill-conditioned covariance matrix. "
-                "The affected t-batches were evaluated without their q x q root.",
+                "Low-rank cholesky updates failed due NaNs or due to an ill-conditioned covariance matrix in a call "
+                "whose flags were read late (a gradient was being recorded); its affected t-batches were evaluated "
+                "without their q x q root.  gen_candidates_scipy re-evaluates such a call through the reference's "
+                "fallback; use acqf.strict_numerics() to check every call before it returns.",
                 BotorchWarning,
                 stacklevel=3,
             )

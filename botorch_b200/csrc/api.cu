@@ -526,6 +526,8 @@ BoCandArgs cand_args(const bo_gp* gp, const bo_nei* nei, int B, int q, const dou
     a.tau_relu = tau_relu; a.tau_max = tau_max;
     a.reduction = nei ? nei->reduction : BO_REDUCE_LOG;
     a.obj_w = (nei && nei->obj_weight != 0.0) ? nei->obj_weight : 1.0;
+    a.schur_jitter = nei ? nei->schur_jitter : 0.0;
+    a.schur_fixed = nei ? nei->schur_fixed : 0;
     a.ldn = w.ldn;
     a.V = w.W1; a.strideV = w.regionStride;
     a.BL = w.W3; a.strideBL = w.regionStride;

@@ -483,8 +483,9 @@ __global__ void __launch_bounds__(CAND_THREADS, (QT <= 4 ? 6 : (QT <= 8 ? 4 : 1)
         if (has_nan) {
             code = -1;
         } else {
-            double jit = 0.0;
-            for (int attempt = 0; attempt <= 6; attempt++) {
+            double jit = a.schur_fixed ? a.schur_jitter : 0.0;
+            const int last = a.schur_fixed ? 0 : 6;  // fixed jitter (joint-factorisation fallback): one attempt
+            for (int attempt = 0; attempt <= last; attempt++) {
 #pragma unroll
                 for (int k = 0; k < QT; k++) r[k] = row0[k] + ((k == lane) ? jit : 0.0);
                 if (chol_warp<QT>(r, q, lane)) { code = attempt; break; }

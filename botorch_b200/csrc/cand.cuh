@@ -52,6 +52,7 @@ struct BoCandArgs {
     // fused forms (8 % q == 0; BoGemm::gram / BoGemm::post):
     const double* gram; long strideGram; int gram_tiles;  // forward: [row tile][ceil(N/8)][8 x 8] partial Grams of the BL block
                                                            // produced by the GEMM epilogue; BL itself is not read
+    double schur_jitter; int schur_fixed;  // forward: one factorisation attempt of the q x q block with this jitter (bo_nei)
     double* post; long stridePost;     // backward: [ceil(N/8)][8 x 8] <- u_coef * Sbar (block diagonal), instead of Uinplace
 };
 

@@ -323,7 +323,7 @@ class NEIState:
     """Baseline factors of qLogNEI (V_b, L_b and its inverse, base samples, best_f) and the fused fwd/bwd."""
 
     def __init__(self, gp: GPState, X_baseline: Tensor, Z_b: Tensor, setup: bool = True,
-                 reduction: int = REDUCE_LOG, obj_weight: float = 1.0) -> None:  # fmt: skip
+                 reduction: int = REDUCE_LOG, obj_weight: float = 1.0, forced_jitter: Optional[float] = None) -> None:  # fmt: skip
         dev = gp.device
         self.gp = gp
         self.device = dev
@@ -374,6 +374,13 @@ class NEIState:
                                    ptr(self.info), _lib.stream_ptr(dev)))  # fmt: skip
             return self.info.clone()
 
+        if forced_jitter is not None:
+            # the joint-factorisation fallback (acquisition._FusedImprovementBase._forward_resolved): ONE attempt with this
+            # jitter on the baseline block and, in the forward kernel, the same jitter on every q x q block
+            self.jitter = torch.full((M,), float(forced_jitter), dtype=torch.float64, device=dev)
+            self.setup_failed = bool(run(self.jitter).any())
+            self.c.schur_jitter, self.c.schur_fixed = float(forced_jitter), 1
+            return
         self.jitter = _retry_with_jitter(run, M, dev, "posterior covariance at X_baseline")
 
     def factor_buffers(self):
@@ -512,6 +519,7 @@ class GraphedEval:
     def __init__(self, nei: "NEIState", B: int, q: int, d: int, Z_q: Tensor, tau_relu: float, tau_max: float,
                  with_grad: bool) -> None:  # fmt: skip
         dev = nei.device
+        self._nei = nei
         self.X = torch.zeros(B, q, d, dtype=torch.float64, device=dev)
         self.busy = False
         self.with_grad = with_grad
@@ -539,6 +547,7 @@ class GraphedEval:
     def run_forward(self, X: Tensor):
         self.X.copy_(X)
         self.fwd.replay()
+        self._nei.last_graph_info = self.info  # per-(model, t-batch) flags of this replay (static buffer)
         self.busy = self.with_grad
         return self.acq.clone(), self.info_minmax.detach()  # alias of a static buffer: consumed (copied to the host) before the next replay
 

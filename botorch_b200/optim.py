@@ -214,6 +214,21 @@ class HostEvaluator:
         self.out_host.copy_(torch.cat([grad.reshape(-1), loss.detach().reshape(1)]), non_blocking=True)
         if self.like.is_cuda:
             torch.cuda.current_stream(self.like.device).synchronize()
+        check = getattr(self.acqf, "check_numerics", None)
+        if check is not None:
+            # the failure flags of this evaluation were queued behind the kernels: they are complete now.  A failed cached
+            # update is re-evaluated through the reference's fallback (standard sampling) before SciPy sees the numbers.
+            check(quiet=True)
+            if getattr(self.acqf, "last_call_failed", False):
+                self.acqf.last_call_failed = False
+                self.acqf.strict_numerics(True)
+                try:
+                    X = self.x_host.to(self.like.device).view(self.shapeX).requires_grad_(True)
+                    loss = (-self.acqf(X)).sum()
+                    (grad,) = torch.autograd.grad(loss, X)
+                    self.out_host.copy_(torch.cat([grad.reshape(-1), loss.detach().reshape(1)]))
+                finally:
+                    self.acqf.strict_numerics(False)
         out = self.out_host.numpy()
         return float(out[-1]), out[:-1].astype(np.float64, copy=True)
 

@@ -110,6 +110,13 @@ typedef struct bo_nei {
     int32_t external_df;       /* bo_qlognei_bwd only.  1: the sample rows of the workspace (bo_qlognei_samples_view) already hold
                                 * d loss / d f, written by the caller -- the reductions ran outside (bo_mc_reduce_*: outcome
                                 * constraints couple the outputs of several models per sample); grad_acq is ignored. */
+    /* The reference's fallback when the cached update fails (acquisition/cached_cholesky.py:139-165): standard sampling
+     * factors the JOINT (n_b+q) covariance with psd_safe_cholesky, i.e. the SAME jitter delta on the baseline block and on
+     * the q x q block: chol(Sigma_bb + delta I) (bo_nei.jitter at setup) and chol(Schur + delta I) here.
+     * schur_fixed = 1: the q x q factorisation makes ONE attempt with schur_jitter on the diagonal (no escalation);
+     * failure is reported as BO_INFO_NOT_PSD and the host moves on to the next delta of the schedule. */
+    double schur_jitter;
+    int32_t schur_fixed;
 } bo_nei;
 
 typedef struct bo_ctx bo_ctx;

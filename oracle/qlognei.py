@@ -113,6 +113,10 @@ class OracleQLogNEI:
         elif mode == "uncached":
             obj, base = self.samples_uncached(X)
             return self._reduce_uncached(obj, base)
+        elif mode == "fallback":
+            # cache_root=True whose cached update raised NanError / NotPSDError (cached_cholesky.py:139-165): standard
+            # sampling from the joint posterior, last q rows, while best_f stays the cached `_baseline_best_f`
+            obj, _ = self.samples_uncached(X)
         else:
             raise ValueError(mode)
         return self._reduce(self.obj_weight * obj, self.best_f)

@@ -88,3 +88,55 @@ def test_size_limits_are_reported_not_crashed(cuda):
         nei.forward(X, Zq, 1e-6, 1e-2, with_grad=False)
     with pytest.raises(Exception):
         gp_state(_problem(10, 129, 1, 8), oracle_gp(_problem(10, 129, 1, 8)), cuda)
+
+
+def test_failed_cached_update_falls_back_to_standard_sampling(cuda):
+    """acquisition/cached_cholesky.py:139-165 / test/acquisition/test_logei.py:672-676: when the cached update fails
+    (NanError / NotPSDError) the reference warns ONCE and samples from the joint posterior over [X_baseline; X] instead,
+    keeping the cached incumbents.  The device state is corrupted the way the reference test corrupts `_baseline_L`;
+    value and gradient must equal the oracle's fallback."""
+    import warnings
+
+    import botorch_b200 as bb
+    from botorch_b200.exceptions import BotorchWarning
+    from botorch_b200.optim import HostEvaluator
+    from botorch_b200.synthetic import make_problem
+    from tests.util import candidates, oracle_acq, oracle_gp, rel_err
+
+    p = make_problem("C2", n=90)
+    h = p.hypers
+    oacq = oracle_acq(p, oracle_gp(p))
+    model = bb.SingleTaskGP(p.train_X.to(cuda), p.train_Y.to(cuda), lengthscale=h["lengthscale"], noise=h["noise"],
+                            mean_constant=h["mean"])  # fmt: skip
+    acqf = bb.qLogNoisyExpectedImprovement(model, p.train_X.to(cuda),
+                                           sampler=bb.SobolQMCNormalSampler(torch.Size([p.mc_samples]), seed=1234))  # fmt: skip
+    X = candidates(p, 6, q=3)
+    ref_val, ref_grad = oacq.value_and_grad(X, mode="fallback")
+    healthy = acqf(X.to(cuda)).cpu()
+    assert rel_err(healthy, ref_val, scale=0.0) < 1e-9  # same numbers as long as nothing fails (delta = 0)
+    acqf._nei.fwd_cat[:, -5:, :] = float("nan")  # the combined root: the samples of every t-batch turn NaN
+    with warnings.catch_warnings(record=True) as ws:
+        warnings.simplefilter("always")
+        with torch.no_grad():
+            val = acqf(X.to(cuda)).cpu()
+    assert sum(issubclass(w.category, BotorchWarning) and "Falling back" in str(w.message) for w in ws) == 1
+    assert rel_err(val, ref_val, scale=0.0) < 1e-9
+    # with a gradient, through the objective gen_candidates_scipy hands to L-BFGS-B: the evaluation is redone
+    ev = HostEvaluator(acqf, X.shape, torch.empty(0, dtype=torch.float64, device=cuda))
+    with warnings.catch_warnings(record=True) as ws:
+        warnings.simplefilter("always")
+        loss, grad = ev(X.numpy().reshape(-1).copy())
+    assert sum(issubclass(w.category, BotorchWarning) and "Falling back" in str(w.message) for w in ws) == 1
+    assert abs(loss + float(ref_val.sum())) < 1e-9 * abs(float(ref_val.sum()))
+    g = torch.from_numpy(grad).reshape(X.shape)
+    gerr = ((-g - ref_grad).flatten(1).abs().max(1).values / ref_grad.flatten(1).abs().max(1).values).max()
+    assert float(gerr) < 1e-9
+    # NaN inputs: psd_safe_cholesky of the fallback raises NanError, as in the reference
+    from botorch_b200.exceptions import NanError
+
+    Xn = X.clone()
+    Xn[0, 0, 0] = float("nan")
+    with pytest.raises(NanError), warnings.catch_warnings():
+        warnings.simplefilter("ignore")
+        with torch.no_grad():
+            acqf(Xn.to(cuda))
