@@ -32,8 +32,47 @@ UNIT = "candidate_evals/s"
 # dram__bytes_read.sum + dram__bytes_write.sum of the four dgemm_dmma_kernel launches of one step, averaged per launch,
 # from the `ncu --set full` capture of this command at the default workload (profiles/r01_ncu_full_step_v4.csv:
 # 10.0 + 154.2 + 334.0 + 67.1 MB).  Algorithmic operand bytes of the same four launches: ~550 MB, i.e. no re-reads.
-NCU_GEMM_TRAFFIC_BYTES_PER_LAUNCH = {("C3", 512): 141.3e6}
-FP64_DMMA_PEAK_TFLOPS = 37.07  # measured on this pool's B200 with tools/fp64_peaks.cu (profiles/r01_fp64_peaks.txt)
+NCU_GEMM_TRAFFIC_BYTES_PER_LAUNCH = {("C3", 512): 141.3e6}  # superseded by profiles/r02_traffic.json (keyed by source digest)
+FP64_DMMA_PEAK_TFLOPS = 37.07  # fallback only: tools/fp64_peaks.cu on this pool (profiles/r01_fp64_peaks.txt); the run measures its own
+
+
+def _measure_fp64_peak(dev, stream):
+    """DMMA.8x8x4 issue-rate microbenchmark of the library (bo_dmma_peak_launch), best of 5 ~25 ms launches, CUDA events."""
+    import ctypes as C
+
+    from botorch_b200 import _lib
+
+    lib = _lib.lib()
+    scratch = torch.zeros(1, dtype=torch.float64, device=dev)
+    flops = C.c_double()
+    best = 0.0
+    for rep in range(6):
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record(stream)
+        _lib.check(lib.bo_dmma_peak_launch(50000, scratch.data_ptr(), C.byref(flops), _lib.stream_ptr(dev)))
+        e1.record(stream)
+        torch.cuda.synchronize(dev)
+        if rep:
+            best = max(best, flops.value / (e0.elapsed_time(e1) * 1e-3) / 1e12)
+    return best
+
+
+def _traffic_record(cfg: str, B: int):
+    """DRAM bytes per launch of the dominant kernel from the committed `ncu --set full` capture, valid only for the library
+    sources it was taken from (profiles/r02_traffic.json holds the digest)."""
+    from botorch_b200 import _lib
+
+    path = os.path.join(ROOT, "profiles", "r02_traffic.json")
+    if not os.path.exists(path):
+        return None, "no committed capture"
+    rec = json.load(open(path))
+    digest = _lib.lib().bo_source_digest().decode()
+    key = f"{cfg}:{B}"
+    if key not in rec.get("workloads", {}):
+        return None, "no committed capture for this workload"
+    if rec.get("source_digest") != digest:
+        return None, f"the committed capture ({rec.get('capture')}) was taken from other library sources; re-capture"
+    return rec["workloads"][key]["dram_bytes_per_launch"], f"{rec.get('capture')}: {rec['workloads'][key]['note']}"
 
 
 def _args():
@@ -182,9 +221,9 @@ def _run_reference(args):
         "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
         "warmup": args.warmup, "ms_per_step": 1e3 * total / args.steps, "higher_is_better": True, "scaling": "weak",
         "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-        "config": {"workload": _workload_name(p, args.restarts or p.num_restarts),
-                   "note": f"CPU oracle restatement of the reference algorithm; each step = a bounded sample of {sample} of the "
-                           "restarts (fwd + autograd bwd), rate scaled per candidate"},
+        "config": _config_dict(p, args.restarts or p.num_restarts),
+        "note": f"CPU oracle restatement of the reference algorithm; each step = a bounded sample of {sample} of the "
+                "restarts (fwd + autograd bwd), rate scaled per candidate",
         "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": "port",
                          "sample": f"{sample} candidates per step, fwd + autograd bwd, faithful order of operations"},
         "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
@@ -193,7 +232,7 @@ def _run_reference(args):
     print(json.dumps(line), flush=True)
 
 
-def _mll_leg(p, dev, stream, cpu: bool):
+def _mll_leg(p, dev, stream, cpu: bool, peak: float = FP64_DMMA_PEAK_TFLOPS):
     """bo_mll_value_grad at the workload's training set: CUDA-event time per evaluation, FP64 rate on its algorithmic
     flops (Cholesky n^3/3 + inverse factor n^3/3 + W = alpha alpha^T - Khat^-1 against the triangular factor n^3 +
     covariance / gradient contractions), and the CPU oracle (torch float64 + autograd) on the same problem."""
@@ -227,7 +266,7 @@ def _mll_leg(p, dev, stream, cpu: bool):
     n, d = p.n, p.d
     flops = n**3 * (1 / 3 + 1 / 3 + 1.0) + 4 * (d + 2) * n * n + 2 * (d + 1) * n * n
     leg = {"mll_evals_per_s": 1e3 / ms, "ms_per_eval": ms, "tflops_fp64": flops / (ms * 1e-3) / 1e12,
-           "frac_of_fp64_peak": flops / (ms * 1e-3) / 1e12 / FP64_DMMA_PEAK_TFLOPS, "n": n, "d": d,
+           "frac_of_fp64_peak": flops / (ms * 1e-3) / 1e12 / peak, "n": n, "d": d,
            "what": "bo_mll_value_grad: log N(y | m, K + s2 I) and its gradient w.r.t. lengthscales, noise, mean "
                    "(one fit_gpytorch_mll closure evaluation), hyperparameters resident in HBM"}  # fmt: skip
     if cpu:
@@ -314,6 +353,16 @@ def _saas_leg(dev, chains: int = 64):
                     "(profiles/r01_saas_potential_nuts.json)"}  # fmt: skip
 
 
+def _config_dict(p, B):
+    """`config` of the JSON line -- identical for both arms (`--impl ours` / `--impl reference`), so the driver can pair them."""
+    n_models = int(p.hypers["lengthscale"].shape[0]) if p.hypers["lengthscale"].dim() == 2 else 1
+    return {"workload": _workload_name(p, B), "kernel": p.kernel, "models": n_models,
+            "l2": "inputs larger than L2: the n x n factor matrices plus the per-step workspace exceed the 126 MB L2 at the "
+                  "default workload (C3: 192 MB + 219 MiB), no flush needed",
+            "timed": "one fused forward + backward of qLogNEI over the restart batch per step (bo_qlognei_fwd + "
+                     "bo_qlognei_bwd on the GPU arm, X resident in HBM; the oracle's value_and_grad on the reference arm)"}  # fmt: skip
+
+
 def _workload_name(p, B):
     return (f"{p.name}: n={p.n} d={p.d} q={p.q} S={p.mc_samples} restarts/GPU={B} "
             f"(BASELINE.json configs[{'C1 C2 C3 C4 C5'.split().index(p.name[:2])}])")  # fmt: skip
@@ -386,7 +435,9 @@ def _run_ours(args):
     clocks = _ClockSampler(local) if rank == 0 else None
     time.sleep(0.3)
     lib.bo_launch_count_reset()
-    lib.bo_prof_enable(1)
+    # roofline of the DOMINANT kernel: the TMA-staged DMMA GEMM where the workload runs it (C3, C4, C5), else every GEMM launch
+    prof_mode = 2 if args.config in ("C3", "C4") else 1
+    lib.bo_prof_enable(prof_mode)
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     barrier()
     torch.cuda.profiler.start()  # `ncu --profile-from-start off` then sees exactly the timed region
@@ -406,6 +457,12 @@ def _run_ours(args):
     if ws > 1:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
     ms_max = float(t)
+
+    fp64_peak = _measure_fp64_peak(dev, stream) if rank == 0 else FP64_DMMA_PEAK_TFLOPS
+    peak_note = ("DMMA.8x8x4 issue-rate microbenchmark run by this process right after the timed region (bo_dmma_peak_launch, "
+                 "best of 5, CUDA events); MEASURED_PEAKS.json holds no FP64 figure")  # fmt: skip
+    if not (20.0 < fp64_peak < 60.0):
+        fp64_peak, peak_note = FP64_DMMA_PEAK_TFLOPS, "fallback constant (profiles/r01_fp64_peaks.txt): the in-run measurement failed"
 
     # ---- e2e: the user-facing call with HOST buffers (gen_candidates_scipy's f_np_wrapper, gen.py:194-222) -----------
     from botorch_b200.optim import HostEvaluator
@@ -508,34 +565,30 @@ def _run_ours(args):
     # ---- hyperparameter side: exact MLL value + gradient per L-BFGS-B evaluation of fit_gpytorch_mll ----
     mll_leg = None
     if ws == 1 and nei.gp.M == 1:
-        mll_leg = _mll_leg(p, dev, stream, cpu=not args.no_cpu_baseline)
+        mll_leg = _mll_leg(p, dev, stream, cpu=not args.no_cpu_baseline, peak=fp64_peak)
     n_models = nei.gp.M
     fwd_f, bwd_f = _algorithmic_flops_per_eval(p.n, nei.n_b, p.d, p.q, p.mc_samples)
     survey_per_eval = 3 * fwd_f * n_models  # SURVEY.md 8(d) convention: fwd+bwd = 3 F_fwd of the trsm-based algorithm
     executed_per_eval = gemm_fl.value / (args.steps * B)  # GEMM flops this implementation runs
     value = ws * B * args.steps / (ms_max * 1e-3)
+    traffic, traffic_note = _traffic_record(args.config, B)
     gemm_tflops = gemm_fl.value / (gemm_ms.value * 1e-3) / 1e12 if gemm_ms.value > 0 else 0.0
     line = {
         "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": ws, "steps": args.steps, "warmup": max(args.warmup, 3),
         "ms_per_step": ms_max / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
         "dtype": "f64", "data": "synthetic",
-        "config": {
-            "workload": _workload_name(p, B), "kernel": p.kernel, "models": n_models,
-            "l2": "inputs larger than L2: the six n x n factor matrices (192 MB at C3) plus the per-step workspace "
-                  f"({work.numel() / 2**20:.0f} MiB) exceed the 126 MB L2, no flush needed",
-            "timed": "bo_qlognei_fwd + bo_qlognei_bwd per step, X resident in HBM",
-        },
+        "config": _config_dict(p, B),
+        "workspace_mib": work.numel() / 2**20,
         "flops_per_eval": {"executed_gemm": executed_per_eval, "survey_8d_minimal_trsm_algorithm": survey_per_eval,
                            "note": "the combined-root path needs fewer flops than SURVEY 8(d)'s count; TFLOP/s figures "
                                    "use executed flops only"},
         "tflops_fp64_executed_whole_step": value * executed_per_eval / 1e12,
         "roofline": {
-            "bound": "tensor", "achieved": gemm_tflops, "peak": FP64_DMMA_PEAK_TFLOPS, "unit": "TFLOP/s",
-            "frac": gemm_tflops / FP64_DMMA_PEAK_TFLOPS, "traffic": NCU_GEMM_TRAFFIC_BYTES_PER_LAUNCH.get((args.config, B)), "kernel": "dgemm_dmma_kernel",
-            "traffic_note": "bytes per launch (mean over the step's GEMM launches) from profiles/r01_ncu_full_step_v4.csv; "
-                            "null for workloads without a committed capture",
-            "peak_source": "FP64 DMMA peak measured on this pool (tools/fp64_peaks.cu, profiles/r01_fp64_peaks.txt); "
-                           "MEASURED_PEAKS.json holds no FP64 figure",
+            "bound": "tensor", "achieved": gemm_tflops, "peak": fp64_peak, "unit": "TFLOP/s",
+            "frac": gemm_tflops / fp64_peak, "traffic": traffic,
+            "kernel": "dgemm_dmma_tma_kernel" if prof_mode == 2 else "dgemm_dmma_kernel (all GEMM launches)",
+            "traffic_note": traffic_note, "peak_source": peak_note,
+            "flops": "algorithmic: 2 x nonzeros(A) x N per launch (triangular operands count their nonzeros only)",
             "launches_per_step": gemm_n.value / args.steps, "avg_launch_ms": gemm_ms.value / max(gemm_n.value, 1),
             "share_of_step": gemm_ms.value / ms,
         },
@@ -550,7 +603,7 @@ def _run_ours(args):
                            "note": "wall clock of one gen_candidates call incl. its one-time setup (SciPy converts the bounds "
                                    "of all B*q*d variables in Python); rank 0 only"},
         "posterior": {"tflops_fp64": post_flops / (post_ms * 1e-3) / 1e12, "frac_of_fp64_peak":
-                      post_flops / (post_ms * 1e-3) / 1e12 / FP64_DMMA_PEAK_TFLOPS, "candidates": Nc,
+                      post_flops / (post_ms * 1e-3) / 1e12 / fp64_peak, "candidates": Nc,
                       "ms": post_ms},  # fmt: skip
         "setup_s": setup_s, "broadcast_bytes": bcast_bytes, "clocks": clk,
     }  # fmt: skip

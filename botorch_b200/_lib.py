@@ -106,6 +106,9 @@ def _declare(lib: C.CDLL) -> None:
     lib.bo_prof_enable.restype = None
     lib.bo_prof_read.argtypes = [C.POINTER(dbl), C.POINTER(i64), C.POINTER(dbl)]
     lib.bo_prof_read.restype = i32
+    lib.bo_dmma_peak_launch.argtypes = [i32, vp, C.POINTER(dbl), vp]
+    lib.bo_dmma_peak_launch.restype = i32
+    lib.bo_source_digest.restype = C.c_char_p
     lib.bo_pad8.restype = i64
     lib.bo_pad8.argtypes = [i64]
     lib.bo_kp.restype = i64
@@ -186,7 +189,48 @@ def lib() -> C.CDLL:
             )
         _lib = C.CDLL(LIB_PATH)
         _declare(_lib)
+        _check_fresh(_lib)
+        if os.environ.get("BOTORCH_B200_NVTX", "0") == "1":
+            _nvtx_wrap(_lib)
     return _lib
+
+
+def _check_fresh(lib_: C.CDLL) -> None:
+    """A binary built from other sources than the ones next to it would run kernels that do not match the code (the
+    .sha256 stamp beside the .so is not proof: it can travel through a checkout while the binary stays).  The digest is
+    compiled into the library; when the sources are present and differ, refuse to run."""
+    from .build import CSRC, SOURCES, source_digest
+
+    if not all(os.path.exists(os.path.join(CSRC, f)) for f in SOURCES):
+        return
+    built = lib_.bo_source_digest().decode()
+    if built not in ("unknown", source_digest()):
+        raise BoError(
+            f"{LIB_PATH} was built from different sources (digest {built[:12]}..., sources {source_digest()[:12]}...): "
+            "run `python -m botorch_b200.build`."
+        )
+
+
+def _nvtx_wrap(lib_: C.CDLL) -> None:
+    """BOTORCH_B200_NVTX=1: an NVTX range around every C-ABI call that enqueues work, so that nsys / ncu timelines show
+    bo_qlognei_fwd, bo_gp_setup, ... as named host ranges."""
+    names = ("bo_gp_setup bo_nei_setup bo_ei_setup bo_qlognei_fwd bo_qlognei_bwd bo_posterior_joint bo_posterior_joint_bwd "
+             "bo_posterior_joint_large bo_posterior_mean_var bo_ts_argmax bo_argmax bo_dgemm bo_kernel_matrix bo_potrf "
+             "bo_mll_value_grad bo_saas_potential bo_paths_setup bo_paths_eval bo_paths_grad bo_mc_reduce_fwd "
+             "bo_mc_reduce_bwd bo_lbfgs_init bo_lbfgs_propose bo_lbfgs_accept bo_kernel_matrix_static").split()  # fmt: skip
+
+    def wrap(name: str, fn):
+        def call(*args):
+            torch.cuda.nvtx.range_push(name)
+            try:
+                return fn(*args)
+            finally:
+                torch.cuda.nvtx.range_pop()
+
+        return call
+
+    for name in names:
+        setattr(lib_, name, wrap(name, getattr(lib_, name)))
 
 
 def check(code: int) -> None:

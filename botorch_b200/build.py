@@ -34,6 +34,11 @@ def _nvcc() -> str:
     raise RuntimeError("nvcc not found: cannot build libbotorch_b200.so")
 
 
+def source_digest() -> str:
+    """sha256 over the CUDA sources, headers and compiler flags: what `bo_source_digest()` of a fresh build returns."""
+    return _digest()
+
+
 def _digest() -> str:
     h = hashlib.sha256()
     for f in SOURCES + HEADERS:
@@ -55,6 +60,8 @@ def build(force: bool = False, verbose: bool = False) -> str:
     for src in SOURCES:
         obj = os.path.join(CSRC, src.replace(".cu", ".o"))
         cmd = [nvcc, *NVCC_FLAGS, "-c", os.path.join(CSRC, src), "-o", obj]
+        if src == "api.cu":  # bo_source_digest(): the loader and bench.py compare it with the sources they see
+            cmd.insert(1, f'-DBO_SOURCE_DIGEST="{digest}"')
         if verbose:
             print(" ".join(cmd), file=sys.stderr)
         procs.append((src, subprocess.Popen(cmd, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True)))

@@ -128,6 +128,10 @@ const char* bo_strerror(int code) {
     }
 }
 const char* bo_last_cuda_error(void) { return g_last_cuda_err; }
+#ifndef BO_SOURCE_DIGEST
+#define BO_SOURCE_DIGEST "unknown"
+#endif
+const char* bo_source_digest(void) { return BO_SOURCE_DIGEST; }
 
 int bo_ctx_create(int device, bo_ctx** out) {
     if (!out) return BO_ERR_INVALID;

@@ -19,14 +19,14 @@ long g_bo_launch_count = 0;
 #include <vector>
 namespace {
 struct ProfRec { cudaEvent_t a, b; };
-bool g_prof_on = false;
+int g_prof_on = 0;  // 0 off, 1 every GEMM launch, 2 only the TMA-staged kernel (the dominant one: bench.py's roofline)
 std::vector<ProfRec> g_prof_recs;
 size_t g_prof_used = 0;
 double g_prof_flops = 0.0;
 }  // namespace
 
 extern "C" void bo_prof_enable(int on) {
-    g_prof_on = on != 0;
+    g_prof_on = on;
     g_prof_used = 0;
     g_prof_flops = 0.0;
 }
@@ -41,6 +41,41 @@ extern "C" int bo_prof_read(double* ms, long* launches, double* flops) {
     if (ms) *ms = tot;
     if (launches) *launches = (long)g_prof_used;
     if (flops) *flops = g_prof_flops;
+    return BO_OK;
+}
+
+// DMMA.8x8x4 issue-rate microbenchmark: the FP64 tensor roofline denominator, measured in the run that quotes it
+// (bench.py times the launch with CUDA events).  8 independent accumulators per warp, 8 warps per CTA, 4 CTAs per SM.
+namespace {
+__global__ void __launch_bounds__(256) dmma_peak_kernel(double* out, int iters, double s) {
+    double c[8][2];
+#pragma unroll
+    for (int i = 0; i < 8; i++) c[i][0] = c[i][1] = 0.0;
+    const double a = s * (threadIdx.x & 31), b = 1.0 - s;
+    for (int it = 0; it < iters; it++) {
+#pragma unroll
+        for (int i = 0; i < 8; i++)
+            asm volatile("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%2}, {%3}, {%0,%1};\n"
+                         : "+d"(c[i][0]), "+d"(c[i][1])
+                         : "d"(a), "d"(b));
+    }
+    double r = 0.0;
+#pragma unroll
+    for (int i = 0; i < 8; i++) r += c[i][0] + c[i][1];
+    if (r == 123.456) out[0] = r;  // keeps the chain alive without a store per thread
+}
+}  // namespace
+
+// launches the microbenchmark on `stream`; *flops receives the FP64 flop count of the launch (2 x 256 FMA per warp-DMMA)
+extern "C" int bo_dmma_peak_launch(int iters, double* scratch, double* flops, void* stream) {
+    if (iters <= 0 || !scratch || !flops) return BO_ERR_INVALID;
+    int dev = 0, sms = 148;
+    BO_CUDA_TRY(cudaGetDevice(&dev));
+    BO_CUDA_TRY(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
+    const int grid = sms * 4;
+    dmma_peak_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(scratch, iters, 0.999);
+    BO_CUDA_TRY(cudaGetLastError());
+    *flops = 2.0 * 256.0 * 8.0 * (double)iters * 8.0 * (double)grid;
     return BO_OK;
 }
 
@@ -624,7 +659,7 @@ int launch_cfg(const BoGemm& g, cudaStream_t stream) {
     dim3 grid((g.N + C::BN - 1) / C::BN, (g.M + C::BM - 1) / C::BM, g.batch);
     if (grid.y > 65535u || grid.z > 65535u) return BO_ERR_UNSUPPORTED;
     ProfRec* rec = nullptr;
-    if (g_prof_on) {
+    if (g_prof_on == 1) {
         if (g_prof_used == g_prof_recs.size()) {
             ProfRec r;
             BO_CUDA_TRY(cudaEventCreate(&r.a));

@@ -131,8 +131,15 @@ void bo_launch_count_reset(void);
 
 /* per-launch CUDA-event timing of the DMMA GEMM kernel (bench.py's roofline leg): enable, run, synchronise, read
  * total milliseconds / launches / algorithmic flops (2MNK, halved for triangular operands) since enable. */
-void bo_prof_enable(int on);
+void bo_prof_enable(int on); /* 0 off, 1 every GEMM launch, 2 only the TMA-staged kernel (the dominant one) */
 int bo_prof_read(double* ms, long* launches, double* flops);
+/* FP64 tensor roofline denominator measured in place: launches a DMMA.8x8x4 issue-rate microbenchmark (8 independent
+ * accumulators per warp, 8 warps per CTA, 4 CTAs per SM) on `stream`; the caller times it with events.  scratch: one device
+ * double; *flops [host] receives the flop count of the launch. */
+int bo_dmma_peak_launch(int iters, double* scratch, double* flops, void* stream);
+/* sha256 over the library's sources and compiler flags at build time (botorch_b200/build.py): lets a loader detect a stale
+ * binary and lets bench.py tie an ncu capture to the code it was taken from. */
+const char* bo_source_digest(void);
 
 /* padded pitches used by every buffer of the ABI */
 long bo_pad8(long x);
