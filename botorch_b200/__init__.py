@@ -39,3 +39,29 @@ from .sampling import (  # noqa: F401
 )
 
 __version__ = "0.1.0"
+
+
+def _register_with_reference_bases() -> None:
+    """When the real BoTorch is importable, make `isinstance(x, botorch.<Base>)` hold for the classes of this package
+     without inheriting behaviour: the reference's bases are ABCs, so `Base.register(cls)` declares a
+    virtual subclass.  `exceptions.py` re-uses the real exception types outright.  No-op when `botorch` is absent (this
+    image: gpytorch / linear_operator are not installed)."""
+    try:
+        from botorch.acquisition.acquisition import AcquisitionFunction as _RefAcq
+        from botorch.models.model import Model as _RefModel
+        from botorch.posteriors.posterior import Posterior as _RefPosterior
+        from botorch.sampling.base import MCSampler as _RefSampler
+    except Exception:  # ImportError, or a broken partial install
+        return
+    from .acquisition import AcquisitionFunction as _Acq
+    from .models import Model as _Model
+    from .posteriors import Posterior as _Posterior
+    from .sampling import MCSampler as _Sampler
+
+    for ref, ours in ((_RefAcq, _Acq), (_RefModel, _Model), (_RefPosterior, _Posterior), (_RefSampler, _Sampler)):
+        register = getattr(ref, "register", None)
+        if register is not None:
+            register(ours)
+
+
+_register_with_reference_bases()

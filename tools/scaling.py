@@ -170,6 +170,37 @@ def c5_sharded(dev, group, n: int = 20000, candidates: int = 1_000_000, chunk: i
     }  # fmt: skip
 
 
+def c5_cpu_baseline(n: int = 20000, candidates: int = 1024):
+    """The oracle's marginal posterior (float64 torch CPU, all host cores) on a bounded sample of the C5 candidate stream:
+    train factorisation timed apart from the per-candidate work (cross-covariance, triangular solve, column norms)."""
+    from botorch_b200.synthetic import make_problem
+    from oracle.gp import rbf
+
+    torch.set_num_threads(os.cpu_count() or 1)
+    p = make_problem("C5", n=n)
+    h = p.hypers
+    ls = h["lengthscale"].unsqueeze(-2)
+    y = p.train_Y.squeeze(-1)
+    targets = (y - y.mean()) / y.std()
+    t0 = time.perf_counter()
+    K = rbf(p.train_X, p.train_X, ls, x1_eq_x2=True)
+    K.diagonal().add_(h["noise"])
+    L = torch.linalg.cholesky(K)
+    del K
+    alpha = torch.cholesky_solve((targets - h["mean"]).unsqueeze(-1), L).squeeze(-1)
+    setup_s = time.perf_counter() - t0
+    Xc = torch.quasirandom.SobolEngine(p.d, scramble=True, seed=1).draw(candidates, dtype=torch.float64)
+    t0 = time.perf_counter()
+    Ktx = rbf(Xc, p.train_X, ls)
+    mean = Ktx @ alpha
+    V = torch.linalg.solve_triangular(L, Ktx.mT, upper=False)
+    var = 1.0 - (V * V).sum(0)
+    score_s = time.perf_counter() - t0
+    assert bool(torch.isfinite(mean).all() and torch.isfinite(var).all())
+    return {"kind": "port", "cores": torch.get_num_threads(), "n": n, "sample": f"{candidates} of the 1M candidates",
+            "setup_s": setup_s, "score_s": score_s, "candidates_per_s": candidates / score_s}
+
+
 # ------------------------------------------------------------------------------------------------- per-shape weak table
 def shape_step(dev, group, cfg: str, steps: int = 20, warmup: int = 5):
     """bench.py's step (bo_qlognei_fwd + bo_qlognei_bwd over the config's restart batch, X resident) for one named shape."""
@@ -227,6 +258,7 @@ def main():
     ap.add_argument("--maxiter", type=int, default=20)
     ap.add_argument("--c5-n", type=int, default=20000)
     ap.add_argument("--c5-candidates", type=int, default=1_000_000)
+    ap.add_argument("--c5-cpu", action="store_true", help="also time the CPU oracle on a bounded C5 sample (rank 0)")
     ap.add_argument("--profile", action="store_true", help="cProfile the last strong-scaling repetition on rank 0")
     ap.add_argument("--sizes", default=None, help="comma list of group sizes (default: powers of two up to the world size)")
     args = ap.parse_args()
@@ -287,6 +319,11 @@ def main():
         if ws > 1:
             torch.cuda.synchronize(dev)
             dist.barrier()
+    if rank == 0 and "c5" in what and args.c5_cpu:
+        out["c5_cpu_baseline"] = c5_cpu_baseline(args.c5_n)
+        print("c5 cpu", json.dumps(out["c5_cpu_baseline"]), file=sys.stderr, flush=True)
+    if ws > 1:
+        dist.barrier()
     if rank == 0:
         t1 = {r["factor_mode"]: r["total_ms"] for r in out["strong_c3"] if r["n_gpus"] == 1}
         base = min(t1.values()) if t1 else None
