@@ -1066,7 +1066,9 @@ static bool takes_tma_mid(const BoGemm& g) {
     if (forced >= 0 || !use_tma || g.tile64) return false;
     if (g.M <= 32 && g.N >= 1024 && g.K >= 64 && g.epi == BO_EPI_LINEAR && g.tri == BO_TRI_NONE) return false;  // skinny
     const long tiles = (long)((g.M + 63) / 64) * ((g.N + 63) / 64) * g.batch;
-    return tiles >= 120 && g.K >= 64 && tma_eligible(g);
+    // K >= 256: below that the 4-stage ring never fills and the 2-stage cp.async form with 4 CTAs/SM is faster
+    // (C4, K = 100, 6144 tiles: step 1.59 vs 1.67 ms)
+    return tiles >= 120 && g.K >= 256 && tma_eligible(g);
 }
 
 int bo_gemm_fused_ok(const BoGemm& g) {
