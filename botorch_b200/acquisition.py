@@ -224,6 +224,11 @@ class _FusedImprovementBase(AcquisitionFunction):
             if arg is not None:
                 raise UnsupportedError(f"`{name}` is not on the fused path yet (SURVEY.md section 8f): pass None")
 
+    def _reduction_mode(self) -> int:
+        if not self._log:
+            return engine.REDUCE_PLAIN
+        return engine.REDUCE_LOG if getattr(self, "_fat", True) else engine.REDUCE_LOG_SOFT
+
     # -- forward --------------------------------------------------------------------------------------
     def forward(self, X: Tensor) -> Tensor:
         """X: (b) x q x d  ->  (b) acquisition values (one per t-batch)."""
@@ -435,12 +440,10 @@ class qLogNoisyExpectedImprovement(_FusedImprovementBase):
                 raise UnsupportedError(f"`{name}` is not on the fused path yet (SURVEY.md section 8f): pass None")
         self._obj_weight = _objective_weight(objective)
         self.objective = objective if objective is not None else IdentityMCObjective()
-        if not fat:
-            raise UnsupportedError("fat=False (plain softplus / logsumexp smoothing) is not on the fused path")
         if X_baseline.dim() != 2:
             raise UnsupportedError("X_baseline must be r x d (one baseline set shared by all t-batches)")
         self.tau_relu, self.tau_max = float(tau_relu), float(tau_max)
-        self._fat = True
+        self._fat = bool(fat)  # False: log_softplus / smooth_amax instead of log_fatplus / fatmax (logei.py:122,532)
         # cache_root=False only changes the order of operations in the reference (joint Cholesky of the
         # (n_b+q) block); the block Cholesky computed here is that same factor, so both settings share the path.
         self._cache_root = bool(cache_root)
@@ -468,8 +471,7 @@ class qLogNoisyExpectedImprovement(_FusedImprovementBase):
         Z_b = self.sampler.base_samples.reshape(S, n_b).to(device=gp.device, dtype=torch.float64).contiguous()
         # setup=False: allocate only; botorch_b200.distributed broadcasts the factors from the rank that computed them
         self._nei = engine.NEIState(gp, self.X_baseline.to(gp.device), Z_b, setup=setup,
-                                    reduction=engine.REDUCE_LOG if self._log else engine.REDUCE_PLAIN,
-                                    obj_weight=self._obj_weight)
+                                    reduction=self._reduction_mode(), obj_weight=self._obj_weight)
         self.q_in = -1
         self._Zq: Optional[Tensor] = None
         self.register_buffer("_baseline_best_f", None)
@@ -599,8 +601,7 @@ class qLogExpectedImprovement(_FusedImprovementBase):
     ) -> None:
         AcquisitionFunction.__init__(self, model=model)
         self._check_fused_args(model, posterior_transform=posterior_transform, constraints=constraints)
-        if not fat:
-            raise UnsupportedError("fat=False (plain softplus / logsumexp smoothing) is not on the fused path")
+        self._fat = bool(fat)
         self.tau_relu, self.tau_max = float(tau_relu), float(tau_max)
         self._obj_weight = _objective_weight(objective)
         self.objective = objective if objective is not None else IdentityMCObjective()
@@ -615,8 +616,7 @@ class qLogExpectedImprovement(_FusedImprovementBase):
         self.sampler = sampler
         self.set_X_pending(X_pending)
         self._nei = engine.EIState(gp, self.best_f.to(gp.device), self.sample_shape[0],
-                                   reduction=engine.REDUCE_LOG if self._log else engine.REDUCE_PLAIN,
-                                   obj_weight=self._obj_weight)  # fmt: skip
+                                   reduction=self._reduction_mode(), obj_weight=self._obj_weight)  # fmt: skip
         self.q_in, self._Zq = -1, None
 
     def _set_sampler(self, q_in: int) -> None:

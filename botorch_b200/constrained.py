@@ -304,6 +304,8 @@ class qLogNEIModelList(AcquisitionFunction):
         self.objective = objective
         self._constraints = list(constraints) if constraints else None
         self._eta, self._fat = eta, bool(fat)
+        if not self._fat and self._reduction == engine.REDUCE_LOG:  # fat = False: log_softplus / smooth_amax (logei.py:122,532)
+            self._reduction = engine.REDUCE_LOG_SOFT
         self.tau_relu, self.tau_max = float(tau_relu), float(tau_max)
         self.set_X_pending(X_pending)
         self.register_buffer("X_baseline", X_baseline.detach())

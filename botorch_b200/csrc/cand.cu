@@ -64,6 +64,28 @@ __device__ __forceinline__ double dlog_fatplus(double z, double tau, double inv_
 }
 __device__ __forceinline__ double pareto2(double u) { return 2.0 / (2.0 + 2.0 * u + u * u); }
 
+// fat = False (acquisition/logei.py:122,532): log_softplus (utils/safe_math.py:226-247, float64 cut-offs -35 / 32) for the
+// improvement and smooth_amax = tau * logsumexp(x / tau) (safe_math.py:250-273) over the q points
+__device__ __forceinline__ double log_softplus_ref(double z, double tau, double inv_tau) {
+    const double u = z * inv_tau;
+    if (!(u > -35.0)) return u + log(tau);
+    return log((u > 32.0) ? z : tau * log1p(exp(u)));
+}
+__device__ __forceinline__ double dlog_softplus_ref(double z, double tau, double inv_tau) {
+    const double u = z * inv_tau;
+    if (!(u > -35.0)) return inv_tau;
+    if (u > 32.0) return 1.0 / z;
+    const double e = exp(u);
+    return (e / (1.0 + e)) / (tau * log1p(e));
+}
+// log-improvement of one sample: reduction BO_REDUCE_LOG (fat) or BO_REDUCE_LOG_SOFT
+__device__ __forceinline__ double log_improvement(int reduction, double z, double tau, double inv_tau) {
+    return reduction == BO_REDUCE_LOG_SOFT ? log_softplus_ref(z, tau, inv_tau) : log_fatplus(z, tau, inv_tau);
+}
+__device__ __forceinline__ double dlog_improvement(int reduction, double z, double tau, double inv_tau) {
+    return reduction == BO_REDUCE_LOG_SOFT ? dlog_softplus_ref(z, tau, inv_tau) : dlog_fatplus(z, tau, inv_tau);
+}
+
 // fatmax over x[0..q) (alpha = 2) with the infinity handling of _inf_max_helper.  QT >= q is a compile-time bound:
 // every loop is fully unrolled with a (j < q) guard so that the per-sample arrays stay in registers.
 // The temperature enters as a multiplication by 1/tau (one rounding away from the reference's division: 1e-16 relative
@@ -130,6 +152,65 @@ __device__ __forceinline__ double fatmax_q_grad(const double (&x)[QT], int q, do
     for (int j = 0; j < QT; j++)
         if (j < q && x[j] == M) g[j] += rest;
     return M + tau * log(sum);
+}
+
+// smooth_amax over x[0..q): tau * logsumexp(x / tau) with the infinity handling of _inf_max_helper (safe_math.py:149-187)
+template <int QT>
+__device__ __forceinline__ double smoothmax_q(const double (&x)[QT], int q, double tau) {
+    const double inv_tau = 1.0 / tau;
+    double M = x[0] * inv_tau;
+#pragma unroll
+    for (int j = 1; j < QT; j++)
+        if (j < q) M = fmax(M, x[j] * inv_tau);
+    if (isinf(M)) {
+        double s = 0.0;
+#pragma unroll
+        for (int j = 0; j < QT; j++)
+            if (j < q && x[j] * inv_tau == M) s += x[j] * inv_tau;
+        return s * tau;
+    }
+    double sum = 0.0;
+#pragma unroll
+    for (int j = 0; j < QT; j++)
+        if (j < q) sum += exp(x[j] * inv_tau - M);
+    return (M + log(sum)) * tau;
+}
+// value and gradient (softmax weights; unit gradient on the infinite maxima)
+template <int QT>
+__device__ __forceinline__ double smoothmax_q_grad(const double (&x)[QT], int q, double tau, double (&g)[QT]) {
+    const double inv_tau = 1.0 / tau;
+    double M = x[0] * inv_tau;
+#pragma unroll
+    for (int j = 1; j < QT; j++)
+        if (j < q) M = fmax(M, x[j] * inv_tau);
+    if (isinf(M)) {
+        double s = 0.0;
+#pragma unroll
+        for (int j = 0; j < QT; j++) {
+            const bool hit = j < q && x[j] * inv_tau == M;
+            g[j] = hit ? 1.0 : 0.0;
+            if (hit) s += x[j] * inv_tau;
+        }
+        return s * tau;
+    }
+    double sum = 0.0;
+#pragma unroll
+    for (int j = 0; j < QT; j++) {
+        g[j] = (j < q) ? exp(x[j] * inv_tau - M) : 0.0;
+        sum += g[j];
+    }
+    const double inv_sum = 1.0 / sum;
+#pragma unroll
+    for (int j = 0; j < QT; j++) g[j] *= inv_sum;
+    return (M + log(sum)) * tau;
+}
+template <int QT>
+__device__ __forceinline__ double qmax_log(int reduction, const double (&x)[QT], int q, double tau) {
+    return reduction == BO_REDUCE_LOG_SOFT ? smoothmax_q<QT>(x, q, tau) : fatmax_q<QT>(x, q, tau);
+}
+template <int QT>
+__device__ __forceinline__ double qmax_log_grad(int reduction, const double (&x)[QT], int q, double tau, double (&g)[QT]) {
+    return reduction == BO_REDUCE_LOG_SOFT ? smoothmax_q_grad<QT>(x, q, tau, g) : fatmax_q_grad<QT>(x, q, tau, g);
 }
 
 // Sum P per-lane values over the 32 lanes of a warp with ~P shuffles instead of 5 P: at every butterfly step each lane
@@ -521,7 +602,7 @@ __global__ void __launch_bounds__(CAND_THREADS, (QT <= 4 ? 6 : (QT <= 8 ? 4 : 1)
                     if (k <= j) v += c.Lq[j * q + k] * zq[k];
                 F[(long)s * a.ldn + c0 + j] = v;
                 if (!isfinite(v)) bad = 1;
-                li[j] = plain ? fmax(a.obj_w * v - bf, 0.0) : log_fatplus(a.obj_w * v - bf, a.tau_relu, inv_tau_relu);
+                li[j] = plain ? fmax(a.obj_w * v - bf, 0.0) : log_improvement(a.reduction, a.obj_w * v - bf, a.tau_relu, inv_tau_relu);
             }
         }
         double m;
@@ -531,7 +612,7 @@ __global__ void __launch_bounds__(CAND_THREADS, (QT <= 4 ? 6 : (QT <= 8 ? 4 : 1)
             for (int j = 1; j < QT; j++)
                 if (j < q) m = fmax(m, li[j]);
         } else {
-            m = fatmax_q<QT>(li, q, a.tau_max);
+            m = qmax_log<QT>(a.reduction, li, q, a.tau_max);
         }
         c.fm[s] = m;
         local_max = fmax(local_max, m);
@@ -617,7 +698,7 @@ __global__ void __launch_bounds__(CAND_THREADS, (QT <= 4 ? 6 : (QT <= 8 ? 4 : 1)
             f[j] = 0.0; li[j] = 0.0; zq[j] = 0.0;
             if (j < q) {
                 f[j] = F[(long)s * a.ldn + c0 + j];
-                li[j] = plain ? fmax(a.obj_w * f[j] - bf, 0.0) : log_fatplus(a.obj_w * f[j] - bf, a.tau_relu, inv_tau_relu);
+                li[j] = plain ? fmax(a.obj_w * f[j] - bf, 0.0) : log_improvement(a.reduction, a.obj_w * f[j] - bf, a.tau_relu, inv_tau_relu);
                 zq[j] = a.Zq[(long)s * q + j];
             }
         }
@@ -633,7 +714,7 @@ __global__ void __launch_bounds__(CAND_THREADS, (QT <= 4 ? 6 : (QT <= 8 ? 4 : 1)
                 if (j < q && li[j] == m) ties++;
             w = 1.0 / (double)a.S;
         } else {
-            m = fatmax_q_grad<QT>(li, q, a.tau_max, gm);
+            m = qmax_log_grad<QT>(a.reduction, li, q, a.tau_max, gm);
             // logmeanexp over samples: softmax weight; +-inf maximum -> unit gradient on the infinite entries
             w = isinf(lse) ? ((m == lse) ? 1.0 : 0.0) : exp(m - lse);
         }
@@ -645,7 +726,7 @@ __global__ void __launch_bounds__(CAND_THREADS, (QT <= 4 ? 6 : (QT <= 8 ? 4 : 1)
                 if (plain) {
                     df = (li[j] == m && a.obj_w * f[j] - bf >= 0.0) ? a.obj_w * g * w / (double)ties : 0.0;
                 } else {
-                    const double dli = isinf(li[j]) ? 0.0 : dlog_fatplus(a.obj_w * f[j] - bf, a.tau_relu, inv_tau_relu);
+                    const double dli = isinf(li[j]) ? 0.0 : dlog_improvement(a.reduction, a.obj_w * f[j] - bf, a.tau_relu, inv_tau_relu);
                     df = a.obj_w * g * w * gm[j] * dli;
                 }
                 F[(long)s * a.ldn + c0 + j] = df;
@@ -1093,7 +1174,7 @@ __global__ void __launch_bounds__(CAND_THREADS) mc_reduce_fwd_kernel(const BoRed
                 const double v = a.F[(long)s * a.ldn + c0 + j];
                 const double lw = a.lw ? a.lw[(long)s * a.ldn + c0 + j] : 0.0;
                 li[j] = plain ? fmax(a.obj_w * v - bf, 0.0) * (a.lw ? exp(lw) : 1.0)
-                              : log_fatplus(a.obj_w * v - bf, a.tau_relu, inv_tau_relu) + lw;
+                              : log_improvement(a.reduction, a.obj_w * v - bf, a.tau_relu, inv_tau_relu) + lw;
             }
         }
         double m;
@@ -1103,7 +1184,7 @@ __global__ void __launch_bounds__(CAND_THREADS) mc_reduce_fwd_kernel(const BoRed
             for (int j = 1; j < QT; j++)
                 if (j < q) m = fmax(m, li[j]);
         } else {
-            m = fatmax_q<QT>(li, q, a.tau_max);
+            m = qmax_log<QT>(a.reduction, li, q, a.tau_max);
         }
         sm[s] = m;
         local_max = fmax(local_max, m);
@@ -1146,7 +1227,7 @@ __global__ void __launch_bounds__(CAND_THREADS) mc_reduce_bwd_kernel(const BoRed
                 f[j] = a.F[(long)s * a.ldn + c0 + j];
                 lwv[j] = a.lw ? a.lw[(long)s * a.ldn + c0 + j] : 0.0;
                 li[j] = plain ? fmax(a.obj_w * f[j] - bf, 0.0) * (a.lw ? exp(lwv[j]) : 1.0)
-                              : log_fatplus(a.obj_w * f[j] - bf, a.tau_relu, inv_tau_relu) + lwv[j];
+                              : log_improvement(a.reduction, a.obj_w * f[j] - bf, a.tau_relu, inv_tau_relu) + lwv[j];
             }
         }
         double m, w;
@@ -1161,7 +1242,7 @@ __global__ void __launch_bounds__(CAND_THREADS) mc_reduce_bwd_kernel(const BoRed
                 if (j < q && li[j] == m) ties++;
             w = 1.0 / (double)a.S;
         } else {
-            m = fatmax_q_grad<QT>(li, q, a.tau_max, gm);
+            m = qmax_log_grad<QT>(a.reduction, li, q, a.tau_max, gm);
             w = isinf(lse) ? ((m == lse) ? 1.0 : 0.0) : exp(m - lse);
         }
 #pragma unroll
@@ -1174,7 +1255,7 @@ __global__ void __launch_bounds__(CAND_THREADS) mc_reduce_bwd_kernel(const BoRed
                 df = (a.obj_w * f[j] - bf >= 0.0) ? hit * a.obj_w * ind : 0.0;
                 dl = hit * li[j];
             } else {
-                const double dli = isinf(li[j]) ? 0.0 : dlog_fatplus(a.obj_w * f[j] - bf, a.tau_relu, inv_tau_relu);
+                const double dli = isinf(li[j]) ? 0.0 : dlog_improvement(a.reduction, a.obj_w * f[j] - bf, a.tau_relu, inv_tau_relu);
                 dl = isinf(li[j]) ? 0.0 : g * w * gm[j];
                 df = a.obj_w * dl * dli;
             }

@@ -18,6 +18,7 @@
 #define BO_KERNEL_MATERN52 1
 #define BO_REDUCE_LOG 0    // log_fatplus / fatmax / logmeanexp  (qLogNEI, qLogEI)
 #define BO_REDUCE_PLAIN 1  // clamp_min(0) / amax / mean           (qNEI, qEI)
+#define BO_REDUCE_LOG_SOFT 2  // log_softplus / smooth_amax / logmeanexp (fat = False)
 
 #define BO_CUDA_TRY(expr)                                                                    \
     do {                                                                                     \

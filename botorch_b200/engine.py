@@ -18,7 +18,7 @@ from . import _lib
 from ._lib import BoGP, BoNEI, BoPaths, check, kp, pad8, ptr
 from .exceptions import NanError, NotPSDError, NumericalWarning
 
-REDUCE_LOG, REDUCE_PLAIN = 0, 1  # BO_REDUCE_* of include/botorch_b200.h
+REDUCE_LOG, REDUCE_PLAIN, REDUCE_LOG_SOFT = 0, 1, 2  # BO_REDUCE_* of include/botorch_b200.h (LOG_SOFT: fat = False)
 MAX_Q = 32  # BO_MAX_Q: largest q-batch of the per-candidate kernels
 
 KERNEL_IDS = {"rbf": 0, "matern52": 1}

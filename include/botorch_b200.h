@@ -37,6 +37,7 @@ extern "C" {
 /* sample / q reductions of SampleReducingMCAcquisitionFunction (acquisition/monte_carlo.py:180-252) */
 #define BO_REDUCE_LOG 0   /* log_fatplus, fatmax, logmeanexp: qLogNEI, qLogEI (acquisition/logei.py:73-135) */
 #define BO_REDUCE_PLAIN 1 /* clamp_min(0), amax, mean: qNEI, qEI (acquisition/monte_carlo.py:333-414,417-560) */
+#define BO_REDUCE_LOG_SOFT 2 /* fat = False: log_softplus, smooth_amax, logmeanexp (acquisition/logei.py:122,532; utils/safe_math.py:226-273) */
 
 /* info codes written per (model, t-batch element) by bo_qlognei_fwd */
 #define BO_INFO_OK 0

@@ -146,9 +146,13 @@ class OracleConstrainedQLogNEI:
             imp = (obj - self.best_f.view(self.S, 1, 1)).clamp_min(0)
             imp = imp * smoothed_log_feasibility(self.constraints, smp, self.eta, self.fat).exp()
             return imp.amax(dim=-1).mean(dim=0)
-        li = safe_math.log_improvement(obj, self.best_f.view(self.S, 1), tau=self.tau_relu)
+        if self.fat:
+            li = safe_math.log_improvement(obj, self.best_f.view(self.S, 1), tau=self.tau_relu)
+        else:  # the reference's `fat` flag switches the ReLU smoothing, the q-reduction AND the sigmoid (logei.py:122,532)
+            li = safe_math.log_softplus(obj - self.best_f.view(self.S, 1, 1), tau=self.tau_relu)
         li = li + smoothed_log_feasibility(self.constraints, smp, self.eta, self.fat)
-        return safe_math.logmeanexp(safe_math.fatmax(li, dim=-1, tau=self.tau_max), dim=0)
+        qmax = safe_math.fatmax if self.fat else safe_math.smooth_amax
+        return safe_math.logmeanexp(qmax(li, dim=-1, tau=self.tau_max), dim=0)
 
     def value_and_grad(self, X: Tensor):
         Xg = X.detach().clone().requires_grad_(True)

@@ -31,8 +31,10 @@ class OracleQLogNEI:
         tau_relu: float = TAU_RELU,
         tau_max: float = TAU_MAX,
         obj_weight: float = 1.0,
+        fat: bool = True,
     ):
         self.model = model
+        self.fat = bool(fat)  # logei.py:122,532: fatmax / log_fatplus, or smooth_amax / log_softplus
         self.obj_weight = float(obj_weight)  # one-outcome LinearMCObjective (objective.py:217-256): obj = w * samples
         self.X_baseline = X_baseline
         self.S = num_samples
@@ -97,7 +99,7 @@ class OracleQLogNEI:
     def _reduce(self, obj: Tensor, best_f: Tensor) -> Tensor:
         # obj: S x B x (M?) x q ; best_f: S x (M?) -> S x 1 x (M?)   (logei.py:422-446)
         bf = best_f.unsqueeze(1)
-        acq = safe_math.qlognei_reduction(obj, bf, self.tau_relu, self.tau_max)  # B x (M?)
+        acq = safe_math.qlognei_reduction(obj, bf, self.tau_relu, self.tau_max, fat=self.fat)  # B x (M?)
         if self.is_ensemble:  # transforms.py:289-293
             acq = safe_math.logmeanexp(acq, dim=-1)
         return acq

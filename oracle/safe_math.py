@@ -112,12 +112,33 @@ def fatmax(x: Tensor, dim: Dim, keepdim: bool = False, tau: float = 1.0, alpha: 
     return inf_aware_max(reduce, x=x, dim=dim, keepdim=keepdim)
 
 
-def qlognei_reduction(obj: Tensor, best_f: Tensor, tau_relu: float, tau_max: float) -> Tensor:
+def log_softplus(x: Tensor, tau: float) -> Tensor:
+    """log(softplus(x, beta=1/tau)) with the reference's cut-offs (safe_math.py:226-247; float64: upper 32, lower -35)."""
+    tau_t = torch.as_tensor(tau, dtype=x.dtype)
+    upper, lower = (16, -15) if x.dtype == torch.float32 else (32, -35)
+    mask = x / tau_t > lower
+    return torch.where(
+        mask,
+        softplus(x.masked_fill(~mask, lower), beta=(1 / tau_t), threshold=upper).log(),
+        x / tau_t + tau_t.log(),
+    )
+
+
+def smooth_amax(x: Tensor, dim: Dim = -1, keepdim: bool = False, tau: float = 1.0) -> Tensor:
+    """tau * logsumexp(x / tau)  (safe_math.py:250-273)."""
+    return logsumexp(x / tau, dim=dim, keepdim=keepdim) * tau
+
+
+def qlognei_reduction(obj: Tensor, best_f: Tensor, tau_relu: float, tau_max: float, fat: bool = True) -> Tensor:
     """samples -> acquisition value (monte_carlo.py:253-274 with logei.py:122,129,347-362).
 
     obj: S x batch x q objective samples, best_f: S (x model batch) best baseline
     objective per MC sample.  Returns ``batch``.
     """
-    li = log_improvement(obj, best_f, tau=tau_relu)
-    per_sample = fatmax(li, dim=-1, tau=tau_max)
+    if fat:
+        li = log_improvement(obj, best_f, tau=tau_relu)
+        per_sample = fatmax(li, dim=-1, tau=tau_max)
+    else:  # logei.py:122 (smooth_amax), :532 (log_softplus)
+        li = log_softplus(obj - best_f.unsqueeze(-1).to(obj), tau=tau_relu)
+        per_sample = smooth_amax(li, dim=-1, tau=tau_max)
     return logmeanexp(per_sample, dim=0)

@@ -30,6 +30,39 @@ sys.path.insert(0, ROOT)
 from oracle import refstub  # noqa: E402
 
 
+def _nofat_part() -> dict:
+    """fat = False pieces of the reference (utils/safe_math.py:226-273: log_softplus, smooth_amax), values and gradients,
+    and the per-sample qLogNEI chain with them (acquisition/logei.py:122,532).  Own generator: the fixtures of
+    `_reference_part` stay bit-identical.  -> tests/golden/reference_nofat.pt"""
+    ref = refstub.load()
+    sm = ref.safe_math
+    g = torch.Generator().manual_seed(777)
+    cases = {}
+    x = torch.randn(64, 7, generator=g, dtype=torch.float64) * torch.logspace(-8, 2, 64, dtype=torch.float64)[:, None]
+    for tau in (1e-6, 1e-2, 1.0):
+        xg = x.clone().requires_grad_(True)
+        v = sm.log_softplus(xg, tau=tau)
+        (gr,) = torch.autograd.grad(v.sum(), xg)
+        cases[f"log_softplus_tau{tau:g}"] = {"x": x, "value": v.detach(), "grad": gr}
+    y = torch.randn(33, 5, 8, generator=g, dtype=torch.float64) * 3
+    for tau in (1e-2, 1.0):
+        yg = y.clone().requires_grad_(True)
+        v = sm.smooth_amax(yg, dim=-1, tau=tau)
+        (gr,) = torch.autograd.grad(v.sum(), yg)
+        cases[f"smooth_amax_tau{tau:g}"] = {"x": y, "value": v.detach(), "grad": gr}
+    inf = float("inf")
+    z = torch.tensor([[1.0, -inf, 2.0, 0.5], [-inf, -inf, -inf, -inf], [inf, 1.0, inf, -3.0]], dtype=torch.float64)
+    cases["smooth_amax_inf"] = {"x": z, "value": sm.smooth_amax(z, dim=-1, tau=1e-2)}
+    obj = torch.randn(16, 6, 3, generator=g, dtype=torch.float64)
+    best = torch.randn(16, 1, generator=g, dtype=torch.float64)
+    og = obj.clone().requires_grad_(True)
+    li = sm.log_softplus(og - best.unsqueeze(-1), tau=1e-6)
+    acq = sm.logmeanexp(sm.smooth_amax(li, dim=-1, tau=1e-2), dim=0)
+    (gr,) = torch.autograd.grad(acq.sum(), og)
+    cases["qlognei_chain_nofat"] = {"obj": obj, "best_f": best, "value": acq.detach(), "grad": gr}
+    return cases
+
+
 def _reference_part() -> dict:
     ref = refstub.load()
     sm, out = ref.safe_math, {}
@@ -137,10 +170,15 @@ def _oracle_part() -> dict:
 
 
 def main() -> None:
+    if "--nofat-only" in sys.argv:  # add the fat = False fixtures without touching the committed ones
+        torch.save(_nofat_part(), os.path.join(HERE, "reference_nofat.pt"))
+        print("reference_nofat.pt", os.path.getsize(os.path.join(HERE, "reference_nofat.pt")), "bytes")
+        return
     torch.manual_seed(0)
     torch.save(_reference_part(), os.path.join(HERE, "reference_modules.pt"))
     torch.save(_oracle_part(), os.path.join(HERE, "oracle_configs.pt"))
-    for f in ("reference_modules.pt", "oracle_configs.pt"):
+    torch.save(_nofat_part(), os.path.join(HERE, "reference_nofat.pt"))
+    for f in ("reference_modules.pt", "oracle_configs.pt", "reference_nofat.pt"):
         print(f, os.path.getsize(os.path.join(HERE, f)), "bytes")
 
 

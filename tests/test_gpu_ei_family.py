@@ -185,3 +185,37 @@ def test_prune_inferior_points_with_objective(cuda):
         return [int((p.train_X == r).all(-1).nonzero()[0, 0]) for r in K.cpu()]
     assert int(torch.argmax(y)) in _rows(keep_max) and int(torch.argmin(y)) in _rows(keep_min)
     assert set(_rows(keep_max)) != set(_rows(keep_min))
+
+
+@pytest.mark.parametrize("cfg,kw,q,B", [("C2", {}, 4, 16), ("C1", {}, 1, 8), ("C3", {"n": 300}, 8, 6), ("C4", {"M": 4}, 3, 5)])
+def test_fat_false_uses_log_softplus_and_smooth_amax(cuda, cfg, kw, q, B):
+    """acquisition/logei.py:122,532: fat = False switches log_fatplus -> log_softplus and fatmax -> smooth_amax (both pinned
+    to the reference's utils/safe_math.py in tests/test_oracle_golden.py); qLogNEI and qLogEI, values and gradients."""
+    import botorch_b200 as bb
+    from botorch_b200.synthetic import make_problem
+    from oracle.qlognei import OracleQLogNEI
+    from tests.test_gpu_qlognei import _grad_rel
+    from tests.util import candidates, oracle_gp, rel_err
+
+    p = make_problem(cfg, **kw)
+    ogp = oracle_gp(p)
+    oacq = OracleQLogNEI(ogp, p.train_X, num_samples=p.mc_samples, seed=1234, fat=False)
+    h = p.hypers
+    if p.kernel == "rbf":
+        model = bb.SingleTaskGP(p.train_X.to(cuda), p.train_Y.to(cuda), lengthscale=h["lengthscale"], noise=h["noise"],
+                                mean_constant=h["mean"])  # fmt: skip
+    else:
+        model = bb.SaasFullyBayesianSingleTaskGP(p.train_X.to(cuda), p.train_Y.to(cuda))
+        model.load_mcmc_samples(h)
+    acqf = bb.qLogNoisyExpectedImprovement(model, p.train_X.to(cuda), fat=False,
+                                           sampler=bb.SobolQMCNormalSampler(torch.Size([p.mc_samples]), seed=1234))  # fmt: skip
+    X = candidates(p, B, q=q)
+    Xd = X.to(cuda).requires_grad_(True)
+    val = acqf(Xd)
+    (grad,) = torch.autograd.grad(val.sum(), Xd)
+    ref_val, ref_grad = oacq.value_and_grad(X, mode="faithful")
+    assert rel_err(val, ref_val, scale=0.0) < 1e-9
+    assert _grad_rel(grad, ref_grad) < 1e-9
+    fat_val = bb.qLogNoisyExpectedImprovement(model, p.train_X.to(cuda),
+                                              sampler=bb.SobolQMCNormalSampler(torch.Size([p.mc_samples]), seed=1234))(X.to(cuda))  # fmt: skip
+    assert float((fat_val.cpu() - ref_val).abs().max()) > 1e-6  # the two smoothings really differ

@@ -459,3 +459,36 @@ def test_oracle_gp_algebra_matches_mpmath(case, p):
         gref = t(case["grad"])
         gerr = ((grad - gref).flatten(1).abs().max(1).values / gref.flatten(1).abs().max(1).values).max()
         assert float(gerr) < 1e-10, mode  # measured 1.2e-12
+
+
+def test_oracle_nofat_reductions_match_reference_fixtures():
+    """fat = False (acquisition/logei.py:122,532): the oracle's log_softplus / smooth_amax and the per-sample chain against
+    fixtures minted from the reference's own utils/safe_math.py (tests/golden/make_golden.py::_nofat_part)."""
+    import os
+
+    from oracle import safe_math as osm
+
+    fx = torch.load(os.path.join(os.path.dirname(__file__), "golden", "reference_nofat.pt"))
+    for name, c in fx.items():
+        x = c.get("x")
+        if name.startswith("log_softplus_tau"):
+            tau = float(name.split("tau")[1])
+            xg = x.clone().requires_grad_(True)
+            v = osm.log_softplus(xg, tau=tau)
+            (g,) = torch.autograd.grad(v.sum(), xg)
+            assert torch.equal(v.detach(), c["value"]) and torch.equal(g, c["grad"]), name
+        elif name.startswith("smooth_amax_tau"):
+            tau = float(name.split("tau")[1])
+            xg = x.clone().requires_grad_(True)
+            v = osm.smooth_amax(xg, dim=-1, tau=tau)
+            (g,) = torch.autograd.grad(v.sum(), xg)
+            assert torch.allclose(v.detach(), c["value"], rtol=1e-15, atol=0) and torch.allclose(g, c["grad"], rtol=1e-14, atol=1e-300), name
+        elif name == "smooth_amax_inf":
+            v = osm.smooth_amax(x, dim=-1, tau=1e-2)
+            assert torch.equal(torch.isinf(v), torch.isinf(c["value"])) and torch.equal(v[torch.isinf(v)], c["value"][torch.isinf(v)])
+            assert torch.allclose(v[~torch.isinf(v)], c["value"][~torch.isinf(v)], rtol=1e-15)
+        elif name == "qlognei_chain_nofat":
+            og = c["obj"].clone().requires_grad_(True)
+            acq = osm.qlognei_reduction(og, c["best_f"].squeeze(-1).unsqueeze(-1) if False else c["best_f"], 1e-6, 1e-2, fat=False)
+            (g,) = torch.autograd.grad(acq.sum(), og)
+            assert torch.allclose(acq.detach(), c["value"], rtol=1e-14) and torch.allclose(g, c["grad"], rtol=1e-12, atol=1e-300)
