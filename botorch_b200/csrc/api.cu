@@ -456,6 +456,11 @@ static bool fuse_enabled() {
     return on;
 }
 
+static bool fuse_enabled_h() {  // BO_FUSE_H=0: keep the separate (d+1)-row gradient GEMM (A/B measurements)
+    static const bool on = [] { const char* e = getenv("BO_FUSE_H"); return !e || atoi(e) != 0; }();
+    return on;
+}
+
 QWork qlayout(const bo_gp* gp, const bo_nei* nei, int B, int q, int with_grad, void* work, size_t cap) {
     QWork w{};
     const long n = gp->n, nb = nei->n_b, M = gp->M, Kp = bo_kp(gp->d);
@@ -667,8 +672,21 @@ int bo_qlognei_bwd(bo_ctx* ctx, const bo_gp* gp, const bo_nei* nei, int B, int q
         if (!fuse_u && !fuse_post)
             BO_TRY(bo_colblock_inplace(w.W1 + S1p * w.ldn, w.regionStride, w.Sbar, (int)n, B, q, (int)M, w.ldn, -2.0, st));
         if (fuse_post) { g.post = w.post; g.stridePost = w.stridePost; g.post_k0 = (int)S1p; }
+        // 4r. H = [train_X^T; 1] G  ((d+1) x N), then gradX += (H_t - x_t H_d) / l_t^2.  With the fused adjoint the
+        //     contraction rides on the GEMM's accumulators (BoGemm::hfuse): per-row-tile partials of H land in the region
+        //     that used to hold G, G itself is never written, and the separate (d+1)-row GEMM disappears.
+        const int tiles_m = (int)((n + BO_GRAM_BM - 1) / BO_GRAM_BM);
+        const bool fuse_h = fuse_post && gp->xt_aug != nullptr && gp->d + 1 <= BO_HFUSE_ROWS &&
+                            (long)tiles_m * BO_HFUSE_ROWS <= n && fuse_enabled_h();
+        if (fuse_h) {
+            g.hA = gp->xt_aug; g.ldhA = np; g.hrows = gp->d + 1;
+            g.hpart = w.W2; g.strideHpart = w.regionStride;
+            g.C = nullptr;
+            BO_TRY(bo_gemm_launch(g, st));
+            return bo_kgrad_finalize(h, w.W2, w.regionStride, w.ldn, X, N, 1.0, grad_X, tiles_m,
+                                     (long)BO_HFUSE_ROWS * w.ldn, st);
+        }
         BO_TRY(bo_gemm_launch(g, st));
-        // 4r. H = [train_X^T; 1] G  ((d+1) x N), then gradX += (H_t - x_t H_d) / l_t^2
         return kernel_gradient(gp, h, w, w.W2, X, N, grad_X, st);
     }
     a.Vbar_mu = w.W5 + n * w.ldn;

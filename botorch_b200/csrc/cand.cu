@@ -12,6 +12,9 @@
 namespace {
 
 constexpr int CAND_THREADS = 128;
+#ifndef BO_CAND_MINB4
+#define BO_CAND_MINB4 4  // resident CTAs per SM the q <= 4 kernels are compiled for; 6 and 8 (80 / 64 registers, spills) measured within noise at C4
+#endif
 constexpr int PANEL_ROWS = 64;
 
 // ---------------------------------------------------------------------------------------------
@@ -495,7 +498,7 @@ __device__ __forceinline__ double pair_r2(const double* X, int d, const double* 
 }
 
 template <int QT>
-__global__ void __launch_bounds__(CAND_THREADS, (QT <= 4 ? 6 : (QT <= 8 ? 4 : 1))) cand_fwd_kernel(const BoCandArgs a) {
+__global__ void __launch_bounds__(CAND_THREADS, (QT <= 4 ? BO_CAND_MINB4 : (QT <= 8 ? 4 : 1))) cand_fwd_kernel(const BoCandArgs a) {
     extern __shared__ __align__(16) double sm[];
     __shared__ double red[CAND_THREADS / 32];
     __shared__ int s_info;
@@ -653,7 +656,7 @@ namespace {
 //   out: F <- d loss / d f ;  Sbar = adjoint of the Schur block (symmetric);
 //        Vbar row n <- y_std * d loss / d mu ;  gradX <- contribution of k(X, X)
 template <int QT>
-__global__ void __launch_bounds__(CAND_THREADS, (QT <= 4 ? 6 : (QT <= 8 ? 4 : 1))) cand_bwd_kernel(const BoCandArgs a) {
+__global__ void __launch_bounds__(CAND_THREADS, (QT <= 4 ? BO_CAND_MINB4 : (QT <= 8 ? 4 : 1))) cand_bwd_kernel(const BoCandArgs a) {
     extern __shared__ __align__(16) double sm[];
     const int q = a.q, b = blockIdx.x, z = blockIdx.y, tid = threadIdx.x, T = blockDim.x;
     const int c0 = b * q;
@@ -996,6 +999,23 @@ __global__ void kgrad_finalize_kernel(BoKernelHyper h, const double* H, long str
         hd += Hz[k * strideKs + (long)d * ldn + c];
     }
     gradX[(long)z * N * d + idx] += scale * il * il * (ht - X[idx] * hd);
+}
+// The same for per-row-tile partials of a fused contraction (BoGemm::hfuse: dozens of slices instead of <= 8): one thread per
+// (input dimension, column) with the column fastest, so that every slice row is read coalesced.
+__global__ void kgrad_finalize_cols_kernel(BoKernelHyper h, const double* H, long strideH, long ldn, const double* X, long N,
+                                           double scale, double* gradX, int ksplit, long strideKs) {
+    const int z = blockIdx.z, d = h.d, t = blockIdx.y;
+    const long c = blockIdx.x * (long)blockDim.x + threadIdx.x;
+    if (c >= N) return;
+    const double il = h.inv_ls[(long)z * d + t];
+    const double* Hz = H + (long)z * strideH;
+    double ht = 0.0, hd = 0.0;
+#pragma unroll 4
+    for (int k = 0; k < ksplit; k++) {
+        ht += Hz[k * strideKs + (long)t * ldn + c];
+        hd += Hz[k * strideKs + (long)d * ldn + c];
+    }
+    gradX[(long)z * N * d + c * d + t] += scale * il * il * (ht - X[c * d + t] * hd);
 }
 size_t kgrad_smem_bytes(int q, int d, int T) {
     const int QD = q * d;
@@ -1382,6 +1402,12 @@ int bo_kgrad(const BoKernelHyper& h, const double* Xpts, int npts, const double*
 int bo_kgrad_finalize(const BoKernelHyper& h, const double* H, long strideH, long ldn, const double* X, long N,
                       double scale, double* gradX, int ksplit, long strideKs, cudaStream_t stream) {
     if (N <= 0) return BO_OK;
+    if (ksplit > 8) {  // many slices: coalesced form
+        dim3 gridc((unsigned)((N + 127) / 128), (unsigned)h.d, (unsigned)h.M);
+        kgrad_finalize_cols_kernel<<<gridc, 128, 0, stream>>>(h, H, strideH, ldn, X, N, scale, gradX, ksplit, strideKs);
+        BO_LAUNCH_CHECK();
+        return BO_OK;
+    }
     dim3 grid((unsigned)((N * h.d + 255) / 256), h.M);
     kgrad_finalize_kernel<<<grid, 256, 0, stream>>>(h, H, strideH, ldn, X, N, scale, gradX, ksplit, strideKs);
     BO_LAUNCH_CHECK();

@@ -90,7 +90,14 @@ struct BoGemm {
     //     never materialised.
     double* gram; long strideGram; int gram_row0;
     const double* post; long stridePost; int post_k0;
+    //   hfuse (backward, together with post): the (d+1)-row contraction H = hA C that follows this GEMM on the gradient
+    //     path is formed from the accumulators of every 64-row tile on the DMMA pipe and written as per-row-tile partials
+    //     hpart[z][row tile][BO_HFUSE_ROWS][ldc] (rows >= hrows are zero); summed over the tiles in order by
+    //     kgrad_finalize.  C itself is not stored when g.C is null: nobody reads G any more.
+    const double* hA; long ldhA; int hrows;   // [hrows x ldhA], shared by the batch: H = hA[:, 0:M] C
+    double* hpart; long strideHpart;
 };
+#define BO_HFUSE_ROWS 24  // padded row count of the fused gradient contraction (d + 1 <= 24)
 
 #define BO_GRAM_BM 64  // row-tile height of the gram partials
 // 1 if bo_gemm_launch(g) will run the kernel that honours g.gram / g.post

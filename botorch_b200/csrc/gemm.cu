@@ -280,6 +280,24 @@ __global__ void __launch_bounds__(C::THREADS) dgemm_dmma_kernel(const BoGemm p) 
                 *reinterpret_cast<double2*>(Cs + (wm0 + i * 8 + g) * LDC_S + wn0 + j * 8 + 2 * t) =
                     make_double2(acc[i][j][0], acc[i][j][1]);
         __syncthreads();
+        if (p.epi == BO_EPI_RBF && !p.diag_exact && p.diag_add == nullptr && CTz == nullptr && m0 + C::BM <= p.M &&
+            n0 + C::BN <= p.N) {
+            // interior tile of the plain RBF cross-covariance (the K = d+2 launch of every forward): two columns per
+            // thread and iteration, 16-byte loads / stores, four independent exp chains in flight, no per-element bounds or
+            // mode tests -- the generic loop below spent more issue slots on those than on the exp itself (ncu: 55 % issue
+            // utilisation, FP64 pipe 14 %)
+            const double os = p.os ? p.os[z] : 1.0;
+            constexpr int HALF = C::BN / 2;
+#pragma unroll 4
+            for (int e = tid; e < C::BM * HALF; e += C::THREADS) {
+                const int r = e / HALF, c2 = (e % HALF) * 2;
+                const double2 a = *reinterpret_cast<const double2*>(Cs + r * LDC_S + c2);
+                const double v0 = os * exp(-0.5 * (a.x > 0.0 ? a.x : 0.0));
+                const double v1 = os * exp(-0.5 * (a.y > 0.0 ? a.y : 0.0));
+                *reinterpret_cast<double2*>(Cz + (long)(m0 + r) * p.ldc + n0 + c2) = make_double2(v0, v1);
+            }
+            return;
+        }
 #pragma unroll 2
         for (int e = tid; e < C::BM * C::BN; e += C::THREADS) {
             const int r = e / C::BN, c = e % C::BN;
@@ -398,7 +416,7 @@ dgemm_dmma_tma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_cons
     else if (p.tri == BO_TRI_B_LOWER) kb = (n0 / C::BK) * C::BK;
     // fused adjoint (p.post): tiles of [post_k0, ke) first (through tmA / tmB), then the tiles of [0, post_k0) through the
     // second pair of maps, whose k extent ends at post_k0 (the tile that straddles it is zero-filled beyond)
-    constexpr bool has_post = (MODE == 2);
+    constexpr bool has_post = (MODE == 2 || MODE == 3);
     if (has_post) kb = p.post_k0;
     const int n_first = ke > kb ? (ke - kb + C::BK - 1) / C::BK : 0;
     const int ntiles = n_first + (has_post ? (p.post_k0 + C::BK - 1) / C::BK : 0);
@@ -558,6 +576,88 @@ dgemm_dmma_tma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_cons
         __syncthreads();  // the covariance epilogue below may stage through the same memory
     }
 
+    if constexpr (MODE == 3) {
+        // Fused gradient contraction: G = epilogue(acc) replaces the accumulators in place (LINEAR epilogue with the
+        // elementwise factor E), then Hpart[f][col] = sum_{r in tile} hA[f][m0 + r] G[r][col] on the DMMA pipe: the A
+        // operand comes from global memory (a (d+1) x 64 strip of hA), the B operand is the accumulator block re-laid by two
+        // shuffles + a select per k4 step, as in the gram mode.  Per-warp partials meet in shared memory (the ring is idle)
+        // and the warps stacked in M are added in a fixed order.
+        double* hs = tiles;  // [CONSUMERS][3][TN][64]
+        if (warp < C::CONSUMERS) {
+#pragma unroll
+            for (int i = 0; i < TM; i++) {
+                const int row = m0 + wm0 + i * 8 + g;
+#pragma unroll
+                for (int j = 0; j < TN; j++) {
+                    const int col = n0 + wn0 + j * 8 + 2 * t;
+                    const bool rv = row < p.M;
+                    acc[i][j][0] = (rv && col < p.N) ? epilogue_value(p, z, acc[i][j][0], row, col) : 0.0;
+                    acc[i][j][1] = (rv && col + 1 < p.N) ? epilogue_value(p, z, acc[i][j][1], row, col + 1) : 0.0;
+                }
+            }
+        }
+        __syncthreads();  // every warp is done reading the ring
+        if (warp < C::CONSUMERS) {
+#pragma unroll
+            for (int j = 0; j < TN; j++) {
+                double h[3][2];
+#pragma unroll
+                for (int fb = 0; fb < 3; fb++) h[fb][0] = h[fb][1] = 0.0;
+#pragma unroll
+                for (int i = 0; i < TM; i++) {
+#pragma unroll
+                    for (int hh = 0; hh < 2; hh++) {
+                        const int src = ((hh * 4 + t) << 2) | (g >> 1);
+                        const double y0 = __shfl_sync(0xffffffffu, acc[i][j][0], src);
+                        const double y1 = __shfl_sync(0xffffffffu, acc[i][j][1], src);
+                        const double bv = (g & 1) ? y1 : y0;  // G[row i*8 + hh*4 + t][col j*8 + g]
+                        const int arow = m0 + wm0 + i * 8 + hh * 4 + t;
+#pragma unroll
+                        for (int fb = 0; fb < 3; fb++) {
+                            const int f = fb * 8 + g;
+                            const double av = (f < p.hrows && arow < p.M) ? p.hA[(long)f * p.ldhA + arow] : 0.0;
+                            dmma884(h[fb][0], h[fb][1], av, bv);
+                        }
+                    }
+                }
+#pragma unroll
+                for (int fb = 0; fb < 3; fb++)
+                    *reinterpret_cast<double2*>(hs + ((warp * 3 + fb) * TN + j) * 64 + g * 8 + 2 * t) =
+                        make_double2(h[fb][0], h[fb][1]);
+            }
+        }
+        __syncthreads();
+        double* Hz = p.hpart + (long)z * p.strideHpart + (long)mt * BO_HFUSE_ROWS * p.ldc;
+        for (int e = tid; e < BO_HFUSE_ROWS * C::BN; e += C::THREADS) {
+            const int f = e / C::BN, c = e % C::BN;
+            if (n0 + c >= p.N) continue;
+            const int fb = f / 8, fg = f % 8, wn = (c / 8) / TN, j = (c / 8) % TN, cc = c % 8;
+            double s_ = 0.0;
+#pragma unroll
+            for (int wmi = 0; wmi < C::WARPS_M; wmi++)
+                s_ += hs[(((wmi * C::WARPS_N + wn) * 3 + fb) * TN + j) * 64 + fg * 8 + cc];
+            Hz[(long)f * p.ldc + n0 + c] = s_;
+        }
+        if (p.C == nullptr) return;
+        // G is still wanted: the accumulators already hold the epilogue values
+        double* __restrict__ Gz = p.C + (long)z * p.strideC;
+        if (warp < C::CONSUMERS) {
+#pragma unroll
+            for (int i = 0; i < TM; i++) {
+                const int row = m0 + wm0 + i * 8 + g;
+                if (row >= p.M) continue;
+#pragma unroll
+                for (int j = 0; j < TN; j++) {
+                    const int col = n0 + wn0 + j * 8 + 2 * t;
+                    if (col >= p.N) continue;
+                    if (col + 1 < p.N) *reinterpret_cast<double2*>(Gz + (long)row * p.ldc + col) = make_double2(acc[i][j][0], acc[i][j][1]);
+                    else Gz[(long)row * p.ldc + col] = acc[i][j][0];
+                }
+            }
+        }
+        return;
+    }
+
     double* __restrict__ Cz = p.C + (long)z * p.strideC;
     double* __restrict__ CTz = p.CT ? p.CT + (long)z * p.strideCT : nullptr;
     constexpr bool kStageFits = (size_t)C::BM * (C::BN + 2) * sizeof(double) <= (size_t)C::STAGES * C::STAGE_BYTES;
@@ -706,9 +806,9 @@ __device__ __forceinline__ TileGeo tile_geometry(const BoGemm& p, long L, int gx
     if (p.tri == BO_TRI_A_LOWER) q.ke = min(p.K, q.m0 + C::BM + p.tri_off);
     else if (p.tri == BO_TRI_A_UPPER) q.kb = q.m0 > p.tri_off ? ((q.m0 - p.tri_off) / C::BK) * C::BK : 0;
     else if (p.tri == BO_TRI_B_LOWER) q.kb = (q.n0 / C::BK) * C::BK;
-    if (MODE == 2) q.kb = p.post_k0;
+    if (MODE == 2 || MODE == 3) q.kb = p.post_k0;
     q.n_first = q.ke > q.kb ? (q.ke - q.kb + C::BK - 1) / C::BK : 0;
-    q.ntiles = q.n_first + (MODE == 2 ? (p.post_k0 + C::BK - 1) / C::BK : 0);
+    q.ntiles = q.n_first + ((MODE == 2 || MODE == 3) ? (p.post_k0 + C::BK - 1) / C::BK : 0);
     return q;
 }
 
@@ -798,7 +898,7 @@ dgemm_dmma_tma_persistent_kernel(const __grid_constant__ CUtensorMap tmA, const 
 #pragma unroll
             for (int j = 0; j < TN; j++) acc[i][j][0] = acc[i][j][1] = 0.0;
         for (int kt = 0; kt < q.ntiles; kt++, it++) {
-            if (MODE == 2 && kt == q.n_first) {
+            if ((MODE == 2 || MODE == 3) && kt == q.n_first) {
                 const double* P = p.post + (long)z * p.stridePost;
                 const int src_lo = (lane & ~3) | (t >> 1), src_hi = src_lo | 2;
 #pragma unroll
@@ -973,6 +1073,8 @@ template <class C>
 int launch_tma(const BoGemm& g, cudaStream_t stream) {
     if (g.gram != nullptr && g.post != nullptr) return BO_ERR_INVALID;
     if (g.gram != nullptr) return launch_tma_mode<C, 1>(g, stream);
+    if (g.post != nullptr && g.hpart != nullptr) return launch_tma_mode<C, 3>(g, stream);
+    if (g.hpart != nullptr) return BO_ERR_INVALID;  // hfuse rides on the post mode
     if (g.post != nullptr) return launch_tma_mode<C, 2>(g, stream);
     return launch_tma_mode<C, 0>(g, stream);
 }
@@ -994,7 +1096,10 @@ int launch_tma_mode(const BoGemm& g, cudaStream_t stream) {
     // at 3 resident CTAs to the end (14.3 of 15 warps active), the static work lists leave 12.2.  Off unless
     // BO_GEMM_PERSISTENT=1.
     static const bool pers_on = [] { const char* e = getenv("BO_GEMM_PERSISTENT"); return e && atoi(e) != 0; }();
-    const bool persistent = pers_on && g.epi == BO_EPI_LINEAR;
+    const bool persistent = pers_on && g.epi == BO_EPI_LINEAR && MODE != 3;
+    if (MODE == 3 && (g.hA == nullptr || g.hrows <= 0 || g.hrows > BO_HFUSE_ROWS || C::BM != BO_GRAM_BM ||
+                      (size_t)C::CONSUMERS * 3 * (C::WN / 8) * 64 * sizeof(double) > (size_t)C::STAGES * C::STAGE_BYTES))
+        return BO_ERR_INVALID;
     constexpr size_t SMEM_P = C::SMEM + (size_t)C::CONSUMERS * (C::WN / 8) * 64 * sizeof(double);
     static bool attr_set = false;
     if (!attr_set) {

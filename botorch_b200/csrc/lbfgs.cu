@@ -169,7 +169,10 @@ __global__ void __launch_bounds__(LB_THREADS) lbfgs_accept_kernel(const bo_lbfgs
     dec = block_sum(dec, red);
     moved = block_max(moved, red);
     const double f0 = s.f[b], f1 = f_trial[b];
-    const bool ok = isfinite(f1) && f1 <= f0 + c1 * dec && moved > 0.0;
+    // the clipped step must be a descent direction (after projection a quasi-Newton step can point uphill: dec > 0 would
+    // let an INCREASE of f pass the Armijo test and then look like convergence); such a trial is rejected and the step
+    // shrinks, ending in the steepest-descent restart below
+    const bool ok = isfinite(f1) && dec < 0.0 && f1 <= f0 + c1 * dec && moved > 0.0;
     if (ok) {
         double pg = 0.0;
         for (int i = tid; i < D; i += LB_THREADS) {

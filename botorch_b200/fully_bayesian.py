@@ -64,7 +64,10 @@ class SaasPotential:
         """Unconstrained [C x (d+4)] -> the dict ``postprocess_mcmc_samples`` produces (fully_bayesian.py:248-265)."""
         d = self.d
         tausq, ils = u[:, 0].exp(), u[:, 1 : 1 + d].exp()
-        return {"mean": u[:, 1 + d], "noise": MIN_INFERRED_NOISE_LEVEL + u[:, 2 + d].exp(), "outputscale": u[:, 3 + d].exp(),
+        # "noise" is the raw Gamma site, as pyro records it: the likelihood inside NUTS uses 1e-4 + noise
+        # (fully_bayesian.py:215-221) but the stored draw is the site value, and `load_mcmc_samples` clamps it from below
+        # (`clamp_min(MIN_INFERRED_NOISE_LEVEL)`, fully_bayesian.py:298) -- max(g, 1e-4), not g + 1e-4.  Same here.
+        return {"mean": u[:, 1 + d], "noise": u[:, 2 + d].exp(), "outputscale": u[:, 3 + d].exp(),
                 "lengthscale": (tausq.unsqueeze(-1) * ils).rsqrt()}  # fmt: skip
 
     def __call__(self, u: Tensor) -> Tuple[Tensor, Tensor]:

@@ -93,5 +93,7 @@ def potential_and_grad(U: Tensor, X: Tensor, y: Tensor, divergent_as_inf: bool =
 def constrained(U: Tensor, d: int) -> Dict[str, Tensor]:
     """What ``postprocess_mcmc_samples`` hands to ``load_mcmc_samples`` (:248-265): mean, noise, outputscale, lengthscale."""
     tausq, ils = U[:, 0].exp(), U[:, 1 : 1 + d].exp()
-    return {"mean": U[:, 1 + d], "noise": MIN_INFERRED_NOISE_LEVEL + U[:, 2 + d].exp(), "outputscale": U[:, 3 + d].exp(),
+    # "noise" is the raw pyro site (the Gamma draw): the likelihood adds MIN_INFERRED_NOISE_LEVEL inside `sample_noise`
+    # (:215-221) but MCMC records the site value, and `load_mcmc_samples` clamps it from below (:298)
+    return {"mean": U[:, 1 + d], "noise": U[:, 2 + d].exp(), "outputscale": U[:, 3 + d].exp(),
             "lengthscale": (tausq.unsqueeze(-1) * ils).rsqrt()}  # fmt: skip
