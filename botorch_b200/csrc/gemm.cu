@@ -597,6 +597,14 @@ dgemm_dmma_tma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_cons
             }
         }
         __syncthreads();  // every warp is done reading the ring
+        // the (d+1) x 64 strip of hA of this row tile, staged once (pitch 68: conflict-free fragment reads)
+        constexpr int HP = C::BM + 4;
+        double* hstrip = tiles + C::CONSUMERS * 3 * TN * 64;
+        for (int e = tid; e < BO_HFUSE_ROWS * C::BM; e += C::THREADS) {
+            const int f = e / C::BM, r = e % C::BM;
+            hstrip[f * HP + r] = (f < p.hrows && m0 + r < p.M) ? p.hA[(long)f * p.ldhA + m0 + r] : 0.0;
+        }
+        __syncthreads();
         if (warp < C::CONSUMERS) {
 #pragma unroll
             for (int j = 0; j < TN; j++) {
@@ -611,13 +619,9 @@ dgemm_dmma_tma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_cons
                         const double y0 = __shfl_sync(0xffffffffu, acc[i][j][0], src);
                         const double y1 = __shfl_sync(0xffffffffu, acc[i][j][1], src);
                         const double bv = (g & 1) ? y1 : y0;  // G[row i*8 + hh*4 + t][col j*8 + g]
-                        const int arow = m0 + wm0 + i * 8 + hh * 4 + t;
+                        const int ar = wm0 + i * 8 + hh * 4 + t;
 #pragma unroll
-                        for (int fb = 0; fb < 3; fb++) {
-                            const int f = fb * 8 + g;
-                            const double av = (f < p.hrows && arow < p.M) ? p.hA[(long)f * p.ldhA + arow] : 0.0;
-                            dmma884(h[fb][0], h[fb][1], av, bv);
-                        }
+                        for (int fb = 0; fb < 3; fb++) dmma884(h[fb][0], h[fb][1], hstrip[(fb * 8 + g) * HP + ar], bv);
                     }
                 }
 #pragma unroll
@@ -1098,7 +1102,8 @@ int launch_tma_mode(const BoGemm& g, cudaStream_t stream) {
     static const bool pers_on = [] { const char* e = getenv("BO_GEMM_PERSISTENT"); return e && atoi(e) != 0; }();
     const bool persistent = pers_on && g.epi == BO_EPI_LINEAR && MODE != 3;
     if (MODE == 3 && (g.hA == nullptr || g.hrows <= 0 || g.hrows > BO_HFUSE_ROWS || C::BM != BO_GRAM_BM ||
-                      (size_t)C::CONSUMERS * 3 * (C::WN / 8) * 64 * sizeof(double) > (size_t)C::STAGES * C::STAGE_BYTES))
+                      ((size_t)C::CONSUMERS * 3 * (C::WN / 8) * 64 + (size_t)BO_HFUSE_ROWS * (C::BM + 4)) * sizeof(double) >
+                          (size_t)C::STAGES * C::STAGE_BYTES))
         return BO_ERR_INVALID;
     constexpr size_t SMEM_P = C::SMEM + (size_t)C::CONSUMERS * (C::WN / 8) * 64 * sizeof(double);
     static bool attr_set = false;
@@ -1133,7 +1138,8 @@ int launch_tma_mode(const BoGemm& g, cudaStream_t stream) {
             g_prof_recs.push_back(r);
         }
         rec = &g_prof_recs[g_prof_used++];
-        g_prof_flops += 2.0 * gemm_macs(g) * g.N * g.batch;
+        // algorithmic flops of the launch: the product itself plus, in hfuse mode, the (d+1)-row contraction it absorbs
+        g_prof_flops += 2.0 * gemm_macs(g) * g.N * g.batch + (MODE == 3 ? 2.0 * g.hrows * (double)g.M * g.N * g.batch : 0.0);
         BO_CUDA_TRY(cudaEventRecord(rec->a, stream));
     }
     const int za = (g.batch > 1 && g.strideA == 0) ? 0 : 1, zb = (g.batch > 1 && g.strideB == 0) ? 0 : 1;
