@@ -28,7 +28,8 @@ from ._lib import check, pad8, ptr
 from .acquisition import DEFAULT_MC_SAMPLES, TAU_MAX, TAU_RELU, AcquisitionFunction, LinearMCObjective, _FusedImprovementBase
 from .exceptions import UnsupportedError
 from .models import Model, _FusedExactGP
-from .sampling import IIDNormalSampler, MCSampler, SobolQMCNormalSampler, draw_sobol_normal_samples, manual_seed
+from .sampling import (IIDNormalSampler, MCSampler, SobolQMCNormalSampler, _normal_from_uniform, draw_sobol_normal_samples,
+                       manual_seed, sobol_draw)  # fmt: skip
 
 _INV_SQRT_3 = math.sqrt(1.0 / 3.0)  # utils/safe_math.py: inflection point of the fatmoid
 
@@ -330,10 +331,16 @@ class qLogNEIModelList(AcquisitionFunction):
         self._best_f = self._compute_best_feasible_objective(base, self.baseline_obj).to(torch.float64).contiguous()
         self._baseline_best_f = self._best_f
 
-    def _draw(self, rows: int, m: int) -> Tensor:
+    def _draw(self, rows: int, m: int, first_row: int = 0) -> Tensor:
         """S x rows x m standard-normal base samples, generated as the reference's sampler does for a collapsed
-        ``S x 1 x rows x m`` posterior (sampling/normal.py:178-209 Sobol, :133-175 iid)."""
-        if isinstance(self.sampler, SobolQMCNormalSampler):
+        ``S x 1 x rows x m`` posterior (sampling/normal.py:178-209 Sobol, :133-175 iid).  ``first_row`` > 0: rows before it
+        are not needed by the caller and are left at zero (their Sobol dimensions are not computed)."""
+        if isinstance(self.sampler, SobolQMCNormalSampler) and first_row > 0:
+            cols = torch.arange(first_row * m, rows * m)
+            z = torch.zeros(self.S, rows * m, dtype=torch.float64)
+            u = sobol_draw(rows * m, self.S, seed=self.sampler.seed, dtype=torch.float64, columns=cols)
+            z[:, cols] = _normal_from_uniform(u)
+        elif isinstance(self.sampler, SobolQMCNormalSampler):
             z = draw_sobol_normal_samples(d=rows * m, n=self.S, dtype=torch.float64, seed=self.sampler.seed)
         else:
             with manual_seed(seed=self.sampler.seed):
@@ -346,7 +353,7 @@ class qLogNEIModelList(AcquisitionFunction):
         if q not in self._Zq_cache:
             n_b, m = self._Zb.shape[1], self._Zb.shape[2]
             dev = self._neis[0].device
-            full = self._draw(n_b + q, m)
+            full = self._draw(n_b + q, m, first_row=n_b)
             self._Zq_cache[q] = [full[:, n_b:, k].to(dev).contiguous() for k in range(m)]
         return self._Zq_cache[q]
 

@@ -17,6 +17,7 @@ it.  Applying the base samples (f = mu + L z) happens ins
 from __future__ import annotations
 
 import math
+import os
 from contextlib import contextmanager
 from typing import Optional, Tuple
 
@@ -42,6 +43,84 @@ def manual_seed(seed: Optional[int] = None):
             torch.random.set_rng_state(saved)
 
 
+_SOBOL_THREADS = max(1, min(8, os.cpu_count() or 1))
+_sobol_pool = None
+
+
+def _pool():
+    global _sobol_pool
+    if _sobol_pool is None:
+        from concurrent.futures import ThreadPoolExecutor
+
+        _sobol_pool = ThreadPoolExecutor(max_workers=_SOBOL_THREADS, thread_name_prefix="bo-sobol")
+    return _sobol_pool
+
+
+def sobol_draw(dimension: int, n: int, seed: Optional[int] = None, dtype: Optional[torch.dtype] = None,
+               columns: Optional[Tensor] = None) -> Tensor:  # fmt: skip
+    """The first ``n`` points of ``SobolEngine(dimension, scramble=True, seed=seed)`` -- bit for bit -- or only their
+    ``columns`` (a sorted 1-D index tensor), computed without scrambling the dimensions nobody reads.
+
+    The reference draws its base samples and raw candidates from torch's engine (sampling/qmc.py:39-105,
+    utils/sampling.py:97-140) and so do we; what changes is how the host work is laid out.  Owen scrambling is
+    independent per dimension: the random bits are one stream (``shift`` then the lower-triangular matrices, both drawn
+    for ALL dimensions so the stream position of every dimension is unchanged), but the 30 x 30 bit-matrix products and
+    the Gray-code recurrence touch one dimension at a time.  So (1) the appended-points draw of the cached-Cholesky path
+    needs q of the n_b + q dimensions (the baseline columns are overwritten, cached_cholesky.py:167-186) and pays for q;
+    (2) a full draw is split by dimension over host threads (torch's ops release the GIL).  At n_b = 2000, q = 8 the
+    first goes from ~70 ms to ~10 ms and the second from ~70 ms to ~25 ms on 8 cores; tests/test_host_logic.py holds
+    both to ``torch.equal`` with the stock engine.
+    """
+    if dimension > SobolEngine.MAXDIM or dimension < 1:
+        raise ValueError(f"Supported range of dimensionality for SobolEngine is [1, {SobolEngine.MAXDIM}]")
+    dtype = torch.get_default_dtype() if dtype is None else dtype
+    bits = SobolEngine.MAXBIT
+    cpu = torch.device("cpu")
+    state = torch.zeros(dimension, bits, device=cpu, dtype=torch.long)
+    torch._sobol_engine_initialize_state_(state, dimension)
+    g = None
+    if seed is not None:
+        g = torch.Generator()
+        g.manual_seed(seed)
+    shift_bits = torch.randint(2, (dimension, bits), device=cpu, generator=g)
+    ltm = torch.randint(2, (dimension, bits, bits), device=cpu, generator=g)
+    pow2 = torch.pow(2, torch.arange(0, bits, device=cpu))
+    if columns is None:
+        width = dimension
+    else:
+        columns = columns.to(device=cpu, dtype=torch.long)
+        width = columns.numel()
+    out = torch.empty(n, width, dtype=dtype)
+    if width == 0 or n == 0:
+        return out
+
+    def work(a: int, b: int) -> None:
+        sel = slice(a, b) if columns is None else columns[a:b]
+        st = state[sel].contiguous()
+        lower = ltm[sel].tril().contiguous()
+        torch._sobol_engine_scramble_(st, lower, b - a)
+        quasi = torch.mv(shift_bits[sel], pow2).clone(memory_format=torch.contiguous_format)
+        out[0, a:b] = (quasi / 2**bits).to(dtype)
+        if n > 1:
+            rest, _ = torch._sobol_engine_draw(quasi, n - 1, st, b - a, 0, dtype=dtype)
+            out[1:, a:b] = rest
+
+    chunks = max(1, min(_SOBOL_THREADS, width // 16))
+    edges = [(width * i) // chunks for i in range(chunks + 1)]
+    if chunks == 1:
+        work(0, width)
+    else:
+        for f in [_pool().submit(work, edges[i], edges[i + 1]) for i in range(chunks)]:
+            f.result()
+    return out
+
+
+def _normal_from_uniform(u: Tensor) -> Tensor:
+    """Inverse normal CDF after shrinking the uniforms away from {0, 1} by one ulp (sampling/qmc.py:92-96)."""
+    v = 0.5 + (1 - torch.finfo(u.dtype).eps) * (u - 0.5)
+    return torch.erfinv(2 * v - 1) * math.sqrt(2)
+
+
 class NormalQMCEngine:
     """Quasi-random N(0, I_d) draws from a scrambled Sobol sequence.
 
@@ -54,14 +133,23 @@ class NormalQMCEngine:
         self._seed = seed
         self._inv_transform = inv_transform
         sobol_dim = d if inv_transform else 2 * math.ceil(d / 2)
-        self._sobol_engine = SobolEngine(dimension=sobol_dim, scramble=True, seed=seed)
+        self._sobol_dim = sobol_dim
+        self._sobol_engine = None  # torch's engine, built only for a second draw (the first goes through sobol_draw)
+        self._drawn = 0
 
     def draw(self, n: int = 1, out: Optional[Tensor] = None, dtype: Optional[torch.dtype] = None) -> Optional[Tensor]:
         dtype = torch.get_default_dtype() if dtype is None else dtype
-        u = self._sobol_engine.draw(n, dtype=dtype)
+        if self._drawn == 0 and self._seed is not None:
+            u = sobol_draw(self._sobol_dim, n, seed=self._seed, dtype=dtype)
+        else:
+            if self._sobol_engine is None:
+                self._sobol_engine = SobolEngine(dimension=self._sobol_dim, scramble=True, seed=self._seed)
+                if self._drawn:
+                    self._sobol_engine.fast_forward(self._drawn)
+            u = self._sobol_engine.draw(n, dtype=dtype)
+        self._drawn += n
         if self._inv_transform:
-            v = 0.5 + (1 - torch.finfo(u.dtype).eps) * (u - 0.5)
-            z = torch.erfinv(2 * v - 1) * math.sqrt(2)
+            z = _normal_from_uniform(u)
         else:
             even = torch.arange(0, u.shape[-1], 2)
             radius = torch.sqrt(-2 * torch.log(u[:, even]))
@@ -85,8 +173,8 @@ def draw_sobol_samples(
     batch_shape = torch.Size(batch_shape or ())
     d = bounds.shape[-1]
     lower, width = bounds[0], bounds[1] - bounds[0]
-    engine = SobolEngine(q * d, scramble=True, seed=seed)
-    u = engine.draw(batch_shape.numel() * n, dtype=lower.dtype).view(*batch_shape, n, q, d).to(device=lower.device)
+    u = sobol_draw(q * d, batch_shape.numel() * n, seed=seed, dtype=lower.dtype)
+    u = u.view(*batch_shape, n, q, d).to(device=lower.device)
     if len(batch_shape) > 0:  # the sample index leads
         u = u.movedim(len(batch_shape), 0)
     return lower + width * u
@@ -100,8 +188,7 @@ def draw_sobol_normal_samples(
     seed: Optional[int] = None,
 ) -> Tensor:
     """``n x d`` quasi-random standard normal draws (inverse-CDF Sobol)."""
-    engine = NormalQMCEngine(d=d, seed=seed, inv_transform=True)
-    return engine.draw(n, dtype=dtype).to(device=device)
+    return _normal_from_uniform(sobol_draw(d, n, seed=seed, dtype=dtype)).to(device=device)
 
 
 class MCSampler(Module):
@@ -185,7 +272,9 @@ class IIDNormalSampler(NormalMCSampler):
 class SobolQMCNormalSampler(NormalMCSampler):
     """Scrambled-Sobol N(0,1) base samples through the inverse CDF."""
 
-    def _construct_base_samples(self, posterior) -> None:
+    def _construct_base_samples(self, posterior, skip_leading: int = 0) -> None:
+        """``skip_leading`` > 0: the caller overwrites the first ``skip_leading`` entries of the last dimension, so only
+        the other Sobol dimensions are computed (``sobol_draw(columns=...)``); the skipped entries are left at zero."""
         target = self._get_collapsed_shape(posterior=posterior)
         if self.base_samples is None or self.base_samples.shape != target:
             dim = target[len(self.sample_shape) :].numel()
@@ -193,11 +282,23 @@ class SobolQMCNormalSampler(NormalMCSampler):
                 raise UnsupportedError(
                     f"SobolQMCSampler only supports dimensions `q * o <= {SobolEngine.MAXDIM}`. Requested: {dim}"
                 )
-            z = draw_sobol_normal_samples(
-                d=dim, n=self.sample_shape.numel(), device=posterior.device, dtype=posterior.dtype, seed=self.seed
-            )
+            n = self.sample_shape.numel()
+            if skip_leading > 0:
+                cols = torch.nonzero(torch.arange(dim) % target[-1] >= skip_leading).squeeze(-1)
+                z = torch.zeros(n, dim, dtype=posterior.dtype)
+                z[:, cols] = _normal_from_uniform(sobol_draw(dim, n, seed=self.seed, dtype=posterior.dtype, columns=cols))
+                z = z.to(device=posterior.device)
+            else:
+                z = draw_sobol_normal_samples(d=dim, n=n, device=posterior.device, dtype=posterior.dtype, seed=self.seed)
             self.register_buffer("base_samples", z.view(target))
         self.to(device=posterior.device, dtype=posterior.dtype)
+
+    def _update_base_samples(self, posterior, base_sampler: "NormalMCSampler") -> None:
+        self._instance_check(base_sampler=base_sampler)
+        prev = base_sampler.base_samples
+        if prev is not None:
+            self._construct_base_samples(posterior=posterior, skip_leading=prev.shape[-1])
+        super()._update_base_samples(posterior=posterior, base_sampler=base_sampler)
 
 
 def get_sampler(posterior, sample_shape: torch.Size, seed: Optional[int] = None) -> MCSampler:

@@ -148,6 +148,48 @@ def test_sampler_shapes_seeding_and_baseline_columns():
         bb.SobolQMCNormalSampler(S)._construct_base_samples(big)
 
 
+def test_sobol_draw_is_bit_identical_to_the_stock_engine():
+    """``sampling.sobol_draw`` (column-sliced, split by dimension over host threads) against torch's ``SobolEngine`` --
+    the generator the reference's samplers use (sampling/qmc.py:39-105, utils/sampling.py:97-140): ``torch.equal``."""
+    from torch.quasirandom import SobolEngine
+
+    from botorch_b200.sampling import NormalQMCEngine, sobol_draw
+
+    for dim, n, dtype in [(1, 1, torch.float64), (7, 5, torch.float64), (160, 1024, torch.float64), (408, 64, torch.float32),
+                          (1203, 33, torch.float64)]:  # fmt: skip
+        ref = SobolEngine(dim, scramble=True, seed=99).draw(n, dtype=dtype)
+        assert torch.equal(sobol_draw(dim, n, seed=99, dtype=dtype), ref)
+        cols = torch.arange(dim)[-(dim // 3 + 1) :]
+        assert torch.equal(sobol_draw(dim, n, seed=99, dtype=dtype, columns=cols), ref[:, cols])
+        cols = torch.nonzero(torch.arange(dim) % 5 >= 3).squeeze(-1)  # strided selection (ensemble-collapsed layout)
+        assert torch.equal(sobol_draw(dim, n, seed=99, dtype=dtype, columns=cols), ref[:, cols])
+    # unseeded: the scramble bits come from the global stream in the same order
+    torch.manual_seed(7)
+    ref = SobolEngine(40, scramble=True).draw(16, dtype=torch.float64)
+    torch.manual_seed(7)
+    assert torch.equal(sobol_draw(40, 16, dtype=torch.float64), ref)
+    with pytest.raises(ValueError):
+        sobol_draw(SobolEngine.MAXDIM + 1, 2, seed=0)
+    # the normal engine keeps its position across draws
+    e = NormalQMCEngine(d=6, seed=5, inv_transform=True)
+    a, b = e.draw(4, dtype=torch.float64), e.draw(3, dtype=torch.float64)
+    u = SobolEngine(6, scramble=True, seed=5).draw(7, dtype=torch.float64)
+    v = 0.5 + (1 - torch.finfo(u.dtype).eps) * (u - 0.5)
+    assert torch.equal(torch.cat([a, b]), torch.erfinv(2 * v - 1) * 2**0.5)
+    # appended points of the cached-Cholesky path: only the last q Sobol dimensions are computed
+    from copy import deepcopy
+
+    S, n_b, q = torch.Size([16]), 300, 4
+    s = bb.SobolQMCNormalSampler(S, seed=11)
+    s._construct_base_samples(_ShapeOnlyPosterior(torch.Size(), n_b, torch.device("cpu"), torch.float64))
+    base = deepcopy(s)
+    s._update_base_samples(_ShapeOnlyPosterior(torch.Size([1]), n_b + q, torch.device("cpu"), torch.float64), base)
+    u = SobolEngine(n_b + q, scramble=True, seed=11).draw(16, dtype=torch.float64)
+    v = 0.5 + (1 - torch.finfo(u.dtype).eps) * (u - 0.5)
+    assert torch.equal(s.base_samples[:, 0, n_b:], (torch.erfinv(2 * v - 1) * 2**0.5)[:, n_b:])
+    assert torch.equal(s.base_samples[:, 0, :n_b], base.base_samples)
+
+
 def test_initialize_q_batch_semantics():
     """optim/initializers.py:893-965 and test/optim/test_initializers.py:131-243."""
     torch.manual_seed(0)
