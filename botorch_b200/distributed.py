@@ -184,18 +184,23 @@ def all_gather_blocks(local: Tensor, total: int) -> Tensor:
     return torch.cat([o[: hi - lo] for o, (lo, hi) in zip(out, sizes)], dim=0)
 
 
-def sharded_raw_sample_values(acq_function, X_rnd: Tensor, device, batch_limit: Optional[int] = None) -> Tensor:
-    """Acquisition values of all raw q-batches; each rank evaluates its contiguous block (global order kept)."""
+def sharded_raw_sample_values(acq_function, X_rnd: Tensor, device, batch_limit: Optional[int] = None,
+                              total: Optional[int] = None) -> Tensor:  # fmt: skip
+    """Acquisition values of all raw q-batches; each rank evaluates its contiguous block (global order kept).  ``X_rnd`` is
+    the whole set (every rank holds it and slices its block) or, with ``total`` given, this rank's block of ``total``."""
     from .optim import evaluate_raw_samples
 
     rank, ws = world()
-    lo, hi = shard_range(X_rnd.shape[0], rank, ws)
-    y_local = evaluate_raw_samples(acq_function, X_rnd[lo:hi], device, batch_limit)
+    if total is None:
+        total = X_rnd.shape[0]
+        lo, hi = shard_range(total, rank, ws)
+        X_rnd = X_rnd[lo:hi]
+    y_local = evaluate_raw_samples(acq_function, X_rnd, device, batch_limit)
     if ws == 1:
         return y_local
     backend = _backend()
     y_dev = y_local.to(device) if backend == "nccl" else y_local
-    return all_gather_blocks(y_dev, X_rnd.shape[0]).cpu()
+    return all_gather_blocks(y_dev, total).cpu()
 
 
 def gather_best(values: Tensor, candidates: Tensor, index_offset: int) -> Tuple[Tensor, Tensor, int]:
@@ -364,7 +369,7 @@ def optimize_acqf_sharded(
     """
     from time import perf_counter
 
-    from .optim import gen_candidates_scipy, initialize_q_batch
+    from .optim import gen_candidates_scipy, initialize_q_batch_indices
     from .sampling import draw_sobol_samples
 
     options = dict(options or {})
@@ -384,22 +389,31 @@ def optimize_acqf_sharded(
     seed = shared_seed(options.get("seed"), device)
     # the base samples of the q new points are drawn on a host thread while this one draws the raw samples
     pending = acq_function.prefetch_base_samples(q) if hasattr(acq_function, "prefetch_base_samples") else None
-    X_rnd = draw_sobol_samples(bounds=bounds.cpu(), n=raw_samples, q=q, seed=seed)
+    # each rank draws only the rows of the raw samples it evaluates (the engine fast-forwarded to its block): the draw,
+    # the box scaling and the host->device copy all shrink with the world size
+    lo_r, hi_r = shard_range(raw_samples, rank, ws)
+    X_loc = draw_sobol_samples(bounds=bounds.cpu(), n=raw_samples, q=q, seed=seed, rows=(lo_r, hi_r))
     if pending is not None:
         pending.join()
     t = mark("raw_sample_draw_s", t)
-    Y_rnd = sharded_raw_sample_values(acq_function, X_rnd, device, options.get("init_batch_limit"))
+    Y_rnd = sharded_raw_sample_values(acq_function, X_loc, device, options.get("init_batch_limit"), total=raw_samples)
     t = mark("raw_sample_eval_and_allgather_s", t)
-    # identical host RNG stream on every rank => identical initial conditions everywhere
+    # identical host RNG stream on every rank => identical selection everywhere; the selected rows are then fetched from
+    # the ranks that drew them (one all-gather of the blocks, on the device under NCCL)
     gen = torch.random.get_rng_state()
     torch.manual_seed(seed or 0)
-    ics = initialize_q_batch(X=X_rnd, Y=Y_rnd, n=num_restarts, **({"eta": options["eta"]} if "eta" in options else {}))
+    idcs = initialize_q_batch_indices(Y=Y_rnd, n=num_restarts, **({"eta": options["eta"]} if "eta" in options else {}))
     torch.random.set_rng_state(gen)
-    t = mark("initial_condition_selection_s", t)
     lo, hi = shard_range(num_restarts, rank, ws)
+    if ws == 1:
+        ics_local = X_loc[idcs[lo:hi]]
+    else:
+        X_dev = X_loc.to(device) if _backend() == "nccl" else X_loc
+        ics_local = all_gather_blocks(X_dev, raw_samples)[idcs[lo:hi].to(X_dev.device)]
+    t = mark("initial_condition_selection_s", t)
     gen_candidates = gen_candidates or gen_candidates_scipy
     gen_opts = {k: v for k, v in options.items() if k in ("maxiter", "method", "with_grad", "disp", "ftol", "gtol")}
-    cands, vals = gen_candidates(ics[lo:hi].to(device), acq_function, lower_bounds=bounds[0], upper_bounds=bounds[1],
+    cands, vals = gen_candidates(ics_local.to(device), acq_function, lower_bounds=bounds[0], upper_bounds=bounds[1],
                                  options=gen_opts)  # fmt: skip
     t = mark("restart_optimisation_s", t)
     cand, val, _ = gather_best(vals, cands, lo)

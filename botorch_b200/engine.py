@@ -313,10 +313,13 @@ def path_values(ps: "PathState", X: Tensor) -> Tensor:
     return ps.evaluate(X.detach())
 
 
-# CUDA graphs pay only where a step is launch-bound (C1 / C2: 0.1 ms for ~11 launches).  Capturing one shape costs ~25 ms
-# (profiles/r02_strong_c3_host_profile.txt); at C3 a step is 1.6 ms of kernels that the host enqueues well ahead of the
-# GPU, so shapes whose workspace exceeds this stay eager.
+# CUDA graphs pay only where a step is launch-bound (C1 / C2: 0.1 ms for ~11 launches) AND the shape recurs often enough
+# to amortise the capture (tools/graph_cost.py: 30-46 ms for the first capture of a process, 2-4 ms afterwards, <= 20 us
+# saved per replay).  At C3 a step is 1.5 ms of kernels that the host enqueues well ahead of the GPU, so shapes whose
+# workspace exceeds GRAPH_MAX_WORKSPACE_BYTES stay eager; smaller ones are captured at their GRAPH_MIN_USES-th use
+# (BOTORCH_B200_GRAPH_AFTER overrides, BOTORCH_B200_GRAPHS=0 disables).
 GRAPH_MAX_WORKSPACE_BYTES = 16 << 20
+GRAPH_MIN_USES = 64
 
 
 class NEIState:
@@ -407,13 +410,16 @@ class NEIState:
         cache = self.__dict__.setdefault("_graphs", {})
         ge = cache.get(key)
         if ge is None:
-            # Capture pays for itself only when a shape recurs (the L-BFGS loop): a capture runs the launch sequence three
-            # times and pins a private workspace.  One-shot shapes -- the raw-sample sweep of gen_batch_initial_conditions
-            # (32 768 t-batches, ~9 GB of workspace at C3), the final evaluation -- stay eager: first use of a key only
-            # counts it.  Shapes whose kernels run for milliseconds gain nothing from saving ~10 launch latencies either.
+            # Capture pays for itself only when a shape recurs MANY times.  Measured (tools/graph_cost.py,
+            # profiles/r02_graph_cost.json): the first capture in a process costs 30-46 ms and later ones 2-4 ms, while a
+            # replay saves at most ~20 us per evaluation over the eager launches when the caller does not synchronise per
+            # round (C1, B = 8: 0.098 -> 0.077 ms) and nothing at C3 shapes -- so the shrinking-batch L-BFGS loop of one
+            # acquisition (20-40 rounds per shape) lost 22 ms of 150 to captures it never amortised.  A key is captured at
+            # its GRAPH_MIN_USES-th use (long SciPy loops on small problems); one-shot and short-lived shapes stay eager.
             seen = self.__dict__.setdefault("_graph_seen", {})
             seen[key] = seen.get(key, 0) + 1
-            if seen[key] < 2 or self.workspace_bytes(B, q, with_grad) > GRAPH_MAX_WORKSPACE_BYTES:
+            min_uses = int(os.environ.get("BOTORCH_B200_GRAPH_AFTER", GRAPH_MIN_USES))
+            if seen[key] < min_uses or self.workspace_bytes(B, q, with_grad) > GRAPH_MAX_WORKSPACE_BYTES:
                 return None
             if len(cache) >= 6:  # each entry pins its workspace; keep the most recent shapes only
                 cache.pop(next(iter(cache)))

@@ -44,6 +44,34 @@ INIT_OPTION_KEYS = {
 # -------------------------------------------------------------------------------------------------
 # initial conditions
 # -------------------------------------------------------------------------------------------------
+def initialize_q_batch_indices(Y: Tensor, n: int, eta: float = 1.0) -> Tensor:
+    """Indices ``initialize_q_batch`` selects: ``n`` of the raw q-batches with probability ~ exp(eta * zscore(Y)), the best
+    one always kept (initializers.py:906-951).  Consumes torch's host RNG stream exactly as the reference does."""
+    n_samples = Y.shape[0]
+    if n > n_samples:
+        raise RuntimeError(f"n ({n}) cannot be larger than the number of provided samples ({n_samples})")
+    if n == n_samples:
+        return torch.arange(n_samples, device=Y.device)
+    Ystd = Y.std(dim=0)
+    if bool(torch.any(Ystd == 0)):
+        warnings.warn(
+            "All acquisition values for raw samples points are the same for at least one batch. Choosing initial "
+            "conditions at random.",
+            BadInitialCandidatesWarning,
+        )
+        return torch.randperm(n=n_samples, device=Y.device)[:n]
+    max_idx = torch.argmax(Y, dim=0)
+    etaZ = eta * (Y - Y.mean(dim=0)) / Ystd
+    weights = torch.exp(etaZ)
+    while bool(torch.isinf(weights).any()):
+        etaZ = etaZ * 0.5
+        weights = torch.exp(etaZ)
+    idcs = torch.multinomial(weights, n)
+    if max_idx not in idcs:
+        idcs[-1] = max_idx
+    return idcs
+
+
 def initialize_q_batch(X: Tensor, Y: Tensor, n: int, eta: float = 1.0) -> Tensor:
     """Pick ``n`` of the raw q-batches with probability ~ exp(eta * zscore(Y)); the best one is always kept.
 
@@ -57,24 +85,7 @@ def initialize_q_batch(X: Tensor, Y: Tensor, n: int, eta: float = 1.0) -> Tensor
         return X
     if X.dim() != 3:
         raise UnsupportedError("initialize_q_batch on the fused path takes b x q x d raw samples (no extra batch dims)")
-    Ystd = Y.std(dim=0)
-    if bool(torch.any(Ystd == 0)):
-        warnings.warn(
-            "All acquisition values for raw samples points are the same for at least one batch. Choosing initial "
-            "conditions at random.",
-            BadInitialCandidatesWarning,
-        )
-        return X[torch.randperm(n=n_samples, device=X.device)][:n]
-    max_idx = torch.argmax(Y, dim=0)
-    etaZ = eta * (Y - Y.mean(dim=0)) / Ystd
-    weights = torch.exp(etaZ)
-    while bool(torch.isinf(weights).any()):
-        etaZ = etaZ * 0.5
-        weights = torch.exp(etaZ)
-    idcs = torch.multinomial(weights, n)
-    if max_idx not in idcs:
-        idcs[-1] = max_idx
-    return X[idcs]
+    return X[initialize_q_batch_indices(Y, n, eta).to(X.device)]
 
 
 def gen_batch_initial_conditions(

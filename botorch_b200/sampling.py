@@ -57,9 +57,11 @@ def _pool():
 
 
 def sobol_draw(dimension: int, n: int, seed: Optional[int] = None, dtype: Optional[torch.dtype] = None,
-               columns: Optional[Tensor] = None) -> Tensor:  # fmt: skip
-    """The first ``n`` points of ``SobolEngine(dimension, scramble=True, seed=seed)`` -- bit for bit -- or only their
-    ``columns`` (a sorted 1-D index tensor), computed without scrambling the dimensions nobody reads.
+               columns: Optional[Tensor] = None, first: int = 0) -> Tensor:  # fmt: skip
+    """Points ``first .. first + n - 1`` of ``SobolEngine(dimension, scramble=True, seed=seed)`` -- bit for bit -- or only
+    their ``columns`` (a sorted 1-D index tensor), computed without scrambling the dimensions nobody reads.  ``first`` > 0
+    is the engine's ``fast_forward(first)`` (integer recurrence only): a rank that evaluates rows [lo, hi) of the raw
+    samples draws those rows and no others.
 
     The reference draws its base samples and raw candidates from torch's engine (sampling/qmc.py:39-105,
     utils/sampling.py:97-140) and so do we; what changes is how the host work is laid out.  Owen scrambling is
@@ -100,10 +102,16 @@ def sobol_draw(dimension: int, n: int, seed: Optional[int] = None, dtype: Option
         lower = ltm[sel].tril().contiguous()
         torch._sobol_engine_scramble_(st, lower, b - a)
         quasi = torch.mv(shift_bits[sel], pow2).clone(memory_format=torch.contiguous_format)
-        out[0, a:b] = (quasi / 2**bits).to(dtype)
-        if n > 1:
-            rest, _ = torch._sobol_engine_draw(quasi, n - 1, st, b - a, 0, dtype=dtype)
-            out[1:, a:b] = rest
+        if first == 0:  # point 0 is the shift itself (quasirandom.py:77-113)
+            out[0, a:b] = (quasi / 2**bits).to(dtype)
+            if n > 1:
+                rest, _ = torch._sobol_engine_draw(quasi, n - 1, st, b - a, 0, dtype=dtype)
+                out[1:, a:b] = rest
+        else:
+            if first > 1:
+                torch._sobol_engine_ff_(quasi, first - 1, st, b - a, 0)
+            rest, _ = torch._sobol_engine_draw(quasi, n, st, b - a, first - 1, dtype=dtype)
+            out[:, a:b] = rest
 
     chunks = max(1, min(_SOBOL_THREADS, width // 16))
     edges = [(width * i) // chunks for i in range(chunks + 1)]
@@ -168,11 +176,16 @@ def draw_sobol_samples(
     q: int,
     batch_shape: Optional[torch.Size] = None,
     seed: Optional[int] = None,
+    rows: Optional[Tuple[int, int]] = None,
 ) -> Tensor:
     """``n x batch_shape x q x d`` scrambled-Sobol points inside the box ``bounds`` (2 x d)."""
     batch_shape = torch.Size(batch_shape or ())
     d = bounds.shape[-1]
     lower, width = bounds[0], bounds[1] - bounds[0]
+    if rows is not None:  # rows [lo, hi) of the n points only (no batch shape): one rank's block of the raw samples
+        lo, hi = rows
+        u = sobol_draw(q * d, hi - lo, seed=seed, dtype=lower.dtype, first=lo).view(hi - lo, q, d).to(device=lower.device)
+        return lower + width * u
     u = sobol_draw(q * d, batch_shape.numel() * n, seed=seed, dtype=lower.dtype)
     u = u.view(*batch_shape, n, q, d).to(device=lower.device)
     if len(batch_shape) > 0:  # the sample index leads

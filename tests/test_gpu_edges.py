@@ -140,3 +140,44 @@ def test_failed_cached_update_falls_back_to_standard_sampling(cuda):
         warnings.simplefilter("ignore")
         with torch.no_grad():
             acqf(Xn.to(cuda))
+
+
+def test_graph_replay_equals_eager_launches_bit_for_bit(cuda, monkeypatch):
+    """A recurring small shape is captured into a CUDA graph at its GRAPH_MIN_USES-th use (engine.NEIState.graphed):
+    replays must return the bits the eager launch sequence returns, for values and gradients, and one-shot shapes must
+    stay eager."""
+    import botorch_b200 as bb
+    from botorch_b200 import engine
+    from botorch_b200.synthetic import make_problem
+    from tests.util import candidates
+
+    monkeypatch.setenv("BOTORCH_B200_GRAPH_AFTER", "3")
+    p = make_problem("C1")
+    h = p.hypers
+    model = bb.SingleTaskGP(p.train_X.to(cuda), p.train_Y.to(cuda), lengthscale=h["lengthscale"], noise=h["noise"],
+                            mean_constant=h["mean"])  # fmt: skip
+    acqf = bb.qLogNoisyExpectedImprovement(model, p.train_X.to(cuda),
+                                           sampler=bb.SobolQMCNormalSampler(torch.Size([p.mc_samples]), seed=1234))  # fmt: skip
+    X = candidates(p, 4).to(cuda)
+
+    def value_and_grad(Xd):
+        Xd = Xd.clone().requires_grad_(True)
+        v = acqf(Xd)
+        (g,) = torch.autograd.grad(v.sum(), Xd)
+        return v.detach().clone(), g.clone()
+
+    v0, g0 = value_and_grad(X)  # uses 1 and 2 of the key: eager
+    v1, g1 = value_and_grad(X)
+    assert not acqf._nei.__dict__.get("_graphs")
+    v2, g2 = value_and_grad(X)  # third use: captured and replayed
+    v3, g3 = value_and_grad(X)
+    graphs = acqf._nei.__dict__.get("_graphs")
+    assert graphs and all(isinstance(ge, engine.GraphedEval) for ge in graphs.values())
+    for v, g in ((v1, g1), (v2, g2), (v3, g3)):
+        assert torch.equal(v, v0) and torch.equal(g, g0)
+    X2 = candidates(p, 4, seed=5).to(cuda)
+    va, ga = value_and_grad(X2)  # replay with new inputs
+    monkeypatch.setenv("BOTORCH_B200_GRAPHS", "0")
+    vb, gb = value_and_grad(X2)  # eager
+    assert torch.equal(va, vb) and torch.equal(ga, gb)
+    assert engine.GRAPH_MIN_USES >= 32  # default: short-lived shapes are never captured (profiles/r02_graph_cost.json)
