@@ -1082,35 +1082,58 @@ __global__ void __launch_bounds__(CAND_THREADS) cand_posterior_bwd_kernel(const 
     }
 }
 
-__global__ void col_mean_var_kernel(const double* V, long strideV, long ldn, int n, long Nc, double y_mean,
-                                    double y_std, const double* mean_const, const double* outputscale, double* mean,
-                                    double* var) {
-    const int z = blockIdx.y;
-    const long c = blockIdx.x * (long)blockDim.x + threadIdx.x;
-    if (c >= Nc) return;
+// Column statistics of a row-major panel.  Block = 32 columns x COL_LANES row lanes: a warp reads 32 consecutive doubles
+// of one row (256 B, coalesced), lane group `ty` owns rows ty, ty + COL_LANES, ... and the lanes are combined in fixed
+// order through shared memory, so the result depends on neither the grid nor the scheduling.  (The first version had one
+// thread per column and 128-column blocks: 128 CTAs for a 16 384-candidate chunk, 0.19 of HBM peak, and TWO CTAs for the
+// 256 sample columns of bo_nei_setup -- profiles/r02_kernel_rooflines.md.)
+constexpr int COL_LANES = 8;
+__global__ void __launch_bounds__(32 * COL_LANES) col_mean_var_kernel(const double* V, long strideV, long ldn, int n,
+                                                                      long Nc, double y_mean, double y_std,
+                                                                      const double* mean_const, const double* outputscale,
+                                                                      double* mean, double* var) {
+    __shared__ double part[COL_LANES][33];
+    const int z = blockIdx.y, tx = threadIdx.x, ty = threadIdx.y;
+    const long c = blockIdx.x * 32L + tx;
     const double* Vz = V + (long)z * strideV;
-    double s0 = 0.0, s1 = 0.0, s2 = 0.0, s3 = 0.0;  // 4 independent chains, fixed order
-    int i = 0;
-    for (; i + 3 < n; i += 4) {
-        const double v0 = Vz[(long)i * ldn + c], v1 = Vz[(long)(i + 1) * ldn + c];
-        const double v2 = Vz[(long)(i + 2) * ldn + c], v3 = Vz[(long)(i + 3) * ldn + c];
-        s0 += v0 * v0; s1 += v1 * v1; s2 += v2 * v2; s3 += v3 * v3;
+    double s0 = 0.0, s1 = 0.0, s2 = 0.0, s3 = 0.0;  // 4 independent chains per lane, fixed order
+    if (c < Nc) {
+        int i = ty;
+        for (; i + 3 * COL_LANES < n; i += 4 * COL_LANES) {
+            const double v0 = Vz[(long)i * ldn + c], v1 = Vz[(long)(i + COL_LANES) * ldn + c];
+            const double v2 = Vz[(long)(i + 2 * COL_LANES) * ldn + c], v3 = Vz[(long)(i + 3 * COL_LANES) * ldn + c];
+            s0 += v0 * v0; s1 += v1 * v1; s2 += v2 * v2; s3 += v3 * v3;
+        }
+        for (; i < n; i += COL_LANES) { const double v = Vz[(long)i * ldn + c]; s0 += v * v; }
     }
-    for (; i < n; i++) { const double v = Vz[(long)i * ldn + c]; s0 += v * v; }
+    part[ty][tx] = (s0 + s1) + (s2 + s3);
+    __syncthreads();
+    if (ty != 0 || c >= Nc) return;
+    double ss = 0.0;
+    #pragma unroll
+    for (int l = 0; l < COL_LANES; l++) ss += part[l][tx];
     const double os = outputscale ? outputscale[z] : 1.0;
     mean[(long)z * Nc + c] = y_mean + y_std * (mean_const[z] + Vz[(long)n * ldn + c]);
-    var[(long)z * Nc + c] = y_std * y_std * (os - ((s0 + s1) + (s2 + s3)));
+    var[(long)z * Nc + c] = y_std * y_std * (os - ss);
 }
 
-__global__ void col_max_kernel(const double* Fb, long strideF, long ldf, const double* mean_b, long strideMb,
-                               int rows, int cols, double* out, long strideOut, double w) {
-    const int z = blockIdx.y;
-    const int s = blockIdx.x * blockDim.x + threadIdx.x;
-    if (s >= cols) return;
+constexpr int MAX_LANES = 32;
+__global__ void __launch_bounds__(32 * MAX_LANES) col_max_kernel(const double* Fb, long strideF, long ldf,
+                                                                 const double* mean_b, long strideMb, int rows, int cols,
+                                                                 double* out, long strideOut, double w) {
+    __shared__ double part[MAX_LANES][33];
+    const int z = blockIdx.y, tx = threadIdx.x, ty = threadIdx.y;
+    const int s = blockIdx.x * 32 + tx;
     const double* Fz = Fb + (long)z * strideF;
     const double* mb = mean_b + (long)z * strideMb;
     double m = -INFINITY;
-    for (int i = 0; i < rows; i++) m = fmax(m, w * (mb[i] + Fz[(long)i * ldf + s]));  // objective value w * f
+    if (s < cols)
+        for (int i = ty; i < rows; i += MAX_LANES) m = fmax(m, w * (mb[i] + Fz[(long)i * ldf + s]));  // objective value w * f
+    part[ty][tx] = m;
+    __syncthreads();
+    if (ty != 0 || s >= cols) return;
+    #pragma unroll
+    for (int l = 1; l < MAX_LANES; l++) m = fmax(m, part[l][tx]);  // max is exact in any order
     out[(long)z * strideOut + s] = m;
 }
 
@@ -1436,16 +1459,16 @@ int bo_col_mean_var(const double* V, long strideV, long ldn, int n, long Nc, int
                     const double* mean_const, const double* outputscale, double* mean, double* var,
                     cudaStream_t stream) {
     if (Nc <= 0) return BO_OK;
-    dim3 grid((unsigned)((Nc + 127) / 128), M);
-    col_mean_var_kernel<<<grid, 128, 0, stream>>>(V, strideV, ldn, n, Nc, y_mean, y_std, mean_const, outputscale, mean,
+    dim3 grid((unsigned)((Nc + 31) / 32), M);
+    col_mean_var_kernel<<<grid, dim3(32, COL_LANES), 0, stream>>>(V, strideV, ldn, n, Nc, y_mean, y_std, mean_const, outputscale, mean,
                                                   var);
     BO_LAUNCH_CHECK();
     return BO_OK;
 }
 int bo_col_max(const double* Fb, long strideF, long ldf, const double* mean_b, long strideMb, int rows, int cols,
                int M, double* out, long strideOut, double obj_w, cudaStream_t stream) {
-    dim3 grid((cols + 127) / 128, M);
-    col_max_kernel<<<grid, 128, 0, stream>>>(Fb, strideF, ldf, mean_b, strideMb, rows, cols, out, strideOut, obj_w);
+    dim3 grid((cols + 31) / 32, M);
+    col_max_kernel<<<grid, dim3(32, MAX_LANES), 0, stream>>>(Fb, strideF, ldf, mean_b, strideMb, rows, cols, out, strideOut, obj_w);
     BO_LAUNCH_CHECK();
     return BO_OK;
 }
