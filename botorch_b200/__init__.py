@@ -7,6 +7,7 @@ There is no CPU fallback: importing is cheap, the first compute call raises if t
 """
 from .acquisition import (  # noqa: F401
     AcquisitionFunction,
+    GenericMCObjective,
     IdentityMCObjective,
     LinearMCObjective,
     prune_inferior_points,

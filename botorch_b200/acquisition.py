@@ -19,7 +19,7 @@ from __future__ import annotations
 import math
 import warnings
 from copy import deepcopy
-from typing import Optional
+from typing import Callable, Optional
 
 import torch
 from torch import Tensor
@@ -84,6 +84,39 @@ class LinearMCObjective(Module):
         if samples.shape[-1] != self.weights.shape[-1]:
             raise RuntimeError("Output shape of samples not equal to that of weights")
         return torch.einsum("...m, m", [samples, self.weights])
+
+
+class GenericMCObjective(Module):
+    """Objective from a callable ``f(samples, X)`` mapping ``sample_shape x batch_shape x q x m`` samples (and the
+    ``batch_shape x q x d`` inputs) to ``sample_shape x batch_shape x q`` objective values (acquisition/objective.py:344-384).
+    Arbitrary Python cannot run inside the fused kernels: acquisition functions given one evaluate it with torch on the
+    materialised samples, between the sample kernels and the reduction kernels (``botorch_b200/constrained.py``)."""
+
+    def __init__(self, objective: Callable[[Tensor, Optional[Tensor]], Tensor]) -> None:
+        super().__init__()
+        self.objective = objective
+
+    def forward(self, samples: Tensor, X: Optional[Tensor] = None) -> Tensor:
+        return self.objective(samples, X=X)
+
+
+def _needs_sample_path(model, objective, constraints) -> bool:
+    """True when the call cannot use the all-in-kernel path of a single model: outcome constraints or a generic objective
+    need the samples in HBM and torch between the kernels (the model-list classes of ``constrained.py``)."""
+    from .constrained import ModelListGP
+
+    return isinstance(model, ModelListGP) or constraints is not None or isinstance(objective, GenericMCObjective)
+
+
+def _as_model_list(model):
+    from .constrained import ModelListGP
+
+    if isinstance(model, ModelListGP):
+        return model
+    if not isinstance(model, _FusedExactGP) or model._is_fully_bayesian:
+        raise UnsupportedError("outcome constraints / generic objectives on the fused path need exact (non-ensemble) "
+                               "botorch_b200 GP models")  # fmt: skip
+    return ModelListGP(model)
 
 
 def _objective_weight(objective) -> float:
@@ -404,11 +437,13 @@ class qLogNoisyExpectedImprovement(_FusedImprovementBase):
     _log = True
 
     def __new__(cls, model=None, *args, **kwargs):
-        if cls is qLogNoisyExpectedImprovement:  # several outcomes / outcome constraints: botorch_b200/constrained.py
-            from .constrained import ModelListGP, qLogNEIModelList
+        if cls is qLogNoisyExpectedImprovement:  # several outcomes / outcome constraints / generic objective: constrained.py
+            from .constrained import qLogNEIModelList
 
-            if isinstance(model, ModelListGP):
-                return qLogNEIModelList(model, *args, **kwargs)
+            objective = kwargs.get("objective", args[2] if len(args) > 2 else None)
+            constraints = kwargs.get("constraints", args[5] if len(args) > 5 else None)
+            if _needs_sample_path(model, objective, constraints):
+                return qLogNEIModelList(_as_model_list(model), *args, **kwargs)
         return super().__new__(cls)
 
     def __init__(
@@ -551,10 +586,12 @@ class qNoisyExpectedImprovement(qLogNoisyExpectedImprovement):
 
     def __new__(cls, model=None, *args, **kwargs):
         if cls is qNoisyExpectedImprovement:
-            from .constrained import ModelListGP, qNEIModelList
+            from .constrained import qNEIModelList
 
-            if isinstance(model, ModelListGP):
-                return qNEIModelList(model, *args, **kwargs)
+            objective = kwargs.get("objective", args[2] if len(args) > 2 else None)
+            constraints = kwargs.get("constraints", args[7] if len(args) > 7 else None)
+            if _needs_sample_path(model, objective, constraints):
+                return qNEIModelList(_as_model_list(model), *args, **kwargs)
         return object.__new__(cls)
 
     def __init__(
@@ -584,6 +621,17 @@ class qLogExpectedImprovement(_FusedImprovementBase):
     joint posterior over the q points, log_fatplus(f - best_f), fatmax over q, logmeanexp over samples."""
 
     _log = True
+
+    def __new__(cls, model=None, *args, **kwargs):
+        if cls in (qLogExpectedImprovement, qExpectedImprovement):  # constraints / generic objective: constrained.py
+            from .constrained import qEIModelList, qLogEIModelList
+
+            objective = kwargs.get("objective", args[2] if len(args) > 2 else None)
+            constraints = kwargs.get("constraints", args[5] if len(args) > 5 else None)
+            if _needs_sample_path(model, objective, constraints):
+                target = qLogEIModelList if cls is qLogExpectedImprovement else qEIModelList
+                return target(_as_model_list(model), *args, **kwargs)
+        return object.__new__(cls)
 
     def __init__(
         self,

@@ -25,7 +25,8 @@ from torch.quasirandom import SobolEngine
 
 from . import _lib, engine
 from ._lib import check, pad8, ptr
-from .acquisition import DEFAULT_MC_SAMPLES, TAU_MAX, TAU_RELU, AcquisitionFunction, LinearMCObjective, _FusedImprovementBase
+from .acquisition import (DEFAULT_MC_SAMPLES, TAU_MAX, TAU_RELU, AcquisitionFunction, GenericMCObjective, IdentityMCObjective,
+                          LinearMCObjective, _FusedImprovementBase)  # fmt: skip
 from .exceptions import UnsupportedError
 from .models import Model, _FusedExactGP
 from .sampling import (IIDNormalSampler, MCSampler, SobolQMCNormalSampler, _normal_from_uniform, draw_sobol_normal_samples,
@@ -137,17 +138,29 @@ class ModelListGP(Model):
 
 
 def _one_outcome(objective, m: int) -> Tuple[int, float]:
-    """(index, weight) of a LinearMCObjective that reads exactly one outcome."""
+    """(index, weight) of an objective that reads exactly one outcome linearly -- the form the reduction kernels apply
+    themselves.  A ``GenericMCObjective`` returns (-1, 1.0): its values are computed by torch on the sample tensor."""
+    if isinstance(objective, GenericMCObjective):
+        return -1, 1.0
+    if m == 1 and (objective is None or isinstance(objective, IdentityMCObjective)):
+        return 0, 1.0
     if not isinstance(objective, LinearMCObjective):
         raise UnsupportedError(
             "with several outcomes the fused path needs `objective=LinearMCObjective(weights)` selecting ONE outcome "
-            "(one nonzero weight); constraints may read every outcome"
+            "(one nonzero weight) or a `GenericMCObjective`; constraints may read every outcome"
         )
     w = objective.weights.detach().reshape(-1).cpu().double()
     nz = torch.nonzero(w).reshape(-1)
     if w.numel() != m or nz.numel() != 1:
         raise UnsupportedError(f"objective weights must have length {m} with exactly one nonzero entry, got {w.tolist()}")
     return int(nz[0]), float(w[nz[0]])
+
+
+def _objective_values(objective, obj_idx: int, obj_w: float, samples: Tensor, X: Optional[Tensor]) -> Tensor:
+    """objective(samples, X) for ``... x m`` samples: the linear one-outcome form, or the generic callable."""
+    if obj_idx >= 0:
+        return obj_w * samples[..., obj_idx]
+    return objective(samples, X=X)
 
 
 def prune_inferior_points_list(model: ModelListGP, X: Tensor, objective, constraints=None, num_samples: int = 2048,
@@ -182,7 +195,7 @@ def prune_inferior_points_list(model: ModelListGP, X: Tensor, objective, constra
             base = z[..., k].reshape(torch.Size([S]) + post.base_sample_shape)
             cols.append(post.rsample_from_base_samples(torch.Size([S]), base).reshape(S, n))
         samples = torch.stack(cols, dim=-1)  # S x n x m
-        obj_vals = obj_w * samples[..., obj_idx]
+        obj_vals = _objective_values(objective, obj_idx, obj_w, samples, X).clone()
         infeas = ~compute_feasibility_indicator(constraints, samples)
         if bool(infeas.any()):
             obj_vals[infeas] = obj_vals.min() - 1
@@ -220,12 +233,18 @@ class _ConstrainedFn(torch.autograd.Function):
                                                                    fat=acqf._fat).reshape(S, N)  # fmt: skip
         acq = torch.empty(B, dtype=torch.float64, device=Xd.device)
         lse = torch.empty(B, dtype=torch.float64, device=Xd.device)
-        Fobj = views[acqf._obj_idx]
+        if acqf._obj_idx >= 0:  # linear one-outcome objective: the kernel reads that outcome's samples in place
+            Fobj = views[acqf._obj_idx]
+        else:  # generic objective (acquisition/objective.py:344-384): arbitrary callable, torch on the device
+            Fobj = torch.zeros(S, ldn, dtype=torch.float64, device=Xd.device)
+            with torch.no_grad():
+                Fobj[:, :N] = acqf.objective(samples, X=Xd).reshape(S, N)
         lib = _lib.lib()
         check(lib.bo_mc_reduce_fwd(acqf._ctx, S, B, q, Fobj.stride(0), ptr_view(Fobj), ptr(lw), ptr(acqf._best_f),
                                    acqf._obj_w, acqf.tau_relu, acqf.tau_max, acqf._reduction, ptr(acq), ptr(lse),
                                    _lib.stream_ptr(Xd.device)))  # fmt: skip
         ctx.acqf, ctx.works, ctx.views, ctx.Zq = acqf, works, views, Zq
+        ctx.Fobj = Fobj
         ctx.lw, ctx.lse, ctx.in_dtype = lw, lse, X.dtype
         ctx.save_for_backward(Xd, samples)
         return acq.to(X.dtype)
@@ -238,7 +257,7 @@ class _ConstrainedFn(torch.autograd.Function):
         N, S, m = B * q, acqf.S, len(ctx.views)
         ldn = pad8(N)
         dev = Xd.device
-        Fobj = ctx.views[acqf._obj_idx]
+        Fobj = ctx.Fobj
         dF = torch.zeros(S, Fobj.stride(0), dtype=torch.float64, device=dev)
         lw_bar = None if ctx.lw is None else torch.zeros(S, Fobj.stride(0), dtype=torch.float64, device=dev)
         lw_arg = None
@@ -259,6 +278,16 @@ class _ConstrainedFn(torch.autograd.Function):
                 else:  # constraints that do not read the samples differentiably (constants, hard thresholds)
                     gs = None
         grad = None
+        if acqf._obj_idx < 0:  # chain d loss / d objective through the generic callable into the samples and into X
+            with torch.enable_grad():
+                s = samples.detach().requires_grad_(True)
+                Xg = Xd.detach().requires_grad_(True)
+                obj = acqf.objective(s, X=Xg)
+                if obj.requires_grad:
+                    go, gx = torch.autograd.grad(obj, [s, Xg], grad_outputs=dF[:, :N].reshape(S, B, q), allow_unused=True)
+                    if go is not None:
+                        gs = go if gs is None else gs + go
+                    grad = gx
         for k, nei in enumerate(acqf._neis):
             dFk = torch.zeros(S, N, dtype=torch.float64, device=dev) if gs is None else gs[..., k].reshape(S, N).clone()
             if k == acqf._obj_idx:
@@ -268,7 +297,9 @@ class _ConstrainedFn(torch.autograd.Function):
             ctx.views[k][:, :N] = dFk
             gk = nei.backward_external(Xd, ctx.Zq[k], acqf.tau_relu, acqf.tau_max, ctx.works[k])[0]
             grad = gk if grad is None else grad + gk
-        ctx.works = ctx.views = None
+        ctx.works = ctx.views = ctx.Fobj = None
+        if grad is None:
+            grad = torch.zeros_like(Xd)
         return grad.to(ctx.in_dtype), None
 
 
@@ -327,7 +358,7 @@ class qLogNEIModelList(AcquisitionFunction):
         base = torch.stack([engine.root_apply(nei.baseline_L.contiguous(), nei.mean_b[:, : nei.n_b],
                                               nei.Z_b.unsqueeze(1).expand(nei.S, 1, nei.n_b))[:, 0] for nei in self._neis], dim=-1)  # fmt: skip
         self.baseline_samples = base  # S x n_b x m
-        self.baseline_obj = self._obj_w * base[..., self._obj_idx]
+        self.baseline_obj = _objective_values(self.objective, self._obj_idx, self._obj_w, base, Xb)
         self._best_f = self._compute_best_feasible_objective(base, self.baseline_obj).to(torch.float64).contiguous()
         self._baseline_best_f = self._best_f
 
@@ -368,7 +399,8 @@ class qLogNEIModelList(AcquisitionFunction):
             wts = torch.rand(32, Xb.shape[-2], dtype=Xb.dtype, device=Xb.device)
             wts = wts / wts.sum(dim=0, keepdim=True)
             post = self.model.posterior(wts @ Xb)
-            lb = self._obj_w * (post.mean - 6 * post.variance.clamp_min(0).sqrt())[..., self._obj_idx]
+            lb = _objective_values(self.objective, self._obj_idx, self._obj_w,
+                                   post.mean - 6 * post.variance.clamp_min(0).sqrt(), wts @ Xb)
             infeasible_value = float(-(-(lb.min().clamp_max(0.0))))
         return torch.where(is_feasible, obj, torch.full_like(obj, infeasible_value)).amax(dim=-1)
 
@@ -405,3 +437,74 @@ class qNEIModelList(qLogNEIModelList):
         super().__init__(model, X_baseline, sampler=sampler, objective=objective, posterior_transform=posterior_transform,
                          X_pending=X_pending, constraints=constraints, eta=eta, fat=False, prune_baseline=prune_baseline,
                          cache_root=cache_root, marginalize_dim=marginalize_dim)  # fmt: skip
+
+
+class qLogEIModelList(qLogNEIModelList):
+    """``qLogExpectedImprovement(model, best_f, objective=..., constraints=[...])`` (acquisition/logei.py:138-234 with
+    ``_apply_constraints``, monte_carlo.py:305-330) when outcome constraints or a generic objective are present: the joint
+    posterior over the q candidate points of every outcome (``engine.EIState``: no baseline block), the fixed incumbent
+    ``best_f``, log improvement + log feasibility, the q-reduction and logmeanexp in the same reduction kernels."""
+
+    def __init__(self, model: ModelListGP, best_f, sampler: Optional[MCSampler] = None, objective=None,
+                 posterior_transform=None, X_pending: Optional[Tensor] = None,
+                 constraints: Optional[Sequence[Callable[[Tensor], Tensor]]] = None, eta: Union[Tensor, float] = 1e-3,
+                 fat: bool = True, tau_max: float = TAU_MAX, tau_relu: float = TAU_RELU) -> None:  # fmt: skip
+        AcquisitionFunction.__init__(self, model=model)
+        if posterior_transform is not None:
+            raise UnsupportedError("posterior_transform is not on the constrained fused path")
+        m = model.num_outputs
+        self._obj_idx, self._obj_w = _one_outcome(objective, m)
+        self.objective = objective
+        self._constraints = list(constraints) if constraints else None
+        self._eta, self._fat = eta, bool(fat)
+        if not self._fat and self._reduction == engine.REDUCE_LOG:
+            self._reduction = engine.REDUCE_LOG_SOFT
+        self.tau_relu, self.tau_max = float(tau_relu), float(tau_max)
+        self.set_X_pending(X_pending)
+        gps = [mod.gp_state for mod in model.models]
+        dev = gps[0].device
+        self._ctx = gps[0].ctx
+        self.register_buffer("best_f", torch.as_tensor(best_f, dtype=torch.float64))
+        if self.best_f.numel() != 1:
+            raise UnsupportedError("the fused path takes a scalar best_f for non-batched models")
+        self.sampler = sampler
+        self.sample_shape = torch.Size([DEFAULT_MC_SAMPLES]) if sampler is None else sampler.sample_shape
+        if len(self.sample_shape) != 1:
+            raise UnsupportedError("the fused path takes a one-dimensional sample_shape")
+        if sampler is not None and not isinstance(sampler, (SobolQMCNormalSampler, IIDNormalSampler)):
+            raise UnsupportedError("the fused path takes a Sobol or iid normal sampler")
+        self.S = int(self.sample_shape[0])
+        self._best_f = self.best_f.reshape(1).expand(self.S).to(dev).contiguous()  # per-sample incumbent, all equal
+        self._neis = [engine.EIState(gp, self.best_f.to(dev), self.S, reduction=self._reduction,
+                                     obj_weight=(self._obj_w if k == self._obj_idx else 1.0)) for k, gp in enumerate(gps)]  # fmt: skip
+        self._Zq_cache = {}
+
+    def _base_samples_q(self, q: int) -> List[Tensor]:
+        """Per outcome S x q base samples: ONE draw over the (q points x m outcomes) block of the joint posterior
+        (sampling/normal.py:34-86; get_sampler: Sobol when q * m fits the engine, iid otherwise)."""
+        if q not in self._Zq_cache:
+            m = len(self._neis)
+            if self.sampler is None:
+                cls = SobolQMCNormalSampler if q * m <= SobolEngine.MAXDIM else IIDNormalSampler
+                self.sampler = cls(sample_shape=self.sample_shape)
+            dev = self._neis[0].device
+            full = self._draw(q, m)
+            self._Zq_cache[q] = [full[:, :, k].to(dev).contiguous() for k in range(m)]
+        return self._Zq_cache[q]
+
+
+class qEIModelList(qLogEIModelList):
+    """``qExpectedImprovement(model, best_f, objective=..., constraints=[...])`` (acquisition/monte_carlo.py:333-414): relu
+    improvement times the plain sigmoid feasibility weights, ``amax`` over q, mean over the samples."""
+
+    _log = False
+    _reduction = engine.REDUCE_PLAIN
+
+    def __init__(self, model: ModelListGP, best_f, sampler: Optional[MCSampler] = None, objective=None,
+                 posterior_transform=None, X_pending: Optional[Tensor] = None, constraints=None,
+                 eta: Union[Tensor, float] = 1e-3) -> None:  # fmt: skip
+        from .acquisition import legacy_ei_numerics_warning
+
+        legacy_ei_numerics_warning("qExpectedImprovement")
+        super().__init__(model, best_f, sampler=sampler, objective=objective, posterior_transform=posterior_transform,
+                         X_pending=X_pending, constraints=constraints, eta=eta, fat=False)

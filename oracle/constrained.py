@@ -97,8 +97,10 @@ class OracleConstrainedQLogNEI:
 
     def __init__(self, models: List[OracleGP], X_baseline: Tensor, constraints: List[Callable[[Tensor], Tensor]], eta,
                  obj_idx: int = 0, obj_weight: float = 1.0, num_samples: int = 64, seed: int = 1234, fat: bool = True,
-                 tau_relu: float = TAU_RELU, tau_max: float = TAU_MAX, convex_weights: Optional[Tensor] = None, plain: bool = False):  # fmt: skip
-        self.plain = plain
+                 tau_relu: float = TAU_RELU, tau_max: float = TAU_MAX, convex_weights: Optional[Tensor] = None, plain: bool = False,
+                 objective: Optional[Callable[[Tensor, Tensor], Tensor]] = None):  # fmt: skip
+        # objective: a GenericMCObjective callable f(samples, X) (acquisition/objective.py:344-384); None = obj_weight * outcome obj_idx
+        self.plain, self.objective = plain, objective
         self.m, self.S, self.seed = len(models), num_samples, seed
         self.constraints = constraints
         # utils/objective.py:167-168: a float eta becomes torch.full((n,), eta) in the DEFAULT dtype (float32 unless the caller
@@ -118,7 +120,7 @@ class OracleConstrainedQLogNEI:
                 o.baseline_samples = torch.einsum("ij,sj->si", o.baseline_L, o.Z_b) + mean_b
             self.parts.append(o)
         base = torch.stack([o.baseline_samples for o in self.parts], dim=-1)  # S x n_b x m
-        obj_b = self.obj_w * base[..., obj_idx]
+        obj_b = self._obj(base, X_baseline)
         feas = feasibility(constraints, base)
         if bool(feas.any(dim=-1).all()):
             infeasible_value = -float("inf")
@@ -126,6 +128,11 @@ class OracleConstrainedQLogNEI:
             assert convex_weights is not None, "pass the 32 x n_b uniform draws of _estimate_objective_lower_bound"
             infeasible_value = objective_lower_bound(models, X_baseline, convex_weights, obj_idx, self.obj_w)
         self.best_f = torch.where(feas, obj_b, torch.full_like(obj_b, infeasible_value)).amax(dim=-1)  # S
+
+    def _obj(self, samples: Tensor, X: Tensor) -> Tensor:
+        if self.objective is not None:
+            return self.objective(samples, X)
+        return self.obj_w * samples[..., self.obj_idx]
 
     def _set_q(self, q: int) -> None:
         full = qmc.sobol_normal(d=(self.n_b + q) * self.m, n=self.S, seed=self.seed).view(self.S, self.n_b + q, self.m)
@@ -141,16 +148,18 @@ class OracleConstrainedQLogNEI:
         if X.dim() == 2:
             X = X.unsqueeze(0)
         smp = self.samples(X)
-        obj = self.obj_w * smp[..., self.obj_idx]
+        obj = self._obj(smp, X)
         if self.plain:  # qNEI (monte_carlo.py:305-330, 417-620): relu improvement times the feasibility weights, amax, mean
             imp = (obj - self.best_f.view(self.S, 1, 1)).clamp_min(0)
-            imp = imp * smoothed_log_feasibility(self.constraints, smp, self.eta, self.fat).exp()
+            if self.constraints:
+                imp = imp * smoothed_log_feasibility(self.constraints, smp, self.eta, self.fat).exp()
             return imp.amax(dim=-1).mean(dim=0)
         if self.fat:
             li = safe_math.log_improvement(obj, self.best_f.view(self.S, 1), tau=self.tau_relu)
         else:  # the reference's `fat` flag switches the ReLU smoothing, the q-reduction AND the sigmoid (logei.py:122,532)
             li = safe_math.log_softplus(obj - self.best_f.view(self.S, 1, 1), tau=self.tau_relu)
-        li = li + smoothed_log_feasibility(self.constraints, smp, self.eta, self.fat)
+        if self.constraints:
+            li = li + smoothed_log_feasibility(self.constraints, smp, self.eta, self.fat)
         qmax = safe_math.fatmax if self.fat else safe_math.smooth_amax
         return safe_math.logmeanexp(qmax(li, dim=-1, tau=self.tau_max), dim=0)
 
@@ -159,3 +168,30 @@ class OracleConstrainedQLogNEI:
         acq = self.forward(Xg)
         (g,) = torch.autograd.grad(acq.sum(), Xg)
         return acq.detach(), g
+
+
+class OracleConstrainedQLogEI(OracleConstrainedQLogNEI):
+    """acquisition/logei.py:138-234 (qLogExpectedImprovement) / monte_carlo.py:333-414 (qExpectedImprovement, ``plain``) with
+    outcome constraints and/or a generic objective: joint posterior over the q candidate points of every outcome
+    (posteriors/gpytorch.py:121-165: mean + chol(Sigma) z), base samples S x 1 x q x m from ONE draw over the q * m block
+    (sampling/normal.py:34-86), the FIXED incumbent ``best_f``; ``forward`` is the parent's."""
+
+    def __init__(self, models: List[OracleGP], best_f: float, constraints, eta, obj_idx: int = 0, obj_weight: float = 1.0,
+                 num_samples: int = 64, seed: int = 1234, fat: bool = True, tau_relu: float = TAU_RELU,
+                 tau_max: float = TAU_MAX, plain: bool = False, objective=None):  # fmt: skip
+        self.plain, self.objective = plain, objective
+        self.models, self.m, self.S, self.seed = models, len(models), num_samples, seed
+        self.constraints = constraints or []
+        self.eta = list(torch.full((len(self.constraints),), eta)) if not isinstance(eta, Tensor) else list(eta)
+        self.fat, self.obj_idx, self.obj_w = fat, obj_idx, float(obj_weight)
+        self.tau_relu, self.tau_max = tau_relu, tau_max
+        self.best_f = torch.full((self.S,), float(best_f), dtype=torch.float64)
+
+    def samples(self, X: Tensor) -> Tensor:
+        q = X.shape[-2]
+        Z = qmc.sobol_normal(d=q * self.m, n=self.S, seed=self.seed).view(self.S, q, self.m)
+        cols = []
+        for k, gp in enumerate(self.models):
+            mean, cov = gp.posterior(X)  # B x q, B x q x q
+            cols.append(torch.einsum("...ij,sj->s...i", psd_safe_cholesky(cov), Z[:, :, k]) + mean)
+        return torch.stack(cols, dim=-1)  # S x B x q x m

@@ -497,3 +497,32 @@ def test_saas_prior_terms_and_adaptation_schedule():
     assert fb._adaptation_windows(20) == (20, [])
     with pytest.raises(RuntimeError):
         fb.SaasPotential(torch.rand(5, 2, dtype=torch.float64), torch.rand(5, dtype=torch.float64))
+
+
+def test_generic_objective_and_sample_path_dispatch_rules():
+    """acquisition/objective.py:344-384: the callable receives (samples, X=X); which constructor arguments send an
+    acquisition function to the sample-path classes of constrained.py (no device needed for the rule itself)."""
+    from botorch_b200.acquisition import _needs_sample_path
+    from botorch_b200.constrained import _objective_values, _one_outcome
+
+    seen = {}
+
+    def f(Y, X=None):
+        seen["X"] = X
+        return Y[..., 0] * Y[..., 1]
+
+    obj = bb.GenericMCObjective(f)
+    Y, X = torch.rand(5, 3, 2, 2, dtype=torch.float64), torch.rand(3, 2, 4, dtype=torch.float64)
+    assert torch.equal(obj(Y, X=X), Y[..., 0] * Y[..., 1]) and seen["X"] is X
+    assert _one_outcome(obj, 2) == (-1, 1.0)
+    assert _one_outcome(None, 1) == (0, 1.0) and _one_outcome(bb.IdentityMCObjective(), 1) == (0, 1.0)
+    assert _one_outcome(bb.LinearMCObjective(torch.tensor([0.0, -2.0])), 2) == (1, -2.0)
+    with pytest.raises(bex.UnsupportedError):
+        _one_outcome(None, 2)
+    with pytest.raises(bex.UnsupportedError):
+        _one_outcome(bb.LinearMCObjective(torch.tensor([1.0, 1.0])), 2)
+    assert torch.equal(_objective_values(obj, -1, 1.0, Y, X), Y[..., 0] * Y[..., 1])
+    assert torch.equal(_objective_values(None, 1, -2.0, Y, X), -2.0 * Y[..., 1])
+    assert not _needs_sample_path(object(), None, None)
+    assert not _needs_sample_path(object(), bb.LinearMCObjective(torch.tensor([1.0])), None)
+    assert _needs_sample_path(object(), obj, None) and _needs_sample_path(object(), None, [lambda Z: Z[..., 0]])
