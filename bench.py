@@ -489,6 +489,7 @@ def _run_ours(args):
     if ws > 1:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
     e2e_s = float(t)
+    direct_route = evaluate.direct_calls > 0
     clk = clocks.stop() if clocks else None
 
     # ---- the whole candidate-generation loop (A4): SciPy L-BFGS-B on the host vs the device-resident optimiser -------------
@@ -598,9 +599,12 @@ def _run_ours(args):
         },
         "e2e": {
             "value": ws * B * args.steps / e2e_s, "unit": UNIT, "h2d_bytes_per_step": X_host.numel() * 8,
-            "d2h_bytes_per_step": X_host.numel() * 8 + 8,
+            "d2h_bytes_per_step": (X_host.numel() * 8 + B * 12) if direct_route else (X_host.numel() * 8 + 8),
             "api": "botorch_b200.optim.HostEvaluator (the objective gen_candidates_scipy hands to L-BFGS-B): host x in, "
-                   "qLogNoisyExpectedImprovement.forward + torch.autograd.grad, gradient + loss out",
+                   + ("forward + reverse kernels with d loss / d acq = -1 into preallocated buffers (direct route), gradient + "
+                      "per-restart values + failure flags out" if direct_route else
+                      "qLogNoisyExpectedImprovement.forward + torch.autograd.grad, gradient + loss out"),
+            "route": "direct" if direct_route else "autograd",
         },
         "gpu_launches": launches,
         "optimizer_loop": {"maxiter": opt_iters, "restarts": B, **opt,

@@ -430,12 +430,15 @@ class NEIState:
         return _lib.lib().bo_qlognei_workspace_bytes(C.byref(self.gp.c), C.byref(self.c), B, q, int(with_grad))
 
     def forward(self, X: Tensor, Z_q: Tensor, tau_relu: float, tau_max: float, with_grad: bool,
-                work: Optional[Tensor] = None):  # fmt: skip
-        """X: B x q x d, Z_q: S x q -> (acq [M x B], info [M x B] int32, workspace)."""
+                work: Optional[Tensor] = None, out: Optional[Tuple[Tensor, Tensor]] = None):  # fmt: skip
+        """X: B x q x d, Z_q: S x q -> (acq [M x B], info [M x B] int32, workspace).  ``out``: caller-owned (acq, info)."""
         B, q, _ = X.shape
         dev = self.device
-        acq = torch.empty(self.gp.M, B, dtype=torch.float64, device=dev)
-        info = torch.empty(self.gp.M, B, dtype=torch.int32, device=dev)
+        if out is None:
+            acq = torch.empty(self.gp.M, B, dtype=torch.float64, device=dev)
+            info = torch.empty(self.gp.M, B, dtype=torch.int32, device=dev)
+        else:
+            acq, info = out
         if work is None:
             work = _lib.workspace(self.workspace_bytes(B, q, with_grad), dev)
         check(_lib.lib().bo_qlognei_fwd(self.gp.ctx, C.byref(self.gp.c), C.byref(self.c), B, q, ptr(X), ptr(Z_q),
@@ -443,10 +446,11 @@ class NEIState:
                                         int(with_grad), _lib.stream_ptr(dev)))  # fmt: skip
         return acq, info, work
 
-    def backward(self, X: Tensor, Z_q: Tensor, tau_relu: float, tau_max: float, grad_acq: Tensor, work: Tensor) -> Tensor:
-        """grad_acq: [M x B] -> grad_X [M x B x q x d] (per model)."""
+    def backward(self, X: Tensor, Z_q: Tensor, tau_relu: float, tau_max: float, grad_acq: Tensor, work: Tensor,
+                 out: Optional[Tensor] = None) -> Tensor:  # fmt: skip
+        """grad_acq: [M x B] -> grad_X [M x B x q x d] (per model), written into ``out`` when given."""
         B, q, d = X.shape
-        grad_X = torch.empty(self.gp.M, B, q, d, dtype=torch.float64, device=self.device)
+        grad_X = torch.empty(self.gp.M, B, q, d, dtype=torch.float64, device=self.device) if out is None else out
         check(_lib.lib().bo_qlognei_bwd(self.gp.ctx, C.byref(self.gp.c), C.byref(self.c), B, q, ptr(X), ptr(Z_q),
                                         tau_relu, tau_max, ptr(grad_acq.contiguous()), ptr(grad_X), work.data_ptr(),
                                         work.numel(), _lib.stream_ptr(self.device)))  # fmt: skip

@@ -202,7 +202,16 @@ class _Timeout(Exception):
 class HostEvaluator:
     """``f_np_wrapper`` of gen_candidates_scipy (gen.py:194-222) with the host round trip trimmed to the minimum:
     x goes through a pinned staging buffer (asynchronous H2D), the gradient and the loss come back in ONE asynchronous
-    D2H into pinned memory, and the host waits once per evaluation."""
+    D2H into pinned memory, and the host waits once per evaluation.
+
+    Two routes.  The general one is the reference's: ``loss = -acqf(X).sum()`` and ``torch.autograd.grad``.  For a plain
+    fused acquisition function (one exact model, no pending points, float64) the objective is known in closed form, so the
+    DIRECT route calls the forward and the reverse kernels itself with ``d loss / d acq = -1``, into buffers allocated once:
+    no autograd graph, no per-call allocations, no reduction or concatenation launches -- the values come back next to
+    the gradient and are summed on the host.  Measured at C3 (tools/e2e_profile.py): the host needs 0.29 ms to reach the
+    first kernel launch on the general route and the GPU idles for it; the direct route cuts that to ~0.05 ms.  Failure
+    flags come back with the same copy; an evaluation that raised any is redone on the general route, which owns the
+    warnings and the reference's fallback.  ``BOTORCH_B200_DIRECT_EVAL=0`` disables the direct route."""
 
     def __init__(self, acquisition_function, shapeX: torch.Size, like: Tensor) -> None:
         self.acqf, self.shapeX, self.like = acquisition_function, torch.Size(shapeX), like
@@ -211,9 +220,66 @@ class HostEvaluator:
         self.x_host = torch.empty(numel, dtype=like.dtype, pin_memory=pin)
         self.out_host = torch.empty(numel + 1, dtype=like.dtype, pin_memory=pin)
         self.calls = 0
+        self.direct_calls = 0
+        self._direct = None  # None: not decided yet; False: general route only; else the preallocated state
+
+    # -- direct route ----------------------------------------------------------------------------------
+    def _direct_state(self):
+        if self._direct is not None:
+            return self._direct
+        import os
+        from types import SimpleNamespace
+
+        from . import _lib
+        from .acquisition import _FusedImprovementBase
+
+        a = self.acqf
+        nei = getattr(a, "_nei", None)
+        ok = (isinstance(a, _FusedImprovementBase) and nei is not None and self.like.is_cuda
+              and self.like.dtype == torch.float64 and len(self.shapeX) == 3 and getattr(a, "X_pending", None) is None
+              and nei.gp.M == 1 and not a.model._is_ensemble and self.like.device == nei.device
+              and os.environ.get("BOTORCH_B200_DIRECT_EVAL", "1") != "0")  # fmt: skip
+        if not ok:
+            self._direct = False
+            return False
+        B, q, d = self.shapeX
+        dev, numel = nei.device, self.shapeX.numel()
+        out = torch.empty(numel + B, dtype=torch.float64, device=dev)  # [gradient | acquisition values]: one D2H
+        st = SimpleNamespace(
+            X=torch.empty(B, q, d, dtype=torch.float64, device=dev), out=out, grad=out[:numel].view(1, B, q, d),
+            acq=out[numel:].view(1, B), info=torch.empty(1, B, dtype=torch.int32, device=dev),
+            gin=torch.full((1, B), -1.0, dtype=torch.float64, device=dev),  # d(-sum acq) / d acq
+            work=_lib.workspace(nei.workspace_bytes(B, q, True), dev),
+            out_host=torch.empty(numel + B, dtype=torch.float64, pin_memory=True),
+            info_host=torch.empty(B, dtype=torch.int32, pin_memory=True), numel=numel)  # fmt: skip
+        st.out_np, st.info_np, st.x_np = st.out_host.numpy(), st.info_host.numpy(), self.x_host.numpy()
+        self._direct = st
+        return st
+
+    def _call_direct(self, st, x: np.ndarray):
+        a = self.acqf
+        nei = a._nei
+        np.copyto(st.x_np, x)
+        st.X.copy_(self.x_host.view(self.shapeX), non_blocking=True)
+        a._set_sampler(q_in=self.shapeX[1])
+        nei.forward(st.X, a._Zq, a.tau_relu, a.tau_max, True, work=st.work, out=(st.acq, st.info))
+        nei.backward(st.X, a._Zq, a.tau_relu, a.tau_max, st.gin, st.work, out=st.grad)
+        st.out_host.copy_(st.out, non_blocking=True)
+        st.info_host.copy_(st.info.view(-1), non_blocking=True)
+        torch.cuda.current_stream(nei.device).synchronize()
+        if st.info_np.any():  # jitter was added or a cached update failed: the general route warns / falls back
+            return None
+        self.direct_calls += 1
+        return -float(st.out_np[st.numel :].sum()), st.out_np[: st.numel].astype(np.float64, copy=True)
 
     def __call__(self, x: np.ndarray, with_grad: bool = True):
         self.calls += 1
+        if with_grad and not getattr(self.acqf, "_strict_numerics", False):
+            st = self._direct_state()
+            if st:
+                res = self._call_direct(st, x)
+                if res is not None:
+                    return res
         self.x_host.copy_(torch.from_numpy(x))
         X = self.x_host.to(self.like.device, non_blocking=True).view(self.shapeX)
         if not with_grad:

@@ -442,3 +442,40 @@ def test_fixed_observation_noise_model(cuda):
     assert rel_err(grad, g_ref) < 1e-8
     with pytest.raises(ValueError):
         bb.SingleTaskGP(p.train_X.to(cuda), p.train_Y.to(cuda), Yvar.to(cuda), noise=0.1)
+
+
+def test_host_evaluator_direct_route_equals_the_autograd_route(cuda, monkeypatch):
+    """optim.HostEvaluator (f_np_wrapper, gen.py:194-222): the direct route (forward + reverse kernels with
+    d loss / d acq = -1, preallocated buffers) returns the gradient bit for bit and the loss to rounding of the sum."""
+    import numpy as np
+
+    import botorch_b200 as bb
+    from botorch_b200.optim import HostEvaluator
+    from botorch_b200.synthetic import make_problem
+    from tests.util import candidates
+
+    p = make_problem("C2")
+    h = p.hypers
+    model = bb.SingleTaskGP(p.train_X.to(cuda), p.train_Y.to(cuda), lengthscale=h["lengthscale"], noise=h["noise"],
+                            mean_constant=h["mean"])  # fmt: skip
+    like = torch.empty(0, dtype=torch.float64, device=cuda)
+    for cls, args in ((bb.qLogNoisyExpectedImprovement, (p.train_X.to(cuda),)), (bb.qLogExpectedImprovement, (float(p.train_Y.max()),))):
+        acqf = cls(model, *args, sampler=bb.SobolQMCNormalSampler(torch.Size([p.mc_samples]), seed=3))
+        X = candidates(p, 16)
+        x = X.numpy().reshape(-1).copy()
+        ev = HostEvaluator(acqf, X.shape, like)
+        loss_d, grad_d = ev(x)
+        loss_d2, grad_d2 = ev(x + 0.0)
+        assert ev.direct_calls == 2 and loss_d == loss_d2 and np.array_equal(grad_d, grad_d2)
+        monkeypatch.setenv("BOTORCH_B200_DIRECT_EVAL", "0")
+        ev_a = HostEvaluator(acqf, X.shape, like)
+        loss_a, grad_a = ev_a(x)
+        monkeypatch.delenv("BOTORCH_B200_DIRECT_EVAL")
+        assert ev_a.direct_calls == 0
+        assert np.array_equal(grad_d, grad_a)
+        assert abs(loss_d - loss_a) <= 1e-13 * abs(loss_a)
+    # pending points, ensembles and float32 callers stay on the general route
+    acqf.set_X_pending(candidates(p, 1)[0].to(cuda))
+    ev_p = HostEvaluator(acqf, X.shape, like)
+    ev_p(x)
+    assert ev_p.direct_calls == 0
