@@ -43,7 +43,14 @@ def manual_seed(seed: Optional[int] = None):
             torch.random.set_rng_state(saved)
 
 
-_SOBOL_THREADS = max(1, min(8, os.cpu_count() or 1))
+def _usable_cpus() -> int:
+    try:
+        return len(os.sched_getaffinity(0))
+    except AttributeError:  # pragma: no cover - non-Linux
+        return os.cpu_count() or 1
+
+
+_SOBOL_THREADS = max(1, min(8, _usable_cpus()))
 _sobol_pool = None
 
 

@@ -269,9 +269,10 @@ def main():
     dev = torch.device("cuda", local)
     from botorch_b200 import distributed as bd
 
-    # torchrun exports OMP_NUM_THREADS=1; the host side of the path (Sobol draws, restart selection) is the reference's own
-    # torch CPU code and gets its share of the box's cores
-    torch.set_num_threads(max(1, (os.cpu_count() or 1) // max(ws, 1)))
+    # torchrun exports OMP_NUM_THREADS=1 and it stays: os.cpu_count() reports the HOST's cores, not the container's share, and
+    # giving each rank cpu_count / world OpenMP threads oversubscribed the box (the strong-scaling phases of the first 8-GPU
+    # run of this tool were 3-5x slower on the host than the same function called from bench.py, which keeps the default).
+    # The Sobol draws use their own small thread pool (botorch_b200/sampling.py).
     if ws > 1:
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
         dist.init_process_group("nccl", device_id=dev)
