@@ -237,7 +237,7 @@ class HostEvaluator:
         nei = getattr(a, "_nei", None)
         ok = (isinstance(a, _FusedImprovementBase) and nei is not None and self.like.is_cuda
               and self.like.dtype == torch.float64 and len(self.shapeX) == 3 and getattr(a, "X_pending", None) is None
-              and nei.gp.M == 1 and not a.model._is_ensemble and self.like.device == nei.device
+              and (nei.gp.M == 1) != bool(a.model._is_ensemble) and self.like.device == nei.device
               and os.environ.get("BOTORCH_B200_DIRECT_EVAL", "1") != "0")  # fmt: skip
         if not ok:
             self._direct = False
@@ -245,13 +245,19 @@ class HostEvaluator:
         B, q, d = self.shapeX
         dev, numel = nei.device, self.shapeX.numel()
         out = torch.empty(numel + B, dtype=torch.float64, device=dev)  # [gradient | acquisition values]: one D2H
+        M = nei.gp.M
         st = SimpleNamespace(
             X=torch.empty(B, q, d, dtype=torch.float64, device=dev), out=out, grad=out[:numel].view(1, B, q, d),
-            acq=out[numel:].view(1, B), info=torch.empty(1, B, dtype=torch.int32, device=dev),
-            gin=torch.full((1, B), -1.0, dtype=torch.float64, device=dev),  # d(-sum acq) / d acq
+            acq=out[numel:].view(1, B), info=torch.empty(M, B, dtype=torch.int32, device=dev),
+            gin=torch.full((M, B), -1.0 / M, dtype=torch.float64, device=dev),  # d(-sum_b mean_m acq) / d acq
             work=_lib.workspace(nei.workspace_bytes(B, q, True), dev),
             out_host=torch.empty(numel + B, dtype=torch.float64, pin_memory=True),
-            info_host=torch.empty(B, dtype=torch.int32, pin_memory=True), numel=numel)  # fmt: skip
+            info_host=torch.empty(M * B, dtype=torch.int32, pin_memory=True), numel=numel, M=M)  # fmt: skip
+        if M > 1:  # ensemble: per-model values and gradients, mixed on the device (utils/transforms.py:289-293)
+            st.mix = st.acq.view(B)
+            st.acq = torch.empty(M, B, dtype=torch.float64, device=dev)
+            st.grad_sum = st.grad.view(B, q, d)
+            st.grad = torch.empty(M, B, q, d, dtype=torch.float64, device=dev)
         st.out_np, st.info_np, st.x_np = st.out_host.numpy(), st.info_host.numpy(), self.x_host.numpy()
         self._direct = st
         return st
@@ -263,7 +269,16 @@ class HostEvaluator:
         st.X.copy_(self.x_host.view(self.shapeX), non_blocking=True)
         a._set_sampler(q_in=self.shapeX[1])
         nei.forward(st.X, a._Zq, a.tau_relu, a.tau_max, True, work=st.work, out=(st.acq, st.info))
+        if st.M > 1 and a._log:  # loss = -sum_b logmeanexp_m acq[m, b]:  d loss / d acq = -softmax over the models
+            torch.logsumexp(st.acq, dim=0, out=st.mix)
+            st.mix.sub_(math.log(st.M))
+            torch.softmax(st.acq, dim=0, out=st.gin)
+            st.gin.neg_()
+        elif st.M > 1:
+            torch.mean(st.acq, dim=0, out=st.mix)
         nei.backward(st.X, a._Zq, a.tau_relu, a.tau_max, st.gin, st.work, out=st.grad)
+        if st.M > 1:
+            torch.sum(st.grad, dim=0, out=st.grad_sum)
         st.out_host.copy_(st.out, non_blocking=True)
         st.info_host.copy_(st.info.view(-1), non_blocking=True)
         torch.cuda.current_stream(nei.device).synchronize()

@@ -474,7 +474,28 @@ def test_host_evaluator_direct_route_equals_the_autograd_route(cuda, monkeypatch
         assert ev_a.direct_calls == 0
         assert np.array_equal(grad_d, grad_a)
         assert abs(loss_d - loss_a) <= 1e-13 * abs(loss_a)
-    # pending points, ensembles and float32 callers stay on the general route
+    # SAAS ensemble: the mixture (logmeanexp over the models, utils/transforms.py:289-293) and its softmax weights are formed
+    # on the device between the forward and the reverse kernels
+    pe = make_problem("C4", n=40, M=5)
+    me = bb.SaasFullyBayesianSingleTaskGP(pe.train_X.to(cuda), pe.train_Y.to(cuda))
+    me.load_mcmc_samples(pe.hypers)
+    for cls, args in ((bb.qLogNoisyExpectedImprovement, (pe.train_X.to(cuda),)), (bb.qNoisyExpectedImprovement, (pe.train_X.to(cuda),))):
+        import warnings
+
+        with warnings.catch_warnings():
+            warnings.simplefilter("ignore")
+            ae = cls(me, *args, sampler=bb.SobolQMCNormalSampler(torch.Size([64]), seed=3), prune_baseline=False)
+        Xe = candidates(pe, 6)
+        xe = Xe.numpy().reshape(-1).copy()
+        ev_e = HostEvaluator(ae, Xe.shape, like)
+        loss_d, grad_d = ev_e(xe)
+        assert ev_e.direct_calls == 1
+        monkeypatch.setenv("BOTORCH_B200_DIRECT_EVAL", "0")
+        loss_a, grad_a = HostEvaluator(ae, Xe.shape, like)(xe)
+        monkeypatch.delenv("BOTORCH_B200_DIRECT_EVAL")
+        assert abs(loss_d - loss_a) <= 1e-12 * abs(loss_a)
+        assert float(np.abs(grad_d - grad_a).max()) <= 1e-12 * float(np.abs(grad_a).max())
+    # pending points and float32 callers stay on the general route
     acqf.set_X_pending(candidates(p, 1)[0].to(cuda))
     ev_p = HostEvaluator(acqf, X.shape, like)
     ev_p(x)
