@@ -540,14 +540,19 @@ def _run_ours(args):
     if args.config == "C3" and not args.no_strong:
         from tools.scaling import _Solo, strong_c3
 
-        torch.set_num_threads(max(1, (os.cpu_count() or 1) // ws))  # torchrun exports OMP_NUM_THREADS=1
+        # torchrun's OMP_NUM_THREADS=1 stays (os.cpu_count() is the host's, not the container's share: DESIGN.md section 7)
         bdist.warm_up(dev)
         world_group = dist.group.WORLD if ws > 1 else None
         r_1 = None
-        if ws > 1:  # the single-GPU time of the same job first, on rank 0 alone (the other ranks wait at the barrier)
+        if ws > 1:  # the single-GPU time of the same job first, on rank 0 alone; the other ranks SLEEP on the rendezvous
+            # store until it is done (an NCCL barrier would spin one host core per idle rank next to the job being timed)
+            store = dist.distributed_c10d._get_default_store()
             if rank == 0:
                 with _Solo(bdist, True):
                     r_1 = strong_c3(dev, None, maxiter=20, factor_mode="recompute")
+                store.set("bo_bench_solo_done", "1")
+            else:
+                store.wait(["bo_bench_solo_done"])
             barrier()
         r_n = strong_c3(dev, world_group, maxiter=20, factor_mode="broadcast")
         r_1 = r_n if r_1 is None else r_1

@@ -64,7 +64,7 @@ def _pool():
 
 
 def sobol_draw(dimension: int, n: int, seed: Optional[int] = None, dtype: Optional[torch.dtype] = None,
-               columns: Optional[Tensor] = None, first: int = 0) -> Tensor:  # fmt: skip
+               columns: Optional[Tensor] = None, first: int = 0, post=None) -> Tensor:  # fmt: skip
     """Points ``first .. first + n - 1`` of ``SobolEngine(dimension, scramble=True, seed=seed)`` -- bit for bit -- or only
     their ``columns`` (a sorted 1-D index tensor), computed without scrambling the dimensions nobody reads.  ``first`` > 0
     is the engine's ``fast_forward(first)`` (integer recurrence only): a rank that evaluates rows [lo, hi) of the raw
@@ -78,7 +78,10 @@ def sobol_draw(dimension: int, n: int, seed: Optional[int] = None, dtype: Option
     needs q of the n_b + q dimensions (the baseline columns are overwritten, cached_cholesky.py:167-186) and pays for q;
     (2) a full draw is split by dimension over host threads (torch's ops release the GIL).  At n_b = 2000, q = 8 the
     first goes from ~70 ms to ~10 ms and the second from ~70 ms to ~25 ms on 8 cores; tests/test_host_logic.py holds
-    both to ``torch.equal`` with the stock engine.
+    both to ``torch.equal`` with the stock engine.  ``post(block, sel)`` (optional) is an elementwise map applied by each
+    worker to its block of columns ``sel`` before it is stored -- the inverse normal CDF, the affine map into a box -- so
+    that this work is threaded too (under torchrun ``OMP_NUM_THREADS=1`` makes torch's own elementwise loops serial: the
+    42 MB affine map of the C3 raw samples alone took ~30 ms on one core).
     """
     if dimension > SobolEngine.MAXDIM or dimension < 1:
         raise ValueError(f"Supported range of dimensionality for SobolEngine is [1, {SobolEngine.MAXDIM}]")
@@ -110,15 +113,15 @@ def sobol_draw(dimension: int, n: int, seed: Optional[int] = None, dtype: Option
         torch._sobol_engine_scramble_(st, lower, b - a)
         quasi = torch.mv(shift_bits[sel], pow2).clone(memory_format=torch.contiguous_format)
         if first == 0:  # point 0 is the shift itself (quasirandom.py:77-113)
-            out[0, a:b] = (quasi / 2**bits).to(dtype)
+            blk = (quasi / 2**bits).to(dtype).reshape(1, -1)
             if n > 1:
                 rest, _ = torch._sobol_engine_draw(quasi, n - 1, st, b - a, 0, dtype=dtype)
-                out[1:, a:b] = rest
+                blk = torch.cat((blk, rest), dim=0)
         else:
             if first > 1:
                 torch._sobol_engine_ff_(quasi, first - 1, st, b - a, 0)
-            rest, _ = torch._sobol_engine_draw(quasi, n, st, b - a, first - 1, dtype=dtype)
-            out[:, a:b] = rest
+            blk, _ = torch._sobol_engine_draw(quasi, n, st, b - a, first - 1, dtype=dtype)
+        out[:, a:b] = blk if post is None else post(blk, sel)
 
     chunks = max(1, min(_SOBOL_THREADS, width // 16))
     edges = [(width * i) // chunks for i in range(chunks + 1)]
@@ -189,15 +192,20 @@ def draw_sobol_samples(
     batch_shape = torch.Size(batch_shape or ())
     d = bounds.shape[-1]
     lower, width = bounds[0], bounds[1] - bounds[0]
+    lo_flat, w_flat = lower.cpu().repeat(q), width.cpu().repeat(q)
+
+    def into_box(u: Tensor, sel) -> Tensor:  # lower + width * u on one block of columns (same two roundings as the reference)
+        return lo_flat[sel] + w_flat[sel] * u
+
     if rows is not None:  # rows [lo, hi) of the n points only (no batch shape): one rank's block of the raw samples
         lo, hi = rows
-        u = sobol_draw(q * d, hi - lo, seed=seed, dtype=lower.dtype, first=lo).view(hi - lo, q, d).to(device=lower.device)
-        return lower + width * u
-    u = sobol_draw(q * d, batch_shape.numel() * n, seed=seed, dtype=lower.dtype)
-    u = u.view(*batch_shape, n, q, d).to(device=lower.device)
+        x = sobol_draw(q * d, hi - lo, seed=seed, dtype=lower.dtype, first=lo, post=into_box)
+        return x.view(hi - lo, q, d).to(device=lower.device)
+    x = sobol_draw(q * d, batch_shape.numel() * n, seed=seed, dtype=lower.dtype, post=into_box)
+    x = x.view(*batch_shape, n, q, d).to(device=lower.device)
     if len(batch_shape) > 0:  # the sample index leads
-        u = u.movedim(len(batch_shape), 0)
-    return lower + width * u
+        x = x.movedim(len(batch_shape), 0)
+    return x
 
 
 def draw_sobol_normal_samples(
@@ -208,7 +216,7 @@ def draw_sobol_normal_samples(
     seed: Optional[int] = None,
 ) -> Tensor:
     """``n x d`` quasi-random standard normal draws (inverse-CDF Sobol)."""
-    return _normal_from_uniform(sobol_draw(d, n, seed=seed, dtype=dtype)).to(device=device)
+    return sobol_draw(d, n, seed=seed, dtype=dtype, post=lambda u, sel: _normal_from_uniform(u)).to(device=device)
 
 
 class MCSampler(Module):
@@ -306,7 +314,8 @@ class SobolQMCNormalSampler(NormalMCSampler):
             if skip_leading > 0:
                 cols = torch.nonzero(torch.arange(dim) % target[-1] >= skip_leading).squeeze(-1)
                 z = torch.zeros(n, dim, dtype=posterior.dtype)
-                z[:, cols] = _normal_from_uniform(sobol_draw(dim, n, seed=self.seed, dtype=posterior.dtype, columns=cols))
+                z[:, cols] = sobol_draw(dim, n, seed=self.seed, dtype=posterior.dtype, columns=cols,
+                                        post=lambda u, sel: _normal_from_uniform(u))
                 z = z.to(device=posterior.device)
             else:
                 z = draw_sobol_normal_samples(d=dim, n=n, device=posterior.device, dtype=posterior.dtype, seed=self.seed)

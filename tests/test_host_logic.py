@@ -163,6 +163,16 @@ def test_sobol_draw_is_bit_identical_to_the_stock_engine():
         assert torch.equal(sobol_draw(dim, n, seed=99, dtype=dtype, columns=cols), ref[:, cols])
         cols = torch.nonzero(torch.arange(dim) % 5 >= 3).squeeze(-1)  # strided selection (ensemble-collapsed layout)
         assert torch.equal(sobol_draw(dim, n, seed=99, dtype=dtype, columns=cols), ref[:, cols])
+    # the box map and the inverse normal CDF are applied per column block by the workers: same roundings as the reference's
+    # `lower + width * u` / `erfinv(2 v - 1) sqrt 2` over the whole tensor
+    bounds = torch.tensor([[-1.0, 0.5, 2.0], [1.0, 0.75, 5.0]], dtype=torch.float64)
+    u = SobolEngine(12, scramble=True, seed=5).draw(1000, dtype=torch.float64).view(1000, 4, 3)
+    ref = bounds[0] + (bounds[1] - bounds[0]) * u
+    assert torch.equal(bb.draw_sobol_samples(bounds, 1000, 4, seed=5), ref)
+    assert torch.equal(bb.draw_sobol_samples(bounds, 1000, 4, seed=5, rows=(100, 300)), ref[100:300])
+    u = SobolEngine(300, scramble=True, seed=2).draw(64, dtype=torch.float64)
+    v = 0.5 + (1 - torch.finfo(u.dtype).eps) * (u - 0.5)
+    assert torch.equal(bb.draw_sobol_normal_samples(300, 64, dtype=torch.float64, seed=2), torch.erfinv(2 * v - 1) * 2**0.5)
     # unseeded: the scramble bits come from the global stream in the same order
     torch.manual_seed(7)
     ref = SobolEngine(40, scramble=True).draw(16, dtype=torch.float64)

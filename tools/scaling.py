@@ -317,8 +317,14 @@ def main():
             finally:
                 if ctx is not None:
                     ctx.__exit__(None, None, None)
-        if ws > 1:
+        if ws > 1:  # ranks outside the group SLEEP on the rendezvous store while it works (an NCCL barrier spins a host core
+            # per idle rank next to the job being timed); then everyone meets
             torch.cuda.synchronize(dev)
+            store = dist.distributed_c10d._get_default_store()
+            if rank == 0:
+                store.set(f"bo_scaling_done_{n}", "1")
+            else:
+                store.wait([f"bo_scaling_done_{n}"])
             dist.barrier()
     if rank == 0 and "c5" in what and args.c5_cpu:
         out["c5_cpu_baseline"] = c5_cpu_baseline(args.c5_n)
