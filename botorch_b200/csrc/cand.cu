@@ -590,16 +590,34 @@ __global__ void __launch_bounds__(CAND_THREADS, (QT <= 4 ? BO_CAND_MINB4 : (QT <
     double local_max = -INFINITY;
     const bool plain = (a.reduction == BO_REDUCE_PLAIN);
     const double inv_tau_relu = 1.0 / a.tau_relu;
-    for (int s = tid; s < a.S; s += T) {
-        double li[QT], zq[QT];
-        const double bf = a.best_f[(long)z * a.Sp + s];
+    // The sample rows are read one iteration ahead (BO_CAND_PREFETCH): the store to row s at the end of an iteration would
+    // otherwise keep the compiler from hoisting the load of row s + T above it (same pointer), and every iteration would
+    // start by waiting out a full global-load latency.
+    double fnext[QT], znext[QT], bnext = 0.0;
 #pragma unroll
-        for (int j = 0; j < QT; j++) zq[j] = (j < q) ? a.Zq[(long)s * q + j] : 0.0;
+    for (int j = 0; j < QT; j++) {
+        fnext[j] = (j < q && tid < a.S && !a.f_zero) ? F[(long)tid * a.ldn + c0 + j] : 0.0;
+        znext[j] = (j < q && tid < a.S) ? a.Zq[(long)tid * q + j] : 0.0;
+    }
+    if (tid < a.S) bnext = a.best_f[(long)z * a.Sp + tid];
+    for (int s = tid; s < a.S; s += T) {
+        double li[QT], zq[QT], fcur[QT];
+        const double bf = bnext;
+#pragma unroll
+        for (int j = 0; j < QT; j++) { fcur[j] = fnext[j]; zq[j] = znext[j]; }
+        if (s + T < a.S) {
+#pragma unroll
+            for (int j = 0; j < QT; j++) {
+                fnext[j] = (j < q && !a.f_zero) ? F[(long)(s + T) * a.ldn + c0 + j] : 0.0;
+                znext[j] = (j < q) ? a.Zq[(long)(s + T) * q + j] : 0.0;
+            }
+            bnext = a.best_f[(long)z * a.Sp + s + T];
+        }
 #pragma unroll
         for (int j = 0; j < QT; j++) {
             li[j] = 0.0;
             if (j < q) {
-                double v = (a.f_zero ? 0.0 : F[(long)s * a.ldn + c0 + j]) + c.mu[j];
+                double v = fcur[j] + c.mu[j];
 #pragma unroll
                 for (int k = 0; k < QT; k++)
                     if (k <= j) v += c.Lq[j * q + k] * zq[k];
@@ -682,13 +700,22 @@ __global__ void __launch_bounds__(CAND_THREADS, (QT <= 4 ? BO_CAND_MINB4 : (QT <
     for (int j = 0; j < QT; j++) am[j] = 0.0;
 #pragma unroll
     for (int p = 0; p < PT; p++) al[p] = 0.0;
+    double fnext[QT];  // sample rows read one iteration ahead, as in the forward kernel
+#pragma unroll
+    for (int j = 0; j < QT; j++) fnext[j] = (j < q && tid < a.S) ? F[(long)tid * a.ldn + c0 + j] : 0.0;
     for (int s = tid; s < a.S; s += T) {
-        double f[QT], li[QT], gm[QT], zq[QT];
+        double f[QT], li[QT], gm[QT], zq[QT], fcur[QT];
+#pragma unroll
+        for (int j = 0; j < QT; j++) fcur[j] = fnext[j];
+        if (s + T < a.S) {
+#pragma unroll
+            for (int j = 0; j < QT; j++) fnext[j] = (j < q) ? F[(long)(s + T) * a.ldn + c0 + j] : 0.0;
+        }
         if (a.df_external) {  // F already holds d loss / d f: only the accumulations below
             int p2 = 0;
 #pragma unroll
             for (int j = 0; j < QT; j++) {
-                const double df = (j < q) ? F[(long)s * a.ldn + c0 + j] : 0.0;
+                const double df = fcur[j];
                 am[j] += df;
 #pragma unroll
                 for (int k = 0; k <= j; k++) al[p2++] += df * ((k < q) ? a.Zq[(long)s * q + k] : 0.0);
@@ -700,7 +727,7 @@ __global__ void __launch_bounds__(CAND_THREADS, (QT <= 4 ? BO_CAND_MINB4 : (QT <
         for (int j = 0; j < QT; j++) {
             f[j] = 0.0; li[j] = 0.0; zq[j] = 0.0;
             if (j < q) {
-                f[j] = F[(long)s * a.ldn + c0 + j];
+                f[j] = fcur[j];
                 li[j] = plain ? fmax(a.obj_w * f[j] - bf, 0.0) : log_improvement(a.reduction, a.obj_w * f[j] - bf, a.tau_relu, inv_tau_relu);
                 zq[j] = a.Zq[(long)s * q + j];
             }
@@ -1340,13 +1367,16 @@ int bo_mc_reduce_bwd_launch(const BoReduceArgs& a, cudaStream_t stream) {
 
 // Threads per (model, t-batch) CTA.  With thousands of small problems (SAAS: 256 models x 64 t-batches) narrower CTAs win a
 // little: the serial sections (q x q Cholesky on one warp, block reductions) idle fewer warps and more problems are in
-// flight per SM.  Measured at C4 (16 384 problems, step time): 128 threads 1.604 ms, 64 threads 1.546 ms, 32 threads
-// 1.563 ms -- the kernels are bound by FP64 transcendental instruction issue, not by their geometry.
+// flight per SM.  Measured at C4 (16 384 problems, step time): 128 threads 1.62 ms, 64 threads 1.45 ms, 32 threads
+// 1.35 ms with the sample rows read one iteration ahead (before that: 1.60 / 1.55 / 1.56): one warp per problem has no
+// block barrier to wait at and 8 samples per thread to hide each load behind.
 // BO_CAND_THREADS overrides (32 / 64 / 128) for A/B measurements.
 static int cand_threads(const BoCandArgs& a) {
     static const int forced = [] { const char* e = getenv("BO_CAND_THREADS"); return e ? atoi(e) : 0; }();
     if (forced == 32 || forced == 64 || forced == 128) return forced;
-    return ((long)a.B * a.h.M >= 4096 && a.q <= 8) ? 64 : CAND_THREADS;
+    const long problems = (long)a.B * a.h.M;
+    if (problems >= 8192 && a.q <= 4) return 32;
+    return (problems >= 4096 && a.q <= 8) ? 64 : CAND_THREADS;
 }
 
 int bo_cand_fwd(const BoCandArgs& a, cudaStream_t stream) {
