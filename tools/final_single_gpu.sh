@@ -11,3 +11,8 @@ ncu --metrics gpu__time_duration.sum --clock-control none --profile-from-start o
 python bench.py --no-cpu-baseline --no-strong --steps 20 > gpurun_out/b_after.json 2>/dev/null; python tools/_pj.py gpurun_out/b_after.json
 cat gpurun_out/final_gpu_tests.txt
 python tools/_pj.py gpurun_out/r02_bench_c3_1gpu.json
+# C4 step: full counter set for the per-kernel table
+timeout 600 ncu --set full --clock-control none --profile-from-start off -c 10 -o /tmp/step_C4 -f python bench.py --config C4 --steps 1 --warmup 3 --no-cpu-baseline --no-strong > gpurun_out/ncu_C4.log 2>&1
+ncu -i /tmp/step_C4.ncu-rep --page raw --csv > gpurun_out/r02_ncu_full_c4_step.csv 2>/dev/null
+ncu --metrics gpu__time_duration.sum --clock-control none --profile-from-start off -c 10 --csv --log-file gpurun_out/r02_launches_C4_step.csv python bench.py --config C4 --steps 2 --warmup 3 --no-cpu-baseline --no-strong > /dev/null 2>&1
+python -c "import __graft_entry__ as g; g.smoke(); print('smoke ok')"
