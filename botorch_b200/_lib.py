@@ -69,6 +69,7 @@ class BoNEI(C.Structure):
         ("external_df", C.c_int32),
         ("schur_jitter", C.c_double),
         ("schur_fixed", C.c_int32),
+        ("local_derivs", C.c_int32),
     ]
 
 

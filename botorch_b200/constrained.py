@@ -352,7 +352,8 @@ class qLogNEIModelList(AcquisitionFunction):
         self._Zb = self._draw(n_b, m)  # S x n_b x m: one draw over the (points x outcomes) block, like the reference
         Xb = self.X_baseline.to(dev)
         self._neis = [engine.NEIState(gp, Xb, self._Zb[:, :, k].to(dev).contiguous(), reduction=self._reduction,
-                                      obj_weight=(self._obj_w if k == self._obj_idx else 1.0)) for k, gp in enumerate(gps)]  # fmt: skip
+                                      obj_weight=(self._obj_w if k == self._obj_idx else 1.0)).keep_samples()
+                      for k, gp in enumerate(gps)]  # fmt: skip
         self._Zq_cache = {}
         # incumbent: best FEASIBLE objective over the baseline samples of all outcomes (acquisition/utils.py:90-163)
         base = torch.stack([engine.root_apply(nei.baseline_L.contiguous(), nei.mean_b[:, : nei.n_b],
@@ -476,7 +477,8 @@ class qLogEIModelList(qLogNEIModelList):
         self.S = int(self.sample_shape[0])
         self._best_f = self.best_f.reshape(1).expand(self.S).to(dev).contiguous()  # per-sample incumbent, all equal
         self._neis = [engine.EIState(gp, self.best_f.to(dev), self.S, reduction=self._reduction,
-                                     obj_weight=(self._obj_w if k == self._obj_idx else 1.0)) for k, gp in enumerate(gps)]  # fmt: skip
+                                     obj_weight=(self._obj_w if k == self._obj_idx else 1.0)).keep_samples()
+                      for k, gp in enumerate(gps)]  # fmt: skip
         self._Zq_cache = {}
 
     def _base_samples_q(self, q: int) -> List[Tensor]:

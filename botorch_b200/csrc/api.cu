@@ -427,6 +427,7 @@ struct QWork {
     long ldn, R, regionStride;
     double *baug, *W0, *W1, *W2, *W3, *F, *W5, *W6, *Lq, *lse, *Sbar, *Wd, *H;
     double *gram, *post;           // fused combined-root pieces (BoGemm::gram / BoGemm::post), 8 % q == 0 only
+    double* msave;                 // per-sample maxima of the forward [M][B][Sp] (bo_nei::local_derivs), with_grad only
     long strideGram, stridePost;
     int gram_tiles;
     long strideH;
@@ -503,6 +504,7 @@ QWork qlayout(const bo_gp* gp, const bo_nei* nei, int B, int q, int with_grad, v
         w.gram = b.doubles(M * w.strideGram);
         if (with_grad) w.post = b.doubles(M * w.stridePost);
     }
+    if (with_grad) w.msave = b.doubles(M * (long)B * bo_pad8(nei->S));  // appended last as well
     w.ok = b.ok;
     w.bytes = b.off;
     return w;
@@ -537,6 +539,9 @@ BoCandArgs cand_args(const bo_gp* gp, const bo_nei* nei, int B, int q, const dou
     a.obj_w = (nei && nei->obj_weight != 0.0) ? nei->obj_weight : 1.0;
     a.schur_jitter = nei ? nei->schur_jitter : 0.0;
     a.schur_fixed = nei ? nei->schur_fixed : 0;
+    // local derivatives only where the reductions are the log ones and nobody else writes the sample rows
+    a.local_derivs = (nei && nei->local_derivs && nei->reduction != BO_REDUCE_PLAIN && !nei->external_df && w.msave && q <= 8) ? 1 : 0;
+    a.msave = w.msave;
     a.ldn = w.ldn;
     a.V = w.W1; a.strideV = w.regionStride;
     a.BL = w.W3; a.strideBL = w.regionStride;

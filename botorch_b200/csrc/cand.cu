@@ -497,7 +497,7 @@ __device__ __forceinline__ double pair_r2(const double* X, int d, const double* 
     return r2;
 }
 
-template <int QT>
+template <int QT, bool PRE>
 __global__ void __launch_bounds__(CAND_THREADS, (QT <= 4 ? BO_CAND_MINB4 : (QT <= 8 ? 4 : 1))) cand_fwd_kernel(const BoCandArgs a) {
     extern __shared__ __align__(16) double sm[];
     __shared__ double red[CAND_THREADS / 32];
@@ -621,13 +621,28 @@ __global__ void __launch_bounds__(CAND_THREADS, (QT <= 4 ? BO_CAND_MINB4 : (QT <
 #pragma unroll
                 for (int k = 0; k < QT; k++)
                     if (k <= j) v += c.Lq[j * q + k] * zq[k];
-                F[(long)s * a.ldn + c0 + j] = v;
+                if (!PRE) F[(long)s * a.ldn + c0 + j] = v;
                 if (!isfinite(v)) bad = 1;
+                fcur[j] = v;
                 li[j] = plain ? fmax(a.obj_w * v - bf, 0.0) : log_improvement(a.reduction, a.obj_w * v - bf, a.tau_relu, inv_tau_relu);
             }
         }
         double m;
-        if (plain) {  // (obj - best_f).clamp_min(0).amax(q)   (monte_carlo.py:410,536-547)
+        if (PRE) {
+            // bo_nei::local_derivs: everything of the reverse pass that depends on this sample alone is formed here, while
+            // li is in registers -- d qmax_s / d f[s][j] = (fatmax weight) x (d log_fatplus) -- and replaces the sample in
+            // its row; the reverse kernel multiplies by the logmeanexp weight exp(m_s - lse) and the upstream gradient.
+            double gm[QT];
+            m = qmax_log_grad<QT>(a.reduction, li, q, a.tau_max, gm);
+#pragma unroll
+            for (int j = 0; j < QT; j++) {
+                if (j < q) {
+                    const double dli = isinf(li[j]) ? 0.0 : dlog_improvement(a.reduction, a.obj_w * fcur[j] - bf, a.tau_relu, inv_tau_relu);
+                    F[(long)s * a.ldn + c0 + j] = gm[j] * dli;
+                }
+            }
+            a.msave[((long)z * a.B + b) * a.Sp + s] = m;
+        } else if (plain) {  // (obj - best_f).clamp_min(0).amax(q)   (monte_carlo.py:410,536-547)
             m = li[0];
 #pragma unroll
             for (int j = 1; j < QT; j++)
@@ -716,6 +731,24 @@ __global__ void __launch_bounds__(CAND_THREADS, (QT <= 4 ? BO_CAND_MINB4 : (QT <
 #pragma unroll
             for (int j = 0; j < QT; j++) {
                 const double df = fcur[j];
+                am[j] += df;
+#pragma unroll
+                for (int k = 0; k <= j; k++) al[p2++] += df * ((k < q) ? a.Zq[(long)s * q + k] : 0.0);
+            }
+            continue;
+        }
+        if (a.local_derivs) {  // the forward left d qmax_s / d f in the row and qmax_s in msave: scale and accumulate
+            const double m = a.msave[((long)z * a.B + b) * a.Sp + s];
+            const double w = isinf(lse) ? ((m == lse) ? 1.0 : 0.0) : exp(m - lse);
+            const double gw = a.obj_w * g * w;
+            int p2 = 0;
+#pragma unroll
+            for (int j = 0; j < QT; j++) {
+                double df = 0.0;
+                if (j < q) {
+                    df = gw * fcur[j];
+                    F[(long)s * a.ldn + c0 + j] = df;
+                }
                 am[j] += df;
 #pragma unroll
                 for (int k = 0; k <= j; k++) al[p2++] += df * ((k < q) ? a.Zq[(long)s * q + k] : 0.0);
@@ -1386,18 +1419,25 @@ int bo_cand_fwd(const BoCandArgs& a, cudaStream_t stream) {
     const size_t smem = cand_smem_bytes(a.q, CAND_THREADS, a.S);
     if (smem > 200 * 1024) return BO_ERR_UNSUPPORTED;
     dim3 grid(a.B, a.h.M);
-    if (a.q <= 4) {
-        BO_TRY(set_smem_limit((const void*)cand_fwd_kernel<4>, smem));
-        cand_fwd_kernel<4><<<grid, CT, smem, stream>>>(a);
+    if (a.local_derivs && a.q > 8) return BO_ERR_INVALID;  // cand_args clears it for q > 8
+    if (a.q <= 4 && a.local_derivs) {
+        BO_TRY(set_smem_limit((const void*)cand_fwd_kernel<4, true>, smem));
+        cand_fwd_kernel<4, true><<<grid, CT, smem, stream>>>(a);
+    } else if (a.q <= 4) {
+        BO_TRY(set_smem_limit((const void*)cand_fwd_kernel<4, false>, smem));
+        cand_fwd_kernel<4, false><<<grid, CT, smem, stream>>>(a);
+    } else if (a.q <= 8 && a.local_derivs) {
+        BO_TRY(set_smem_limit((const void*)cand_fwd_kernel<8, true>, smem));
+        cand_fwd_kernel<8, true><<<grid, CT, smem, stream>>>(a);
     } else if (a.q <= 8) {
-        BO_TRY(set_smem_limit((const void*)cand_fwd_kernel<8>, smem));
-        cand_fwd_kernel<8><<<grid, CT, smem, stream>>>(a);
+        BO_TRY(set_smem_limit((const void*)cand_fwd_kernel<8, false>, smem));
+        cand_fwd_kernel<8, false><<<grid, CT, smem, stream>>>(a);
     } else if (a.q <= 16) {
-        BO_TRY(set_smem_limit((const void*)cand_fwd_kernel<16>, smem));
-        cand_fwd_kernel<16><<<grid, CT, smem, stream>>>(a);
+        BO_TRY(set_smem_limit((const void*)cand_fwd_kernel<16, false>, smem));
+        cand_fwd_kernel<16, false><<<grid, CT, smem, stream>>>(a);
     } else {
-        BO_TRY(set_smem_limit((const void*)cand_fwd_kernel<BO_MAX_Q>, smem));
-        cand_fwd_kernel<BO_MAX_Q><<<grid, CT, smem, stream>>>(a);
+        BO_TRY(set_smem_limit((const void*)cand_fwd_kernel<BO_MAX_Q, false>, smem));
+        cand_fwd_kernel<BO_MAX_Q, false><<<grid, CT, smem, stream>>>(a);
     }
     BO_LAUNCH_CHECK();
     return BO_OK;

@@ -53,6 +53,8 @@ struct BoCandArgs {
     const double* gram; long strideGram; int gram_tiles;  // forward: [row tile][ceil(N/8)][8 x 8] partial Grams of the BL block
                                                            // produced by the GEMM epilogue; BL itself is not read
     double schur_jitter; int schur_fixed;  // forward: one factorisation attempt of the q x q block with this jitter (bo_nei)
+    // bo_nei::local_derivs: the forward leaves d qmax_s / d f[s][j] in the sample rows and qmax_s in msave [M][B][Sp]
+    double* msave; int local_derivs;
     double* post; long stridePost;     // backward: [ceil(N/8)][8 x 8] <- u_coef * Sbar (block diagonal), instead of Uinplace
 };
 

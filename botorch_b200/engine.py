@@ -322,6 +322,13 @@ GRAPH_MAX_WORKSPACE_BYTES = 16 << 20
 GRAPH_MIN_USES = 64
 
 
+def _local_derivs_default(reduction: int) -> int:
+    """bo_nei.local_derivs: with the log reductions a gradient-carrying forward leaves d qmax_s / d f in the sample rows
+    (the reverse kernel then only scales them).  ``keep_samples()`` switches it off for callers that read the samples.
+    BOTORCH_B200_LOCAL_DERIVS=0 disables it for A/B measurements."""
+    return int(int(reduction) != REDUCE_PLAIN and os.environ.get("BOTORCH_B200_LOCAL_DERIVS", "1") != "0")
+
+
 class NEIState:
     """Baseline factors of qLogNEI (V_b, L_b and its inverse, base samples, best_f) and the fused fwd/bwd."""
 
@@ -362,7 +369,7 @@ class NEIState:
             lb_inv_t=ptr(self.lb_inv_t), zb_pad=ptr(self.zb_pad), zb_t=ptr(self.zb_t), mean_b=ptr(self.mean_b),
             best_f=ptr(self.best_f_pad), qmat=ptr(self.qmat), qmat_t=ptr(self.qmat_t),
             fwd_cat=ptr(self.fwd_cat), bwd_cat=ptr(self.bwd_cat), reduction=int(reduction), no_baseline=0,
-            obj_weight=float(obj_weight),
+            obj_weight=float(obj_weight), local_derivs=_local_derivs_default(reduction),
         )  # fmt: skip
         self.jitter = torch.zeros(M, dtype=torch.float64, device=dev)
         if not setup:
@@ -458,8 +465,15 @@ class NEIState:
 
 
     # -- outcome constraints across several models (SURVEY 8f N2): sample rows of the workspace, external sample adjoints --
+    def keep_samples(self) -> "NEIState":
+        """The caller reads the samples after a forward (outcome constraints, generic objectives): leave them in place."""
+        self.c.local_derivs = 0
+        return self
+
     def samples_view(self, work: Tensor, B: int, q: int) -> Tensor:
         """[S x pitch] view of the cached-Cholesky samples a gradient-carrying forward left in ``work`` (M = 1)."""
+        if self.c.local_derivs:
+            raise _lib.BoError("samples_view needs keep_samples(): this state leaves local derivatives in the sample rows")
         off, pitch = C.c_int64(), C.c_int64()
         check(_lib.lib().bo_qlognei_samples_view(C.byref(self.gp.c), C.byref(self.c), B, q, C.byref(off), C.byref(pitch)))
         flat = work[off.value * 8 : (off.value + self.S * pitch.value) * 8].view(torch.float64)
@@ -503,7 +517,7 @@ class EIState(NEIState):
         self.info = torch.zeros(M, dtype=torch.int32, device=dev)
         self.c = BoNEI(n_b=0, S=self.S, baseline_is_train=0, best_f=ptr(self.best_f_pad), fwd_cat=ptr(self.fwd_cat),
                        bwd_cat=ptr(self.bwd_cat), reduction=int(reduction), no_baseline=1,
-                       obj_weight=float(obj_weight))  # fmt: skip
+                       obj_weight=float(obj_weight), local_derivs=_local_derivs_default(reduction))  # fmt: skip
         if not setup:
             return
         lib = _lib.lib()

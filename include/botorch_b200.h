@@ -118,6 +118,13 @@ typedef struct bo_nei {
      * failure is reported as BO_INFO_NOT_PSD and the host moves on to the next delta of the schedule. */
     double schur_jitter;
     int32_t schur_fixed;
+    /* local_derivs = 1 (log reductions only): a gradient-carrying bo_qlognei_fwd leaves in the sample rows of the workspace
+     * NOT the samples f[s][j] but the per-sample local derivative d qmax_s / d f[s][j] (fatmax weight x d log_fatplus), and
+     * the per-sample maxima next to them; bo_qlognei_bwd then only scales them by the logmeanexp weights instead of
+     * re-evaluating log_fatplus / fatmax for every (sample, point).  Same numbers up to the association of one product.
+     * Must be 0 when the caller reads the samples (bo_qlognei_samples_view: outcome constraints, generic objectives) and
+     * must not change between a forward and its backward. */
+    int32_t local_derivs;
 } bo_nei;
 
 typedef struct bo_ctx bo_ctx;

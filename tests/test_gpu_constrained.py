@@ -105,7 +105,10 @@ def test_single_model_list_equals_plain_qlognei(cuda):
     (ga,) = torch.autograd.grad(va.sum(), Xa)
     (gb,) = torch.autograd.grad(vb.sum(), Xb)
     assert rel_err(vb, va, scale=1.0) < 1e-13
-    assert rel_err(gb, ga, scale=float(ga.abs().max())) < 1e-12
+    # the plain route forms d qmax / d f in its forward kernel (bo_nei.local_derivs) and multiplies by the sample weight in
+    # the reverse one, the split route forms the same product in one place: one association differs, and this d = 3
+    # problem amplifies a last-bit difference of the sample adjoints ~1e4-fold (see the note at the top of the file)
+    assert rel_err(gb, ga, scale=float(ga.abs().max())) < 1e-11
 
 
 def test_constrained_acquisition_under_optimize_acqf(cuda):

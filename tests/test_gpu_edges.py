@@ -181,3 +181,35 @@ def test_graph_replay_equals_eager_launches_bit_for_bit(cuda, monkeypatch):
     vb, gb = value_and_grad(X2)  # eager
     assert torch.equal(va, vb) and torch.equal(ga, gb)
     assert engine.GRAPH_MIN_USES >= 32  # default: short-lived shapes are never captured (profiles/r02_graph_cost.json)
+
+
+@pytest.mark.parametrize("cfg,B,reduction", [("C2", 16, "log"), ("C1", 5, "log"), ("C2", 7, "soft")])
+def test_local_derivative_mode_equals_the_recomputing_reverse_pass(cuda, cfg, B, reduction):
+    """bo_nei.local_derivs: the forward leaves d qmax_s / d f in the sample rows and the reverse kernel scales them, instead
+    of re-evaluating log_fatplus / fatmax per (sample, point).  Same value, same gradient up to the association of one
+    product; the state with ``keep_samples()`` is the recomputing route (what outcome constraints use)."""
+    from botorch_b200 import engine
+    from botorch_b200.synthetic import make_problem
+    from tests.util import candidates, gp_state, oracle_acq, oracle_gp
+
+    p = make_problem(cfg)
+    ogp = oracle_gp(p)
+    oacq = oracle_acq(p, ogp)
+    st = gp_state(p, ogp, cuda)
+    red = engine.REDUCE_LOG if reduction == "log" else engine.REDUCE_LOG_SOFT
+    fast = engine.NEIState(st, p.train_X.to(cuda), oacq.Z_b.to(cuda), reduction=red)
+    slow = engine.NEIState(st, p.train_X.to(cuda), oacq.Z_b.to(cuda), reduction=red).keep_samples()
+    assert fast.c.local_derivs == 1 and slow.c.local_derivs == 0
+    X = candidates(p, B).to(cuda)
+    Zq = oacq.Z_q(p.q).to(cuda).contiguous()
+    gin = torch.linspace(-1.5, 0.5, B, dtype=torch.float64, device=cuda).reshape(1, B).contiguous()
+    out = []
+    for nei in (fast, slow):
+        acq, info, work = nei.forward(X, Zq, oacq.tau_relu, oacq.tau_max, with_grad=True)
+        assert int(info.abs().sum()) == 0
+        out.append((acq.clone(), nei.backward(X, Zq, oacq.tau_relu, oacq.tau_max, gin, work).clone()))
+    (a1, g1), (a0, g0) = out
+    assert float((a1 - a0).abs().max()) <= 1e-14 * float(a0.abs().max())
+    assert float((g1 - g0).abs().max()) <= 1e-12 * float(g0.abs().max())
+    with pytest.raises(Exception):
+        fast.samples_view(work, B, p.q)  # the sample rows do not hold samples in this mode
