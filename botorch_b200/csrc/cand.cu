@@ -89,6 +89,29 @@ __device__ __forceinline__ double dlog_improvement(int reduction, double z, doub
     return reduction == BO_REDUCE_LOG_SOFT ? dlog_softplus_ref(z, tau, inv_tau) : dlog_fatplus(z, tau, inv_tau);
 }
 
+// value and derivative in one pass (the forward kernel with bo_nei::local_derivs): the same operations in the same order
+// as the two functions above, sharing exp(u), 1 / (1 + u^2) and the softplus -- the derivative costs one more division
+__device__ __forceinline__ double log_improvement_vg(int reduction, double z, double tau, double inv_tau, double& d) {
+    const double u = z * inv_tau;
+    if (reduction == BO_REDUCE_LOG_SOFT) {
+        if (!(u > -35.0)) { d = inv_tau; return u + log(tau); }
+        if (u > 32.0) { d = 1.0 / z; return log(z); }
+        const double e = exp(u), l1 = log1p(e);
+        d = (e / (1.0 + e)) / (tau * l1);
+        return log(tau * l1);
+    }
+    double sp = (u > 20.0) ? u : 0.0, sig = (u > 20.0) ? 1.0 : 0.0;
+    if (u >= -746.0 && u <= 20.0) {
+        const double e = exp(u);
+        sp = log1p(e);
+        sig = e / (e + 1.0);
+    }
+    const double c = 1.0 / fma(u, u, 1.0);
+    const double val = sp + 0.1 * c;
+    d = (val > 0.0) ? (sig - 0.2 * u * c * c) / (val * tau) : 0.0;
+    return log(tau * val);
+}
+
 // fatmax over x[0..q) (alpha = 2) with the infinity handling of _inf_max_helper.  QT >= q is a compile-time bound:
 // every loop is fully unrolled with a (j < q) guard so that the per-sample arrays stay in registers.
 // The temperature enters as a multiplication by 1/tau (one rounding away from the reference's division: 1e-16 relative
@@ -623,8 +646,8 @@ __global__ void __launch_bounds__(CAND_THREADS, (QT <= 4 ? BO_CAND_MINB4 : (QT <
                     if (k <= j) v += c.Lq[j * q + k] * zq[k];
                 if (!PRE) F[(long)s * a.ldn + c0 + j] = v;
                 if (!isfinite(v)) bad = 1;
-                fcur[j] = v;
-                li[j] = plain ? fmax(a.obj_w * v - bf, 0.0) : log_improvement(a.reduction, a.obj_w * v - bf, a.tau_relu, inv_tau_relu);
+                if (PRE) li[j] = log_improvement_vg(a.reduction, a.obj_w * v - bf, a.tau_relu, inv_tau_relu, fcur[j]);  // fcur <- d li / d z
+                else li[j] = plain ? fmax(a.obj_w * v - bf, 0.0) : log_improvement(a.reduction, a.obj_w * v - bf, a.tau_relu, inv_tau_relu);
             }
         }
         double m;
@@ -636,10 +659,7 @@ __global__ void __launch_bounds__(CAND_THREADS, (QT <= 4 ? BO_CAND_MINB4 : (QT <
             m = qmax_log_grad<QT>(a.reduction, li, q, a.tau_max, gm);
 #pragma unroll
             for (int j = 0; j < QT; j++) {
-                if (j < q) {
-                    const double dli = isinf(li[j]) ? 0.0 : dlog_improvement(a.reduction, a.obj_w * fcur[j] - bf, a.tau_relu, inv_tau_relu);
-                    F[(long)s * a.ldn + c0 + j] = gm[j] * dli;
-                }
+                if (j < q) F[(long)s * a.ldn + c0 + j] = gm[j] * (isinf(li[j]) ? 0.0 : fcur[j]);
             }
             a.msave[((long)z * a.B + b) * a.Sp + s] = m;
         } else if (plain) {  // (obj - best_f).clamp_min(0).amax(q)   (monte_carlo.py:410,536-547)
