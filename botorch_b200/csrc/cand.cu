@@ -735,16 +735,20 @@ __global__ void __launch_bounds__(CAND_THREADS, (QT <= 4 ? BO_CAND_MINB4 : (QT <
     for (int j = 0; j < QT; j++) am[j] = 0.0;
 #pragma unroll
     for (int p = 0; p < PT; p++) al[p] = 0.0;
-    double fnext[QT];  // sample rows read one iteration ahead, as in the forward kernel
+    double fnext[QT], mnext = 0.0;  // sample rows (and saved maxima) read one iteration ahead, as in the forward kernel
+    const double* msv = a.local_derivs ? a.msave + ((long)z * a.B + b) * a.Sp : nullptr;
 #pragma unroll
     for (int j = 0; j < QT; j++) fnext[j] = (j < q && tid < a.S) ? F[(long)tid * a.ldn + c0 + j] : 0.0;
+    if (msv && tid < a.S) mnext = msv[tid];
     for (int s = tid; s < a.S; s += T) {
         double f[QT], li[QT], gm[QT], zq[QT], fcur[QT];
+        const double mcur = mnext;
 #pragma unroll
         for (int j = 0; j < QT; j++) fcur[j] = fnext[j];
         if (s + T < a.S) {
 #pragma unroll
             for (int j = 0; j < QT; j++) fnext[j] = (j < q) ? F[(long)(s + T) * a.ldn + c0 + j] : 0.0;
+            if (msv) mnext = msv[s + T];
         }
         if (a.df_external) {  // F already holds d loss / d f: only the accumulations below
             int p2 = 0;
@@ -758,7 +762,7 @@ __global__ void __launch_bounds__(CAND_THREADS, (QT <= 4 ? BO_CAND_MINB4 : (QT <
             continue;
         }
         if (a.local_derivs) {  // the forward left d qmax_s / d f in the row and qmax_s in msave: scale and accumulate
-            const double m = a.msave[((long)z * a.B + b) * a.Sp + s];
+            const double m = mcur;
             const double w = isinf(lse) ? ((m == lse) ? 1.0 : 0.0) : exp(m - lse);
             const double gw = a.obj_w * g * w;
             int p2 = 0;
