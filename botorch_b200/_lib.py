@@ -70,6 +70,7 @@ class BoNEI(C.Structure):
         ("schur_jitter", C.c_double),
         ("schur_fixed", C.c_int32),
         ("local_derivs", C.c_int32),
+        ("setup_phase", C.c_int32),
     ]
 
 

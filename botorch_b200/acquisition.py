@@ -500,13 +500,17 @@ class qLogNoisyExpectedImprovement(_FusedImprovementBase):
         if len(sampler.sample_shape) != 1:
             raise UnsupportedError("the fused path takes a one-dimensional sample_shape")
         self.sampler = sampler
-        self.sampler._construct_base_samples(shape_post)  # S x (1 per model-batch dim) x n_b
-        self.base_sampler = deepcopy(self.sampler)
         S = self.sample_shape[0]
-        Z_b = self.sampler.base_samples.reshape(S, n_b).to(device=gp.device, dtype=torch.float64).contiguous()
-        # setup=False: allocate only; botorch_b200.distributed broadcasts the factors from the rank that computed them
-        self._nei = engine.NEIState(gp, self.X_baseline.to(gp.device), Z_b, setup=setup,
-                                    reduction=self._reduction_mode(), obj_weight=self._obj_weight)
+
+        def draw_base_samples() -> Tensor:  # host: a scrambled Sobol engine of dimension n_b (S x (1 per model-batch dim) x n_b)
+            self.sampler._construct_base_samples(shape_post)
+            return self.sampler.base_samples.reshape(S, n_b)
+
+        # setup=False: allocate only; botorch_b200.distributed broadcasts the factors from the rank that computed them.
+        # Otherwise the device factors the baseline posterior while the host draws the base samples (engine.NEIState).
+        self._nei = engine.NEIState(gp, self.X_baseline.to(gp.device), draw_base_samples if setup else draw_base_samples(),
+                                    setup=setup, reduction=self._reduction_mode(), obj_weight=self._obj_weight, S=S)
+        self.base_sampler = deepcopy(self.sampler)
         self.q_in = -1
         self._Zq: Optional[Tensor] = None
         self.register_buffer("_baseline_best_f", None)

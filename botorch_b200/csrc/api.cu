@@ -289,81 +289,96 @@ int bo_nei_setup(bo_ctx* ctx, const bo_gp* gp, const bo_nei* nei, void* work, si
     nei_setup_layout(gp, nei, work, work_bytes, &baug_b, &kb, &fb, &scratch, &nz, &khinv, &khs, &qr, &ok);
     if (!ok) return BO_ERR_WORKSPACE;
     const BoKernelHyper h = hyper_of(gp);
-    BO_CUDA_TRY(cudaMemsetAsync(info, 0, sizeof(int32_t) * M, st));
-    // base samples with padded pitch, and transposed
-    BO_TRY(bo_fill(nei->zb_pad, S * nbp, 0.0, st));
-    BO_TRY(bo_copy2d(nei->Z_b, nb, 0, nei->zb_pad, nbp, 0, (int)S, (int)nb, 1, st));
-    BO_TRY(bo_fill(nei->zb_t, nb * Sp, 0.0, st));
-    BO_TRY(bo_transpose(nei->zb_pad, nbp, 0, nei->zb_t, Sp, 0, (int)S, (int)nb, 1, st));
-    // cross covariance K(X_tr, X_b) and V_b = inv(L) K, mean row
-    const double* rows_b = gp->aug_train;
-    if (!nei->baseline_is_train) {
-        BO_TRY(bo_aug_rows(h, nei->X_b, nb, nei->aug_b, Kp, nb * Kp, st));
-        rows_b = nei->aug_b;
+    // bo_nei::setup_phase: 1 = the factors that do not read Z_b, 2 = only what reads Z_b, 0 = both (same launches, same order
+    // within each part, so 1 followed by 2 leaves the same bits as 0)
+    const bool do_factors = nei->setup_phase != 2, do_samples = nei->setup_phase != 1;
+    if (do_samples && !nei->Z_b) return BO_ERR_INVALID;
+    if (do_factors) BO_CUDA_TRY(cudaMemsetAsync(info, 0, sizeof(int32_t) * M, st));
+    if (do_samples) {  // base samples with padded pitch, and transposed
+        BO_TRY(bo_fill(nei->zb_pad, S * nbp, 0.0, st));
+        BO_TRY(bo_copy2d(nei->Z_b, nb, 0, nei->zb_pad, nbp, 0, (int)S, (int)nb, 1, st));
+        BO_TRY(bo_fill(nei->zb_t, nb * Sp, 0.0, st));
+        BO_TRY(bo_transpose(nei->zb_pad, nbp, 0, nei->zb_t, Sp, 0, (int)S, (int)nb, 1, st));
     }
-    BO_TRY(bo_aug_cols(h, nei->X_b, nb, baug_b, Kp, nbp, Kp * nbp, st));
-    BO_TRY(kmat(gp, gp->aug_train, (int)n, baug_b, nbp, nb, kb, nbp, n * nbp, 0, nullptr, st));
-    BO_TRY(gemm((int)n + 1, (int)nb, (int)n, (int)M, 1.0, gp->linv_aug, np, (n + 1) * np, kb, nbp, n * nbp, 0.0, nullptr,
-                0, 0, nei->vb, nbp, (n + 1) * nbp, BO_TRI_A_LOWER, 0, st));
-    BO_TRY(bo_fill(nei->vb_t, M * nb * np, 0.0, st));
-    BO_TRY(bo_transpose(nei->vb, nbp, (n + 1) * nbp, nei->vb_t, np, nb * np, (int)n, (int)nb, (int)M, st));
-    dim3 mgrid((unsigned)((nb + 127) / 128), (unsigned)M);
-    mean_b_kernel<<<mgrid, 128, 0, st>>>(nei->vb, (n + 1) * nbp, nbp, (int)n, (int)nb, gp->y_mean, gp->y_std, gp->mean,
-                                         nei->mean_b);
-    g_bo_launch_count++;
-    // Sigma_bb = ys^2 (K(X_b,X_b) - V_b^T V_b), lower block-triangle, then its Cholesky root and inverse
-    BO_TRY(kmat(gp, rows_b, (int)nb, baug_b, nbp, nb, nei->lb, nbp, nb * nbp, 1, nullptr, st));
-    BO_TRY(gemm((int)nb, (int)nb, (int)n, (int)M, -ys2, nei->vb_t, np, nb * np, nei->vb, nbp, (n + 1) * nbp, ys2, nei->lb,
-                nbp, nb * nbp, nei->lb, nbp, nb * nbp, BO_TRI_NONE, 1, st));
-    BO_TRY(bo_add_diag(nei->lb, nbp, nb * nbp, (int)nb, (int)M, nei->jitter, st));
-    BO_TRY(bo_potrf_blocked(nei->lb, nbp, nb * nbp, (int)nb, (int)M, nei->lb_inv, nbp, nb * nbp, scratch, info, st));
-    BO_TRY(bo_trtri_blocked(nei->lb, nbp, nb * nbp, (int)nb, (int)M, nei->lb_inv, nbp, nb * nbp, scratch, st));
-    BO_TRY(bo_fill(nei->lb_inv_t, M * nb * nbp, 0.0, st));
-    BO_TRY(bo_transpose(nei->lb_inv, nbp, nb * nbp, nei->lb_inv_t, nbp, nb * nbp, (int)nb, (int)nb, (int)M, st));
-    // baseline samples f_b[s] = mean_b + L_b z_s and best_f[s] = max_i f_b[s][i]
-    BO_TRY(gemm((int)nb, (int)S, (int)nb, (int)M, 1.0, nei->lb, nbp, nb * nbp, nei->zb_t, Sp, 0, 0.0, nullptr, 0, 0, fb, Sp,
-                nb * Sp, BO_TRI_A_LOWER, 0, st));
-    BO_TRY(bo_col_max(fb, nb * Sp, Sp, nei->mean_b, nbp, (int)nb, (int)S, (int)M, nei->best_f, Sp,
-                      nei->obj_weight != 0.0 ? nei->obj_weight : 1.0, st));
+    if (do_factors) {
+        // cross covariance K(X_tr, X_b) and V_b = inv(L) K, mean row
+        const double* rows_b = gp->aug_train;
+        if (!nei->baseline_is_train) {
+            BO_TRY(bo_aug_rows(h, nei->X_b, nb, nei->aug_b, Kp, nb * Kp, st));
+            rows_b = nei->aug_b;
+        }
+        BO_TRY(bo_aug_cols(h, nei->X_b, nb, baug_b, Kp, nbp, Kp * nbp, st));
+        BO_TRY(kmat(gp, gp->aug_train, (int)n, baug_b, nbp, nb, kb, nbp, n * nbp, 0, nullptr, st));
+        BO_TRY(gemm((int)n + 1, (int)nb, (int)n, (int)M, 1.0, gp->linv_aug, np, (n + 1) * np, kb, nbp, n * nbp, 0.0, nullptr,
+                    0, 0, nei->vb, nbp, (n + 1) * nbp, BO_TRI_A_LOWER, 0, st));
+        BO_TRY(bo_fill(nei->vb_t, M * nb * np, 0.0, st));
+        BO_TRY(bo_transpose(nei->vb, nbp, (n + 1) * nbp, nei->vb_t, np, nb * np, (int)n, (int)nb, (int)M, st));
+        dim3 mgrid((unsigned)((nb + 127) / 128), (unsigned)M);
+        mean_b_kernel<<<mgrid, 128, 0, st>>>(nei->vb, (n + 1) * nbp, nbp, (int)n, (int)nb, gp->y_mean, gp->y_std, gp->mean,
+                                             nei->mean_b);
+        g_bo_launch_count++;
+        // Sigma_bb = ys^2 (K(X_b,X_b) - V_b^T V_b), lower block-triangle, then its Cholesky root and inverse
+        BO_TRY(kmat(gp, rows_b, (int)nb, baug_b, nbp, nb, nei->lb, nbp, nb * nbp, 1, nullptr, st));
+        BO_TRY(gemm((int)nb, (int)nb, (int)n, (int)M, -ys2, nei->vb_t, np, nb * np, nei->vb, nbp, (n + 1) * nbp, ys2, nei->lb,
+                    nbp, nb * nbp, nei->lb, nbp, nb * nbp, BO_TRI_NONE, 1, st));
+        BO_TRY(bo_add_diag(nei->lb, nbp, nb * nbp, (int)nb, (int)M, nei->jitter, st));
+        BO_TRY(bo_potrf_blocked(nei->lb, nbp, nb * nbp, (int)nb, (int)M, nei->lb_inv, nbp, nb * nbp, scratch, info, st));
+        BO_TRY(bo_trtri_blocked(nei->lb, nbp, nb * nbp, (int)nb, (int)M, nei->lb_inv, nbp, nb * nbp, scratch, st));
+        BO_TRY(bo_fill(nei->lb_inv_t, M * nb * nbp, 0.0, st));
+        BO_TRY(bo_transpose(nei->lb_inv, nbp, nb * nbp, nei->lb_inv_t, nbp, nb * nbp, (int)nb, (int)nb, (int)M, st));
+    }
+    if (do_samples) {  // baseline samples f_b[s] = mean_b + L_b z_s and best_f[s] = max_i f_b[s][i]
+        BO_TRY(gemm((int)nb, (int)S, (int)nb, (int)M, 1.0, nei->lb, nbp, nb * nbp, nei->zb_t, Sp, 0, 0.0, nullptr, 0, 0, fb, Sp,
+                    nb * Sp, BO_TRI_A_LOWER, 0, st));
+        BO_TRY(bo_col_max(fb, nb * Sp, Sp, nei->mean_b, nbp, (int)nb, (int)S, (int)M, nei->best_f, Sp,
+                          nei->obj_weight != 0.0 ? nei->obj_weight : 1.0, st));
+    }
     if (nei->baseline_is_train && nei->qmat && nei->qmat_t) {
         // X_baseline == train_X: Sigma(X_b, X) = ys^2 (K - K Khat^-1 K_x) = ys^2 s2 Khat^-1 K_x with Khat = K + s2 I,
         // so bl_chol^T = inv(L_b) Sigma(X_b, X) = Q K(X_tr, X),  Q = ys^2 s2 inv(L_b) Khat^-1  (no cancellation).
-        vec_add_kernel<<<(unsigned)((M + 127) / 128), 128, 0, st>>>(gp->noise, gp->jitter, nz, (int)M);
-        g_bo_launch_count++;
-        const long n1p = bo_pad8(n + 1);
-        BO_TRY(gemm((int)n, (int)n, (int)n, (int)M, 1.0, gp->linv_aug_t, n1p, n * n1p, gp->linv_aug, np, (n + 1) * np, 0.0,
-                    nullptr, 0, 0, khinv, np, n * np, BO_TRI_A_UPPER, 0, st));
-        // Khat - K = D (s2 I, or diag(noise_vec) for fixed per-observation noise): Sigma(X_b, X) = ys^2 D Khat^-1 K_x
-        const double* qrhs = khinv;
-        if (gp->noise_vec) {
-            BO_TRY(bo_scale_rows(khinv, khs, np, n * np, (int)n, (int)n, (int)M, gp->noise_vec, n, gp->jitter, st));
-            qrhs = khs;
+        if (do_factors) {
+            vec_add_kernel<<<(unsigned)((M + 127) / 128), 128, 0, st>>>(gp->noise, gp->jitter, nz, (int)M);
+            g_bo_launch_count++;
+            const long n1p = bo_pad8(n + 1);
+            BO_TRY(gemm((int)n, (int)n, (int)n, (int)M, 1.0, gp->linv_aug_t, n1p, n * n1p, gp->linv_aug, np, (n + 1) * np, 0.0,
+                        nullptr, 0, 0, khinv, np, n * np, BO_TRI_A_UPPER, 0, st));
+            // Khat - K = D (s2 I, or diag(noise_vec) for fixed per-observation noise): Sigma(X_b, X) = ys^2 D Khat^-1 K_x
+            const double* qrhs = khinv;
+            if (gp->noise_vec) {
+                BO_TRY(bo_scale_rows(khinv, khs, np, n * np, (int)n, (int)n, (int)M, gp->noise_vec, n, gp->jitter, st));
+                qrhs = khs;
+            }
+            BoGemm g{};
+            g.A = nei->lb_inv; g.lda = nbp; g.strideA = nb * nbp;
+            g.B = qrhs; g.ldb = np; g.strideB = n * np;
+            g.C = nei->qmat; g.ldc = np; g.strideC = nb * np;
+            g.CT = nei->qmat_t; g.ldct = nbp; g.strideCT = n * nbp;
+            g.alpha = ys2; g.alpha_vec = gp->noise_vec ? nullptr : nz; g.M = (int)nb; g.N = (int)n; g.K = (int)nb; g.batch = (int)M;
+            g.tri = BO_TRI_A_LOWER; g.epi = BO_EPI_LINEAR;
+            BO_TRY(bo_fill(nei->qmat_t, M * n * nbp, 0.0, st));
+            BO_TRY(bo_gemm_launch(g, st));
         }
-        BoGemm g{};
-        g.A = nei->lb_inv; g.lda = nbp; g.strideA = nb * nbp;
-        g.B = qrhs; g.ldb = np; g.strideB = n * np;
-        g.C = nei->qmat; g.ldc = np; g.strideC = nb * np;
-        g.CT = nei->qmat_t; g.ldct = nbp; g.strideCT = n * nbp;
-        g.alpha = ys2; g.alpha_vec = gp->noise_vec ? nullptr : nz; g.M = (int)nb; g.N = (int)n; g.K = (int)nb; g.batch = (int)M;
-        g.tri = BO_TRI_A_LOWER; g.epi = BO_EPI_LINEAR;
-        BO_TRY(bo_fill(nei->qmat_t, M * n * nbp, 0.0, st));
-        BO_TRY(bo_gemm_launch(g, st));
         if (nei->fwd_cat && nei->bwd_cat) {
             // W = ys^2 Khat^-1 + Q^T Q = L_W L_W^T, factored in place inside the backward operand [ . | L_W ]
             const long S1 = S + 1, S1p = bo_pad8(S1), ldk = S1p + np, rowsF = S1p + n;
             double* lw = nei->bwd_cat + S1p;
-            BO_TRY(bo_fill(nei->bwd_cat, M * n * ldk, 0.0, st));
-            BO_TRY(bo_fill(nei->fwd_cat, M * rowsF * np, 0.0, st));
-            BO_TRY(gemm((int)n, (int)n, (int)nb, (int)M, 1.0, nei->qmat_t, nbp, n * nbp, nei->qmat, np, nb * np, ys2, khinv, np,
-                        n * np, lw, ldk, n * ldk, BO_TRI_NONE, 1, st));
-            BO_TRY(cholqr2_root(gp, nei->qmat, nb, lw, ldk, qr, scratch, info, st));
-            BO_TRY(bo_transpose(lw, ldk, n * ldk, nei->fwd_cat + S1p * np, np, rowsF * np, (int)n, (int)n, (int)M, st));
-            // rows 0..S-1: Z_b Q, row S: alpha; then their transpose into the leading columns of the backward operand
-            BO_TRY(gemm((int)S, (int)n, (int)nb, (int)M, 1.0, nei->zb_pad, nbp, 0, nei->qmat, np, nb * np, 0.0, nullptr, 0, 0,
-                        nei->fwd_cat, np, rowsF * np, BO_TRI_NONE, 0, st));
-            BO_TRY(bo_copy2d(gp->linv_aug + n * np, np, (n + 1) * np, nei->fwd_cat + S * np, np, rowsF * np, 1, (int)n, (int)M,
-                             st));
-            BO_TRY(bo_transpose(nei->fwd_cat, np, rowsF * np, nei->bwd_cat, ldk, n * ldk, (int)S1, (int)n, (int)M, st));
+            if (do_factors) {
+                BO_TRY(bo_fill(nei->bwd_cat, M * n * ldk, 0.0, st));
+                BO_TRY(bo_fill(nei->fwd_cat, M * rowsF * np, 0.0, st));
+                BO_TRY(gemm((int)n, (int)n, (int)nb, (int)M, 1.0, nei->qmat_t, nbp, n * nbp, nei->qmat, np, nb * np, ys2, khinv, np,
+                            n * np, lw, ldk, n * ldk, BO_TRI_NONE, 1, st));
+                BO_TRY(cholqr2_root(gp, nei->qmat, nb, lw, ldk, qr, scratch, info, st));
+                BO_TRY(bo_transpose(lw, ldk, n * ldk, nei->fwd_cat + S1p * np, np, rowsF * np, (int)n, (int)n, (int)M, st));
+                // row S: alpha
+                BO_TRY(bo_copy2d(gp->linv_aug + n * np, np, (n + 1) * np, nei->fwd_cat + S * np, np, rowsF * np, 1, (int)n,
+                                 (int)M, st));
+            }
+            if (do_samples) {
+                // rows 0..S-1: Z_b Q; then rows 0..S transposed into the leading columns of the backward operand
+                BO_TRY(gemm((int)S, (int)n, (int)nb, (int)M, 1.0, nei->zb_pad, nbp, 0, nei->qmat, np, nb * np, 0.0, nullptr, 0, 0,
+                            nei->fwd_cat, np, rowsF * np, BO_TRI_NONE, 0, st));
+                BO_TRY(bo_transpose(nei->fwd_cat, np, rowsF * np, nei->bwd_cat, ldk, n * ldk, (int)S1, (int)n, (int)M, st));
+            }
         }
     }
     BO_CUDA_TRY(cudaGetLastError());

@@ -332,13 +332,24 @@ def _local_derivs_default(reduction: int) -> int:
 class NEIState:
     """Baseline factors of qLogNEI (V_b, L_b and its inverse, base samples, best_f) and the fused fwd/bwd."""
 
-    def __init__(self, gp: GPState, X_baseline: Tensor, Z_b: Tensor, setup: bool = True,
-                 reduction: int = REDUCE_LOG, obj_weight: float = 1.0, forced_jitter: Optional[float] = None) -> None:  # fmt: skip
+    def __init__(self, gp: GPState, X_baseline: Tensor, Z_b, setup: bool = True,
+                 reduction: int = REDUCE_LOG, obj_weight: float = 1.0, forced_jitter: Optional[float] = None,
+                 S: Optional[int] = None) -> None:  # fmt: skip
+        """``Z_b``: the S x n_b base samples of the baseline points, or a callable returning them (then ``S`` is required):
+        the factors that do not read them are enqueued first (``bo_nei.setup_phase`` 1) and the callable runs on the host
+        while the device works -- drawing them is a scrambled Sobol engine of dimension n_b, ~10 ms at n_b = 2000, about
+        what the device needs for the factors."""
         dev = gp.device
         self.gp = gp
         self.device = dev
         self.X_b = _f64(X_baseline, dev)
-        self.Z_b = _f64(Z_b, dev)
+        z_producer = Z_b if callable(Z_b) else None
+        if z_producer is not None:
+            if S is None:
+                raise ValueError("S is required when the base samples are produced lazily")
+            self.Z_b = torch.empty(int(S), self.X_b.shape[0], dtype=torch.float64, device=dev)
+        else:
+            self.Z_b = _f64(Z_b, dev)
         self.S, self.n_b = self.Z_b.shape
         if self.X_b.shape != (self.n_b, gp.d):
             raise ValueError(f"X_baseline {tuple(self.X_b.shape)} does not match base samples {tuple(self.Z_b.shape)}")
@@ -384,14 +395,47 @@ class NEIState:
                                    ptr(self.info), _lib.stream_ptr(dev)))  # fmt: skip
             return self.info.clone()
 
+        drawn: dict = {}
+        drawer = None
+        if z_producer is not None:  # the host draws the base samples on a thread while this one enqueues and awaits phase 1
+            import threading
+
+            def draw() -> None:
+                try:
+                    drawn["z"] = z_producer()
+                except BaseException as e:  # re-raised on the constructing thread
+                    drawn["error"] = e
+
+            drawer = threading.Thread(target=draw, daemon=True)
+            drawer.start()
+
+        def finish_samples() -> None:  # phase 2: the Z_b-dependent pieces, once the host has produced the base samples
+            if drawer is None:
+                return
+            drawer.join()
+            if "error" in drawn:
+                raise drawn["error"]
+            z = _f64(drawn["z"], dev)
+            if z.shape != self.Z_b.shape:
+                raise ValueError(f"base samples {tuple(z.shape)} do not match {tuple(self.Z_b.shape)}")
+            self.Z_b.copy_(z)
+            self.c.setup_phase = 2
+            try:
+                run(self._jitter)
+            finally:
+                self.c.setup_phase = 0
+
+        self.c.setup_phase = 0 if z_producer is None else 1
         if forced_jitter is not None:
             # the joint-factorisation fallback (acquisition._FusedImprovementBase._forward_resolved): ONE attempt with this
             # jitter on the baseline block and, in the forward kernel, the same jitter on every q x q block
             self.jitter = torch.full((M,), float(forced_jitter), dtype=torch.float64, device=dev)
             self.setup_failed = bool(run(self.jitter).any())
             self.c.schur_jitter, self.c.schur_fixed = float(forced_jitter), 1
+            finish_samples()
             return
         self.jitter = _retry_with_jitter(run, M, dev, "posterior covariance at X_baseline")
+        finish_samples()
 
     def factor_buffers(self):
         """Device buffers bo_nei_setup fills (broadcast payload)."""

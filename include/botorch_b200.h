@@ -125,6 +125,12 @@ typedef struct bo_nei {
      * Must be 0 when the caller reads the samples (bo_qlognei_samples_view: outcome constraints, generic objectives) and
      * must not change between a forward and its backward. */
     int32_t local_derivs;
+    /* bo_nei_setup only.  0: everything.  1: every factor that does not read the base samples Z_b (cross covariance, the
+     * baseline posterior covariance, its root and inverse, the combined root) -- the expensive part.  2: only what reads
+     * Z_b (zb_pad / zb_t, the baseline samples and best_f, the Z_b Q rows of fwd_cat / columns of bwd_cat), on buffers that
+     * a phase-1 call filled.  The host draws Z_b (a scrambled Sobol engine of dimension n_b: ~10 ms at n_b = 2000) while
+     * the device runs phase 1.  1 then 2 leaves exactly what 0 leaves. */
+    int32_t setup_phase;
 } bo_nei;
 
 typedef struct bo_ctx bo_ctx;

@@ -213,3 +213,35 @@ def test_local_derivative_mode_equals_the_recomputing_reverse_pass(cuda, cfg, B,
     assert float((g1 - g0).abs().max()) <= 1e-12 * float(g0.abs().max())
     with pytest.raises(Exception):
         fast.samples_view(work, B, p.q)  # the sample rows do not hold samples in this mode
+
+
+@pytest.mark.parametrize("cfg,general", [("C2", False), ("C2", True), ("C4", False)])
+def test_two_phase_baseline_setup_leaves_the_same_bits(cuda, cfg, general):
+    """bo_nei.setup_phase: the factors that do not read the base samples (phase 1) are enqueued while the host still draws
+    them; phase 2 adds what reads them.  Every buffer must equal the single-call setup bit for bit -- shared baseline
+    (combined root), general baseline (X_baseline != train_X), ensemble."""
+    from botorch_b200 import engine
+    from botorch_b200.synthetic import make_problem
+    from tests.util import gp_state, oracle_acq, oracle_gp
+
+    p = make_problem(cfg, n=60) if cfg == "C4" else make_problem(cfg)
+    ogp = oracle_gp(p)
+    oacq = oracle_acq(p, ogp)
+    st = gp_state(p, ogp, cuda)
+    Xb, Zb = p.train_X.to(cuda), oacq.Z_b.to(cuda)
+    if general:
+        Xb, Zb = Xb[:37].contiguous(), Zb[:, :37].contiguous()
+    one = engine.NEIState(st, Xb, Zb)
+    calls = []
+
+    def produce():
+        calls.append(1)
+        return Zb.cpu()
+
+    two = engine.NEIState(st, Xb, produce, S=Zb.shape[0])
+    assert calls == [1] and two.c.setup_phase == 0
+    for a, b in zip(one.factor_buffers(), two.factor_buffers()):
+        assert torch.equal(a, b)
+    assert torch.equal(one.Z_b, two.Z_b)
+    with pytest.raises(ValueError):
+        engine.NEIState(st, Xb, produce)  # S is required with a producer
