@@ -384,6 +384,8 @@ class NEIState:
         )  # fmt: skip
         self.jitter = torch.zeros(M, dtype=torch.float64, device=dev)
         if not setup:
+            if z_producer is not None:  # allocate-only state (factors arrive by broadcast): just take the base samples
+                self.Z_b.copy_(_f64(z_producer(), dev))
             return
         lib = _lib.lib()
         work = _lib.workspace(lib.bo_nei_setup_workspace_bytes(C.byref(gp.c), C.byref(self.c)), dev)
