@@ -51,6 +51,14 @@ def _worker(rank: int, ws: int, port: int, outdir: str) -> None:
         # sharded optimize_acqf: both ranks return the same winner, close to the optimum
         cand, val = bdist.optimize_acqf_sharded(acq, bounds, q=2, num_restarts=6, raw_samples=32,
                                                 options={"seed": 0, "maxiter": 100})  # fmt: skip
+        # each rank draws only ITS rows of the raw samples (the engine fast-forwarded to its block) and the selected rows are
+        # fetched by an all-gather: with an "optimiser" that returns its starting points, the winner must be exactly the
+        # best of the initial conditions a single process selects from the full draw (uneven blocks: 37 = 19 + 18)
+        def identity(ics, acqf, lower_bounds=None, upper_bounds=None, options=None):
+            return ics, acqf(ics)
+
+        cand_i, val_i = bdist.optimize_acqf_sharded(acq, bounds, q=2, num_restarts=5, raw_samples=37, options={"seed": 3},
+                                                    gen_candidates=identity)  # fmt: skip
         # no seed given: rank 0 draws it and broadcasts it, although the ranks' global RNGs differ (every rank used
         # to scramble its own Sobol sequence, so the gathered values belonged to other ranks' points)
         torch.manual_seed(100 + rank)
@@ -76,7 +84,8 @@ def _worker(rank: int, ws: int, port: int, outdir: str) -> None:
         draws, _ = bdist.nuts_sample_sharded(make_potential, 2, 3, num_samples=40, warmup_steps=60, device=torch.device("cpu"),
                                              seed=5)  # fmt: skip
         assert draws.shape == (40, 6, 2)
-        torch.save({"cand": cand, "val": val, "draws": draws, "cand_u": cand_u, "val_u": val_u, "seeds": seeds}, os.path.join(outdir, f"r{rank}.pt"))
+        torch.save({"cand": cand, "val": val, "draws": draws, "cand_u": cand_u, "val_u": val_u, "seeds": seeds,
+                    "cand_i": cand_i, "val_i": val_i}, os.path.join(outdir, f"r{rank}.pt"))
     finally:
         dist.destroy_process_group()
 
@@ -91,6 +100,20 @@ def test_world_size_2_gloo():
     assert a["seeds"] == b["seeds"] and a["seeds"][0] != a["seeds"][1]
     assert torch.equal(a["cand_u"], b["cand_u"]) and torch.equal(a["val_u"], b["val_u"])
     assert torch.allclose(a["cand_u"], torch.tensor([0.25, 0.6, 0.9], dtype=torch.float64).expand(2, 3), atol=1e-4)
+    # row-sharded raw samples: the single-process selection from the full draw, same seed, same host RNG protocol
+    from botorch_b200.optim import initialize_q_batch_indices
+    from botorch_b200.sampling import draw_sobol_samples
+
+    bounds = torch.stack([torch.zeros(3), torch.ones(3)]).double()
+    X_full = draw_sobol_samples(bounds, n=37, q=2, seed=3)
+    Y_full = _Quad()(X_full)
+    state = torch.random.get_rng_state()
+    torch.manual_seed(3)
+    ics = X_full[initialize_q_batch_indices(Y_full, 5)]
+    torch.random.set_rng_state(state)
+    best = int(torch.argmax(_Quad()(ics)))
+    assert torch.equal(a["cand_i"], ics[best]) and torch.equal(b["cand_i"], ics[best])
+    assert float(a["val_i"]) == float(_Quad()(ics)[best])
     assert torch.equal(a["draws"], b["draws"])  # every rank holds the same gathered chains ...
     chains = a["draws"].transpose(0, 1)
     assert all(not torch.equal(chains[i], chains[j]) for i in range(6) for j in range(i))  # ... and the chains are distinct
