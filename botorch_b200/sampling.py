@@ -63,6 +63,23 @@ def _pool():
     return _sobol_pool
 
 
+_state_cache: dict = {}
+
+
+def _initial_state(dimension: int) -> Tensor:
+    """The unscrambled direction-number table of ``SobolEngine(dimension)`` (a pure function of the dimension, read-only
+    here: the workers copy the rows they scramble).  One acquisition builds three engines and a BO loop reuses the same
+    few dimensions, so the last few tables are kept."""
+    state = _state_cache.get(dimension)
+    if state is None:
+        state = torch.zeros(dimension, SobolEngine.MAXBIT, device=torch.device("cpu"), dtype=torch.long)
+        torch._sobol_engine_initialize_state_(state, dimension)
+        if len(_state_cache) >= 8:
+            _state_cache.pop(next(iter(_state_cache)))
+        _state_cache[dimension] = state
+    return state
+
+
 def sobol_draw(dimension: int, n: int, seed: Optional[int] = None, dtype: Optional[torch.dtype] = None,
                columns: Optional[Tensor] = None, first: int = 0, post=None) -> Tensor:  # fmt: skip
     """Points ``first .. first + n - 1`` of ``SobolEngine(dimension, scramble=True, seed=seed)`` -- bit for bit -- or only
@@ -88,8 +105,7 @@ def sobol_draw(dimension: int, n: int, seed: Optional[int] = None, dtype: Option
     dtype = torch.get_default_dtype() if dtype is None else dtype
     bits = SobolEngine.MAXBIT
     cpu = torch.device("cpu")
-    state = torch.zeros(dimension, bits, device=cpu, dtype=torch.long)
-    torch._sobol_engine_initialize_state_(state, dimension)
+    state = _initial_state(dimension)
     g = None
     if seed is not None:
         g = torch.Generator()
@@ -108,7 +124,7 @@ def sobol_draw(dimension: int, n: int, seed: Optional[int] = None, dtype: Option
 
     def work(a: int, b: int) -> None:
         sel = slice(a, b) if columns is None else columns[a:b]
-        st = state[sel].contiguous()
+        st = state[sel].clone(memory_format=torch.contiguous_format)  # the table is shared (cached): scramble a copy
         lower = ltm[sel].tril().contiguous()
         torch._sobol_engine_scramble_(st, lower, b - a)
         quasi = torch.mv(shift_bits[sel], pow2).clone(memory_format=torch.contiguous_format)
